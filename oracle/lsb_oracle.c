@@ -1,0 +1,570 @@
+/*
+ * lsb_oracle.c -- CPU ORACLE for the lidarshooter trace path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg may
+ * load this library.  The product (lidarshooter_b200/, liblsb200.so) never links, imports or
+ * calls anything in oracle/.
+ *
+ * What it is: a plain-C restatement of the arithmetic of the reference's Embree CPU path
+ * (/root/reference, SRC = ros_ws/src/lidarshooter/src):
+ *
+ *   lso_quat_to_rotation / lso_inverse3      SRC/LidarDevice.cpp:808-813 (Eigen Quaternionf::toRotationMatrix,
+ *                                            Matrix3f::inverse; quaternion is NOT normalised)
+ *   lso_affine_from_components               SRC/MeshTransformer.cpp:467-477  (T * Rz * Ry * Rx)
+ *   lso_transform_vertices                   SRC/MeshTransformer.cpp:173-194 + SRC/LidarDevice.cpp:383-391
+ *   lso_ray_tables / lso_ray_dirs            SRC/LidarDevice.cpp:294-342, 598-617, 824-845 (ray id = channel*H + az)
+ *   lso_intersect (Moeller-Trumbore)         Embree v3.13.4 kernels/geometry/triangle_intersector_moeller.h
+ *                                            (third-party, NOT in /root/reference; pinned by
+ *                                            .devcontainer/Dockerfile:24-27; call site SRC/EmbreeTracer.cpp:472-480)
+ *   lso_trace_brute / lso_trace_bvh          SRC/EmbreeTracer.cpp:297-367 (closest hit per ray, tnear 0, tfar inf)
+ *   lso_pack_points                          SRC/XYZIRBytes.cpp:24-40, SRC/EmbreeTracer.cpp:331-335
+ *
+ * PARITY STATUS: the reference's own tests pin only point COUNTS at this boundary (1668 / 1781 / 0,
+ * SRC/test/EmbreeTracer_test.cpp:134, SRC/test/OptixTracer_test.cpp:168,307); tests/test_oracle.py checks
+ * those.  Per-ray hit mask / triangle id / range are "parity unpinned" against Embree itself: Embree is a
+ * closed binary dependency that is absent here, its t = T*rcp(|den|) uses the hardware reciprocal estimate and
+ * its dot/cross use FMA on AVX2+ hosts, so no CPU restatement can be bit-identical to it.  Deviations chosen
+ * here, all deterministic: non-fused IEEE fp32 everywhere (compile with -ffp-contract=off), t = T/|den| with a
+ * true division, closest hit = lexicographic minimum of (t, global triangle id).
+ *
+ * Everything is IEEE-754 binary32 with round-to-nearest and no contraction, so the CUDA kernels (which
+ * use __fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn in the same order) can match bit for bit.
+ */
+#define _GNU_SOURCE 1
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <float.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#if defined(__GNUC__)
+#define LSO_API __attribute__((visibility("default")))
+#else
+#define LSO_API
+#endif
+
+/* ------------------------------------------------------------------------------------------------
+ * small fixed-size linear algebra, Eigen 3.4 evaluation order (best effort; Eigen is absent here).
+ * Eigen's unrolled 3-term reduction is a0 + (a1 + a2) (redux_novec_unroller halves the range).
+ * ---------------------------------------------------------------------------------------------- */
+static inline float dot3_eigen(float a0, float b0, float a1, float b1, float a2, float b2)
+{
+    float p0 = a0 * b0, p1 = a1 * b1, p2 = a2 * b2;
+    float s12 = p1 + p2;
+    return p0 + s12;
+}
+
+/* Row-major 3x3 times vector, Eigen coefficient order. */
+static inline void mat3_mul_vec(const float *M, const float *p, float *o)
+{
+    float x = dot3_eigen(M[0], p[0], M[1], p[1], M[2], p[2]);
+    float y = dot3_eigen(M[3], p[0], M[4], p[1], M[5], p[2]);
+    float z = dot3_eigen(M[6], p[0], M[7], p[1], M[8], p[2]);
+    o[0] = x; o[1] = y; o[2] = z;
+}
+
+static void mat3_mul_mat3(const float *A, const float *B, float *C)
+{
+    float T[9];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            T[3 * i + j] = dot3_eigen(A[3 * i + 0], B[0 + j], A[3 * i + 1], B[3 + j], A[3 * i + 2], B[6 + j]);
+    memcpy(C, T, sizeof(T));
+}
+
+/* Eigen::Quaternionf::toRotationMatrix(), q = (w,x,y,z), no normalisation (SRC/LidarDevice.cpp:812). */
+LSO_API void lso_quat_to_rotation(const float q[4], float R[9])
+{
+    const float w = q[0], x = q[1], y = q[2], z = q[3];
+    const float tx = 2.0f * x, ty = 2.0f * y, tz = 2.0f * z;
+    const float twx = tx * w, twy = ty * w, twz = tz * w;
+    const float txx = tx * x, txy = ty * x, txz = tz * x;
+    const float tyy = ty * y, tyz = tz * y, tzz = tz * z;
+    R[0] = 1.0f - (tyy + tzz); R[1] = txy - twz;          R[2] = txz + twy;
+    R[3] = txy + twz;          R[4] = 1.0f - (txx + tzz); R[5] = tyz - twx;
+    R[6] = txz - twy;          R[7] = tyz + twx;          R[8] = 1.0f - (txx + tyy);
+}
+
+/* Eigen::Matrix3f::inverse() (SRC/LidarDevice.cpp:813), restated from Eigen 3.4 LU/InverseImpl.h
+ * compute_inverse_size3_helper: cofactor(i,j) = m(i1,j1)*m(i2,j2) - m(i1,j2)*m(i2,j1) with i1=(i+1)%3 ...,
+ * det = sum_i cofactor(i,0)*m(i,0), inverse(j,i) = cofactor(i,j) / det (as a multiply by 1/det). */
+static inline float cof3(const float *M, int i, int j)
+{
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    return M[3 * i1 + j1] * M[3 * i2 + j2] - M[3 * i1 + j2] * M[3 * i2 + j1];
+}
+LSO_API void lso_inverse3(const float M[9], float Minv[9])
+{
+    const float c0 = cof3(M, 0, 0), c1 = cof3(M, 1, 0), c2 = cof3(M, 2, 0);
+    const float det = dot3_eigen(c0, M[0], c1, M[3], c2, M[6]);
+    const float invdet = 1.0f / det;
+    Minv[0] = c0 * invdet; Minv[1] = c1 * invdet; Minv[2] = c2 * invdet;
+    for (int j = 1; j < 3; ++j)
+        for (int i = 0; i < 3; ++i)
+            Minv[3 * j + i] = cof3(M, i, j) * invdet;
+}
+
+/* Eigen::AngleAxisf(angle, UnitX/Y/Z).toRotationMatrix() products: A = Translation(t)*Rz*Ry*Rx
+ * (SRC/MeshTransformer.cpp:467-477).  A is row-major 3x4: [L | t]. */
+LSO_API void lso_affine_from_components(const float t[3], const float r[3], float A[12])
+{
+    const float cx = cosf(r[0]), sx = sinf(r[0]);
+    const float cy = cosf(r[1]), sy = sinf(r[1]);
+    const float cz = cosf(r[2]), sz = sinf(r[2]);
+    const float Rx[9] = {1, 0, 0, 0, cx, -sx, 0, sx, cx};
+    const float Ry[9] = {cy, 0, sy, 0, 1, 0, -sy, 0, cy};
+    const float Rz[9] = {cz, -sz, 0, sz, cz, 0, 0, 0, 1};
+    float Rzy[9], L[9];
+    mat3_mul_mat3(Rz, Ry, Rzy);
+    mat3_mul_mat3(Rzy, Rx, L);
+    for (int i = 0; i < 3; ++i) {
+        A[4 * i + 0] = L[3 * i + 0];
+        A[4 * i + 1] = L[3 * i + 1];
+        A[4 * i + 2] = L[3 * i + 2];
+        A[4 * i + 3] = t[i];
+    }
+}
+
+/* Per-vertex: p1 = t + L*p  (Eigen Transform*vector: res = translation; res += linear*p), then
+ * originToSensor: p2 = Rinv * (p1 - T) (SRC/LidarDevice.cpp:383-391).
+ * mode 0 = sensor frame (reference arithmetic), mode 1 = world frame (stop after p1).
+ * verts: byte blob, xyz float32 at offset 0 of each `stride`-byte record (pcl::PCLPointCloud2 layout). */
+LSO_API void lso_transform_vertices(const uint8_t *verts, int64_t n, int stride, const float A[12],
+                                    const float Rinv[9], const float T[3], int mode, float *out_xyz)
+{
+    const float L[9] = {A[0], A[1], A[2], A[4], A[5], A[6], A[8], A[9], A[10]};
+#pragma omp parallel for schedule(static) if (n > 65536)
+    for (int64_t j = 0; j < n; ++j) {
+        float p[3], q[3];
+        memcpy(p, verts + (size_t)j * (size_t)stride, 12);
+        mat3_mul_vec(L, p, q);
+        q[0] = A[3] + q[0]; q[1] = A[7] + q[1]; q[2] = A[11] + q[2];
+        if (mode == 0) {
+            float d[3] = {q[0] - T[0], q[1] - T[1], q[2] - T[2]};
+            mat3_mul_vec(Rinv, d, q);
+        }
+        out_xyz[3 * j + 0] = q[0]; out_xyz[3 * j + 1] = q[1]; out_xyz[3 * j + 2] = q[2];
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Ray generation (SRC/LidarDevice.cpp:294-342).  theta/phi are computed in double from the float
+ * angle and narrowed to float BEFORE the float sin/cos, exactly like the reference.
+ * ---------------------------------------------------------------------------------------------- */
+LSO_API float lso_azimuth_step(float begin, float end, unsigned count)
+{
+    /* SRC/LidarDevice.cpp:611: float / float(unsigned) */
+    return (end - begin) / (float)(count - 1u);
+}
+
+LSO_API void lso_ray_tables(const float *elev_deg, int V, float az_begin, float az_step, int H,
+                            float *sin_t, float *cos_t, float *sin_p, float *cos_p)
+{
+    for (int v = 0; v < V; ++v) {
+        float theta = (float)((90.0 - (double)elev_deg[v]) * M_PI / 180.0);
+        sin_t[v] = sinf(theta);
+        cos_t[v] = cosf(theta);
+    }
+    for (int h = 0; h < H; ++h) {
+        float prePhi = az_begin + az_step * (float)h;
+        float phi = (float)((double)prePhi * M_PI / 180.0);
+        sin_p[h] = sinf(phi);
+        cos_p[h] = cosf(phi);
+    }
+}
+
+LSO_API void lso_ray_dirs(const float *sin_t, const float *cos_t, int V, const float *sin_p, const float *cos_p,
+                          int H, float *dirs)
+{
+    for (int v = 0; v < V; ++v)
+        for (int h = 0; h < H; ++h) {
+            float *d = dirs + 3 * ((size_t)v * H + h);
+            d[0] = sin_t[v] * cos_p[h];
+            d[1] = sin_t[v] * sin_p[h];
+            d[2] = cos_t[v];
+        }
+}
+
+/* World-frame mode: d_w = R * d_s, row dot products evaluated left to right. */
+LSO_API void lso_rotate_dirs(const float R[9], const float *dirs_s, int64_t n, float *dirs_w)
+{
+#pragma omp parallel for schedule(static) if (n > 65536)
+    for (int64_t i = 0; i < n; ++i) {
+        const float *d = dirs_s + 3 * i;
+        float x = (R[0] * d[0] + R[1] * d[1]) + R[2] * d[2];
+        float y = (R[3] * d[0] + R[4] * d[1]) + R[5] * d[2];
+        float z = (R[6] * d[0] + R[7] * d[1]) + R[8] * d[2];
+        dirs_w[3 * i + 0] = x; dirs_w[3 * i + 1] = y; dirs_w[3 * i + 2] = z;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Embree-ordered Moeller-Trumbore (triangle stored as v0, e1 = v0-v1, e2 = v2-v0, Ng = cross(e2,e1)).
+ * Returns 1 and *t_out when the ray (org, dir, tnear = 0, tfar = +inf) hits.  No back-face culling.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct { float v0[3], e1[3], e2[3]; } lso_tri;
+
+static inline void cross3(const float *a, const float *b, float *o)
+{
+    o[0] = a[1] * b[2] - a[2] * b[1];
+    o[1] = a[2] * b[0] - a[0] * b[2];
+    o[2] = a[0] * b[1] - a[1] * b[0];
+}
+static inline float dot3(const float *a, const float *b)
+{
+    return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2];
+}
+
+static inline void tri_setup(const float *a, const float *b, const float *c, lso_tri *t)
+{
+    for (int k = 0; k < 3; ++k) {
+        t->v0[k] = a[k];
+        t->e1[k] = a[k] - b[k];
+        t->e2[k] = c[k] - a[k];
+    }
+}
+
+static inline int lso_intersect(const lso_tri *tri, const float *org, const float *dir, float *t_out)
+{
+    float Ng[3], C[3], R[3];
+    cross3(tri->e2, tri->e1, Ng);
+    C[0] = tri->v0[0] - org[0]; C[1] = tri->v0[1] - org[1]; C[2] = tri->v0[2] - org[2];
+    cross3(C, dir, R);
+    const float den = dot3(Ng, dir);
+    const float absDen = fabsf(den);
+    const int neg = signbit(den) != 0;
+    float U = dot3(R, tri->e2); if (neg) U = -U;
+    float V = dot3(R, tri->e1); if (neg) V = -V;
+    if (!(den != 0.0f)) return 0;
+    if (!(U >= 0.0f)) return 0;
+    if (!(V >= 0.0f)) return 0;
+    if (!(U + V <= absDen)) return 0;
+    float T = dot3(Ng, C); if (neg) T = -T;
+    if (!(absDen * 0.0f < T)) return 0;      /* tnear = 0, strict */
+    const float t = T / absDen;
+    if (!(t <= FLT_MAX)) return 0;           /* tfar = +inf; rejects inf/NaN */
+    *t_out = t;
+    return 1;
+}
+
+/* Single-triangle entry for unit tests. */
+LSO_API int lso_intersect_one(const float a[3], const float b[3], const float c[3], const float org[3],
+                              const float dir[3], float *t_out)
+{
+    lso_tri tri; tri_setup(a, b, c, &tri);
+    return lso_intersect(&tri, org, dir, t_out);
+}
+
+/* Brute force O(R*T) closest hit; misses -> t = +inf, tri = -1.  dirs: nR x 3.  orgs: per-ray origins
+ * when org_stride == 3, a single shared origin when org_stride == 0. */
+LSO_API void lso_trace_brute(const float *verts, const uint32_t *tris, int64_t nT, const float *orgs, int org_stride,
+                             const float *dirs, int64_t nR, float *t_out, int32_t *tri_out)
+{
+    lso_tri *T = (lso_tri *)malloc(sizeof(lso_tri) * (size_t)(nT > 0 ? nT : 1));
+    for (int64_t i = 0; i < nT; ++i)
+        tri_setup(verts + 3 * (size_t)tris[3 * i], verts + 3 * (size_t)tris[3 * i + 1],
+                  verts + 3 * (size_t)tris[3 * i + 2], &T[i]);
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t r = 0; r < nR; ++r) {
+        const float *o = orgs + (size_t)org_stride * r;
+        const float *d = dirs + 3 * r;
+        float best = INFINITY; int32_t bi = -1;
+        for (int64_t i = 0; i < nT; ++i) {
+            float t;
+            if (lso_intersect(&T[i], o, d, &t) && t < best) { best = t; bi = (int32_t)i; }
+            /* ascending i with strict '<' == lexicographic min of (t, i) */
+        }
+        t_out[r] = best; tri_out[r] = bi;
+    }
+    free(T);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * CPU BVH (binned SAH, binary, <= 4 triangles per leaf): the stand-in for rtcCommitScene +
+ * rtcIntersect (SRC/EmbreeTracer.cpp:290-295, 472-480) at sizes brute force cannot reach, and the CPU
+ * baseline that bench.py times.  Boxes are padded so traversal can never reject a triangle that
+ * lso_intersect would accept; results are identical to lso_trace_brute (tests/test_oracle.py).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    float lo[3]; int32_t left;    /* internal: index of left child (right = left+1); leaf: first triangle slot */
+    float hi[3]; int32_t count;   /* 0 = internal, >0 = leaf triangle count */
+} lso_node;
+
+typedef struct lso_bvh {
+    lso_node *nodes; int64_t n_nodes;
+    lso_tri *tris;           /* in leaf order */
+    int32_t *tri_ids;        /* leaf order -> global triangle id */
+    int64_t n_tris;
+    int64_t node_cap;
+} lso_bvh;
+
+typedef struct { float lo[3], hi[3], c[3]; } prim_box;
+
+#define LSO_BINS 16
+#define LSO_LEAF 4
+
+static inline float fminf3(float a, float b) { return a < b ? a : b; }
+static inline float fmaxf3(float a, float b) { return a > b ? a : b; }
+
+static inline float half_area(const float *lo, const float *hi)
+{
+    float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+typedef struct {
+    lso_bvh *bvh;
+    prim_box *pb;
+    int32_t *idx;
+    int64_t next_node;   /* atomic */
+} build_ctx;
+
+static int64_t alloc_nodes(build_ctx *bc, int n)
+{
+    int64_t r;
+#pragma omp atomic capture
+    { r = bc->next_node; bc->next_node += n; }
+    return r;
+}
+
+static void build_rec(build_ctx *bc, int64_t node_i, int64_t first, int64_t count, int depth)
+{
+    lso_node *node = &bc->bvh->nodes[node_i];
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int64_t i = first; i < first + count; ++i) {
+        const prim_box *p = &bc->pb[bc->idx[i]];
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = fminf3(lo[k], p->lo[k]); hi[k] = fmaxf3(hi[k], p->hi[k]);
+            clo[k] = fminf3(clo[k], p->c[k]); chi[k] = fmaxf3(chi[k], p->c[k]);
+        }
+    }
+    for (int k = 0; k < 3; ++k) { node->lo[k] = lo[k]; node->hi[k] = hi[k]; }
+    if (count <= LSO_LEAF) { node->left = (int32_t)first; node->count = (int32_t)count; return; }
+
+    /* binned SAH over the widest-centroid axis first, all three axes evaluated */
+    int best_axis = -1, best_bin = -1; float best_cost = INFINITY;
+    for (int ax = 0; ax < 3; ++ax) {
+        float ext = chi[ax] - clo[ax];
+        if (!(ext > 0.0f)) continue;
+        float scale = (float)LSO_BINS / ext;
+        int cnt[LSO_BINS]; float blo[LSO_BINS][3], bhi[LSO_BINS][3];
+        for (int b = 0; b < LSO_BINS; ++b) {
+            cnt[b] = 0;
+            for (int k = 0; k < 3; ++k) { blo[b][k] = INFINITY; bhi[b][k] = -INFINITY; }
+        }
+        for (int64_t i = first; i < first + count; ++i) {
+            const prim_box *p = &bc->pb[bc->idx[i]];
+            int b = (int)((p->c[ax] - clo[ax]) * scale);
+            if (b >= LSO_BINS) b = LSO_BINS - 1;
+            if (b < 0) b = 0;
+            cnt[b]++;
+            for (int k = 0; k < 3; ++k) { blo[b][k] = fminf3(blo[b][k], p->lo[k]); bhi[b][k] = fmaxf3(bhi[b][k], p->hi[k]); }
+        }
+        float rarea[LSO_BINS]; int rcnt[LSO_BINS];
+        float alo[3] = {INFINITY, INFINITY, INFINITY}, ahi[3] = {-INFINITY, -INFINITY, -INFINITY}; int ac = 0;
+        for (int b = LSO_BINS - 1; b > 0; --b) {
+            for (int k = 0; k < 3; ++k) { alo[k] = fminf3(alo[k], blo[b][k]); ahi[k] = fmaxf3(ahi[k], bhi[b][k]); }
+            ac += cnt[b]; rcnt[b] = ac; rarea[b] = ac ? half_area(alo, ahi) : 0.0f;
+        }
+        for (int k = 0; k < 3; ++k) { alo[k] = INFINITY; ahi[k] = -INFINITY; }
+        ac = 0;
+        for (int b = 0; b < LSO_BINS - 1; ++b) {
+            for (int k = 0; k < 3; ++k) { alo[k] = fminf3(alo[k], blo[b][k]); ahi[k] = fmaxf3(ahi[k], bhi[b][k]); }
+            ac += cnt[b];
+            if (ac == 0 || rcnt[b + 1] == 0) continue;
+            float cost = half_area(alo, ahi) * (float)ac + rarea[b + 1] * (float)rcnt[b + 1];
+            if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = b; }
+        }
+    }
+    int64_t mid;
+    if (best_axis < 0) {
+        mid = first + count / 2;   /* all centroids coincide: median split in index order */
+    } else {
+        float ext = chi[best_axis] - clo[best_axis];
+        float scale = (float)LSO_BINS / ext;
+        int64_t i = first, j = first + count - 1;
+        while (i <= j) {
+            const prim_box *p = &bc->pb[bc->idx[i]];
+            int b = (int)((p->c[best_axis] - clo[best_axis]) * scale);
+            if (b >= LSO_BINS) b = LSO_BINS - 1;
+            if (b < 0) b = 0;
+            if (b <= best_bin) ++i;
+            else { int32_t tmp = bc->idx[i]; bc->idx[i] = bc->idx[j]; bc->idx[j] = tmp; --j; }
+        }
+        mid = i;
+        if (mid == first || mid == first + count) mid = first + count / 2;
+    }
+    int64_t l = alloc_nodes(bc, 2);
+    node->left = (int32_t)l; node->count = 0;
+    int64_t lc = mid - first, rc = count - lc;
+    if (count > 8192 && depth < 24) {
+#pragma omp task default(shared) firstprivate(l, first, lc, depth)
+        build_rec(bc, l, first, lc, depth + 1);
+#pragma omp task default(shared) firstprivate(l, mid, rc, depth)
+        build_rec(bc, l + 1, mid, rc, depth + 1);
+#pragma omp taskwait
+    } else {
+        build_rec(bc, l, first, lc, depth + 1);
+        build_rec(bc, l + 1, mid, rc, depth + 1);
+    }
+}
+
+LSO_API lso_bvh *lso_bvh_build(const float *verts, const uint32_t *tris, int64_t nT)
+{
+    lso_bvh *bvh = (lso_bvh *)calloc(1, sizeof(lso_bvh));
+    bvh->n_tris = nT;
+    if (nT <= 0) return bvh;
+    prim_box *pb = (prim_box *)malloc(sizeof(prim_box) * (size_t)nT);
+    int32_t *idx = (int32_t *)malloc(sizeof(int32_t) * (size_t)nT);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < nT; ++i) {
+        const float *a = verts + 3 * (size_t)tris[3 * i], *b = verts + 3 * (size_t)tris[3 * i + 1],
+                    *c = verts + 3 * (size_t)tris[3 * i + 2];
+        prim_box *p = &pb[i];
+        for (int k = 0; k < 3; ++k) {
+            float lo = fminf3(a[k], fminf3(b[k], c[k])), hi = fmaxf3(a[k], fmaxf3(b[k], c[k]));
+            /* pad: Moeller-Trumbore in fp32 may accept rays passing a few ulp outside the exact box */
+            float m = fmaxf3(fabsf(lo), fabsf(hi));
+            float pad = m * 4e-6f + 1e-30f;
+            p->lo[k] = lo - pad; p->hi[k] = hi + pad;
+            p->c[k] = 0.5f * (lo + hi);
+        }
+        idx[i] = (int32_t)i;
+    }
+    bvh->node_cap = 2 * nT + 2;
+    bvh->nodes = (lso_node *)malloc(sizeof(lso_node) * (size_t)bvh->node_cap);
+    build_ctx bc = {bvh, pb, idx, 1};
+#pragma omp parallel
+#pragma omp single nowait
+    build_rec(&bc, 0, 0, nT, 0);
+    bvh->n_nodes = bc.next_node;
+    bvh->tris = (lso_tri *)malloc(sizeof(lso_tri) * (size_t)nT);
+    bvh->tri_ids = idx;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < nT; ++i) {
+        int32_t g = idx[i];
+        tri_setup(verts + 3 * (size_t)tris[3 * g], verts + 3 * (size_t)tris[3 * g + 1],
+                  verts + 3 * (size_t)tris[3 * g + 2], &bvh->tris[i]);
+    }
+    free(pb);
+    return bvh;
+}
+
+LSO_API void lso_bvh_free(lso_bvh *bvh)
+{
+    if (!bvh) return;
+    free(bvh->nodes); free(bvh->tris); free(bvh->tri_ids); free(bvh);
+}
+
+LSO_API int64_t lso_bvh_node_count(const lso_bvh *bvh) { return bvh ? bvh->n_nodes : 0; }
+
+static inline int slab(const lso_node *n, const float *o, const float *inv, float tbest, float *tnear_out)
+{
+    float t0 = 0.0f, t1 = tbest;
+    for (int k = 0; k < 3; ++k) {
+        float a = (n->lo[k] - o[k]) * inv[k];
+        float b = (n->hi[k] - o[k]) * inv[k];
+        float mn = a < b ? a : b, mx = a < b ? b : a;   /* NaN (0*inf) falls through to 'b'/'a' harmlessly below */
+        if (mn != mn) mn = -INFINITY;
+        if (mx != mx) mx = INFINITY;
+        if (mn > t0) t0 = mn;
+        if (mx < t1) t1 = mx;
+    }
+    *tnear_out = t0;
+    return t0 <= t1 * 1.0000005f;
+}
+
+static void trace_one(const lso_bvh *bvh, const float *o, const float *d, float *t_out, int32_t *tri_out)
+{
+    float best = INFINITY; int32_t bi = -1;
+    if (bvh->n_tris > 0) {
+        float inv[3] = {1.0f / d[0], 1.0f / d[1], 1.0f / d[2]};
+        int32_t stack[128]; int sp = 0;
+        stack[sp++] = 0;
+        while (sp) {
+            const lso_node *n = &bvh->nodes[stack[--sp]];
+            float tn;
+            if (!slab(n, o, inv, best, &tn)) continue;
+            for (;;) {
+                if (n->count) {
+                    for (int32_t i = n->left; i < n->left + n->count; ++i) {
+                        float t;
+                        if (lso_intersect(&bvh->tris[i], o, d, &t)) {
+                            int32_t g = bvh->tri_ids[i];
+                            if (t < best || (t == best && g < bi)) { best = t; bi = g; }
+                        }
+                    }
+                    break;
+                }
+                const lso_node *l = &bvh->nodes[n->left], *r = l + 1;
+                float tl, tr;
+                int hl = slab(l, o, inv, best, &tl), hr = slab(r, o, inv, best, &tr);
+                if (hl && hr) {
+                    if (tr < tl) { const lso_node *tmp = l; l = r; r = tmp; }
+                    if (sp < 127) stack[sp++] = (int32_t)(r - bvh->nodes);
+                    n = l;
+                } else if (hl) n = l;
+                else if (hr) n = r;
+                else break;
+            }
+        }
+    }
+    *t_out = best; *tri_out = bi;
+}
+
+LSO_API void lso_trace_bvh(const lso_bvh *bvh, const float *orgs, int org_stride, const float *dirs, int64_t nR,
+                           float *t_out, int32_t *tri_out)
+{
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t r = 0; r < nR; ++r)
+        trace_one(bvh, orgs + (size_t)org_stride * r, dirs + 3 * r, &t_out[r], &tri_out[r]);
+}
+
+/* Reference-faithful threading (SRC/EmbreeTracer.cpp:304-313): fixed thread count. */
+LSO_API void lso_set_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+LSO_API int lso_max_threads(void)
+{
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Point packing (SRC/XYZIRBytes.cpp:24-40; SRC/EmbreeTracer.cpp:331-335): 32 bytes per hit,
+ * x,y,z f32 | 4 zero | intensity f32 (64.0) | ring i32 | 8 zero.  Point = t * d_sensor.  Emitted in
+ * ray-id order (the reference's order is mutex-nondeterministic; parity is on the set).
+ * ring_mode 0: ring = channel (OptiX path, SRC/LidarDeviceKernels.cu:51); 1: ring = 0 (Embree path quirk).
+ * Returns the number of points written.
+ * ---------------------------------------------------------------------------------------------- */
+LSO_API int64_t lso_pack_points(const float *dirs_s, const float *t, const int32_t *tri, int64_t nR, int H,
+                                int ring_mode, uint8_t *out)
+{
+    int64_t n = 0;
+    for (int64_t r = 0; r < nR; ++r) {
+        if (tri[r] < 0) continue;
+        float rec[8];
+        memset(rec, 0, sizeof(rec));
+        rec[0] = t[r] * dirs_s[3 * r + 0];
+        rec[1] = t[r] * dirs_s[3 * r + 1];
+        rec[2] = t[r] * dirs_s[3 * r + 2];
+        rec[4] = 64.0f;
+        int32_t ring = ring_mode ? 0 : (int32_t)(r / H);
+        memcpy(&rec[5], &ring, 4);
+        memcpy(out + 32 * n, rec, 32);
+        ++n;
+    }
+    return n;
+}

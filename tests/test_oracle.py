@@ -1,0 +1,116 @@
+"""The CPU oracle against the reference's own pins (point counts) and its internal consistency.
+
+Reference pins: 1668 (SRC/test/EmbreeTracer_test.cpp:134, SRC/test/OptixTracer_test.cpp:119),
+1781 (SRC/test/OptixTracer_test.cpp:168), 0 for the empty scene (SRC/test/OptixTracer_test.cpp:307),
+98 / 162 vertices / triangles for ground.stl (SRC/test/EmbreeTracer_test.cpp:89-90).
+"""
+import numpy as np
+import pytest
+
+from conftest import xt32_sensor_args
+from oracle import lso
+
+
+def _sensor(uid="0000"):
+    return lso.Sensor(*xt32_sensor_args(uid))
+
+
+def test_mesh_counts(meshes):
+    assert meshes["ground_v"].shape == (98, 3) and meshes["ground_t"].shape == (162, 3)
+    assert meshes["ben_v"].shape == (2823, 3) and meshes["ben_t"].shape == (5489, 3)
+
+
+def test_ray_count_and_tables():
+    s = _sensor()
+    assert s.n_rays == 150 * 32                     # SRC/test/LidarDevice_test.cpp:58
+    step = lso.azimuth_step(0.0, 360.0, 150)
+    assert np.float32(0.0) + step * np.float32(149) == np.float32(360.0)
+    d = lso.ray_dirs(s.tables)
+    assert np.allclose(np.linalg.norm(d.astype(np.float64), axis=1), 1.0, atol=1e-6)
+    # ray id = channel * H + azimuth; channel 15 is the horizontal one (elevation 0)
+    assert abs(d[15 * 150, 2]) < 1e-7 and d[0, 2] > 0 and d[31 * 150, 2] < 0
+
+
+@pytest.mark.parametrize("uid,n_ground,n_both", [("0000", 1668, 1781), ("0001", 1633, 1769)])
+def test_reference_point_counts(meshes, uid, n_ground, n_both):
+    s = _sensor(uid)
+    g = (meshes["ground_v"], meshes["ground_t"], lso.IDENTITY_AFFINE)
+    b = (meshes["ben_v"], meshes["ben_t"], lso.IDENTITY_AFFINE)
+    r = lso.scan(s, [g])
+    assert r["points"].shape[0] == n_ground
+    r = lso.scan(s, [g, b])
+    assert r["points"].shape[0] == n_both
+    r = lso.scan(s, [])
+    assert r["points"].shape[0] == 0 and (r["tri"] == -1).all()
+
+
+def test_golden_vectors(meshes, golden):
+    for uid in ("0000", "0001"):
+        s = _sensor(uid)
+        g = (meshes["ground_v"], meshes["ground_t"], lso.IDENTITY_AFFINE)
+        b = (meshes["ben_v"], meshes["ben_t"], lso.IDENTITY_AFFINE)
+        for tag, ms in (("ground", [g]), ("ground_ben", [g, b])):
+            r = lso.scan(s, ms)
+            assert np.array_equal(r["tri"], golden[f"l{uid}_{tag}_tri"])
+            assert np.array_equal(r["t"], golden[f"l{uid}_{tag}_t"])
+
+
+def test_bvh_equals_brute_on_random_soup():
+    rng = np.random.default_rng(5)
+    nT = 3000
+    c = rng.uniform(-20, 20, (nT, 1, 3)).astype(np.float32)
+    v = (c + rng.normal(0, 0.7, (nT, 3, 3)).astype(np.float32)).reshape(-1, 3)
+    t = np.arange(3 * nT, dtype=np.uint32).reshape(-1, 3)
+    d = rng.normal(size=(4000, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = rng.uniform(-5, 5, (4000, 3)).astype(np.float32)
+    tb, ib = lso.trace_brute(v, t, o, d)
+    bv = lso.Bvh(v, t)
+    tv, iv = bv.trace(o, d)
+    assert np.array_equal(ib, iv) and np.array_equal(tb, tv)
+    assert (ib >= 0).sum() > 500
+
+
+def test_world_frame_mode_agrees_with_sensor_frame(meshes):
+    """Moving the rays instead of the scene changes rounding only: same hits away from edges, t within 1e-4 rel."""
+    s = _sensor()
+    g = (meshes["ground_v"], meshes["ground_t"], lso.IDENTITY_AFFINE)
+    b = (meshes["ben_v"], meshes["ben_t"], lso.IDENTITY_AFFINE)
+    r0, r1 = lso.scan(s, [g, b], mode=0), lso.scan(s, [g, b], mode=1)
+    same = r0["tri"] == r1["tri"]
+    assert (~same).sum() <= 8
+    both = same & (r0["tri"] >= 0)
+    assert np.allclose(r0["t"][both], r1["t"][both], rtol=1e-4, atol=0)
+
+
+def test_point_record_layout(meshes):
+    """SRC/XYZIRBytes.cpp:24-40: x y z | 4 zero | intensity 64.0 | ring i32 | 8 zero."""
+    s = _sensor()
+    r = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], lso.IDENTITY_AFFINE)])
+    p = r["points"]
+    assert p.shape[1] == 32
+    f = p.view(np.float32).reshape(-1, 8)
+    i = p.view(np.int32).reshape(-1, 8)
+    assert (f[:, 4] == 64.0).all() and (i[:, 3] == 0).all() and (i[:, 6:] == 0).all()
+    hit = np.flatnonzero(r["tri"] >= 0)
+    assert np.array_equal(i[:, 5], (hit // s.H).astype(np.int32))
+    d = lso.ray_dirs(s.tables)[hit]
+    assert np.array_equal(f[:, :3], d * r["t"][hit, None])
+    r0 = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], lso.IDENTITY_AFFINE)], ring_mode=1)
+    assert (r0["points"].view(np.int32).reshape(-1, 8)[:, 5] == 0).all()    # Embree-path quirk, SRC/EmbreeTracer.cpp:333
+
+
+def test_intersect_conventions():
+    a, b, c = [0, 0, 1], [1, 0, 1], [0, 1, 1]
+    hit, t = lso.intersect_one(a, b, c, [0.2, 0.2, 0], [0, 0, 1])
+    assert hit and t == np.float32(1.0)
+    hit, _ = lso.intersect_one(a, c, b, [0.2, 0.2, 0], [0, 0, 1])          # no back-face culling
+    assert hit
+    hit, _ = lso.intersect_one(a, b, c, [0.2, 0.2, 2], [0, 0, 1])          # behind the origin
+    assert not hit
+    hit, _ = lso.intersect_one(a, b, c, [0.2, 0.2, 1], [0, 0, 1])          # t = 0 is excluded (tnear strict)
+    assert not hit
+    hit, _ = lso.intersect_one(a, b, c, [0.2, 0.2, 0], [1, 0, 0])          # parallel: den = 0
+    assert not hit
+    hit, _ = lso.intersect_one(a, a, a, [0, 0, 0], [0, 0, 1])              # degenerate triangle
+    assert not hit
