@@ -1,0 +1,187 @@
+/*
+ * lsb200.h -- C ABI of the B200-native LiDAR ray-casting backend (liblsb200.so).
+ *
+ * This is the drop-in boundary for lidarshooter's trace step.  Each entry point replaces one call of the
+ * reference's tracer interface (reference tree /root/reference, SRC = ros_ws/src/lidarshooter/src); the C++
+ * adapter `lidarshooter::B200Tracer : ITracer` (lidarshooter_b200/host/B200Tracer.hpp) is a thin marshaller
+ * over these functions.  Plain C types only, no exceptions cross, every function returns an lsb200_status
+ * (>= 0 ok, < 0 error; lsb200_last_error() gives the text).
+ *
+ * Frames.  LSB200_FRAME_SENSOR reproduces the reference's arithmetic: every vertex is moved into the sensor
+ * frame (SRC/MeshTransformer.cpp:173-194, SRC/LidarDevice.cpp:383-391), rays start at 0.  One context == one
+ * LiDAR device, like one EmbreeTracer.  LSB200_FRAME_WORLD keeps the scene in the world frame, builds ONE
+ * BVH per frame and moves the rays instead (o = T, d = R d_s), so many sensors share a context.
+ *
+ * Per-ray results: t (f32, +inf on a miss) and the global triangle id (i32, -1 on a miss).  The global
+ * triangle id is the position of the triangle in the concatenation of all geometries in ascending
+ * geometry-id order.  Closest hit = lexicographic minimum of (t, global triangle id).
+ */
+#ifndef LSB200_H
+#define LSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define LSB200_API
+#else
+#define LSB200_API __attribute__((visibility("default")))
+#endif
+
+typedef struct lsb200_ctx lsb200_ctx;
+
+typedef enum lsb200_status {
+    LSB200_OK = 0,
+    LSB200_ERR_INVALID = -1,      /* bad argument / unknown geometry (SRC/EmbreeTracer.cpp:224-225 returns -1) */
+    LSB200_ERR_EMPTY_SCENE = -1,  /* commit/trace on an empty scene return -1 (SRC/OptixTracer.cpp:263-288) */
+    LSB200_ERR_CUDA = -2,
+    LSB200_ERR_CAPACITY = -3,     /* caller's output buffer too small; *n_pts still holds the hit count */
+    LSB200_ERR_STATE = -4,        /* e.g. trace before commit, sensor not set */
+    LSB200_ERR_NOMEM = -5
+} lsb200_status;
+
+/* geometry element types; values match Embree's RTCGeometryType used by ITracer::addGeometry
+ * (SRC/ITracer.hpp:50; SRC/EmbreeTracer.cpp:115-201): TRIANGLE = 0, QUAD = 1. */
+enum { LSB200_GEOMETRY_TRIANGLE = 0, LSB200_GEOMETRY_QUAD = 1 };
+
+enum { LSB200_FRAME_SENSOR = 0, LSB200_FRAME_WORLD = 1 };
+
+/* lsb200_commit_scene modes: AUTO = rebuild when topology (add/remove/index data) changed since the last
+ * build, otherwise refit (what OptiX's BUILD/UPDATE switch does, SRC/OptixTracer.cpp:529-535). */
+enum { LSB200_COMMIT_AUTO = 0, LSB200_COMMIT_REBUILD = 1, LSB200_COMMIT_REFIT = 2 };
+
+/* lsb200_trace_* flags */
+enum {
+    LSB200_TRACE_ORDERED = 1u << 0,    /* points emitted in ray-id order (scan); default: warp-aggregated atomics */
+    LSB200_TRACE_RING_ZERO = 1u << 1,  /* ring = 0 for every point (Embree-path quirk, SRC/EmbreeTracer.cpp:333-334) */
+    LSB200_TRACE_XYZI16 = 1u << 2,     /* 16-byte x,y,z,intensity records instead of the 32-byte PointCloud2 record */
+    LSB200_TRACE_NO_POINTS = 1u << 3,  /* per-ray t / triangle only (lsb200_trace_raw uses this) */
+    LSB200_TRACE_WORLD_POINTS = 1u << 4 /* emit points in the world frame: R p + T (SRC/LidarDevice.cpp:393-401) */
+};
+
+/* traversal kernel variants (lsb200_set_option LSB200_OPT_TRAVERSAL) -- for the ncu before/after evidence */
+enum {
+    LSB200_OPT_TRAVERSAL = 1,      /* 0 = persistent + smem-staged top levels (default), 1 = persistent, no staging,
+                                      2 = one thread per ray (no persistent fetch), 3 = brute force (all triangles) */
+    LSB200_OPT_LEAF_SIZE = 2,      /* max triangles per leaf, 1..8 (default 4) */
+    LSB200_OPT_TOP_NODES = 3,      /* number of BVH nodes staged into shared memory by TMA bulk copy (default 1024) */
+    LSB200_OPT_STAGE_TIMING = 4,   /* 1 = record CUDA events around every stage (lsb200_get_stats) */
+    LSB200_OPT_CTAS_PER_SM = 5     /* persistent grid = 148 * this (default 0 = occupancy query) */
+};
+
+/* ---- life cycle -------------------------------------------------------------------------------------- */
+/* replaces EmbreeTracer::create / rtcNewDevice + rtcNewScene (SRC/EmbreeTracer.cpp:20-34, 482-486) */
+LSB200_API int lsb200_create(int cuda_device, lsb200_ctx **out);
+LSB200_API int lsb200_destroy(lsb200_ctx *ctx);
+/* all work of this context is enqueued on `cuda_stream` (a cudaStream_t; NULL = the context's own stream) */
+LSB200_API int lsb200_set_stream(lsb200_ctx *ctx, void *cuda_stream);
+LSB200_API int lsb200_set_frame_mode(lsb200_ctx *ctx, int frame_mode);
+LSB200_API int lsb200_set_option(lsb200_ctx *ctx, int option, int value);
+LSB200_API const char *lsb200_last_error(const lsb200_ctx *ctx);
+LSB200_API const char *lsb200_version(void);
+
+/* ---- sensor: what LidarDevice holds for the path (SRC/LidarDevice.cpp:598-617 channels, 788-816 transform) ---
+ * elev_deg[V] degrees above horizontal; azimuth table az[h] = az_begin + step * h with
+ * step = (az_end - az_begin) / (H - 1) in fp32; q_wxyz is NOT normalised (SRC/LidarDevice.cpp:808-813);
+ * t_xyz = (base_to_origin.tx, base_to_origin.ty, sensor_to_base.tz).  The sin/cos tables are computed on the
+ * host with the reference's own narrowing (double -> float before sinf/cosf, SRC/LidarDevice.cpp:312-318).
+ * sensor_index 0 is the context's device; indices > 0 are allowed in LSB200_FRAME_WORLD only. */
+LSB200_API int lsb200_set_sensor(lsb200_ctx *ctx, int sensor_index, const float *elev_deg, int V, float az_begin,
+                                 float az_end, int H, const float q_wxyz[4], const float t_xyz[3]);
+LSB200_API int lsb200_get_ray_count(const lsb200_ctx *ctx, int sensor_index);
+
+/* ---- geometry: ITracer::addGeometry / removeGeometry / updateGeometry (SRC/ITracer.hpp:50-85) ------------- */
+/* replaces EmbreeTracer::addGeometry (SRC/EmbreeTracer.cpp:115-218).  Returns the geometry id (>= 0), lowest
+ * free id first like rtcAttachGeometry; unsupported geometry_type -> LSB200_ERR_INVALID. */
+LSB200_API int lsb200_add_geometry(lsb200_ctx *ctx, const char *name, int geometry_type, int n_vertices,
+                                   int n_elements);
+/* replaces EmbreeTracer::removeGeometry (SRC/EmbreeTracer.cpp:220-260): returns the removed id, -1 if unknown;
+ * the scene is re-committed like the reference does (:252) when any geometry is left. */
+LSB200_API int lsb200_remove_geometry(lsb200_ctx *ctx, const char *name);
+LSB200_API int lsb200_get_geometry_count(const lsb200_ctx *ctx);
+LSB200_API int lsb200_get_geometry_id(const lsb200_ctx *ctx, const char *name);
+/* replaces EmbreeTracer::updateGeometry(name, Affine3f, mesh) (SRC/EmbreeTracer.cpp:262-274) and
+ * MeshTransformer::transformIntoBuffer (SRC/MeshTransformer.cpp:142-205).  verts: n_vertices records of
+ * vert_stride_bytes, xyz float32 at offset 0 (pcl::PCLPointCloud2 blob).  elems: n_elements x 3 (or x 4)
+ * uint32; NULL = topology unchanged since the last call (the reference re-copies it every frame,
+ * SRC/MeshTransformer.cpp:486-552).  affine3x4 row-major [L | t].  Host pointers are read before return. */
+LSB200_API int lsb200_update_geometry(lsb200_ctx *ctx, const char *name, const void *verts, int vert_stride_bytes,
+                                      const uint32_t *elems, const float affine3x4[12]);
+/* replaces updateGeometry(name, translation, eulerXYZ, mesh): A = T * Rz * Ry * Rx (SRC/MeshTransformer.cpp:467-477) */
+LSB200_API int lsb200_update_geometry_euler(lsb200_ctx *ctx, const char *name, const void *verts,
+                                            int vert_stride_bytes, const uint32_t *elems, const float translation[3],
+                                            const float euler_xyz[3]);
+/* vertices already resident on the device from an earlier update: only the transform changes (no H2D copy) */
+LSB200_API int lsb200_update_transform(lsb200_ctx *ctx, const char *name, const float affine3x4[12]);
+LSB200_API void lsb200_affine_from_components(const float translation[3], const float euler_xyz[3], float affine3x4[12]);
+
+/* ---- commit: replaces EmbreeTracer::commitScene / rtcCommitScene (SRC/EmbreeTracer.cpp:290-295) ----------
+ * transform kernel -> Morton codes -> radix sort -> Karras hierarchy -> bottom-up AABB fit (rebuild), or
+ * transform -> leaf + AABB refit (refit).  Empty scene -> -1. */
+LSB200_API int lsb200_commit_scene(lsb200_ctx *ctx, int mode);
+
+/* ---- trace: replaces EmbreeTracer::traceScene (SRC/EmbreeTracer.cpp:297-367) ---------------------------
+ * out_points: HOST buffer of capacity_pts records (32 B, or 16 B with LSB200_TRACE_XYZI16); *n_pts = hits.
+ * Record (SRC/XYZIRBytes.cpp:24-40): x y z f32 | 4 zero bytes | intensity f32 = 64.0 | ring i32 | 8 zero bytes;
+ * point = t * d_sensor.  Empty scene: *n_pts = 0 and -1 (SRC/OptixTracer.cpp:279-288). */
+LSB200_API int lsb200_trace_scene(lsb200_ctx *ctx, int sensor_index, uint32_t frame_index, void *out_points,
+                                  size_t capacity_pts, uint32_t *n_pts, uint32_t flags);
+/* same, results stay in device memory (lsb200_device_results) -- no synchronisation, no copies */
+LSB200_API int lsb200_trace_device(lsb200_ctx *ctx, int sensor_index, uint32_t flags);
+/* one launch for the sensors [first_sensor, first_sensor + n_sensors) (LSB200_FRAME_WORLD): the batch form of
+ * lsb200_trace_device, used when many LiDAR devices share one scene */
+LSB200_API int lsb200_trace_batch(lsb200_ctx *ctx, int first_sensor, int n_sensors, uint32_t flags);
+/* per-ray results for parity tests: t_out[R], tri_out[R] host buffers */
+LSB200_API int lsb200_trace_raw(lsb200_ctx *ctx, int sensor_index, float *t_out, int32_t *tri_out);
+/* device pointers of the last trace of `sensor_index`: points, point count (uint32), t, triangle id */
+LSB200_API int lsb200_device_results(lsb200_ctx *ctx, int sensor_index, void **d_points, uint32_t **d_count,
+                                     float **d_t, int32_t **d_tri);
+/* copies the device point buffer of sensor_index to the host (count first, then count records) */
+LSB200_API int lsb200_fetch_points(lsb200_ctx *ctx, int sensor_index, void *out_points, size_t capacity_pts,
+                                   uint32_t *n_pts, uint32_t flags);
+LSB200_API int lsb200_synchronize(lsb200_ctx *ctx);
+
+/* ---- PointCloud2 header: replaces LidarDevice::initMessage (SRC/LidarDevice.cpp:94-115) ------------------ */
+typedef struct lsb200_cloud_header {
+    uint32_t seq;          /* = frame index */
+    uint32_t height;       /* 1 */
+    uint32_t width;        /* number of points */
+    uint32_t point_step;   /* 32 */
+    uint32_t row_step;     /* 0, as the reference leaves it (SRC/LidarDevice.cpp:112) */
+    uint8_t is_bigendian;  /* 0 */
+    uint8_t is_dense;      /* 1 */
+    uint8_t n_fields;      /* 5: x y z intensity ring */
+    uint8_t reserved;
+} lsb200_cloud_header;
+LSB200_API int lsb200_init_message(const lsb200_ctx *ctx, uint32_t frame_index, lsb200_cloud_header *out);
+
+/* ---- diagnostics ----------------------------------------------------------------------------------------- */
+typedef struct lsb200_stats {
+    int64_t n_vertices, n_triangles, n_nodes, n_leaves;
+    int32_t last_commit_was_rebuild;
+    int32_t top_nodes;             /* nodes staged into shared memory */
+    int32_t trace_grid, trace_block;
+    /* milliseconds of the last commit / trace (CUDA events; valid with LSB200_OPT_STAGE_TIMING = 1) */
+    float ms_transform, ms_morton, ms_sort, ms_hierarchy, ms_fit, ms_toplevel, ms_trace, ms_compact;
+    /* launches issued since the context was created / since lsb200_reset_counters */
+    int64_t kernel_launches;
+    float scene_lo[3], scene_hi[3];
+} lsb200_stats;
+LSB200_API int lsb200_get_stats(lsb200_ctx *ctx, lsb200_stats *out);
+LSB200_API int lsb200_reset_counters(lsb200_ctx *ctx);
+/* copies the BVH to the host for structural tests: nodes (n_nodes x 16 floats), leaf-ordered triangle ids */
+LSB200_API int lsb200_debug_copy_bvh(lsb200_ctx *ctx, float *nodes16, int64_t node_capacity, int32_t *leaf_tri_ids,
+                                     int64_t tri_capacity, int32_t *root);
+/* device sort self-test entry (parity tests of the radix sort): sorts n (key,value) pairs held in HOST arrays */
+LSB200_API int lsb200_debug_sort_pairs(lsb200_ctx *ctx, uint32_t *keys, uint32_t *vals, int64_t n);
+/* transformed vertices (n x 3 f32, concatenation order) of the last commit, for bit-exact transform tests */
+LSB200_API int lsb200_debug_copy_vertices(lsb200_ctx *ctx, float *xyz, int64_t capacity_vertices);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LSB200_H */

@@ -1,0 +1,281 @@
+"""ctypes binding of the C ABI in include/lsb200.h (liblsb200.so).
+
+This is plumbing for tests and bench.py: every call goes straight into the CUDA library.  There is no CPU
+fallback: if liblsb200.so is missing or no CUDA device is present the import / lsb200_create fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblsb200.so")
+
+GEOMETRY_TRIANGLE, GEOMETRY_QUAD = 0, 1
+FRAME_SENSOR, FRAME_WORLD = 0, 1
+COMMIT_AUTO, COMMIT_REBUILD, COMMIT_REFIT = 0, 1, 2
+TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS = 1, 2, 4, 8, 16
+OPT_TRAVERSAL, OPT_LEAF_SIZE, OPT_TOP_NODES, OPT_STAGE_TIMING, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
+ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5
+
+# every symbol include/lsb200.h declares (tests/test_abi.py checks the library exports each one)
+SYMBOLS = [
+    "lsb200_create", "lsb200_destroy", "lsb200_set_stream", "lsb200_set_frame_mode", "lsb200_set_option",
+    "lsb200_last_error", "lsb200_version", "lsb200_set_sensor", "lsb200_get_ray_count", "lsb200_add_geometry",
+    "lsb200_remove_geometry", "lsb200_get_geometry_count", "lsb200_get_geometry_id", "lsb200_update_geometry",
+    "lsb200_update_geometry_euler", "lsb200_update_transform", "lsb200_affine_from_components",
+    "lsb200_commit_scene", "lsb200_trace_scene", "lsb200_trace_device", "lsb200_trace_batch", "lsb200_trace_raw",
+    "lsb200_device_results", "lsb200_fetch_points", "lsb200_synchronize", "lsb200_init_message", "lsb200_get_stats",
+    "lsb200_reset_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
+]
+
+
+class CloudHeader(C.Structure):
+    _fields_ = [("seq", C.c_uint32), ("height", C.c_uint32), ("width", C.c_uint32), ("point_step", C.c_uint32),
+                ("row_step", C.c_uint32), ("is_bigendian", C.c_uint8), ("is_dense", C.c_uint8),
+                ("n_fields", C.c_uint8), ("reserved", C.c_uint8)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_vertices", C.c_int64), ("n_triangles", C.c_int64), ("n_nodes", C.c_int64), ("n_leaves", C.c_int64),
+                ("last_commit_was_rebuild", C.c_int32), ("top_nodes", C.c_int32), ("trace_grid", C.c_int32),
+                ("trace_block", C.c_int32),
+                ("ms_transform", C.c_float), ("ms_morton", C.c_float), ("ms_sort", C.c_float),
+                ("ms_hierarchy", C.c_float), ("ms_fit", C.c_float), ("ms_toplevel", C.c_float),
+                ("ms_trace", C.c_float), ("ms_compact", C.c_float),
+                ("kernel_launches", C.c_int64), ("scene_lo", C.c_float * 3), ("scene_hi", C.c_float * 3)]
+
+
+_lib = None
+
+
+def lib():
+    """Loads liblsb200.so (raises OSError with the build hint when it is absent)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OSError(f"{LIB_PATH} not found: build it with `make -C lidarshooter_b200` "
+                      "(or __graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, f32p, u32p, i32p = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
+    L.lsb200_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.lsb200_destroy.argtypes = [vp]
+    L.lsb200_set_stream.argtypes = [vp, vp]
+    L.lsb200_set_frame_mode.argtypes = [vp, C.c_int]
+    L.lsb200_set_option.argtypes = [vp, C.c_int, C.c_int]
+    L.lsb200_last_error.argtypes = [vp]
+    L.lsb200_last_error.restype = C.c_char_p
+    L.lsb200_version.restype = C.c_char_p
+    L.lsb200_set_sensor.argtypes = [vp, C.c_int, f32p, C.c_int, C.c_float, C.c_float, C.c_int, f32p, f32p]
+    L.lsb200_get_ray_count.argtypes = [vp, C.c_int]
+    L.lsb200_add_geometry.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_int]
+    L.lsb200_remove_geometry.argtypes = [vp, C.c_char_p]
+    L.lsb200_get_geometry_count.argtypes = [vp]
+    L.lsb200_get_geometry_id.argtypes = [vp, C.c_char_p]
+    L.lsb200_update_geometry.argtypes = [vp, C.c_char_p, vp, C.c_int, vp, f32p]
+    L.lsb200_update_geometry_euler.argtypes = [vp, C.c_char_p, vp, C.c_int, vp, f32p, f32p]
+    L.lsb200_update_transform.argtypes = [vp, C.c_char_p, f32p]
+    L.lsb200_affine_from_components.argtypes = [f32p, f32p, f32p]
+    L.lsb200_affine_from_components.restype = None
+    L.lsb200_commit_scene.argtypes = [vp, C.c_int]
+    L.lsb200_trace_scene.argtypes = [vp, C.c_int, C.c_uint32, vp, C.c_size_t, u32p, C.c_uint32]
+    L.lsb200_trace_device.argtypes = [vp, C.c_int, C.c_uint32]
+    L.lsb200_trace_batch.argtypes = [vp, C.c_int, C.c_int, C.c_uint32]
+    L.lsb200_trace_raw.argtypes = [vp, C.c_int, f32p, i32p]
+    L.lsb200_device_results.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    L.lsb200_fetch_points.argtypes = [vp, C.c_int, vp, C.c_size_t, u32p, C.c_uint32]
+    L.lsb200_synchronize.argtypes = [vp]
+    L.lsb200_init_message.argtypes = [vp, C.c_uint32, C.POINTER(CloudHeader)]
+    L.lsb200_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.lsb200_reset_counters.argtypes = [vp]
+    L.lsb200_debug_copy_bvh.argtypes = [vp, f32p, C.c_int64, i32p, C.c_int64, i32p]
+    L.lsb200_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_int64]
+    L.lsb200_debug_copy_vertices.argtypes = [vp, f32p, C.c_int64]
+    _lib = L
+    return L
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class Lsb200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"lsb200 error {code}: {msg}")
+        self.code = code
+
+
+class Context:
+    """Thin object wrapper: one lsb200_ctx.  Methods return the ABI's status codes where the reference's
+    interface does (add/remove/commit/trace) and raise Lsb200Error on CUDA failures."""
+
+    def __init__(self, device=0, frame_mode=FRAME_SENSOR, stream=None):
+        self._L = lib()
+        h = C.c_void_p()
+        rc = self._L.lsb200_create(int(device), C.byref(h))
+        if rc != 0:
+            raise Lsb200Error(rc, "lsb200_create failed (no CUDA device? this library has no CPU path)")
+        self._h = h
+        self._keep = {}
+        if frame_mode != FRAME_SENSOR:
+            self._chk(self._L.lsb200_set_frame_mode(h, frame_mode))
+        if stream is not None:
+            self.set_stream(stream)
+
+    # -- helpers
+    def _chk(self, rc):
+        if rc < 0:
+            raise Lsb200Error(rc, self.last_error())
+        return rc
+
+    def last_error(self):
+        return self._L.lsb200_last_error(self._h).decode()
+
+    def close(self):
+        if self._h:
+            self._L.lsb200_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream_handle):
+        self._chk(self._L.lsb200_set_stream(self._h, C.c_void_p(int(cuda_stream_handle) if cuda_stream_handle else None)))
+
+    def set_option(self, opt, value):
+        self._chk(self._L.lsb200_set_option(self._h, opt, int(value)))
+
+    def set_frame_mode(self, mode):
+        self._chk(self._L.lsb200_set_frame_mode(self._h, mode))
+
+    def set_sensor(self, elev_deg, az_begin, az_end, H, q_wxyz=(1, 0, 0, 0), t_xyz=(0, 0, 0), index=0):
+        e = np.ascontiguousarray(elev_deg, np.float32)
+        q = np.ascontiguousarray(q_wxyz, np.float32)
+        t = np.ascontiguousarray(t_xyz, np.float32)
+        self._chk(self._L.lsb200_set_sensor(self._h, index, _fp(e), e.size, float(np.float32(az_begin)),
+                                            float(np.float32(az_end)), int(H), _fp(q), _fp(t)))
+
+    def ray_count(self, index=0):
+        return self._L.lsb200_get_ray_count(self._h, index)
+
+    # -- ITracer-shaped calls (return codes like the reference)
+    def add_geometry(self, name, geometry_type, n_vertices, n_elements):
+        return self._L.lsb200_add_geometry(self._h, name.encode(), geometry_type, n_vertices, n_elements)
+
+    def remove_geometry(self, name):
+        return self._L.lsb200_remove_geometry(self._h, name.encode())
+
+    def geometry_count(self):
+        return self._L.lsb200_get_geometry_count(self._h)
+
+    def geometry_id(self, name):
+        return self._L.lsb200_get_geometry_id(self._h, name.encode())
+
+    def update_geometry(self, name, verts=None, elems=None, affine=None, stride=None):
+        """verts: (n,3) float32 array or a uint8 blob with `stride`; elems: (m,3|4) uint32; affine: 12 floats."""
+        A = np.ascontiguousarray(affine if affine is not None else [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], np.float32)
+        vptr, eptr = None, None
+        if verts is not None:
+            if stride is None:
+                verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 3)
+                stride = 12
+            else:
+                verts = np.ascontiguousarray(verts, np.uint8)
+            vptr = verts.ctypes.data
+        if elems is not None:
+            elems = np.ascontiguousarray(elems, np.uint32)
+            eptr = elems.ctypes.data
+        self._keep[name] = (verts, elems)      # pinned callers may hand memory that is read asynchronously
+        return self._L.lsb200_update_geometry(self._h, name.encode(), vptr, int(stride or 0), eptr, _fp(A))
+
+    def update_geometry_euler(self, name, verts, elems, translation, euler_xyz, stride=None):
+        A = affine_from_components(translation, euler_xyz)
+        return self.update_geometry(name, verts, elems, A, stride)
+
+    def update_transform(self, name, affine):
+        A = np.ascontiguousarray(affine, np.float32)
+        return self._L.lsb200_update_transform(self._h, name.encode(), _fp(A))
+
+    def commit_scene(self, mode=COMMIT_AUTO):
+        return self._L.lsb200_commit_scene(self._h, mode)
+
+    def trace_scene(self, frame_index=0, flags=0, sensor=0, out=None):
+        """Returns (status, points) with points a (n, 32|16) uint8 array (host)."""
+        R = max(self.ray_count(sensor), 0)
+        rec = 16 if flags & TRACE_XYZI16 else 32
+        if out is None:
+            out = np.empty((R, rec), np.uint8)
+        n = C.c_uint32(0)
+        rc = self._L.lsb200_trace_scene(self._h, sensor, frame_index, out.ctypes.data, out.shape[0], C.byref(n), flags)
+        return rc, out[:n.value]
+
+    def trace_device(self, sensor=0, flags=0):
+        return self._L.lsb200_trace_device(self._h, sensor, flags)
+
+    def trace_batch(self, first, count, flags=0):
+        return self._L.lsb200_trace_batch(self._h, first, count, flags)
+
+    def fetch_points(self, sensor=0, flags=0, out=None):
+        R = max(self.ray_count(sensor), 0)
+        rec = 16 if flags & TRACE_XYZI16 else 32
+        if out is None:
+            out = np.empty((R, rec), np.uint8)
+        n = C.c_uint32(0)
+        rc = self._L.lsb200_fetch_points(self._h, sensor, out.ctypes.data, out.shape[0], C.byref(n), flags)
+        return rc, out[:n.value]
+
+    def trace_raw(self, sensor=0):
+        R = self.ray_count(sensor)
+        t, tri = np.empty(R, np.float32), np.empty(R, np.int32)
+        rc = self._L.lsb200_trace_raw(self._h, sensor, _fp(t), tri.ctypes.data_as(C.POINTER(C.c_int32)))
+        return rc, t, tri
+
+    def synchronize(self):
+        self._chk(self._L.lsb200_synchronize(self._h))
+
+    def init_message(self, frame_index):
+        h = CloudHeader()
+        self._chk(self._L.lsb200_init_message(self._h, frame_index, C.byref(h)))
+        return h
+
+    def stats(self):
+        s = Stats()
+        self._chk(self._L.lsb200_get_stats(self._h, C.byref(s)))
+        return s
+
+    def reset_counters(self):
+        self._L.lsb200_reset_counters(self._h)
+
+    def debug_copy_bvh(self):
+        s = self.stats()
+        nodes = np.empty((max(int(s.n_nodes), 1), 16), np.float32)
+        ids = np.empty(int(s.n_triangles), np.int32)
+        root = C.c_int32(0)
+        self._chk(self._L.lsb200_debug_copy_bvh(self._h, _fp(nodes), nodes.shape[0], ids.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                ids.size, C.byref(root)))
+        return nodes, ids, root.value
+
+    def debug_sort_pairs(self, keys, vals):
+        k = np.ascontiguousarray(keys, np.uint32).copy()
+        v = np.ascontiguousarray(vals, np.uint32).copy()
+        self._chk(self._L.lsb200_debug_sort_pairs(self._h, k.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                                  v.ctypes.data_as(C.POINTER(C.c_uint32)), k.size))
+        return k, v
+
+    def debug_copy_vertices(self):
+        s = self.stats()
+        out = np.empty((int(s.n_vertices), 3), np.float32)
+        self._chk(self._L.lsb200_debug_copy_vertices(self._h, _fp(out), out.shape[0]))
+        return out
+
+
+def affine_from_components(translation, euler_xyz):
+    t = np.ascontiguousarray(translation, np.float32)
+    r = np.ascontiguousarray(euler_xyz, np.float32)
+    A = np.empty(12, np.float32)
+    lib().lsb200_affine_from_components(_fp(t), _fp(r), _fp(A))
+    return A

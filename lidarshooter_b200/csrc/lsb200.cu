@@ -1,0 +1,880 @@
+// lsb200.cu -- context, memory management and the C ABI (include/lsb200.h) of liblsb200.so.
+// Host side is C++17; every entry point is extern "C", takes plain pointers and sizes, catches everything.
+#include "../../include/lsb200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "radix_sort.cuh"
+#include "build.cuh"
+#include "trace.cuh"
+
+using namespace lsb;
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    // grows geometrically; contents are NOT preserved unless keep == true
+    cudaError_t reserve(size_t bytes, cudaStream_t s, bool keep = false, bool zero_new = false)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        size_t ncap = std::max(bytes, cap + cap / 2);
+        ncap = (ncap + 255) & ~size_t(255);
+        void *np = nullptr;
+        cudaError_t e = cudaMalloc(&np, ncap);
+        if (e != cudaSuccess) return e;
+        if (zero_new) { e = cudaMemsetAsync(np, 0, ncap, s); if (e != cudaSuccess) return e; }
+        if (keep && p && cap) { e = cudaMemcpyAsync(np, p, cap, cudaMemcpyDeviceToDevice, s); if (e != cudaSuccess) return e; }
+        if (p) { cudaStreamSynchronize(s); cudaFree(p); }
+        p = np; cap = ncap;
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct Geometry {
+    std::string name;
+    int id = -1, type = 0, n_verts = 0, n_elems = 0, verts_per_elem = 3, stride = 12;
+    DevBuf verts, elems;
+    bool has_verts = false, has_elems = false;
+    float A[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    int n_tris() const { return verts_per_elem == 4 ? 2 * n_elems : n_elems; }
+};
+
+struct Sensor {
+    bool set = false;
+    int V = 0, H = 0;
+    float R[9], Rinv[9], T[3], q[4];
+    DevBuf tables;                     // sin_t[V] cos_t[V] sin_p[H] cos_p[H]
+    DevBuf t, tri, points, blocks;     // per-ray results, compacted points, ordered-compaction scratch
+    int n_rays() const { return V * H; }
+};
+
+}  // namespace
+
+struct lsb200_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr, own_stream = nullptr;
+    int frame_mode = LSB200_FRAME_SENSOR;
+    int opt_traversal = 0, opt_leaf = 4, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0;
+    int sm_count = kSmCount;
+    std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
+    std::map<std::string, int> by_name;
+    bool topology_dirty = true, committed = false;
+    int built_leaf = 0, built_top = 0;
+    std::vector<Sensor> sensors;
+    bool sensors_dirty = true;
+    // scene arrays
+    DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
+        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_counts, d_sensor_xf;
+    std::vector<GeomDesc> h_geoms;
+    std::vector<SensorDev> h_sensors;
+    float h_xf[12];
+    uint32_t *h_count = nullptr;                                 // pinned
+    int n_verts = 0, n_tris = 0;
+    lsb200_stats stats{};
+    cudaEvent_t ev[12] = {};
+    std::string err;
+    std::mutex mtx;
+};
+
+namespace {
+
+int fail(lsb200_ctx *c, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    if (c) c->err = buf;
+    return code;
+}
+
+#define LSB_CU(c, call)                                                                                  \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return fail((c), LSB200_ERR_CUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+// ---- small host linear algebra in the reference's evaluation order (oracle/lsb_oracle.c mirrors it) -------
+inline float dot3e(float a0, float b0, float a1, float b1, float a2, float b2)
+{
+    const float p0 = a0 * b0, p1 = a1 * b1, p2 = a2 * b2;
+    const float s12 = p1 + p2;
+    return p0 + s12;
+}
+void mat3_mul(const float *A, const float *B, float *C)
+{
+    float T[9];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            T[3 * i + j] = dot3e(A[3 * i], B[j], A[3 * i + 1], B[3 + j], A[3 * i + 2], B[6 + j]);
+    std::memcpy(C, T, sizeof(T));
+}
+// Eigen::Quaternionf::toRotationMatrix(), no normalisation (SRC/LidarDevice.cpp:808-812)
+void quat_to_rotation(const float q[4], float R[9])
+{
+    const float w = q[0], x = q[1], y = q[2], z = q[3];
+    const float tx = 2.0f * x, ty = 2.0f * y, tz = 2.0f * z;
+    const float twx = tx * w, twy = ty * w, twz = tz * w;
+    const float txx = tx * x, txy = ty * x, txz = tz * x;
+    const float tyy = ty * y, tyz = tz * y, tzz = tz * z;
+    R[0] = 1.0f - (tyy + tzz); R[1] = txy - twz;          R[2] = txz + twy;
+    R[3] = txy + twz;          R[4] = 1.0f - (txx + tzz); R[5] = tyz - twx;
+    R[6] = txz - twy;          R[7] = tyz + twx;          R[8] = 1.0f - (txx + tyy);
+}
+inline float cof3(const float *M, int i, int j)
+{
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    return M[3 * i1 + j1] * M[3 * i2 + j2] - M[3 * i1 + j2] * M[3 * i2 + j1];
+}
+// Eigen::Matrix3f::inverse() (SRC/LidarDevice.cpp:813): cofactors / determinant
+void inverse3(const float M[9], float Mi[9])
+{
+    const float c0 = cof3(M, 0, 0), c1 = cof3(M, 1, 0), c2 = cof3(M, 2, 0);
+    const float det = dot3e(c0, M[0], c1, M[3], c2, M[6]);
+    const float invdet = 1.0f / det;
+    Mi[0] = c0 * invdet; Mi[1] = c1 * invdet; Mi[2] = c2 * invdet;
+    for (int j = 1; j < 3; ++j)
+        for (int i = 0; i < 3; ++i) Mi[3 * j + i] = cof3(M, i, j) * invdet;
+}
+
+Geometry *find_geom(lsb200_ctx *c, const char *name)
+{
+    if (!name) return nullptr;
+    auto it = c->by_name.find(name);
+    if (it == c->by_name.end()) return nullptr;
+    return &c->geoms[it->second];
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+void count_launch(lsb200_ctx *c, int n = 1) { c->stats.kernel_launches += n; }
+
+SceneDev scene_dev(lsb200_ctx *c)
+{
+    SceneDev S{};
+    S.geoms = c->d_geoms.as<GeomDesc>(); S.n_geoms = (int)c->geoms.size();
+    S.n_verts = c->n_verts; S.n_tris = c->n_tris;
+    S.xverts = c->d_xverts.as<float4>(); S.bounds = c->d_bounds.as<uint32_t>();
+    S.keys = c->d_keys.as<uint32_t>(); S.vals = c->d_vals.as<uint32_t>();
+    S.tris = c->d_tris.as<float4>(); S.leaf_ids = c->d_leaf_ids.as<int32_t>();
+    S.nodes = c->d_nodes.as<float4>(); S.node_parent = c->d_node_parent.as<int32_t>();
+    S.leaf_parent = c->d_leaf_parent.as<int32_t>(); S.flags = c->d_flags.as<uint32_t>();
+    S.top_cap = c->built_top; S.leaf_max = c->built_leaf;
+    return S;
+}
+
+int upload_geometry(lsb200_ctx *c, Geometry &g, const void *verts, int stride, const uint32_t *elems)
+{
+    if (verts) {
+        if (stride < 12 || (stride & 3)) return fail(c, LSB200_ERR_INVALID, "vertex stride %d must be >= 12 and a multiple of 4", stride);
+        const size_t bytes = (size_t)g.n_verts * (size_t)stride;
+        LSB_CU(c, g.verts.reserve(std::max<size_t>(bytes, 16), c->stream));
+        if (bytes) LSB_CU(c, cudaMemcpyAsync(g.verts.p, verts, bytes, cudaMemcpyHostToDevice, c->stream));
+        g.stride = stride; g.has_verts = true;
+    }
+    if (elems) {
+        const size_t bytes = (size_t)g.n_elems * g.verts_per_elem * sizeof(uint32_t);
+        LSB_CU(c, g.elems.reserve(std::max<size_t>(bytes, 16), c->stream));
+        if (bytes) LSB_CU(c, cudaMemcpyAsync(g.elems.p, elems, bytes, cudaMemcpyHostToDevice, c->stream));
+        g.has_elems = true;
+        c->topology_dirty = true;
+    }
+    return 0;
+}
+
+}  // namespace
+
+// =============================================================================================================
+//  C ABI
+// =============================================================================================================
+extern "C" {
+
+const char *lsb200_version(void) { return "lsb200 0.1 (sm_100a)"; }
+
+const char *lsb200_last_error(const lsb200_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int lsb200_create(int cuda_device, lsb200_ctx **out)
+{
+    if (!out) return LSB200_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) return LSB200_ERR_CUDA;   // no CPU fallback, by design
+    if (cuda_device < 0 || cuda_device >= n) return LSB200_ERR_INVALID;
+    lsb200_ctx *c = new (std::nothrow) lsb200_ctx();
+    if (!c) return LSB200_ERR_NOMEM;
+    c->device = cuda_device;
+    DeviceGuard dg(cuda_device);
+    cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
+    c->stream = c->own_stream;
+    for (auto &e : c->ev) cudaEventCreate(&e);
+    cudaMallocHost((void **)&c->h_count, 16 * sizeof(uint32_t));
+    if (c->d_bounds.reserve(256, c->stream) != cudaSuccess || c->d_misc.reserve(256, c->stream, false, true) != cudaSuccess ||
+        c->d_sensor_xf.reserve(256, c->stream) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
+    c->sensors.resize(1);
+    *out = c;
+    return LSB200_OK;
+}
+
+int lsb200_destroy(lsb200_ctx *c)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    {
+        DeviceGuard dg(c->device);
+        cudaStreamSynchronize(c->stream);
+        for (auto &kv : c->geoms) { kv.second.verts.release(); kv.second.elems.release(); }
+        for (auto &s : c->sensors) { s.tables.release(); s.t.release(); s.tri.release(); s.points.release(); s.blocks.release(); }
+        DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
+                          &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
+                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_counts, &c->d_sensor_xf};
+        for (auto *b : bufs) b->release();
+        if (c->h_count) cudaFreeHost(c->h_count);
+        for (auto &e : c->ev) if (e) cudaEventDestroy(e);
+        if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    }
+    delete c;
+    return LSB200_OK;
+}
+
+int lsb200_set_stream(lsb200_ctx *c, void *cuda_stream)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    DeviceGuard dg(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return LSB200_OK;
+}
+
+int lsb200_set_frame_mode(lsb200_ctx *c, int mode)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (mode != LSB200_FRAME_SENSOR && mode != LSB200_FRAME_WORLD) return fail(c, LSB200_ERR_INVALID, "bad frame mode %d", mode);
+    if (mode != c->frame_mode) { c->frame_mode = mode; c->committed = false; }
+    return LSB200_OK;
+}
+
+int lsb200_set_option(lsb200_ctx *c, int option, int value)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    switch (option) {
+    case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 3) break; c->opt_traversal = value; return LSB200_OK;
+    case LSB200_OPT_LEAF_SIZE: if (value < 1 || value > kMaxLeaf) break; c->opt_leaf = value; c->topology_dirty = true; return LSB200_OK;
+    case LSB200_OPT_TOP_NODES: if (value < 0 || value > 3072) break; c->opt_top = value; c->topology_dirty = true; return LSB200_OK;
+    case LSB200_OPT_STAGE_TIMING: c->opt_timing = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_CTAS_PER_SM: if (value < 0 || value > 32) break; c->opt_ctas_per_sm = value; return LSB200_OK;
+    default: break;
+    }
+    return fail(c, LSB200_ERR_INVALID, "bad option %d = %d", option, value);
+}
+
+int lsb200_set_sensor(lsb200_ctx *c, int idx, const float *elev_deg, int V, float az_begin, float az_end, int H,
+                      const float q_wxyz[4], const float t_xyz[3])
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || idx >= kMaxSensors || !elev_deg || V <= 0 || H <= 0 || !q_wxyz || !t_xyz)
+        return fail(c, LSB200_ERR_INVALID, "set_sensor: bad arguments");
+    if ((int64_t)V * H > (int64_t)1 << 30) return fail(c, LSB200_ERR_INVALID, "set_sensor: too many rays");
+    DeviceGuard dg(c->device);
+    if ((size_t)idx >= c->sensors.size()) c->sensors.resize(idx + 1);
+    Sensor &s = c->sensors[idx];
+    s.V = V; s.H = H;
+    std::memcpy(s.q, q_wxyz, 16); std::memcpy(s.T, t_xyz, 12);
+    quat_to_rotation(s.q, s.R);
+    inverse3(s.R, s.Rinv);
+    // tables with the reference's narrowing: theta, phi are double expressions narrowed to float BEFORE the
+    // float sin/cos (SRC/LidarDevice.cpp:305-318); step = (end - begin) / (count - 1) (SRC/LidarDevice.cpp:611)
+    std::vector<float> tab(2 * (size_t)V + 2 * (size_t)H);
+    for (int v = 0; v < V; ++v) {
+        const float theta = (float)((90.0 - (double)elev_deg[v]) * M_PI / 180.0);
+        tab[v] = sinf(theta); tab[V + v] = cosf(theta);
+    }
+    const float step = (az_end - az_begin) / (float)((unsigned)H - 1u);
+    for (int h = 0; h < H; ++h) {
+        const float prePhi = az_begin + step * (float)h;
+        const float phi = (float)((double)prePhi * M_PI / 180.0);
+        tab[2 * V + h] = sinf(phi); tab[2 * V + H + h] = cosf(phi);
+    }
+    LSB_CU(c, s.tables.reserve(tab.size() * 4, c->stream));
+    LSB_CU(c, cudaMemcpyAsync(s.tables.p, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    LSB_CU(c, cudaStreamSynchronize(c->stream));     // tab is a local
+    s.set = true;
+    c->sensors_dirty = true;
+    if (idx == 0 && c->frame_mode == LSB200_FRAME_SENSOR) c->committed = false;   // scene lives in this sensor's frame
+    return LSB200_OK;
+}
+
+int lsb200_get_ray_count(const lsb200_ctx *c, int idx)
+{
+    if (!c || idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set) return LSB200_ERR_INVALID;
+    return c->sensors[idx].n_rays();
+}
+
+int lsb200_add_geometry(lsb200_ctx *c, const char *name, int type, int n_vertices, int n_elements)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (!name || n_vertices < 0 || n_elements < 0) return fail(c, LSB200_ERR_INVALID, "add_geometry: bad arguments");
+    if (type != LSB200_GEOMETRY_TRIANGLE && type != LSB200_GEOMETRY_QUAD)
+        return fail(c, LSB200_ERR_INVALID, "add_geometry: unsupported geometry type %d", type);
+    if (c->by_name.count(name)) return fail(c, LSB200_ERR_INVALID, "add_geometry: '%s' already exists", name);
+    int id = 0;
+    while (c->geoms.count(id)) ++id;           // lowest free id, like rtcAttachGeometry
+    Geometry &g = c->geoms[id];
+    g.name = name; g.id = id; g.type = type; g.n_verts = n_vertices; g.n_elems = n_elements;
+    g.verts_per_elem = (type == LSB200_GEOMETRY_QUAD) ? 4 : 3;
+    c->by_name[name] = id;
+    c->topology_dirty = true;
+    c->committed = false;
+    return id;
+}
+
+int lsb200_get_geometry_count(const lsb200_ctx *c) { return c ? (int)c->geoms.size() : LSB200_ERR_INVALID; }
+
+int lsb200_get_geometry_id(const lsb200_ctx *c, const char *name)
+{
+    if (!c || !name) return LSB200_ERR_INVALID;
+    auto it = c->by_name.find(name);
+    return it == c->by_name.end() ? -1 : it->second;
+}
+
+void lsb200_affine_from_components(const float t[3], const float r[3], float A[12])
+{
+    // Translation(t) * Rz * Ry * Rx  (SRC/MeshTransformer.cpp:467-477; Eigen AngleAxisf about the unit axes)
+    const float cx = cosf(r[0]), sx = sinf(r[0]), cy = cosf(r[1]), sy = sinf(r[1]), cz = cosf(r[2]), sz = sinf(r[2]);
+    const float Rx[9] = {1, 0, 0, 0, cx, -sx, 0, sx, cx};
+    const float Ry[9] = {cy, 0, sy, 0, 1, 0, -sy, 0, cy};
+    const float Rz[9] = {cz, -sz, 0, sz, cz, 0, 0, 0, 1};
+    float Rzy[9], L[9];
+    mat3_mul(Rz, Ry, Rzy);
+    mat3_mul(Rzy, Rx, L);
+    for (int i = 0; i < 3; ++i) { A[4 * i] = L[3 * i]; A[4 * i + 1] = L[3 * i + 1]; A[4 * i + 2] = L[3 * i + 2]; A[4 * i + 3] = t[i]; }
+}
+
+int lsb200_update_geometry(lsb200_ctx *c, const char *name, const void *verts, int stride, const uint32_t *elems,
+                           const float A[12])
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    Geometry *g = find_geom(c, name);
+    if (!g) return fail(c, LSB200_ERR_INVALID, "update_geometry: unknown geometry '%s'", name ? name : "(null)");
+    if (!A) return fail(c, LSB200_ERR_INVALID, "update_geometry: null transform");
+    DeviceGuard dg(c->device);
+    int rc = upload_geometry(c, *g, verts, stride, elems);
+    if (rc) return rc;
+    std::memcpy(g->A, A, sizeof(g->A));
+    return LSB200_OK;
+}
+
+int lsb200_update_geometry_euler(lsb200_ctx *c, const char *name, const void *verts, int stride, const uint32_t *elems,
+                                 const float t[3], const float r[3])
+{
+    if (!c || !t || !r) return LSB200_ERR_INVALID;
+    float A[12];
+    lsb200_affine_from_components(t, r, A);
+    return lsb200_update_geometry(c, name, verts, stride, elems, A);
+}
+
+int lsb200_update_transform(lsb200_ctx *c, const char *name, const float A[12])
+{
+    return lsb200_update_geometry(c, name, nullptr, 0, nullptr, A);
+}
+
+// ---- commit ----------------------------------------------------------------------------------------------
+static int commit_locked(lsb200_ctx *c, int mode)
+{
+    DeviceGuard dg(c->device);
+    int64_t nv = 0, nt = 0;
+    for (auto &kv : c->geoms) {
+        const Geometry &g = kv.second;
+        if (g.n_verts > 0 && g.n_tris() > 0 && !(g.has_verts && g.has_elems))
+            return fail(c, LSB200_ERR_STATE, "commit_scene: geometry '%s' was never given vertices/elements", g.name.c_str());
+        nv += g.n_verts; nt += g.n_tris();
+    }
+    if (c->geoms.empty() || nt == 0 || nv == 0) {
+        c->committed = false; c->n_tris = 0; c->n_verts = 0;
+        return fail(c, LSB200_ERR_EMPTY_SCENE, "commit_scene: empty scene");
+    }
+    if (nt >= (1 << kLeafShift) || nv >= (int64_t)1 << 31) return fail(c, LSB200_ERR_INVALID, "commit_scene: scene too large");
+    if (c->frame_mode == LSB200_FRAME_SENSOR && !c->sensors[0].set)
+        return fail(c, LSB200_ERR_STATE, "commit_scene: sensor 0 not set (sensor-frame mode)");
+    // a refit needs a hierarchy that was built for exactly this set of geometries
+    const bool rebuild = (mode == LSB200_COMMIT_REBUILD) || c->topology_dirty;
+    cudaStream_t st = c->stream;
+    c->n_verts = (int)nv; c->n_tris = (int)nt;
+    if (rebuild) { c->built_leaf = c->opt_leaf; c->built_top = c->opt_top; }
+
+    // geometry descriptor table (small pageable copy: staged by the runtime before the call returns)
+    const size_t ng = c->geoms.size();
+    c->h_geoms.resize(ng);
+    {
+        size_t k = 0; int voff = 0, toff = 0;
+        for (auto &kv : c->geoms) {
+            Geometry &g = kv.second;
+            GeomDesc &d = c->h_geoms[k++];
+            d.verts = g.verts.as<uint8_t>(); d.elems = g.elems.as<uint32_t>();
+            std::memcpy(d.A, g.A, sizeof(d.A));
+            d.stride = g.stride; d.verts_per_elem = g.verts_per_elem;
+            d.vert_off = voff; d.n_verts = g.n_verts; d.tri_off = toff; d.n_tris = g.n_tris();
+            voff += g.n_verts; toff += g.n_tris();
+        }
+    }
+    LSB_CU(c, c->d_geoms.reserve(ng * sizeof(GeomDesc), st));
+    LSB_CU(c, cudaMemcpyAsync(c->d_geoms.p, c->h_geoms.data(), ng * sizeof(GeomDesc), cudaMemcpyHostToDevice, st));
+
+    const size_t T = (size_t)nt;
+    LSB_CU(c, c->d_xverts.reserve((size_t)nv * sizeof(float4), st));
+    LSB_CU(c, c->d_tris.reserve(T * 48, st));
+    LSB_CU(c, c->d_leaf_ids.reserve(T * 4, st));
+    if (rebuild) {
+        LSB_CU(c, c->d_keys.reserve(T * 4, st)); LSB_CU(c, c->d_vals.reserve(T * 4, st));
+        LSB_CU(c, c->d_keys_tmp.reserve(T * 4, st)); LSB_CU(c, c->d_vals_tmp.reserve(T * 4, st));
+        LSB_CU(c, c->d_sort_scratch.reserve(rsort::scratch_words(nt) * 4, st));
+        LSB_CU(c, c->d_nodes.reserve(((size_t)c->built_top + T) * 64, st));
+        LSB_CU(c, c->d_node_parent.reserve(T * 4, st)); LSB_CU(c, c->d_leaf_parent.reserve(T * 4, st));
+        LSB_CU(c, c->d_flags.reserve(T * 4, st, false, true));
+    }
+    SceneDev S = scene_dev(c);
+    const bool timing = c->opt_timing != 0;
+    int evi = 0;
+    auto mark = [&]() { if (timing) cudaEventRecord(c->ev[evi++], st); };
+
+    // (1) transform + scene bounds
+    if (c->frame_mode == LSB200_FRAME_SENSOR) {
+        std::memcpy(c->h_xf, c->sensors[0].Rinv, 36); std::memcpy(c->h_xf + 9, c->sensors[0].T, 12);
+        LSB_CU(c, cudaMemcpyAsync(c->d_sensor_xf.p, c->h_xf, 48, cudaMemcpyHostToDevice, st));
+    }
+    LSB_CU(c, cudaMemsetAsync(S.bounds, 0xFF, 12, st));
+    LSB_CU(c, cudaMemsetAsync(S.bounds + 3, 0x00, 12, st));
+    mark();
+    k_transform<<<(unsigned)((nv + 255) / 256), 256, 0, st>>>(S, c->frame_mode == LSB200_FRAME_SENSOR, c->d_sensor_xf.as<float>());
+    count_launch(c);
+    mark();
+    if (rebuild) {
+        // (2) Morton codes  (3) radix sort  (4) Karras hierarchy
+        k_morton<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(S);
+        count_launch(c);
+        mark();
+        count_launch(c, rsort::sort_pairs(S.keys, S.vals, c->d_keys_tmp.as<uint32_t>(), c->d_vals_tmp.as<uint32_t>(), nt,
+                                          c->d_sort_scratch.as<uint32_t>(), st));
+        mark();
+        if (nt > 1) k_hierarchy<<<(unsigned)((nt - 1 + 255) / 256), 256, 0, st>>>(S, S.keys);
+        else k_single_leaf_root<<<1, 1, 0, st>>>(S);
+        count_launch(c);
+        mark();
+    }
+    // (5) leaf records + bottom-up boxes
+    k_fit<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(S, S.vals);
+    count_launch(c);
+    mark();
+    // (6) top-level block for the TMA-staged traversal
+    if (c->built_top > 0) {
+        k_top_level<<<1, 1024, (size_t)c->built_top * sizeof(int), st>>>(S, c->d_misc.as<int>());
+        count_launch(c);
+    }
+    mark();
+    LSB_CU(c, cudaGetLastError());
+    c->stats.last_commit_was_rebuild = rebuild ? 1 : 0;
+    if (timing) {
+        LSB_CU(c, cudaStreamSynchronize(st));
+        float ms = 0; int k = 0;
+        cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]); c->stats.ms_transform = ms; ++k;
+        if (rebuild) {
+            cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]); c->stats.ms_morton = ms; ++k;
+            cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]); c->stats.ms_sort = ms; ++k;
+            cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]); c->stats.ms_hierarchy = ms; ++k;
+        } else { c->stats.ms_morton = c->stats.ms_sort = c->stats.ms_hierarchy = 0; }
+        cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]); c->stats.ms_fit = ms; ++k;
+        cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]); c->stats.ms_toplevel = ms; ++k;
+    }
+    c->topology_dirty = false;
+    c->committed = true;
+    return LSB200_OK;
+}
+
+int lsb200_commit_scene(lsb200_ctx *c, int mode)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (mode < 0 || mode > 2) return fail(c, LSB200_ERR_INVALID, "commit_scene: bad mode %d", mode);
+    return commit_locked(c, mode);
+}
+
+int lsb200_remove_geometry(lsb200_ctx *c, const char *name)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    Geometry *g = find_geom(c, name);
+    if (!g) return fail(c, -1, "remove_geometry: unknown geometry '%s'", name ? name : "(null)");
+    DeviceGuard dg(c->device);
+    const int id = g->id;
+    cudaStreamSynchronize(c->stream);
+    g->verts.release(); g->elems.release();
+    c->by_name.erase(g->name);
+    c->geoms.erase(id);
+    c->topology_dirty = true;
+    c->committed = false;
+    // the reference re-commits inside removeGeometry (SRC/EmbreeTracer.cpp:252); an empty scene stays uncommitted
+    if (!c->geoms.empty()) {
+        bool ready = true;
+        for (auto &kv : c->geoms) ready = ready && kv.second.has_verts && kv.second.has_elems;
+        if (ready && (c->frame_mode == LSB200_FRAME_WORLD || c->sensors[0].set)) commit_locked(c, LSB200_COMMIT_REBUILD);
+    } else { c->n_tris = 0; c->n_verts = 0; }
+    return id;
+}
+
+}  // extern "C"
+
+// ---- trace -------------------------------------------------------------------------------------------------
+static size_t record_bytes(uint32_t flags) { return (flags & LSB200_TRACE_XYZI16) ? 16 : 32; }
+
+// (re)allocates the per-sensor result buffers of [first, first+count) and refreshes the device sensor table
+static int prepare_sensors(lsb200_ctx *c, int first, int count)
+{
+    cudaStream_t st = c->stream;
+    const size_t ns = c->sensors.size();
+    LSB_CU(c, c->d_counts.reserve(std::max<size_t>(ns, 16) * 4, st, true, true));
+    bool dirty = c->sensors_dirty || c->h_sensors.size() != ns;
+    for (int i = first; i < first + count; ++i) {
+        Sensor &s = c->sensors[i];
+        if (!s.set) return fail(c, LSB200_ERR_STATE, "trace: sensor %d not set", i);
+        const size_t R = (size_t)s.n_rays();
+        const size_t nblk = (R + kCompactRays - 1) / kCompactRays;
+        if (s.t.cap < R * 4 || s.tri.cap < R * 4 || s.points.cap < R * 32 || s.blocks.cap < nblk * 4) dirty = true;
+        LSB_CU(c, s.t.reserve(R * 4, st)); LSB_CU(c, s.tri.reserve(R * 4, st));
+        LSB_CU(c, s.points.reserve(R * 32, st)); LSB_CU(c, s.blocks.reserve(std::max<size_t>(nblk, 4) * 4, st));
+    }
+    if (!dirty) return 0;
+    c->h_sensors.assign(ns, SensorDev{});
+    int unit = 0;
+    for (size_t i = 0; i < ns; ++i) {
+        Sensor &s = c->sensors[i];
+        SensorDev &d = c->h_sensors[i];
+        d.unit_base = unit;
+        if (!s.set) continue;
+        const float *tab = s.tables.as<float>();
+        d.sin_t = tab; d.cos_t = tab + s.V; d.sin_p = tab + 2 * s.V; d.cos_p = tab + 2 * s.V + s.H;
+        std::memcpy(d.R, s.R, 36); std::memcpy(d.Rinv, s.Rinv, 36); std::memcpy(d.T, s.T, 12);
+        d.V = s.V; d.H = s.H; d.n_rays = s.n_rays();
+        d.t_out = s.t.as<float>(); d.tri_out = s.tri.as<int32_t>(); d.points = s.points.as<uint8_t>();
+        d.count = c->d_counts.as<uint32_t>() + i; d.block_counts = s.blocks.as<uint32_t>();
+        unit += (d.n_rays + 31) / 32;
+    }
+    LSB_CU(c, c->d_sensors.reserve(ns * sizeof(SensorDev), st));
+    LSB_CU(c, cudaMemcpyAsync(c->d_sensors.p, c->h_sensors.data(), ns * sizeof(SensorDev), cudaMemcpyHostToDevice, st));
+    c->sensors_dirty = false;
+    return 0;
+}
+
+template <int MODE>
+static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
+{
+    const size_t smem = (MODE == 0) ? (size_t)P.top_cap * 64 : 0;
+    static bool attr_set[4] = {false, false, false, false};
+    if (MODE == 0 && !attr_set[MODE]) {
+        LSB_CU(c, cudaFuncSetAttribute(k_trace<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set[MODE] = true;
+    }
+    int grid;
+    if (MODE == 2) {
+        grid = (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32);
+    } else {
+        int per_sm = c->opt_ctas_per_sm;
+        if (per_sm <= 0) LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<MODE>, kTraceThreads, smem));
+        if (per_sm <= 0) return fail(c, LSB200_ERR_CUDA, "trace kernel does not fit on an SM (smem %zu)", smem);
+        grid = c->sm_count * per_sm;
+        grid = std::min(grid, (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32));
+        grid = std::max(grid, 1);
+    }
+    k_trace<MODE><<<grid, kTraceThreads, smem, c->stream>>>(P);
+    c->stats.trace_grid = grid; c->stats.trace_block = kTraceThreads;
+    count_launch(c);
+    return 0;
+}
+
+static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags)
+{
+    if (first < 0 || count <= 0 || (size_t)(first + count) > c->sensors.size())
+        return fail(c, LSB200_ERR_INVALID, "trace: bad sensor range [%d, %d)", first, first + count);
+    if (c->frame_mode == LSB200_FRAME_SENSOR && (first != 0 || count != 1))
+        return fail(c, LSB200_ERR_INVALID, "trace: sensor-frame contexts hold exactly one sensor (index 0)");
+    DeviceGuard dg(c->device);
+    cudaStream_t st = c->stream;
+    if (int rc = prepare_sensors(c, first, count)) return rc;
+    if (c->geoms.empty() || c->n_tris == 0) {
+        // empty scene: an initialised, empty cloud and -1 (SRC/OptixTracer.cpp:279-288)
+        LSB_CU(c, cudaMemsetAsync(c->d_counts.as<uint32_t>() + first, 0, (size_t)count * 4, st));
+        for (int i = first; i < first + count; ++i) {
+            Sensor &s = c->sensors[i];
+            LSB_CU(c, cudaMemsetAsync(s.tri.p, 0xFF, (size_t)s.n_rays() * 4, st));          // -1
+            LSB_CU(c, cudaMemsetAsync(s.t.p, 0, (size_t)s.n_rays() * 4, st));
+        }
+        return fail(c, LSB200_ERR_EMPTY_SCENE, "trace_scene: empty scene");
+    }
+    if (!c->committed) return fail(c, LSB200_ERR_STATE, "trace_scene: scene not committed");
+    TraceParams P{};
+    P.nodes = c->d_nodes.as<float4>(); P.tris = c->d_tris.as<float4>(); P.leaf_ids = c->d_leaf_ids.as<int32_t>();
+    P.bounds = c->d_bounds.as<uint32_t>(); P.n_top = c->d_misc.as<int>();
+    P.sensors = c->d_sensors.as<SensorDev>() ; P.n_sensors = (int)c->sensors.size();
+    P.top_cap = c->built_top; P.n_tris = c->n_tris;
+    P.world_frame = c->frame_mode == LSB200_FRAME_WORLD;
+    P.flags = flags;
+    P.work = c->d_misc.as<uint32_t>() + 4;
+    // work units of the batch: [unit_base(first), unit_base(last) + units(last))
+    const int unit_lo = c->h_sensors[first].unit_base;
+    const SensorDev &last = c->h_sensors[first + count - 1];
+    const int unit_hi = last.unit_base + (last.n_rays + 31) / 32;
+    P.unit_lo = unit_lo; P.n_units = unit_hi;
+    const bool timing = c->opt_timing != 0;
+    const bool unordered_points = !(flags & (LSB200_TRACE_ORDERED | LSB200_TRACE_NO_POINTS));
+    if (unordered_points) LSB_CU(c, cudaMemsetAsync(c->d_counts.as<uint32_t>() + first, 0, (size_t)count * 4, st));
+    if (timing) cudaEventRecord(c->ev[8], st);
+    int mode = c->opt_traversal;
+    if (mode == 0 && c->built_top == 0) mode = 1;
+    int rc = 0;
+    const int n_units = unit_hi - unit_lo;
+    switch (mode) {
+    case 0: rc = launch_trace<0>(c, P, n_units); break;
+    case 1: rc = launch_trace<1>(c, P, n_units); break;
+    case 2: rc = launch_trace<2>(c, P, n_units); break;
+    default: rc = launch_trace<3>(c, P, n_units); break;
+    }
+    if (rc) return rc;
+    if (timing) cudaEventRecord(c->ev[9], st);
+    if ((flags & LSB200_TRACE_ORDERED) && !(flags & LSB200_TRACE_NO_POINTS)) {
+        int max_rays = 0;
+        for (int i = first; i < first + count; ++i) max_rays = std::max(max_rays, c->sensors[i].n_rays());
+        dim3 grid((unsigned)((max_rays + kCompactRays - 1) / kCompactRays), (unsigned)count);
+        const SensorDev *sd = c->d_sensors.as<SensorDev>();
+        k_count_hits<<<grid, kCompactThreads, 0, st>>>(sd, first);
+        k_scan_counts<<<count, 256, 0, st>>>(sd, first);
+        k_scatter_hits<<<grid, kCompactThreads, 0, st>>>(sd, first, flags);
+        count_launch(c, 3);
+    }
+    if (timing) {
+        cudaEventRecord(c->ev[10], st);
+        LSB_CU(c, cudaStreamSynchronize(st));
+        cudaEventElapsedTime(&c->stats.ms_trace, c->ev[8], c->ev[9]);
+        cudaEventElapsedTime(&c->stats.ms_compact, c->ev[9], c->ev[10]);
+    }
+    LSB_CU(c, cudaGetLastError());
+    return LSB200_OK;
+}
+
+static int fetch_locked(lsb200_ctx *c, int idx, void *out, size_t capacity, uint32_t *n_pts, uint32_t flags)
+{
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set) return fail(c, LSB200_ERR_INVALID, "fetch: bad sensor %d", idx);
+    if (!c->d_counts.p || !c->sensors[idx].points.p) return fail(c, LSB200_ERR_STATE, "fetch: sensor %d was never traced", idx);
+    DeviceGuard dg(c->device);
+    cudaStream_t st = c->stream;
+    LSB_CU(c, cudaMemcpyAsync(c->h_count, c->d_counts.as<uint32_t>() + idx, 4, cudaMemcpyDeviceToHost, st));
+    LSB_CU(c, cudaStreamSynchronize(st));
+    const uint32_t n = c->h_count[0];
+    if (n_pts) *n_pts = n;
+    const size_t ncopy = std::min<size_t>(n, capacity);
+    if (out && ncopy) {
+        LSB_CU(c, cudaMemcpyAsync(out, c->sensors[idx].points.p, ncopy * record_bytes(flags), cudaMemcpyDeviceToHost, st));
+        LSB_CU(c, cudaStreamSynchronize(st));
+    }
+    if (n > capacity && out) return fail(c, LSB200_ERR_CAPACITY, "fetch: %u points, capacity %zu", n, capacity);
+    return LSB200_OK;
+}
+
+extern "C" {
+
+int lsb200_trace_device(lsb200_ctx *c, int idx, uint32_t flags)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    return trace_locked(c, idx, 1, flags);
+}
+
+int lsb200_trace_batch(lsb200_ctx *c, int first, int count, uint32_t flags)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    return trace_locked(c, first, count, flags);
+}
+
+int lsb200_trace_scene(lsb200_ctx *c, int idx, uint32_t frame, void *out, size_t capacity, uint32_t *n_pts, uint32_t flags)
+{
+    (void)frame;     // the frame index only goes into the PointCloud2 header (lsb200_init_message)
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (n_pts) *n_pts = 0;
+    flags &= ~(uint32_t)LSB200_TRACE_NO_POINTS;
+    int rc = trace_locked(c, idx, 1, flags);
+    if (rc) return rc;
+    return fetch_locked(c, idx, out, capacity, n_pts, flags);
+}
+
+int lsb200_fetch_points(lsb200_ctx *c, int idx, void *out, size_t capacity, uint32_t *n_pts, uint32_t flags)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    return fetch_locked(c, idx, out, capacity, n_pts, flags);
+}
+
+int lsb200_trace_raw(lsb200_ctx *c, int idx, float *t_out, int32_t *tri_out)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    int rc = trace_locked(c, idx, 1, LSB200_TRACE_NO_POINTS);
+    if (rc && rc != LSB200_ERR_EMPTY_SCENE) return rc;
+    DeviceGuard dg(c->device);
+    Sensor &s = c->sensors[idx];
+    const size_t R = (size_t)s.n_rays();
+    if (rc == LSB200_ERR_EMPTY_SCENE) {
+        for (size_t i = 0; i < R; ++i) { if (t_out) t_out[i] = INFINITY; if (tri_out) tri_out[i] = -1; }
+        return rc;
+    }
+    if (t_out) LSB_CU(c, cudaMemcpyAsync(t_out, s.t.p, R * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (tri_out) LSB_CU(c, cudaMemcpyAsync(tri_out, s.tri.p, R * 4, cudaMemcpyDeviceToHost, c->stream));
+    LSB_CU(c, cudaStreamSynchronize(c->stream));
+    return LSB200_OK;
+}
+
+int lsb200_device_results(lsb200_ctx *c, int idx, void **d_points, uint32_t **d_count, float **d_t, int32_t **d_tri)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set) return fail(c, LSB200_ERR_INVALID, "bad sensor %d", idx);
+    Sensor &s = c->sensors[idx];
+    if (d_points) *d_points = s.points.p;
+    if (d_count) *d_count = c->d_counts.p ? c->d_counts.as<uint32_t>() + idx : nullptr;
+    if (d_t) *d_t = s.t.as<float>();
+    if (d_tri) *d_tri = s.tri.as<int32_t>();
+    return LSB200_OK;
+}
+
+int lsb200_synchronize(lsb200_ctx *c)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    DeviceGuard dg(c->device);
+    LSB_CU(c, cudaStreamSynchronize(c->stream));
+    return LSB200_OK;
+}
+
+int lsb200_init_message(const lsb200_ctx *c, uint32_t frame, lsb200_cloud_header *h)
+{
+    if (!c || !h) return LSB200_ERR_INVALID;
+    std::memset(h, 0, sizeof(*h));
+    h->seq = frame; h->height = 1; h->width = 0; h->point_step = 32; h->row_step = 0;
+    h->is_bigendian = 0; h->is_dense = 1; h->n_fields = 5;
+    return LSB200_OK;
+}
+
+int lsb200_get_stats(lsb200_ctx *c, lsb200_stats *out)
+{
+    if (!c || !out) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    DeviceGuard dg(c->device);
+    c->stats.n_vertices = c->n_verts; c->stats.n_triangles = c->n_tris;
+    c->stats.n_nodes = c->n_tris > 0 ? std::max(c->n_tris - 1, 1) : 0;
+    c->stats.n_leaves = c->n_tris;
+    c->stats.top_nodes = 0;
+    if (c->committed) {
+        uint32_t b[6]; int ntop = 0;
+        LSB_CU(c, cudaMemcpyAsync(b, c->d_bounds.p, 24, cudaMemcpyDeviceToHost, c->stream));
+        LSB_CU(c, cudaMemcpyAsync(&ntop, c->d_misc.p, 4, cudaMemcpyDeviceToHost, c->stream));
+        LSB_CU(c, cudaStreamSynchronize(c->stream));
+        for (int k = 0; k < 3; ++k) { c->stats.scene_lo[k] = ord2f(b[k]); c->stats.scene_hi[k] = ord2f(b[3 + k]); }
+        c->stats.top_nodes = c->built_top > 0 ? ntop : 0;
+    }
+    *out = c->stats;
+    return LSB200_OK;
+}
+
+int lsb200_reset_counters(lsb200_ctx *c)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    c->stats.kernel_launches = 0;
+    return LSB200_OK;
+}
+
+int lsb200_debug_copy_bvh(lsb200_ctx *c, float *nodes16, int64_t node_cap, int32_t *leaf_ids, int64_t tri_cap, int32_t *root)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (!c->committed) return fail(c, LSB200_ERR_STATE, "debug_copy_bvh: not committed");
+    DeviceGuard dg(c->device);
+    const int64_t nn = std::max(c->n_tris - 1, 1);
+    if (nodes16) {
+        if (node_cap < nn) return fail(c, LSB200_ERR_CAPACITY, "debug_copy_bvh: need %lld nodes", (long long)nn);
+        LSB_CU(c, cudaMemcpyAsync(nodes16, c->d_nodes.as<float4>() + 4 * (size_t)c->built_top, (size_t)nn * 64, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (leaf_ids) {
+        if (tri_cap < c->n_tris) return fail(c, LSB200_ERR_CAPACITY, "debug_copy_bvh: need %d ids", c->n_tris);
+        LSB_CU(c, cudaMemcpyAsync(leaf_ids, c->d_leaf_ids.p, (size_t)c->n_tris * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
+    LSB_CU(c, cudaStreamSynchronize(c->stream));
+    if (root) *root = c->built_top;     // unified index of Karras node 0; child refs >= top_cap are (ref - top_cap)
+    return LSB200_OK;
+}
+
+int lsb200_debug_sort_pairs(lsb200_ctx *c, uint32_t *keys, uint32_t *vals, int64_t n)
+{
+    if (!c || !keys || !vals || n < 0) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (n == 0) return LSB200_OK;
+    DeviceGuard dg(c->device);
+    DevBuf k, v, kt, vt, sc;
+    cudaStream_t st = c->stream;
+    int rc = LSB200_OK;
+    auto body = [&]() -> int {
+        LSB_CU(c, k.reserve(n * 4, st)); LSB_CU(c, v.reserve(n * 4, st)); LSB_CU(c, kt.reserve(n * 4, st));
+        LSB_CU(c, vt.reserve(n * 4, st)); LSB_CU(c, sc.reserve(rsort::scratch_words(n) * 4, st));
+        LSB_CU(c, cudaMemcpyAsync(k.p, keys, n * 4, cudaMemcpyHostToDevice, st));
+        LSB_CU(c, cudaMemcpyAsync(v.p, vals, n * 4, cudaMemcpyHostToDevice, st));
+        count_launch(c, rsort::sort_pairs(k.as<uint32_t>(), v.as<uint32_t>(), kt.as<uint32_t>(), vt.as<uint32_t>(), n, sc.as<uint32_t>(), st));
+        LSB_CU(c, cudaMemcpyAsync(keys, k.p, n * 4, cudaMemcpyDeviceToHost, st));
+        LSB_CU(c, cudaMemcpyAsync(vals, v.p, n * 4, cudaMemcpyDeviceToHost, st));
+        LSB_CU(c, cudaStreamSynchronize(st));
+        LSB_CU(c, cudaGetLastError());
+        return LSB200_OK;
+    };
+    rc = body();
+    cudaStreamSynchronize(st);
+    k.release(); v.release(); kt.release(); vt.release(); sc.release();
+    return rc;
+}
+
+int lsb200_debug_copy_vertices(lsb200_ctx *c, float *xyz, int64_t cap)
+{
+    if (!c || !xyz) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (!c->committed) return fail(c, LSB200_ERR_STATE, "debug_copy_vertices: not committed");
+    if (cap < c->n_verts) return fail(c, LSB200_ERR_CAPACITY, "debug_copy_vertices: need %d", c->n_verts);
+    DeviceGuard dg(c->device);
+    std::vector<float> tmp((size_t)c->n_verts * 4);
+    LSB_CU(c, cudaMemcpyAsync(tmp.data(), c->d_xverts.p, tmp.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+    LSB_CU(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < c->n_verts; ++i) { xyz[3 * i] = tmp[4 * i]; xyz[3 * i + 1] = tmp[4 * i + 1]; xyz[3 * i + 2] = tmp[4 * i + 2]; }
+    return LSB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,305 @@
+"""GPU parity: the CUDA path, called through the C ABI (include/lsb200.h), against the CPU oracle.
+
+Bar (BASELINE.json north_star): hit/miss mask and triangle id bit-exact, range within 1e-4 relative.  The CUDA
+kernels use the oracle's operation order without FMA contraction, so these tests demand MORE: t bit-exact too.
+Reference pins: 1668 / 1781 / 0 points (SRC/test/EmbreeTracer_test.cpp:134, SRC/test/OptixTracer_test.cpp:168,307).
+"""
+import numpy as np
+import pytest
+
+from conftest import xt32_sensor_args
+from lidarshooter_b200 import capi, synth
+from oracle import lso
+
+pytestmark = pytest.mark.gpu
+
+IDENT = lso.IDENTITY_AFFINE
+
+
+def make_ctx(uid="0000", frame_mode=capi.FRAME_SENSOR, **opts):
+    ctx = capi.Context(0, frame_mode)
+    for k, v in opts.items():
+        ctx.set_option(k, v)
+    elev, b, e, H, q, t = xt32_sensor_args(uid)
+    ctx.set_sensor(elev, b, e, H, q, t)
+    return ctx
+
+
+def add_mesh(ctx, name, v, t, A=IDENT):
+    gid = ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0])
+    assert gid >= 0
+    assert ctx.update_geometry(name, v, t, A) == 0
+    return gid
+
+
+def sort_rows(p):
+    """Canonical order of a point set: lexicographic over the raw 32-bit words."""
+    w = np.ascontiguousarray(p).view(np.uint32).reshape(p.shape[0], -1)
+    return p[np.lexsort(w.T[::-1])]
+
+
+@pytest.mark.parametrize("uid,n_ground,n_both", [("0000", 1668, 1781), ("0001", 1633, 1769)])
+def test_xt32_reference_counts_and_golden(meshes, golden, uid, n_ground, n_both):
+    ctx = make_ctx(uid)
+    add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
+    assert ctx.commit_scene() == 0
+    rc, pts = ctx.trace_scene(0, capi.TRACE_ORDERED)
+    assert rc == 0 and pts.shape == (n_ground, 32)
+    rc, t, tri = ctx.trace_raw()
+    assert rc == 0
+    assert np.array_equal(tri, golden[f"l{uid}_ground_tri"])
+    assert np.array_equal(t, golden[f"l{uid}_ground_t"])
+
+    add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
+    assert ctx.commit_scene() == 0
+    rc, t, tri = ctx.trace_raw()
+    assert np.array_equal(tri, golden[f"l{uid}_ground_ben_tri"])
+    assert np.array_equal(t, golden[f"l{uid}_ground_ben_t"])
+    rc, pts = ctx.trace_scene(1, capi.TRACE_ORDERED)
+    assert rc == 0 and pts.shape[0] == n_both
+
+    # oracle on the same inputs: packed points byte-identical in ray order; default (atomic) order is a permutation
+    s = lso.Sensor(*xt32_sensor_args(uid))
+    ref = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)])
+    assert np.array_equal(pts, ref["points"])
+    rc, pts_u = ctx.trace_scene(2, 0)
+    assert rc == 0 and pts_u.shape[0] == n_both
+    assert np.array_equal(sort_rows(pts_u), sort_rows(ref["points"]))
+    # Embree-path quirk: ring 0 (SRC/EmbreeTracer.cpp:333-334)
+    rc, pts0 = ctx.trace_scene(3, capi.TRACE_ORDERED | capi.TRACE_RING_ZERO)
+    ref0 = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)], ring_mode=1)
+    assert np.array_equal(pts0, ref0["points"])
+    # 16-byte XYZI records
+    rc, p16 = ctx.trace_scene(4, capi.TRACE_ORDERED | capi.TRACE_XYZI16)
+    f = ref["points"].view(np.float32).reshape(-1, 8)
+    assert np.array_equal(p16.view(np.float32).reshape(-1, 4), f[:, [0, 1, 2, 4]])
+
+    # remove ben -> back to the ground-only count (SRC/test/OptixTracer_test.cpp:217-290)
+    assert ctx.remove_geometry("ben") == 1
+    assert ctx.geometry_count() == 1
+    rc, pts = ctx.trace_scene(5, capi.TRACE_ORDERED)
+    assert rc == 0 and pts.shape[0] == n_ground
+    # remove the last one -> empty scene: -1 and an empty cloud (SRC/test/OptixTracer_test.cpp:297-310)
+    assert ctx.remove_geometry("ground") == 0
+    assert ctx.geometry_count() == 0
+    assert ctx.commit_scene() == -1
+    rc, pts = ctx.trace_scene(6, 0)
+    assert rc == -1 and pts.shape[0] == 0
+    assert ctx.remove_geometry("nope") == -1
+    ctx.close()
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("leaf", [1, 4, 8])
+def test_traversal_variants_agree(meshes, golden, mode, leaf):
+    ctx = make_ctx("0000", **{capi.OPT_TRAVERSAL: mode, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TOP_NODES: 256})
+    add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
+    add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
+    assert ctx.commit_scene() == 0
+    rc, t, tri = ctx.trace_raw()
+    assert rc == 0
+    assert np.array_equal(tri, golden["l0000_ground_ben_tri"])
+    assert np.array_equal(t, golden["l0000_ground_ben_t"])
+    ctx.close()
+
+
+def test_transform_bit_exact_and_refit(meshes):
+    """updateGeometry with translation + Euler angles (SRC/MeshTransformer.cpp:467-477), rebuild vs refit."""
+    s = lso.Sensor(*xt32_sensor_args("0000"))
+    ctx = make_ctx("0000")
+    add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
+    add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
+    poses = synth.trajectory_poses([(1.0, (0, 5, 0), (0, 0, 1)), (0.5, (1, 0, 0), (0.3, -0.2, -1))])
+    for k, (lin, ang) in enumerate(poses):
+        A = lso.affine_from_components(lin, ang)
+        assert np.array_equal(A, capi.affine_from_components(lin, ang))
+        assert ctx.update_geometry_euler("ben", None, None, lin, ang) == 0
+        assert ctx.commit_scene(capi.COMMIT_AUTO) == 0
+        st = ctx.stats()
+        assert st.last_commit_was_rebuild == (1 if k == 0 else 0)
+        ref = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], A)])
+        if k in (0, 7, 14):
+            assert np.array_equal(ctx.debug_copy_vertices(), ref["verts"])
+        rc, t, tri = ctx.trace_raw()
+        assert rc == 0
+        assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+    # a forced rebuild gives the same answers as the refitted tree
+    assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
+    rc, t2, tri2 = ctx.trace_raw()
+    assert np.array_equal(tri2, tri) and np.array_equal(t2, t)
+    ctx.close()
+
+
+def test_strided_vertex_blob_and_quads():
+    """pcl::PCLPointCloud2 blobs carry point_step bytes per vertex; quads are split (v0 v1 v3), (v2 v3 v1)."""
+    rng = np.random.default_rng(3)
+    n = 40
+    xs, ys = np.meshgrid(np.linspace(-30, 30, n + 1), np.linspace(-30, 30, n + 1), indexing="xy")
+    v = np.stack([xs, ys, rng.normal(-2.0, 0.3, xs.shape)], -1).reshape(-1, 3).astype(np.float32)
+    i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="xy")
+    v00 = (j * (n + 1) + i).astype(np.uint32)
+    quads = np.stack([v00, v00 + 1, v00 + n + 2, v00 + n + 1], -1).reshape(-1, 4)
+    tris = np.stack([quads[:, [0, 1, 3]], quads[:, [2, 3, 1]]], 1).reshape(-1, 3)
+    blob = np.zeros((v.shape[0], 8), np.float32)
+    blob[:, :3] = v
+    blob[:, 3:] = 7.0
+    elev, b, e, H = synth.XT32_ELEV, 0.0, 360.0, 150
+    ctx = capi.Context(0)
+    ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), (0, 0, 0))
+    assert ctx.add_geometry("q", capi.GEOMETRY_QUAD, v.shape[0], quads.shape[0]) == 0
+    assert ctx.add_geometry("bad", 24, 3, 1) < 0                      # unsupported RTCGeometryType
+    assert ctx.update_geometry("q", blob.view(np.uint8), quads, IDENT, stride=32) == 0
+    assert ctx.commit_scene() == 0
+    rc, t, tri = ctx.trace_raw()
+    s = lso.Sensor(elev, b, e, H)
+    ref = lso.scan(s, [(v, tris, IDENT)])
+    assert (ref["tri"] >= 0).sum() > 500
+    assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+    ctx.close()
+
+
+def test_world_frame_multi_sensor(meshes):
+    """World-frame mode: one BVH, rays moved (o = T, d = R d_s); bit-exact against the oracle in the same mode."""
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    sens = []
+    for k, uid in enumerate(("0000", "0001")):
+        args = xt32_sensor_args(uid)
+        ctx.set_sensor(*args, index=k)
+        sens.append(lso.Sensor(*args))
+    add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
+    add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
+    assert ctx.commit_scene() == 0
+    assert ctx.trace_batch(0, 2, capi.TRACE_ORDERED) == 0
+    for k in range(2):
+        ref = lso.scan(sens[k], [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)], mode=1)
+        rc, pts = ctx.fetch_points(k, capi.TRACE_ORDERED)
+        assert rc == 0
+        assert np.array_equal(pts, ref["points"])
+        rc, t, tri = ctx.trace_raw(k)
+        assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+    ctx.close()
+
+
+@pytest.mark.parametrize("n_tris", [1, 2, 3, 5, 1000, 20000])
+def test_random_soup_vs_brute(n_tris):
+    rng = np.random.default_rng(n_tris)
+    c = rng.uniform(-20, 20, (n_tris, 1, 3)).astype(np.float32)
+    v = (c + rng.normal(0, 0.7, (n_tris, 3, 3)).astype(np.float32)).reshape(-1, 3)
+    tr = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
+    elev = np.linspace(80, -80, 64).astype(np.float32)
+    ctx = capi.Context(0)
+    ctx.set_sensor(elev, 0.0, 360.0, 181, (1, 0, 0, 0), (0, 0, 0))
+    add_mesh(ctx, "soup", v, tr)
+    assert ctx.commit_scene() == 0
+    rc, t, tri = ctx.trace_raw()
+    s = lso.Sensor(elev, 0.0, 360.0, 181)
+    ref = lso.scan(s, [(v, tr, IDENT)], use_bvh=False)
+    assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+    ctx.close()
+
+
+def test_duplicate_and_degenerate_triangles():
+    """Coincident triangles (equal t): the smaller global id wins; zero-area triangles never hit."""
+    v = np.array([[5, -1, -1], [5, 1, -1], [5, 0, 1], [6, 0, 0], [6, 0, 0], [6, 0, 0]], np.float32)
+    tr = np.array([[0, 1, 2], [3, 4, 5], [0, 1, 2], [2, 1, 0]], np.uint32)
+    ctx = capi.Context(0)
+    ctx.set_sensor(np.array([0.0], np.float32), -10.0, 10.0, 21, (1, 0, 0, 0), (0, 0, 0))
+    add_mesh(ctx, "m", v, tr)
+    assert ctx.commit_scene() == 0
+    rc, t, tri = ctx.trace_raw()
+    s = lso.Sensor(np.array([0.0], np.float32), -10.0, 10.0, 21)
+    ref = lso.scan(s, [(v, tr, IDENT)], use_bvh=False)
+    assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+    assert set(np.unique(tri)) <= {-1, 0}
+    ctx.close()
+
+
+@pytest.mark.parametrize("n", [0, 1, 255, 4096, 4097, 100_000, 3_000_001])
+def test_radix_sort_pairs(n):
+    rng = np.random.default_rng(n + 1)
+    keys = rng.integers(0, 1 << 30, n, dtype=np.uint32)
+    if n > 1000:
+        keys[: n // 3] &= np.uint32(0x3FF)          # long runs of equal high digits + duplicates
+    vals = np.arange(n, dtype=np.uint32)
+    ctx = capi.Context(0)
+    k, v = ctx.debug_sort_pairs(keys, vals)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(k, keys[order])
+    assert np.array_equal(v, vals[order])           # stable
+    ctx.close()
+
+
+def test_full_32bit_keys_sort():
+    rng = np.random.default_rng(9)
+    keys = rng.integers(0, 1 << 32, 50_000, dtype=np.uint64).astype(np.uint32)
+    keys[:100] = 0xFFFFFFFF
+    vals = np.arange(keys.size, dtype=np.uint32)
+    ctx = capi.Context(0)
+    k, v = ctx.debug_sort_pairs(keys, vals)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(k, keys[order]) and np.array_equal(v, vals[order])
+    ctx.close()
+
+
+def test_bvh_structure(meshes):
+    """Every triangle is referenced by exactly one leaf; child boxes contain their triangles."""
+    ctx = make_ctx("0000", **{capi.OPT_LEAF_SIZE: 4})
+    add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
+    add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
+    assert ctx.commit_scene() == 0
+    nodes, ids, root = ctx.debug_copy_bvh()
+    nT = ids.size
+    assert sorted(ids.tolist()) == list(range(nT))
+    xv = ctx.debug_copy_vertices()
+    s = lso.Sensor(*xt32_sensor_args("0000"))
+    gv, gt = lso.concat_scene(s, [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)])
+    assert np.array_equal(xv, gv)
+    tri_lo = gv[gt].min(1)[ids]          # leaf order
+    tri_hi = gv[gt].max(1)[ids]
+    child = nodes[:, 12:14].view(np.int32)
+    seen = np.zeros(nT, np.int32)
+    stack = [0]
+    visited = 0
+    while stack:
+        k = stack.pop()
+        visited += 1
+        n = nodes[k]
+        boxes = [((n[0], n[2], n[8]), (n[1], n[3], n[9])), ((n[4], n[6], n[10]), (n[5], n[7], n[11]))]
+        for sl in range(2):
+            c = int(child[k, sl])
+            lo, hi = np.array(boxes[sl][0]), np.array(boxes[sl][1])
+            if c < 0:
+                enc = ~c
+                first, cnt = enc & ((1 << 28) - 1), (enc >> 28) + 1
+                assert cnt <= 4
+                seen[first:first + cnt] += 1
+                assert (tri_lo[first:first + cnt] >= lo).all() and (tri_hi[first:first + cnt] <= hi).all()
+            else:
+                stack.append(c - root)
+    assert (seen == 1).all()
+    assert visited < nT
+    ctx.close()
+
+
+def test_heightfield_1m_tris_vs_oracle_bvh():
+    """BASELINE config 3: 128 channels x 3601 azimuth steps against the 1M-triangle heightfield."""
+    v, tr = synth.heightfield()
+    assert tr.shape[0] == 1_000_000 and v.shape[0] == 501_501
+    elev, b, e, H = synth.lidar_table()
+    T = (0.0, 0.0, 4.0)
+    ctx = capi.Context(0)
+    ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), T)
+    add_mesh(ctx, "terrain", v, tr)
+    assert ctx.commit_scene() == 0
+    rc, t, tri = ctx.trace_raw()
+    assert rc == 0
+    s = lso.Sensor(elev, b, e, H, (1, 0, 0, 0), T)
+    ref = lso.scan(s, [(v, tr, IDENT)], use_bvh=True)
+    n_hit = int((ref["tri"] >= 0).sum())
+    assert n_hit > 200_000
+    mism = int((tri != ref["tri"]).sum())
+    assert mism == 0, f"{mism} rays differ in triangle id"
+    assert np.array_equal(t, ref["t"])
+    rc, pts = ctx.trace_scene(0, 0)
+    assert pts.shape[0] == n_hit
+    ctx.close()
