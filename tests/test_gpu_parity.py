@@ -16,9 +16,9 @@ pytestmark = pytest.mark.gpu
 IDENT = lso.IDENTITY_AFFINE
 
 
-def make_ctx(uid="0000", frame_mode=capi.FRAME_SENSOR, **opts):
+def make_ctx(uid="0000", frame_mode=capi.FRAME_SENSOR, opts=None):
     ctx = capi.Context(0, frame_mode)
-    for k, v in opts.items():
+    for k, v in (opts or {}).items():
         ctx.set_option(k, v)
     elev, b, e, H, q, t = xt32_sensor_args(uid)
     ctx.set_sensor(elev, b, e, H, q, t)
@@ -92,7 +92,7 @@ def test_xt32_reference_counts_and_golden(meshes, golden, uid, n_ground, n_both)
 @pytest.mark.parametrize("mode", [0, 1, 2, 3])
 @pytest.mark.parametrize("leaf", [1, 4, 8])
 def test_traversal_variants_agree(meshes, golden, mode, leaf):
-    ctx = make_ctx("0000", **{capi.OPT_TRAVERSAL: mode, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TOP_NODES: 256})
+    ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: mode, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TOP_NODES: 256})
     add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
     add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
     assert ctx.commit_scene() == 0
@@ -243,7 +243,7 @@ def test_full_32bit_keys_sort():
 
 def test_bvh_structure(meshes):
     """Every triangle is referenced by exactly one leaf; child boxes contain their triangles."""
-    ctx = make_ctx("0000", **{capi.OPT_LEAF_SIZE: 4})
+    ctx = make_ctx("0000", opts={capi.OPT_LEAF_SIZE: 4})
     add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
     add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
     assert ctx.commit_scene() == 0
