@@ -1,0 +1,414 @@
+#!/usr/bin/env python
+"""bench.py -- the trace-path benchmark of lidarshooter-b200 (contract: see DESIGN.md "Measurement").
+
+Workload (BASELINE.json configs[3], the configuration the metric is quoted on): the synthetic 10 M-triangle city,
+64 LiDAR devices (128 channels x 3601 azimuth steps = 460 928 rays each, 29.5 M rays per frame), world-frame mode.
+One STEP = one frame on every rank: per-geometry affine update -> vertex transform -> full LBVH rebuild (Morton,
+radix sort, Karras, AABB fit, top-level block) -> closest-hit trace of all 64 devices in one launch -> stream
+compaction into 32-byte PointCloud2 records.  Ranks shard the trajectory FRAMES (rank r works on frame
+step * N + r); the scene is replicated per GPU and there is no data-path collective ("scaling": "weak").
+
+  value      Mrays/s, whole job, inputs resident in HBM, device-timed (CUDA events on the launching stream)
+  e2e        the same through the C ABI with HOST buffers: H2D of every mesh's vertices from pinned memory and D2H
+             of every device's point cloud inside the timed region
+  roofline   the traversal kernel against the measured HBM peak, algorithmic bytes per SURVEY.md section 8(d)
+  cpu_baseline / --impl reference   the CPU oracle (oracle/, a port: Embree is not installable here) on the host cores
+
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_SENSORS = 64
+METRIC = "Mrays/s (10M-tri city, 64 devices x 460928 rays, per-frame rebuild + trace + compaction)"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def b_ray(n_tris, hit_fraction):
+    """Algorithmic bytes per ray: one root-to-leaf path of 64-B nodes + one 48-B triangle + output."""
+    return 64.0 * math.ceil(math.log2(max(n_tris, 2))) + 48.0 + 32.0 * hit_fraction
+
+
+def build_workload(small=False):
+    from lidarshooter_b200 import synth
+    if small:
+        meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
+        poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
+        table = synth.lidar_table(32, 361)
+    else:
+        meshes = synth.city()
+        poses = synth.sensor_lattice(8)
+        table = synth.lidar_table()
+    return meshes, poses, table
+
+
+def frame_affine(frame, gi):
+    """Per-frame rigid motion of geometry gi (buildings sway by centimetres so that every frame is new work)."""
+    A = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], np.float32)
+    if gi > 0:
+        A[3] = np.float32(0.05 * math.sin(0.37 * frame + gi))
+        A[7] = np.float32(0.05 * math.cos(0.23 * frame + 2 * gi))
+    return A
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.thread = [], None, None
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ts, line in self.rows:
+            if ts < t0 - 0.05 or ts > t1 + 0.15:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except Exception:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:      # region shorter than one sample: take whatever was seen
+            for ts, line in self.rows[-3:]:
+                f = [x.strip() for x in line.split(",")]
+                try:
+                    sm.append(float(f[0])); mx.append(float(f[1]))
+                except Exception:
+                    pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_trace_sample(meshes, poses, table, n_threads=None, sensors=(0,), repeats=1):
+    """The CPU oracle on the host cores: world-frame transform + binned-SAH BVH build once, then closest-hit trace of
+    the rays of `sensors`.  Returns dict(mrays_trace, t_build, t_trace, rays, cores)."""
+    from oracle import lso
+    lso.build()
+    if n_threads:
+        lso.set_threads(n_threads)
+    cores = lso.max_threads()
+    elev, b, e, H = table
+    t0 = time.perf_counter()
+    ident = lso.IDENTITY_AFFINE
+    s0 = lso.Sensor(elev, b, e, H, poses[0][0], poses[0][1])
+    verts, tris = lso.concat_scene(s0, [(v, t, ident) for _, v, t in meshes], mode=1)
+    t1 = time.perf_counter()
+    bvh = lso.Bvh(verts, tris)
+    t2 = time.perf_counter()
+    rays, t_trace, hits = 0, 0.0, 0
+    for _ in range(repeats):
+        for si in sensors:
+            s = lso.Sensor(elev, b, e, H, poses[si][0], poses[si][1])
+            dirs = lso.rotate_dirs(s.R, lso.ray_dirs(s.tables))
+            ta = time.perf_counter()
+            t, tri = bvh.trace(s.T, dirs)
+            t_trace += time.perf_counter() - ta
+            rays += dirs.shape[0]
+            hits += int((tri >= 0).sum())
+    bvh.close()
+    return {"mrays_trace": rays / t_trace / 1e6, "t_transform": t1 - t0, "t_build": t2 - t1, "t_trace": t_trace,
+            "rays": rays, "hits": hits, "cores": cores, "n_tris": int(tris.shape[0])}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm for the path.  Embree 3.13.4 (the reference's intersector) is
+    a closed binary that is neither in /root/reference nor installable here, so this is the oracle PORT (oracle/),
+    all host threads.  Each step traces one device's 460 928 rays against the 10 M-triangle CPU BVH."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import lso
+    lso.build()
+    meshes, poses, table = build_workload(args.small)
+    elev, b, e, H = table
+    ident = lso.IDENTITY_AFFINE
+    s0 = lso.Sensor(elev, b, e, H, poses[0][0], poses[0][1])
+    verts, tris = lso.concat_scene(s0, [(v, t, ident) for _, v, t in meshes], mode=1)
+    t0 = time.perf_counter()
+    bvh = lso.Bvh(verts, tris)
+    t_build = time.perf_counter() - t0
+    cores = lso.max_threads()
+    R = elev.size * H
+    times = []
+    for step in range(args.warmup + args.steps):
+        si = step % len(poses)
+        s = lso.Sensor(elev, b, e, H, poses[si][0], poses[si][1])
+        ta = time.perf_counter()
+        dirs_s = lso.ray_dirs(s.tables)
+        dirs = lso.rotate_dirs(s.R, dirs_s)
+        t, tri = bvh.trace(s.T, dirs)
+        pts = lso.pack_points(dirs_s, t, tri, H)
+        dt = time.perf_counter() - ta
+        if step >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    val = R * len(times) / total / 1e6
+    sample = (f"each step = ray generation + closest-hit trace + point packing of ONE of the {len(poses)} devices "
+              f"({R} rays) against the {tris.shape[0]}-triangle scene; CPU BVH (binned SAH) built once outside the "
+              f"timed region in {t_build:.1f} s (the reference rebuilds per device per frame: not charged)")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.small), "n_triangles": int(tris.shape[0]), "rays_per_step": R},
+            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(small):
+    return ("SMALL smoke city (not the benchmark)" if small else
+            "configs[3]: synthetic 10M-triangle city, 64 LiDAR devices (128ch x 3601 az), world frame")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--small", action="store_true", help="tiny scene for smoke runs (NOT the benchmark)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--traversal", type=int, default=None)
+    ap.add_argument("--top-nodes", type=int, default=None)
+    ap.add_argument("--leaf", type=int, default=None)
+    ap.add_argument("--commit", default="rebuild", choices=["rebuild", "auto"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from lidarshooter_b200 import capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    meshes, poses, table = build_workload(args.small)
+    elev, b, e, H = table
+    R = elev.size * H
+    n_sens = len(poses)
+    stream = torch.cuda.Stream()
+    ctx = capi.Context(local, capi.FRAME_WORLD, stream=stream.cuda_stream)
+    if args.traversal is not None:
+        ctx.set_option(capi.OPT_TRAVERSAL, args.traversal)
+    if args.top_nodes is not None:
+        ctx.set_option(capi.OPT_TOP_NODES, args.top_nodes)
+    if args.leaf is not None:
+        ctx.set_option(capi.OPT_LEAF_SIZE, args.leaf)
+    for k, (q, t) in enumerate(poses):
+        ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    # pinned host copies of the meshes (what a host application owns) and of the output clouds
+    host_v, host_t = [], []
+    for name, v, t in meshes:
+        pv = torch.from_numpy(v).pin_memory()
+        host_v.append(pv)
+        host_t.append(t)
+        assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0]) >= 0
+        assert ctx.update_geometry(name, pv.numpy(), t, frame_affine(0, len(host_v) - 1)) == 0
+    n_tris = sum(t.shape[0] for t in host_t)
+    commit_mode = capi.COMMIT_REBUILD if args.commit == "rebuild" else capi.COMMIT_AUTO
+    names = [m[0] for m in meshes]
+
+    def step_resident(frame):
+        for gi, name in enumerate(names):
+            ctx.update_transform(name, frame_affine(frame, gi))
+        rc = ctx.commit_scene(commit_mode)
+        assert rc == 0, ctx.last_error()
+        return 0
+
+    def sync_all():
+        stream.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident leg (value) ---------------------------------------------------------------------
+    frame = 0
+    for w in range(args.warmup):
+        step_resident(frame * world + rank); rc = ctx.trace_batch(0, n_sens, 0); assert rc == 0, ctx.last_error()
+        frame += 1
+    sync_all()
+    ctx.reset_counters()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    sampler = ClockSampler(local) if rank == 0 else None
+    t_wall0 = time.time()
+    e_begin, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_begin.record(stream)
+    for k in range(args.steps):
+        ev[k][0].record(stream)
+        step_resident(frame * world + rank)
+        ev[k][1].record(stream)
+        rc = ctx.trace_batch(0, n_sens, 0)
+        ev[k][2].record(stream)
+        frame += 1
+    e_end.record(stream)
+    sync_all()
+    t_wall1 = time.time()
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    assert rc == 0, ctx.last_error()
+    ms_total = e_begin.elapsed_time(e_end)
+    launches = int(ctx.stats().kernel_launches)
+    ms_commit = float(np.mean([ev[k][0].elapsed_time(ev[k][1]) for k in range(args.steps)]))
+    ms_trace = float(np.mean([ev[k][1].elapsed_time(ev[k][2]) for k in range(args.steps)]))
+    if world > 1:
+        tt = torch.tensor([ms_total, ms_trace, ms_commit], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total, ms_trace, ms_commit = [float(x) for x in tt.tolist()]
+    rays_per_step_rank = n_sens * R
+    value = world * rays_per_step_rank * args.steps / (ms_total * 1e-3) / 1e6
+
+    # hit fraction (for the byte model) from the last frame
+    rc, counts = ctx.fetch_batch(0, n_sens, [0] * n_sens, [0] * n_sens, 0)
+    hits = int(counts.sum())
+    hit_fraction = hits / rays_per_step_rank
+
+    # stage breakdown of one more frame with per-stage events (outside the timed region)
+    ctx.set_option(capi.OPT_STAGE_TIMING, 1)
+    step_resident(frame * world + rank); ctx.trace_batch(0, n_sens, 0)
+    st = ctx.stats()
+    ctx.set_option(capi.OPT_STAGE_TIMING, 0)
+    stages = {k: round(float(getattr(st, "ms_" + k)), 4) for k in
+              ("transform", "morton", "sort", "hierarchy", "fit", "toplevel", "trace", "compact")}
+
+    # ---- end-to-end leg: host buffers in, host point clouds out --------------------------------------------
+    rec = 32
+    out_bufs = [torch.empty((R, rec), dtype=torch.uint8).pin_memory() for _ in range(n_sens)]
+    out_ptrs = [t.data_ptr() for t in out_bufs]
+    caps = [R] * n_sens
+    h2d = sum(v.numel() * 4 for v in host_v) + 48 * len(names)
+
+    def step_e2e(frame):
+        for gi, name in enumerate(names):
+            rc_ = ctx.update_geometry(name, host_v[gi].numpy(), None, frame_affine(frame, gi))
+            assert rc_ == 0, ctx.last_error()
+        assert ctx.commit_scene(commit_mode) == 0, ctx.last_error()
+        assert ctx.trace_batch(0, n_sens, 0) == 0, ctx.last_error()
+        rc_, cnt = ctx.fetch_batch(0, n_sens, out_ptrs, caps, 0)
+        assert rc_ == 0, ctx.last_error()
+        return int(cnt.sum())
+
+    for w in range(2):
+        step_e2e(frame * world + rank); frame += 1
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record(stream)
+    d2h_pts = 0
+    for k in range(args.steps):
+        d2h_pts += step_e2e(frame * world + rank); frame += 1
+    e1.record(stream)
+    sync_all()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)   # host-side waits count
+    if world > 1:
+        tt = torch.tensor([ms_e2e], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_e2e = float(tt.item())
+    e2e_value = world * rays_per_step_rank * args.steps / (ms_e2e * 1e-3) / 1e6
+    d2h = d2h_pts // args.steps * rec + 4 * n_sens
+
+    # ---- roofline of the traversal kernel -------------------------------------------------------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md 6.65 TB/s)"
+    bytes_per_launch = rays_per_step_rank * b_ray(n_tris, hit_fraction)
+    achieved = bytes_per_launch / (ms_trace * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "trace_traffic.json"))).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+
+    line = None
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.small), "n_triangles": n_tris, "devices_per_gpu": n_sens,
+                       "rays_per_device": R, "rays_per_step_per_gpu": rays_per_step_rank, "frames_per_step": world,
+                       "commit": args.commit, "sharding": "trajectory frames over ranks, scene replicated per GPU",
+                       "l2": "inputs larger than L2 (BVH + triangles 1.1 GB, outputs 1.2 GB per frame); no flush needed",
+                       "point_record_bytes": rec, "hit_fraction": round(hit_fraction, 4)},
+            "scans_per_s": world * n_sens * args.steps / (ms_total * 1e-3),
+            "trace_only_mrays_per_s": world * rays_per_step_rank / (ms_trace * 1e-3) / 1e6,
+            "ms_commit": ms_commit, "ms_trace": ms_trace, "stages_ms": stages,
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches,
+            "roofline": {"kernel": "k_trace", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "bytes_per_ray": b_ray(n_tris, hit_fraction), "rays_per_launch": rays_per_step_rank,
+                         "ms_per_launch": ms_trace},
+        }
+    ctx.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            log("[bench] timing the CPU oracle on the host cores (bounded sample) ...")
+            c = cpu_trace_sample(meshes, poses, table)
+            line["cpu_baseline"] = {
+                "value": c["mrays_trace"], "unit": "Mrays/s", "cores": c["cores"], "kind": "port",
+                "sample": (f"closest-hit trace of 1 of the {n_sens} devices ({c['rays']} rays) against the same "
+                           f"{c['n_tris']}-triangle scene with the oracle's binned-SAH CPU BVH, all host threads; "
+                           f"trace only -- CPU transform {c['t_transform']:.2f} s and BVH build {c['t_build']:.2f} s "
+                           f"are NOT charged (the GPU value pays its rebuild every frame)"),
+                "t_build_s": c["t_build"], "t_trace_s": c["t_trace"]}
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

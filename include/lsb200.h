@@ -143,6 +143,10 @@ LSB200_API int lsb200_device_results(lsb200_ctx *ctx, int sensor_index, void **d
 /* copies the device point buffer of sensor_index to the host (count first, then count records) */
 LSB200_API int lsb200_fetch_points(lsb200_ctx *ctx, int sensor_index, void *out_points, size_t capacity_pts,
                                    uint32_t *n_pts, uint32_t flags);
+/* batch form: the hit counts of n_sensors sensors in one copy, then every point buffer; outs[i] / caps[i] / n_pts[i]
+ * belong to sensor first_sensor + i (host arrays; pinned memory makes the copies asynchronous until the final sync) */
+LSB200_API int lsb200_fetch_batch(lsb200_ctx *ctx, int first_sensor, int n_sensors, void *const *outs, const size_t *caps,
+                                  uint32_t *n_pts, uint32_t flags);
 LSB200_API int lsb200_synchronize(lsb200_ctx *ctx);
 
 /* ---- PointCloud2 header: replaces LidarDevice::initMessage (SRC/LidarDevice.cpp:94-115) ------------------ */

@@ -25,7 +25,7 @@ SYMBOLS = [
     "lsb200_remove_geometry", "lsb200_get_geometry_count", "lsb200_get_geometry_id", "lsb200_update_geometry",
     "lsb200_update_geometry_euler", "lsb200_update_transform", "lsb200_affine_from_components",
     "lsb200_commit_scene", "lsb200_trace_scene", "lsb200_trace_device", "lsb200_trace_batch", "lsb200_trace_raw",
-    "lsb200_device_results", "lsb200_fetch_points", "lsb200_synchronize", "lsb200_init_message", "lsb200_get_stats",
+    "lsb200_device_results", "lsb200_fetch_points", "lsb200_fetch_batch", "lsb200_synchronize", "lsb200_init_message", "lsb200_get_stats",
     "lsb200_reset_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
 ]
 
@@ -85,6 +85,7 @@ def lib():
     L.lsb200_trace_raw.argtypes = [vp, C.c_int, f32p, i32p]
     L.lsb200_device_results.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     L.lsb200_fetch_points.argtypes = [vp, C.c_int, vp, C.c_size_t, u32p, C.c_uint32]
+    L.lsb200_fetch_batch.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), C.POINTER(C.c_size_t), u32p, C.c_uint32]
     L.lsb200_synchronize.argtypes = [vp]
     L.lsb200_init_message.argtypes = [vp, C.c_uint32, C.POINTER(CloudHeader)]
     L.lsb200_get_stats.argtypes = [vp, C.POINTER(Stats)]
@@ -227,6 +228,14 @@ class Context:
         n = C.c_uint32(0)
         rc = self._L.lsb200_fetch_points(self._h, sensor, out.ctypes.data, out.shape[0], C.byref(n), flags)
         return rc, out[:n.value]
+
+    def fetch_batch(self, first, count, out_ptrs, caps, flags=0):
+        """out_ptrs: host addresses (ints), caps: capacities in records.  Returns (status, counts[count])."""
+        outs = (C.c_void_p * count)(*[C.c_void_p(int(p)) for p in out_ptrs])
+        cps = (C.c_size_t * count)(*[int(x) for x in caps])
+        n = np.zeros(count, np.uint32)
+        rc = self._L.lsb200_fetch_batch(self._h, first, count, outs, cps, n.ctypes.data_as(C.POINTER(C.c_uint32)), flags)
+        return rc, n
 
     def trace_raw(self, sensor=0):
         R = self.ray_count(sensor)

@@ -737,6 +737,30 @@ int lsb200_fetch_points(lsb200_ctx *c, int idx, void *out, size_t capacity, uint
     return fetch_locked(c, idx, out, capacity, n_pts, flags);
 }
 
+int lsb200_fetch_batch(lsb200_ctx *c, int first, int count, void *const *outs, const size_t *caps, uint32_t *n_pts, uint32_t flags)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (first < 0 || count <= 0 || count > 16 * 256 || (size_t)(first + count) > c->sensors.size() || !outs || !caps || !n_pts)
+        return fail(c, LSB200_ERR_INVALID, "fetch_batch: bad arguments");
+    if (!c->d_counts.p) return fail(c, LSB200_ERR_STATE, "fetch_batch: nothing traced yet");
+    DeviceGuard dg(c->device);
+    cudaStream_t st = c->stream;
+    // one copy for all hit counts, one synchronisation, then all point copies back to back
+    LSB_CU(c, cudaMemcpyAsync(n_pts, c->d_counts.as<uint32_t>() + first, (size_t)count * 4, cudaMemcpyDeviceToHost, st));
+    LSB_CU(c, cudaStreamSynchronize(st));
+    int rc = LSB200_OK;
+    for (int i = 0; i < count; ++i) {
+        const Sensor &s = c->sensors[first + i];
+        if (!s.set || !s.points.p) return fail(c, LSB200_ERR_STATE, "fetch_batch: sensor %d was never traced", first + i);
+        const size_t ncopy = std::min<size_t>(n_pts[i], caps[i]);
+        if (n_pts[i] > caps[i]) rc = fail(c, LSB200_ERR_CAPACITY, "fetch_batch: sensor %d has %u points, capacity %zu", first + i, n_pts[i], caps[i]);
+        if (outs[i] && ncopy) LSB_CU(c, cudaMemcpyAsync(outs[i], s.points.p, ncopy * record_bytes(flags), cudaMemcpyDeviceToHost, st));
+    }
+    LSB_CU(c, cudaStreamSynchronize(st));
+    return rc;
+}
+
 int lsb200_trace_raw(lsb200_ctx *c, int idx, float *t_out, int32_t *tri_out)
 {
     if (!c) return LSB200_ERR_INVALID;

@@ -69,17 +69,27 @@ def _box(cx, cy, wx, wy, h, n=10):
     return np.concatenate(vs).astype(np.float32), np.concatenate(ts).astype(np.uint32)
 
 
-def city(n_boxes=8000, ground_cells=1000, extent=1000.0, seed=2024, n_groups=8):
-    """Config 4 scene: ground grid 1000 x 1000 cells over 1 km^2 (2 000 000 triangles) + 8000 boxes x 1000
-    triangles = 10 000 000 triangles.  Returns a list of (name, verts, tris): 'ground' + n_groups building
-    meshes (the boxes dealt round-robin), i.e. 9 geometries."""
+CITY_PITCH = 2000.0 / 90.0      # street-grid pitch of city(): 90 x 90 lots over 2 km
+
+
+def city(n_boxes=8000, ground_cells=1000, extent=2000.0, seed=2024, n_groups=8, lots=90):
+    """Config 4 scene: ground grid 1000 x 1000 cells over 2 km x 2 km (2 000 000 triangles) + 8000 box buildings x
+    1000 triangles = 10 000 000 triangles.  Buildings stand on a lots x lots street grid (one per lot, the lots left
+    empty chosen by the seeded stream), centre jittered by +-2 m, footprint 8-16 m, height 5-80 m, so streets stay
+    open and no two buildings overlap (built-up fraction ~30 %).  Returns a list of (name, verts, tris): 'ground' +
+    n_groups building meshes (buildings dealt round-robin), i.e. 9 geometries."""
     rng = np.random.default_rng(seed)
     half = extent / 2
+    pitch = extent / lots
     ground = grid_mesh(ground_cells, ground_cells, -half, half, -half, half, lambda X, Y: np.zeros_like(X))
-    cx = rng.uniform(-half + 25, half - 25, n_boxes)
-    cy = rng.uniform(-half + 25, half - 25, n_boxes)
-    wx = rng.uniform(10, 40, n_boxes)
-    wy = rng.uniform(10, 40, n_boxes)
+    n_boxes = min(n_boxes, lots * lots)
+    lot = rng.permutation(lots * lots)[:n_boxes]
+    li, lj = np.divmod(lot, lots)
+    cx = (lj + 0.5) * pitch - half + rng.uniform(-2, 2, n_boxes)
+    cy = (li + 0.5) * pitch - half + rng.uniform(-2, 2, n_boxes)
+    fmax = min(16.0, pitch - 6.0)
+    wx = rng.uniform(fmax / 2, fmax, n_boxes)
+    wy = rng.uniform(fmax / 2, fmax, n_boxes)
     hh = rng.uniform(5, 80, n_boxes)
     # one template box, scaled/translated per instance (fast, vectorised)
     tv, tt = _box(0.0, 0.0, 1.0, 1.0, 1.0)
@@ -110,16 +120,18 @@ def yaw_quat(yaw):
     return np.array([np.cos(yaw / 2), 0.0, 0.0, np.sin(yaw / 2)], np.float32)
 
 
-def sensor_lattice(n_side=8, spacing=110.0, z=5.0, seed=7):
-    """Config 4 devices: n_side^2 sensors on a lattice centred on the origin, yaw from the seeded stream."""
+def sensor_lattice(n_side=8, spacing=10 * CITY_PITCH, z=5.0, seed=7):
+    """Config 4 devices: n_side^2 sensors on a lattice centred on the origin, yaw from the seeded stream.  With the
+    default spacing (10 lots) every sensor stands on a street crossing of city(): lot corners are at integer
+    multiples of the pitch and (k - 3.5) * 10 is an integer."""
     rng = np.random.default_rng(seed)
     yaws = rng.uniform(0, 2 * np.pi, n_side * n_side)
     c = (np.arange(n_side) - (n_side - 1) / 2) * spacing
     poses = []
     for k in range(n_side * n_side):
         i, j = divmod(k, n_side)
-        # offset by a few metres so that sensors do not sit exactly on grid lines of the ground mesh
-        poses.append((yaw_quat(yaws[k]), np.array([c[j] + 1.37, c[i] + 2.11, z], np.float32)))
+        # a small offset so that sensors do not sit exactly above grid lines of the ground mesh
+        poses.append((yaw_quat(yaws[k]), np.array([c[j] + 0.137, c[i] + 0.211, z], np.float32)))
     return poses
 
 
