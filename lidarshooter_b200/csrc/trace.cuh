@@ -206,9 +206,10 @@ __device__ __forceinline__ void hit_point(const SensorDev &S, uint32_t flags, fl
 {
     x = __fmul_rn(t, dsx); y = __fmul_rn(t, dsy); z = __fmul_rn(t, dsz);      // t * d_sensor (SRC/EmbreeTracer.cpp:331-333)
     if (flags & 16u /*LSB200_TRACE_WORLD_POINTS*/) {                          // R p + T (SRC/LidarDevice.cpp:393-401)
-        const float wx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(S.R[0], x), __fmul_rn(S.R[1], y)), __fmul_rn(S.R[2], z)), S.T[0]);
-        const float wy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(S.R[3], x), __fmul_rn(S.R[4], y)), __fmul_rn(S.R[5], z)), S.T[1]);
-        const float wz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(S.R[6], x), __fmul_rn(S.R[7], y)), __fmul_rn(S.R[8], z)), S.T[2]);
+        // Eigen 3-term dot order a0 + (a1 + a2), then the translation (LidarDevice::originToSensorInverse)
+        const float wx = __fadd_rn(__fadd_rn(__fmul_rn(S.R[0], x), __fadd_rn(__fmul_rn(S.R[1], y), __fmul_rn(S.R[2], z))), S.T[0]);
+        const float wy = __fadd_rn(__fadd_rn(__fmul_rn(S.R[3], x), __fadd_rn(__fmul_rn(S.R[4], y), __fmul_rn(S.R[5], z))), S.T[1]);
+        const float wz = __fadd_rn(__fadd_rn(__fmul_rn(S.R[6], x), __fadd_rn(__fmul_rn(S.R[7], y), __fmul_rn(S.R[8], z))), S.T[2]);
         x = wx; y = wy; z = wz;
     }
 }

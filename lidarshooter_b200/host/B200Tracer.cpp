@@ -1,0 +1,170 @@
+#include "B200Tracer.hpp"
+
+#include <cstring>
+
+#include "lsb200.h"
+
+namespace lidarshooter {
+
+ITracer::ITracer(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceStorage)
+    : _config(_sensorConfig), _geometryCount(0)
+{
+    // SRC/ITracer.cpp:16-25: own the cloud when none is given; zero width/height
+    _traceCloud = _traceStorage ? _traceStorage : PointCloud2::Ptr(new PointCloud2());
+    _traceCloud->width = 0;
+    _traceCloud->height = 0;
+}
+
+B200Tracer::Ptr B200Tracer::create(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceStorage, int _cudaDevice)
+{
+    return B200Tracer::Ptr(new B200Tracer(_sensorConfig, _traceStorage, _cudaDevice));
+}
+
+B200Tracer::B200Tracer(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceStorage, int _cudaDevice)
+    : ITracer(_sensorConfig, _traceStorage)
+{
+    const int rc = lsb200_create(_cudaDevice, &_ctx);
+    if (rc != LSB200_OK || !_ctx)
+        throw TraceException(__FILE__, "lsb200_create failed: no usable CUDA device (B200Tracer has no CPU path)", rc);
+    LidarDevice::Ptr dev = getSensorConfig();
+    if (dev) {
+        float q[4], t[3];
+        dev->quaternion(q);
+        dev->translation(t);
+        const auto &vert = dev->verticalAngles();
+        const int src = lsb200_set_sensor(_ctx, 0, vert.data(), static_cast<int>(vert.size()), dev->azimuthBegin(), dev->azimuthEnd(),
+                                          static_cast<int>(dev->getScanRayCount()), q, t);
+        if (src != LSB200_OK) {
+            const std::string msg = lsb200_last_error(_ctx);
+            lsb200_destroy(_ctx); _ctx = nullptr;
+            throw TraceException(__FILE__, "lsb200_set_sensor failed: " + msg, src);
+        }
+    }
+}
+
+B200Tracer::~B200Tracer()
+{
+    if (_ctx) lsb200_destroy(_ctx);
+}
+
+std::string B200Tracer::lastError() const { return lsb200_last_error(_ctx); }
+
+int B200Tracer::getGeometryId(const std::string &_meshName) const { return lsb200_get_geometry_id(_ctx, _meshName.c_str()); }
+
+RTCGeometryType B200Tracer::getGeometryType(const std::string &_meshName)
+{
+    auto it = _geoms.find(_meshName);
+    if (it == _geoms.end()) throw TraceException(__FILE__, "Geometry key does not exist in geometry types map", 8);
+    return it->second.type;
+}
+
+long B200Tracer::getVertexCount(const std::string &_meshName)
+{
+    auto it = _geoms.find(_meshName);
+    if (it == _geoms.end()) throw TraceException(__FILE__, "Geometry key does not exist in vertex count map", 1);
+    return it->second.nVerts;
+}
+
+long B200Tracer::getElementCount(const std::string &_meshName)
+{
+    auto it = _geoms.find(_meshName);
+    if (it == _geoms.end()) throw TraceException(__FILE__, "Geometry key does not exist in element count map", 4);
+    return it->second.nElems;
+}
+
+int B200Tracer::addGeometry(const std::string &_meshName, enum RTCGeometryType _geometryType, int _numVertices, int _numElements)
+{
+    // SRC/EmbreeTracer.cpp:115-218: TRIANGLE and QUAD are supported, everything else "returns false"
+    if (_geometryType != RTC_GEOMETRY_TYPE_TRIANGLE && _geometryType != RTC_GEOMETRY_TYPE_QUAD) return 0;
+    const int id = lsb200_add_geometry(_ctx, _meshName.c_str(), static_cast<int>(_geometryType), _numVertices, _numElements);
+    if (id < 0) return id;
+    _geoms[_meshName] = Geom{_geometryType, _numVertices, _numElements, false};
+    setGeometryCount(getGeometryCount() + 1);
+    return id;
+}
+
+int B200Tracer::removeGeometry(const std::string &_meshName)
+{
+    const int id = lsb200_remove_geometry(_ctx, _meshName.c_str());
+    if (id < 0) return -1;                                     // SRC/EmbreeTracer.cpp:224-225
+    _geoms.erase(_meshName);
+    setGeometryCount(getGeometryCount() - 1);
+    return id;
+}
+
+Affine3f B200Tracer::transformFromComponents(Vector3f _translation, Vector3f _rotation)
+{
+    Affine3f A;
+    lsb200_affine_from_components(_translation.v, _rotation.v, A.m);
+    return A;
+}
+
+int B200Tracer::update(const std::string &_meshName, const float A[12], PolygonMesh::Ptr &_mesh)
+{
+    if (!_mesh) throw MeshNotSetException(__FILE__, "No mesh data to transform", 1);       // SRC/MeshTransformer.cpp:144-151
+    auto it = _geoms.find(_meshName);
+    if (it == _geoms.end()) throw TraceException(__FILE__, "Geometry key does not exist in geometry types map", 8);
+    Geom &g = it->second;
+    const int arity = g.type == RTC_GEOMETRY_TYPE_QUAD ? 4 : 3;
+    if (static_cast<long>(_mesh->vertexCount()) < g.nVerts || static_cast<long>(_mesh->polygons.size()) < g.nElems)
+        return -1;
+    const uint32_t *elems = nullptr;
+    if (!g.topologySent) {
+        // index copy (SRC/MeshTransformer.cpp:486-552), once: the reference repeats it every frame (its TODO at :153)
+        _elemScratch.resize(static_cast<size_t>(g.nElems) * arity);
+        for (long e = 0; e < g.nElems; ++e) {
+            const auto &poly = _mesh->polygons[e].vertices;
+            if (static_cast<int>(poly.size()) != arity)
+                throw BadGeometryException(__FILE__, "Wrong number of vertices in an element", 1, arity, static_cast<long>(poly.size()));
+            std::memcpy(&_elemScratch[static_cast<size_t>(e) * arity], poly.data(), sizeof(uint32_t) * arity);
+        }
+        elems = _elemScratch.data();
+    }
+    const int rc = lsb200_update_geometry(_ctx, _meshName.c_str(), _mesh->cloud.data.data(), static_cast<int>(_mesh->cloud.point_step), elems, A);
+    if (rc == LSB200_OK) g.topologySent = true;
+    return rc;
+}
+
+int B200Tracer::updateGeometry(const std::string &_meshName, Affine3f _transform, PolygonMesh::Ptr &_mesh)
+{
+    return update(_meshName, _transform.m, _mesh);
+}
+
+int B200Tracer::updateGeometry(const std::string &_meshName, Vector3f _translation, Vector3f _rotation, PolygonMesh::Ptr &_mesh)
+{
+    const Affine3f A = transformFromComponents(_translation, _rotation);
+    return update(_meshName, A.m, _mesh);
+}
+
+int B200Tracer::commitScene()
+{
+    return lsb200_commit_scene(_ctx, LSB200_COMMIT_AUTO);
+}
+
+int B200Tracer::traceScene(std::uint32_t _frameIndex)
+{
+    // SRC/EmbreeTracer.cpp:297-367: header, clear, trace, width = number of hits.  The cloud is rewritten in place.
+    PointCloud2::Ptr cloud = getTraceCloud();
+    getSensorConfig()->initMessage(cloud, static_cast<int>(_frameIndex));
+    const size_t capacity = getSensorConfig()->getTotalRays();
+    cloud->data.resize(capacity * 32);
+    uint32_t n = 0;
+    uint32_t flags = 0;
+    if (_ordered) flags |= LSB200_TRACE_ORDERED;
+    if (_ringZero) flags |= LSB200_TRACE_RING_ZERO;
+    if (_worldPoints) flags |= LSB200_TRACE_WORLD_POINTS;
+    const int rc = lsb200_trace_scene(_ctx, 0, _frameIndex, cloud->data.data(), capacity, &n, flags);
+    cloud->data.resize(static_cast<size_t>(n) * 32);
+    cloud->width = n;
+    return rc;
+}
+
+int B200Tracer::traceRaw(std::vector<float> &_t, std::vector<int32_t> &_tri)
+{
+    const size_t R = getSensorConfig()->getTotalRays();
+    _t.resize(R);
+    _tri.resize(R);
+    return lsb200_trace_raw(_ctx, 0, _t.data(), _tri.data());
+}
+
+}  // namespace lidarshooter
