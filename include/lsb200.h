@@ -65,12 +65,16 @@ enum {
 
 /* traversal kernel variants (lsb200_set_option LSB200_OPT_TRAVERSAL) -- for the ncu before/after evidence */
 enum {
-    LSB200_OPT_TRAVERSAL = 1,      /* 0 = persistent + smem-staged top levels (default), 1 = persistent, no staging,
-                                      2 = one thread per ray (no persistent fetch), 3 = brute force (all triangles) */
+    LSB200_OPT_TRAVERSAL = 1,      /* 0 = persistent CTAs, 32-ray units queued by ray octant, sign-specialised slab test
+                                      (default); 1 = persistent, generic slab test, ray order; 2 = one thread per ray
+                                      (no persistent fetch); 3 = brute force (all triangles); 4 = variant 1 + top BVH
+                                      levels staged into shared memory by TMA bulk copy; 5 = variant 1, while-while */
     LSB200_OPT_LEAF_SIZE = 2,      /* max triangles per leaf, 1..8 (default 4) */
     LSB200_OPT_TOP_NODES = 3,      /* number of BVH nodes staged into shared memory by TMA bulk copy (default 1024) */
     LSB200_OPT_STAGE_TIMING = 4,   /* 1 = record CUDA events around every stage (lsb200_get_stats) */
-    LSB200_OPT_CTAS_PER_SM = 5     /* persistent grid = 148 * this (default 0 = occupancy query) */
+    LSB200_OPT_CTAS_PER_SM = 5,    /* persistent grid = 148 * this (default 0 = occupancy query) */
+    LSB200_OPT_TRACE_STATS = 6,    /* 1 = instrumented traversal: per-launch node / leaf / triangle counters */
+    LSB200_OPT_MORTON_UNIFORM = 7  /* 1 = Morton codes on cubic cells (one scale for x, y, z); default 0 = per-axis */
 };
 
 /* ---- life cycle -------------------------------------------------------------------------------------- */
@@ -148,6 +152,24 @@ LSB200_API int lsb200_fetch_points(lsb200_ctx *ctx, int sensor_index, void *out_
 LSB200_API int lsb200_fetch_batch(lsb200_ctx *ctx, int first_sensor, int n_sensors, void *const *outs, const size_t *caps,
                                   uint32_t *n_pts, uint32_t flags);
 LSB200_API int lsb200_synchronize(lsb200_ctx *ctx);
+/* ---- pipelined frames: the throughput form of the per-frame loop of MeshProjector::traceMeshWrapper
+ * (SRC/MeshProjector.cpp:446-471: updateGeometry for every mesh, commitScene, traceScene) over a batch of
+ * trajectory frames.  For each frame: optional vertex re-upload, per-geometry affine, commit, one trace launch
+ * for the sensors [first_sensor, first_sensor + n_sensors), then the hit counts and the point clouds go to the
+ * caller's HOST buffers on a second stream while the next frame is already being built and traced (two device
+ * output slots).  Results are identical to calling the per-frame entry points in sequence.  Pinned host buffers
+ * are needed for the overlap (pageable ones still work, serialised by the runtime). */
+typedef struct lsb200_frame {
+    const float *affines;          /* [n_geometries][12], ascending geometry id; NULL = transforms unchanged */
+    const void *const *verts;      /* [n_geometries] host vertex blobs to re-upload (stride as first given); NULL
+                                      array or NULL entry = vertices already resident */
+    void *const *out_points;       /* [n_sensors] host buffers of capacities[i] records */
+    const size_t *capacities;      /* [n_sensors] */
+    uint32_t *n_pts;               /* [n_sensors] out: hit counts */
+} lsb200_frame;
+LSB200_API int lsb200_run_frames(lsb200_ctx *ctx, const lsb200_frame *frames, int n_frames, int first_sensor,
+                                 int n_sensors, int commit_mode, uint32_t flags);
+
 
 /* ---- PointCloud2 header: replaces LidarDevice::initMessage (SRC/LidarDevice.cpp:94-115) ------------------ */
 typedef struct lsb200_cloud_header {
@@ -177,6 +199,9 @@ typedef struct lsb200_stats {
 } lsb200_stats;
 LSB200_API int lsb200_get_stats(lsb200_ctx *ctx, lsb200_stats *out);
 LSB200_API int lsb200_reset_counters(lsb200_ctx *ctx);
+/* totals of the last LSB200_OPT_TRACE_STATS launch: out[0..n) = rays, nodes visited, leaves visited, triangles tested,
+ * 32-ray units with one octant, units with mixed octants, deepest stack, hits */
+LSB200_API int lsb200_get_trace_counters(lsb200_ctx *ctx, uint64_t *out, int n);
 /* copies the BVH to the host for structural tests: nodes (n_nodes x 16 floats), leaf-ordered triangle ids */
 LSB200_API int lsb200_debug_copy_bvh(lsb200_ctx *ctx, float *nodes16, int64_t node_capacity, int32_t *leaf_tri_ids,
                                      int64_t tri_capacity, int32_t *root);

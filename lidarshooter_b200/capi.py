@@ -16,6 +16,7 @@ FRAME_SENSOR, FRAME_WORLD = 0, 1
 COMMIT_AUTO, COMMIT_REBUILD, COMMIT_REFIT = 0, 1, 2
 TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS = 1, 2, 4, 8, 16
 OPT_TRAVERSAL, OPT_LEAF_SIZE, OPT_TOP_NODES, OPT_STAGE_TIMING, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
+OPT_TRACE_STATS, OPT_MORTON_UNIFORM = 6, 7
 ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5
 
 # every symbol include/lsb200.h declares (tests/test_abi.py checks the library exports each one)
@@ -25,8 +26,8 @@ SYMBOLS = [
     "lsb200_remove_geometry", "lsb200_get_geometry_count", "lsb200_get_geometry_id", "lsb200_update_geometry",
     "lsb200_update_geometry_euler", "lsb200_update_transform", "lsb200_affine_from_components",
     "lsb200_commit_scene", "lsb200_trace_scene", "lsb200_trace_device", "lsb200_trace_batch", "lsb200_trace_raw",
-    "lsb200_device_results", "lsb200_fetch_points", "lsb200_fetch_batch", "lsb200_synchronize", "lsb200_init_message", "lsb200_get_stats",
-    "lsb200_reset_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
+    "lsb200_device_results", "lsb200_fetch_points", "lsb200_fetch_batch", "lsb200_synchronize", "lsb200_run_frames", "lsb200_init_message", "lsb200_get_stats",
+    "lsb200_reset_counters", "lsb200_get_trace_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
 ]
 
 
@@ -34,6 +35,11 @@ class CloudHeader(C.Structure):
     _fields_ = [("seq", C.c_uint32), ("height", C.c_uint32), ("width", C.c_uint32), ("point_step", C.c_uint32),
                 ("row_step", C.c_uint32), ("is_bigendian", C.c_uint8), ("is_dense", C.c_uint8),
                 ("n_fields", C.c_uint8), ("reserved", C.c_uint8)]
+
+
+class Frame(C.Structure):
+    _fields_ = [("affines", C.POINTER(C.c_float)), ("verts", C.POINTER(C.c_void_p)), ("out_points", C.POINTER(C.c_void_p)),
+                ("capacities", C.POINTER(C.c_size_t)), ("n_pts", C.POINTER(C.c_uint32))]
 
 
 class Stats(C.Structure):
@@ -87,9 +93,11 @@ def lib():
     L.lsb200_fetch_points.argtypes = [vp, C.c_int, vp, C.c_size_t, u32p, C.c_uint32]
     L.lsb200_fetch_batch.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), C.POINTER(C.c_size_t), u32p, C.c_uint32]
     L.lsb200_synchronize.argtypes = [vp]
+    L.lsb200_run_frames.argtypes = [vp, C.POINTER(Frame), C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32]
     L.lsb200_init_message.argtypes = [vp, C.c_uint32, C.POINTER(CloudHeader)]
     L.lsb200_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.lsb200_reset_counters.argtypes = [vp]
+    L.lsb200_get_trace_counters.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
     L.lsb200_debug_copy_bvh.argtypes = [vp, f32p, C.c_int64, i32p, C.c_int64, i32p]
     L.lsb200_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_int64]
     L.lsb200_debug_copy_vertices.argtypes = [vp, f32p, C.c_int64]
@@ -237,6 +245,30 @@ class Context:
         rc = self._L.lsb200_fetch_batch(self._h, first, count, outs, cps, n.ctypes.data_as(C.POINTER(C.c_uint32)), flags)
         return rc, n
 
+    def run_frames(self, affines, out_ptrs, caps, first=0, count=1, commit_mode=COMMIT_AUTO, flags=0, verts=None):
+        """Pipelined batch of frames.  affines: (F, G, 12) float32; out_ptrs: F lists of `count` host addresses;
+        caps: `count` capacities (records); verts: optional list of G host addresses re-uploaded every frame.
+        Returns (status, counts[F, count])."""
+        A = np.ascontiguousarray(affines, np.float32)
+        F = A.shape[0]
+        counts = np.zeros((F, count), np.uint32)
+        cps = (C.c_size_t * count)(*[int(x) for x in caps])
+        vv = None
+        if verts is not None:
+            vv = (C.c_void_p * len(verts))(*[C.c_void_p(int(p)) if p else None for p in verts])
+        frames = (Frame * F)()
+        keep = []
+        for f in range(F):
+            outs = (C.c_void_p * count)(*[C.c_void_p(int(p)) for p in out_ptrs[f]])
+            keep.append(outs)
+            frames[f].affines = A[f].ctypes.data_as(C.POINTER(C.c_float))
+            frames[f].verts = C.cast(vv, C.POINTER(C.c_void_p)) if vv is not None else None
+            frames[f].out_points = C.cast(outs, C.POINTER(C.c_void_p))
+            frames[f].capacities = C.cast(cps, C.POINTER(C.c_size_t))
+            frames[f].n_pts = counts[f].ctypes.data_as(C.POINTER(C.c_uint32))
+        rc = self._L.lsb200_run_frames(self._h, frames, F, first, count, commit_mode, flags)
+        return rc, counts
+
     def trace_raw(self, sensor=0):
         R = self.ray_count(sensor)
         t, tri = np.empty(R, np.float32), np.empty(R, np.int32)
@@ -255,6 +287,13 @@ class Context:
         s = Stats()
         self._chk(self._L.lsb200_get_stats(self._h, C.byref(s)))
         return s
+
+    def trace_counters(self):
+        """Totals of the last OPT_TRACE_STATS launch as a dict."""
+        out = (C.c_uint64 * 9)()
+        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 9))
+        names = ("rays", "nodes", "leaves", "tris", "units_uniform", "units_mixed", "max_stack", "hits", "culled_pops")
+        return {k: int(out[i]) for i, k in enumerate(names)}
 
     def reset_counters(self):
         self._L.lsb200_reset_counters(self._h)

@@ -21,6 +21,7 @@ struct SceneDev {
     uint32_t *flags;         // [n_tris] arrival counters of the bottom-up pass (parity: never re-zeroed)
     int top_cap;             // nodes reserved for the top-level copy
     int leaf_max;
+    int morton_uniform;      // 1: one scale (the largest extent) for all three axes -> cubic Morton cells
 };
 
 // Eigen-ordered 3-term dot: a0*b0 + (a1*b1 + a2*b2)  (oracle/lsb_oracle.c: dot3_eigen)
@@ -113,7 +114,8 @@ __global__ void __launch_bounds__(256) k_morton(SceneDev S)
     const float cx = 0.5f * (fminf(A.x, fminf(B.x, C.x)) + fmaxf(A.x, fmaxf(B.x, C.x)));
     const float cy = 0.5f * (fminf(A.y, fminf(B.y, C.y)) + fmaxf(A.y, fmaxf(B.y, C.y)));
     const float cz = 0.5f * (fminf(A.z, fminf(B.z, C.z)) + fmaxf(A.z, fmaxf(B.z, C.z)));
-    const float ex = shi[0] - slo[0], ey = shi[1] - slo[1], ez = shi[2] - slo[2];
+    float ex = shi[0] - slo[0], ey = shi[1] - slo[1], ez = shi[2] - slo[2];
+    if (S.morton_uniform) ex = ey = ez = fmaxf(ex, fmaxf(ey, ez));
     const float nx = ex > 0.0f ? (cx - slo[0]) / ex : 0.0f;
     const float ny = ey > 0.0f ? (cy - slo[1]) / ey : 0.0f;
     const float nz = ez > 0.0f ? (cz - slo[2]) / ez : 0.0f;

@@ -61,6 +61,7 @@ struct Sensor {
     float R[9], Rinv[9], T[3], q[4];
     DevBuf tables;                     // sin_t[V] cos_t[V] sin_p[H] cos_p[H]
     DevBuf t, tri, points, blocks;     // per-ray results, compacted points, ordered-compaction scratch
+    DevBuf points_b;                   // second output slot: lsb200_run_frames overlaps its D2H with the next frame
     int n_rays() const { return V * H; }
 };
 
@@ -70,7 +71,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 0, opt_leaf = 4, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0;
+    int opt_traversal = 0, opt_leaf = 4, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -80,9 +81,14 @@ struct lsb200_ctx {
     bool sensors_dirty = true;
     // scene arrays
     DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
-        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_counts, d_sensor_xf;
+        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist;
     std::vector<GeomDesc> h_geoms;
-    std::vector<SensorDev> h_sensors;
+    std::vector<SensorDev> h_sensors, h_sensors_b;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_traced[2] = {}, ev_copied[2] = {};
+    // octant queues of the traversal (variant 0): valid for (units_first, units_count, units_epoch, units_world)
+    int64_t sensors_epoch = 0, units_epoch = -1;
+    int units_first = -1, units_count = -1, units_world = -1;
     float h_xf[12];
     uint32_t *h_count = nullptr;                                 // pinned
     int n_verts = 0, n_tris = 0;
@@ -179,6 +185,7 @@ SceneDev scene_dev(lsb200_ctx *c)
     S.nodes = c->d_nodes.as<float4>(); S.node_parent = c->d_node_parent.as<int32_t>();
     S.leaf_parent = c->d_leaf_parent.as<int32_t>(); S.flags = c->d_flags.as<uint32_t>();
     S.top_cap = c->built_top; S.leaf_max = c->built_leaf;
+    S.morton_uniform = c->opt_morton_uniform;
     return S;
 }
 
@@ -227,7 +234,9 @@ int lsb200_create(int cuda_device, lsb200_ctx **out)
     if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
     c->stream = c->own_stream;
     for (auto &e : c->ev) cudaEventCreate(&e);
-    cudaMallocHost((void **)&c->h_count, 16 * sizeof(uint32_t));
+    cudaMallocHost((void **)&c->h_count, (16 + 2 * kMaxSensors) * sizeof(uint32_t));
+    cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    for (int k = 0; k < 2; ++k) { cudaEventCreateWithFlags(&c->ev_traced[k], cudaEventDisableTiming); cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming); }
     if (c->d_bounds.reserve(256, c->stream) != cudaSuccess || c->d_misc.reserve(256, c->stream, false, true) != cudaSuccess ||
         c->d_sensor_xf.reserve(256, c->stream) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
     c->sensors.resize(1);
@@ -242,13 +251,15 @@ int lsb200_destroy(lsb200_ctx *c)
         DeviceGuard dg(c->device);
         cudaStreamSynchronize(c->stream);
         for (auto &kv : c->geoms) { kv.second.verts.release(); kv.second.elems.release(); }
-        for (auto &s : c->sensors) { s.tables.release(); s.t.release(); s.tri.release(); s.points.release(); s.blocks.release(); }
+        for (auto &s : c->sensors) { s.tables.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
-                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_counts, &c->d_sensor_xf};
+                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist};
         for (auto *b : bufs) b->release();
         if (c->h_count) cudaFreeHost(c->h_count);
         for (auto &e : c->ev) if (e) cudaEventDestroy(e);
+        for (int k = 0; k < 2; ++k) { if (c->ev_traced[k]) cudaEventDestroy(c->ev_traced[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
+        if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
         if (c->own_stream) cudaStreamDestroy(c->own_stream);
     }
     delete c;
@@ -279,7 +290,9 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     if (!c) return LSB200_ERR_INVALID;
     std::lock_guard<std::mutex> lk(c->mtx);
     switch (option) {
-    case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 3) break; c->opt_traversal = value; return LSB200_OK;
+    case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 5) break; c->opt_traversal = value; return LSB200_OK;
+    case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_MORTON_UNIFORM: c->opt_morton_uniform = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_LEAF_SIZE: if (value < 1 || value > kMaxLeaf) break; c->opt_leaf = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TOP_NODES: if (value < 0 || value > 3072) break; c->opt_top = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_STAGE_TIMING: c->opt_timing = value ? 1 : 0; return LSB200_OK;
@@ -322,6 +335,7 @@ int lsb200_set_sensor(lsb200_ctx *c, int idx, const float *elev_deg, int V, floa
     LSB_CU(c, cudaStreamSynchronize(c->stream));     // tab is a local
     s.set = true;
     c->sensors_dirty = true;
+    ++c->sensors_epoch;
     if (idx == 0 && c->frame_mode == LSB200_FRAME_SENSOR) c->committed = false;   // scene lives in this sensor's frame
     return LSB200_OK;
 }
@@ -550,12 +564,13 @@ int lsb200_remove_geometry(lsb200_ctx *c, const char *name)
 // ---- trace -------------------------------------------------------------------------------------------------
 static size_t record_bytes(uint32_t flags) { return (flags & LSB200_TRACE_XYZI16) ? 16 : 32; }
 
-// (re)allocates the per-sensor result buffers of [first, first+count) and refreshes the device sensor table
-static int prepare_sensors(lsb200_ctx *c, int first, int count)
+// (re)allocates the per-sensor result buffers of [first, first+count) and refreshes the device sensor tables.
+// slot 0 = the context's ordinary output buffers; slot 1 = the second set used by lsb200_run_frames.
+static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
 {
     cudaStream_t st = c->stream;
     const size_t ns = c->sensors.size();
-    LSB_CU(c, c->d_counts.reserve(std::max<size_t>(ns, 16) * 4, st, true, true));
+    LSB_CU(c, c->d_counts.reserve((size_t)2 * kMaxSensors * 4, st, true, true));
     bool dirty = c->sensors_dirty || c->h_sensors.size() != ns;
     for (int i = first; i < first + count; ++i) {
         Sensor &s = c->sensors[i];
@@ -563,8 +578,10 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count)
         const size_t R = (size_t)s.n_rays();
         const size_t nblk = (R + kCompactRays - 1) / kCompactRays;
         if (s.t.cap < R * 4 || s.tri.cap < R * 4 || s.points.cap < R * 32 || s.blocks.cap < nblk * 4) dirty = true;
+        if (slot == 1 && s.points_b.cap < R * 32) dirty = true;
         LSB_CU(c, s.t.reserve(R * 4, st)); LSB_CU(c, s.tri.reserve(R * 4, st));
         LSB_CU(c, s.points.reserve(R * 32, st)); LSB_CU(c, s.blocks.reserve(std::max<size_t>(nblk, 4) * 4, st));
+        if (slot == 1) LSB_CU(c, s.points_b.reserve(R * 32, st));
     }
     if (!dirty) return 0;
     c->h_sensors.assign(ns, SensorDev{});
@@ -582,39 +599,60 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count)
         d.count = c->d_counts.as<uint32_t>() + i; d.block_counts = s.blocks.as<uint32_t>();
         unit += (d.n_rays + 31) / 32;
     }
+    c->h_sensors_b = c->h_sensors;
+    for (size_t i = 0; i < ns; ++i) {
+        c->h_sensors_b[i].points = c->sensors[i].points_b.as<uint8_t>();      // null until slot 1 is first used
+        c->h_sensors_b[i].count = c->d_counts.as<uint32_t>() + kMaxSensors + i;
+    }
     LSB_CU(c, c->d_sensors.reserve(ns * sizeof(SensorDev), st));
+    LSB_CU(c, c->d_sensors_b.reserve(ns * sizeof(SensorDev), st));
     LSB_CU(c, cudaMemcpyAsync(c->d_sensors.p, c->h_sensors.data(), ns * sizeof(SensorDev), cudaMemcpyHostToDevice, st));
+    LSB_CU(c, cudaMemcpyAsync(c->d_sensors_b.p, c->h_sensors_b.data(), ns * sizeof(SensorDev), cudaMemcpyHostToDevice, st));
     c->sensors_dirty = false;
     return 0;
 }
 
-template <int MODE>
+template <int MODE, bool STATS>
 static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
 {
-    const size_t smem = (MODE == 0) ? (size_t)P.top_cap * 64 : 0;
-    static bool attr_set[4] = {false, false, false, false};
-    if (MODE == 0 && !attr_set[MODE]) {
-        LSB_CU(c, cudaFuncSetAttribute(k_trace<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set[MODE] = true;
+    constexpr bool TOP = (MODE == 4);
+    const size_t smem = TOP ? (size_t)P.top_cap * 64 : 0;
+    static bool attr_set = false;          // one flag per instantiation
+    if (TOP && !attr_set) {
+        LSB_CU(c, cudaFuncSetAttribute(k_trace<MODE, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
     }
     int grid;
     if (MODE == 2) {
         grid = (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32);
     } else {
         int per_sm = c->opt_ctas_per_sm;
-        if (per_sm <= 0) LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<MODE>, kTraceThreads, smem));
+        if (per_sm <= 0) LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<MODE, STATS>, kTraceThreads, smem));
         if (per_sm <= 0) return fail(c, LSB200_ERR_CUDA, "trace kernel does not fit on an SM (smem %zu)", smem);
         grid = c->sm_count * per_sm;
         grid = std::min(grid, (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32));
         grid = std::max(grid, 1);
     }
-    k_trace<MODE><<<grid, kTraceThreads, smem, c->stream>>>(P);
+    k_trace<MODE, STATS><<<grid, kTraceThreads, smem, c->stream>>>(P);
     c->stats.trace_grid = grid; c->stats.trace_block = kTraceThreads;
     count_launch(c);
     return 0;
 }
 
-static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags)
+template <bool STATS>
+static int launch_trace_mode(lsb200_ctx *c, const TraceParams &P, int n_units, int mode)
+{
+    switch (mode) {
+    case 0: return launch_trace<0, STATS>(c, P, n_units);
+    case 1: return launch_trace<1, STATS>(c, P, n_units);
+    case 2: return launch_trace<2, STATS>(c, P, n_units);
+    case 3: return launch_trace<3, STATS>(c, P, n_units);
+    case 4: return launch_trace<4, STATS>(c, P, n_units);
+    default: return launch_trace<5, STATS>(c, P, n_units);
+    }
+}
+
+static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int slot = 0)
 {
     if (first < 0 || count <= 0 || (size_t)(first + count) > c->sensors.size())
         return fail(c, LSB200_ERR_INVALID, "trace: bad sensor range [%d, %d)", first, first + count);
@@ -622,10 +660,12 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags)
         return fail(c, LSB200_ERR_INVALID, "trace: sensor-frame contexts hold exactly one sensor (index 0)");
     DeviceGuard dg(c->device);
     cudaStream_t st = c->stream;
-    if (int rc = prepare_sensors(c, first, count)) return rc;
+    if (int rc = prepare_sensors(c, first, count, slot)) return rc;
+    uint32_t *d_cnt = c->d_counts.as<uint32_t>() + (slot ? kMaxSensors : 0);
+    const SensorDev *d_sens = slot ? c->d_sensors_b.as<SensorDev>() : c->d_sensors.as<SensorDev>();
     if (c->geoms.empty() || c->n_tris == 0) {
         // empty scene: an initialised, empty cloud and -1 (SRC/OptixTracer.cpp:279-288)
-        LSB_CU(c, cudaMemsetAsync(c->d_counts.as<uint32_t>() + first, 0, (size_t)count * 4, st));
+        LSB_CU(c, cudaMemsetAsync(d_cnt + first, 0, (size_t)count * 4, st));
         for (int i = first; i < first + count; ++i) {
             Sensor &s = c->sensors[i];
             LSB_CU(c, cudaMemsetAsync(s.tri.p, 0xFF, (size_t)s.n_rays() * 4, st));          // -1
@@ -637,7 +677,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags)
     TraceParams P{};
     P.nodes = c->d_nodes.as<float4>(); P.tris = c->d_tris.as<float4>(); P.leaf_ids = c->d_leaf_ids.as<int32_t>();
     P.bounds = c->d_bounds.as<uint32_t>(); P.n_top = c->d_misc.as<int>();
-    P.sensors = c->d_sensors.as<SensorDev>() ; P.n_sensors = (int)c->sensors.size();
+    P.sensors = d_sens; P.n_sensors = (int)c->sensors.size();
     P.top_cap = c->built_top; P.n_tris = c->n_tris;
     P.world_frame = c->frame_mode == LSB200_FRAME_WORLD;
     P.flags = flags;
@@ -649,17 +689,37 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags)
     P.unit_lo = unit_lo; P.n_units = unit_hi;
     const bool timing = c->opt_timing != 0;
     const bool unordered_points = !(flags & (LSB200_TRACE_ORDERED | LSB200_TRACE_NO_POINTS));
-    if (unordered_points) LSB_CU(c, cudaMemsetAsync(c->d_counts.as<uint32_t>() + first, 0, (size_t)count * 4, st));
+    if (unordered_points) LSB_CU(c, cudaMemsetAsync(d_cnt + first, 0, (size_t)count * 4, st));
     if (timing) cudaEventRecord(c->ev[8], st);
     int mode = c->opt_traversal;
-    if (mode == 0 && c->built_top == 0) mode = 1;
     int rc = 0;
     const int n_units = unit_hi - unit_lo;
-    switch (mode) {
-    case 0: rc = launch_trace<0>(c, P, n_units); break;
-    case 1: rc = launch_trace<1>(c, P, n_units); break;
-    case 2: rc = launch_trace<2>(c, P, n_units); break;
-    default: rc = launch_trace<3>(c, P, n_units); break;
+    if (mode == 0) {
+        // octant queues: depend on the sensor table only, rebuilt when it (or the traced range) changes
+        const int wf = P.world_frame ? 1 : 0;
+        if (c->units_epoch != c->sensors_epoch || c->units_first != first || c->units_count != count || c->units_world != wf) {
+            LSB_CU(c, c->d_unit_oct.reserve((size_t)n_units, st));
+            LSB_CU(c, c->d_unit_list.reserve((size_t)n_units * 4, st));
+            LSB_CU(c, c->d_oct_hist.reserve(32 * 4, st));
+            LSB_CU(c, cudaMemsetAsync(c->d_oct_hist.p, 0, 32 * 4, st));
+            const unsigned blocks = (unsigned)((n_units + 255) / 256);
+            k_classify_units<<<blocks, 256, 0, st>>>(d_sens, P.n_sensors, unit_lo, unit_hi, wf, c->d_unit_oct.as<uint8_t>(),
+                                                     c->d_oct_hist.as<uint32_t>());
+            k_scatter_units<<<blocks, 256, 0, st>>>(unit_lo, unit_hi, c->d_unit_oct.as<uint8_t>(), c->d_oct_hist.as<uint32_t>(),
+                                                    c->d_oct_hist.as<uint32_t>() + 16, c->d_unit_list.as<int>());
+            count_launch(c, 2);
+            c->units_epoch = c->sensors_epoch; c->units_first = first; c->units_count = count; c->units_world = wf;
+        }
+        P.unit_list = c->d_unit_list.as<int>();
+        P.oct_hist = c->d_oct_hist.as<uint32_t>();
+    }
+    if (c->opt_stats) {
+        LSB_CU(c, c->d_counters.reserve(kCntCount * sizeof(unsigned long long), st));
+        LSB_CU(c, cudaMemsetAsync(c->d_counters.p, 0, kCntCount * sizeof(unsigned long long), st));
+        P.counters = c->d_counters.as<unsigned long long>();
+        rc = launch_trace_mode<true>(c, P, n_units, mode);
+    } else {
+        rc = launch_trace_mode<false>(c, P, n_units, mode);
     }
     if (rc) return rc;
     if (timing) cudaEventRecord(c->ev[9], st);
@@ -667,7 +727,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags)
         int max_rays = 0;
         for (int i = first; i < first + count; ++i) max_rays = std::max(max_rays, c->sensors[i].n_rays());
         dim3 grid((unsigned)((max_rays + kCompactRays - 1) / kCompactRays), (unsigned)count);
-        const SensorDev *sd = c->d_sensors.as<SensorDev>();
+        const SensorDev *sd = d_sens;
         k_count_hits<<<grid, kCompactThreads, 0, st>>>(sd, first);
         k_scan_counts<<<count, 256, 0, st>>>(sd, first);
         k_scatter_hits<<<grid, kCompactThreads, 0, st>>>(sd, first, flags);
@@ -761,6 +821,74 @@ int lsb200_fetch_batch(lsb200_ctx *c, int first, int count, void *const *outs, c
     return rc;
 }
 
+// Pipelined frames: frame f's point clouds travel to the host on the copy stream while frame f+1 is being
+// transformed, rebuilt and traced on the compute stream (two output slots, events between the streams).
+int lsb200_run_frames(lsb200_ctx *c, const lsb200_frame *frames, int n_frames, int first, int count, int commit_mode,
+                      uint32_t flags)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (!frames || n_frames <= 0 || first < 0 || count <= 0 || (size_t)(first + count) > c->sensors.size() || count > kMaxSensors)
+        return fail(c, LSB200_ERR_INVALID, "run_frames: bad arguments");
+    if (commit_mode < 0 || commit_mode > 2) return fail(c, LSB200_ERR_INVALID, "run_frames: bad commit mode %d", commit_mode);
+    for (int f = 0; f < n_frames; ++f)
+        if (!frames[f].out_points || !frames[f].capacities || !frames[f].n_pts)
+            return fail(c, LSB200_ERR_INVALID, "run_frames: frame %d has null output arrays", f);
+    DeviceGuard dg(c->device);
+    cudaStream_t st = c->stream, cs = c->copy_stream;
+    flags &= ~(uint32_t)LSB200_TRACE_NO_POINTS;
+    const size_t rec = record_bytes(flags);
+    int result = LSB200_OK;
+    bool slot_used[2] = {false, false};
+
+    auto finish = [&](int f) -> int {             // frame f is traced (or being traced): counts, then the clouds
+        const int slot = f & 1;
+        LSB_CU(c, cudaEventSynchronize(c->ev_traced[slot]));
+        const uint32_t *hc = c->h_count + 16 + (size_t)slot * kMaxSensors;
+        for (int i = 0; i < count; ++i) {
+            const Sensor &s = c->sensors[first + i];
+            const uint32_t n = hc[first + i];
+            frames[f].n_pts[i] = n;
+            const size_t cap = frames[f].capacities[i];
+            if (n > cap) result = fail(c, LSB200_ERR_CAPACITY, "run_frames: frame %d sensor %d has %u points, capacity %zu", f, first + i, n, cap);
+            const size_t ncopy = std::min<size_t>(n, cap);
+            const void *src = slot ? s.points_b.p : s.points.p;
+            if (frames[f].out_points[i] && ncopy)
+                LSB_CU(c, cudaMemcpyAsync(frames[f].out_points[i], src, ncopy * rec, cudaMemcpyDeviceToHost, cs));
+        }
+        LSB_CU(c, cudaEventRecord(c->ev_copied[slot], cs));
+        return 0;
+    };
+    auto body = [&]() -> int {
+        for (int f = 0; f < n_frames; ++f) {
+            const int slot = f & 1;
+            if (slot_used[slot]) LSB_CU(c, cudaStreamWaitEvent(st, c->ev_copied[slot], 0));   // frame f-2 has left the slot
+            size_t k = 0;
+            for (auto &kv : c->geoms) {
+                Geometry &g = kv.second;
+                const void *v = (frames[f].verts && frames[f].verts[k]) ? frames[f].verts[k] : nullptr;
+                if (v) { if (int rc = upload_geometry(c, g, v, g.stride, nullptr)) return rc; }
+                if (frames[f].affines) std::memcpy(g.A, frames[f].affines + 12 * k, sizeof(g.A));
+                ++k;
+            }
+            if (int rc = commit_locked(c, commit_mode)) return rc;
+            if (int rc = trace_locked(c, first, count, flags, slot)) return rc;
+            LSB_CU(c, cudaMemcpyAsync(c->h_count + 16 + (size_t)slot * kMaxSensors + first,
+                                      c->d_counts.as<uint32_t>() + (size_t)slot * kMaxSensors + first, (size_t)count * 4,
+                                      cudaMemcpyDeviceToHost, st));
+            LSB_CU(c, cudaEventRecord(c->ev_traced[slot], st));
+            slot_used[slot] = true;
+            if (f > 0) { if (int rc = finish(f - 1)) return rc; }
+        }
+        return finish(n_frames - 1);
+    };
+    const int rc = body();
+    cudaStreamSynchronize(cs);
+    cudaStreamSynchronize(st);
+    if (rc) return rc;
+    return result;
+}
+
 int lsb200_trace_raw(lsb200_ctx *c, int idx, float *t_out, int32_t *tri_out)
 {
     if (!c) return LSB200_ERR_INVALID;
@@ -829,6 +957,19 @@ int lsb200_get_stats(lsb200_ctx *c, lsb200_stats *out)
         c->stats.top_nodes = c->built_top > 0 ? ntop : 0;
     }
     *out = c->stats;
+    return LSB200_OK;
+}
+
+int lsb200_get_trace_counters(lsb200_ctx *c, uint64_t *out, int n)
+{
+    if (!c || !out || n <= 0) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (!c->d_counters.p) return fail(c, LSB200_ERR_STATE, "trace counters: no LSB200_OPT_TRACE_STATS launch yet");
+    DeviceGuard dg(c->device);
+    unsigned long long tmp[kCntCount];
+    LSB_CU(c, cudaMemcpyAsync(tmp, c->d_counters.p, sizeof(tmp), cudaMemcpyDeviceToHost, c->stream));
+    LSB_CU(c, cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < n; ++k) out[k] = k < kCntCount ? (uint64_t)tmp[k] : 0;
     return LSB200_OK;
 }
 

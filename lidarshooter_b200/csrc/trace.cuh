@@ -26,8 +26,14 @@ struct TraceParams {
     int top_cap, n_tris;
     int world_frame;
     uint32_t flags;
-    uint32_t *work;               // [0] next unit, [1] finished CTAs
+    uint32_t *work;               // [0] next unit, [1] finished CTAs, [2..10] next entry of each octant queue
+    unsigned long long *counters; // STATS builds only: see TraceCounter
+    const int *unit_list;         // MODE 0: unit ids grouped by octant class
+    const uint32_t *oct_hist;     // MODE 0: [9] units per class (0..7 octants, 8 mixed)
 };
+
+// Instrumented (STATS) launches accumulate these per-launch totals (lsb200_get_trace_counters).
+enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUniform, kCntUnitsMixed, kCntMaxStack, kCntHits, kCntCulled, kCntCount };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -106,10 +112,31 @@ __device__ __forceinline__ void test_leaf(const TraceParams &P, int ref, const R
     }
 }
 
+struct RayStats { unsigned nodes, leaves, tris, max_sp, culled; };
+
+// Entry / exit distance of one child box from the six slab products.  OCT 0..7: the signs of (dx, dy, dz) are
+// known (bit k set = component k negative), so the near and far plane of every slab are picked by name instead
+// of by min/max -- 6 FMNMX fewer per child.  OCT 8: generic min/max form (also relaxes the exit by 4 ulp).
+template <int OCT>
+__device__ __forceinline__ void slab_nf(float l0, float h0, float l1, float h1, float l2, float h2, float far_lim,
+                                        float &n, float &f)
+{
+    if (OCT < 8) {
+        n = fmaxf(fmaxf((OCT & 1) ? h0 : l0, (OCT & 2) ? h1 : l1), fmaxf((OCT & 4) ? h2 : l2, 0.0f));
+        f = fminf(fminf((OCT & 1) ? l0 : h0, (OCT & 2) ? l1 : h1), fminf((OCT & 4) ? l2 : h2, far_lim));
+    } else {
+        n = fmaxf(fmaxf(fminf(l0, h0), fminf(l1, h1)), fmaxf(fminf(l2, h2), 0.0f));
+        f = fminf(fminf(fmaxf(l0, h0), fmaxf(l1, h1)), fminf(fmaxf(l2, h2), far_lim)) * 1.0000005f;
+    }
+}
+
 // Closest hit of one ray.  TOP: node references below n_top are read from the shared-memory copy.
-template <bool TOP>
+// OCT 0..7: sign-specialised slab test (the caller guarantees the ray's direction signs); 8: generic.
+// Every form only ever rejects a box that the eps-widened exact slab test rejects, so the per-ray results do
+// not depend on the form.
+template <bool TOP, int OCT, bool STATS>
 __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_top, int n_top, float eps, const Ray &r,
-                                          float &best_out, int &bi_out)
+                                          float &best_out, int &bi_out, RayStats &rs)
 {
     // slab set-up: t_lo = (lo - (o + eps)) * inv, t_hi = (hi - (o - eps)) * inv, in FMA form
     const float tiny = 1e-30f;
@@ -121,8 +148,11 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
     const int cap = P.top_cap;
 
     float best = INFINITY;
+    float far_lim = INFINITY;          // best * (1 + 4 ulp), refreshed when best changes
     int bi = -1;
-    int stack[kStackSize];
+    // stack entries carry the entry distance of the deferred child: when the entry is popped after a closer
+    // hit has been found it is dropped without loading the node
+    int2 stack[kStackSize];
     int sp = 0;
     int cur = TOP ? 0 : cap;          // root: top slot 0, or Karras node 0
     if (TOP && n_top == 0) cur = cap;
@@ -135,34 +165,100 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
                 const float4 *n = P.nodes + 4 * (size_t)cur;
                 q0 = __ldg(n); q1 = __ldg(n + 1); q2 = __ldg(n + 2); q3 = __ldg(n + 3);
             }
-            const float far_lim = best * 1.0000005f;
-            // child 0
-            float l0 = fmaf(q0.x, ix, ax), h0 = fmaf(q0.y, ix, bx);
-            float l1 = fmaf(q0.z, iy, ay), h1 = fmaf(q0.w, iy, by);
-            float l2 = fmaf(q2.x, iz, az), h2 = fmaf(q2.y, iz, bz);
-            const float n0 = fmaxf(fmaxf(fminf(l0, h0), fminf(l1, h1)), fmaxf(fminf(l2, h2), 0.0f));
-            const float f0 = fminf(fminf(fmaxf(l0, h0), fmaxf(l1, h1)), fminf(fmaxf(l2, h2), far_lim));
-            // child 1
-            l0 = fmaf(q1.x, ix, ax); h0 = fmaf(q1.y, ix, bx);
-            l1 = fmaf(q1.z, iy, ay); h1 = fmaf(q1.w, iy, by);
-            l2 = fmaf(q2.z, iz, az); h2 = fmaf(q2.w, iz, bz);
-            const float n1 = fmaxf(fmaxf(fminf(l0, h0), fminf(l1, h1)), fmaxf(fminf(l2, h2), 0.0f));
-            const float f1 = fminf(fminf(fmaxf(l0, h0), fmaxf(l1, h1)), fminf(fmaxf(l2, h2), far_lim));
-            const bool hit0 = n0 <= f0 * 1.0000005f, hit1 = n1 <= f1 * 1.0000005f;
+            if (STATS) ++rs.nodes;
+            float n0, f0, n1, f1;
+            slab_nf<OCT>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
+                         fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
+            slab_nf<OCT>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
+                         fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
+            const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
             const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
             if (hit0 && hit1) {
                 const bool swap = n1 < n0;
                 cur = swap ? c1 : c0;
-                stack[sp++] = swap ? c0 : c1;
+                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
                 continue;
             }
             if (hit0) { cur = c0; continue; }
             if (hit1) { cur = c1; continue; }
         } else {
+            if (STATS) { ++rs.leaves; rs.tris += (unsigned)(((~cur) >> kLeafShift) + 1); }
             test_leaf(P, cur, r, best, bi);
+            far_lim = best * 1.0000005f;
         }
-        if (sp == 0) break;
-        cur = stack[--sp];
+        bool found = false;
+        while (sp > 0) {
+            const int2 e = stack[--sp];
+            if (__int_as_float(e.y) <= far_lim * 1.0000005f) { cur = e.x; found = true; break; }
+            if (STATS) ++rs.culled;
+        }
+        if (!found) break;
+    }
+    best_out = best;
+    bi_out = bi;
+}
+
+// "while-while" form of trace_ray (Aila & Laine 2009): an inner loop that only visits nodes, left by a lane when
+// it reaches a leaf (or runs out of work); the warp reconverges behind it, so the (long) triangle tests of the
+// lanes run together instead of being interleaved with other lanes' node visits.  Generic slab test, global nodes.
+template <bool STATS>
+__device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, const Ray &r, float &best_out, int &bi_out,
+                                             RayStats &rs)
+{
+    const float tiny = 1e-30f;
+    const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
+    const float iy = 1.0f / (fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
+    const float iz = 1.0f / (fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
+    const float ax = -(r.ox + eps) * ix, ay = -(r.oy + eps) * iy, az = -(r.oz + eps) * iz;
+    const float bx = -(r.ox - eps) * ix, by = -(r.oy - eps) * iy, bz = -(r.oz - eps) * iz;
+    constexpr int kDone = 0x7fffffff;       // never a node index (n_tris < 2^28)
+    float best = INFINITY, far_lim = INFINITY;
+    int bi = -1;
+    int2 stack[kStackSize];
+    int sp = 0;
+    int cur = P.top_cap;
+    while (cur != kDone) {
+        while ((unsigned)cur < (unsigned)kDone) {           // cur >= 0 and not kDone: an inner node
+            const float4 *n = P.nodes + 4 * (size_t)cur;
+            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2), q3 = __ldg(n + 3);
+            if (STATS) ++rs.nodes;
+            float n0, f0, n1, f1;
+            slab_nf<8>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
+                       fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
+            slab_nf<8>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
+                       fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
+            const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
+            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+            if (hit0 && hit1) {
+                const bool swap = n1 < n0;
+                cur = swap ? c1 : c0;
+                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
+            } else if (hit0) {
+                cur = c0;
+            } else if (hit1) {
+                cur = c1;
+            } else {
+                cur = kDone;
+                while (sp > 0) {
+                    const int2 e = stack[--sp];
+                    if (__int_as_float(e.y) <= far_lim * 1.0000005f) { cur = e.x; break; }
+                    if (STATS) ++rs.culled;
+                }
+            }
+        }
+        if (cur < 0) {
+            if (STATS) { ++rs.leaves; rs.tris += (unsigned)(((~cur) >> kLeafShift) + 1); }
+            test_leaf(P, cur, r, best, bi);
+            far_lim = best * 1.0000005f;
+            cur = kDone;
+            while (sp > 0) {
+                const int2 e = stack[--sp];
+                if (__int_as_float(e.y) <= far_lim * 1.0000005f) { cur = e.x; break; }
+                if (STATS) ++rs.culled;
+            }
+        }
     }
     best_out = best;
     bi_out = bi;
@@ -214,18 +310,123 @@ __device__ __forceinline__ void hit_point(const SensorDev &S, uint32_t flags, fl
     }
 }
 
-// MODE 0: persistent CTAs, top BVH levels staged into shared memory by TMA bulk copy
-// MODE 1: persistent CTAs, all nodes from global memory (L1/L2)
-// MODE 2: one thread per ray, no work fetching
+// Ray `ray` of sensor S: d_s = (sin t cos p, sin t sin p, cos t) (SRC/LidarDevice.cpp:319-321), ray id = channel * H
+// + azimuth; world-frame mode moves the ray instead of the scene (o = T, d = R d_s).  Used by the traversal AND by
+// the octant classification, so both see bit-identical direction signs.
+__device__ __forceinline__ void make_ray(const SensorDev &S, int world_frame, int ray, Ray &r, float &dsx, float &dsy,
+                                         float &dsz, int &v, float &omax)
+{
+    v = ray / S.H;
+    const int h = ray - v * S.H;
+    const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v), sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
+    dsx = __fmul_rn(st, cp); dsy = __fmul_rn(st, sp_); dsz = ct;
+    if (world_frame) {
+        r.ox = S.T[0]; r.oy = S.T[1]; r.oz = S.T[2];
+        r.dx = __fadd_rn(__fadd_rn(__fmul_rn(S.R[0], dsx), __fmul_rn(S.R[1], dsy)), __fmul_rn(S.R[2], dsz));
+        r.dy = __fadd_rn(__fadd_rn(__fmul_rn(S.R[3], dsx), __fmul_rn(S.R[4], dsy)), __fmul_rn(S.R[5], dsz));
+        r.dz = __fadd_rn(__fadd_rn(__fmul_rn(S.R[6], dsx), __fmul_rn(S.R[7], dsy)), __fmul_rn(S.R[8], dsz));
+        omax = fmaxf(fabsf(r.ox), fmaxf(fabsf(r.oy), fabsf(r.oz)));
+    } else {
+        r.ox = r.oy = r.oz = 0.0f; r.dx = dsx; r.dy = dsy; r.dz = dsz;
+        omax = 0.0f;
+    }
+}
+
+__device__ __forceinline__ int ray_octant(const Ray &r)
+{
+    return (int)((__float_as_uint(r.dx) >> 31) | ((__float_as_uint(r.dy) >> 31) << 1) | ((__float_as_uint(r.dz) >> 31) << 2));
+}
+
+// One 32-ray work unit: generate the rays, trace them, store t / triangle id, append the hits.
+// MODE: see k_trace.  OCT: slab form for every ray of the unit (0..7 only when classified uniform).
+template <int MODE, int OCT, bool STATS>
+__device__ __forceinline__ void process_unit(const TraceParams &P, const float4 *s_top, int n_top, float smax, int unit,
+                                             unsigned lane)
+{
+    constexpr bool TOP = (MODE == 4);
+    const int si = find_sensor_by_unit(P.sensors, P.n_sensors, unit);
+    const SensorDev &S = P.sensors[si];
+    const int ray = (unit - S.unit_base) * 32 + (int)lane;
+    const bool valid = ray < S.n_rays;
+    float best = INFINITY; int bi = -1;
+    float dsx = 0.f, dsy = 0.f, dsz = 1.f;
+    int v = 0;
+    RayStats rs{0u, 0u, 0u, 0u, 0u};
+    if (valid) {
+        Ray r;
+        float omax;
+        make_ray(S, P.world_frame, ray, r, dsx, dsy, dsz, v, omax);
+        const float eps = 8e-6f * (smax + omax) + 1e-30f;
+        if (MODE == 3) brute_ray(P, r, best, bi);
+        else if (MODE == 5) trace_ray_ww<STATS>(P, eps, r, best, bi, rs);
+        else trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, best, bi, rs);
+        S.t_out[ray] = best;
+        S.tri_out[ray] = bi;
+    }
+    if (STATS) {
+        unsigned a = __reduce_add_sync(0xffffffffu, rs.nodes), b = __reduce_add_sync(0xffffffffu, rs.leaves);
+        unsigned c = __reduce_add_sync(0xffffffffu, rs.tris), d = __reduce_max_sync(0xffffffffu, rs.max_sp);
+        unsigned cu = __reduce_add_sync(0xffffffffu, rs.culled);
+        unsigned nv = __reduce_add_sync(0xffffffffu, valid ? 1u : 0u), nh = __reduce_add_sync(0xffffffffu, (valid && bi >= 0) ? 1u : 0u);
+        if (lane == 0) {
+            atomicAdd(P.counters + kCntRays, (unsigned long long)nv); atomicAdd(P.counters + kCntNodes, (unsigned long long)a);
+            atomicAdd(P.counters + kCntLeaves, (unsigned long long)b); atomicAdd(P.counters + kCntTris, (unsigned long long)c);
+            atomicAdd(P.counters + kCntHits, (unsigned long long)nh); atomicMax(P.counters + kCntMaxStack, (unsigned long long)d);
+            atomicAdd(P.counters + kCntCulled, (unsigned long long)cu);
+            if (MODE == 0) atomicAdd(P.counters + (OCT < 8 ? kCntUnitsUniform : kCntUnitsMixed), 1ull);
+        }
+    }
+    if (!(P.flags & (1u | 8u))) {     // neither ORDERED nor NO_POINTS: warp-aggregated atomic append
+        const bool hit = valid && bi >= 0;
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (m) {
+            uint32_t base = 0;
+            if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(S.count, (uint32_t)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            if (hit) {
+                float x, y, z;
+                hit_point(S, P.flags, best, dsx, dsy, dsz, x, y, z);
+                store_point(S.points, base + __popc(m & lanemask_lt()), P.flags, x, y, z, (P.flags & 2u) ? 0 : v);
+            }
+        }
+    }
+}
+
+// MODE 0 only: drains the queue of octant OCT (units whose 32 rays all have the direction signs OCT; 8 = mixed).
+template <int OCT, bool STATS>
+__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane)
+{
+    int begin = 0;
+#pragma unroll
+    for (int o = 0; o < OCT; ++o) begin += (int)__ldg(P.oct_hist + o);
+    const int count = (int)__ldg(P.oct_hist + OCT);
+    while (true) {
+        int k = 0;
+        if (lane == 0) k = (int)atomicAdd(&P.work[2 + OCT], 1u);
+        k = __shfl_sync(0xffffffffu, k, 0);
+        if (k >= count) break;
+        process_unit<0, OCT, STATS>(P, nullptr, 0, smax, __ldg(P.unit_list + begin + k), lane);
+    }
+}
+
+// MODE 0: persistent CTAs, nodes through L1/L2, units pre-sorted by ray octant (k_classify_units / k_scatter_units)
+//         and drained octant by octant with a sign-specialised slab test -- every CTA runs the same small loop at
+//         a time, so the eight specialisations do not compete for the instruction cache
+// MODE 1: persistent CTAs, nodes through L1/L2, generic min/max slab test, units in ray order
+// MODE 2: one thread per ray, no work fetching (generic slab test)
 // MODE 3: brute force (persistent)
-template <int MODE>
+// MODE 4: MODE 1 + top BVH levels staged into shared memory by TMA bulk copy
+// MODE 5: MODE 1 in while-while form (node loop and leaf tests separated)
+// STATS: per-ray node / leaf / triangle counters summed into P.counters (diagnostic launches only)
+template <int MODE, bool STATS>
 __global__ void __launch_bounds__(kTraceThreads, 2) k_trace(TraceParams P)
 {
+    constexpr bool TOP = (MODE == 4);
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float4 *s_top = reinterpret_cast<float4 *>(smem_raw);
     __shared__ __align__(8) uint64_t s_bar;
     int n_top = 0;
-    if (MODE == 0) {
+    if (TOP) {
         n_top = min(*P.n_top, P.top_cap);
         if (threadIdx.x == 0) mbar_init(&s_bar, 1);
         __syncthreads();
@@ -245,67 +446,85 @@ __global__ void __launch_bounds__(kTraceThreads, 2) k_trace(TraceParams P)
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
 
     const unsigned lane = lane_id();
-    const int warps_per_cta = kTraceThreads / 32;
-    int unit = (MODE == 2) ? P.unit_lo + (int)(blockIdx.x * warps_per_cta + (threadIdx.x >> 5)) : 0;
-    while (true) {
-        if (MODE != 2) {
+    if (MODE == 0) {
+        run_phase<8, STATS>(P, smax, lane);
+        run_phase<0, STATS>(P, smax, lane); run_phase<1, STATS>(P, smax, lane);
+        run_phase<2, STATS>(P, smax, lane); run_phase<3, STATS>(P, smax, lane);
+        run_phase<4, STATS>(P, smax, lane); run_phase<5, STATS>(P, smax, lane);
+        run_phase<6, STATS>(P, smax, lane); run_phase<7, STATS>(P, smax, lane);
+    } else if (MODE == 2) {
+        const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
+        if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit, lane);
+    } else {
+        while (true) {
+            int unit = 0;
             if (lane == 0) unit = P.unit_lo + (int)atomicAdd(&P.work[0], 1u);
             unit = __shfl_sync(0xffffffffu, unit, 0);
+            if (unit >= P.n_units) break;
+            process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit, lane);
         }
-        if (unit >= P.n_units) break;
-        const int si = find_sensor_by_unit(P.sensors, P.n_sensors, unit);
-        const SensorDev &S = P.sensors[si];
-        const int ray = (unit - S.unit_base) * 32 + (int)lane;
-        const bool valid = ray < S.n_rays;
-        float best = INFINITY; int bi = -1;
-        float dsx = 0.f, dsy = 0.f, dsz = 1.f;
-        int v = 0;
-        if (valid) {
-            v = ray / S.H;
-            const int h = ray - v * S.H;
-            // d_s = (sin t cos p, sin t sin p, cos t)  (SRC/LidarDevice.cpp:319-321); ray id = channel * H + azimuth
-            const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v), sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
-            dsx = __fmul_rn(st, cp); dsy = __fmul_rn(st, sp_); dsz = ct;
-            Ray r;
-            float omax = 0.0f;
-            if (P.world_frame) {
-                r.ox = S.T[0]; r.oy = S.T[1]; r.oz = S.T[2];
-                r.dx = __fadd_rn(__fadd_rn(__fmul_rn(S.R[0], dsx), __fmul_rn(S.R[1], dsy)), __fmul_rn(S.R[2], dsz));
-                r.dy = __fadd_rn(__fadd_rn(__fmul_rn(S.R[3], dsx), __fmul_rn(S.R[4], dsy)), __fmul_rn(S.R[5], dsz));
-                r.dz = __fadd_rn(__fadd_rn(__fmul_rn(S.R[6], dsx), __fmul_rn(S.R[7], dsy)), __fmul_rn(S.R[8], dsz));
-                omax = fmaxf(fabsf(r.ox), fmaxf(fabsf(r.oy), fabsf(r.oz)));
-            } else {
-                r.ox = r.oy = r.oz = 0.0f; r.dx = dsx; r.dy = dsy; r.dz = dsz;
-            }
-            const float eps = 8e-6f * (smax + omax) + 1e-30f;
-            if (MODE == 3) brute_ray(P, r, best, bi);
-            else trace_ray<MODE == 0>(P, s_top, n_top, eps, r, best, bi);
-            S.t_out[ray] = best;
-            S.tri_out[ray] = bi;
-        }
-        if (!(P.flags & (1u | 8u))) {     // neither ORDERED nor NO_POINTS: warp-aggregated atomic append
-            const bool hit = valid && bi >= 0;
-            const unsigned m = __ballot_sync(0xffffffffu, hit);
-            if (m) {
-                uint32_t base = 0;
-                if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(S.count, (uint32_t)__popc(m));
-                base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-                if (hit) {
-                    float x, y, z;
-                    hit_point(S, P.flags, best, dsx, dsy, dsz, x, y, z);
-                    store_point(S.points, base + __popc(m & lanemask_lt()), P.flags, x, y, z, (P.flags & 2u) ? 0 : v);
-                }
-            }
-        }
-        if (MODE == 2) break;
     }
     if (MODE != 2) {
         // the last CTA to leave re-arms the work counters for the next launch
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence();
-            if (atomicAdd(&P.work[1], 1u) == gridDim.x - 1) { P.work[0] = 0; P.work[1] = 0; __threadfence(); }
+            if (atomicAdd(&P.work[1], 1u) == gridDim.x - 1) {
+                P.work[0] = 0; P.work[1] = 0;
+                if (MODE == 0) for (int o = 0; o < 9; ++o) P.work[2 + o] = 0;
+                __threadfence();
+            }
         }
+    }
+}
+
+// ---- octant classification of the 32-ray units (MODE 0) ----------------------------------------------------
+// unit_oct[u - unit_lo] = common octant of the unit's rays (bit k = sign bit of direction component k) or 8 when
+// they disagree; hist[o] = number of units per class.  Only depends on the sensor table: cached by the host.
+__global__ void __launch_bounds__(256) k_classify_units(const SensorDev *__restrict__ sensors, int n_sensors, int unit_lo,
+                                                        int unit_hi, int world_frame, uint8_t *__restrict__ unit_oct,
+                                                        uint32_t *__restrict__ hist)
+{
+    const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    int oct = -1;
+    if (u < unit_hi) {
+        const SensorDev &S = sensors[find_sensor_by_unit(sensors, n_sensors, u)];
+        const int ray0 = (u - S.unit_base) * 32;
+        for (int l = 0; l < 32 && ray0 + l < S.n_rays; ++l) {
+            Ray r; float a, b, c, om; int v;
+            make_ray(S, world_frame, ray0 + l, r, a, b, c, v, om);
+            const int o = ray_octant(r);
+            oct = (oct < 0 || oct == o) ? o : 8;
+            if (oct == 8) break;
+        }
+        if (oct < 0) oct = 8;
+        unit_oct[u - unit_lo] = (uint8_t)oct;
+    }
+#pragma unroll
+    for (int o = 0; o < 9; ++o) {
+        const unsigned m = __ballot_sync(0xffffffffu, oct == o);
+        if (m && lane_id() == 0) atomicAdd(&hist[o], (uint32_t)__popc(m));
+    }
+}
+
+// unit_list = unit ids grouped by class (class o occupies [sum hist[<o], +hist[o])), in chunks of up to 32
+// consecutive units (one atomic per class per warp), so neighbouring units stay neighbours in the queues.
+__global__ void __launch_bounds__(256) k_scatter_units(int unit_lo, int unit_hi, const uint8_t *__restrict__ unit_oct,
+                                                       const uint32_t *__restrict__ hist, uint32_t *__restrict__ cursor,
+                                                       int *__restrict__ unit_list)
+{
+    const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    const int oct = (u < unit_hi) ? (int)unit_oct[u - unit_lo] : -1;
+    uint32_t base = 0;
+#pragma unroll
+    for (int o = 0; o < 9; ++o) {
+        const unsigned m = __ballot_sync(0xffffffffu, oct == o);
+        if (m == 0) { base += hist[o]; continue; }
+        uint32_t off = 0;
+        if (lane_id() == (unsigned)(__ffs(m) - 1)) off = atomicAdd(&cursor[o], (uint32_t)__popc(m));
+        off = __shfl_sync(0xffffffffu, off, __ffs(m) - 1);
+        if (oct == o) unit_list[base + off + __popc(m & lanemask_lt())] = u;
+        base += hist[o];
     }
 }
 

@@ -89,7 +89,7 @@ def test_xt32_reference_counts_and_golden(meshes, golden, uid, n_ground, n_both)
     ctx.close()
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5])
 @pytest.mark.parametrize("leaf", [1, 4, 8])
 def test_traversal_variants_agree(meshes, golden, mode, leaf):
     ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: mode, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TOP_NODES: 256})
@@ -177,6 +177,51 @@ def test_world_frame_multi_sensor(meshes):
         assert np.array_equal(pts, ref["points"])
         rc, t, tri = ctx.trace_raw(k)
         assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+    ctx.close()
+
+
+@pytest.mark.parametrize("flags,vert_upload", [(capi.TRACE_ORDERED, False), (0, True), (capi.TRACE_ORDERED | capi.TRACE_XYZI16, True)])
+def test_run_frames_pipelined_matches_per_frame_calls(meshes, flags, vert_upload):
+    """lsb200_run_frames (two output slots, D2H of frame f overlapped with frame f+1) == the per-frame
+    updateGeometry / commitScene / traceScene sequence, and == the oracle, for two sensors along a trajectory."""
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    sens = []
+    for k, uid in enumerate(("0000", "0001")):
+        args = xt32_sensor_args(uid)
+        ctx.set_sensor(*args, index=k)
+        sens.append(lso.Sensor(*args))
+    gv, gt, bv, bt = meshes["ground_v"], meshes["ground_t"], meshes["ben_v"], meshes["ben_t"]
+    add_mesh(ctx, "ground", gv, gt)
+    add_mesh(ctx, "ben", bv, bt)
+    poses = synth.trajectory_poses([(0.7, (0, 5, 0), (0, 0, 1))])
+    F = len(poses)
+    A = np.zeros((F, 2, 12), np.float32)
+    for f, (lin, ang) in enumerate(poses):
+        A[f, 0] = IDENT
+        A[f, 1] = lso.affine_from_components(lin, ang)
+    rec = 16 if flags & capi.TRACE_XYZI16 else 32
+    R = ctx.ray_count(0)
+    outs = [[np.zeros((R, rec), np.uint8) for _ in range(2)] for _ in range(F)]
+    ptrs = [[o.ctypes.data for o in row] for row in outs]
+    gvc, bvc = np.ascontiguousarray(gv, np.float32), np.ascontiguousarray(bv, np.float32)
+    verts = [gvc.ctypes.data, bvc.ctypes.data] if vert_upload else None
+    rc, counts = ctx.run_frames(A, ptrs, [R, R], first=0, count=2, commit_mode=capi.COMMIT_AUTO, flags=flags, verts=verts)
+    assert rc == 0, ctx.last_error()
+    for f in range(F):
+        for k in range(2):
+            ref = lso.scan(sens[k], [(gv, gt, IDENT), (bv, bt, A[f, 1])], mode=1)
+            want = ref["points"]
+            if rec == 16:
+                want = np.ascontiguousarray(want.view(np.float32).reshape(-1, 8)[:, [0, 1, 2, 4]]).view(np.uint8).reshape(-1, 16)
+            got = outs[f][k][:counts[f, k]]
+            assert counts[f, k] == want.shape[0]
+            if flags & capi.TRACE_ORDERED:
+                assert np.array_equal(got, want)
+            else:
+                assert np.array_equal(sort_rows(got), sort_rows(want))
+    # capacity error is reported, counts still filled
+    rc, counts2 = ctx.run_frames(A[:2], ptrs[:2], [10, 10], first=0, count=2, flags=flags)
+    assert rc == capi.ERR_CAPACITY and np.array_equal(counts2, counts[:2])
     ctx.close()
 
 

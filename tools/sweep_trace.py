@@ -1,0 +1,93 @@
+#!/usr/bin/env python
+"""Traversal design sweep on the bench workload (configs[3], 10 M-triangle city, 64 devices): for every
+(Morton scaling, leaf size, top-block size, kernel variant) the trace launch is timed with CUDA events and an
+instrumented launch reports nodes / leaves / triangles per ray.  Every variant's per-ray (t, triangle id) of two
+sensors is compared bit-for-bit with the first variant's.  Output: one JSON object per line (gpurun_out/...).
+
+Evidence tool, not the product path: it only calls the C ABI."""
+import argparse
+import json
+import os
+import sys
+import zlib
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep_trace.jsonl"))
+    ap.add_argument("--small", action="store_true")
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--leaves", default="1,2,4,8")
+    ap.add_argument("--modes", default="0,4,1,2")
+    ap.add_argument("--tops", default="1024")
+    ap.add_argument("--morton", default="0,1")
+    args = ap.parse_args()
+    from bench import build_workload, frame_affine
+    from lidarshooter_b200 import capi
+
+    meshes, poses, table = build_workload(args.small)
+    elev, b, e, H = table
+    R = elev.size * H
+    ns = len(poses)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    for k, (q, t) in enumerate(poses):
+        ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    for gi, (name, v, t) in enumerate(meshes):
+        assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0]) >= 0
+        assert ctx.update_geometry(name, v, t, frame_affine(0, gi)) == 0
+    os.makedirs(os.path.dirname(args.out), exist_ok=True)
+    fout = open(args.out, "w")
+    base_sig = None
+    check_sensors = (0, ns - 1)
+    ctx.set_option(capi.OPT_STAGE_TIMING, 1)
+    for mu in [int(x) for x in args.morton.split(",")]:
+        for leaf in [int(x) for x in args.leaves.split(",")]:
+            for top in [int(x) for x in args.tops.split(",")]:
+                ctx.set_option(capi.OPT_MORTON_UNIFORM, mu)
+                ctx.set_option(capi.OPT_LEAF_SIZE, leaf)
+                ctx.set_option(capi.OPT_TOP_NODES, top)
+                assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
+                st = ctx.stats()
+                build_ms = {k: round(float(getattr(st, "ms_" + k)), 4) for k in
+                            ("transform", "morton", "sort", "hierarchy", "fit", "toplevel")}
+                for mode in [int(x) for x in args.modes.split(",")]:
+                    ctx.set_option(capi.OPT_TRAVERSAL, mode)
+                    ctx.set_option(capi.OPT_TRACE_STATS, 0)
+                    ms = []
+                    for r in range(args.reps + 1):
+                        assert ctx.trace_batch(0, ns, 0) == 0, ctx.last_error()
+                        ms.append(float(ctx.stats().ms_trace))
+                    ms = ms[1:]
+                    ctx.set_option(capi.OPT_TRACE_STATS, 1)
+                    assert ctx.trace_batch(0, ns, capi.TRACE_NO_POINTS) == 0, ctx.last_error()
+                    cnt = ctx.trace_counters()
+                    ctx.set_option(capi.OPT_TRACE_STATS, 0)
+                    sig = []
+                    for s in check_sensors:
+                        rc, t, tri = ctx.trace_raw(s)
+                        assert rc == 0
+                        sig.append((zlib.crc32(t.tobytes()), zlib.crc32(tri.tobytes()), int((tri >= 0).sum())))
+                    if base_sig is None:
+                        base_sig = sig
+                    rays = max(cnt["rays"], 1)
+                    row = {"morton_uniform": mu, "leaf": leaf, "top": top, "mode": mode,
+                           "ms_trace_min": min(ms), "ms_trace_mean": float(np.mean(ms)),
+                           "mrays_per_s": ns * R / (min(ms) * 1e-3) / 1e6,
+                           "nodes_per_ray": cnt["nodes"] / rays, "leaves_per_ray": cnt["leaves"] / rays,
+                           "tris_per_ray": cnt["tris"] / rays, "max_stack": cnt["max_stack"], "culled_pops_per_ray": cnt["culled_pops"] / rays,
+                           "units_uniform": cnt["units_uniform"], "units_mixed": cnt["units_mixed"],
+                           "hit_fraction": cnt["hits"] / rays, "same_results_as_first": sig == base_sig,
+                           "grid": int(ctx.stats().trace_grid), "build_ms": build_ms}
+                    print(json.dumps(row), flush=True)
+                    fout.write(json.dumps(row) + "\n")
+                    fout.flush()
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
