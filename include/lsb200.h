@@ -69,7 +69,7 @@ enum {
                                       (default); 1 = persistent, generic slab test, ray order; 2 = one thread per ray
                                       (no persistent fetch); 3 = brute force (all triangles); 4 = variant 1 + top BVH
                                       levels staged into shared memory by TMA bulk copy; 5 = variant 1, while-while */
-    LSB200_OPT_LEAF_SIZE = 2,      /* max triangles per leaf, 1..8 (default 4) */
+    LSB200_OPT_LEAF_SIZE = 2,      /* max triangles per leaf, 1..8 (default 2) */
     LSB200_OPT_TOP_NODES = 3,      /* number of BVH nodes staged into shared memory by TMA bulk copy (default 1024) */
     LSB200_OPT_STAGE_TIMING = 4,   /* 1 = record CUDA events around every stage (lsb200_get_stats) */
     LSB200_OPT_CTAS_PER_SM = 5,    /* persistent grid = 148 * this (default 0 = occupancy query) */
