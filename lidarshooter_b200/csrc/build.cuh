@@ -16,7 +16,7 @@ struct SceneDev {
     float4 *tris;            // [n_tris * 3] leaf-ordered triangle records
     int32_t *leaf_ids;       // [n_tris] leaf order -> global triangle id
     float4 *nodes;           // [top_cap + n_tris] * 4  (top-level copy first, then Karras nodes)
-    int32_t *node_parent;    // [n_tris] internal node -> (parent << 1 | slot)
+    int32_t *node_parent;    // [n_tris] internal node -> (parent << 2 | block-local << 1 | slot), see k_hierarchy
     int32_t *leaf_parent;    // [n_tris]
     uint32_t *flags;         // [n_tris] arrival counters of the bottom-up pass (parity: never re-zeroed)
     int top_cap;             // nodes reserved for the top-level copy
@@ -134,6 +134,8 @@ __device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, i
     return (ki == kj) ? 32 + __clz((uint32_t)i ^ (uint32_t)j) : __clz(ki ^ kj);
 }
 
+constexpr int kFitBlock = 256;         // leaves per k_fit CTA
+
 __device__ __forceinline__ int leaf_ref(int first, int count) { return ~(first | ((count - 1) << kLeafShift)); }
 
 // One thread per internal node i in [0, n-1).  Node i covers sorted leaves [first, last]; its left child covers
@@ -163,8 +165,11 @@ __global__ void __launch_bounds__(256) k_hierarchy(SceneDev S, const uint32_t *_
     const int first = min(i, j), last = max(i, j);
     const int lcount = split - first + 1, rcount = last - split;
     int c0, c1;
-    if (lcount == 1) S.leaf_parent[split] = (i << 1); else S.node_parent[split] = (i << 1);
-    if (rcount == 1) S.leaf_parent[split + 1] = (i << 1) | 1; else S.node_parent[split + 1] = (i << 1) | 1;
+    // parent links: (parent << 2) | (parent's leaf range lies inside one kFitBlock-aligned block) << 1 | child slot.
+    // k_fit handles such block-local parents with shared-memory arrival flags instead of global atomics.
+    const int link = (i << 2) | ((first / kFitBlock == last / kFitBlock) ? 2 : 0);
+    if (lcount == 1) S.leaf_parent[split] = link; else S.node_parent[split] = link;
+    if (rcount == 1) S.leaf_parent[split + 1] = link | 1; else S.node_parent[split + 1] = link | 1;
     // internal children are stored in the traversal kernel's unified index space: Karras node k -> top_cap + k
     c0 = (lcount <= S.leaf_max) ? leaf_ref(first, lcount) : S.top_cap + split;
     c1 = (rcount <= S.leaf_max) ? leaf_ref(split + 1, rcount) : S.top_cap + split + 1;
@@ -176,11 +181,17 @@ __global__ void __launch_bounds__(256) k_hierarchy(SceneDev S, const uint32_t *_
 // ---- (4) leaf set-up + bottom-up AABB fit (rebuild and refit) --------------------------------------------
 // One thread per leaf slot i: gathers the triangle's transformed vertices, writes the 48-byte intersection
 // record, then climbs: it stores its box into its parent's child slot, and the second thread to arrive at a
-// node merges both slots and continues.  Arrival counters are never reset: each node receives exactly two
-// arrivals per fit, so the first arrival always sees an even count.
-__global__ void __launch_bounds__(256) k_fit(SceneDev S, const uint32_t *__restrict__ sorted_ids)
+// node merges both slots and continues.  A Karras node whose leaf range lies inside this CTA's 256 leaves (its
+// index then lies in the range too) is met by two threads of THIS CTA: its arrival flag lives in shared memory
+// and a block-scope fence orders the box store -- ~99 % of the nodes.  Only nodes that straddle CTAs use the
+// global arrival counters, which are never reset: each receives exactly two arrivals per fit, so the first
+// arrival always sees an even count.
+__global__ void __launch_bounds__(kFitBlock) k_fit(SceneDev S, const uint32_t *__restrict__ sorted_ids)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ uint32_t s_flags[kFitBlock];
+    s_flags[threadIdx.x] = 0u;
+    __syncthreads();
+    const int i = blockIdx.x * kFitBlock + threadIdx.x;
     if (i >= S.n_tris) return;
     const int g = (int)__ldg(sorted_ids + i);
     int a, b, c;
@@ -203,12 +214,18 @@ __global__ void __launch_bounds__(256) k_fit(SceneDev S, const uint32_t *__restr
     float loz = fminf(A.z, fminf(B.z, C.z)), hiz = fmaxf(A.z, fmaxf(B.z, C.z));
     int up = S.leaf_parent[i];
     while (up >= 0) {
-        const int p = up >> 1, slot = up & 1;
+        const int p = up >> 2, slot = up & 1;
         float4 *node = S.nodes + 4 * ((size_t)S.top_cap + p);
         node[slot] = make_float4(lox, hix, loy, hiy);
         reinterpret_cast<float2 *>(node + 2)[slot] = make_float2(loz, hiz);
-        __threadfence();
-        const uint32_t old = atomicAdd(&S.flags[p], 1u);
+        uint32_t old;
+        if (up & 2) {                                               // both children arrive from this CTA
+            __threadfence_block();
+            old = atomicAdd(&s_flags[p - blockIdx.x * kFitBlock], 1u);
+        } else {
+            __threadfence();
+            old = atomicAdd(&S.flags[p], 1u);
+        }
         if ((old & 1u) == 0u) return;                           // first to arrive: the sibling finishes the node
         const float4 sxy = __ldcg(node + (slot ^ 1));
         const float2 sz = __ldcg(reinterpret_cast<const float2 *>(node + 2) + (slot ^ 1));
@@ -226,7 +243,7 @@ __global__ void k_single_leaf_root(SceneDev S)
     node[1] = make_float4(INFINITY, -INFINITY, INFINITY, -INFINITY);
     reinterpret_cast<float2 *>(node + 2)[1] = make_float2(INFINITY, -INFINITY);
     node[3] = make_float4(__int_as_float(leaf_ref(0, 1)), __int_as_float(leaf_ref(0, 1)), __int_as_float(0), __int_as_float(0));
-    S.leaf_parent[0] = 0;
+    S.leaf_parent[0] = 0;            // parent 0, slot 0, global arrival counter
     S.node_parent[0] = -1;
     S.flags[0] |= 1u;    // the lone leaf arrives as the "second" child, so the counter is even again after the fit
 }

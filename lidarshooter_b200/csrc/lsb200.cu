@@ -500,7 +500,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
         mark();
     }
     // (5) leaf records + bottom-up boxes
-    k_fit<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(S, S.vals);
+    k_fit<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, 0, st>>>(S, S.vals);
     count_launch(c);
     mark();
     // (6) top-level block for the TMA-staged traversal
