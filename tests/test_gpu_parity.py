@@ -348,3 +348,99 @@ def test_heightfield_1m_tris_vs_oracle_bvh():
     rc, pts = ctx.trace_scene(0, 0)
     assert pts.shape[0] == n_hit
     ctx.close()
+
+
+@pytest.mark.parametrize("mode", [0, 1, 4, 5])
+def test_small_city_world_frame_vs_oracle_bvh(mode):
+    """BASELINE config 4 in miniature (same generator, 4 yawed sensors, world frame): every traversal variant
+    bit-exact against the oracle's CPU BVH; rebuild == refit after the buildings move."""
+    meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
+    poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
+    elev, b, e, H = synth.lidar_table(32, 721)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx.set_option(capi.OPT_TRAVERSAL, mode)
+    for k, (q, t) in enumerate(poses):
+        ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    A = [IDENT.copy() for _ in meshes]
+    for gi, (name, v, tr) in enumerate(meshes):
+        add_mesh(ctx, name, v, tr, A[gi])
+    for it in range(2):
+        assert ctx.commit_scene(capi.COMMIT_AUTO) == 0
+        assert ctx.stats().last_commit_was_rebuild == (1 if it == 0 else 0)
+        assert ctx.trace_batch(0, len(poses), capi.TRACE_ORDERED) == 0
+        s0 = lso.Sensor(elev, b, e, H, poses[0][0], poses[0][1])
+        verts, tris = lso.concat_scene(s0, [(v, tr, A[gi]) for gi, (_, v, tr) in enumerate(meshes)], mode=1)
+        bvh = lso.Bvh(verts, tris)
+        for k, (q, t) in enumerate(poses):
+            s = lso.Sensor(elev, b, e, H, q, t)
+            dirs_s = lso.ray_dirs(s.tables)
+            t_ref, tri_ref = bvh.trace(s.T, lso.rotate_dirs(s.R, dirs_s))
+            rc, tt, tri = ctx.trace_raw(k)
+            assert rc == 0
+            assert np.array_equal(tri, tri_ref) and np.array_equal(tt, t_ref)
+            rc, pts = ctx.fetch_points(k, capi.TRACE_ORDERED)
+            # trace_raw re-traced without points: fetch the ordered clouds of the batch again
+        assert ctx.trace_batch(0, len(poses), capi.TRACE_ORDERED) == 0
+        for k, (q, t) in enumerate(poses):
+            s = lso.Sensor(elev, b, e, H, q, t)
+            dirs_s = lso.ray_dirs(s.tables)
+            t_ref, tri_ref = bvh.trace(s.T, lso.rotate_dirs(s.R, dirs_s))
+            rc, pts = ctx.fetch_points(k, capi.TRACE_ORDERED)
+            assert rc == 0 and np.array_equal(pts, lso.pack_points(dirs_s, t_ref, tri_ref, H))
+        bvh.close()
+        # move every building group a little and refit
+        for gi in range(1, len(meshes)):
+            A[gi] = lso.affine_from_components((0.3 * gi, -0.2 * gi, 0.0), (0.0, 0.0, 0.01 * gi))
+            assert ctx.update_geometry(meshes[gi][0], None, None, A[gi]) == 0
+    ctx.close()
+
+
+def test_city_10m_size_independent_properties():
+    """BASELINE config 4 at full size (10 M triangles): properties that need no CPU re-trace.
+    (1) every variant returns the same (t, triangle) bits; (2) each hit point t*d lies on its triangle (float64
+    barycentric check) and no vertex of the hit triangle is behind the origin plane; (3) refit == rebuild."""
+    meshes = synth.city()
+    poses = synth.sensor_lattice(8)
+    elev, b, e, H = synth.lidar_table()
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    pick = (0, 27, 63)
+    for k, si in enumerate(pick):
+        ctx.set_sensor(elev, b, e, H, poses[si][0], poses[si][1], index=k)
+    for name, v, tr in meshes:
+        add_mesh(ctx, name, v, tr)
+    assert sum(m[2].shape[0] for m in meshes) == 10_000_000
+    assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
+    res = {}
+    for mode in (0, 1, 4, 5, 2):
+        ctx.set_option(capi.OPT_TRAVERSAL, mode)
+        res[mode] = [ctx.trace_raw(k)[1:] for k in range(len(pick))]
+    for mode in (1, 4, 5, 2):
+        for k in range(len(pick)):
+            assert np.array_equal(res[mode][k][0], res[0][k][0]) and np.array_equal(res[mode][k][1], res[0][k][1])
+    ctx.set_option(capi.OPT_TRAVERSAL, 0)
+    assert ctx.commit_scene(capi.COMMIT_REFIT) == 0 and ctx.stats().last_commit_was_rebuild == 0
+    for k in range(len(pick)):
+        rc, t, tri = ctx.trace_raw(k)
+        assert np.array_equal(t, res[0][k][0]) and np.array_equal(tri, res[0][k][1])
+    # geometric check of the hits of one sensor
+    V = np.concatenate([m[1] for m in meshes]).astype(np.float64)
+    off = np.cumsum([0] + [m[1].shape[0] for m in meshes])[:-1]
+    Tg = np.concatenate([m[2].astype(np.int64) + o for m, o in zip(meshes, off)])
+    t, tri = res[0][1]
+    s = lso.Sensor(elev, b, e, H, poses[pick[1]][0], poses[pick[1]][1])
+    d = lso.rotate_dirs(s.R, lso.ray_dirs(s.tables)).astype(np.float64)
+    hit = tri >= 0
+    assert hit.mean() > 0.9
+    P = np.asarray(s.T, np.float64)[None, :] + t[hit, None].astype(np.float64) * d[hit]
+    a, bb, c = V[Tg[tri[hit], 0]], V[Tg[tri[hit], 1]], V[Tg[tri[hit], 2]]
+    n = np.cross(bb - a, c - a)
+    area2 = np.linalg.norm(n, axis=1)
+    dist = np.abs(np.einsum("ij,ij->i", P - a, n)) / area2          # distance to the triangle's plane
+    assert dist.max() < 2e-3, dist.max()
+    # barycentric coordinates inside [-tol, 1+tol]
+    def bary(p, q, r):
+        return np.einsum("ij,ij->i", np.cross(q - p, r - p), n) / (area2 * area2)
+    w0, w1, w2 = bary(P, bb, c), bary(P, c, a), bary(P, a, bb)
+    tol = 2e-3
+    assert min(w0.min(), w1.min(), w2.min()) > -tol and abs((w0 + w1 + w2) - 1).max() < 1e-6
+    ctx.close()
