@@ -74,7 +74,9 @@ enum {
     LSB200_OPT_STAGE_TIMING = 4,   /* 1 = record CUDA events around every stage (lsb200_get_stats) */
     LSB200_OPT_CTAS_PER_SM = 5,    /* persistent grid = 148 * this (default 0 = occupancy query) */
     LSB200_OPT_TRACE_STATS = 6,    /* 1 = instrumented traversal: per-launch node / leaf / triangle counters */
-    LSB200_OPT_MORTON_UNIFORM = 7  /* 1 = Morton codes on cubic cells (one scale for x, y, z); default 0 = per-axis */
+    LSB200_OPT_MORTON_UNIFORM = 7, /* 1 = Morton codes on cubic cells (one scale for x, y, z); default 0 = per-axis */
+    LSB200_OPT_ORIGIN_CHAIN = 8    /* 1 (default) = per-sensor origin chain: rays start from the list of subtrees that hang off
+                                      the root-to-origin chain instead of from the root; 0 = every ray starts at the root */
 };
 
 /* ---- life cycle -------------------------------------------------------------------------------------- */
@@ -200,7 +202,7 @@ typedef struct lsb200_stats {
 LSB200_API int lsb200_get_stats(lsb200_ctx *ctx, lsb200_stats *out);
 LSB200_API int lsb200_reset_counters(lsb200_ctx *ctx);
 /* totals of the last LSB200_OPT_TRACE_STATS launch: out[0..n) = rays, nodes visited, leaves visited, triangles tested,
- * 32-ray units with one octant, units with mixed octants, deepest stack, hits */
+ * 32-ray units with one octant, units with mixed octants, deepest stack, hits, culled pops, origin-chain box tests */
 LSB200_API int lsb200_get_trace_counters(lsb200_ctx *ctx, uint64_t *out, int n);
 /* copies the BVH to the host for structural tests: nodes (n_nodes x 16 floats), leaf-ordered triangle ids */
 LSB200_API int lsb200_debug_copy_bvh(lsb200_ctx *ctx, float *nodes16, int64_t node_capacity, int32_t *leaf_tri_ids,

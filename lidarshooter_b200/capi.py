@@ -16,7 +16,7 @@ FRAME_SENSOR, FRAME_WORLD = 0, 1
 COMMIT_AUTO, COMMIT_REBUILD, COMMIT_REFIT = 0, 1, 2
 TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS = 1, 2, 4, 8, 16
 OPT_TRAVERSAL, OPT_LEAF_SIZE, OPT_TOP_NODES, OPT_STAGE_TIMING, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
-OPT_TRACE_STATS, OPT_MORTON_UNIFORM = 6, 7
+OPT_TRACE_STATS, OPT_MORTON_UNIFORM, OPT_ORIGIN_CHAIN = 6, 7, 8
 ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5
 
 # every symbol include/lsb200.h declares (tests/test_abi.py checks the library exports each one)
@@ -290,9 +290,9 @@ class Context:
 
     def trace_counters(self):
         """Totals of the last OPT_TRACE_STATS launch as a dict."""
-        out = (C.c_uint64 * 9)()
-        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 9))
-        names = ("rays", "nodes", "leaves", "tris", "units_uniform", "units_mixed", "max_stack", "hits", "culled_pops")
+        out = (C.c_uint64 * 10)()
+        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 10))
+        names = ("rays", "nodes", "leaves", "tris", "units_uniform", "units_mixed", "max_stack", "hits", "culled_pops", "chain_tests")
         return {k: int(out[i]) for i, k in enumerate(names)}
 
     def reset_counters(self):

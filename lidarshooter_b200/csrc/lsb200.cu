@@ -71,17 +71,17 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 0, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0;
+    int opt_traversal = 0, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_chain = 1;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
-    bool topology_dirty = true, committed = false;
+    bool topology_dirty = true, committed = false, top_valid = false;
     int built_leaf = 0, built_top = 0;
     std::vector<Sensor> sensors;
     bool sensors_dirty = true;
     // scene arrays
     DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
-        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist;
+        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts;
     std::vector<GeomDesc> h_geoms;
     std::vector<SensorDev> h_sensors, h_sensors_b;
     cudaStream_t copy_stream = nullptr;
@@ -89,6 +89,7 @@ struct lsb200_ctx {
     // octant queues of the traversal (variant 0): valid for (units_first, units_count, units_epoch, units_world)
     int64_t sensors_epoch = 0, units_epoch = -1;
     int units_first = -1, units_count = -1, units_world = -1;
+    int64_t commit_epoch = 0, chain_commit_epoch = -1, chain_sensors_epoch = -1;
     float h_xf[12];
     uint32_t *h_count = nullptr;                                 // pinned
     int n_verts = 0, n_tris = 0;
@@ -254,7 +255,7 @@ int lsb200_destroy(lsb200_ctx *c)
         for (auto &s : c->sensors) { s.tables.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
-                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist};
+                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts};
         for (auto *b : bufs) b->release();
         if (c->h_count) cudaFreeHost(c->h_count);
         for (auto &e : c->ev) if (e) cudaEventDestroy(e);
@@ -292,6 +293,7 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     switch (option) {
     case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 5) break; c->opt_traversal = value; return LSB200_OK;
     case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_MORTON_UNIFORM: c->opt_morton_uniform = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_LEAF_SIZE: if (value < 1 || value > kMaxLeaf) break; c->opt_leaf = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TOP_NODES: if (value < 0 || value > 3072) break; c->opt_top = value; c->topology_dirty = true; return LSB200_OK;
@@ -504,9 +506,11 @@ static int commit_locked(lsb200_ctx *c, int mode)
     count_launch(c);
     mark();
     // (6) top-level block for the TMA-staged traversal
-    if (c->built_top > 0) {
+    c->top_valid = false;
+    if (c->built_top > 0 && c->opt_traversal == 4) {       // only the TMA-staged variant reads the top block
         k_top_level<<<1, 1024, (size_t)c->built_top * sizeof(int), st>>>(S, c->d_misc.as<int>());
         count_launch(c);
+        c->top_valid = true;
     }
     mark();
     LSB_CU(c, cudaGetLastError());
@@ -525,6 +529,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
     }
     c->topology_dirty = false;
     c->committed = true;
+    ++c->commit_epoch;
     return LSB200_OK;
 }
 
@@ -693,7 +698,27 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     if (timing) cudaEventRecord(c->ev[8], st);
     int mode = c->opt_traversal;
     int rc = 0;
+    if (mode == 4 && c->built_top > 0 && !c->top_valid) {  // variant switched on after the commit
+        k_top_level<<<1, 1024, (size_t)c->built_top * sizeof(int), st>>>(scene_dev(c), c->d_misc.as<int>());
+        count_launch(c);
+        c->top_valid = true;
+    }
     const int n_units = unit_hi - unit_lo;
+    if (c->opt_chain && mode != 3 && mode != 5) {
+        // origin chains: one list per sensor, valid for this BVH and these sensor poses
+        const size_t ns = c->sensors.size();
+        if (c->chain_commit_epoch != c->commit_epoch || c->chain_sensors_epoch != c->sensors_epoch) {
+            LSB_CU(c, c->d_chains.reserve(ns * 2 * kMaxChain * sizeof(float4), st));
+            LSB_CU(c, c->d_chain_counts.reserve(std::max<size_t>(ns, 4) * 4, st));
+            // both sensor tables hold the same poses; the chain kernel only reads T
+            k_origin_chain<<<(unsigned)((ns + 63) / 64), 64, 0, st>>>(P.nodes, P.top_cap, c->d_sensors.as<SensorDev>(), (int)ns,
+                                                                     P.world_frame, c->d_chains.as<float4>(), c->d_chain_counts.as<int>());
+            count_launch(c);
+            c->chain_commit_epoch = c->commit_epoch; c->chain_sensors_epoch = c->sensors_epoch;
+        }
+        P.chains = c->d_chains.as<float4>();
+        P.chain_counts = c->d_chain_counts.as<int>();
+    }
     if (mode == 0) {
         // octant queues: depend on the sensor table only, rebuilt when it (or the traced range) changes
         const int wf = P.world_frame ? 1 : 0;
@@ -954,7 +979,7 @@ int lsb200_get_stats(lsb200_ctx *c, lsb200_stats *out)
         LSB_CU(c, cudaMemcpyAsync(&ntop, c->d_misc.p, 4, cudaMemcpyDeviceToHost, c->stream));
         LSB_CU(c, cudaStreamSynchronize(c->stream));
         for (int k = 0; k < 3; ++k) { c->stats.scene_lo[k] = ord2f(b[k]); c->stats.scene_hi[k] = ord2f(b[3 + k]); }
-        c->stats.top_nodes = c->built_top > 0 ? ntop : 0;
+        c->stats.top_nodes = (c->built_top > 0 && c->top_valid) ? ntop : 0;
     }
     *out = c->stats;
     return LSB200_OK;

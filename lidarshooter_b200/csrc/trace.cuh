@@ -34,10 +34,12 @@ struct TraceParams {
     unsigned long long *counters; // STATS builds only: see TraceCounter
     const int *unit_list;         // MODE 0: unit ids grouped by octant class
     const uint32_t *oct_hist;     // MODE 0: [9] units per class (0..7 octants, 8 mixed)
+    const float4 *chains;         // [n_sensors][kMaxChain][2] origin-chain lists (k_origin_chain)
+    const int *chain_counts;      // [n_sensors] entries per list; nullptr = lists off (start at the root)
 };
 
 // Instrumented (STATS) launches accumulate these per-launch totals (lsb200_get_trace_counters).
-enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUniform, kCntUnitsMixed, kCntMaxStack, kCntHits, kCntCulled, kCntCount };
+enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUniform, kCntUnitsMixed, kCntMaxStack, kCntHits, kCntCulled, kCntChainTests, kCntCount };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -116,7 +118,7 @@ __device__ __forceinline__ void test_leaf(const TraceParams &P, int ref, const R
     }
 }
 
-struct RayStats { unsigned nodes, leaves, tris, max_sp, culled; };
+struct RayStats { unsigned nodes, leaves, tris, max_sp, culled, chain_tests; };
 
 // Entry / exit distance of one child box from the six slab products.  OCT 0..7: the signs of (dx, dy, dz) are
 // known (bit k set = component k negative), so the near and far plane of every slab are picked by name instead
@@ -134,12 +136,23 @@ __device__ __forceinline__ void slab_nf(float l0, float h0, float l1, float h1, 
     }
 }
 
+// Origin chain of one sensor (k_origin_chain): every ray of a LiDAR starts at the same point, so the root-to-leaf
+// chain of nodes whose box contains that point is entered by all of its rays.  Instead of walking it ray by ray
+// (one 56-byte node visit per level, the chain child trivially hit), the chain is cut out once per sensor and
+// frame: what remains is the list of sibling subtrees that hang off it, shallow (far) to deep (near), plus the
+// subtree or leaf the chain ends in.  A ray tests the boxes of that list (32 bytes each, no divergence) and
+// seeds its stack with the ones it enters.  The union of the listed subtrees is the whole scene and closest hit
+// = min (t, triangle id) does not depend on the visiting order, so results are unchanged.
+constexpr int kMaxChain = 48;          // entries per sensor (2 x float4 each)
+
 // Closest hit of one ray.  TOP: node references below n_top are read from the shared-memory copy.
 // OCT 0..7: sign-specialised slab test (the caller guarantees the ray's direction signs); 8: generic.
+// chain / n_chain: the sensor's origin-chain list (n_chain == 0: start at the root).
 // Every form only ever rejects a box that the eps-widened exact slab test rejects, so the per-ray results do
 // not depend on the form.
 template <bool TOP, int OCT, bool STATS>
 __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_top, int n_top, float eps, const Ray &r,
+                                          const float4 *__restrict__ chain, int n_chain,
                                           float &best_out, int &bi_out, RayStats &rs)
 {
     // slab set-up: t_lo = (lo - (o + eps)) * inv, t_hi = (hi - (o - eps)) * inv, in FMA form
@@ -158,10 +171,35 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
     // hit has been found it is dropped without loading the node
     int2 stack[kStackSize];
     int sp = 0;
-    int cur = TOP ? 0 : cap;          // root: top slot 0, or Karras node 0
-    if (TOP && n_top == 0) cur = cap;
+    if (n_chain > 0) {
+        for (int k = 0; k < n_chain; ++k) {
+            const float4 e0 = __ldg(chain + 2 * k), e1 = __ldg(chain + 2 * k + 1);
+            float n, f;
+            slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
+                         fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
+            if (STATS) ++rs.chain_tests;
+            if (n <= f) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n));
+        }
+        if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
+    } else {
+        stack[sp++] = make_int2((TOP && n_top > 0) ? 0 : cap, 0);      // root: top slot 0, or Karras node 0
+    }
     while (true) {
-        if (cur >= 0) {
+        int cur = 0;
+        bool found = false;
+        while (sp > 0) {
+            const int2 e = stack[--sp];
+            if (__int_as_float(e.y) <= far_lim * 1.0000005f) { cur = e.x; found = true; break; }
+            if (STATS) ++rs.culled;
+        }
+        if (!found) break;
+        while (true) {                                               // descend until a leaf or a dead end
+            if (cur < 0) {
+                if (STATS) { ++rs.leaves; rs.tris += (unsigned)(((~cur) >> kLeafShift) + 1); }
+                test_leaf(P, cur, r, best, bi);
+                far_lim = best * 1.0000005f;
+                break;
+            }
             float4 q0, q1, q2, q3;
             if (TOP && cur < cap) {
                 q0 = s_top[cur]; q1 = s_top[cap + cur]; q2 = s_top[2 * cap + cur]; q3 = s_top[3 * cap + cur];
@@ -182,22 +220,14 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
                 cur = swap ? c1 : c0;
                 stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
                 if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
-                continue;
+            } else if (hit0) {
+                cur = c0;
+            } else if (hit1) {
+                cur = c1;
+            } else {
+                break;
             }
-            if (hit0) { cur = c0; continue; }
-            if (hit1) { cur = c1; continue; }
-        } else {
-            if (STATS) { ++rs.leaves; rs.tris += (unsigned)(((~cur) >> kLeafShift) + 1); }
-            test_leaf(P, cur, r, best, bi);
-            far_lim = best * 1.0000005f;
         }
-        bool found = false;
-        while (sp > 0) {
-            const int2 e = stack[--sp];
-            if (__int_as_float(e.y) <= far_lim * 1.0000005f) { cur = e.x; found = true; break; }
-            if (STATS) ++rs.culled;
-        }
-        if (!found) break;
     }
     best_out = best;
     bi_out = bi;
@@ -355,7 +385,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
     float best = INFINITY; int bi = -1;
     float dsx = 0.f, dsy = 0.f, dsz = 1.f;
     int v = 0;
-    RayStats rs{0u, 0u, 0u, 0u, 0u};
+    RayStats rs{0u, 0u, 0u, 0u, 0u, 0u};
     if (valid) {
         Ray r;
         float omax;
@@ -363,20 +393,24 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
         const float eps = 8e-6f * (smax + omax) + 1e-30f;
         if (MODE == 3) brute_ray(P, r, best, bi);
         else if (MODE == 5) trace_ray_ww<STATS>(P, eps, r, best, bi, rs);
-        else trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, best, bi, rs);
+        else {
+            const int n_chain = P.chain_counts ? __ldg(P.chain_counts + si) : 0;
+            trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)si * (2 * kMaxChain), n_chain, best, bi, rs);
+        }
         S.t_out[ray] = best;
         S.tri_out[ray] = bi;
     }
     if (STATS) {
         unsigned a = __reduce_add_sync(0xffffffffu, rs.nodes), b = __reduce_add_sync(0xffffffffu, rs.leaves);
         unsigned c = __reduce_add_sync(0xffffffffu, rs.tris), d = __reduce_max_sync(0xffffffffu, rs.max_sp);
-        unsigned cu = __reduce_add_sync(0xffffffffu, rs.culled);
+        unsigned cu = __reduce_add_sync(0xffffffffu, rs.culled), ct = __reduce_add_sync(0xffffffffu, rs.chain_tests);
         unsigned nv = __reduce_add_sync(0xffffffffu, valid ? 1u : 0u), nh = __reduce_add_sync(0xffffffffu, (valid && bi >= 0) ? 1u : 0u);
         if (lane == 0) {
             atomicAdd(P.counters + kCntRays, (unsigned long long)nv); atomicAdd(P.counters + kCntNodes, (unsigned long long)a);
             atomicAdd(P.counters + kCntLeaves, (unsigned long long)b); atomicAdd(P.counters + kCntTris, (unsigned long long)c);
             atomicAdd(P.counters + kCntHits, (unsigned long long)nh); atomicMax(P.counters + kCntMaxStack, (unsigned long long)d);
             atomicAdd(P.counters + kCntCulled, (unsigned long long)cu);
+            atomicAdd(P.counters + kCntChainTests, (unsigned long long)ct);
             if (MODE == 0) atomicAdd(P.counters + (OCT < 8 ? kCntUnitsUniform : kCntUnitsMixed), 1ull);
         }
     }
@@ -530,6 +564,44 @@ __global__ void __launch_bounds__(256) k_scatter_units(int unit_lo, int unit_hi,
         if (oct == o) unit_list[base + off + __popc(m & lanemask_lt())] = u;
         base += hist[o];
     }
+}
+
+// ---- origin chains -----------------------------------------------------------------------------------------
+// One thread per sensor: walks from the root along the children whose box contains the sensor origin and lists
+// the sibling of every step (box + reference), then the node or leaf the walk ends in.  Entry layout:
+//   e0 = (lo.x, hi.x, lo.y, hi.y)   e1 = (lo.z, hi.z, ref, 0)
+// The walk stops when neither child box contains the origin, at a leaf, or when the list is nearly full.
+__global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, const SensorDev *__restrict__ sensors,
+                               int n_sensors, int world_frame, float4 *__restrict__ chains, int *__restrict__ counts)
+{
+    const int si = blockIdx.x * blockDim.x + threadIdx.x;
+    if (si >= n_sensors) return;
+    const SensorDev &S = sensors[si];
+    const float ox = world_frame ? S.T[0] : 0.0f, oy = world_frame ? S.T[1] : 0.0f, oz = world_frame ? S.T[2] : 0.0f;
+    float4 *out = chains + (size_t)si * (2 * kMaxChain);
+    int n = 0;
+    int cur = top_cap;                                   // Karras node 0
+    float4 cb0 = make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);      // box of `cur`
+    float2 cbz = make_float2(-INFINITY, INFINITY);
+    while (cur >= 0 && n < kMaxChain - 2) {
+        const float4 *nd = nodes + 4 * (size_t)cur;
+        const float4 q0 = nd[0], q1 = nd[1], q2 = nd[2], q3 = nd[3];
+        const bool in0 = ox >= q0.x && ox <= q0.y && oy >= q0.z && oy <= q0.w && oz >= q2.x && oz <= q2.y;
+        const bool in1 = ox >= q1.x && ox <= q1.y && oy >= q1.z && oy <= q1.w && oz >= q2.z && oz <= q2.w;
+        if (!in0 && !in1) break;
+        const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+        if (in0) {
+            out[2 * n] = q1; out[2 * n + 1] = make_float4(q2.z, q2.w, __int_as_float(c1), 0.0f);
+            cur = c0; cb0 = q0; cbz = make_float2(q2.x, q2.y);
+        } else {
+            out[2 * n] = q0; out[2 * n + 1] = make_float4(q2.x, q2.y, __int_as_float(c0), 0.0f);
+            cur = c1; cb0 = q1; cbz = make_float2(q2.z, q2.w);
+        }
+        ++n;
+    }
+    out[2 * n] = cb0; out[2 * n + 1] = make_float4(cbz.x, cbz.y, __int_as_float(cur), 0.0f);
+    ++n;
+    counts[si] = n;
 }
 
 // ---- ordered compaction: count -> scan -> scatter (points in ray-id order) ---------------------------------
