@@ -65,18 +65,22 @@ enum {
 
 /* traversal kernel variants (lsb200_set_option LSB200_OPT_TRAVERSAL) -- for the ncu before/after evidence */
 enum {
-    LSB200_OPT_TRAVERSAL = 1,      /* 0 = persistent CTAs, 32-ray units queued by ray octant, sign-specialised slab test
-                                      (default); 1 = persistent, generic slab test, ray order; 2 = one thread per ray
-                                      (no persistent fetch); 3 = brute force (all triangles); 4 = variant 1 + top BVH
-                                      levels staged into shared memory by TMA bulk copy; 5 = variant 1, while-while */
+    LSB200_OPT_TRAVERSAL = 1,      /* 6 (default) = persistent CTAs, 32-ray units queued by ray octant, sign-specialised
+                                      slab test, while-while loop (node visits and leaf tests separated); 0 = the same
+                                      with leaf tests inside the node loop; 1 = persistent, generic slab test, units in
+                                      table order; 2 = one thread per ray (no persistent fetch); 3 = brute force (all
+                                      triangles); 4 = variant 1 + top BVH levels staged into shared memory by TMA bulk
+                                      copy; 5 = variant 1, while-while */
     LSB200_OPT_LEAF_SIZE = 2,      /* max triangles per leaf, 1..8 (default 2) */
     LSB200_OPT_TOP_NODES = 3,      /* number of BVH nodes staged into shared memory by TMA bulk copy (default 1024) */
     LSB200_OPT_STAGE_TIMING = 4,   /* 1 = record CUDA events around every stage (lsb200_get_stats) */
     LSB200_OPT_CTAS_PER_SM = 5,    /* persistent grid = 148 * this (default 0 = occupancy query) */
     LSB200_OPT_TRACE_STATS = 6,    /* 1 = instrumented traversal: per-launch node / leaf / triangle counters */
     LSB200_OPT_MORTON_UNIFORM = 7, /* 1 = Morton codes on cubic cells (one scale for x, y, z); default 0 = per-axis */
-    LSB200_OPT_ORIGIN_CHAIN = 8    /* 1 (default) = per-sensor origin chain: rays start from the list of subtrees that hang off
+    LSB200_OPT_ORIGIN_CHAIN = 8,   /* 1 (default) = per-sensor origin chain: rays start from the list of subtrees that hang off
                                       the root-to-origin chain instead of from the root; 0 = every ray starts at the root */
+    LSB200_OPT_TILE_WIDTH = 9      /* a 32-ray work unit is a tile of W azimuth steps x 32/W channels of one device's
+                                      table; W = 1, 2, 4, 8, 16 or 32 */
 };
 
 /* ---- life cycle -------------------------------------------------------------------------------------- */

@@ -38,6 +38,7 @@ struct SensorDev {           // one per LiDAR device
     float T[3];
     int V, H, n_rays;
     int unit_base;                // first 32-ray work unit of this sensor in a batch
+    int tiles_h;                  // work units per row of tiles: ceil(H / tile width)
     float *t_out;                 // [n_rays]
     int32_t *tri_out;             // [n_rays]
     uint8_t *points;              // [n_rays] records

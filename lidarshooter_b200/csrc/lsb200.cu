@@ -71,7 +71,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 0, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_chain = 1;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_chain = 1, opt_tile_w_log2 = 3;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -291,9 +291,15 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     if (!c) return LSB200_ERR_INVALID;
     std::lock_guard<std::mutex> lk(c->mtx);
     switch (option) {
-    case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 5) break; c->opt_traversal = value; return LSB200_OK;
+    case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 6) break; c->opt_traversal = value; return LSB200_OK;
     case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_TILE_WIDTH: {
+        int w = 0;
+        while (w <= 5 && (1 << w) != value) ++w;
+        if (w > 5) break;
+        c->opt_tile_w_log2 = w; c->sensors_dirty = true; ++c->sensors_epoch; return LSB200_OK;
+    }
     case LSB200_OPT_MORTON_UNIFORM: c->opt_morton_uniform = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_LEAF_SIZE: if (value < 1 || value > kMaxLeaf) break; c->opt_leaf = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TOP_NODES: if (value < 0 || value > 3072) break; c->opt_top = value; c->topology_dirty = true; return LSB200_OK;
@@ -591,6 +597,7 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
     if (!dirty) return 0;
     c->h_sensors.assign(ns, SensorDev{});
     int unit = 0;
+    const int tw = 1 << c->opt_tile_w_log2, th = 32 >> c->opt_tile_w_log2;
     for (size_t i = 0; i < ns; ++i) {
         Sensor &s = c->sensors[i];
         SensorDev &d = c->h_sensors[i];
@@ -602,7 +609,8 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
         d.V = s.V; d.H = s.H; d.n_rays = s.n_rays();
         d.t_out = s.t.as<float>(); d.tri_out = s.tri.as<int32_t>(); d.points = s.points.as<uint8_t>();
         d.count = c->d_counts.as<uint32_t>() + i; d.block_counts = s.blocks.as<uint32_t>();
-        unit += (d.n_rays + 31) / 32;
+        d.tiles_h = (s.H + tw - 1) / tw;
+        unit += ((s.V + th - 1) / th) * d.tiles_h;
     }
     c->h_sensors_b = c->h_sensors;
     for (size_t i = 0; i < ns; ++i) {
@@ -653,7 +661,8 @@ static int launch_trace_mode(lsb200_ctx *c, const TraceParams &P, int n_units, i
     case 2: return launch_trace<2, STATS>(c, P, n_units);
     case 3: return launch_trace<3, STATS>(c, P, n_units);
     case 4: return launch_trace<4, STATS>(c, P, n_units);
-    default: return launch_trace<5, STATS>(c, P, n_units);
+    case 5: return launch_trace<5, STATS>(c, P, n_units);
+    default: return launch_trace<6, STATS>(c, P, n_units);
     }
 }
 
@@ -685,12 +694,13 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     P.sensors = d_sens; P.n_sensors = (int)c->sensors.size();
     P.top_cap = c->built_top; P.n_tris = c->n_tris;
     P.world_frame = c->frame_mode == LSB200_FRAME_WORLD;
+    P.tile_w_log2 = c->opt_tile_w_log2;
     P.flags = flags;
     P.work = c->d_misc.as<uint32_t>() + 4;
     // work units of the batch: [unit_base(first), unit_base(last) + units(last))
     const int unit_lo = c->h_sensors[first].unit_base;
     const SensorDev &last = c->h_sensors[first + count - 1];
-    const int unit_hi = last.unit_base + (last.n_rays + 31) / 32;
+    const int unit_hi = last.unit_base + ((last.V + (32 >> c->opt_tile_w_log2) - 1) / (32 >> c->opt_tile_w_log2)) * last.tiles_h;
     P.unit_lo = unit_lo; P.n_units = unit_hi;
     const bool timing = c->opt_timing != 0;
     const bool unordered_points = !(flags & (LSB200_TRACE_ORDERED | LSB200_TRACE_NO_POINTS));
@@ -704,38 +714,40 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         c->top_valid = true;
     }
     const int n_units = unit_hi - unit_lo;
-    if (c->opt_chain && mode != 3 && mode != 5) {
+    if (c->opt_chain && mode != 3) {
         // origin chains: one list per sensor, valid for this BVH and these sensor poses
         const size_t ns = c->sensors.size();
         if (c->chain_commit_epoch != c->commit_epoch || c->chain_sensors_epoch != c->sensors_epoch) {
-            LSB_CU(c, c->d_chains.reserve(ns * 2 * kMaxChain * sizeof(float4), st));
-            LSB_CU(c, c->d_chain_counts.reserve(std::max<size_t>(ns, 4) * 4, st));
+            LSB_CU(c, c->d_chains.reserve(ns * 9 * 2 * kMaxChain * sizeof(float4), st));
+            LSB_CU(c, c->d_chain_counts.reserve(ns * 9 * 4, st));
             // both sensor tables hold the same poses; the chain kernel only reads T
-            k_origin_chain<<<(unsigned)((ns + 63) / 64), 64, 0, st>>>(P.nodes, P.top_cap, c->d_sensors.as<SensorDev>(), (int)ns,
-                                                                     P.world_frame, c->d_chains.as<float4>(), c->d_chain_counts.as<int>());
+            k_origin_chain<<<(unsigned)((ns * 9 + 63) / 64), 64, 0, st>>>(P.nodes, P.top_cap, c->d_sensors.as<SensorDev>(), (int)ns,
+                                                                         P.world_frame, P.bounds, c->d_chains.as<float4>(),
+                                                                         c->d_chain_counts.as<int>());
             count_launch(c);
             c->chain_commit_epoch = c->commit_epoch; c->chain_sensors_epoch = c->sensors_epoch;
         }
         P.chains = c->d_chains.as<float4>();
         P.chain_counts = c->d_chain_counts.as<int>();
     }
-    if (mode == 0) {
+    if (mode == 0 || mode == 6) {
         // octant queues: depend on the sensor table only, rebuilt when it (or the traced range) changes
         const int wf = P.world_frame ? 1 : 0;
         if (c->units_epoch != c->sensors_epoch || c->units_first != first || c->units_count != count || c->units_world != wf) {
             LSB_CU(c, c->d_unit_oct.reserve((size_t)n_units, st));
-            LSB_CU(c, c->d_unit_list.reserve((size_t)n_units * 4, st));
+            LSB_CU(c, c->d_unit_list.reserve((size_t)n_units * sizeof(int4), st));
             LSB_CU(c, c->d_oct_hist.reserve(32 * 4, st));
             LSB_CU(c, cudaMemsetAsync(c->d_oct_hist.p, 0, 32 * 4, st));
             const unsigned blocks = (unsigned)((n_units + 255) / 256);
-            k_classify_units<<<blocks, 256, 0, st>>>(d_sens, P.n_sensors, unit_lo, unit_hi, wf, c->d_unit_oct.as<uint8_t>(),
+            k_classify_units<<<blocks, 256, 0, st>>>(d_sens, P.n_sensors, unit_lo, unit_hi, wf, P.tile_w_log2, c->d_unit_oct.as<uint8_t>(),
                                                      c->d_oct_hist.as<uint32_t>());
-            k_scatter_units<<<blocks, 256, 0, st>>>(unit_lo, unit_hi, c->d_unit_oct.as<uint8_t>(), c->d_oct_hist.as<uint32_t>(),
-                                                    c->d_oct_hist.as<uint32_t>() + 16, c->d_unit_list.as<int>());
+            k_scatter_units<<<blocks, 256, 0, st>>>(d_sens, P.n_sensors, unit_lo, unit_hi, P.tile_w_log2, c->d_unit_oct.as<uint8_t>(),
+                                                    c->d_oct_hist.as<uint32_t>(), c->d_oct_hist.as<uint32_t>() + 16,
+                                                    c->d_unit_list.as<int4>());
             count_launch(c, 2);
             c->units_epoch = c->sensors_epoch; c->units_first = first; c->units_count = count; c->units_world = wf;
         }
-        P.unit_list = c->d_unit_list.as<int>();
+        P.unit_list = c->d_unit_list.as<int4>();
         P.oct_hist = c->d_oct_hist.as<uint32_t>();
     }
     if (c->opt_stats) {

@@ -29,13 +29,14 @@ struct TraceParams {
     int unit_lo, n_units;         // this launch covers the 32-ray work units [unit_lo, n_units) of the sensor table
     int top_cap, n_tris;
     int world_frame;
+    int tile_w_log2;              // a work unit is a tile of 2^w azimuth steps x 32 / 2^w channels of one sensor
     uint32_t flags;
     uint32_t *work;               // [0] next unit, [1] finished CTAs, [2..10] next entry of each octant queue
     unsigned long long *counters; // STATS builds only: see TraceCounter
-    const int *unit_list;         // MODE 0: unit ids grouped by octant class
+    const int4 *unit_list;        // MODE 0: unit descriptors (sensor, first ray, its channel, its azimuth step) grouped by octant class
     const uint32_t *oct_hist;     // MODE 0: [9] units per class (0..7 octants, 8 mixed)
-    const float4 *chains;         // [n_sensors][kMaxChain][2] origin-chain lists (k_origin_chain)
-    const int *chain_counts;      // [n_sensors] entries per list; nullptr = lists off (start at the root)
+    const float4 *chains;         // [n_sensors][9][kMaxChain][2] origin-chain lists per octant class (k_origin_chain)
+    const int *chain_counts;      // [n_sensors][9] entries per list; nullptr = lists off (start at the root)
 };
 
 // Instrumented (STATS) launches accumulate these per-launch totals (lsb200_get_trace_counters).
@@ -235,10 +236,11 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
 
 // "while-while" form of trace_ray (Aila & Laine 2009): an inner loop that only visits nodes, left by a lane when
 // it reaches a leaf (or runs out of work); the warp reconverges behind it, so the (long) triangle tests of the
-// lanes run together instead of being interleaved with other lanes' node visits.  Generic slab test, global nodes.
-template <bool STATS>
-__device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, const Ray &r, float &best_out, int &bi_out,
-                                             RayStats &rs)
+// lanes run together instead of being interleaved with other lanes' node visits.  Nodes from global memory.
+template <int OCT, bool STATS>
+__device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, const Ray &r,
+                                             const float4 *__restrict__ chain, int n_chain,
+                                             float &best_out, int &bi_out, RayStats &rs)
 {
     const float tiny = 1e-30f;
     const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
@@ -252,16 +254,29 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
     int2 stack[kStackSize];
     int sp = 0;
     int cur = P.top_cap;
+    if (n_chain > 0) {
+        for (int k = 0; k < n_chain; ++k) {
+            const float4 e0 = __ldg(chain + 2 * k), e1 = __ldg(chain + 2 * k + 1);
+            float n, f;
+            slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
+                         fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
+            if (STATS) ++rs.chain_tests;
+            if (n <= f) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n));
+        }
+        if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
+        cur = sp > 0 ? stack[--sp].x : kDone;
+    }
     while (cur != kDone) {
         while ((unsigned)cur < (unsigned)kDone) {           // cur >= 0 and not kDone: an inner node
             const float4 *n = P.nodes + 4 * (size_t)cur;
-            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2), q3 = __ldg(n + 3);
+            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
+            const float2 q3 = __ldg(reinterpret_cast<const float2 *>(n + 3));
             if (STATS) ++rs.nodes;
             float n0, f0, n1, f1;
-            slab_nf<8>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
-                       fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
-            slab_nf<8>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
-                       fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
+            slab_nf<OCT>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
+                         fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
+            slab_nf<OCT>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
+                         fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
             const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
             const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
             if (hit0 && hit1) {
@@ -347,11 +362,9 @@ __device__ __forceinline__ void hit_point(const SensorDev &S, uint32_t flags, fl
 // Ray `ray` of sensor S: d_s = (sin t cos p, sin t sin p, cos t) (SRC/LidarDevice.cpp:319-321), ray id = channel * H
 // + azimuth; world-frame mode moves the ray instead of the scene (o = T, d = R d_s).  Used by the traversal AND by
 // the octant classification, so both see bit-identical direction signs.
-__device__ __forceinline__ void make_ray(const SensorDev &S, int world_frame, int ray, Ray &r, float &dsx, float &dsy,
-                                         float &dsz, int &v, float &omax)
+__device__ __forceinline__ void make_ray(const SensorDev &S, int world_frame, int v, int h, Ray &r, float &dsx, float &dsy,
+                                         float &dsz, float &omax)
 {
-    v = ray / S.H;
-    const int h = ray - v * S.H;
     const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v), sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
     dsx = __fmul_rn(st, cp); dsy = __fmul_rn(st, sp_); dsz = ct;
     if (world_frame) {
@@ -371,31 +384,50 @@ __device__ __forceinline__ int ray_octant(const Ray &r)
     return (int)((__float_as_uint(r.dx) >> 31) | ((__float_as_uint(r.dy) >> 31) << 1) | ((__float_as_uint(r.dz) >> 31) << 2));
 }
 
+// Position of work unit `unit`: (sensor, first channel, first azimuth step) of its tile.
+__device__ __forceinline__ int4 unit_descriptor(const SensorDev *sensors, int n_sensors, int unit, int tile_w_log2)
+{
+    const int si = find_sensor_by_unit(sensors, n_sensors, unit);
+    const int local = unit - sensors[si].unit_base;
+    const int tv = local / sensors[si].tiles_h;
+    return make_int4(si, tv << (5 - tile_w_log2), (local - tv * sensors[si].tiles_h) << tile_w_log2, 0);
+}
+
+// Lane -> (channel, azimuth step) inside the tile of descriptor ud; false when the lane falls off the table.
+__device__ __forceinline__ bool unit_lane_ray(const SensorDev &S, int4 ud, int tile_w_log2, unsigned lane, int &v, int &h)
+{
+    v = ud.y + (int)(lane >> tile_w_log2);
+    h = ud.z + (int)(lane & ((1u << tile_w_log2) - 1u));
+    return v < S.V && h < S.H;
+}
+
 // One 32-ray work unit: generate the rays, trace them, store t / triangle id, append the hits.
 // MODE: see k_trace.  OCT: slab form for every ray of the unit (0..7 only when classified uniform).
 template <int MODE, int OCT, bool STATS>
-__device__ __forceinline__ void process_unit(const TraceParams &P, const float4 *s_top, int n_top, float smax, int unit,
+__device__ __forceinline__ void process_unit(const TraceParams &P, const float4 *s_top, int n_top, float smax, int4 ud,
                                              unsigned lane)
 {
     constexpr bool TOP = (MODE == 4);
-    const int si = find_sensor_by_unit(P.sensors, P.n_sensors, unit);
+    const int si = ud.x;
     const SensorDev &S = P.sensors[si];
-    const int ray = (unit - S.unit_base) * 32 + (int)lane;
-    const bool valid = ray < S.n_rays;
+    int v, h;
+    const bool valid = unit_lane_ray(S, ud, P.tile_w_log2, lane, v, h);
+    const int ray = v * S.H + h;                          // ray id = channel * H + azimuth step
     float best = INFINITY; int bi = -1;
     float dsx = 0.f, dsy = 0.f, dsz = 1.f;
-    int v = 0;
     RayStats rs{0u, 0u, 0u, 0u, 0u, 0u};
     if (valid) {
         Ray r;
         float omax;
-        make_ray(S, P.world_frame, ray, r, dsx, dsy, dsz, v, omax);
+        make_ray(S, P.world_frame, v, h, r, dsx, dsy, dsz, omax);
         const float eps = 8e-6f * (smax + omax) + 1e-30f;
         if (MODE == 3) brute_ray(P, r, best, bi);
-        else if (MODE == 5) trace_ray_ww<STATS>(P, eps, r, best, bi, rs);
         else {
-            const int n_chain = P.chain_counts ? __ldg(P.chain_counts + si) : 0;
-            trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)si * (2 * kMaxChain), n_chain, best, bi, rs);
+            const int list = si * 9 + OCT;
+            const int n_chain = P.chain_counts ? __ldg(P.chain_counts + list) : 0;
+            if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
+            else
+            trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
         }
         S.t_out[ray] = best;
         S.tri_out[ray] = bi;
@@ -411,7 +443,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             atomicAdd(P.counters + kCntHits, (unsigned long long)nh); atomicMax(P.counters + kCntMaxStack, (unsigned long long)d);
             atomicAdd(P.counters + kCntCulled, (unsigned long long)cu);
             atomicAdd(P.counters + kCntChainTests, (unsigned long long)ct);
-            if (MODE == 0) atomicAdd(P.counters + (OCT < 8 ? kCntUnitsUniform : kCntUnitsMixed), 1ull);
+            if (MODE == 0 || MODE == 6) atomicAdd(P.counters + (OCT < 8 ? kCntUnitsUniform : kCntUnitsMixed), 1ull);
         }
     }
     if (!(P.flags & (1u | 8u))) {     // neither ORDERED nor NO_POINTS: warp-aggregated atomic append
@@ -431,7 +463,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
 }
 
 // MODE 0 only: drains the queue of octant OCT (units whose 32 rays all have the direction signs OCT; 8 = mixed).
-template <int OCT, bool STATS>
+template <int MODE, int OCT, bool STATS>
 __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane)
 {
     int begin = 0;
@@ -443,7 +475,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
         if (lane == 0) k = (int)atomicAdd(&P.work[2 + OCT], 1u);
         k = __shfl_sync(0xffffffffu, k, 0);
         if (k >= count) break;
-        process_unit<0, OCT, STATS>(P, nullptr, 0, smax, __ldg(P.unit_list + begin + k), lane);
+        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, __ldg(P.unit_list + begin + k), lane);
     }
 }
 
@@ -455,6 +487,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
 // MODE 3: brute force (persistent)
 // MODE 4: MODE 1 + top BVH levels staged into shared memory by TMA bulk copy
 // MODE 5: MODE 1 in while-while form (node loop and leaf tests separated)
+// MODE 6: MODE 0 in while-while form
 // STATS: per-ray node / leaf / triangle counters summed into P.counters (diagnostic launches only)
 template <int MODE, bool STATS>
 __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TraceParams P)
@@ -484,22 +517,22 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
 
     const unsigned lane = lane_id();
-    if (MODE == 0) {
-        run_phase<8, STATS>(P, smax, lane);
-        run_phase<0, STATS>(P, smax, lane); run_phase<1, STATS>(P, smax, lane);
-        run_phase<2, STATS>(P, smax, lane); run_phase<3, STATS>(P, smax, lane);
-        run_phase<4, STATS>(P, smax, lane); run_phase<5, STATS>(P, smax, lane);
-        run_phase<6, STATS>(P, smax, lane); run_phase<7, STATS>(P, smax, lane);
+    if (MODE == 0 || MODE == 6) {
+        run_phase<MODE, 8, STATS>(P, smax, lane);
+        run_phase<MODE, 0, STATS>(P, smax, lane); run_phase<MODE, 1, STATS>(P, smax, lane);
+        run_phase<MODE, 2, STATS>(P, smax, lane); run_phase<MODE, 3, STATS>(P, smax, lane);
+        run_phase<MODE, 4, STATS>(P, smax, lane); run_phase<MODE, 5, STATS>(P, smax, lane);
+        run_phase<MODE, 6, STATS>(P, smax, lane); run_phase<MODE, 7, STATS>(P, smax, lane);
     } else if (MODE == 2) {
         const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
-        if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit, lane);
+        if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
     } else {
         while (true) {
             int unit = 0;
             if (lane == 0) unit = P.unit_lo + (int)atomicAdd(&P.work[0], 1u);
             unit = __shfl_sync(0xffffffffu, unit, 0);
             if (unit >= P.n_units) break;
-            process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit, lane);
+            process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
         }
     }
     if (MODE != 2) {
@@ -509,7 +542,7 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
             __threadfence();
             if (atomicAdd(&P.work[1], 1u) == gridDim.x - 1) {
                 P.work[0] = 0; P.work[1] = 0;
-                if (MODE == 0) for (int o = 0; o < 9; ++o) P.work[2 + o] = 0;
+                if (MODE == 0 || MODE == 6) for (int o = 0; o < 9; ++o) P.work[2 + o] = 0;
                 __threadfence();
             }
         }
@@ -520,17 +553,19 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
 // unit_oct[u - unit_lo] = common octant of the unit's rays (bit k = sign bit of direction component k) or 8 when
 // they disagree; hist[o] = number of units per class.  Only depends on the sensor table: cached by the host.
 __global__ void __launch_bounds__(256) k_classify_units(const SensorDev *__restrict__ sensors, int n_sensors, int unit_lo,
-                                                        int unit_hi, int world_frame, uint8_t *__restrict__ unit_oct,
-                                                        uint32_t *__restrict__ hist)
+                                                        int unit_hi, int world_frame, int tile_w_log2,
+                                                        uint8_t *__restrict__ unit_oct, uint32_t *__restrict__ hist)
 {
     const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
     int oct = -1;
     if (u < unit_hi) {
-        const SensorDev &S = sensors[find_sensor_by_unit(sensors, n_sensors, u)];
-        const int ray0 = (u - S.unit_base) * 32;
-        for (int l = 0; l < 32 && ray0 + l < S.n_rays; ++l) {
-            Ray r; float a, b, c, om; int v;
-            make_ray(S, world_frame, ray0 + l, r, a, b, c, v, om);
+        const int4 ud = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
+        const SensorDev &S = sensors[ud.x];
+        for (unsigned l = 0; l < 32u; ++l) {
+            int v, h;
+            if (!unit_lane_ray(S, ud, tile_w_log2, l, v, h)) continue;
+            Ray r; float a, b, c, om;
+            make_ray(S, world_frame, v, h, r, a, b, c, om);
             const int o = ray_octant(r);
             oct = (oct < 0 || oct == o) ? o : 8;
             if (oct == 8) break;
@@ -545,11 +580,12 @@ __global__ void __launch_bounds__(256) k_classify_units(const SensorDev *__restr
     }
 }
 
-// unit_list = unit ids grouped by class (class o occupies [sum hist[<o], +hist[o])), in chunks of up to 32
+// unit_list = unit descriptors grouped by class (class o occupies [sum hist[<o], +hist[o])), in chunks of up to 32
 // consecutive units (one atomic per class per warp), so neighbouring units stay neighbours in the queues.
-__global__ void __launch_bounds__(256) k_scatter_units(int unit_lo, int unit_hi, const uint8_t *__restrict__ unit_oct,
+__global__ void __launch_bounds__(256) k_scatter_units(const SensorDev *__restrict__ sensors, int n_sensors, int unit_lo,
+                                                       int unit_hi, int tile_w_log2, const uint8_t *__restrict__ unit_oct,
                                                        const uint32_t *__restrict__ hist, uint32_t *__restrict__ cursor,
-                                                       int *__restrict__ unit_list)
+                                                       int4 *__restrict__ unit_list)
 {
     const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
     const int oct = (u < unit_hi) ? (int)unit_oct[u - unit_lo] : -1;
@@ -561,29 +597,46 @@ __global__ void __launch_bounds__(256) k_scatter_units(int unit_lo, int unit_hi,
         uint32_t off = 0;
         if (lane_id() == (unsigned)(__ffs(m) - 1)) off = atomicAdd(&cursor[o], (uint32_t)__popc(m));
         off = __shfl_sync(0xffffffffu, off, __ffs(m) - 1);
-        if (oct == o) unit_list[base + off + __popc(m & lanemask_lt())] = u;
+        if (oct == o) unit_list[base + off + __popc(m & lanemask_lt())] = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
         base += hist[o];
     }
 }
 
 // ---- origin chains -----------------------------------------------------------------------------------------
-// One thread per sensor: walks from the root along the children whose box contains the sensor origin and lists
-// the sibling of every step (box + reference), then the node or leaf the walk ends in.  Entry layout:
-//   e0 = (lo.x, hi.x, lo.y, hi.y)   e1 = (lo.z, hi.z, ref, 0)
+// One thread per (sensor, octant class): walks from the root along the children whose box contains the sensor
+// origin and lists the sibling of every step (box + reference), then the node or leaf the walk ends in.
+// Entry layout:   e0 = (lo.x, hi.x, lo.y, hi.y)   e1 = (lo.z, hi.z, ref, 0)
 // The walk stops when neither child box contains the origin, at a leaf, or when the list is nearly full.
+// Class 8 keeps every entry.  Class o < 8 (direction signs known: bit k set = component k negative) drops the
+// entries that lie entirely behind the origin along some axis -- hi < o - eps on a non-negative axis, lo > o + eps
+// on a negative one: no ray of that octant can reach them (eps = the traversal's own box padding), so the rays
+// of a sign-uniform unit test about half of the list.
 __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, const SensorDev *__restrict__ sensors,
-                               int n_sensors, int world_frame, float4 *__restrict__ chains, int *__restrict__ counts)
+                               int n_sensors, int world_frame, const uint32_t *__restrict__ bounds,
+                               float4 *__restrict__ chains, int *__restrict__ counts)
 {
-    const int si = blockIdx.x * blockDim.x + threadIdx.x;
-    if (si >= n_sensors) return;
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n_sensors * 9) return;
+    const int si = id / 9, cls = id - si * 9;
     const SensorDev &S = sensors[si];
     const float ox = world_frame ? S.T[0] : 0.0f, oy = world_frame ? S.T[1] : 0.0f, oz = world_frame ? S.T[2] : 0.0f;
-    float4 *out = chains + (size_t)si * (2 * kMaxChain);
+    float smax = 0.0f;
+    for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(bounds[k])));
+    const float eps = 8e-6f * (smax + fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz)))) + 1e-30f;
+    auto reachable = [&](const float4 bxy, const float2 bz) -> bool {
+        if (cls == 8) return true;
+        const bool x_ok = (cls & 1) ? (bxy.x <= ox + eps) : (bxy.y >= ox - eps);
+        const bool y_ok = (cls & 2) ? (bxy.z <= oy + eps) : (bxy.w >= oy - eps);
+        const bool z_ok = (cls & 4) ? (bz.x <= oz + eps) : (bz.y >= oz - eps);
+        return x_ok && y_ok && z_ok;
+    };
+    float4 *out = chains + (size_t)id * (2 * kMaxChain);
     int n = 0;
     int cur = top_cap;                                   // Karras node 0
     float4 cb0 = make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);      // box of `cur`
     float2 cbz = make_float2(-INFINITY, INFINITY);
-    while (cur >= 0 && n < kMaxChain - 2) {
+    int steps = 0;
+    while (cur >= 0 && steps < kMaxChain - 2) {
         const float4 *nd = nodes + 4 * (size_t)cur;
         const float4 q0 = nd[0], q1 = nd[1], q2 = nd[2], q3 = nd[3];
         const bool in0 = ox >= q0.x && ox <= q0.y && oy >= q0.z && oy <= q0.w && oz >= q2.x && oz <= q2.y;
@@ -591,17 +644,20 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
         if (!in0 && !in1) break;
         const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
         if (in0) {
-            out[2 * n] = q1; out[2 * n + 1] = make_float4(q2.z, q2.w, __int_as_float(c1), 0.0f);
+            if (reachable(q1, make_float2(q2.z, q2.w))) {
+                out[2 * n] = q1; out[2 * n + 1] = make_float4(q2.z, q2.w, __int_as_float(c1), 0.0f); ++n;
+            }
             cur = c0; cb0 = q0; cbz = make_float2(q2.x, q2.y);
         } else {
-            out[2 * n] = q0; out[2 * n + 1] = make_float4(q2.x, q2.y, __int_as_float(c0), 0.0f);
+            if (reachable(q0, make_float2(q2.x, q2.y))) {
+                out[2 * n] = q0; out[2 * n + 1] = make_float4(q2.x, q2.y, __int_as_float(c0), 0.0f); ++n;
+            }
             cur = c1; cb0 = q1; cbz = make_float2(q2.z, q2.w);
         }
-        ++n;
+        ++steps;
     }
-    out[2 * n] = cb0; out[2 * n + 1] = make_float4(cbz.x, cbz.y, __int_as_float(cur), 0.0f);
-    ++n;
-    counts[si] = n;
+    if (reachable(cb0, cbz)) { out[2 * n] = cb0; out[2 * n + 1] = make_float4(cbz.x, cbz.y, __int_as_float(cur), 0.0f); ++n; }
+    counts[id] = n;
 }
 
 // ---- ordered compaction: count -> scan -> scatter (points in ray-id order) ---------------------------------

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--tops", default="1024")
     ap.add_argument("--morton", default="0,1")
     ap.add_argument("--chain", default="1")
+    ap.add_argument("--tiles", default="32")
     args = ap.parse_args()
     from bench import build_workload, frame_affine
     from lidarshooter_b200 import capi
@@ -56,9 +57,10 @@ def main():
                 st = ctx.stats()
                 build_ms = {k: round(float(getattr(st, "ms_" + k)), 4) for k in
                             ("transform", "morton", "sort", "hierarchy", "fit", "toplevel")}
-                for mode, chain in [(int(x), int(y)) for x in args.modes.split(",") for y in args.chain.split(",")]:
+                for mode, chain, tile in [(int(x), int(y), int(z)) for x in args.modes.split(",") for y in args.chain.split(",") for z in args.tiles.split(",")]:
                     ctx.set_option(capi.OPT_TRAVERSAL, mode)
                     ctx.set_option(capi.OPT_ORIGIN_CHAIN, chain)
+                    ctx.set_option(capi.OPT_TILE_WIDTH, tile)
                     ctx.set_option(capi.OPT_TRACE_STATS, 0)
                     ms = []
                     for r in range(args.reps + 1):
@@ -77,7 +79,7 @@ def main():
                     if base_sig is None:
                         base_sig = sig
                     rays = max(cnt["rays"], 1)
-                    row = {"morton_uniform": mu, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "chain_tests_per_ray": cnt["chain_tests"] / rays,
+                    row = {"morton_uniform": mu, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "tile_w": tile, "chain_tests_per_ray": cnt["chain_tests"] / rays,
                            "ms_trace_min": min(ms), "ms_trace_mean": float(np.mean(ms)),
                            "mrays_per_s": ns * R / (min(ms) * 1e-3) / 1e6,
                            "nodes_per_ray": cnt["nodes"] / rays, "leaves_per_ray": cnt["leaves"] / rays,
