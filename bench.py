@@ -145,6 +145,86 @@ def cpu_trace_sample(meshes, poses, table, n_threads=None, sensors=(0,), repeats
             "rays": rays, "hits": hits, "cores": cores, "n_tris": int(tris.shape[0])}
 
 
+def xt32_scan_leg(local, reps=1000, cpu=True):
+    """BASELINE configs[0]: Hesai XT-32 lidar_0000, one scan of ground + ben (5 651 triangles, 4 800
+    rays), sensor-frame mode like the reference.  Tiny and latency-bound, so it is reported as us/scan and scans/s:
+      e2e      = per scan what MeshProjector does per frame (SRC/MeshProjector.cpp:446-471): updateGeometry of both
+                 meshes from host vertices, commitScene (full rebuild, as rtcCommitScene does), traceScene into a host
+                 cloud of 32-byte records -- wall clock of the blocking C-ABI calls;
+      resident = transform update + rebuild + trace with no host copies, CUDA events;
+      cpu      = the oracle's scan (same arithmetic as the reference's CPU path) on the host cores."""
+    import torch
+    from lidarshooter_b200 import capi
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import GOLDEN, xt32_sensor_args
+    z = np.load(os.path.join(GOLDEN, "meshes.npz"))
+    args = xt32_sensor_args("0000")
+    stream = torch.cuda.Stream()
+    ctx = capi.Context(local, capi.FRAME_SENSOR, stream=stream.cuda_stream)
+    ctx.set_sensor(*args)
+    ident = np.asarray([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], np.float32)
+    host = {}
+    for name in ("ground", "ben"):
+        v = torch.from_numpy(np.ascontiguousarray(z[name + "_v"], np.float32)).pin_memory()
+        t = np.ascontiguousarray(z[name + "_t"], np.uint32)
+        host[name] = (v, t)
+        assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0]) >= 0
+        assert ctx.update_geometry(name, v.numpy(), t, ident) == 0
+    R = ctx.ray_count(0)
+    out = torch.empty((R, 32), dtype=torch.uint8).pin_memory().numpy()
+
+    def scan_e2e():
+        for name, (v, t) in host.items():
+            ctx.update_geometry(name, v.numpy(), None, ident)
+        rc = ctx.commit_scene(capi.COMMIT_REBUILD)
+        rc2, pts = ctx.trace_scene(0, 0, out=out)
+        return rc, rc2, pts
+
+    for _ in range(20):
+        rc, rc2, pts = scan_e2e()
+    assert rc == 0 and rc2 == 0 and pts.shape[0] == 1781, (rc, rc2, pts.shape)    # SRC/test/OptixTracer_test.cpp:168
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        scan_e2e()
+    us_e2e = (time.perf_counter() - t0) / reps * 1e6
+    launches0 = int(ctx.stats().kernel_launches)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stream.synchronize()
+    e0.record(stream)
+    for _ in range(reps):
+        ctx.update_transform("ben", ident)
+        ctx.commit_scene(capi.COMMIT_REBUILD)
+        ctx.trace_device(0, 0)
+    e1.record(stream)
+    stream.synchronize()
+    us_res = e0.elapsed_time(e1) * 1e3 / reps
+    launches = (int(ctx.stats().kernel_launches) - launches0) / reps
+    ctx.close()
+    leg = {"workload": "configs[0]: XT-32 lidar_0000, ground + ben, 5651 triangles, 4800 rays, sensor frame, rebuild per scan",
+           "points": 1781, "reps": reps,
+           "e2e_us_per_scan": us_e2e, "e2e_scans_per_s": 1e6 / us_e2e, "e2e_mrays_per_s": R / us_e2e,
+           "resident_us_per_scan": us_res, "resident_scans_per_s": 1e6 / us_res, "launches_per_scan": launches}
+    if cpu:
+        from oracle import lso
+        lso.build()
+        sens = lso.Sensor(*args)
+        ms = [(z[n + "_v"], z[n + "_t"], lso.IDENTITY_AFFINE) for n in ("ground", "ben")]
+        best = None
+        for use_bvh in (False, True):
+            lso.scan(sens, ms, use_bvh=use_bvh)
+            t0 = time.perf_counter()
+            n = 5
+            for _ in range(n):
+                lso.scan(sens, ms, use_bvh=use_bvh)
+            us = (time.perf_counter() - t0) / n * 1e6
+            if best is None or us < best[0]:
+                best = (us, "bvh" if use_bvh else "brute")
+        leg["cpu_us_per_scan"] = best[0]
+        leg["cpu_scans_per_s"] = 1e6 / best[0]
+        leg["cpu_kind"] = f"oracle port ({best[1]}), {lso.max_threads()} host threads, transform + build + trace + packing"
+    return leg
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU algorithm for the path.  Embree 3.13.4 (the reference's intersector) is
     a closed binary that is neither in /root/reference nor installable here, so this is the oracle PORT (oracle/),
@@ -398,6 +478,8 @@ def main():
                          "ms_per_launch": ms_trace},
         }
     ctx.close()
+    if rank == 0:
+        line["xt32_scan"] = xt32_scan_leg(local, cpu=(world == 1 and not args.no_cpu_baseline))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblsb200.so")
+LIB_PATH = os.environ.get("LSB200_LIB") or os.path.join(_HERE, "liblsb200.so")   # override: A/B builds of tools/
 
 GEOMETRY_TRIANGLE, GEOMETRY_QUAD = 0, 1
 FRAME_SENSOR, FRAME_WORLD = 0, 1
