@@ -79,8 +79,11 @@ enum {
     LSB200_OPT_MORTON_UNIFORM = 7, /* 1 = Morton codes on cubic cells (one scale for x, y, z); default 0 = per-axis */
     LSB200_OPT_ORIGIN_CHAIN = 8,   /* 1 (default) = per-sensor origin chain: rays start from the list of subtrees that hang off
                                       the root-to-origin chain instead of from the root; 0 = every ray starts at the root */
-    LSB200_OPT_TILE_WIDTH = 9      /* a 32-ray work unit is a tile of W azimuth steps x 32/W channels of one device's
-                                      table; W = 1, 2, 4, 8, 16 or 32 */
+    LSB200_OPT_TILE_WIDTH = 9,     /* a 32-ray work unit is a tile of W azimuth steps x 32/W channels of one device's
+                                      table; W = 1, 2, 4, 8 (default), 16 or 32 */
+    LSB200_OPT_SMALL_BUILD = 10    /* 1 (default) = scenes of <= 16384 triangles in <= 16 geometries are committed by ONE
+                                      fused single-CTA kernel (transform, Morton, sort, hierarchy, fit); 0 = always the
+                                      multi-kernel pipeline */
 };
 
 /* ---- life cycle -------------------------------------------------------------------------------------- */

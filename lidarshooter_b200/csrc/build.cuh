@@ -33,25 +33,32 @@ __device__ __forceinline__ float dot3_eigen(float a0, float b0, float a1, float 
 // ---- (1) vertex transform: p1 = t + L p ; sensor frame: p2 = Rinv (p1 - T) ------------------------------
 // SRC/MeshTransformer.cpp:187-188, SRC/LidarDevice.cpp:383-391.  One thread per vertex of the whole scene;
 // block-reduced scene bounds (needed to normalise the Morton codes) go to `bounds` with ordered-uint atomics.
+__device__ __forceinline__ void transform_vertex(const SceneDev &S, int sensor_frame, const float *__restrict__ RinvT, int j,
+                                                 float &x, float &y, float &z)
+{
+    const int gi = find_geom_by_vert(S.geoms, S.n_geoms, j);
+    const GeomDesc &G = S.geoms[gi];
+    const float *src = reinterpret_cast<const float *>(G.verts + (size_t)(j - G.vert_off) * (size_t)G.stride);
+    const float px = __ldg(src), py = __ldg(src + 1), pz = __ldg(src + 2);
+    x = __fadd_rn(G.A[3], dot3_eigen(G.A[0], px, G.A[1], py, G.A[2], pz));
+    y = __fadd_rn(G.A[7], dot3_eigen(G.A[4], px, G.A[5], py, G.A[6], pz));
+    z = __fadd_rn(G.A[11], dot3_eigen(G.A[8], px, G.A[9], py, G.A[10], pz));
+    if (sensor_frame) {
+        const float dx = __fsub_rn(x, RinvT[9]), dy = __fsub_rn(y, RinvT[10]), dz = __fsub_rn(z, RinvT[11]);
+        x = dot3_eigen(RinvT[0], dx, RinvT[1], dy, RinvT[2], dz);
+        y = dot3_eigen(RinvT[3], dx, RinvT[4], dy, RinvT[5], dz);
+        z = dot3_eigen(RinvT[6], dx, RinvT[7], dy, RinvT[8], dz);
+    }
+    S.xverts[j] = make_float4(x, y, z, 0.0f);
+}
+
 __global__ void __launch_bounds__(256) k_transform(SceneDev S, int sensor_frame, const float *__restrict__ RinvT /*9+3*/)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     if (j < S.n_verts) {
-        const int gi = find_geom_by_vert(S.geoms, S.n_geoms, j);
-        const GeomDesc &G = S.geoms[gi];
-        const float *src = reinterpret_cast<const float *>(G.verts + (size_t)(j - G.vert_off) * (size_t)G.stride);
-        const float px = __ldg(src), py = __ldg(src + 1), pz = __ldg(src + 2);
-        float x = __fadd_rn(G.A[3], dot3_eigen(G.A[0], px, G.A[1], py, G.A[2], pz));
-        float y = __fadd_rn(G.A[7], dot3_eigen(G.A[4], px, G.A[5], py, G.A[6], pz));
-        float z = __fadd_rn(G.A[11], dot3_eigen(G.A[8], px, G.A[9], py, G.A[10], pz));
-        if (sensor_frame) {
-            const float dx = __fsub_rn(x, RinvT[9]), dy = __fsub_rn(y, RinvT[10]), dz = __fsub_rn(z, RinvT[11]);
-            x = dot3_eigen(RinvT[0], dx, RinvT[1], dy, RinvT[2], dz);
-            y = dot3_eigen(RinvT[3], dx, RinvT[4], dy, RinvT[5], dz);
-            z = dot3_eigen(RinvT[6], dx, RinvT[7], dy, RinvT[8], dz);
-        }
-        S.xverts[j] = make_float4(x, y, z, 0.0f);
+        float x, y, z;
+        transform_vertex(S, sensor_frame, RinvT, j, x, y, z);
         lo[0] = hi[0] = x; lo[1] = hi[1] = y; lo[2] = hi[2] = z;
     }
 #pragma unroll
@@ -102,15 +109,11 @@ __device__ __forceinline__ uint32_t expand10(uint32_t v)
 }
 
 // ---- (2) 30-bit Morton code of each triangle's AABB centre, normalised to the scene bounds -----------------
-__global__ void __launch_bounds__(256) k_morton(SceneDev S)
+__device__ __forceinline__ uint32_t morton_key(const SceneDev &S, int g, const float slo[3], const float shi[3])
 {
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= S.n_tris) return;
     int a, b, c;
     tri_vertex_ids(S, g, a, b, c);
     const float4 A = S.xverts[a], B = S.xverts[b], C = S.xverts[c];
-    const float slo[3] = {ord2f(S.bounds[0]), ord2f(S.bounds[1]), ord2f(S.bounds[2])};
-    const float shi[3] = {ord2f(S.bounds[3]), ord2f(S.bounds[4]), ord2f(S.bounds[5])};
     const float cx = 0.5f * (fminf(A.x, fminf(B.x, C.x)) + fmaxf(A.x, fmaxf(B.x, C.x)));
     const float cy = 0.5f * (fminf(A.y, fminf(B.y, C.y)) + fmaxf(A.y, fmaxf(B.y, C.y)));
     const float cz = 0.5f * (fminf(A.z, fminf(B.z, C.z)) + fmaxf(A.z, fmaxf(B.z, C.z)));
@@ -122,15 +125,36 @@ __global__ void __launch_bounds__(256) k_morton(SceneDev S)
     const uint32_t ix = (uint32_t)fminf(fmaxf(nx * 1024.0f, 0.0f), 1023.0f);
     const uint32_t iy = (uint32_t)fminf(fmaxf(ny * 1024.0f, 0.0f), 1023.0f);
     const uint32_t iz = (uint32_t)fminf(fmaxf(nz * 1024.0f, 0.0f), 1023.0f);
-    S.keys[g] = (expand10(ix) << 2) | (expand10(iy) << 1) | expand10(iz);
+    return (expand10(ix) << 2) | (expand10(iy) << 1) | expand10(iz);
+}
+
+__global__ void __launch_bounds__(256) k_morton(SceneDev S)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= S.n_tris) return;
+    const float slo[3] = {ord2f(S.bounds[0]), ord2f(S.bounds[1]), ord2f(S.bounds[2])};
+    const float shi[3] = {ord2f(S.bounds[3]), ord2f(S.bounds[4]), ord2f(S.bounds[5])};
+    S.keys[g] = morton_key(S, g, slo, shi);
     S.vals[g] = (uint32_t)g;
 }
 
 // ---- (3) Karras 2012 hierarchy over the sorted codes ------------------------------------------------------
-__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i, uint32_t ki, int j)
+// Sorted Morton codes as the hierarchy reads them: from global memory through the read-only path (multi-kernel
+// pipeline) or from the shared-memory sort buffer of the fused small build (code in the high word of each entry).
+struct KeysGlobal {
+    const uint32_t *p;
+    __device__ __forceinline__ uint32_t operator()(int j) const { return __ldg(p + j); }
+};
+struct KeysShared64 {
+    const unsigned long long *p;
+    __device__ __forceinline__ uint32_t operator()(int j) const { return (uint32_t)(p[j] >> 32); }
+};
+
+template <class Keys>
+__device__ __forceinline__ int delta(const Keys &keys, int n, int i, uint32_t ki, int j)
 {
     if (j < 0 || j >= n) return -1;
-    const uint32_t kj = __ldg(keys + j);
+    const uint32_t kj = keys(j);
     return (ki == kj) ? 32 + __clz((uint32_t)i ^ (uint32_t)j) : __clz(ki ^ kj);
 }
 
@@ -141,12 +165,11 @@ __device__ __forceinline__ int leaf_ref(int first, int count) { return ~(first |
 // One thread per internal node i in [0, n-1).  Node i covers sorted leaves [first, last]; its left child covers
 // [first, split], its right child [split+1, last].  A child whose range holds <= leaf_max triangles is
 // referenced as a leaf (the internal nodes below it stay in the bottom-up pass but are never traversed).
-__global__ void __launch_bounds__(256) k_hierarchy(SceneDev S, const uint32_t *__restrict__ keys)
+template <class Keys>
+__device__ __forceinline__ void hierarchy_node(const SceneDev &S, const Keys &keys, int i)
 {
     const int n = S.n_tris;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1) return;
-    const uint32_t ki = __ldg(keys + i);
+    const uint32_t ki = keys(i);
     const int d = (delta(keys, n, i, ki, i + 1) - delta(keys, n, i, ki, i - 1)) >= 0 ? 1 : -1;
     const int dmin = delta(keys, n, i, ki, i - d);
     int lmax = 2;
@@ -178,6 +201,13 @@ __global__ void __launch_bounds__(256) k_hierarchy(SceneDev S, const uint32_t *_
     node[3] = make_float4(__int_as_float(c0), __int_as_float(c1), __int_as_float(first), __int_as_float(last));
 }
 
+__global__ void __launch_bounds__(256) k_hierarchy(SceneDev S, const uint32_t *__restrict__ keys)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S.n_tris - 1) return;
+    hierarchy_node(S, KeysGlobal{keys}, i);
+}
+
 // ---- (4) leaf set-up + bottom-up AABB fit (rebuild and refit) --------------------------------------------
 // One thread per leaf slot i: gathers the triangle's transformed vertices, writes the 48-byte intersection
 // record, then climbs: it stores its box into its parent's child slot, and the second thread to arrive at a
@@ -186,14 +216,12 @@ __global__ void __launch_bounds__(256) k_hierarchy(SceneDev S, const uint32_t *_
 // and a block-scope fence orders the box store -- ~99 % of the nodes.  Only nodes that straddle CTAs use the
 // global arrival counters, which are never reset: each receives exactly two arrivals per fit, so the first
 // arrival always sees an even count.
-__global__ void __launch_bounds__(kFitBlock) k_fit(SceneDev S, const uint32_t *__restrict__ sorted_ids)
+// Leaf slot i: triangle record + climb.  LOCAL 1: arrival flags of block-local parents (link bit 1) live in s_flags
+// (indexed from flag_base), the others in the global parity counters.  LOCAL 2 (fused small build, one CTA): every
+// arrival flag lives in s_flags.
+template <int LOCAL>
+__device__ __forceinline__ void fit_leaf(const SceneDev &S, int g, int i, uint32_t *s_flags, int flag_base)
 {
-    __shared__ uint32_t s_flags[kFitBlock];
-    s_flags[threadIdx.x] = 0u;
-    __syncthreads();
-    const int i = blockIdx.x * kFitBlock + threadIdx.x;
-    if (i >= S.n_tris) return;
-    const int g = (int)__ldg(sorted_ids + i);
     int a, b, c;
     tri_vertex_ids(S, g, a, b, c);
     const float4 A = S.xverts[a], B = S.xverts[b], C = S.xverts[c];
@@ -219,9 +247,9 @@ __global__ void __launch_bounds__(kFitBlock) k_fit(SceneDev S, const uint32_t *_
         node[slot] = make_float4(lox, hix, loy, hiy);
         reinterpret_cast<float2 *>(node + 2)[slot] = make_float2(loz, hiz);
         uint32_t old;
-        if (up & 2) {                                               // both children arrive from this CTA
+        if (LOCAL == 2 || (LOCAL == 1 && (up & 2))) {               // both children arrive from this CTA
             __threadfence_block();
-            old = atomicAdd(&s_flags[p - blockIdx.x * kFitBlock], 1u);
+            old = atomicAdd(&s_flags[p - flag_base], 1u);
         } else {
             __threadfence();
             old = atomicAdd(&S.flags[p], 1u);
@@ -234,6 +262,267 @@ __global__ void __launch_bounds__(kFitBlock) k_fit(SceneDev S, const uint32_t *_
         loz = fminf(loz, sz.x); hiz = fmaxf(hiz, sz.y);
         up = S.node_parent[p];
     }
+}
+
+__global__ void __launch_bounds__(kFitBlock) k_fit(SceneDev S, const uint32_t *__restrict__ sorted_ids)
+{
+    __shared__ uint32_t s_flags[kFitBlock];
+    s_flags[threadIdx.x] = 0u;
+    __syncthreads();
+    const int i = blockIdx.x * kFitBlock + threadIdx.x;
+    if (i >= S.n_tris) return;
+    fit_leaf<1>(S, (int)__ldg(sorted_ids + i), i, s_flags, blockIdx.x * kFitBlock);
+}
+
+// ---- origin chains (see trace.cuh: trace_ray) --------------------------------------------------------------
+// Walks from the root along the children whose box contains the sensor origin and lists the sibling of every step
+// (box + reference), then the node or leaf the walk ends in.  Entry: e0 = (lo.x, hi.x, lo.y, hi.y), e1 = (lo.z,
+// hi.z, ref, 0).  The walk stops when neither child box contains the origin, at a leaf, or when the list is nearly
+// full.  Class 8 keeps every entry.  Class o < 8 (direction signs known: bit k set = component k negative) drops
+// the entries that lie entirely behind the origin along some axis -- hi < o - eps on a non-negative axis, lo > o +
+// eps on a negative one: no ray of that octant can reach them (eps = the traversal's own box padding), so the
+// rays of a sign-uniform unit test about half of the list.  Nodes are read past L1 (they may have just been
+// written by other CTAs of the fused small build).
+constexpr int kMaxChain = 48;          // entries per list (2 x float4 each)
+
+__device__ __forceinline__ void origin_chain_walk(const float4 *nodes, int top_cap, float ox, float oy, float oz, float smax,
+                                                  int cls, float4 *out, int *count)
+{
+    const float eps = 8e-6f * (smax + fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz)))) + 1e-30f;
+    auto reachable = [&](const float4 bxy, const float2 bz) -> bool {
+        if (cls == 8) return true;
+        const bool x_ok = (cls & 1) ? (bxy.x <= ox + eps) : (bxy.y >= ox - eps);
+        const bool y_ok = (cls & 2) ? (bxy.z <= oy + eps) : (bxy.w >= oy - eps);
+        const bool z_ok = (cls & 4) ? (bz.x <= oz + eps) : (bz.y >= oz - eps);
+        return x_ok && y_ok && z_ok;
+    };
+    int n = 0;
+    int cur = top_cap;                                   // Karras node 0
+    float4 cb0 = make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);      // box of `cur`
+    float2 cbz = make_float2(-INFINITY, INFINITY);
+    int steps = 0;
+    while (cur >= 0 && steps < kMaxChain - 2) {
+        const float4 *nd = nodes + 4 * (size_t)cur;
+        const float4 q0 = __ldcg(nd), q1 = __ldcg(nd + 1), q2 = __ldcg(nd + 2), q3 = __ldcg(nd + 3);
+        const bool in0 = ox >= q0.x && ox <= q0.y && oy >= q0.z && oy <= q0.w && oz >= q2.x && oz <= q2.y;
+        const bool in1 = ox >= q1.x && ox <= q1.y && oy >= q1.z && oy <= q1.w && oz >= q2.z && oz <= q2.w;
+        if (!in0 && !in1) break;
+        const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+        if (in0) {
+            if (reachable(q1, make_float2(q2.z, q2.w))) {
+                out[2 * n] = q1; out[2 * n + 1] = make_float4(q2.z, q2.w, __int_as_float(c1), 0.0f); ++n;
+            }
+            cur = c0; cb0 = q0; cbz = make_float2(q2.x, q2.y);
+        } else {
+            if (reachable(q0, make_float2(q2.x, q2.y))) {
+                out[2 * n] = q0; out[2 * n + 1] = make_float4(q2.x, q2.y, __int_as_float(c0), 0.0f); ++n;
+            }
+            cur = c1; cb0 = q1; cbz = make_float2(q2.z, q2.w);
+        }
+        ++steps;
+    }
+    if (reachable(cb0, cbz)) { out[2 * n] = cb0; out[2 * n + 1] = make_float4(cbz.x, cbz.y, __int_as_float(cur), 0.0f); ++n; }
+    *count = n;
+}
+
+// ---- fused build of a small scene: ONE thread-block cluster ------------------------------------------------
+// Scenes of a few thousand triangles (the reference's own: XT-32 + ground + ben = 5 651) are launch-latency bound:
+// eleven tiny dependent launches cost more than the work.  One cluster of 8 CTAs x 1024 threads (8 SMs of one GPC)
+// does the whole commit instead, with hardware cluster barriers between the phases:
+//   transform + bounds (per-CTA partial bounds, read by every CTA through distributed shared memory)
+//   Morton codes
+//   LSD radix sort, 4 x 8 bits: per-warp digit counts with MATCH.ANY, per-CTA digit totals exchanged through
+//   distributed shared memory, stable scatter (global ping-pong buffers, L2-resident)
+//   Karras hierarchy with the sorted codes staged in each CTA's shared memory
+//   leaf records + bottom-up boxes (same arrival-flag scheme as k_fit)
+//   origin chains of up to 8 sensors (saves the k_origin_chain launch of the next trace)
+// Same tree, same records, same results as the multi-kernel pipeline (tests/test_gpu_parity.py).
+constexpr int kClusterCtas = 8;
+constexpr int kSmallThreads = 1024;
+constexpr int kSmallMaxTris = 16384;      // sorted codes of the whole scene fit in each CTA's shared memory (64 KB)
+constexpr int kSmallMaxGeoms = 16;        // descriptors travel as kernel parameters: no H2D copy per commit
+struct SmallArgs {
+    GeomDesc geoms[kSmallMaxGeoms];
+    float RinvT[12];                      // sensor-frame mode: Rinv (9) and T (3) of sensor 0
+    uint32_t *keys_tmp, *vals_tmp;        // ping-pong partner of S.keys / S.vals
+    float origins[8][3];                  // ray origins of the first n_origins sensors (sensor frame: one origin, 0)
+    int n_origins;                        // 0 = the trace call computes the origin chains itself
+    float4 *chains; int *chain_counts;    // [n_origins][9] lists (trace.cuh: TraceParams)
+};
+
+struct KeysShared {
+    const uint32_t *p;
+    __device__ __forceinline__ uint32_t operator()(int j) const { return p[j]; }
+};
+
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of `p` (a shared-memory variable of this CTA) in the shared memory of CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t dsmem_ld_u32(const uint32_t *p, int rank)
+{
+    uint32_t remote, v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(rank));
+    asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(remote) : "memory");
+    return v;
+}
+
+__global__ void __cluster_dims__(kClusterCtas, 1, 1) __launch_bounds__(kSmallThreads, 1)
+k_build_small(SceneDev S, const __grid_constant__ SmallArgs args, int sensor_frame, int rebuild)
+{
+    extern __shared__ __align__(16) uint32_t s_codes[];                  // [n_tris] sorted Morton codes (hierarchy phase)
+    __shared__ uint32_t s_hist[kSmallThreads / 32][256];                 // per-warp digit counts -> running offsets
+    __shared__ uint32_t s_ctot[256], s_base[256], s_wsum[8];
+    __shared__ uint32_t s_bounds[6], s_gbounds[6];
+    __shared__ uint32_t s_flags[kSmallThreads];
+    S.geoms = args.geoms;
+    const float *RinvT = args.RinvT;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rank = blockIdx.x;                                          // one cluster: rank in cluster == blockIdx.x
+    constexpr int kAll = kClusterCtas * kSmallThreads;
+    const int gtid = rank * kSmallThreads + tid;
+    const int n = S.n_tris;
+#ifdef LSB_SMALL_CLK
+    long long clk[16]; int nclk = 0;
+#define LSB_CLK() do { if (gtid == 0) clk[nclk++] = clock64(); } while (0)
+#else
+#define LSB_CLK() do { } while (0)
+#endif
+    LSB_CLK();
+    if (tid < 3) s_bounds[tid] = 0xFFFFFFFFu; else if (tid < 6) s_bounds[tid] = 0u;
+    __syncthreads();
+    // (1) transform + bounds
+    {
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (int j = gtid; j < S.n_verts; j += kAll) {
+            float x, y, z;
+            transform_vertex(S, sensor_frame, RinvT, j, x, y, z);
+            lo[0] = fminf(lo[0], x); hi[0] = fmaxf(hi[0], x);
+            lo[1] = fminf(lo[1], y); hi[1] = fmaxf(hi[1], y);
+            lo[2] = fminf(lo[2], z); hi[2] = fmaxf(hi[2], z);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+                hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+            }
+            if (lane == 0 && lo[k] <= hi[k]) { atomicMin(&s_bounds[k], f2ord(lo[k])); atomicMax(&s_bounds[3 + k], f2ord(hi[k])); }
+        }
+    }
+    cluster_sync_all();
+    LSB_CLK();
+    if (tid < 6) {
+        uint32_t v = dsmem_ld_u32(&s_bounds[tid], 0);
+        for (int r = 1; r < kClusterCtas; ++r) {
+            const uint32_t w = dsmem_ld_u32(&s_bounds[tid], r);
+            v = tid < 3 ? min(v, w) : max(v, w);
+        }
+        s_gbounds[tid] = v;
+        if (rank == 0) S.bounds[tid] = v;
+    }
+    __syncthreads();
+    if (rebuild) {
+        // (2) Morton codes
+        const float slo[3] = {ord2f(s_gbounds[0]), ord2f(s_gbounds[1]), ord2f(s_gbounds[2])};
+        const float shi[3] = {ord2f(s_gbounds[3]), ord2f(s_gbounds[4]), ord2f(s_gbounds[5])};
+        for (int g = gtid; g < n; g += kAll) { S.keys[g] = morton_key(S, g, slo, shi); S.vals[g] = (uint32_t)g; }
+        cluster_sync_all();
+        LSB_CLK();
+        // (3) stable LSD radix sort; warp w of CTA r owns the contiguous chunk [(r * 32 + w) * per_warp, +per_warp)
+        const int per_warp = (((n + kAll / 32 - 1) / (kAll / 32)) + 31) & ~31;
+        const int chunk_lo = (rank * (kSmallThreads / 32) + warp) * per_warp;
+        const int chunk_hi = min(n, chunk_lo + per_warp);
+        uint32_t *src_k = S.keys, *src_v = S.vals, *dst_k = args.keys_tmp, *dst_v = args.vals_tmp;
+        for (int shift = 0; shift < 32; shift += 8) {
+            for (int k = tid; k < (kSmallThreads / 32) * 256; k += kSmallThreads) (&s_hist[0][0])[k] = 0u;
+            __syncthreads();
+            for (int base = chunk_lo; base < chunk_hi; base += 32) {
+                const int i = base + lane;
+                const uint32_t d = i < chunk_hi ? ((__ldcg(src_k + i) >> shift) & 255u) : (256u + (uint32_t)lane);
+                const unsigned m = __match_any_sync(0xffffffffu, d);
+                if (d < 256u && lane == __ffs(m) - 1) s_hist[warp][d] += (uint32_t)__popc(m);
+                __syncwarp();
+            }
+            __syncthreads();
+            if (tid < 256) {                     // counts -> exclusive prefix over the warps of this CTA, and the CTA total
+                uint32_t run = 0;
+                for (int w = 0; w < kSmallThreads / 32; ++w) { const uint32_t c = s_hist[w][tid]; s_hist[w][tid] = run; run += c; }
+                s_ctot[tid] = run;
+            }
+            cluster_sync_all();
+            if (tid < 256) {                     // digit total over the cluster, and what earlier CTAs hold of this digit
+                uint32_t total = 0, before = 0;
+                for (int r = 0; r < kClusterCtas; ++r) {
+                    const uint32_t v = dsmem_ld_u32(&s_ctot[tid], r);
+                    before += r < rank ? v : 0u;
+                    total += v;
+                }
+                uint32_t incl = total;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+                if (lane == 31) s_wsum[warp] = incl;
+                s_base[tid] = incl - total + before;      // + sum of the earlier warps' totals, added below
+            }
+            __syncthreads();
+            if (tid < 256) { uint32_t add = 0; for (int w = 0; w < warp; ++w) add += s_wsum[w]; s_base[tid] += add; }
+            __syncthreads();
+            for (int base = chunk_lo; base < chunk_hi; base += 32) {
+                const int i = base + lane;
+                const bool ok = i < chunk_hi;
+                const uint32_t key = ok ? __ldcg(src_k + i) : 0u, val = ok ? __ldcg(src_v + i) : 0u;
+                const uint32_t d = ok ? ((key >> shift) & 255u) : (256u + (uint32_t)lane);
+                const unsigned m = __match_any_sync(0xffffffffu, d);
+                if (ok) {
+                    const uint32_t pos = s_base[d] + s_hist[warp][d] + (uint32_t)__popc(m & lanemask_lt());
+                    dst_k[pos] = key; dst_v[pos] = val;
+                }
+                __syncwarp();
+                if (ok && lane == __ffs(m) - 1) s_hist[warp][d] += (uint32_t)__popc(m);
+                __syncwarp();
+            }
+            cluster_sync_all();
+            LSB_CLK();
+            uint32_t *t = src_k; src_k = dst_k; dst_k = t;
+            t = src_v; src_v = dst_v; dst_v = t;
+        }
+        // (4) hierarchy, sorted codes staged in shared memory
+        for (int i = tid; i < n; i += kSmallThreads) s_codes[i] = __ldcg(S.keys + i);
+        __syncthreads();
+        if (n > 1) { for (int i = gtid; i < n - 1; i += kAll) hierarchy_node(S, KeysShared{s_codes}, i); }
+        else if (gtid == 0) {
+            float4 *node = S.nodes + 4 * (size_t)S.top_cap;
+            node[1] = make_float4(INFINITY, -INFINITY, INFINITY, -INFINITY);
+            reinterpret_cast<float2 *>(node + 2)[1] = make_float2(INFINITY, -INFINITY);
+            node[3] = make_float4(__int_as_float(leaf_ref(0, 1)), __int_as_float(leaf_ref(0, 1)), __int_as_float(0), __int_as_float(0));
+            S.leaf_parent[0] = 0; S.node_parent[0] = -1; S.flags[0] |= 1u;
+        }
+        cluster_sync_all();
+        LSB_CLK();
+    }
+    // (5) leaf records + bottom-up boxes: CTA r, round k owns the leaves [k * 8192 + r * 1024, +1024)
+    for (int base = rank * kSmallThreads; base < n; base += kAll) {
+        s_flags[tid] = 0u;
+        __syncthreads();
+        const int i = base + tid;
+        if (i < n) fit_leaf<1>(S, (int)__ldcg(S.vals + i), i, s_flags, base);
+        __syncthreads();
+    }
+    cluster_sync_all();                       // every box is final; no CTA leaves while its shared memory may still be read
+    // (6) origin chains
+    if (rank == 0 && tid < args.n_origins * 9) {
+        const int si = tid / 9, cls = tid - si * 9;
+        float smax = 0.0f;
+        for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(s_gbounds[k])));
+        origin_chain_walk(S.nodes, S.top_cap, args.origins[si][0], args.origins[si][1], args.origins[si][2], smax, cls,
+                          args.chains + (size_t)tid * (2 * kMaxChain), args.chain_counts + tid);
+    }
+    LSB_CLK();
+#ifdef LSB_SMALL_CLK
+    if (gtid == 0) { printf("small build clocks:"); for (int k = 1; k < nclk; ++k) printf(" %lld", clk[k] - clk[k - 1]); printf("\n"); }
+#endif
 }
 
 // Single-triangle scene: node 0 = (leaf 0, empty box).

@@ -71,7 +71,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_chain = 1, opt_tile_w_log2 = 3;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -294,6 +294,7 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 6) break; c->opt_traversal = value; return LSB200_OK;
     case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TILE_WIDTH: {
         int w = 0;
         while (w <= 5 && (1 << w) != value) ++w;
@@ -463,8 +464,12 @@ static int commit_locked(lsb200_ctx *c, int mode)
             voff += g.n_verts; toff += g.n_tris();
         }
     }
-    LSB_CU(c, c->d_geoms.reserve(ng * sizeof(GeomDesc), st));
-    LSB_CU(c, cudaMemcpyAsync(c->d_geoms.p, c->h_geoms.data(), ng * sizeof(GeomDesc), cudaMemcpyHostToDevice, st));
+    // small scenes: one fused kernel, descriptors passed as kernel parameters (build.cuh: k_build_small)
+    const bool small = c->opt_small_build && nt <= kSmallMaxTris && ng <= (size_t)kSmallMaxGeoms;
+    if (!small) {
+        LSB_CU(c, c->d_geoms.reserve(ng * sizeof(GeomDesc), st));
+        LSB_CU(c, cudaMemcpyAsync(c->d_geoms.p, c->h_geoms.data(), ng * sizeof(GeomDesc), cudaMemcpyHostToDevice, st));
+    }
 
     const size_t T = (size_t)nt;
     LSB_CU(c, c->d_xverts.reserve((size_t)nv * sizeof(float4), st));
@@ -473,7 +478,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
     if (rebuild) {
         LSB_CU(c, c->d_keys.reserve(T * 4, st)); LSB_CU(c, c->d_vals.reserve(T * 4, st));
         LSB_CU(c, c->d_keys_tmp.reserve(T * 4, st)); LSB_CU(c, c->d_vals_tmp.reserve(T * 4, st));
-        LSB_CU(c, c->d_sort_scratch.reserve(rsort::scratch_words(nt) * 4, st));
+        if (!small) LSB_CU(c, c->d_sort_scratch.reserve(rsort::scratch_words(nt) * 4, st));
         LSB_CU(c, c->d_nodes.reserve(((size_t)c->built_top + T) * 64, st));
         LSB_CU(c, c->d_node_parent.reserve(T * 4, st)); LSB_CU(c, c->d_leaf_parent.reserve(T * 4, st));
         LSB_CU(c, c->d_flags.reserve(T * 4, st, false, true));
@@ -482,6 +487,56 @@ static int commit_locked(lsb200_ctx *c, int mode)
     const bool timing = c->opt_timing != 0;
     int evi = 0;
     auto mark = [&]() { if (timing) cudaEventRecord(c->ev[evi++], st); };
+
+    if (small) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            LSB_CU(c, cudaFuncSetAttribute(k_build_small, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallMaxTris * 4));
+            attr_set = true;
+        }
+        SmallArgs args;
+        std::memcpy(args.geoms, c->h_geoms.data(), ng * sizeof(GeomDesc));
+        if (c->frame_mode == LSB200_FRAME_SENSOR) { std::memcpy(args.RinvT, c->sensors[0].Rinv, 36); std::memcpy(args.RinvT + 9, c->sensors[0].T, 12); }
+        else std::memset(args.RinvT, 0, sizeof(args.RinvT));
+        args.keys_tmp = c->d_keys_tmp.as<uint32_t>(); args.vals_tmp = c->d_vals_tmp.as<uint32_t>();
+        // origin chains of the sensors folded into the same kernel when there are few of them
+        args.n_origins = 0; args.chains = nullptr; args.chain_counts = nullptr;
+        const size_t ns = c->sensors.size();
+        bool all_set = ns > 0;
+        for (const Sensor &sn : c->sensors) all_set = all_set && sn.set;
+        if (c->opt_chain && all_set && ns <= 8 && c->opt_traversal != 3) {
+            LSB_CU(c, c->d_chains.reserve(ns * 9 * 2 * kMaxChain * sizeof(float4), st));
+            LSB_CU(c, c->d_chain_counts.reserve(ns * 9 * 4, st));
+            args.n_origins = (int)ns; args.chains = c->d_chains.as<float4>(); args.chain_counts = c->d_chain_counts.as<int>();
+            for (size_t i = 0; i < ns; ++i)
+                for (int k = 0; k < 3; ++k) args.origins[i][k] = c->frame_mode == LSB200_FRAME_WORLD ? c->sensors[i].T[k] : 0.0f;
+        }
+        mark();
+        // one cluster of kClusterCtas CTAs (__cluster_dims__ on the kernel)
+        k_build_small<<<kClusterCtas, kSmallThreads, (size_t)nt * 4, st>>>(S, args, c->frame_mode == LSB200_FRAME_SENSOR, rebuild ? 1 : 0);
+        count_launch(c);
+        mark();
+        c->top_valid = false;
+        if (c->built_top > 0 && c->opt_traversal == 4) {
+            k_top_level<<<1, 1024, (size_t)c->built_top * sizeof(int), st>>>(S, c->d_misc.as<int>());
+            count_launch(c);
+            c->top_valid = true;
+        }
+        LSB_CU(c, cudaGetLastError());
+        c->stats.last_commit_was_rebuild = rebuild ? 1 : 0;
+        if (timing) {
+            LSB_CU(c, cudaStreamSynchronize(st));
+            float ms = 0;
+            cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+            c->stats.ms_transform = c->stats.ms_morton = c->stats.ms_sort = c->stats.ms_hierarchy = c->stats.ms_toplevel = 0;
+            c->stats.ms_fit = ms;                 // the fused kernel, reported as one stage
+        }
+        c->topology_dirty = false;
+        c->committed = true;
+        ++c->commit_epoch;
+        if (args.n_origins > 0) { c->chain_commit_epoch = c->commit_epoch; c->chain_sensors_epoch = c->sensors_epoch; }
+        return LSB200_OK;
+    }
 
     // (1) transform + scene bounds
     if (c->frame_mode == LSB200_FRAME_SENSOR) {
@@ -640,7 +695,14 @@ static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
         grid = (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32);
     } else {
         int per_sm = c->opt_ctas_per_sm;
-        if (per_sm <= 0) LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<MODE, STATS>, kTraceThreads, smem));
+        static int occ = 0; static size_t occ_smem = ~size_t(0);      // one query per instantiation and smem size
+        if (per_sm <= 0) {
+            if (occ <= 0 || occ_smem != smem) {
+                LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<MODE, STATS>, kTraceThreads, smem));
+                occ_smem = smem;
+            }
+            per_sm = occ;
+        }
         if (per_sm <= 0) return fail(c, LSB200_ERR_CUDA, "trace kernel does not fit on an SM (smem %zu)", smem);
         grid = c->sm_count * per_sm;
         grid = std::min(grid, (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32));

@@ -144,7 +144,7 @@ __device__ __forceinline__ void slab_nf(float l0, float h0, float l1, float h1, 
 // subtree or leaf the chain ends in.  A ray tests the boxes of that list (32 bytes each, no divergence) and
 // seeds its stack with the ones it enters.  The union of the listed subtrees is the whole scene and closest hit
 // = min (t, triangle id) does not depend on the visiting order, so results are unchanged.
-constexpr int kMaxChain = 48;          // entries per sensor (2 x float4 each)
+// kMaxChain (entries per list, 2 x float4 each) and the walk itself live in build.cuh: origin_chain_walk.
 
 // Closest hit of one ray.  TOP: node references below n_top are read from the shared-memory copy.
 // OCT 0..7: sign-specialised slab test (the caller guarantees the ray's direction signs); 8: generic.
@@ -462,7 +462,9 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
     }
 }
 
-// MODE 0 only: drains the queue of octant OCT (units whose 32 rays all have the direction signs OCT; 8 = mixed).
+// MODE 0 / 6: drains the queue of octant class OCT (units whose 32 rays all have the direction signs OCT; 8 = mixed).
+// An empty class costs no atomic.  (Requesting the next ticket before processing the current unit was measured: no
+// gain -- other warps already hide the round trip -- and it costs a live register across the traversal.)
 template <int MODE, int OCT, bool STATS>
 __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane)
 {
@@ -470,6 +472,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
 #pragma unroll
     for (int o = 0; o < OCT; ++o) begin += (int)__ldg(P.oct_hist + o);
     const int count = (int)__ldg(P.oct_hist + OCT);
+    if (count == 0) return;
     while (true) {
         int k = 0;
         if (lane == 0) k = (int)atomicAdd(&P.work[2 + OCT], 1u);
@@ -622,42 +625,7 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
     const float ox = world_frame ? S.T[0] : 0.0f, oy = world_frame ? S.T[1] : 0.0f, oz = world_frame ? S.T[2] : 0.0f;
     float smax = 0.0f;
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(bounds[k])));
-    const float eps = 8e-6f * (smax + fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz)))) + 1e-30f;
-    auto reachable = [&](const float4 bxy, const float2 bz) -> bool {
-        if (cls == 8) return true;
-        const bool x_ok = (cls & 1) ? (bxy.x <= ox + eps) : (bxy.y >= ox - eps);
-        const bool y_ok = (cls & 2) ? (bxy.z <= oy + eps) : (bxy.w >= oy - eps);
-        const bool z_ok = (cls & 4) ? (bz.x <= oz + eps) : (bz.y >= oz - eps);
-        return x_ok && y_ok && z_ok;
-    };
-    float4 *out = chains + (size_t)id * (2 * kMaxChain);
-    int n = 0;
-    int cur = top_cap;                                   // Karras node 0
-    float4 cb0 = make_float4(-INFINITY, INFINITY, -INFINITY, INFINITY);      // box of `cur`
-    float2 cbz = make_float2(-INFINITY, INFINITY);
-    int steps = 0;
-    while (cur >= 0 && steps < kMaxChain - 2) {
-        const float4 *nd = nodes + 4 * (size_t)cur;
-        const float4 q0 = nd[0], q1 = nd[1], q2 = nd[2], q3 = nd[3];
-        const bool in0 = ox >= q0.x && ox <= q0.y && oy >= q0.z && oy <= q0.w && oz >= q2.x && oz <= q2.y;
-        const bool in1 = ox >= q1.x && ox <= q1.y && oy >= q1.z && oy <= q1.w && oz >= q2.z && oz <= q2.w;
-        if (!in0 && !in1) break;
-        const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-        if (in0) {
-            if (reachable(q1, make_float2(q2.z, q2.w))) {
-                out[2 * n] = q1; out[2 * n + 1] = make_float4(q2.z, q2.w, __int_as_float(c1), 0.0f); ++n;
-            }
-            cur = c0; cb0 = q0; cbz = make_float2(q2.x, q2.y);
-        } else {
-            if (reachable(q0, make_float2(q2.x, q2.y))) {
-                out[2 * n] = q0; out[2 * n + 1] = make_float4(q2.x, q2.y, __int_as_float(c0), 0.0f); ++n;
-            }
-            cur = c1; cb0 = q1; cbz = make_float2(q2.z, q2.w);
-        }
-        ++steps;
-    }
-    if (reachable(cb0, cbz)) { out[2 * n] = cb0; out[2 * n + 1] = make_float4(cbz.x, cbz.y, __int_as_float(cur), 0.0f); ++n; }
-    counts[id] = n;
+    origin_chain_walk(nodes, top_cap, ox, oy, oz, smax, cls, chains + (size_t)id * (2 * kMaxChain), counts + id);
 }
 
 // ---- ordered compaction: count -> scan -> scatter (points in ray-id order) ---------------------------------
