@@ -200,10 +200,43 @@ def xt32_scan_leg(local, reps=1000, cpu=True):
     us_res = e0.elapsed_time(e1) * 1e3 / reps
     launches = (int(ctx.stats().kernel_launches) - launches0) / reps
     ctx.close()
+
+    # throughput with one tracer per device (the reference runs one tracer per LiDAR, SRC/mainwindow.cpp:256-274):
+    # K independent contexts on K streams, scans issued round-robin from this one host thread, nothing read back
+    K = 16
+    streams = [torch.cuda.Stream() for _ in range(K)]
+    ctxs = []
+    for k in range(K):
+        cx = capi.Context(local, capi.FRAME_SENSOR, stream=streams[k].cuda_stream)
+        cx.set_sensor(*args)
+        for name, (v, t) in host.items():
+            cx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0])
+            cx.update_geometry(name, v.numpy(), t, ident)
+        ctxs.append(cx)
+
+    def round_robin(n):
+        for _ in range(n):
+            for cx in ctxs:
+                cx.update_transform("ben", ident)
+                cx.commit_scene(capi.COMMIT_REBUILD)
+                cx.trace_device(0, 0)
+
+    round_robin(5)
+    torch.cuda.synchronize()
+    rr = max(reps // K, 10)
+    t0 = time.perf_counter()
+    round_robin(rr)
+    torch.cuda.synchronize()
+    us_conc = (time.perf_counter() - t0) / (rr * K) * 1e6
+    n_check = ctxs[-1].fetch_points(0)[1].shape[0]
+    assert n_check == 1781, n_check
+    for cx in ctxs:
+        cx.close()
     leg = {"workload": "configs[0]: XT-32 lidar_0000, ground + ben, 5651 triangles, 4800 rays, sensor frame, rebuild per scan",
            "points": 1781, "reps": reps,
            "e2e_us_per_scan": us_e2e, "e2e_scans_per_s": 1e6 / us_e2e, "e2e_mrays_per_s": R / us_e2e,
-           "resident_us_per_scan": us_res, "resident_scans_per_s": 1e6 / us_res, "launches_per_scan": launches}
+           "resident_us_per_scan": us_res, "resident_scans_per_s": 1e6 / us_res, "launches_per_scan": launches,
+           "concurrent_tracers": K, "concurrent_us_per_scan": us_conc, "concurrent_scans_per_s": 1e6 / us_conc}
     if cpu:
         from oracle import lso
         lso.build()
