@@ -105,6 +105,12 @@ LSB200_API const char *lsb200_version(void);
  * sensor_index 0 is the context's device; indices > 0 are allowed in LSB200_FRAME_WORLD only. */
 LSB200_API int lsb200_set_sensor(lsb200_ctx *ctx, int sensor_index, const float *elev_deg, int V, float az_begin,
                                  float az_end, int H, const float q_wxyz[4], const float t_xyz[3]);
+/* Sensor limits the reference carries in its device config but never applies (config/hesai-pandar-XT-32-lidar_0000.json:
+ * 14-18 "detection_radius", "horizontal_angle_range").  Semantics defined here: a ray whose closest
+ * hit lies beyond max_range returns nothing (max_range <= 0: unlimited); an azimuth step whose angle, wrapped into
+ * (-180, 180], lies outside [az_min_deg, az_max_deg] is not fired.  Cleared by lsb200_set_sensor.  Off by default, so
+ * the drop-in behaviour equals the reference's. */
+LSB200_API int lsb200_set_sensor_limits(lsb200_ctx *ctx, int sensor_index, float max_range, float az_min_deg, float az_max_deg);
 LSB200_API int lsb200_get_ray_count(const lsb200_ctx *ctx, int sensor_index);
 
 /* ---- geometry: ITracer::addGeometry / removeGeometry / updateGeometry (SRC/ITracer.hpp:50-85) ------------- */

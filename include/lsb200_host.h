@@ -65,6 +65,19 @@ LSB200_API int lsbh_tracer_set_flags(lsbh_tracer *t, int ordered, int ring_zero,
 /* getTraceCloud(): header + payload of the cloud the tracer rewrites in place */
 LSB200_API int lsbh_tracer_cloud(lsbh_tracer *t, lsb200_cloud_header *hdr, const uint8_t **data, size_t *n_bytes);
 LSB200_API int lsbh_tracer_trace_raw(lsbh_tracer *t, float *t_out, int32_t *tri_out);
+/* detection_radius / horizontal_angle_range of the device config (config/hesai-pandar-XT-32-lidar_0000.json:14-18) and
+ * the switch that applies them through lsb200_set_sensor_limits (off = the reference's behaviour) */
+LSB200_API int lsbh_device_limits(const lsbh_device *d, float *radius, float *az_lo, float *az_hi);
+LSB200_API int lsbh_tracer_set_sensor_limits(lsbh_tracer *t, int on);
+/* ROS-1 wire bytes of the traced sensor_msgs/PointCloud2 (what SRC/MeshProjector.cpp:380-390 publishes through roscpp),
+ * host/CloudSerializer.hpp.  stamp < 0 keeps the cloud's own stamp.  Returns the message length (also when it exceeds
+ * `capacity`, in which case nothing is written), < 0 on error. */
+LSB200_API long lsbh_tracer_serialize_cloud(lsbh_tracer *t, double stamp, int fix_row_step, uint8_t *out, size_t capacity);
+/* parse + serialise again (round-trip check of the reader); fills hdr / stamp from the parsed message */
+LSB200_API long lsbh_cloud_reserialize(const uint8_t *msg, size_t len, uint8_t *out, size_t capacity, lsb200_cloud_header *hdr,
+                                       double *stamp);
+/* appends "uint32 length + message" to a file */
+LSB200_API int lsbh_tracer_append_cloud_to_file(lsbh_tracer *t, const char *path, int fix_row_step);
 
 /* AffineMesh + Trajectory (SRC/AffineMesh.cpp:108-128, 275-284; config/trajectory.json): poses[k] = lin xyz, ang xyz
  * after tick k.  Returns the number of ticks (may exceed capacity; only `capacity` are written), < 0 on error. */

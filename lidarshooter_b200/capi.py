@@ -22,7 +22,7 @@ ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1,
 # every symbol include/lsb200.h declares (tests/test_abi.py checks the library exports each one)
 SYMBOLS = [
     "lsb200_create", "lsb200_destroy", "lsb200_set_stream", "lsb200_set_frame_mode", "lsb200_set_option",
-    "lsb200_last_error", "lsb200_version", "lsb200_set_sensor", "lsb200_get_ray_count", "lsb200_add_geometry",
+    "lsb200_last_error", "lsb200_version", "lsb200_set_sensor", "lsb200_set_sensor_limits", "lsb200_get_ray_count", "lsb200_add_geometry",
     "lsb200_remove_geometry", "lsb200_get_geometry_count", "lsb200_get_geometry_id", "lsb200_update_geometry",
     "lsb200_update_geometry_euler", "lsb200_update_transform", "lsb200_affine_from_components",
     "lsb200_commit_scene", "lsb200_trace_scene", "lsb200_trace_device", "lsb200_trace_batch", "lsb200_trace_raw",
@@ -74,6 +74,7 @@ def lib():
     L.lsb200_last_error.restype = C.c_char_p
     L.lsb200_version.restype = C.c_char_p
     L.lsb200_set_sensor.argtypes = [vp, C.c_int, f32p, C.c_int, C.c_float, C.c_float, C.c_int, f32p, f32p]
+    L.lsb200_set_sensor_limits.argtypes = [vp, C.c_int, C.c_float, C.c_float, C.c_float]
     L.lsb200_get_ray_count.argtypes = [vp, C.c_int]
     L.lsb200_add_geometry.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_int]
     L.lsb200_remove_geometry.argtypes = [vp, C.c_char_p]
@@ -167,6 +168,9 @@ class Context:
         t = np.ascontiguousarray(t_xyz, np.float32)
         self._chk(self._L.lsb200_set_sensor(self._h, index, _fp(e), e.size, float(np.float32(az_begin)),
                                             float(np.float32(az_end)), int(H), _fp(q), _fp(t)))
+
+    def set_sensor_limits(self, max_range=0.0, az_min_deg=-180.0, az_max_deg=180.0, index=0):
+        return self._L.lsb200_set_sensor_limits(self._h, index, float(max_range), float(az_min_deg), float(az_max_deg))
 
     def ray_count(self, index=0):
         return self._L.lsb200_get_ray_count(self._h, index)

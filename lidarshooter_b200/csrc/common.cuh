@@ -39,6 +39,8 @@ struct SensorDev {           // one per LiDAR device
     int V, H, n_rays;
     int unit_base;                // first 32-ray work unit of this sensor in a batch
     int tiles_h;                  // work units per row of tiles: ceil(H / tile width)
+    float max_range;              // hits beyond this range are dropped (+inf: none) -- lsb200_set_sensor_limits
+    const uint8_t *az_mask;       // [H] 1 = azimuth step fired; nullptr = all
     float *t_out;                 // [n_rays]
     int32_t *tri_out;             // [n_rays]
     uint8_t *points;              // [n_rays] records

@@ -60,6 +60,10 @@ struct Sensor {
     int V = 0, H = 0;
     float R[9], Rinv[9], T[3], q[4];
     DevBuf tables;                     // sin_t[V] cos_t[V] sin_p[H] cos_p[H]
+    DevBuf az_mask;                    // [H] bytes, only while an azimuth window is set
+    bool has_mask = false;
+    float max_range = INFINITY;
+    std::vector<float> az_deg;         // azimuth of every step, as the ray generator computes it
     DevBuf t, tri, points, blocks;     // per-ray results, compacted points, ordered-compaction scratch
     DevBuf points_b;                   // second output slot: lsb200_run_frames overlaps its D2H with the next frame
     int n_rays() const { return V * H; }
@@ -252,7 +256,7 @@ int lsb200_destroy(lsb200_ctx *c)
         DeviceGuard dg(c->device);
         cudaStreamSynchronize(c->stream);
         for (auto &kv : c->geoms) { kv.second.verts.release(); kv.second.elems.release(); }
-        for (auto &s : c->sensors) { s.tables.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
+        for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
                           &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts};
@@ -339,6 +343,9 @@ int lsb200_set_sensor(lsb200_ctx *c, int idx, const float *elev_deg, int V, floa
         const float phi = (float)((double)prePhi * M_PI / 180.0);
         tab[2 * V + h] = sinf(phi); tab[2 * V + H + h] = cosf(phi);
     }
+    s.az_deg.resize(H);
+    for (int h = 0; h < H; ++h) s.az_deg[h] = az_begin + step * (float)h;
+    s.has_mask = false; s.max_range = INFINITY;
     LSB_CU(c, s.tables.reserve(tab.size() * 4, c->stream));
     LSB_CU(c, cudaMemcpyAsync(s.tables.p, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, c->stream));
     LSB_CU(c, cudaStreamSynchronize(c->stream));     // tab is a local
@@ -346,6 +353,33 @@ int lsb200_set_sensor(lsb200_ctx *c, int idx, const float *elev_deg, int V, floa
     c->sensors_dirty = true;
     ++c->sensors_epoch;
     if (idx == 0 && c->frame_mode == LSB200_FRAME_SENSOR) c->committed = false;   // scene lives in this sensor's frame
+    return LSB200_OK;
+}
+
+int lsb200_set_sensor_limits(lsb200_ctx *c, int idx, float max_range, float az_min_deg, float az_max_deg)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set)
+        return fail(c, LSB200_ERR_INVALID, "set_sensor_limits: sensor %d not set", idx);
+    if (!(az_min_deg <= az_max_deg)) return fail(c, LSB200_ERR_INVALID, "set_sensor_limits: empty azimuth window");
+    DeviceGuard dg(c->device);
+    Sensor &s = c->sensors[idx];
+    s.max_range = (max_range > 0.0f) ? max_range : INFINITY;
+    s.has_mask = !(az_min_deg <= -180.0f && az_max_deg >= 180.0f);
+    if (s.has_mask) {
+        std::vector<uint8_t> m((size_t)s.H);
+        for (int h = 0; h < s.H; ++h) {
+            float w = s.az_deg[h];                       // wrapped into (-180, 180]
+            while (w > 180.0f) w -= 360.0f;
+            while (w <= -180.0f) w += 360.0f;
+            m[h] = (w >= az_min_deg && w <= az_max_deg) ? 1 : 0;
+        }
+        LSB_CU(c, s.az_mask.reserve(m.size(), c->stream));
+        LSB_CU(c, cudaMemcpyAsync(s.az_mask.p, m.data(), m.size(), cudaMemcpyHostToDevice, c->stream));
+        LSB_CU(c, cudaStreamSynchronize(c->stream));
+    }
+    c->sensors_dirty = true;
     return LSB200_OK;
 }
 
@@ -662,6 +696,7 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
         d.sin_t = tab; d.cos_t = tab + s.V; d.sin_p = tab + 2 * s.V; d.cos_p = tab + 2 * s.V + s.H;
         std::memcpy(d.R, s.R, 36); std::memcpy(d.Rinv, s.Rinv, 36); std::memcpy(d.T, s.T, 12);
         d.V = s.V; d.H = s.H; d.n_rays = s.n_rays();
+        d.max_range = s.max_range; d.az_mask = s.has_mask ? s.az_mask.as<uint8_t>() : nullptr;
         d.t_out = s.t.as<float>(); d.tri_out = s.tri.as<int32_t>(); d.points = s.points.as<uint8_t>();
         d.count = c->d_counts.as<uint32_t>() + i; d.block_counts = s.blocks.as<uint32_t>();
         d.tiles_h = (s.H + tw - 1) / tw;

@@ -416,7 +416,9 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
     float best = INFINITY; int bi = -1;
     float dsx = 0.f, dsy = 0.f, dsz = 1.f;
     RayStats rs{0u, 0u, 0u, 0u, 0u, 0u};
-    if (valid) {
+    const bool fired = valid && (S.az_mask == nullptr || __ldg(S.az_mask + h) != 0);
+    if (valid && !fired) { S.t_out[ray] = INFINITY; S.tri_out[ray] = -1; }      // outside the azimuth window: no return
+    if (fired) {
         Ray r;
         float omax;
         make_ray(S, P.world_frame, v, h, r, dsx, dsy, dsz, omax);
@@ -429,6 +431,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             else
             trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
         }
+        if (!(best <= S.max_range)) { best = INFINITY; bi = -1; }                // detection radius (closest hit beyond it: no return)
         S.t_out[ray] = best;
         S.tri_out[ray] = bi;
     }

@@ -42,6 +42,14 @@ B200Tracer::B200Tracer(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceSt
     }
 }
 
+int B200Tracer::setSensorLimits(bool _on)
+{
+    float lo = -180.0f, hi = 180.0f;
+    auto dev = getSensorConfig();
+    if (_on) dev->horizontalAngleRange(lo, hi);
+    return lsb200_set_sensor_limits(_ctx, 0, _on ? dev->detectionRadius() : 0.0f, lo, hi);
+}
+
 B200Tracer::~B200Tracer()
 {
     if (_ctx) lsb200_destroy(_ctx);

@@ -39,6 +39,8 @@ public:
     void setOrderedOutput(bool _on) { _ordered = _on; }       // points in ray-id order (deterministic)
     void setRingZeroCompat(bool _on) { _ringZero = _on; }     // ring = 0 like the Embree path (SRC/EmbreeTracer.cpp:333-334)
     void setWorldFramePoints(bool _on) { _worldPoints = _on; } // emit R p + T (CloudTransformer, SRC/CloudTransformer.cpp:202-265)
+    // apply the device config's detection_radius / horizontal_angle_range (lsb200_set_sensor_limits); off = reference behaviour
+    int setSensorLimits(bool _on);
     int traceRaw(std::vector<float> &_t, std::vector<int32_t> &_tri);   // per-ray results (parity tests)
     lsb200_ctx *context() { return _ctx; }
     std::string lastError() const;

@@ -175,6 +175,11 @@ int LidarDevice::loadTransformationFromJson(const json::Value &t)
         _device.tz = s["tz"].asFloat(0.0f);
         updateRotation();
     }
+    if (t.isMember("detection_radius")) _device.detectionRadius = t["detection_radius"].asFloat(0.0f);
+    if (t.isMember("horizontal_angle_range") && t["horizontal_angle_range"].size() == 2) {
+        _device.horizontalAngleRange[0] = t["horizontal_angle_range"][size_t(0)].asFloat(-180.0f);
+        _device.horizontalAngleRange[1] = t["horizontal_angle_range"][size_t(1)].asFloat(180.0f);
+    }
     return 0;
 }
 
@@ -183,7 +188,10 @@ void LidarDevice::initMessage(PointCloud2::Ptr _msg, int _frameIndex)
     _msg->fields.clear();
     for (const auto &field : _message.fields) _msg->fields.push_back(field);
     _msg->header.frame_id = _message.frameId;
-    _msg->header.stamp = std::chrono::duration<double>(std::chrono::system_clock::now().time_since_epoch()).count();
+    {
+        const auto ns = std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::system_clock::now().time_since_epoch()).count();
+        _msg->header.stamp = Time((uint32_t)(ns / 1000000000LL), (uint32_t)(ns % 1000000000LL));
+    }
     _msg->header.seq = static_cast<uint32_t>(_frameIndex);
     _msg->height = 1;
     _msg->width = 0;

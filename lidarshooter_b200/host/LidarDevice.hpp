@@ -41,6 +41,8 @@ public:
     static Ptr create(const std::vector<float> &_vertical, float _begin, float _end, unsigned _count,
                       const float _qwxyz[4], const float _txyz[3], const std::string &_sensorUid = "synthetic");
     Ptr getPtr() { return shared_from_this(); }
+    float detectionRadius() const { return _device.detectionRadius; }
+    void horizontalAngleRange(float &_lo, float &_hi) const { _lo = _device.horizontalAngleRange[0]; _hi = _device.horizontalAngleRange[1]; }
 
     void initialize(const std::string &_config, const std::string &_sensorUid = "");
     void initMessage(PointCloud2::Ptr _msg, int _frameIndex);                       // SRC/LidarDevice.cpp:94-115
@@ -85,6 +87,9 @@ private:
         unsigned sensorApiPort = 9080;
         float tx = 0.f, ty = 0.f, tz = 0.f, qw = 1.f, qx = 0.f, qy = 0.f, qz = 0.f;
         float R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, Rinv[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+        // carried by the reference's config, never applied by it (config/hesai-pandar-XT-32-lidar_0000.json:14-18)
+        float detectionRadius = 0.f;                 // 0 = unlimited
+        float horizontalAngleRange[2] = {-180.f, 180.f};
     } _device;
     struct {
         std::string frameId = "PandarXT-32";

@@ -42,9 +42,24 @@ struct PointField {
     enum { INT8 = 1, UINT8 = 2, INT16 = 3, UINT16 = 4, INT32 = 5, UINT32 = 6, FLOAT32 = 7, FLOAT64 = 8 };
 };
 
+// ros::Time: whole seconds + nanoseconds (a double cannot hold a present-day stamp to the nanosecond)
+struct Time {
+    uint32_t sec = 0, nsec = 0;
+    Time() = default;
+    Time(uint32_t s, uint32_t ns) : sec(s), nsec(ns) {}
+    explicit Time(double t)
+    {
+        const double whole = t < 0.0 ? 0.0 : (double)(uint64_t)t;
+        double frac = (t < 0.0 ? 0.0 : t - whole) * 1e9 + 0.5;
+        sec = (uint32_t)whole; nsec = (uint32_t)frac;
+        if (nsec >= 1000000000u) { nsec -= 1000000000u; ++sec; }
+    }
+    double toSec() const { return (double)sec + 1e-9 * (double)nsec; }
+};
+
 struct Header {
     uint32_t seq = 0;
-    double stamp = 0.0;        // seconds; the reference uses ros::Time::now()
+    Time stamp;                // the reference uses ros::Time::now()
     std::string frame_id;
 };
 

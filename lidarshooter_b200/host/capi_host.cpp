@@ -8,6 +8,7 @@
 #include "AffineMesh.hpp"
 #include "B200Tracer.hpp"
 #include "CloudConverter.hpp"
+#include "CloudSerializer.hpp"
 #include "LidarDevice.hpp"
 #include "MeshIO.hpp"
 
@@ -178,6 +179,42 @@ int lsbh_tracer_cloud(lsbh_tracer *t, lsb200_cloud_header *h, const uint8_t **da
     h->is_bigendian = c->is_bigendian; h->is_dense = c->is_dense; h->n_fields = (uint8_t)c->fields.size(); h->reserved = 0;
     *data = c->data.data(); *n = c->data.size();
     return 0;
+}
+int lsbh_tracer_set_sensor_limits(lsbh_tracer *t, int on) { return t->p->setSensorLimits(on != 0); }
+int lsbh_device_limits(const lsbh_device *d, float *radius, float *az_lo, float *az_hi)
+{
+    *radius = d->p->detectionRadius();
+    d->p->horizontalAngleRange(*az_lo, *az_hi);
+    return 0;
+}
+long lsbh_tracer_serialize_cloud(lsbh_tracer *t, double stamp, int fix_row_step, uint8_t *out, size_t capacity)
+{
+    PointCloud2::Ptr c = t->p->getTraceCloud();
+    if (stamp >= 0.0) c->header.stamp = Time(stamp);
+    std::vector<uint8_t> msg;
+    const size_t n = serializePointCloud2(*c, msg, fix_row_step != 0);
+    if (n != serializedLength(*c)) return -2;
+    if (out && n <= capacity) std::memcpy(out, msg.data(), n);
+    return (long)n;
+}
+long lsbh_cloud_reserialize(const uint8_t *msg, size_t len, uint8_t *out, size_t capacity, lsb200_cloud_header *hdr, double *stamp)
+{
+    PointCloud2 c;
+    const size_t used = deserializePointCloud2(msg, len, c);
+    if (used == 0) return -1;
+    if (hdr) {
+        hdr->seq = c.header.seq; hdr->height = c.height; hdr->width = c.width; hdr->point_step = c.point_step; hdr->row_step = c.row_step;
+        hdr->is_bigendian = c.is_bigendian; hdr->is_dense = c.is_dense; hdr->n_fields = (uint8_t)c.fields.size(); hdr->reserved = 0;
+    }
+    if (stamp) *stamp = c.header.stamp.toSec();
+    std::vector<uint8_t> again;
+    const size_t n = serializePointCloud2(c, again, false);
+    if (out && n <= capacity) std::memcpy(out, again.data(), n);
+    return (long)n;
+}
+int lsbh_tracer_append_cloud_to_file(lsbh_tracer *t, const char *path, int fix_row_step)
+{
+    return appendCloudToFile(path, *t->p->getTraceCloud(), fix_row_step != 0) ? 0 : -1;
 }
 int lsbh_tracer_trace_raw(lsbh_tracer *t, float *t_out, int32_t *tri_out)
 {

@@ -19,6 +19,8 @@ SYMBOLS = [
     "lsbh_tracer_add_geometry", "lsbh_tracer_remove_geometry", "lsbh_tracer_geometry_count", "lsbh_tracer_geometry_id",
     "lsbh_tracer_update_geometry", "lsbh_tracer_update_geometry_euler", "lsbh_tracer_commit_scene",
     "lsbh_tracer_trace_scene", "lsbh_tracer_set_flags", "lsbh_tracer_cloud", "lsbh_tracer_trace_raw",
+    "lsbh_tracer_serialize_cloud", "lsbh_cloud_reserialize", "lsbh_tracer_append_cloud_to_file",
+    "lsbh_device_limits", "lsbh_tracer_set_sensor_limits",
     "lsbh_trajectory_poses",
 ]
 
@@ -68,6 +70,12 @@ def lib():
         "lsbh_tracer_cloud": (C.c_int, [vp, C.POINTER(capi.CloudHeader), C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_size_t)]),
         "lsbh_tracer_trace_raw": (C.c_int, [vp, f32p, i32p]),
         "lsbh_trajectory_poses": (C.c_int, [cp, C.c_float, f32p, C.c_int]),
+        "lsbh_tracer_serialize_cloud": (C.c_long, [vp, C.c_double, C.c_int, C.POINTER(C.c_uint8), C.c_size_t]),
+        "lsbh_cloud_reserialize": (C.c_long, [C.POINTER(C.c_uint8), C.c_size_t, C.POINTER(C.c_uint8), C.c_size_t,
+                                              C.POINTER(capi.CloudHeader), C.POINTER(C.c_double)]),
+        "lsbh_tracer_append_cloud_to_file": (C.c_int, [vp, cp, C.c_int]),
+        "lsbh_device_limits": (C.c_int, [vp, f32p, f32p, f32p]),
+        "lsbh_tracer_set_sensor_limits": (C.c_int, [vp, C.c_int]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -99,6 +107,12 @@ class LidarDevice:
         if self._h:
             self._L.lsbh_device_destroy(self._h)
             self._h = None
+
+    def limits(self):
+        """(detection_radius, az_lo, az_hi) of the device config."""
+        r, lo, hi = C.c_float(), C.c_float(), C.c_float()
+        self._L.lsbh_device_limits(self._h, C.byref(r), C.byref(lo), C.byref(hi))
+        return r.value, lo.value, hi.value
 
     sensor_uid = property(lambda s: s._L.lsbh_device_sensor_uid(s._h).decode())
     total_rays = property(lambda s: s._L.lsbh_device_total_rays(s._h))
@@ -226,11 +240,41 @@ class B200Tracer:
         buf = np.ctypeslib.as_array(data, shape=(n.value,)).copy() if n.value else np.zeros(0, np.uint8)
         return h, buf.reshape(-1, 32)
 
+    def setSensorLimits(self, on=True):
+        return self._L.lsbh_tracer_set_sensor_limits(self._h, int(on))
+
+    def serializeCloud(self, stamp=-1.0, fix_row_step=False):
+        """ROS-1 wire bytes of the traced sensor_msgs/PointCloud2 (host/CloudSerializer.hpp)."""
+        n = self._L.lsbh_tracer_serialize_cloud(self._h, float(stamp), int(fix_row_step), None, 0)
+        if n < 0:
+            raise RuntimeError("serialize failed")
+        out = np.empty(n, np.uint8)
+        m = self._L.lsbh_tracer_serialize_cloud(self._h, float(stamp), int(fix_row_step), out.ctypes.data_as(C.POINTER(C.c_uint8)), n)
+        assert m == n
+        return out
+
+    def appendCloudToFile(self, path, fix_row_step=False):
+        return self._L.lsbh_tracer_append_cloud_to_file(self._h, str(path).encode(), int(fix_row_step))
+
     def traceRaw(self):
         R = self._dev.total_rays
         t, tri = np.empty(R, np.float32), np.empty(R, np.int32)
         rc = self._L.lsbh_tracer_trace_raw(self._h, _fp(t), tri.ctypes.data_as(C.POINTER(C.c_int32)))
         return rc, t, tri
+
+
+def reserialize_cloud(msg):
+    """Parses ROS-1 PointCloud2 wire bytes with the C++ reader and serialises them again.
+    Returns (bytes, header, stamp); raises on malformed input."""
+    L = lib()
+    msg = np.ascontiguousarray(msg, np.uint8)
+    h, stamp = capi.CloudHeader(), C.c_double()
+    out = np.empty(max(msg.size, 1), np.uint8)
+    n = L.lsbh_cloud_reserialize(msg.ctypes.data_as(C.POINTER(C.c_uint8)), msg.size, out.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                 out.size, C.byref(h), C.byref(stamp))
+    if n < 0:
+        raise ValueError("malformed PointCloud2 message")
+    return out[:n], h, stamp.value
 
 
 def trajectory_poses(path, period=0.1):

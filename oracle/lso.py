@@ -257,7 +257,32 @@ def concat_scene(sensor, meshes, mode=0):
     return np.concatenate(vs), np.concatenate(ts)
 
 
-def scan(sensor, meshes, mode=0, use_bvh=None, ring_mode=0):
+def azimuth_degrees(sensor):
+    """Azimuth of every step as the ray generator computes it: begin + step * float(h) in float32 (SRC/LidarDevice.cpp:306)."""
+    step = azimuth_step(sensor.az_begin, sensor.az_end, sensor.H)
+    return (np.float32(sensor.az_begin) + step * np.arange(sensor.H, dtype=np.float32)).astype(np.float32)
+
+
+def apply_limits(sensor, t, tri, max_range=0.0, az_window=(-180.0, 180.0)):
+    """Sensor limits of include/lsb200.h: lsb200_set_sensor_limits (semantics defined there; the reference only carries
+    the config keys).  Returns new (t, tri)."""
+    t, tri = t.copy(), tri.copy()
+    w = azimuth_degrees(sensor).copy()
+    for _ in range(4):
+        w = np.where(w > np.float32(180), w - np.float32(360), w).astype(np.float32)
+        w = np.where(w <= np.float32(-180), w + np.float32(360), w).astype(np.float32)
+    fired = (w >= np.float32(az_window[0])) & (w <= np.float32(az_window[1]))
+    if az_window[0] <= -180.0 and az_window[1] >= 180.0:
+        fired[:] = True
+    dead = np.tile(~fired, sensor.V)
+    if max_range and max_range > 0:
+        dead |= ~(t <= np.float32(max_range))
+    t[dead] = np.inf
+    tri[dead] = -1
+    return t, tri
+
+
+def scan(sensor, meshes, mode=0, use_bvh=None, ring_mode=0, max_range=0.0, az_window=(-180.0, 180.0)):
     """One traceScene.  mode 0 = sensor frame (the reference's arithmetic: the SCENE is moved into the
     sensor frame, rays start at 0); mode 1 = world frame (rays are moved: o = T, d = R d_s).
     Returns dict(t, tri, points) with points in ray-id order."""
@@ -278,5 +303,7 @@ def scan(sensor, meshes, mode=0, use_bvh=None, ring_mode=0):
         b.close()
     else:
         t, tri = trace_brute(verts, tris, org, dirs)
+    if (max_range and max_range > 0) or az_window[0] > -180.0 or az_window[1] < 180.0:
+        t, tri = apply_limits(sensor, t, tri, max_range, az_window)
     pts = pack_points(dirs_s, t, tri, sensor.H, ring_mode)
     return {"t": t, "tri": tri, "points": pts, "verts": verts, "tris": tris}

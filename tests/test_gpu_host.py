@@ -64,6 +64,27 @@ def test_trace_scene_cloud(setup, meshes):
     rc, t, tri = tracer.traceRaw()
     assert rc == 0 and np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
 
+    # the XT-32 config's own limits (1000 m, +-180 deg) change nothing
+    assert tracer.setSensorLimits(True) == 0 and tracer.traceScene(1) == 0 and tracer.getTraceCloud()[0].width == 1781
+    assert tracer.setSensorLimits(False) == 0
+
+    # ROS-1 wire bytes of the cloud: header of initMessage + the 32-byte records, row_step 0 like the
+    # reference or width * point_step behind the flag
+    from test_host import _ros1_pointcloud2, XT32_FIELDS
+    for fix, row_step in ((False, 0), (True, 1781 * 32)):
+        wire = tracer.serializeCloud(stamp=12.25, fix_row_step=fix)
+        want = _ros1_pointcloud2(1, 12, 250000000, "PandarXT-32", 1, 1781, XT32_FIELDS, False, 32, row_step, pts.tobytes(), True)
+        assert bytes(wire) == want
+    path = os.path.join(os.environ.get("TMPDIR", "/tmp"), "lsb200_cloud_stream.bin")
+    if os.path.exists(path):
+        os.remove(path)
+    assert tracer.appendCloudToFile(path) == 0 and tracer.appendCloudToFile(path, fix_row_step=True) == 0
+    blob = open(path, "rb").read()
+    n0 = int.from_bytes(blob[:4], "little")
+    assert blob[4:4 + n0] == _ros1_pointcloud2(1, 12, 250000000, "PandarXT-32", 1, 1781, XT32_FIELDS, False, 32, 0, pts.tobytes(), True)
+    assert int.from_bytes(blob[4 + n0:8 + n0], "little") == len(blob) - 8 - n0
+    os.remove(path)
+
     # world-frame points = CloudTransformer::applyInverseTransform (SRC/CloudTransformer.cpp:202-265), on the device
     tracer.setFlags(ordered=True, world_points=True)
     assert tracer.traceScene(2) == 0

@@ -479,3 +479,88 @@ def test_city_10m_size_independent_properties():
     tol = 2e-3
     assert min(w0.min(), w1.min(), w2.min()) > -tol and abs((w0 + w1 + w2) - 1).max() < 1e-6
     ctx.close()
+
+
+def test_trajectory_batch_moving_meshes_rebuild_each_frame(meshes):
+    """BASELINE config 5 at reduced frame count: the 1M-triangle heightfield + 16 instances of `ben`,
+    each following the looped trajectory.json twists with a phase offset of 0.9 s, FULL LBVH rebuild every frame,
+    128 x 3601 rays, frames sharded round-robin over 2 ranks (this process plays rank 1).  Every traced frame is
+    compared bit-for-bit (t, triangle id, ordered points) with the oracle's CPU BVH on the same poses."""
+    from lidarshooter_b200 import shard
+    hv, ht = synth.heightfield()
+    bv, bt = meshes["ben_v"], meshes["ben_t"]
+    loop = synth.trajectory_poses([(10.0, (0, 5, 0), (0, 0, 1)), (5.0, (1, 0, 0), (0, 0, -1))])     # 150 ticks
+    n_inst, n_frames_total = 16, 12
+    mine = [f for d, f in shard.shard_scans(1, n_frames_total, rank=1, world=2, major="frame")]
+    assert mine == [1, 3, 5, 7, 9, 11]
+    elev, b, e, H = synth.lidar_table()
+    T = (0.0, 0.0, 4.0)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), T)
+    s = lso.Sensor(elev, b, e, H, (1, 0, 0, 0), T)
+    add_mesh(ctx, "terrain", hv, ht)
+    base = [np.array([(i % 4 - 1.5) * 12.0, (i // 4 - 1.5) * 12.0, 3.0], np.float32) for i in range(n_inst)]
+    for i in range(n_inst):
+        add_mesh(ctx, f"ben{i:02d}", bv, bt)
+
+    def affines(frame):
+        A = np.zeros((1 + n_inst, 12), np.float32)
+        A[0] = IDENT
+        for i in range(n_inst):
+            lin, ang = loop[(frame + 9 * i) % len(loop)]
+            A[1 + i] = lso.affine_from_components(lin * np.float32(0.2) + base[i], ang)
+        return A
+
+    A = np.stack([affines(f) for f in mine])
+    R = ctx.ray_count(0)
+    outs = [[np.zeros((R, 32), np.uint8)] for _ in mine]
+    rc, counts = ctx.run_frames(A, [[o[0].ctypes.data] for o in outs], [R], first=0, count=1,
+                                commit_mode=capi.COMMIT_REBUILD, flags=capi.TRACE_ORDERED)
+    assert rc == 0, ctx.last_error()
+    assert ctx.stats().last_commit_was_rebuild == 1
+    assert int(ctx.stats().n_triangles) == 1_000_000 + n_inst * bt.shape[0]
+    for k, f in enumerate(mine[:3] + mine[-1:]):
+        kk = mine.index(f)
+        ref = lso.scan(s, [(hv, ht, IDENT)] + [(bv, bt, A[kk, 1 + i]) for i in range(n_inst)], mode=1, use_bvh=True)
+        assert counts[kk, 0] == ref["points"].shape[0]
+        assert np.array_equal(outs[kk][0][:counts[kk, 0]], ref["points"])
+    # the last frame is still resident: per-ray results too
+    rc, t, tri = ctx.trace_raw(0)
+    assert np.array_equal(t, ref["t"]) and np.array_equal(tri, ref["tri"])
+    assert (tri >= 1_000_000).sum() > 100          # some rays do hit the moving meshes
+    ctx.close()
+
+
+@pytest.mark.parametrize("mode", [6, 1, 2])
+def test_sensor_limits_detection_radius_and_azimuth_window(meshes, mode):
+    """detection radius and horizontal angle range (config keys the reference never applies), as
+    lsb200_set_sensor_limits defines them; bit-exact against the oracle with the same limits; off by default."""
+    args = xt32_sensor_args("0000")
+    s = lso.Sensor(*args)
+    ms = [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)]
+    ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: mode})
+    add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
+    add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
+    assert ctx.commit_scene() == 0
+    base = lso.scan(s, ms)
+    r_med = float(np.median(base["t"][base["tri"] >= 0]))
+    for max_range, win in ((0.0, (-180.0, 180.0)), (r_med, (-180.0, 180.0)), (0.0, (-90.0, 45.5)), (1.5 * r_med, (100.0, 180.0)),
+                           (1000.0, (-180.0, 180.0))):
+        assert ctx.set_sensor_limits(max_range, win[0], win[1]) == 0
+        rc, pts = ctx.trace_scene(0, capi.TRACE_ORDERED)
+        rc2, t, tri = ctx.trace_raw()
+        ref = lso.scan(s, ms, max_range=max_range, az_window=win)
+        assert rc == 0 and rc2 == 0
+        assert np.array_equal(t, ref["t"]) and np.array_equal(tri, ref["tri"]) and np.array_equal(pts, ref["points"])
+        if max_range == r_med:
+            assert 0 < pts.shape[0] < base["points"].shape[0] and float(t[tri >= 0].max()) <= np.float32(r_med)
+        if win == (-90.0, 45.5):
+            assert 0 < pts.shape[0] < base["points"].shape[0]
+        if max_range in (0.0, 1000.0) and win == (-180.0, 180.0):
+            assert pts.shape[0] == 1781
+    assert ctx.set_sensor_limits(5.0, 10.0, -10.0) == capi.ERR_INVALID
+    # set_sensor clears the limits
+    ctx.set_sensor(*args)
+    assert ctx.commit_scene() == 0
+    assert ctx.trace_scene(0, capi.TRACE_ORDERED)[1].shape[0] == 1781
+    ctx.close()

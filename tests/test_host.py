@@ -38,6 +38,13 @@ def test_lidar_device_config():
     assert d2.sensor_uid == "other_uid"
 
 
+def test_lidar_device_limits_from_config():
+    """detection_radius / horizontal_angle_range (config/hesai-pandar-XT-32-lidar_0000.json:14-18)"""
+    dev = hostapi.LidarDevice(os.path.join(GOLDEN, "xt32_lidar_0000.json"))
+    assert dev.limits() == (1000.0, -180.0, 180.0)
+    dev.close()
+
+
 def test_lidar_device_init_message():
     """SRC/test/LidarDevice_test.cpp:61-76"""
     d = hostapi.LidarDevice(CFG0)
@@ -119,3 +126,33 @@ def test_trajectory_player():
     ref = np.array([np.concatenate(p) for p in ref], np.float32)
     assert np.allclose(poses, ref, rtol=0, atol=2e-4)
     assert np.allclose(poses[99, 3:], [0, 0, 10.0], atol=1e-4) and np.allclose(poses[-1, 3:], [0, 0, 5.0], atol=1e-4)
+
+
+def _ros1_pointcloud2(seq, sec, nsec, frame_id, height, width, fields, bigendian, point_step, row_step, data, dense):
+    """sensor_msgs/PointCloud2 as roscpp serialises it (little-endian, length-prefixed strings and arrays)."""
+    import struct
+    out = struct.pack("<III", seq, sec, nsec) + struct.pack("<I", len(frame_id)) + frame_id.encode()
+    out += struct.pack("<II", height, width) + struct.pack("<I", len(fields))
+    for name, offset, datatype, count in fields:
+        out += struct.pack("<I", len(name)) + name.encode() + struct.pack("<IBI", offset, datatype, count)
+    out += struct.pack("<BII", int(bigendian), point_step, row_step) + struct.pack("<I", len(data)) + bytes(data)
+    return out + struct.pack("<B", int(dense))
+
+
+XT32_FIELDS = [("x", 0, 7, 1), ("y", 4, 7, 1), ("z", 8, 7, 1), ("intensity", 16, 7, 1), ("ring", 20, 4, 1)]
+
+
+def test_pointcloud2_wire_reader_round_trip():
+    """host/CloudSerializer: parse + serialise of a hand-packed ROS-1 message is the identity; truncation is refused."""
+    rng = np.random.default_rng(3)
+    data = rng.integers(0, 256, 7 * 32, dtype=np.uint8)
+    msg = _ros1_pointcloud2(41, 1700000000, 123456789, "PandarXT-32", 1, 7, XT32_FIELDS, False, 32, 0, data, True)
+    again, h, stamp = hostapi.reserialize_cloud(np.frombuffer(msg, np.uint8))
+    assert bytes(again) == msg
+    assert (h.seq, h.height, h.width, h.point_step, h.row_step, h.n_fields, h.is_dense) == (41, 1, 7, 32, 0, 5, 1)
+    assert abs(stamp - 1700000000.123456789) < 1e-6
+    empty = _ros1_pointcloud2(0, 0, 0, "", 1, 0, [], False, 32, 0, b"", False)
+    assert bytes(hostapi.reserialize_cloud(np.frombuffer(empty, np.uint8))[0]) == empty
+    for cut in (3, 20, len(msg) - 1, len(msg) - 40):
+        with pytest.raises(ValueError):
+            hostapi.reserialize_cloud(np.frombuffer(msg[:cut], np.uint8))
