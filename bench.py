@@ -317,6 +317,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--small", action="store_true", help="tiny scene for smoke runs (NOT the benchmark)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-xt32", action="store_true", help="skip the XT-32 scan leg (profiling runs of the main step)")
     ap.add_argument("--traversal", type=int, default=None)
     ap.add_argument("--top-nodes", type=int, default=None)
     ap.add_argument("--leaf", type=int, default=None)
@@ -511,7 +512,7 @@ def main():
                          "ms_per_launch": ms_trace},
         }
     ctx.close()
-    if rank == 0:
+    if rank == 0 and not args.no_xt32:
         line["xt32_scan"] = xt32_scan_leg(local, cpu=(world == 1 and not args.no_cpu_baseline))
     if world > 1:
         dist.barrier()
