@@ -81,6 +81,10 @@ enum {
                                       the root-to-origin chain instead of from the root; 0 = every ray starts at the root */
     LSB200_OPT_TILE_WIDTH = 9,     /* a 32-ray work unit is a tile of W azimuth steps x 32/W channels of one device's
                                       table; W = 1, 2, 4, 8 (default), 16 or 32 */
+    LSB200_OPT_MORTON_LAYOUT = 11, /* Morton bits: (bits of x and of y) << 4 | bits of z, 2 * bxy + bz <= 32, bz <= min(bxy, 10);
+                                      the extra x / y bits are interleaved above the 3-way part.  0 = the default */
+    LSB200_OPT_MORTON_ASPECT = 12, /* 100 * alpha: the next Morton bit goes to the axis with the largest (cell size)^alpha.
+                                      0 = round robin x, y, z; 100 = longest side first (cubic cells); default 60 */
     LSB200_OPT_SMALL_BUILD = 10    /* 1 (default) = scenes of <= 16384 triangles in <= 16 geometries are committed by ONE
                                       fused single-CTA kernel (transform, Morton, sort, hierarchy, fit); 0 = always the
                                       multi-kernel pipeline */

@@ -22,6 +22,9 @@ struct SceneDev {
     int top_cap;             // nodes reserved for the top-level copy
     int leaf_max;
     int morton_uniform;      // 1: one scale (the largest extent) for all three axes -> cubic Morton cells
+    int morton_bxy, morton_bz;   // explicit Morton layout (bits of x and y / of z) when morton_bxy > 0, see morton_plan()
+    float morton_alpha;          // otherwise: bit allocation by extent^alpha (0 = round robin, 1 = cubic cells)
+    struct MortonPlan *plan;     // device copy of the plan of this commit (k_morton_plan)
 };
 
 // Eigen-ordered 3-term dot: a0*b0 + (a1*b1 + a2*b2)  (oracle/lsb_oracle.c: dot3_eigen)
@@ -108,8 +111,83 @@ __device__ __forceinline__ uint32_t expand10(uint32_t v)
     return v;
 }
 
-// ---- (2) 30-bit Morton code of each triangle's AABB centre, normalised to the scene bounds -----------------
-__device__ __forceinline__ uint32_t morton_key(const SceneDev &S, int g, const float slo[3], const float shi[3])
+// ---- (2) Morton code of each triangle's AABB centre, normalised to the scene bounds ------------------------
+// Which key bit belongs to which axis is decided per commit from the scene's extent (MortonPlan): walking down from
+// bit 31, the next bit goes to the axis whose current cell size, raised to the power alpha, is largest, and that
+// cell size is halved.  alpha = 0 is the textbook round-robin x, y, z (every axis normalised to its own extent);
+// alpha = 1 splits the longest side first (cubic cells); the default in between gives a flat scene (a city:
+// 2 km x 2 km x 80 m) a few x / y bits ahead of z without starving z -- measured in profiles/design_choices_r01.md.
+// An explicit layout (bxy bits for x and y, bz for z; the extra x / y bits on top) can be forced for experiments.
+struct MortonPlan {
+    uint32_t mask[3];        // key bits of x, y, z
+    float scale[3];          // 2^bits of each axis
+};
+
+__device__ __forceinline__ void morton_plan(const SceneDev &S, const float slo[3], const float shi[3], MortonPlan &P)
+{
+    P.mask[0] = P.mask[1] = P.mask[2] = 0u;
+    int bits[3] = {0, 0, 0};
+    if (S.morton_bxy > 0) {
+        int L = 2 * S.morton_bxy + S.morton_bz - 1;
+        for (int k = 0; k < S.morton_bxy - S.morton_bz; ++k) { P.mask[0] |= 1u << L--; P.mask[1] |= 1u << L--; }
+        for (int k = 0; k < S.morton_bz; ++k) { P.mask[0] |= 1u << L--; P.mask[1] |= 1u << L--; P.mask[2] |= 1u << L--; }
+        bits[0] = bits[1] = S.morton_bxy; bits[2] = S.morton_bz;
+    } else {
+        float cur[3];
+        float emax = 0.0f;
+        for (int k = 0; k < 3; ++k) emax = fmaxf(emax, shi[k] - slo[k]);
+        for (int k = 0; k < 3; ++k) {
+            const float e = S.morton_uniform ? emax : (shi[k] - slo[k]);
+            cur[k] = (e > 0.0f && emax > 0.0f) ? __powf(e / emax, S.morton_alpha) : (S.morton_alpha > 0.0f ? 0.0f : 1.0f);
+        }
+        for (int L = 31; L >= 0; --L) {
+            int a = 0;
+            if (cur[1] > cur[a]) a = 1;
+            if (cur[2] > cur[a]) a = 2;
+            if (bits[a] >= 16) {                         // an axis never takes more than 16 bits
+                a = (a + 1) % 3;
+                if (bits[a] >= 16 || cur[(a + 1) % 3] > cur[a]) a = bits[(a + 1) % 3] < 16 ? (a + 1) % 3 : a;
+            }
+            P.mask[a] |= 1u << L;
+            ++bits[a];
+            cur[a] *= 0.5f;
+        }
+    }
+    for (int k = 0; k < 3; ++k) P.scale[k] = (float)(1u << bits[k]);
+}
+
+// bit j of v -> the j-th lowest set bit of mask
+__device__ __forceinline__ uint32_t deposit_bits(uint32_t v, uint32_t mask)
+{
+    uint32_t key = 0;
+    while (mask) {
+        const uint32_t low = mask & (0u - mask);
+        if (v & 1u) key |= low;
+        v >>= 1;
+        mask ^= low;
+    }
+    return key;
+}
+
+// Per-CTA lookup tables of the plan: tab[axis][nibble][value] = the key bits of that 4-bit slice of the coordinate.
+struct MortonTables {
+    uint32_t tab[3][4][16];
+    float scale[3];
+};
+__device__ __forceinline__ void morton_tables_fill(const MortonPlan &P, MortonTables &T, int tid)      // tid in [0, 192)
+{
+    if (tid < 192) {
+        const int a = tid >> 6, nib = (tid >> 4) & 3, v = tid & 15;
+        T.tab[a][nib][v] = deposit_bits((uint32_t)v << (4 * nib), P.mask[a]);
+    }
+    if (tid < 3) T.scale[tid] = P.scale[tid];
+}
+__device__ __forceinline__ uint32_t morton_lookup(const MortonTables &T, int a, uint32_t i)
+{
+    return T.tab[a][0][i & 15u] | T.tab[a][1][(i >> 4) & 15u] | T.tab[a][2][(i >> 8) & 15u] | T.tab[a][3][(i >> 12) & 15u];
+}
+
+__device__ __forceinline__ uint32_t morton_key(const SceneDev &S, int g, const float slo[3], const float shi[3], const MortonTables &P)
 {
     int a, b, c;
     tri_vertex_ids(S, g, a, b, c);
@@ -122,19 +200,32 @@ __device__ __forceinline__ uint32_t morton_key(const SceneDev &S, int g, const f
     const float nx = ex > 0.0f ? (cx - slo[0]) / ex : 0.0f;
     const float ny = ey > 0.0f ? (cy - slo[1]) / ey : 0.0f;
     const float nz = ez > 0.0f ? (cz - slo[2]) / ez : 0.0f;
-    const uint32_t ix = (uint32_t)fminf(fmaxf(nx * 1024.0f, 0.0f), 1023.0f);
-    const uint32_t iy = (uint32_t)fminf(fmaxf(ny * 1024.0f, 0.0f), 1023.0f);
-    const uint32_t iz = (uint32_t)fminf(fmaxf(nz * 1024.0f, 0.0f), 1023.0f);
-    return (expand10(ix) << 2) | (expand10(iy) << 1) | expand10(iz);
+    const uint32_t ix = (uint32_t)fminf(fmaxf(nx * P.scale[0], 0.0f), P.scale[0] - 1.0f);
+    const uint32_t iy = (uint32_t)fminf(fmaxf(ny * P.scale[1], 0.0f), P.scale[1] - 1.0f);
+    const uint32_t iz = (uint32_t)fminf(fmaxf(nz * P.scale[2], 0.0f), P.scale[2] - 1.0f);
+    return morton_lookup(P, 0, ix) | morton_lookup(P, 1, iy) | morton_lookup(P, 2, iz);
+}
+
+// one thread: the plan of this commit (after k_transform has reduced the scene bounds)
+__global__ void k_morton_plan(SceneDev S)
+{
+    const float slo[3] = {ord2f(S.bounds[0]), ord2f(S.bounds[1]), ord2f(S.bounds[2])};
+    const float shi[3] = {ord2f(S.bounds[3]), ord2f(S.bounds[4]), ord2f(S.bounds[5])};
+    MortonPlan P;
+    morton_plan(S, slo, shi, P);
+    *S.plan = P;
 }
 
 __global__ void __launch_bounds__(256) k_morton(SceneDev S)
 {
+    __shared__ MortonTables s_plan;
+    morton_tables_fill(*S.plan, s_plan, threadIdx.x);
+    __syncthreads();
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= S.n_tris) return;
     const float slo[3] = {ord2f(S.bounds[0]), ord2f(S.bounds[1]), ord2f(S.bounds[2])};
     const float shi[3] = {ord2f(S.bounds[3]), ord2f(S.bounds[4]), ord2f(S.bounds[5])};
-    S.keys[g] = morton_key(S, g, slo, shi);
+    S.keys[g] = morton_key(S, g, slo, shi, s_plan);
     S.vals[g] = (uint32_t)g;
 }
 
@@ -428,7 +519,13 @@ k_build_small(SceneDev S, const __grid_constant__ SmallArgs args, int sensor_fra
         // (2) Morton codes
         const float slo[3] = {ord2f(s_gbounds[0]), ord2f(s_gbounds[1]), ord2f(s_gbounds[2])};
         const float shi[3] = {ord2f(s_gbounds[3]), ord2f(s_gbounds[4]), ord2f(s_gbounds[5])};
-        for (int g = gtid; g < n; g += kAll) { S.keys[g] = morton_key(S, g, slo, shi); S.vals[g] = (uint32_t)g; }
+        __shared__ MortonPlan s_plan0;
+        __shared__ MortonTables s_plan;
+        if (tid == 0) morton_plan(S, slo, shi, s_plan0);
+        __syncthreads();
+        morton_tables_fill(s_plan0, s_plan, tid);
+        __syncthreads();
+        for (int g = gtid; g < n; g += kAll) { S.keys[g] = morton_key(S, g, slo, shi, s_plan); S.vals[g] = (uint32_t)g; }
         cluster_sync_all();
         LSB_CLK();
         // (3) stable LSD radix sort; warp w of CTA r owns the contiguous chunk [(r * 32 + w) * per_warp, +per_warp)

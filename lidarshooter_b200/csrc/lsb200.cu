@@ -75,7 +75,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -85,7 +85,7 @@ struct lsb200_ctx {
     bool sensors_dirty = true;
     // scene arrays
     DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
-        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts;
+        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan;
     std::vector<GeomDesc> h_geoms;
     std::vector<SensorDev> h_sensors, h_sensors_b;
     cudaStream_t copy_stream = nullptr;
@@ -191,6 +191,9 @@ SceneDev scene_dev(lsb200_ctx *c)
     S.leaf_parent = c->d_leaf_parent.as<int32_t>(); S.flags = c->d_flags.as<uint32_t>();
     S.top_cap = c->built_top; S.leaf_max = c->built_leaf;
     S.morton_uniform = c->opt_morton_uniform;
+    S.morton_bxy = c->opt_morton_layout >> 4; S.morton_bz = c->opt_morton_layout & 15;
+    S.morton_alpha = 0.01f * (float)c->opt_morton_aspect;
+    S.plan = c->d_plan.as<MortonPlan>();
     return S;
 }
 
@@ -243,6 +246,7 @@ int lsb200_create(int cuda_device, lsb200_ctx **out)
     cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     for (int k = 0; k < 2; ++k) { cudaEventCreateWithFlags(&c->ev_traced[k], cudaEventDisableTiming); cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming); }
     if (c->d_bounds.reserve(256, c->stream) != cudaSuccess || c->d_misc.reserve(256, c->stream, false, true) != cudaSuccess ||
+        c->d_plan.reserve(256, c->stream, false, true) != cudaSuccess ||
         c->d_sensor_xf.reserve(256, c->stream) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
     c->sensors.resize(1);
     *out = c;
@@ -259,7 +263,7 @@ int lsb200_destroy(lsb200_ctx *c)
         for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
-                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts};
+                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan};
         for (auto *b : bufs) b->release();
         if (c->h_count) cudaFreeHost(c->h_count);
         for (auto &e : c->ev) if (e) cudaEventDestroy(e);
@@ -306,6 +310,12 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
         c->opt_tile_w_log2 = w; c->sensors_dirty = true; ++c->sensors_epoch; return LSB200_OK;
     }
     case LSB200_OPT_MORTON_UNIFORM: c->opt_morton_uniform = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
+    case LSB200_OPT_MORTON_ASPECT: if (value < 0 || value > 200) break; c->opt_morton_aspect = value; c->topology_dirty = true; return LSB200_OK;
+    case LSB200_OPT_MORTON_LAYOUT: {
+        const int bxy = value >> 4, bz = value & 15;
+        if (value != 0 && (value < 0 || bxy < 1 || bxy > 16 || bz > 10 || bz > bxy || 2 * bxy + bz > 32)) break;
+        c->opt_morton_layout = value; c->topology_dirty = true; return LSB200_OK;
+    }
     case LSB200_OPT_LEAF_SIZE: if (value < 1 || value > kMaxLeaf) break; c->opt_leaf = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TOP_NODES: if (value < 0 || value > 3072) break; c->opt_top = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_STAGE_TIMING: c->opt_timing = value ? 1 : 0; return LSB200_OK;
@@ -585,8 +595,9 @@ static int commit_locked(lsb200_ctx *c, int mode)
     mark();
     if (rebuild) {
         // (2) Morton codes  (3) radix sort  (4) Karras hierarchy
+        k_morton_plan<<<1, 1, 0, st>>>(S);
         k_morton<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(S);
-        count_launch(c);
+        count_launch(c, 2);
         mark();
         count_launch(c, rsort::sort_pairs(S.keys, S.vals, c->d_keys_tmp.as<uint32_t>(), c->d_vals_tmp.as<uint32_t>(), nt,
                                           c->d_sort_scratch.as<uint32_t>(), st));

@@ -27,12 +27,20 @@ def main():
     ap.add_argument("--tops", default="1024")
     ap.add_argument("--morton", default="0,1")
     ap.add_argument("--chain", default="1")
-    ap.add_argument("--tiles", default="32")
+    ap.add_argument("--tiles", default="8")
+    ap.add_argument("--layouts", default="0")
+    ap.add_argument("--aspects", default="50")
+    ap.add_argument("--scene", default="city", choices=["city", "heightfield"])
     args = ap.parse_args()
     from bench import build_workload, frame_affine
     from lidarshooter_b200 import capi
 
     meshes, poses, table = build_workload(args.small)
+    if args.scene == "heightfield":      # BASELINE configs[2]: 1M-triangle heightfield, 4 sensors above it
+        from lidarshooter_b200 import synth
+        v, t = synth.heightfield()
+        meshes = [("terrain", v, t)]
+        poses = [(synth.yaw_quat(0.3 * k), np.array([60.0 * k - 90.0, 20.0 * k - 30.0, 4.0], np.float32)) for k in range(4)]
     elev, b, e, H = table
     R = elev.size * H
     ns = len(poses)
@@ -47,10 +55,12 @@ def main():
     base_sig = None
     check_sensors = (0, ns - 1)
     ctx.set_option(capi.OPT_STAGE_TIMING, 1)
-    for mu in [int(x) for x in args.morton.split(",")]:
+    for mu, layout, aspect in [(int(x), int(y), int(z)) for x in args.morton.split(",") for y in args.layouts.split(",") for z in args.aspects.split(",")]:
         for leaf in [int(x) for x in args.leaves.split(",")]:
             for top in [int(x) for x in args.tops.split(",")]:
                 ctx.set_option(capi.OPT_MORTON_UNIFORM, mu)
+                ctx.set_option(capi.OPT_MORTON_LAYOUT, layout)
+                ctx.set_option(capi.OPT_MORTON_ASPECT, aspect)
                 ctx.set_option(capi.OPT_LEAF_SIZE, leaf)
                 ctx.set_option(capi.OPT_TOP_NODES, top)
                 assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
@@ -79,7 +89,7 @@ def main():
                     if base_sig is None:
                         base_sig = sig
                     rays = max(cnt["rays"], 1)
-                    row = {"morton_uniform": mu, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "tile_w": tile, "chain_tests_per_ray": cnt["chain_tests"] / rays,
+                    row = {"morton_uniform": mu, "morton_layout": layout, "morton_aspect": aspect, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "tile_w": tile, "chain_tests_per_ray": cnt["chain_tests"] / rays,
                            "ms_trace_min": min(ms), "ms_trace_mean": float(np.mean(ms)),
                            "mrays_per_s": ns * R / (min(ms) * 1e-3) / 1e6,
                            "nodes_per_ray": cnt["nodes"] / rays, "leaves_per_ray": cnt["leaves"] / rays,
