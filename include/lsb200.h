@@ -85,6 +85,8 @@ enum {
                                       the extra x / y bits are interleaved above the 3-way part.  0 = the default */
     LSB200_OPT_MORTON_ASPECT = 12, /* 100 * alpha: the next Morton bit goes to the axis with the largest (cell size)^alpha.
                                       0 = round robin x, y, z; 100 = longest side first (cubic cells); default 60 */
+    LSB200_OPT_FIT_RMQ = 13,       /* 1 = block-local node boxes by range queries over the block's leaf boxes (k_fit_rmq; measured
+                                      slower: 0.86 vs 0.54 ms at 10 M triangles); 0 (default) = bottom-up climb (k_fit) */
     LSB200_OPT_SMALL_BUILD = 10    /* 1 (default) = scenes of <= 16384 triangles in <= 16 geometries are committed by ONE
                                       fused single-CTA kernel (transform, Morton, sort, hierarchy, fit); 0 = always the
                                       multi-kernel pipeline */

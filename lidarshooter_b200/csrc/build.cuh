@@ -365,6 +365,139 @@ __global__ void __launch_bounds__(kFitBlock) k_fit(SceneDev S, const uint32_t *_
     fit_leaf<1>(S, (int)__ldg(sorted_ids + i), i, s_flags, blockIdx.x * kFitBlock);
 }
 
+// ---- (4b) fit without the climb: range queries over the block's leaf boxes --------------------------------
+// k_fit's climb is a chain of dependent L2 round trips (ncu: 29 % issue, 46 % DRAM).  A Karras node whose leaf range
+// lies inside one 256-leaf block (99 % of the nodes; their index lies in the block too) does not need its children
+// to "arrive": its child boxes are min / max over contiguous runs of the block's leaf boxes.  Each CTA therefore
+//   1. writes its 256 leaf records and puts the leaf boxes into shared memory,
+//   2. builds a sparse table over them (windows of 1, 2, 4 .. 64 leaves: 7 levels x 256 x 24 B = 42 KB),
+//   3. lets thread t handle internal node (block base + t): two range queries (2-4 table reads each, min / max
+//      tolerate overlapping windows) give both child boxes, written as three coalesced 16-byte stores,
+//   4. and only the roots of the maximal block-local subtrees (and leaves hanging directly off a straddling node)
+//      continue upwards through the global arrival counters, as k_fit does.
+// Same boxes bit for bit (min / max are exact and order-free).
+constexpr int kRmqLevels = 7;
+
+struct Box6 { float lox, hix, loy, hiy, loz, hiz; };
+__device__ __forceinline__ void box_merge(Box6 &a, const Box6 &b)
+{
+    a.lox = fminf(a.lox, b.lox); a.hix = fmaxf(a.hix, b.hix);
+    a.loy = fminf(a.loy, b.loy); a.hiy = fmaxf(a.hiy, b.hiy);
+    a.loz = fminf(a.loz, b.loz); a.hiz = fmaxf(a.hiz, b.hiz);
+}
+
+// Writes leaf record i (triangle g) and returns its box.
+__device__ __forceinline__ Box6 leaf_record(const SceneDev &S, int g, int i)
+{
+    int a, b, c;
+    tri_vertex_ids(S, g, a, b, c);
+    const float4 A = S.xverts[a], B = S.xverts[b], C = S.xverts[c];
+    const float e1x = __fsub_rn(A.x, B.x), e1y = __fsub_rn(A.y, B.y), e1z = __fsub_rn(A.z, B.z);
+    const float e2x = __fsub_rn(C.x, A.x), e2y = __fsub_rn(C.y, A.y), e2z = __fsub_rn(C.z, A.z);
+    const float ngx = __fsub_rn(__fmul_rn(e2y, e1z), __fmul_rn(e2z, e1y));
+    const float ngy = __fsub_rn(__fmul_rn(e2z, e1x), __fmul_rn(e2x, e1z));
+    const float ngz = __fsub_rn(__fmul_rn(e2x, e1y), __fmul_rn(e2y, e1x));
+    float4 *rec = S.tris + 3 * (size_t)i;
+    rec[0] = make_float4(A.x, A.y, A.z, e1x);
+    rec[1] = make_float4(e1y, e1z, e2x, e2y);
+    rec[2] = make_float4(e2z, ngx, ngy, ngz);
+    S.leaf_ids[i] = g;
+    Box6 bx;
+    bx.lox = fminf(A.x, fminf(B.x, C.x)); bx.hix = fmaxf(A.x, fmaxf(B.x, C.x));
+    bx.loy = fminf(A.y, fminf(B.y, C.y)); bx.hiy = fmaxf(A.y, fmaxf(B.y, C.y));
+    bx.loz = fminf(A.z, fminf(B.z, C.z)); bx.hiz = fmaxf(A.z, fmaxf(B.z, C.z));
+    return bx;
+}
+
+// Continues upwards from a child of a node that straddles 256-leaf blocks (every ancestor straddles too).
+__device__ __forceinline__ void climb_global(const SceneDev &S, int up, Box6 bx)
+{
+    while (up >= 0) {
+        const int p = up >> 2, slot = up & 1;
+        float4 *node = S.nodes + 4 * ((size_t)S.top_cap + p);
+        node[slot] = make_float4(bx.lox, bx.hix, bx.loy, bx.hiy);
+        reinterpret_cast<float2 *>(node + 2)[slot] = make_float2(bx.loz, bx.hiz);
+        __threadfence();
+        if ((atomicAdd(&S.flags[p], 1u) & 1u) == 0u) return;          // first to arrive: the sibling finishes the node
+        const float4 sxy = __ldcg(node + (slot ^ 1));
+        const float2 sz = __ldcg(reinterpret_cast<const float2 *>(node + 2) + (slot ^ 1));
+        bx.lox = fminf(bx.lox, sxy.x); bx.hix = fmaxf(bx.hix, sxy.y);
+        bx.loy = fminf(bx.loy, sxy.z); bx.hiy = fmaxf(bx.hiy, sxy.w);
+        bx.loz = fminf(bx.loz, sz.x); bx.hiz = fmaxf(bx.hiz, sz.y);
+        up = S.node_parent[p];
+    }
+}
+
+struct RmqTable { float v[6][kRmqLevels][kFitBlock]; };
+
+__device__ __forceinline__ Box6 rmq_get(const RmqTable &T, int k, int x)
+{
+    Box6 b;
+    b.lox = T.v[0][k][x]; b.hix = T.v[1][k][x]; b.loy = T.v[2][k][x]; b.hiy = T.v[3][k][x]; b.loz = T.v[4][k][x]; b.hiz = T.v[5][k][x];
+    return b;
+}
+// box of the block-relative leaf run [f, l]
+__device__ __forceinline__ Box6 rmq_query(const RmqTable &T, int f, int l)
+{
+    const int len = l - f + 1;
+    const int k = min(kRmqLevels - 1, 31 - __clz(len));
+    const int w = 1 << k;
+    Box6 b = rmq_get(T, k, f);
+    for (int x = f + w; x + w <= l + 1; x += w) box_merge(b, rmq_get(T, k, x));
+    box_merge(b, rmq_get(T, k, l - w + 1));
+    return b;
+}
+
+__global__ void __launch_bounds__(kFitBlock) k_fit_rmq(SceneDev S, const uint32_t *__restrict__ sorted_ids)
+{
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    RmqTable &T = *reinterpret_cast<RmqTable *>(s_raw);
+    const int t = threadIdx.x;
+    const int base = blockIdx.x * kFitBlock;
+    const int i = base + t;
+    const int n = S.n_tris;
+    Box6 leaf;
+    leaf.lox = leaf.loy = leaf.loz = INFINITY; leaf.hix = leaf.hiy = leaf.hiz = -INFINITY;
+    if (i < n) leaf = leaf_record(S, (int)__ldg(sorted_ids + i), i);
+    T.v[0][0][t] = leaf.lox; T.v[1][0][t] = leaf.hix; T.v[2][0][t] = leaf.loy; T.v[3][0][t] = leaf.hiy; T.v[4][0][t] = leaf.loz; T.v[5][0][t] = leaf.hiz;
+    __syncthreads();
+#pragma unroll
+    for (int k = 1; k < kRmqLevels; ++k) {
+        const int h = 1 << (k - 1);
+        if (t + 2 * h <= kFitBlock) {
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+                const float a = T.v[c][k - 1][t], b = T.v[c][k - 1][t + h];
+                T.v[c][k][t] = (c & 1) ? fmaxf(a, b) : fminf(a, b);
+            }
+        }
+        __syncthreads();
+    }
+    // leaves hanging directly off a straddling node
+    if (i < n) {
+        const int up = S.leaf_parent[i];
+        if (!(up & 2)) climb_global(S, up, leaf);
+    }
+    // internal node i (exists for i < n - 1): block-local when its leaf range lies in this block
+    if (i < n - 1) {
+        float4 *node = S.nodes + 4 * ((size_t)S.top_cap + i);
+        const float4 q3 = node[3];
+        const int c0 = __float_as_int(q3.x), first = __float_as_int(q3.z), last = __float_as_int(q3.w);
+        if (first >= base && last < base + kFitBlock) {
+            int split;
+            if (c0 >= 0) split = c0 - S.top_cap;
+            else { const int enc = ~c0; split = (enc & ((1 << kLeafShift) - 1)) + (enc >> kLeafShift); }
+            const Box6 b0 = rmq_query(T, first - base, split - base);
+            Box6 b1 = rmq_query(T, split + 1 - base, last - base);
+            node[0] = make_float4(b0.lox, b0.hix, b0.loy, b0.hiy);
+            node[1] = make_float4(b1.lox, b1.hix, b1.loy, b1.hiy);
+            node[2] = make_float4(b0.loz, b0.hiz, b1.loz, b1.hiz);
+            const int up = S.node_parent[i];
+            if (up >= 0 && !(up & 2)) { box_merge(b1, b0); climb_global(S, up, b1); }
+        }
+    }
+}
+
 // ---- origin chains (see trace.cuh: trace_ray) --------------------------------------------------------------
 // Walks from the root along the children whose box contains the sensor origin and lists the sibling of every step
 // (box + reference), then the node or leaf the walk ends in.  Entry: e0 = (lo.x, hi.x, lo.y, hi.y), e1 = (lo.z,

@@ -75,7 +75,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -302,6 +302,7 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 6) break; c->opt_traversal = value; return LSB200_OK;
     case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_FIT_RMQ: c->opt_fit_rmq = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TILE_WIDTH: {
         int w = 0;
@@ -608,7 +609,13 @@ static int commit_locked(lsb200_ctx *c, int mode)
         mark();
     }
     // (5) leaf records + bottom-up boxes
-    k_fit<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, 0, st>>>(S, S.vals);
+    if (c->opt_fit_rmq) {
+        static bool attr_set = false;
+        if (!attr_set) { LSB_CU(c, cudaFuncSetAttribute(k_fit_rmq, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RmqTable))); attr_set = true; }
+        k_fit_rmq<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, sizeof(RmqTable), st>>>(S, S.vals);
+    } else {
+        k_fit<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, 0, st>>>(S, S.vals);
+    }
     count_launch(c);
     mark();
     // (6) top-level block for the TMA-staged traversal

@@ -564,3 +564,33 @@ def test_sensor_limits_detection_radius_and_azimuth_window(meshes, mode):
     assert ctx.commit_scene() == 0
     assert ctx.trace_scene(0, capi.TRACE_ORDERED)[1].shape[0] == 1781
     ctx.close()
+
+
+@pytest.mark.parametrize("n_tris", [1, 2, 255, 256, 257, 20000, 300001])
+def test_fit_by_range_queries_equals_climb(n_tris):
+    """k_fit_rmq (block-local node boxes from a sparse table over the block's leaf boxes) writes the same node array as
+    the bottom-up climb of k_fit, for rebuild and refit (multi-kernel pipeline forced)."""
+    rng = np.random.default_rng(n_tris)
+    c = rng.uniform(-50, 50, (n_tris, 1, 3)).astype(np.float32)
+    c[: n_tris // 4] = c[0]                                   # long runs of equal Morton codes
+    v = (c + rng.normal(0, 0.4, (n_tris, 3, 3)).astype(np.float32)).reshape(-1, 3)
+    tr = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
+    A2 = lso.affine_from_components([1.5, -0.5, 0.25], [0.2, 0.1, -0.3])
+    out = []
+    for rmq in (1, 0):
+        ctx = capi.Context(0)
+        ctx.set_option(capi.OPT_SMALL_BUILD, 0)
+        ctx.set_option(capi.OPT_FIT_RMQ, rmq)
+        ctx.set_option(capi.OPT_LEAF_SIZE, 4)
+        ctx.set_sensor(np.linspace(40, -40, 16).astype(np.float32), 0.0, 360.0, 64, (1, 0, 0, 0), (0, 0, 0))
+        add_mesh(ctx, "soup", v, tr)
+        assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
+        nodes, ids, root = ctx.debug_copy_bvh()
+        rc, t, tri = ctx.trace_raw()
+        assert ctx.update_transform("soup", A2) == 0 and ctx.commit_scene(capi.COMMIT_REFIT) == 0
+        nodes2, _, _ = ctx.debug_copy_bvh()
+        rc, t2, tri2 = ctx.trace_raw()
+        out.append((nodes.copy(), ids.copy(), t, tri, nodes2.copy(), t2, tri2))
+        ctx.close()
+    for name, x, y in zip(("nodes", "leaf ids", "t", "tri", "nodes after refit", "t after refit", "tri after refit"), *out):
+        assert np.array_equal(np.atleast_1d(x).view(np.uint8), np.atleast_1d(y).view(np.uint8)), name
