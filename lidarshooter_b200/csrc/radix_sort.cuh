@@ -2,7 +2,7 @@
 //
 // Onesweep organisation (Adinets & Merrill 2022): ONE histogram kernel reads the keys once and produces the
 // digit histograms of all four 8-bit passes; each pass is then ONE kernel that reads every pair once, ranks
-// it inside a 4096-pair tile (warp-level MATCH.ANY multi-split, stable), obtains the tile's global digit
+// it inside an 8192-pair tile (warp-level MATCH.ANY multi-split, stable), obtains the tile's global digit
 // offsets by a decoupled look-back over the preceding tiles' published counts, reorders the tile in shared
 // memory and writes it out in digit runs.  Algorithmic traffic per pair: 4 (histogram) + 4 x (8 read + 8
 // write) = 68 B.  Tile ids are handed out by an atomic ticket so that every tile a block waits on has already
@@ -19,10 +19,18 @@ namespace rsort {
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;            // 256
 constexpr int kPasses = 4;
-constexpr int kThreads = 256;
+// tile shape: measured in profiles/design_choices_r01.md (512 x 16, two CTAs per SM at 64 registers)
+#ifndef LSB_SORT_THREADS
+#define LSB_SORT_THREADS 512
+#endif
+#ifndef LSB_SORT_ITEMS
+#define LSB_SORT_ITEMS 16
+#define LSB_SORT_MINB 2
+#endif
+constexpr int kThreads = LSB_SORT_THREADS;          // >= kRadix (thread d < 256 owns digit d of the tile)
 constexpr int kWarps = kThreads / 32;
-constexpr int kItems = 16;                          // pairs per thread
-constexpr int kTile = kThreads * kItems;            // 4096 pairs per tile
+constexpr int kItems = LSB_SORT_ITEMS;              // pairs per thread
+constexpr int kTile = kThreads * kItems;            // 8192 pairs per tile
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagIncl = 2u << 30, kFlagMask = 3u << 30, kValMask = ~kFlagMask;
 
 inline int64_t num_tiles(int64_t n) { return (n + kTile - 1) / kTile; }
@@ -72,15 +80,32 @@ __global__ void __launch_bounds__(kPasses * 32) k_scan_histograms(uint32_t *__re
     for (int j = 0; j < 8; ++j) { ghist[p * kRadix + lane * 8 + j] = run; run += v[j]; }
 }
 
+// Lanes of the warp whose 8-bit digit equals this lane's: the MATCH.ANY instruction (eight ballots give the same mask
+// and were measured slower: 0.351 vs 0.327 ms per 10 M-pair sort; LSB_SORT_BALLOT selects them for the A/B).
+__device__ __forceinline__ unsigned digit_peers(uint32_t d)
+{
+#ifndef LSB_SORT_BALLOT
+    return __match_any_sync(0xffffffffu, d);
+#else
+    unsigned peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < kRadixBits; ++b) {
+        const unsigned vote = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+        peers &= ((d >> b) & 1u) ? vote : ~vote;
+    }
+    return peers;
+#endif
+}
+
 // ---- kernel 3: one onesweep pass -------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) k_onesweep(const uint32_t *__restrict__ keys_in,
+__global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint32_t *__restrict__ keys_in,
                                                        const uint32_t *__restrict__ vals_in,
                                                        uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
                                                        int64_t n, int shift, const uint32_t *__restrict__ digit_base,
                                                        uint32_t *__restrict__ ticket, volatile uint32_t *status)
 {
-    __shared__ uint32_t s_keys[kTile];
-    __shared__ uint32_t s_vals[kTile];
+    extern __shared__ __align__(16) uint32_t s_dyn[];          // [2][kTile] reordered keys and values
+    uint32_t *s_keys = s_dyn, *s_vals = s_dyn + kTile;
     __shared__ uint32_t s_whist[kWarps][kRadix];   // per-warp digit counts -> per-warp digit bases within the tile
     __shared__ uint32_t s_local[kRadix];           // tile-local exclusive digit offsets
     __shared__ uint32_t s_global[kRadix];          // global position of the tile's first pair of each digit
@@ -110,7 +135,7 @@ __global__ void __launch_bounds__(kThreads) k_onesweep(const uint32_t *__restric
 #pragma unroll
     for (int i = 0; i < kItems; ++i) {
         const uint32_t d = (key[i] >> shift) & (kRadix - 1);
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const unsigned peers = digit_peers(d);
         const uint32_t prev = s_whist[warp][d];
         __syncwarp();
         if ((peers & lt) == 0) s_whist[warp][d] = prev + __popc(peers);
@@ -119,31 +144,33 @@ __global__ void __launch_bounds__(kThreads) k_onesweep(const uint32_t *__restric
     }
     __syncthreads();
 
-    // thread d owns digit d: scan over warps, publish, look back
+    // thread d < 256 owns digit d: scan over warps, publish, look back
     {
         const int d = tid;
         uint32_t run = 0;
+        if (d < kRadix) {
 #pragma unroll
-        for (int w = 0; w < kWarps; ++w) { const uint32_t c = s_whist[w][d]; s_whist[w][d] = run; run += c; }
-        volatile uint32_t *my = status + (size_t)tile * kRadix + d;
-        uint32_t excl = 0;
-        if (tile == 0) {
-            *my = run | kFlagIncl;
-        } else {
-            *my = run | kFlagAgg;
-            int64_t t = (int64_t)tile - 1;
-            while (true) {
-                const uint32_t s = status[(size_t)t * kRadix + d];
-                const uint32_t f = s & kFlagMask;
-                if (f == 0) continue;                       // predecessor has not published yet
-                excl += s & kValMask;
-                if (f == kFlagIncl) break;
-                --t;
+            for (int w = 0; w < kWarps; ++w) { const uint32_t c = s_whist[w][d]; s_whist[w][d] = run; run += c; }
+            volatile uint32_t *my = status + (size_t)tile * kRadix + d;
+            uint32_t excl = 0;
+            if (tile == 0) {
+                *my = run | kFlagIncl;
+            } else {
+                *my = run | kFlagAgg;
+                int64_t t = (int64_t)tile - 1;
+                while (true) {
+                    const uint32_t s = status[(size_t)t * kRadix + d];
+                    const uint32_t f = s & kFlagMask;
+                    if (f == 0) continue;                       // predecessor has not published yet
+                    excl += s & kValMask;
+                    if (f == kFlagIncl) break;
+                    --t;
+                }
+                *my = (excl + run) | kFlagIncl;
             }
-            *my = (excl + run) | kFlagIncl;
+            s_global[d] = digit_base[d] + excl;
         }
-        s_global[d] = digit_base[d] + excl;
-        // tile-local exclusive scan over digits (block scan of `run`)
+        // tile-local exclusive scan over digits (block scan of `run`; threads beyond the radix carry 0)
         uint32_t incl = run;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t t2 = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t2; }
@@ -152,8 +179,8 @@ __global__ void __launch_bounds__(kThreads) k_onesweep(const uint32_t *__restric
         __syncthreads();
         uint32_t woff = 0;
 #pragma unroll
-        for (int w = 0; w < kWarps; ++w) if (w < warp) woff += s_wsum[w];
-        s_local[d] = woff + incl - run;
+        for (int w = 0; w < kRadix / 32; ++w) if (w < warp) woff += s_wsum[w];
+        if (d < kRadix) s_local[d] = woff + incl - run;
     }
     __syncthreads();
 
@@ -192,9 +219,11 @@ inline int sort_pairs(uint32_t *keys, uint32_t *vals, uint32_t *keys_tmp, uint32
     const int hist_blocks = (int)(hb < kSmCount * 8 ? hb : kSmCount * 8);
     k_histogram<<<hist_blocks, kThreads, 0, stream>>>(keys, n, ghist);
     k_scan_histograms<<<1, kPasses * 32, 0, stream>>>(ghist);
+    static bool attr_set = false;
+    if (!attr_set) { cudaFuncSetAttribute(k_onesweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * kTile * sizeof(uint32_t))); attr_set = true; }
     uint32_t *ki = keys, *vi = vals, *ko = keys_tmp, *vo = vals_tmp;
     for (int p = 0; p < kPasses; ++p) {
-        k_onesweep<<<(unsigned)tiles, kThreads, 0, stream>>>(ki, vi, ko, vo, n, p * kRadixBits, ghist + p * kRadix,
+        k_onesweep<<<(unsigned)tiles, kThreads, 2 * kTile * sizeof(uint32_t), stream>>>(ki, vi, ko, vo, n, p * kRadixBits, ghist + p * kRadix,
                                                              tickets + p, status + (size_t)p * tiles * kRadix);
         uint32_t *t = ki; ki = ko; ko = t;
         t = vi; vi = vo; vo = t;
