@@ -87,6 +87,12 @@ enum {
                                       0 = round robin x, y, z; 100 = longest side first (cubic cells); default 60 */
     LSB200_OPT_FIT_RMQ = 13,       /* 1 = block-local node boxes by range queries over the block's leaf boxes (k_fit_rmq; measured
                                       slower: 0.86 vs 0.54 ms at 10 M triangles); 0 (default) = bottom-up climb (k_fit) */
+    LSB200_OPT_TILE_ENTRIES = 14,  /* entries of the per-tile entry lists (0 = off, 2..16; default 16): one thread per 32-ray tile walks
+                                      the part of the BVH descent that the tile's rays share, once, and lists the subtrees / leaves
+                                      the tile's pyramid can reach; the rays start from that list (variant 6, >= 4096 tiles) */
+    LSB200_OPT_TILE_VISITS = 15,   /* node visits a tile may spend on its list (0 = default: 4 x entries) */
+    LSB200_OPT_TILE_MIN_UNITS = 16, /* tile lists are built for launches of at least this many 32-ray tiles (default 4096: below
+                                      that, e.g. an XT-32 with 150 tiles, the extra launch costs more than it saves) */
     LSB200_OPT_SMALL_BUILD = 10    /* 1 (default) = scenes of <= 16384 triangles in <= 16 geometries are committed by ONE
                                       fused single-CTA kernel (transform, Morton, sort, hierarchy, fit); 0 = always the
                                       multi-kernel pipeline */

@@ -75,7 +75,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 16, opt_tile_visits = 0, opt_tile_min_units = 4096;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -85,7 +85,7 @@ struct lsb200_ctx {
     bool sensors_dirty = true;
     // scene arrays
     DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
-        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan;
+        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts;
     std::vector<GeomDesc> h_geoms;
     std::vector<SensorDev> h_sensors, h_sensors_b;
     cudaStream_t copy_stream = nullptr;
@@ -94,6 +94,9 @@ struct lsb200_ctx {
     int64_t sensors_epoch = 0, units_epoch = -1;
     int units_first = -1, units_count = -1, units_world = -1;
     int64_t commit_epoch = 0, chain_commit_epoch = -1, chain_sensors_epoch = -1;
+    // tile entry lists: valid for one BVH, one set of sensor poses, one set of octant queues and one list size
+    int64_t tile_commit_epoch = -1, tile_sensors_epoch = -1;
+    int tile_first = -1, tile_count = -1, tile_cap = -1, tile_visits = -1;
     float h_xf[12];
     uint32_t *h_count = nullptr;                                 // pinned
     int n_verts = 0, n_tris = 0;
@@ -263,7 +266,7 @@ int lsb200_destroy(lsb200_ctx *c)
         for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
-                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan};
+                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts};
         for (auto *b : bufs) b->release();
         if (c->h_count) cudaFreeHost(c->h_count);
         for (auto &e : c->ev) if (e) cudaEventDestroy(e);
@@ -303,6 +306,9 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_FIT_RMQ: c->opt_fit_rmq = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_TILE_ENTRIES: if (value < 0 || value > kMaxTileEntries || value == 1) break; c->opt_tile_entries = value; c->tile_commit_epoch = -1; return LSB200_OK;
+    case LSB200_OPT_TILE_MIN_UNITS: if (value < 0) break; c->opt_tile_min_units = value; return LSB200_OK;
+    case LSB200_OPT_TILE_VISITS: if (value < 0 || value > 4096) break; c->opt_tile_visits = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TILE_WIDTH: {
         int w = 0;
@@ -391,6 +397,7 @@ int lsb200_set_sensor_limits(lsb200_ctx *c, int idx, float max_range, float az_m
         LSB_CU(c, cudaStreamSynchronize(c->stream));
     }
     c->sensors_dirty = true;
+    c->tile_commit_epoch = -1;          // the tile lists bake the detection radius in
     return LSB200_OK;
 }
 
@@ -869,6 +876,30 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         LSB_CU(c, c->d_counters.reserve(kCntCount * sizeof(unsigned long long), st));
         LSB_CU(c, cudaMemsetAsync(c->d_counters.p, 0, kCntCount * sizeof(unsigned long long), st));
         P.counters = c->d_counters.as<unsigned long long>();
+    }
+    // per-tile entry lists (k_tile_entries): worth their launch from a few thousand 32-ray tiles on
+    if (mode == 6 && c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units) {
+        const int cap = c->opt_tile_entries;
+        const int max_visits = c->opt_tile_visits > 0 ? c->opt_tile_visits : 4 * cap;
+        P.tile_cap = cap;
+        const bool stale = c->tile_commit_epoch != c->commit_epoch || c->tile_sensors_epoch != c->sensors_epoch || c->tile_first != first ||
+                           c->tile_count != count || c->tile_cap != cap || c->tile_visits != max_visits;
+        if (stale || c->opt_stats) {
+            LSB_CU(c, c->d_tile_lists.reserve((size_t)n_units * cap * 2 * sizeof(float4), st));
+            LSB_CU(c, c->d_tile_counts.reserve((size_t)n_units, st));
+        }
+        P.tile_lists = c->d_tile_lists.as<float4>();
+        P.tile_counts = c->d_tile_counts.as<uint8_t>();
+        if (stale || c->opt_stats) {
+            const unsigned blocks = (unsigned)((n_units + 127) / 128);
+            if (c->opt_stats) k_tile_entries<true><<<blocks, 128, 0, st>>>(P, max_visits);
+            else k_tile_entries<false><<<blocks, 128, 0, st>>>(P, max_visits);
+            count_launch(c);
+            c->tile_commit_epoch = c->commit_epoch; c->tile_sensors_epoch = c->sensors_epoch; c->tile_first = first; c->tile_count = count;
+            c->tile_cap = cap; c->tile_visits = max_visits;
+        }
+    }
+    if (c->opt_stats) {
         rc = launch_trace_mode<true>(c, P, n_units, mode);
     } else {
         rc = launch_trace_mode<false>(c, P, n_units, mode);

@@ -37,10 +37,16 @@ struct TraceParams {
     const uint32_t *oct_hist;     // MODE 0: [9] units per class (0..7 octants, 8 mixed)
     const float4 *chains;         // [n_sensors][9][kMaxChain][2] origin-chain lists per octant class (k_origin_chain)
     const int *chain_counts;      // [n_sensors][9] entries per list; nullptr = lists off (start at the root)
+    float4 *tile_lists;           // [queue slot][tile_cap][2] per-TILE entry lists (k_tile_entries); nullptr = off
+    uint8_t *tile_counts;         // [queue slot] entries of the tile's list; kTileFallback = use the sensor's origin chain
+    int tile_cap;                 // entries per tile list (<= kMaxTileEntries)
 };
+constexpr int kMaxTileEntries = 16;
+constexpr int kTileFallback = 0xFF;
 
 // Instrumented (STATS) launches accumulate these per-launch totals (lsb200_get_trace_counters).
-enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUniform, kCntUnitsMixed, kCntMaxStack, kCntHits, kCntCulled, kCntChainTests, kCntCount };
+enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUniform, kCntUnitsMixed, kCntMaxStack, kCntHits, kCntCulled, kCntChainTests,
+                    kCntTileVisits, kCntTileEntries, kCntTileFallbacks, kCntTileEmpty, kCntCount };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -111,9 +117,9 @@ __device__ __forceinline__ void test_leaf(const TraceParams &P, int ref, const R
     for (int k = 0; k < count; ++k) {
         const float4 *rec = P.tris + 3 * (size_t)(first + k);
         const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2);
+        const int g = __ldg(P.leaf_ids + first + k);        // with the record: no dependent round trip after a hit
         float t;
         if (intersect_tri(q0, q1, q2, r, t) && t <= best) {
-            const int g = __ldg(P.leaf_ids + first + k);
             if (t < best || g < bi) { best = t; bi = g; }   // lexicographic minimum of (t, global triangle id)
         }
     }
@@ -237,9 +243,9 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
 // "while-while" form of trace_ray (Aila & Laine 2009): an inner loop that only visits nodes, left by a lane when
 // it reaches a leaf (or runs out of work); the warp reconverges behind it, so the (long) triangle tests of the
 // lanes run together instead of being interleaved with other lanes' node visits.  Nodes from global memory.
-template <int OCT, bool STATS>
+template <int OCT, bool STATS, bool SMEM>
 __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, const Ray &r,
-                                             const float4 *__restrict__ chain, int n_chain,
+                                             const float4 *__restrict__ chain, int n_chain, bool reversed,
                                              float &best_out, int &bi_out, RayStats &rs)
 {
     const float tiny = 1e-30f;
@@ -255,8 +261,12 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
     int sp = 0;
     int cur = P.top_cap;
     if (n_chain > 0) {
-        for (int k = 0; k < n_chain; ++k) {
-            const float4 e0 = __ldg(chain + 2 * k), e1 = __ldg(chain + 2 * k + 1);
+        // sensor chains are listed far -> near, tile lists (k_tile_entries) near -> far: the nearest entry ends on top
+        const float4 *e = reversed ? chain + 2 * (n_chain - 1) : chain;
+        const int step = reversed ? -2 : 2;
+        for (int k = 0; k < n_chain; ++k, e += step) {
+            // SMEM: the warp staged the list in shared memory with one coalesced load (process_unit)
+            const float4 e0 = SMEM ? e[0] : __ldg(e), e1 = SMEM ? e[1] : __ldg(e + 1);
             float n, f;
             slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
                          fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
@@ -362,10 +372,9 @@ __device__ __forceinline__ void hit_point(const SensorDev &S, uint32_t flags, fl
 // Ray `ray` of sensor S: d_s = (sin t cos p, sin t sin p, cos t) (SRC/LidarDevice.cpp:319-321), ray id = channel * H
 // + azimuth; world-frame mode moves the ray instead of the scene (o = T, d = R d_s).  Used by the traversal AND by
 // the octant classification, so both see bit-identical direction signs.
-__device__ __forceinline__ void make_ray(const SensorDev &S, int world_frame, int v, int h, Ray &r, float &dsx, float &dsy,
-                                         float &dsz, float &omax)
+__device__ __forceinline__ void ray_from_tables(const SensorDev &S, int world_frame, float st, float ct, float sp_, float cp, Ray &r,
+                                                float &dsx, float &dsy, float &dsz, float &omax)
 {
-    const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v), sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
     dsx = __fmul_rn(st, cp); dsy = __fmul_rn(st, sp_); dsz = ct;
     if (world_frame) {
         r.ox = S.T[0]; r.oy = S.T[1]; r.oz = S.T[2];
@@ -377,6 +386,12 @@ __device__ __forceinline__ void make_ray(const SensorDev &S, int world_frame, in
         r.ox = r.oy = r.oz = 0.0f; r.dx = dsx; r.dy = dsy; r.dz = dsz;
         omax = 0.0f;
     }
+}
+__device__ __forceinline__ void make_ray(const SensorDev &S, int world_frame, int v, int h, Ray &r, float &dsx, float &dsy,
+                                         float &dsz, float &omax)
+{
+    const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v), sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
+    ray_from_tables(S, world_frame, st, ct, sp_, cp, r, dsx, dsy, dsz, omax);
 }
 
 __device__ __forceinline__ int ray_octant(const Ray &r)
@@ -405,7 +420,7 @@ __device__ __forceinline__ bool unit_lane_ray(const SensorDev &S, int4 ud, int t
 // MODE: see k_trace.  OCT: slab form for every ray of the unit (0..7 only when classified uniform).
 template <int MODE, int OCT, bool STATS>
 __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 *s_top, int n_top, float smax, int4 ud,
-                                             unsigned lane)
+                                             unsigned lane, int tile_n = -1, const float4 *s_list = nullptr)
 {
     constexpr bool TOP = (MODE == 4);
     const int si = ud.x;
@@ -416,6 +431,10 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
     float best = INFINITY; int bi = -1;
     float dsx = 0.f, dsy = 0.f, dsz = 1.f;
     RayStats rs{0u, 0u, 0u, 0u, 0u, 0u};
+    // MODE 6: a unit whose tile list (k_tile_entries, near -> far) was prefetched into shared memory by run_phase
+    // starts from it (tile_n entries, 0 = the tile's pyramid reaches nothing); tile_n < 0: no tile list -- the rays
+    // read their sensor's origin chain (far -> near) from global memory.
+    const bool w_tile = MODE == 6 && tile_n >= 0;
     const bool fired = valid && (S.az_mask == nullptr || __ldg(S.az_mask + h) != 0);
     if (valid && !fired) { S.t_out[ray] = INFINITY; S.tri_out[ray] = -1; }      // outside the azimuth window: no return
     if (fired) {
@@ -424,10 +443,12 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
         make_ray(S, P.world_frame, v, h, r, dsx, dsy, dsz, omax);
         const float eps = 8e-6f * (smax + omax) + 1e-30f;
         if (MODE == 3) brute_ray(P, r, best, bi);
+        else if (w_tile && tile_n == 0) { /* nothing to hit */ }
         else {
             const int list = si * 9 + OCT;
             const int n_chain = P.chain_counts ? __ldg(P.chain_counts + list) : 0;
-            if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
+            if (w_tile) trace_ray_ww<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
+            else if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
             else
             trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
         }
@@ -466,23 +487,70 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
 }
 
 // MODE 0 / 6: drains the queue of octant class OCT (units whose 32 rays all have the direction signs OCT; 8 = mixed).
-// An empty class costs no atomic.  (Requesting the next ticket before processing the current unit was measured: no
-// gain -- other warps already hide the round trip -- and it costs a live register across the traversal.)
+// An empty class costs no atomic.
+// The loop is software-pipelined, because with the tile lists the kernel is bound by the chain of dependent memory
+// round trips at the head of every unit (ticket -> descriptor / list size -> list -> ...), not by the SM's load path:
+// the ticket is requested two units ahead, descriptor and list size one unit ahead, and the unit's tile list is
+// copied into the warp's other shared-memory buffer with cp.async (one 16-byte piece per lane, no registers) while
+// the current unit is traced.
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 template <int MODE, int OCT, bool STATS>
-__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane)
+__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list)
 {
     int begin = 0;
 #pragma unroll
     for (int o = 0; o < OCT; ++o) begin += (int)__ldg(P.oct_hist + o);
     const int count = (int)__ldg(P.oct_hist + OCT);
     if (count == 0) return;
-    while (true) {
-        int k = 0;
-        if (lane == 0) k = (int)atomicAdd(&P.work[2 + OCT], 1u);
-        k = __shfl_sync(0xffffffffu, k, 0);
-        if (k >= count) break;
-        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, __ldg(P.unit_list + begin + k), lane);
+    if (MODE != 6) {                                               // variant 0 keeps the plain loop it was measured with
+        while (true) {
+            int k = 0;
+            if (lane == 0) k = (int)atomicAdd(&P.work[2 + OCT], 1u);
+            k = __shfl_sync(0xffffffffu, k, 0);
+            if (k >= count) break;
+            process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, __ldg(P.unit_list + begin + k), lane);
+        }
+        return;
     }
+    const bool lists = MODE == 6 && OCT < 8 && P.tile_counts != nullptr;
+    constexpr int kBuf = 2 * kMaxTileEntries;                     // float4 per buffer
+    auto ticket = [&]() -> int { return lane == 0 ? (int)atomicAdd(&P.work[2 + OCT], 1u) : 0; };
+    auto fetch = [&](int k, int4 &ud, int &tn, float4 *buf) {     // descriptor, list size and list of queue entry k
+        ud = __ldg(P.unit_list + begin + k);
+        tn = -1;
+        if (lists) {
+            const int tc = (int)__ldg(P.tile_counts + begin + k);
+            tn = tc == kTileFallback ? -1 : tc;
+            if ((int)lane < 2 * P.tile_cap) cp_async16(buf + lane, P.tile_lists + (size_t)(begin + k) * (2 * P.tile_cap) + lane);
+        }
+        cp_async_commit();
+    };
+    int k_cur = __shfl_sync(0xffffffffu, ticket(), 0);
+    if (k_cur >= count) return;
+    int raw_next = ticket();                                       // consumed at the top of the loop
+    int4 ud; int tn; int b = 0;
+    fetch(k_cur, ud, tn, s_list);
+    while (true) {
+        const int k_next = __shfl_sync(0xffffffffu, raw_next, 0);
+        const bool more = k_next < count;
+        int4 ud_n = make_int4(0, 0, 0, 0); int tn_n = -1;
+        if (more) { fetch(k_next, ud_n, tn_n, s_list + (b ^ 1) * kBuf); raw_next = ticket(); }
+        else cp_async_commit();
+        cp_async_wait<1>();                                        // everything but the newest group: this unit's list is in
+        __syncwarp();
+        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, ud, lane, tn, s_list + b * kBuf);
+        if (!more) break;
+        __syncwarp();                                              // all lanes are done with buffer b before it is refilled
+        ud = ud_n; tn = tn_n; b ^= 1;
+    }
+    cp_async_wait<0>();
 }
 
 // MODE 0: persistent CTAs, nodes through L1/L2, units pre-sorted by ray octant (k_classify_units / k_scatter_units)
@@ -523,12 +591,14 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
 
     const unsigned lane = lane_id();
+    __shared__ float4 s_lists[(MODE == 6) ? kTraceThreads / 32 : 1][(MODE == 6) ? 4 * kMaxTileEntries : 1];      // 2 buffers per warp
+    float4 *s_list = s_lists[(MODE == 6) ? (threadIdx.x >> 5) : 0];
     if (MODE == 0 || MODE == 6) {
-        run_phase<MODE, 8, STATS>(P, smax, lane);
-        run_phase<MODE, 0, STATS>(P, smax, lane); run_phase<MODE, 1, STATS>(P, smax, lane);
-        run_phase<MODE, 2, STATS>(P, smax, lane); run_phase<MODE, 3, STATS>(P, smax, lane);
-        run_phase<MODE, 4, STATS>(P, smax, lane); run_phase<MODE, 5, STATS>(P, smax, lane);
-        run_phase<MODE, 6, STATS>(P, smax, lane); run_phase<MODE, 7, STATS>(P, smax, lane);
+        run_phase<MODE, 8, STATS>(P, smax, lane, s_list);
+        run_phase<MODE, 0, STATS>(P, smax, lane, s_list); run_phase<MODE, 1, STATS>(P, smax, lane, s_list);
+        run_phase<MODE, 2, STATS>(P, smax, lane, s_list); run_phase<MODE, 3, STATS>(P, smax, lane, s_list);
+        run_phase<MODE, 4, STATS>(P, smax, lane, s_list); run_phase<MODE, 5, STATS>(P, smax, lane, s_list);
+        run_phase<MODE, 6, STATS>(P, smax, lane, s_list); run_phase<MODE, 7, STATS>(P, smax, lane, s_list);
     } else if (MODE == 2) {
         const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
         if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
@@ -629,6 +699,180 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
     float smax = 0.0f;
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(bounds[k])));
     origin_chain_walk(nodes, top_cap, ox, oy, oz, smax, cls, chains + (size_t)id * (2 * kMaxChain), counts + id);
+}
+
+// ---- tile entry lists --------------------------------------------------------------------------------------
+// Every ray of a LiDAR starts at the same point, so the 32 rays of a work unit (a tile of 8 azimuth steps x 4
+// channels, about 0.8 x 1.2 degrees) form a thin pyramid with its apex at the sensor: they walk almost the same
+// root-to-leaf path, 32 times.  k_tile_entries walks that shared part ONCE per tile (one THREAD per tile): a
+// near-first depth-first descent from the sensor's origin chain in which a box is entered when the tile's
+// direction interval can reach it, until `tile_cap` subtrees / leaves are listed.  The rays of the tile then test
+// the <= tile_cap listed boxes (32 bytes each, no divergence) instead of descending ~17 levels each, and seed their
+// stacks with the ones they enter (trace_ray_ww) -- near part of the pyramid resolved down to leaves, far part
+// left coarse (it is dropped unloaded once a closer hit is known).
+//
+// Tile test = interval form of the ray's own slab test.  For a sign-uniform tile |1/d| of axis k lies in
+// [imin_k, imax_k]; entry distances are bounded from below with imin, exit distances from above with imax:
+//     n_tile = max_k (near plane_k - o_k -+ eps) * imin_k  <=  n_ray        f_tile = min_k (far plane_k ...) * imax_k  >=  f_ray
+// so n_ray <= f_ray implies n_tile <= f_tile: a tile never drops a box one of its rays would enter (eps is 1.5 x the
+// rays' padding and the interval is widened by 1e-6, far above the rounding noise of either form).  The union of
+// the listed subtrees therefore covers everything any ray of the tile can hit, and closest hit = min (t, triangle
+// id) does not depend on how the tree was cut: per-ray results are unchanged (tests: every variant bit-identical).
+// Sign-mixed tiles (class 8, ~4 % of a 128 x 3601 table) and tiles whose interval touches 0 keep the sensor chain.
+template <bool STATS>
+__global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_visits)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    int begin8 = 0;                                    // first slot of class 8 = number of sign-uniform units
+#pragma unroll
+    for (int o = 0; o < 8; ++o) begin8 += (int)__ldg(P.oct_hist + o);
+    const int total = begin8 + (int)__ldg(P.oct_hist + 8);
+    if (slot >= total) return;
+    if (slot >= begin8) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
+    int cls = 0, acc = 0;
+#pragma unroll
+    for (int o = 0; o < 8; ++o) { acc += (int)__ldg(P.oct_hist + o); if (slot >= acc) cls = o + 1; }
+
+    const int4 ud = __ldg(P.unit_list + slot);
+    const SensorDev &S = P.sensors[ud.x];
+    // direction interval of the tile's rays (exactly the rays the traversal generates)
+    float dlo[3] = {INFINITY, INFINITY, INFINITY}, dhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    float ox = 0.0f, oy = 0.0f, oz = 0.0f, omax = 0.0f;
+    {
+        // the tile's rays, generated with the traversal's own arithmetic; the tables are read once per row / column
+        const int tw = 1 << P.tile_w_log2, th = 32 >> P.tile_w_log2;
+        float stv[4], ctv[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int v = min(ud.y + a, S.V - 1);
+            stv[a] = __ldg(S.sin_t + v); ctv[a] = __ldg(S.cos_t + v);
+        }
+        for (int b = 0; b < tw; ++b) {
+            const int h = ud.z + b;
+            if (h >= S.H) break;
+            const float sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
+            auto one = [&](float st, float ct) {
+                Ray r; float x, y, z;
+                ray_from_tables(S, P.world_frame, st, ct, sp_, cp, r, x, y, z, omax);
+                ox = r.ox; oy = r.oy; oz = r.oz;
+                dlo[0] = fminf(dlo[0], r.dx); dhi[0] = fmaxf(dhi[0], r.dx);
+                dlo[1] = fminf(dlo[1], r.dy); dhi[1] = fmaxf(dhi[1], r.dy);
+                dlo[2] = fminf(dlo[2], r.dz); dhi[2] = fmaxf(dhi[2], r.dz);
+            };
+            if (th <= 4) {
+#pragma unroll
+                for (int a = 0; a < 4; ++a) if (a < th && ud.y + a < S.V) one(stv[a], ctv[a]);
+            } else {
+                for (int a = 0; a < th && ud.y + a < S.V; ++a) one(__ldg(S.sin_t + ud.y + a), __ldg(S.cos_t + ud.y + a));
+            }
+        }
+    }
+    float smax = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
+    const float eps = 1.5f * (8e-6f * (smax + omax) + 1e-30f);
+    const float o3[3] = {ox, oy, oz};
+    float in[3], an[3], ifr[3], af[3];
+    bool neg[3];
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        neg[k] = ((cls >> k) & 1) != 0;
+        const float amin = neg[k] ? -dhi[k] : dlo[k], amax = neg[k] ? -dlo[k] : dhi[k];     // |d| interval
+        if (!(amin > 1e-6f)) ok = false;                                                     // touches 0 (or no valid ray)
+        const float in_abs = (1.0f / amax) * 0.999999f, if_abs = (1.0f / fmaxf(amin, 1e-6f)) * 1.000001f;
+        in[k] = neg[k] ? -in_abs : in_abs;
+        ifr[k] = neg[k] ? -if_abs : if_abs;
+        an[k] = -o3[k] * in[k] - eps * in_abs;
+        af[k] = -o3[k] * ifr[k] + eps * if_abs;
+    }
+    if (!ok) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
+    const float max_range = S.max_range;
+    // box = (lo.x, hi.x, lo.y, hi.y), (lo.z, hi.z): can a ray of the tile enter it, and not before which distance
+    auto tile_test = [&](const float4 bxy, float bzlo, float bzhi, float &n) -> bool {
+        const float nx = fmaf(neg[0] ? bxy.y : bxy.x, in[0], an[0]), fx = fmaf(neg[0] ? bxy.x : bxy.y, ifr[0], af[0]);
+        const float ny = fmaf(neg[1] ? bxy.w : bxy.z, in[1], an[1]), fy = fmaf(neg[1] ? bxy.z : bxy.w, ifr[1], af[1]);
+        const float nz = fmaf(neg[2] ? bzhi : bzlo, in[2], an[2]), fz = fmaf(neg[2] ? bzlo : bzhi, ifr[2], af[2]);
+        n = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
+        const float f = fminf(fminf(fx, fy), fz);
+        return n <= f && n <= max_range;
+    };
+
+    const int cap = P.tile_cap;
+    // deferred entries: (ref, entry distance, where the box is stored): side 0 / 1 = child slot of node `from`,
+    // side 2 = entry `from` of the sensor's chain.  16 bytes per push / pop; the box itself (24 bytes) is only
+    // re-read when a popped entry is listed without having been split.
+    int4 stk[kMaxTileEntries];
+    int sp = 0;
+    const int list = ud.x * 9 + cls;
+    const float4 *chain = P.chains + (size_t)list * (2 * kMaxChain);
+    {
+        const int n_chain = __ldg(P.chain_counts + list);
+        for (int k = 0; k < n_chain; ++k) {                       // far -> near: the nearest chain entry ends on top
+            const float4 e0 = __ldg(chain + 2 * k), e1 = __ldg(chain + 2 * k + 1);
+            float n;
+            if (!tile_test(e0, e1.x, e1.y, n)) continue;
+            if (sp == cap) { ok = false; break; }
+            stk[sp++] = make_int4(__float_as_int(e1.z), __float_as_int(n), k, 2);
+        }
+    }
+    if (!ok) { P.tile_counts[slot] = (uint8_t)kTileFallback; if (STATS) atomicAdd(P.counters + kCntTileFallbacks, 1ull); return; }
+    float4 *out = P.tile_lists + (size_t)slot * (2 * cap);
+    int n_out = 0, visits = 0;
+    // One flat loop (a step = list the entry in hand, or split it): the lanes of a warp -- neighbouring tiles -- stay
+    // in step instead of serialising an outer pop loop against an inner descent loop.
+    int4 cur = make_int4(0, 0, 0, 0);
+    float4 cxy = make_float4(0.f, 0.f, 0.f, 0.f);
+    float2 cz = make_float2(0.f, 0.f);
+    bool have = sp > 0, have_box = false;
+    if (have) cur = stk[--sp];
+    while (have) {
+        bool pop = false;
+        // a split turns the entry in hand into two: only while the list has room for it
+        if (cur.x < 0 || n_out + sp + 2 > cap || visits >= max_visits) {
+            if (!have_box) {
+                if (cur.w == 2) {
+                    const float4 e1 = __ldg(chain + 2 * cur.z + 1);
+                    cxy = __ldg(chain + 2 * cur.z); cz = make_float2(e1.x, e1.y);
+                } else {
+                    const float4 *nd = P.nodes + 4 * (size_t)cur.z;
+                    cxy = __ldg(nd + cur.w);
+                    cz = __ldg(reinterpret_cast<const float2 *>(nd + 2) + cur.w);
+                }
+            }
+            out[2 * n_out] = cxy; out[2 * n_out + 1] = make_float4(cz.x, cz.y, __int_as_float(cur.x), __int_as_float(cur.y));
+            ++n_out;
+            pop = true;
+        } else {
+            const int node = cur.x;
+            const float4 *nd = P.nodes + 4 * (size_t)node;
+            const float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2);
+            const float2 q3 = __ldg(reinterpret_cast<const float2 *>(nd + 3));
+            ++visits;
+            float n0, n1;
+            const bool h0 = tile_test(q0, q2.x, q2.y, n0), h1 = tile_test(q1, q2.z, q2.w, n1);
+            const bool first1 = h1 && (!h0 || n1 < n0);              // continue with child 1 (the nearer, or the only one)
+            if (h0 && h1)                                            // defer the farther child
+                stk[sp++] = first1 ? make_int4(__float_as_int(q3.x), __float_as_int(n0), node, 0)
+                                   : make_int4(__float_as_int(q3.y), __float_as_int(n1), node, 1);
+            cur = first1 ? make_int4(__float_as_int(q3.y), __float_as_int(n1), node, 1) : make_int4(__float_as_int(q3.x), __float_as_int(n0), node, 0);
+            cxy = first1 ? q1 : q0;
+            cz = first1 ? make_float2(q2.z, q2.w) : make_float2(q2.x, q2.y);
+            have_box = true;
+            pop = !h0 && !h1;
+        }
+        if (pop) {
+            have = sp > 0;
+            have_box = false;
+            if (have) cur = stk[--sp];
+        }
+    }
+    P.tile_counts[slot] = (uint8_t)n_out;
+    if (STATS) {
+        atomicAdd(P.counters + kCntTileVisits, (unsigned long long)visits);
+        atomicAdd(P.counters + kCntTileEntries, (unsigned long long)n_out);
+        if (n_out == 0) atomicAdd(P.counters + kCntTileEmpty, 1ull);
+    }
 }
 
 // ---- ordered compaction: count -> scan -> scatter (points in ray-id order) ---------------------------------

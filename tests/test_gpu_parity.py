@@ -429,6 +429,82 @@ def test_small_city_world_frame_vs_oracle_bvh(mode):
     ctx.close()
 
 
+@pytest.mark.parametrize("entries", [2, 3, 8, 12, 16])
+@pytest.mark.parametrize("leaf,tile", [(1, 8), (2, 8), (4, 32), (8, 2), (2, 16)])
+def test_tile_entry_lists_xt32_golden(meshes, golden, entries, leaf, tile):
+    """Per-tile entry lists (k_tile_entries) forced on for the 150-tile XT-32 scan, sensor frame: every list size,
+    leaf size and tile shape returns the golden per-ray (t, triangle id) bits."""
+    ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: 6, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TILE_WIDTH: tile,
+                                 capi.OPT_TILE_ENTRIES: entries, capi.OPT_TILE_MIN_UNITS: 0})
+    add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
+    add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
+    assert ctx.commit_scene() == 0
+    ctx.set_option(capi.OPT_TRACE_STATS, 1)
+    rc, t, tri = ctx.trace_raw()
+    assert rc == 0
+    cnt = ctx.trace_counters()
+    assert entries < 8 or tile > 8 or cnt["tile_entries"] > 0          # ... and its lists were used (wide tiles of an XT-32 are sign-mixed)
+    assert np.array_equal(tri, golden["l0000_ground_ben_tri"])
+    assert np.array_equal(t, golden["l0000_ground_ben_t"])
+    ctx.set_option(capi.OPT_TRACE_STATS, 0)
+    rc, pts = ctx.trace_scene(0, capi.TRACE_ORDERED)
+    assert rc == 0 and pts.shape[0] == 1781
+    ctx.close()
+
+
+@pytest.mark.parametrize("entries,visits", [(2, 0), (6, 3), (10, 0), (16, 1000)])
+def test_tile_entry_lists_small_city_vs_oracle_bvh(entries, visits):
+    """World frame, 4 yawed sensors in a small city: tile lists of every size bit-exact against the oracle's CPU BVH,
+    after a rebuild and after a refit (the lists are rebuilt with the tree), with a detection radius and an azimuth
+    window (entries beyond the radius are dropped by the tile walk)."""
+    meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
+    poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
+    elev, b, e, H = synth.lidar_table(32, 721)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx.set_option(capi.OPT_TILE_ENTRIES, entries)
+    ctx.set_option(capi.OPT_TILE_VISITS, visits)
+    ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
+    for k, (q, t) in enumerate(poses):
+        ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    A = [IDENT.copy() for _ in meshes]
+    for gi, (name, v, tr) in enumerate(meshes):
+        add_mesh(ctx, name, v, tr, A[gi])
+    for it in range(2):
+        assert ctx.commit_scene(capi.COMMIT_AUTO) == 0
+        s0 = lso.Sensor(elev, b, e, H, poses[0][0], poses[0][1])
+        verts, tris = lso.concat_scene(s0, [(v, tr, A[gi]) for gi, (_, v, tr) in enumerate(meshes)], mode=1)
+        bvh = lso.Bvh(verts, tris)
+        ctx.set_option(capi.OPT_TRACE_STATS, 1)
+        assert ctx.trace_batch(0, len(poses), capi.TRACE_NO_POINTS) == 0
+        cnt = ctx.trace_counters()
+        assert cnt["tile_entries"] + cnt["tile_fallbacks"] > 0 and (entries < 8 or cnt["tile_entries"] > 0)
+        ctx.set_option(capi.OPT_TRACE_STATS, 0)
+        assert ctx.trace_batch(0, len(poses), capi.TRACE_ORDERED) == 0
+        for k, (q, t) in enumerate(poses):
+            s = lso.Sensor(elev, b, e, H, q, t)
+            dirs_s = lso.ray_dirs(s.tables)
+            t_ref, tri_ref = bvh.trace(s.T, lso.rotate_dirs(s.R, dirs_s))
+            rc, pts = ctx.fetch_points(k, capi.TRACE_ORDERED)
+            assert rc == 0 and np.array_equal(pts, lso.pack_points(dirs_s, t_ref, tri_ref, H))
+            rc, tt, tri = ctx.trace_raw(k)
+            assert rc == 0
+            assert np.array_equal(tri, tri_ref) and np.array_equal(tt, t_ref)
+        if it == 1:
+            # detection radius 60 m + azimuth window on sensor 1: same as filtering the unlimited result
+            s = lso.Sensor(elev, b, e, H, poses[1][0], poses[1][1])
+            t_ref, tri_ref = bvh.trace(s.T, lso.rotate_dirs(s.R, lso.ray_dirs(s.tables)))
+            assert ctx.set_sensor_limits(60.0, 30.0, 170.0, index=1) == 0
+            rc, tt, tri = ctx.trace_raw(1)
+            assert rc == 0
+            t_lim, tri_lim = lso.apply_limits(s, t_ref, tri_ref, 60.0, (30.0, 170.0))
+            assert np.array_equal(tri, tri_lim) and np.array_equal(tt, t_lim)
+        bvh.close()
+        for gi in range(1, len(meshes)):
+            A[gi] = lso.affine_from_components((0.3 * gi, -0.2 * gi, 0.0), (0.0, 0.0, 0.01 * gi))
+            assert ctx.update_geometry(meshes[gi][0], None, None, A[gi]) == 0
+    ctx.close()
+
+
 def test_city_10m_size_independent_properties():
     """BASELINE config 4 at full size (10 M triangles): properties that need no CPU re-trace.
     (1) every variant returns the same (t, triangle) bits; (2) each hit point t*d lies on its triangle (float64
@@ -452,7 +528,14 @@ def test_city_10m_size_independent_properties():
     for mode in (1, 4, 5, 6, 2):
         for k in range(len(pick)):
             assert np.array_equal(res[mode][k][0], res[0][k][0]) and np.array_equal(res[mode][k][1], res[0][k][1])
+    # variant 6 with the per-tile entry lists off and at other list sizes
     ctx.set_option(capi.OPT_TRAVERSAL, 6)
+    for entries in (0, 4, 10):
+        ctx.set_option(capi.OPT_TILE_ENTRIES, entries)
+        for k in range(len(pick)):
+            rc, t, tri = ctx.trace_raw(k)
+            assert np.array_equal(t, res[0][k][0]) and np.array_equal(tri, res[0][k][1])
+    ctx.set_option(capi.OPT_TILE_ENTRIES, 16)
     assert ctx.commit_scene(capi.COMMIT_REFIT) == 0 and ctx.stats().last_commit_was_rebuild == 0
     for k in range(len(pick)):
         rc, t, tri = ctx.trace_raw(k)

@@ -17,6 +17,8 @@ def main():
     ap.add_argument("--launches", type=int, default=3)
     ap.add_argument("--small", action="store_true")
     ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--tile-entries", type=int, default=None)
+    ap.add_argument("--tile-visits", type=int, default=None)
     args = ap.parse_args()
     from bench import build_workload, frame_affine
     from lidarshooter_b200 import capi
@@ -36,6 +38,10 @@ def main():
         assert ctx.update_geometry(name, v, t, frame_affine(0, gi)) == 0
     assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
     for _ in range(args.launches):
+        if args.tile_entries is not None:
+            ctx.set_option(capi.OPT_TILE_ENTRIES, args.tile_entries)      # also drops the cached lists
+        if args.tile_visits is not None:
+            ctx.set_option(capi.OPT_TILE_VISITS, args.tile_visits)
         assert ctx.trace_batch(0, len(poses), args.flags) == 0, ctx.last_error()
     ctx.synchronize()
     print("ok")

@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--chain", default="1")
     ap.add_argument("--tiles", default="8")
     ap.add_argument("--layouts", default="0")
+    ap.add_argument("--tile-entries", default="16", help="per-tile entry list sizes (0 = off)")
+    ap.add_argument("--tile-visits", default="0", help="node visits per tile list (0 = 4 x entries)")
     ap.add_argument("--aspects", default="50")
     ap.add_argument("--scene", default="city", choices=["city", "heightfield"])
     args = ap.parse_args()
@@ -67,13 +69,16 @@ def main():
                 st = ctx.stats()
                 build_ms = {k: round(float(getattr(st, "ms_" + k)), 4) for k in
                             ("transform", "morton", "sort", "hierarchy", "fit", "toplevel")}
-                for mode, chain, tile in [(int(x), int(y), int(z)) for x in args.modes.split(",") for y in args.chain.split(",") for z in args.tiles.split(",")]:
+                for mode, chain, tile, te, tv in [(int(x), int(y), int(z), int(u), int(w)) for x in args.modes.split(",") for y in args.chain.split(",")
+                                                  for z in args.tiles.split(",") for u in args.tile_entries.split(",") for w in args.tile_visits.split(",")]:
                     ctx.set_option(capi.OPT_TRAVERSAL, mode)
+                    ctx.set_option(capi.OPT_TILE_VISITS, tv)
                     ctx.set_option(capi.OPT_ORIGIN_CHAIN, chain)
                     ctx.set_option(capi.OPT_TILE_WIDTH, tile)
                     ctx.set_option(capi.OPT_TRACE_STATS, 0)
                     ms = []
                     for r in range(args.reps + 1):
+                        ctx.set_option(capi.OPT_TILE_ENTRIES, te)      # also drops the cached lists: every timed launch rebuilds them
                         assert ctx.trace_batch(0, ns, 0) == 0, ctx.last_error()
                         ms.append(float(ctx.stats().ms_trace))
                     ms = ms[1:]
@@ -89,7 +94,9 @@ def main():
                     if base_sig is None:
                         base_sig = sig
                     rays = max(cnt["rays"], 1)
-                    row = {"morton_uniform": mu, "morton_layout": layout, "morton_aspect": aspect, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "tile_w": tile, "chain_tests_per_ray": cnt["chain_tests"] / rays,
+                    row = {"morton_uniform": mu, "morton_layout": layout, "morton_aspect": aspect, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "tile_w": tile, "tile_entries": te, "tile_visits": tv,
+                           "tile_visits_per_tile": cnt["tile_visits"] / max(cnt["units_uniform"], 1), "tile_entries_per_tile": cnt["tile_entries"] / max(cnt["units_uniform"], 1),
+                           "tile_fallbacks": cnt["tile_fallbacks"], "tile_empty": cnt["tile_empty"], "chain_tests_per_ray": cnt["chain_tests"] / rays,
                            "ms_trace_min": min(ms), "ms_trace_mean": float(np.mean(ms)),
                            "mrays_per_s": ns * R / (min(ms) * 1e-3) / 1e6,
                            "nodes_per_ray": cnt["nodes"] / rays, "leaves_per_ray": cnt["leaves"] / rays,
