@@ -70,7 +70,10 @@ enum {
                                       with leaf tests inside the node loop; 1 = persistent, generic slab test, units in
                                       table order; 2 = one thread per ray (no persistent fetch); 3 = brute force (all
                                       triangles); 4 = variant 1 + top BVH levels staged into shared memory by TMA bulk
-                                      copy; 5 = variant 1, while-while */
+                                      copy; 5 = variant 1, while-while; 7 = variant 6 with node visits and leaf tests in ONE loop
+                                      (fewer dependent round trips per warp, more instructions: measured 3 % slower).
+                                      Variants 6 and 7 start the rays from per-tile entry lists (LSB200_OPT_TILE_ENTRIES) and
+                                      prefetch the next unit's ticket / descriptor / list while the current one is traced */
     LSB200_OPT_LEAF_SIZE = 2,      /* max triangles per leaf, 1..8 (default 2) */
     LSB200_OPT_TOP_NODES = 3,      /* number of BVH nodes staged into shared memory by TMA bulk copy (default 1024) */
     LSB200_OPT_STAGE_TIMING = 4,   /* 1 = record CUDA events around every stage (lsb200_get_stats) */
@@ -87,7 +90,7 @@ enum {
                                       0 = round robin x, y, z; 100 = longest side first (cubic cells); default 60 */
     LSB200_OPT_FIT_RMQ = 13,       /* 1 = block-local node boxes by range queries over the block's leaf boxes (k_fit_rmq; measured
                                       slower: 0.86 vs 0.54 ms at 10 M triangles); 0 (default) = bottom-up climb (k_fit) */
-    LSB200_OPT_TILE_ENTRIES = 14,  /* entries of the per-tile entry lists (0 = off, 2..16; default 16): one thread per 32-ray tile walks
+    LSB200_OPT_TILE_ENTRIES = 14,  /* entries of the per-tile entry lists (0 = off, 2..16; default 10): one thread per 32-ray tile walks
                                       the part of the BVH descent that the tile's rays share, once, and lists the subtrees / leaves
                                       the tile's pyramid can reach; the rays start from that list (variant 6, >= 4096 tiles) */
     LSB200_OPT_TILE_VISITS = 15,   /* node visits a tile may spend on its list (0 = default: 4 x entries) */

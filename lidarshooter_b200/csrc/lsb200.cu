@@ -75,7 +75,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 16, opt_tile_visits = 0, opt_tile_min_units = 4096;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -302,7 +302,7 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     if (!c) return LSB200_ERR_INVALID;
     std::lock_guard<std::mutex> lk(c->mtx);
     switch (option) {
-    case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 6) break; c->opt_traversal = value; return LSB200_OK;
+    case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 7) break; c->opt_traversal = value; return LSB200_OK;
     case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_FIT_RMQ: c->opt_fit_rmq = value ? 1 : 0; return LSB200_OK;
@@ -784,6 +784,7 @@ static int launch_trace_mode(lsb200_ctx *c, const TraceParams &P, int n_units, i
     case 3: return launch_trace<3, STATS>(c, P, n_units);
     case 4: return launch_trace<4, STATS>(c, P, n_units);
     case 5: return launch_trace<5, STATS>(c, P, n_units);
+    case 7: return launch_trace<7, STATS>(c, P, n_units);
     default: return launch_trace<6, STATS>(c, P, n_units);
     }
 }
@@ -852,7 +853,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         P.chains = c->d_chains.as<float4>();
         P.chain_counts = c->d_chain_counts.as<int>();
     }
-    if (mode == 0 || mode == 6) {
+    if (mode == 0 || mode == 6 || mode == 7) {
         // octant queues: depend on the sensor table only, rebuilt when it (or the traced range) changes
         const int wf = P.world_frame ? 1 : 0;
         if (c->units_epoch != c->sensors_epoch || c->units_first != first || c->units_count != count || c->units_world != wf) {
@@ -878,7 +879,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         P.counters = c->d_counters.as<unsigned long long>();
     }
     // per-tile entry lists (k_tile_entries): worth their launch from a few thousand 32-ray tiles on
-    if (mode == 6 && c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units) {
+    if (mode >= 6 && c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units) {
         const int cap = c->opt_tile_entries;
         const int max_visits = c->opt_tile_visits > 0 ? c->opt_tile_visits : 4 * cap;
         P.tile_cap = cap;

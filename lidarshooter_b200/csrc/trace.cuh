@@ -15,6 +15,9 @@ namespace lsb {
 #define LSB_TRACE_THREADS 384
 #define LSB_TRACE_CTAS 3
 #endif
+#ifndef LSB_DEFER_APPEND
+#define LSB_DEFER_APPEND 0       // 1: hit-append slots requested one unit ahead (measured slower: the parked state spills)
+#endif
 constexpr int kTraceThreads = LSB_TRACE_THREADS;     // x LSB_TRACE_CTAS CTAs / SM: 384 x 3 = 1152 threads at <= 56 registers (512 x 2 measured 2 % slower)
 constexpr int kStackSize = 64;         // LBVH depth <= 30 Morton bits + index tie-break bits
 
@@ -323,6 +326,86 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
     bi_out = bi;
 }
 
+// Single-loop form for the tile-list regime (variant 7): a step of a lane is whatever its next item is -- a node visit
+// or a leaf test -- so a warp needs max-over-lanes(items) dependent memory round trips per unit instead of the
+// while-while form's (node rounds + leaf rounds).  More instructions issued (both bodies per mixed step), fewer
+// round trips: the right trade once the kernel is latency-bound rather than issue-bound.
+template <int OCT, bool STATS, bool SMEM>
+__device__ __forceinline__ void trace_ray_il(const TraceParams &P, float eps, const Ray &r,
+                                             const float4 *__restrict__ chain, int n_chain, bool reversed,
+                                             float &best_out, int &bi_out, RayStats &rs)
+{
+    const float tiny = 1e-30f;
+    const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
+    const float iy = 1.0f / (fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
+    const float iz = 1.0f / (fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
+    const float ax = -(r.ox + eps) * ix, ay = -(r.oy + eps) * iy, az = -(r.oz + eps) * iz;
+    const float bx = -(r.ox - eps) * ix, by = -(r.oy - eps) * iy, bz = -(r.oz - eps) * iz;
+    constexpr int kDone = 0x7fffffff;
+    float best = INFINITY, far_lim = INFINITY;
+    int bi = -1;
+    int2 stack[kStackSize];
+    int sp = 0;
+    int cur = P.top_cap;
+    if (n_chain > 0) {
+        const float4 *e = reversed ? chain + 2 * (n_chain - 1) : chain;
+        const int step = reversed ? -2 : 2;
+        for (int k = 0; k < n_chain; ++k, e += step) {
+            const float4 e0 = SMEM ? e[0] : __ldg(e), e1 = SMEM ? e[1] : __ldg(e + 1);
+            float n, f;
+            slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
+                         fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
+            if (STATS) ++rs.chain_tests;
+            if (n <= f) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n));
+        }
+        if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
+        cur = sp > 0 ? stack[--sp].x : kDone;
+    }
+    while (cur != kDone) {
+        bool pop = false;
+        if (cur >= 0) {
+            const float4 *n = P.nodes + 4 * (size_t)cur;
+            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
+            const float2 q3 = __ldg(reinterpret_cast<const float2 *>(n + 3));
+            if (STATS) ++rs.nodes;
+            float n0, f0, n1, f1;
+            slab_nf<OCT>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
+                         fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
+            slab_nf<OCT>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
+                         fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
+            const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
+            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+            if (hit0 && hit1) {
+                const bool swap = n1 < n0;
+                cur = swap ? c1 : c0;
+                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
+            } else if (hit0) {
+                cur = c0;
+            } else if (hit1) {
+                cur = c1;
+            } else {
+                pop = true;
+            }
+        } else {
+            if (STATS) { ++rs.leaves; rs.tris += (unsigned)(((~cur) >> kLeafShift) + 1); }
+            test_leaf(P, cur, r, best, bi);
+            far_lim = best * 1.0000005f;
+            pop = true;
+        }
+        if (pop) {
+            cur = kDone;
+            while (sp > 0) {
+                const int2 e = stack[--sp];
+                if (__int_as_float(e.y) <= far_lim * 1.0000005f) { cur = e.x; break; }
+                if (STATS) ++rs.culled;
+            }
+        }
+    }
+    best_out = best;
+    bi_out = bi;
+}
+
 // Brute force over all leaf-ordered triangles (validation variant; also the tiny-scene path).
 __device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, float &best, int &bi)
 {
@@ -416,11 +499,26 @@ __device__ __forceinline__ bool unit_lane_ray(const SensorDev &S, int4 ud, int t
     return v < S.V && h < S.H;
 }
 
+// A warp's hit append in flight: slots requested (raw = the atomic's return value in the leader lane), points parked in
+// the warp's shared-memory row until the next unit has been traced.
+struct PendingAppend { uint32_t raw; unsigned mask; int sensor; };
+__device__ __forceinline__ void flush_append(const TraceParams &P, PendingAppend &pd, const float4 *s_pts, unsigned lane)
+{
+    if (pd.mask == 0u) return;
+    const uint32_t base = __shfl_sync(0xffffffffu, pd.raw, __ffs(pd.mask) - 1);
+    if ((pd.mask >> lane) & 1u) {
+        const float4 q = s_pts[lane];
+        store_point(P.sensors[pd.sensor].points, base + __popc(pd.mask & lanemask_lt()), P.flags, q.x, q.y, q.z, __float_as_int(q.w));
+    }
+    pd.mask = 0u;
+}
+
 // One 32-ray work unit: generate the rays, trace them, store t / triangle id, append the hits.
 // MODE: see k_trace.  OCT: slab form for every ray of the unit (0..7 only when classified uniform).
 template <int MODE, int OCT, bool STATS>
 __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 *s_top, int n_top, float smax, int4 ud,
-                                             unsigned lane, int tile_n = -1, const float4 *s_list = nullptr)
+                                             unsigned lane, int tile_n = -1, const float4 *s_list = nullptr,
+                                             PendingAppend *pend = nullptr, float4 *s_pts = nullptr)
 {
     constexpr bool TOP = (MODE == 4);
     const int si = ud.x;
@@ -434,7 +532,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
     // MODE 6: a unit whose tile list (k_tile_entries, near -> far) was prefetched into shared memory by run_phase
     // starts from it (tile_n entries, 0 = the tile's pyramid reaches nothing); tile_n < 0: no tile list -- the rays
     // read their sensor's origin chain (far -> near) from global memory.
-    const bool w_tile = MODE == 6 && tile_n >= 0;
+    const bool w_tile = (MODE == 6 || MODE == 7) && tile_n >= 0;
     const bool fired = valid && (S.az_mask == nullptr || __ldg(S.az_mask + h) != 0);
     if (valid && !fired) { S.t_out[ray] = INFINITY; S.tri_out[ray] = -1; }      // outside the azimuth window: no return
     if (fired) {
@@ -447,6 +545,10 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
         else {
             const int list = si * 9 + OCT;
             const int n_chain = P.chain_counts ? __ldg(P.chain_counts + list) : 0;
+            if (MODE == 7) {
+                if (w_tile) trace_ray_il<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
+                else trace_ray_il<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
+            } else
             if (w_tile) trace_ray_ww<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
             else if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
             else
@@ -467,13 +569,26 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             atomicAdd(P.counters + kCntHits, (unsigned long long)nh); atomicMax(P.counters + kCntMaxStack, (unsigned long long)d);
             atomicAdd(P.counters + kCntCulled, (unsigned long long)cu);
             atomicAdd(P.counters + kCntChainTests, (unsigned long long)ct);
-            if (MODE == 0 || MODE == 6) atomicAdd(P.counters + (OCT < 8 ? kCntUnitsUniform : kCntUnitsMixed), 1ull);
+            if (MODE == 0 || MODE == 6 || MODE == 7) atomicAdd(P.counters + (OCT < 8 ? kCntUnitsUniform : kCntUnitsMixed), 1ull);
         }
     }
     if (!(P.flags & (1u | 8u))) {     // neither ORDERED nor NO_POINTS: warp-aggregated atomic append
         const bool hit = valid && bi >= 0;
         const unsigned m = __ballot_sync(0xffffffffu, hit);
-        if (m) {
+        if ((MODE == 6 || MODE == 7) && pend != nullptr) {
+            // deferred form: the slot reservation of THIS unit is requested now and used after the next unit has been
+            // traced (flush_append), so nobody waits for the atomic's round trip; the points wait in shared memory
+            flush_append(P, *pend, s_pts, lane);
+            if (m) {
+                if (hit) {
+                    float x, y, z;
+                    hit_point(S, P.flags, best, dsx, dsy, dsz, x, y, z);
+                    s_pts[lane] = make_float4(x, y, z, __int_as_float((P.flags & 2u) ? 0 : v));
+                }
+                if (lane == (unsigned)(__ffs(m) - 1)) pend->raw = atomicAdd(S.count, (uint32_t)__popc(m));
+                pend->mask = m; pend->sensor = si;
+            }
+        } else if (m) {
             uint32_t base = 0;
             if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(S.count, (uint32_t)__popc(m));
             base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
@@ -502,14 +617,14 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int MODE, int OCT, bool STATS>
-__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list)
+__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list, float4 *s_pts)
 {
     int begin = 0;
 #pragma unroll
     for (int o = 0; o < OCT; ++o) begin += (int)__ldg(P.oct_hist + o);
     const int count = (int)__ldg(P.oct_hist + OCT);
     if (count == 0) return;
-    if (MODE != 6) {                                               // variant 0 keeps the plain loop it was measured with
+    if (MODE != 6 && MODE != 7) {                                  // variant 0 keeps the plain loop it was measured with
         while (true) {
             int k = 0;
             if (lane == 0) k = (int)atomicAdd(&P.work[2 + OCT], 1u);
@@ -519,15 +634,14 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
         }
         return;
     }
-    const bool lists = MODE == 6 && OCT < 8 && P.tile_counts != nullptr;
+    const bool lists = (MODE == 6 || MODE == 7) && OCT < 8 && P.tile_counts != nullptr;
     constexpr int kBuf = 2 * kMaxTileEntries;                     // float4 per buffer
     auto ticket = [&]() -> int { return lane == 0 ? (int)atomicAdd(&P.work[2 + OCT], 1u) : 0; };
     auto fetch = [&](int k, int4 &ud, int &tn, float4 *buf) {     // descriptor, list size and list of queue entry k
         ud = __ldg(P.unit_list + begin + k);
-        tn = -1;
+        tn = kTileFallback;                                        // raw list size; looked at when the unit's turn comes
         if (lists) {
-            const int tc = (int)__ldg(P.tile_counts + begin + k);
-            tn = tc == kTileFallback ? -1 : tc;
+            tn = (int)__ldg(P.tile_counts + begin + k);
             if ((int)lane < 2 * P.tile_cap) cp_async16(buf + lane, P.tile_lists + (size_t)(begin + k) * (2 * P.tile_cap) + lane);
         }
         cp_async_commit();
@@ -536,21 +650,23 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
     if (k_cur >= count) return;
     int raw_next = ticket();                                       // consumed at the top of the loop
     int4 ud; int tn; int b = 0;
+    PendingAppend pend{0u, 0u, 0};
     fetch(k_cur, ud, tn, s_list);
     while (true) {
         const int k_next = __shfl_sync(0xffffffffu, raw_next, 0);
         const bool more = k_next < count;
-        int4 ud_n = make_int4(0, 0, 0, 0); int tn_n = -1;
+        int4 ud_n = make_int4(0, 0, 0, 0); int tn_n = kTileFallback;
         if (more) { fetch(k_next, ud_n, tn_n, s_list + (b ^ 1) * kBuf); raw_next = ticket(); }
         else cp_async_commit();
         cp_async_wait<1>();                                        // everything but the newest group: this unit's list is in
         __syncwarp();
-        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, ud, lane, tn, s_list + b * kBuf);
+        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, ud, lane, tn == kTileFallback ? -1 : tn, s_list + b * kBuf, LSB_DEFER_APPEND ? &pend : nullptr, s_pts);
         if (!more) break;
         __syncwarp();                                              // all lanes are done with buffer b before it is refilled
         ud = ud_n; tn = tn_n; b ^= 1;
     }
     cp_async_wait<0>();
+    flush_append(P, pend, s_pts, lane);
 }
 
 // MODE 0: persistent CTAs, nodes through L1/L2, units pre-sorted by ray octant (k_classify_units / k_scatter_units)
@@ -591,14 +707,16 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
 
     const unsigned lane = lane_id();
-    __shared__ float4 s_lists[(MODE == 6) ? kTraceThreads / 32 : 1][(MODE == 6) ? 4 * kMaxTileEntries : 1];      // 2 buffers per warp
-    float4 *s_list = s_lists[(MODE == 6) ? (threadIdx.x >> 5) : 0];
-    if (MODE == 0 || MODE == 6) {
-        run_phase<MODE, 8, STATS>(P, smax, lane, s_list);
-        run_phase<MODE, 0, STATS>(P, smax, lane, s_list); run_phase<MODE, 1, STATS>(P, smax, lane, s_list);
-        run_phase<MODE, 2, STATS>(P, smax, lane, s_list); run_phase<MODE, 3, STATS>(P, smax, lane, s_list);
-        run_phase<MODE, 4, STATS>(P, smax, lane, s_list); run_phase<MODE, 5, STATS>(P, smax, lane, s_list);
-        run_phase<MODE, 6, STATS>(P, smax, lane, s_list); run_phase<MODE, 7, STATS>(P, smax, lane, s_list);
+    __shared__ float4 s_lists[(MODE >= 6) ? kTraceThreads / 32 : 1][(MODE >= 6) ? 4 * kMaxTileEntries : 1];      // 2 buffers per warp
+    float4 *s_list = s_lists[(MODE >= 6) ? (threadIdx.x >> 5) : 0];
+    __shared__ float4 s_points[(MODE >= 6 && LSB_DEFER_APPEND) ? kTraceThreads : 1];                  // parked hit points (deferred append)
+    float4 *s_pts = s_points + ((MODE >= 6 && LSB_DEFER_APPEND) ? (threadIdx.x & ~31u) : 0u);
+    if (MODE == 0 || MODE == 6 || MODE == 7) {
+        run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts);
+        run_phase<MODE, 0, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 1, STATS>(P, smax, lane, s_list, s_pts);
+        run_phase<MODE, 2, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 3, STATS>(P, smax, lane, s_list, s_pts);
+        run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts);
+        run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts);
     } else if (MODE == 2) {
         const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
         if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
@@ -618,7 +736,7 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
             __threadfence();
             if (atomicAdd(&P.work[1], 1u) == gridDim.x - 1) {
                 P.work[0] = 0; P.work[1] = 0;
-                if (MODE == 0 || MODE == 6) for (int o = 0; o < 9; ++o) P.work[2 + o] = 0;
+                if (MODE == 0 || MODE == 6 || MODE == 7) for (int o = 0; o < 9; ++o) P.work[2 + o] = 0;
                 __threadfence();
             }
         }

@@ -89,7 +89,7 @@ def test_xt32_reference_counts_and_golden(meshes, golden, uid, n_ground, n_both)
     ctx.close()
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5, 6, 7])
 @pytest.mark.parametrize("leaf,tile", [(1, 8), (4, 32), (8, 2), (2, 16)])
 def test_traversal_variants_agree(meshes, golden, mode, leaf, tile):
     ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: mode, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TOP_NODES: 256,
@@ -384,7 +384,7 @@ def test_heightfield_1m_tris_vs_oracle_bvh():
     ctx.close()
 
 
-@pytest.mark.parametrize("mode", [0, 1, 4, 5, 6])
+@pytest.mark.parametrize("mode", [0, 1, 4, 5, 6, 7])
 def test_small_city_world_frame_vs_oracle_bvh(mode):
     """BASELINE config 4 in miniature (same generator, 4 yawed sensors, world frame): every traversal variant
     bit-exact against the oracle's CPU BVH; rebuild == refit after the buildings move."""
@@ -521,11 +521,11 @@ def test_city_10m_size_independent_properties():
     assert sum(m[2].shape[0] for m in meshes) == 10_000_000
     assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
     res = {}
-    for mode in (0, 1, 4, 5, 6, 2):
+    for mode in (0, 1, 4, 5, 6, 7, 2):
         ctx.set_option(capi.OPT_TRAVERSAL, mode)
         ctx.set_option(capi.OPT_TILE_WIDTH, 4 if mode == 1 else 8)
         res[mode] = [ctx.trace_raw(k)[1:] for k in range(len(pick))]
-    for mode in (1, 4, 5, 6, 2):
+    for mode in (1, 4, 5, 6, 7, 2):
         for k in range(len(pick)):
             assert np.array_equal(res[mode][k][0], res[0][k][0]) and np.array_equal(res[mode][k][1], res[0][k][1])
     # variant 6 with the per-tile entry lists off and at other list sizes
