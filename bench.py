@@ -428,6 +428,9 @@ def main():
     ctx.set_option(capi.OPT_STAGE_TIMING, 0)
     stages = {k: round(float(getattr(st, "ms_" + k)), 4) for k in
               ("transform", "morton", "sort", "hierarchy", "fit", "toplevel", "trace", "compact")}
+    # the trace stage = k_tile_entries (per-tile entry lists, rebuilt with every BVH) + k_trace
+    stages["tile_lists"] = round(float(st.ms_tile_lists), 4)
+    stages["k_trace"] = round(float(st.ms_trace) - float(st.ms_tile_lists), 4)
 
     # ---- end-to-end leg: host buffers in, host point clouds out --------------------------------------------
     # The public call for a batch of frames is lsb200_run_frames: per frame it uploads every mesh's vertices from
@@ -506,7 +509,7 @@ def main():
             "clocks": clocks,
             "e2e": e2e["xyzi16"], "e2e_pointcloud2_32": e2e["pointcloud2_32"],
             "gpu_launches": launches,
-            "roofline": {"kernel": "k_trace", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"kernel": "trace stage = k_tile_entries + k_trace (stages_ms: tile_lists, k_trace)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_ray": b_ray(n_tris, hit_fraction), "rays_per_launch": rays_per_step_rank,
                          "ms_per_launch": ms_trace},

@@ -226,6 +226,8 @@ typedef struct lsb200_stats {
     /* launches issued since the context was created / since lsb200_reset_counters */
     int64_t kernel_launches;
     float scene_lo[3], scene_hi[3];
+    float ms_tile_lists;           /* k_tile_entries alone (its time is part of ms_trace); 0 when the lists were reused / off */
+    int32_t reserved0;
 } lsb200_stats;
 LSB200_API int lsb200_get_stats(lsb200_ctx *ctx, lsb200_stats *out);
 LSB200_API int lsb200_reset_counters(lsb200_ctx *ctx);

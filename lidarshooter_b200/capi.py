@@ -50,7 +50,8 @@ class Stats(C.Structure):
                 ("ms_transform", C.c_float), ("ms_morton", C.c_float), ("ms_sort", C.c_float),
                 ("ms_hierarchy", C.c_float), ("ms_fit", C.c_float), ("ms_toplevel", C.c_float),
                 ("ms_trace", C.c_float), ("ms_compact", C.c_float),
-                ("kernel_launches", C.c_int64), ("scene_lo", C.c_float * 3), ("scene_hi", C.c_float * 3)]
+                ("kernel_launches", C.c_int64), ("scene_lo", C.c_float * 3), ("scene_hi", C.c_float * 3),
+                ("ms_tile_lists", C.c_float), ("reserved0", C.c_int32)]
 
 
 _lib = None

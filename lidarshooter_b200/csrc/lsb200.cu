@@ -831,6 +831,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     if (timing) cudaEventRecord(c->ev[8], st);
     int mode = c->opt_traversal;
     int rc = 0;
+    bool tile_timed = false;
     if (mode == 4 && c->built_top > 0 && !c->top_valid) {  // variant switched on after the commit
         k_top_level<<<1, 1024, (size_t)c->built_top * sizeof(int), st>>>(scene_dev(c), c->d_misc.as<int>());
         count_launch(c);
@@ -891,13 +892,16 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         }
         P.tile_lists = c->d_tile_lists.as<float4>();
         P.tile_counts = c->d_tile_counts.as<uint8_t>();
+        tile_timed = false;
         if (stale || c->opt_stats) {
             const unsigned blocks = (unsigned)((n_units + 127) / 128);
+            if (timing) { cudaEventRecord(c->ev[11], st); tile_timed = true; }
             if (c->opt_stats) k_tile_entries<true><<<blocks, 128, 0, st>>>(P, max_visits);
             else k_tile_entries<false><<<blocks, 128, 0, st>>>(P, max_visits);
             count_launch(c);
             c->tile_commit_epoch = c->commit_epoch; c->tile_sensors_epoch = c->sensors_epoch; c->tile_first = first; c->tile_count = count;
             c->tile_cap = cap; c->tile_visits = max_visits;
+            if (timing) cudaEventRecord(c->ev[7], st);
         }
     }
     if (c->opt_stats) {
@@ -922,6 +926,8 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         LSB_CU(c, cudaStreamSynchronize(st));
         cudaEventElapsedTime(&c->stats.ms_trace, c->ev[8], c->ev[9]);
         cudaEventElapsedTime(&c->stats.ms_compact, c->ev[9], c->ev[10]);
+        c->stats.ms_tile_lists = 0.0f;
+        if (tile_timed) cudaEventElapsedTime(&c->stats.ms_tile_lists, c->ev[11], c->ev[7]);
     }
     LSB_CU(c, cudaGetLastError());
     return LSB200_OK;

@@ -15,6 +15,9 @@ namespace lsb {
 #define LSB_TRACE_THREADS 384
 #define LSB_TRACE_CTAS 3
 #endif
+#ifndef LSB_LAZY_LIST
+#define LSB_LAZY_LIST 1          // variant 6: list entries are taken lazily instead of being pushed up front
+#endif
 #ifndef LSB_DEFER_APPEND
 #define LSB_DEFER_APPEND 0       // 1: hit-append slots requested one unit ahead (measured slower: the parked state spills)
 #endif
@@ -326,6 +329,92 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
     bi_out = bi;
 }
 
+// Lazy-list form of trace_ray_ww (variant 6 with LSB_LAZY_LIST): instead of testing every list entry up front and
+// pushing the ones the ray enters (one 8-byte local-memory store per entry and lane -- written through to L2: 2.6 GB
+// of the 4.3 GB the SMs sent to L2 per launch -- and one load per pop), the list itself is the bottom of the stack:
+// entries are taken in near -> far order only when the ray has nothing else left, and tested against the hit
+// distance known by then, so whatever lies behind the first hit fails its own box test.  The stack holds deferred
+// children only.  Same set of subtrees entered or rejected by conservative tests: same results.
+template <int OCT, bool STATS, bool SMEM>
+__device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, const Ray &r,
+                                             const float4 *__restrict__ chain, int n_chain, bool reversed,
+                                             float &best_out, int &bi_out, RayStats &rs)
+{
+    const float tiny = 1e-30f;
+    const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
+    const float iy = 1.0f / (fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
+    const float iz = 1.0f / (fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
+    const float ax = -(r.ox + eps) * ix, ay = -(r.oy + eps) * iy, az = -(r.oz + eps) * iz;
+    const float bx = -(r.ox - eps) * ix, by = -(r.oy - eps) * iy, bz = -(r.oz - eps) * iz;
+    constexpr int kDone = 0x7fffffff;       // never a node index (n_tris < 2^28)
+    float best = INFINITY, far_lim = INFINITY;
+    int bi = -1;
+    int2 stack[kStackSize];
+    int sp = 0;
+    // sensor chains are listed far -> near (walked backwards), tile lists near -> far
+    const float4 *e = reversed ? chain : chain + 2 * (n_chain - 1);
+    const int step = reversed ? 2 : -2;
+    int left = n_chain;                     // list entries not looked at yet
+    int cur = n_chain > 0 ? kDone : P.top_cap;
+    while (true) {
+        if (cur == kDone) {                 // nothing in hand: next list entry the ray enters
+            while (left > 0) {
+                const float4 e0 = SMEM ? e[0] : __ldg(e), e1 = SMEM ? e[1] : __ldg(e + 1);
+                e += step; --left;
+                float n, f;
+                slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
+                             fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
+                if (STATS) ++rs.chain_tests;
+                if (n <= f) { cur = __float_as_int(e1.z); break; }
+            }
+            if (cur == kDone) break;
+        }
+        while ((unsigned)cur < (unsigned)kDone) {           // cur >= 0 and not kDone: an inner node
+            const float4 *n = P.nodes + 4 * (size_t)cur;
+            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
+            const float2 q3 = __ldg(reinterpret_cast<const float2 *>(n + 3));
+            if (STATS) ++rs.nodes;
+            float n0, f0, n1, f1;
+            slab_nf<OCT>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
+                         fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
+            slab_nf<OCT>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
+                         fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
+            const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
+            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+            if (hit0 && hit1) {
+                const bool swap = n1 < n0;
+                cur = swap ? c1 : c0;
+                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
+            } else if (hit0) {
+                cur = c0;
+            } else if (hit1) {
+                cur = c1;
+            } else {
+                cur = kDone;
+                while (sp > 0) {
+                    const int2 t = stack[--sp];
+                    if (__int_as_float(t.y) <= far_lim * 1.0000005f) { cur = t.x; break; }
+                    if (STATS) ++rs.culled;
+                }
+            }
+        }
+        if (cur < 0) {
+            if (STATS) { ++rs.leaves; rs.tris += (unsigned)(((~cur) >> kLeafShift) + 1); }
+            test_leaf(P, cur, r, best, bi);
+            far_lim = best * 1.0000005f;
+            cur = kDone;
+            while (sp > 0) {
+                const int2 t = stack[--sp];
+                if (__int_as_float(t.y) <= far_lim * 1.0000005f) { cur = t.x; break; }
+                if (STATS) ++rs.culled;
+            }
+        }
+    }
+    best_out = best;
+    bi_out = bi;
+}
+
 // Single-loop form for the tile-list regime (variant 7): a step of a lane is whatever its next item is -- a node visit
 // or a leaf test -- so a warp needs max-over-lanes(items) dependent memory round trips per unit instead of the
 // while-while form's (node rounds + leaf rounds).  More instructions issued (both bodies per mixed step), fewer
@@ -548,6 +637,10 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             if (MODE == 7) {
                 if (w_tile) trace_ray_il<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
                 else trace_ray_il<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
+            } else
+            if (MODE == 6 && LSB_LAZY_LIST) {
+                if (w_tile) trace_ray_lz<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
+                else trace_ray_lz<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
             } else
             if (w_tile) trace_ray_ww<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
             else if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);

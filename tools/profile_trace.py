@@ -17,6 +17,7 @@ def main():
     ap.add_argument("--launches", type=int, default=3)
     ap.add_argument("--small", action="store_true")
     ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--max-range", type=float, default=0.0, help="detection radius for every sensor (0 = none)")
     ap.add_argument("--tile-entries", type=int, default=None)
     ap.add_argument("--tile-visits", type=int, default=None)
     args = ap.parse_args()
@@ -33,6 +34,9 @@ def main():
         ctx.set_option(capi.OPT_TOP_NODES, args.top)
     for k, (q, t) in enumerate(poses):
         ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    if args.max_range > 0:
+        for k in range(len(poses)):
+            assert ctx.set_sensor_limits(args.max_range, index=k) == 0
     for gi, (name, v, t) in enumerate(meshes):
         assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0]) >= 0
         assert ctx.update_geometry(name, v, t, frame_affine(0, gi)) == 0
