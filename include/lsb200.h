@@ -93,7 +93,10 @@ enum {
     LSB200_OPT_TILE_ENTRIES = 14,  /* entries of the per-tile entry lists (0 = off, 2..16; default 10): one thread per 32-ray tile walks
                                       the part of the BVH descent that the tile's rays share, once, and lists the subtrees / leaves
                                       the tile's pyramid can reach; the rays start from that list (variant 6, >= 4096 tiles) */
-    LSB200_OPT_TILE_VISITS = 15,   /* node visits a tile may spend on its list (0 = default: 4 x entries) */
+    LSB200_OPT_TILE_VISITS = 15,   /* node visits a tile may spend on its list (0 = default: 3.2 x entries) */
+    LSB200_OPT_SUPER_TILES = 17,   /* 1 = two-level lists: a tile's walk starts from the list of its supertile (4 x 4 tiles, one walk
+                                      per supertile) instead of its sensor's origin chain: 26 -> 9 node visits per tile walk, but
+                                      measured slower overall (1.90 vs 1.74 ms per trace stage); 0 (default) = off */
     LSB200_OPT_TILE_MIN_UNITS = 16, /* tile lists are built for launches of at least this many 32-ray tiles (default 4096: below
                                       that, e.g. an XT-32 with 150 tiles, the extra launch costs more than it saves) */
     LSB200_OPT_SMALL_BUILD = 10    /* 1 (default) = scenes of <= 16384 triangles in <= 16 geometries are committed by ONE

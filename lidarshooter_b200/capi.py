@@ -17,7 +17,7 @@ COMMIT_AUTO, COMMIT_REBUILD, COMMIT_REFIT = 0, 1, 2
 TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS = 1, 2, 4, 8, 16
 OPT_TRAVERSAL, OPT_LEAF_SIZE, OPT_TOP_NODES, OPT_STAGE_TIMING, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
 OPT_TRACE_STATS, OPT_MORTON_UNIFORM, OPT_ORIGIN_CHAIN, OPT_TILE_WIDTH, OPT_SMALL_BUILD, OPT_MORTON_LAYOUT, OPT_MORTON_ASPECT, OPT_FIT_RMQ = 6, 7, 8, 9, 10, 11, 12, 13
-OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS = 14, 15, 16
+OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES = 14, 15, 16, 17
 ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5
 
 # every symbol include/lsb200.h declares (tests/test_abi.py checks the library exports each one)
@@ -296,10 +296,10 @@ class Context:
 
     def trace_counters(self):
         """Totals of the last OPT_TRACE_STATS launch as a dict."""
-        out = (C.c_uint64 * 14)()
-        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 14))
+        out = (C.c_uint64 * 15)()
+        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 15))
         names = ("rays", "nodes", "leaves", "tris", "units_uniform", "units_mixed", "max_stack", "hits", "culled_pops", "chain_tests",
-                 "tile_visits", "tile_entries", "tile_fallbacks", "tile_empty")
+                 "tile_visits", "tile_entries", "tile_fallbacks", "tile_empty", "super_visits")
         return {k: int(out[i]) for i, k in enumerate(names)}
 
     def reset_counters(self):

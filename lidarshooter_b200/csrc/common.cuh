@@ -39,6 +39,7 @@ struct SensorDev {           // one per LiDAR device
     int V, H, n_rays;
     int unit_base;                // first 32-ray work unit of this sensor in a batch
     int tiles_h;                  // work units per row of tiles: ceil(H / tile width)
+    int sup_base, sup_w;          // first supertile (4 x 4 tiles) of this sensor, supertiles per row
     float max_range;              // hits beyond this range are dropped (+inf: none) -- lsb200_set_sensor_limits
     const uint8_t *az_mask;       // [H] 1 = azimuth step fired; nullptr = all
     float *t_out;                 // [n_rays]

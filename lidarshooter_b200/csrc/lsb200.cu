@@ -75,7 +75,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -85,7 +85,7 @@ struct lsb200_ctx {
     bool sensors_dirty = true;
     // scene arrays
     DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
-        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts;
+        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts, d_sup_lists, d_sup_counts, d_tile_iv, d_sup_iv;
     std::vector<GeomDesc> h_geoms;
     std::vector<SensorDev> h_sensors, h_sensors_b;
     cudaStream_t copy_stream = nullptr;
@@ -97,6 +97,9 @@ struct lsb200_ctx {
     // tile entry lists: valid for one BVH, one set of sensor poses, one set of octant queues and one list size
     int64_t tile_commit_epoch = -1, tile_sensors_epoch = -1;
     int tile_first = -1, tile_count = -1, tile_cap = -1, tile_visits = -1;
+    // direction intervals of the tiles / supertiles: valid for one set of sensor tables + poses and one traced range
+    int64_t iv_sensors_epoch = -1;
+    int iv_first = -1, iv_count = -1, iv_world = -1, iv_super = -1;
     float h_xf[12];
     uint32_t *h_count = nullptr;                                 // pinned
     int n_verts = 0, n_tris = 0;
@@ -266,7 +269,7 @@ int lsb200_destroy(lsb200_ctx *c)
         for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
-                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts};
+                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts, &c->d_sup_lists, &c->d_sup_counts, &c->d_tile_iv, &c->d_sup_iv};
         for (auto *b : bufs) b->release();
         if (c->h_count) cudaFreeHost(c->h_count);
         for (auto &e : c->ev) if (e) cudaEventDestroy(e);
@@ -307,6 +310,7 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_FIT_RMQ: c->opt_fit_rmq = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_TILE_ENTRIES: if (value < 0 || value > kMaxTileEntries || value == 1) break; c->opt_tile_entries = value; c->tile_commit_epoch = -1; return LSB200_OK;
+    case LSB200_OPT_SUPER_TILES: c->opt_super_tiles = value ? 1 : 0; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_TILE_MIN_UNITS: if (value < 0) break; c->opt_tile_min_units = value; return LSB200_OK;
     case LSB200_OPT_TILE_VISITS: if (value < 0 || value > 4096) break; c->opt_tile_visits = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
@@ -710,12 +714,12 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
     }
     if (!dirty) return 0;
     c->h_sensors.assign(ns, SensorDev{});
-    int unit = 0;
+    int unit = 0, sup = 0;
     const int tw = 1 << c->opt_tile_w_log2, th = 32 >> c->opt_tile_w_log2;
     for (size_t i = 0; i < ns; ++i) {
         Sensor &s = c->sensors[i];
         SensorDev &d = c->h_sensors[i];
-        d.unit_base = unit;
+        d.unit_base = unit; d.sup_base = sup; d.sup_w = 1;
         if (!s.set) continue;
         const float *tab = s.tables.as<float>();
         d.sin_t = tab; d.cos_t = tab + s.V; d.sin_p = tab + 2 * s.V; d.cos_p = tab + 2 * s.V + s.H;
@@ -725,7 +729,10 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
         d.t_out = s.t.as<float>(); d.tri_out = s.tri.as<int32_t>(); d.points = s.points.as<uint8_t>();
         d.count = c->d_counts.as<uint32_t>() + i; d.block_counts = s.blocks.as<uint32_t>();
         d.tiles_h = (s.H + tw - 1) / tw;
-        unit += ((s.V + th - 1) / th) * d.tiles_h;
+        const int tile_rows = (s.V + th - 1) / th;
+        unit += tile_rows * d.tiles_h;
+        d.sup_base = sup; d.sup_w = (d.tiles_h + kSuperTiles - 1) / kSuperTiles;
+        sup += d.sup_w * ((tile_rows + kSuperTiles - 1) / kSuperTiles);
     }
     c->h_sensors_b = c->h_sensors;
     for (size_t i = 0; i < ns; ++i) {
@@ -882,7 +889,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     // per-tile entry lists (k_tile_entries): worth their launch from a few thousand 32-ray tiles on
     if (mode >= 6 && c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units) {
         const int cap = c->opt_tile_entries;
-        const int max_visits = c->opt_tile_visits > 0 ? c->opt_tile_visits : 4 * cap;
+        const int max_visits = c->opt_tile_visits > 0 ? c->opt_tile_visits : (16 * cap) / 5;
         P.tile_cap = cap;
         const bool stale = c->tile_commit_epoch != c->commit_epoch || c->tile_sensors_epoch != c->sensors_epoch || c->tile_first != first ||
                            c->tile_count != count || c->tile_cap != cap || c->tile_visits != max_visits;
@@ -893,9 +900,48 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         P.tile_lists = c->d_tile_lists.as<float4>();
         P.tile_counts = c->d_tile_counts.as<uint8_t>();
         tile_timed = false;
+        // supertiles of the traced sensors: [sup_base(first), sup_base(last) + supertiles(last))
+        const SensorDev &hs_last = c->h_sensors[first + count - 1];
+        const int last_rows = (hs_last.V + (32 >> c->opt_tile_w_log2) - 1) / (32 >> c->opt_tile_w_log2);
+        const int sup_lo = c->h_sensors[first].sup_base;
+        const int sup_hi = hs_last.sup_base + hs_last.sup_w * ((last_rows + kSuperTiles - 1) / kSuperTiles);
+        {
+            const int wf = P.world_frame ? 1 : 0;
+            const bool iv_stale = c->iv_sensors_epoch != c->sensors_epoch || c->iv_first != first || c->iv_count != count || c->iv_world != wf ||
+                                  c->iv_super != c->opt_super_tiles;
+            if (iv_stale) {
+                LSB_CU(c, c->d_tile_iv.reserve((size_t)n_units * 2 * sizeof(float4), st));
+                if (c->opt_super_tiles) LSB_CU(c, c->d_sup_iv.reserve((size_t)sup_hi * 2 * sizeof(float4), st));
+            }
+            P.tile_iv = c->d_tile_iv.as<float4>();
+            P.sup_iv = c->opt_super_tiles ? c->d_sup_iv.as<float4>() : nullptr;
+            if (iv_stale) {
+                k_tile_intervals<<<(unsigned)((n_units + 127) / 128), 128, 0, st>>>(P);
+                count_launch(c);
+                if (c->opt_super_tiles) {
+                    k_super_intervals<<<(unsigned)((sup_hi - sup_lo + 3) / 4), 128, 0, st>>>(P, first, count, sup_lo, sup_hi);
+                    count_launch(c);
+                }
+                c->iv_sensors_epoch = c->sensors_epoch; c->iv_first = first; c->iv_count = count; c->iv_world = wf; c->iv_super = c->opt_super_tiles;
+            }
+        }
+        if (c->opt_super_tiles) {
+            if (stale || c->opt_stats) {
+                LSB_CU(c, c->d_sup_lists.reserve((size_t)sup_hi * kMaxTileEntries * 2 * sizeof(float4), st));
+                LSB_CU(c, c->d_sup_counts.reserve((size_t)sup_hi, st));
+            }
+            P.sup_lists = c->d_sup_lists.as<float4>();
+            P.sup_counts = c->d_sup_counts.as<uint8_t>();
+        }
         if (stale || c->opt_stats) {
             const unsigned blocks = (unsigned)((n_units + 127) / 128);
             if (timing) { cudaEventRecord(c->ev[11], st); tile_timed = true; }
+            if (c->opt_super_tiles) {
+                const unsigned sblocks = (unsigned)((sup_hi - sup_lo + 127) / 128);
+                if (c->opt_stats) k_super_entries<true><<<sblocks, 128, 0, st>>>(P, first, count, sup_lo, sup_hi, 8 * kMaxTileEntries);
+                else k_super_entries<false><<<sblocks, 128, 0, st>>>(P, first, count, sup_lo, sup_hi, 8 * kMaxTileEntries);
+                count_launch(c);
+            }
             if (c->opt_stats) k_tile_entries<true><<<blocks, 128, 0, st>>>(P, max_visits);
             else k_tile_entries<false><<<blocks, 128, 0, st>>>(P, max_visits);
             count_launch(c);

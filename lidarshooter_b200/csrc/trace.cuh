@@ -46,13 +46,17 @@ struct TraceParams {
     float4 *tile_lists;           // [queue slot][tile_cap][2] per-TILE entry lists (k_tile_entries); nullptr = off
     uint8_t *tile_counts;         // [queue slot] entries of the tile's list; kTileFallback = use the sensor's origin chain
     int tile_cap;                 // entries per tile list (<= kMaxTileEntries)
+    float4 *sup_lists;            // [supertile][kMaxTileEntries][2] entry lists of the supertiles (k_super_entries); nullptr = off
+    uint8_t *sup_counts;          // [supertile] entries, or kTileFallback
+    float4 *tile_iv;              // [queue slot][2] direction interval of the tile: (dlo.xyz, class), (dhi.xyz, max |origin|)
+    float4 *sup_iv;               // [supertile][2] same for the supertiles.  Both depend on the sensor tables / poses only.
 };
 constexpr int kMaxTileEntries = 16;
 constexpr int kTileFallback = 0xFF;
 
 // Instrumented (STATS) launches accumulate these per-launch totals (lsb200_get_trace_counters).
 enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUniform, kCntUnitsMixed, kCntMaxStack, kCntHits, kCntCulled, kCntChainTests,
-                    kCntTileVisits, kCntTileEntries, kCntTileFallbacks, kCntTileEmpty, kCntCount };
+                    kCntTileVisits, kCntTileEntries, kCntTileFallbacks, kCntTileEmpty, kCntSuperVisits, kCntCount };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -916,11 +920,15 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
 // Every ray of a LiDAR starts at the same point, so the 32 rays of a work unit (a tile of 8 azimuth steps x 4
 // channels, about 0.8 x 1.2 degrees) form a thin pyramid with its apex at the sensor: they walk almost the same
 // root-to-leaf path, 32 times.  k_tile_entries walks that shared part ONCE per tile (one THREAD per tile): a
-// near-first depth-first descent from the sensor's origin chain in which a box is entered when the tile's
-// direction interval can reach it, until `tile_cap` subtrees / leaves are listed.  The rays of the tile then test
-// the <= tile_cap listed boxes (32 bytes each, no divergence) instead of descending ~17 levels each, and seed their
-// stacks with the ones they enter (trace_ray_ww) -- near part of the pyramid resolved down to leaves, far part
-// left coarse (it is dropped unloaded once a closer hit is known).
+// near-first depth-first descent in which a box is entered when the tile's direction interval can reach it, until
+// `tile_cap` subtrees / leaves are listed.  The rays of the tile then test the <= tile_cap listed boxes (32 bytes
+// each, no divergence) instead of descending ~17 levels each (trace_ray_lz) -- near part of the pyramid resolved
+// down to leaves, far part left coarse (it fails its box test once a closer hit is known).
+//
+// Two levels: the walk of a tile does not start from its sensor's origin chain but from the list of its SUPERTILE
+// (4 x 4 tiles = 32 azimuth steps x 16 channels, k_super_entries, one thread per supertile, same walk with a wider
+// interval and 16 entries): the ~15 levels between the chain's big sibling subtrees and the neighbourhood of the
+// pyramid are descended once per 16 tiles instead of once per tile.
 //
 // Tile test = interval form of the ray's own slab test.  For a sign-uniform tile |1/d| of axis k lies in
 // [imin_k, imax_k]; entry distances are bounded from below with imin, exit distances from above with imax:
@@ -929,109 +937,175 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
 // rays' padding and the interval is widened by 1e-6, far above the rounding noise of either form).  The union of
 // the listed subtrees therefore covers everything any ray of the tile can hit, and closest hit = min (t, triangle
 // id) does not depend on how the tree was cut: per-ray results are unchanged (tests: every variant bit-identical).
-// Sign-mixed tiles (class 8, ~4 % of a 128 x 3601 table) and tiles whose interval touches 0 keep the sensor chain.
-template <bool STATS>
-__global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_visits)
-{
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    int begin8 = 0;                                    // first slot of class 8 = number of sign-uniform units
-#pragma unroll
-    for (int o = 0; o < 8; ++o) begin8 += (int)__ldg(P.oct_hist + o);
-    const int total = begin8 + (int)__ldg(P.oct_hist + 8);
-    if (slot >= total) return;
-    if (slot >= begin8) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
-    int cls = 0, acc = 0;
-#pragma unroll
-    for (int o = 0; o < 8; ++o) { acc += (int)__ldg(P.oct_hist + o); if (slot >= acc) cls = o + 1; }
+// Sign-mixed tiles (class 8, ~4 % of a 128 x 3601 table) and tiles whose interval touches 0 keep the sensor chain;
+// tiles of a sign-mixed supertile start from the chain as before.
+constexpr int kSuperTiles = 4;          // a supertile is kSuperTiles x kSuperTiles tiles
 
-    const int4 ud = __ldg(P.unit_list + slot);
-    const SensorDev &S = P.sensors[ud.x];
-    // direction interval of the tile's rays (exactly the rays the traversal generates)
-    float dlo[3] = {INFINITY, INFINITY, INFINITY}, dhi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    float ox = 0.0f, oy = 0.0f, oz = 0.0f, omax = 0.0f;
-    {
-        // the tile's rays, generated with the traversal's own arithmetic; the tables are read once per row / column
-        const int tw = 1 << P.tile_w_log2, th = 32 >> P.tile_w_log2;
-        float stv[4], ctv[4];
-#pragma unroll
-        for (int a = 0; a < 4; ++a) {
-            const int v = min(ud.y + a, S.V - 1);
-            stv[a] = __ldg(S.sin_t + v); ctv[a] = __ldg(S.cos_t + v);
-        }
-        for (int b = 0; b < tw; ++b) {
-            const int h = ud.z + b;
-            if (h >= S.H) break;
-            const float sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
-            auto one = [&](float st, float ct) {
-                Ray r; float x, y, z;
-                ray_from_tables(S, P.world_frame, st, ct, sp_, cp, r, x, y, z, omax);
-                ox = r.ox; oy = r.oy; oz = r.oz;
-                dlo[0] = fminf(dlo[0], r.dx); dhi[0] = fmaxf(dhi[0], r.dx);
-                dlo[1] = fminf(dlo[1], r.dy); dhi[1] = fmaxf(dhi[1], r.dy);
-                dlo[2] = fminf(dlo[2], r.dz); dhi[2] = fmaxf(dhi[2], r.dz);
-            };
-            if (th <= 4) {
-#pragma unroll
-                for (int a = 0; a < 4; ++a) if (a < th && ud.y + a < S.V) one(stv[a], ctv[a]);
-            } else {
-                for (int a = 0; a < th && ud.y + a < S.V; ++a) one(__ldg(S.sin_t + ud.y + a), __ldg(S.cos_t + ud.y + a));
-            }
-        }
-    }
-    float smax = 0.0f;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
-    const float eps = 1.5f * (8e-6f * (smax + omax) + 1e-30f);
-    const float o3[3] = {ox, oy, oz};
-    float in[3], an[3], ifr[3], af[3];
+// Direction interval of a block of rays -> the constants of the interval slab test.
+struct TileFrustum {
     bool neg[3];
-    bool ok = true;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        neg[k] = ((cls >> k) & 1) != 0;
-        const float amin = neg[k] ? -dhi[k] : dlo[k], amax = neg[k] ? -dlo[k] : dhi[k];     // |d| interval
-        if (!(amin > 1e-6f)) ok = false;                                                     // touches 0 (or no valid ray)
-        const float in_abs = (1.0f / amax) * 0.999999f, if_abs = (1.0f / fmaxf(amin, 1e-6f)) * 1.000001f;
-        in[k] = neg[k] ? -in_abs : in_abs;
-        ifr[k] = neg[k] ? -if_abs : if_abs;
-        an[k] = -o3[k] * in[k] - eps * in_abs;
-        af[k] = -o3[k] * ifr[k] + eps * if_abs;
-    }
-    if (!ok) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
-    const float max_range = S.max_range;
-    // box = (lo.x, hi.x, lo.y, hi.y), (lo.z, hi.z): can a ray of the tile enter it, and not before which distance
-    auto tile_test = [&](const float4 bxy, float bzlo, float bzhi, float &n) -> bool {
+    float in[3], an[3], ifr[3], af[3];
+    float max_range;
+    // box = (lo.x, hi.x, lo.y, hi.y), (lo.z, hi.z): can a ray of the block enter it, and not before which distance
+    __device__ __forceinline__ bool test(const float4 bxy, float bzlo, float bzhi, float &n) const
+    {
         const float nx = fmaf(neg[0] ? bxy.y : bxy.x, in[0], an[0]), fx = fmaf(neg[0] ? bxy.x : bxy.y, ifr[0], af[0]);
         const float ny = fmaf(neg[1] ? bxy.w : bxy.z, in[1], an[1]), fy = fmaf(neg[1] ? bxy.z : bxy.w, ifr[1], af[1]);
         const float nz = fmaf(neg[2] ? bzhi : bzlo, in[2], an[2]), fz = fmaf(neg[2] ? bzlo : bzhi, ifr[2], af[2]);
         n = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
         const float f = fminf(fminf(fx, fy), fz);
         return n <= f && n <= max_range;
-    };
+    }
+};
 
-    const int cap = P.tile_cap;
-    // deferred entries: (ref, entry distance, where the box is stored): side 0 / 1 = child slot of node `from`,
-    // side 2 = entry `from` of the sensor's chain.  16 bytes per push / pop; the box itself (24 bytes) is only
-    // re-read when a popped entry is listed without having been split.
-    int4 stk[kMaxTileEntries];
-    int sp = 0;
-    const int list = ud.x * 9 + cls;
-    const float4 *chain = P.chains + (size_t)list * (2 * kMaxChain);
-    {
-        const int n_chain = __ldg(P.chain_counts + list);
-        for (int k = 0; k < n_chain; ++k) {                       // far -> near: the nearest chain entry ends on top
-            const float4 e0 = __ldg(chain + 2 * k), e1 = __ldg(chain + 2 * k + 1);
-            float n;
-            if (!tile_test(e0, e1.x, e1.y, n)) continue;
-            if (sp == cap) { ok = false; break; }
-            stk[sp++] = make_int4(__float_as_int(e1.z), __float_as_int(n), k, 2);
+// Rays (channels [v0, v0 + nv) x azimuth steps [h0, h0 + nh)) of sensor S, generated with the traversal's own
+// arithmetic: their direction interval and origin.  Returns the common sign class (bit k = component k negative) or
+// 8 when the signs differ.  The tables are read once per row / column.
+__device__ __forceinline__ int block_interval(const SensorDev &S, int world_frame, int v0, int nv, int h0, int nh,
+                                              float dlo[3], float dhi[3], float o3[3], float &omax)
+{
+    dlo[0] = dlo[1] = dlo[2] = INFINITY; dhi[0] = dhi[1] = dhi[2] = -INFINITY;
+    o3[0] = o3[1] = o3[2] = 0.0f; omax = 0.0f;
+    unsigned sign_or = 0u, sign_and = 7u;
+    const int v1 = min(v0 + nv, S.V), h1 = min(h0 + nh, S.H);
+    auto one = [&](float st, float ct, float sp_, float cp) {
+        Ray r; float x, y, z;
+        ray_from_tables(S, world_frame, st, ct, sp_, cp, r, x, y, z, omax);
+        o3[0] = r.ox; o3[1] = r.oy; o3[2] = r.oz;
+        dlo[0] = fminf(dlo[0], r.dx); dhi[0] = fmaxf(dhi[0], r.dx);
+        dlo[1] = fminf(dlo[1], r.dy); dhi[1] = fmaxf(dhi[1], r.dy);
+        dlo[2] = fminf(dlo[2], r.dz); dhi[2] = fmaxf(dhi[2], r.dz);
+        const unsigned o = (unsigned)ray_octant(r);
+        sign_or |= o; sign_and &= o;
+    };
+    if (nv <= 4) {
+        float stv[4], ctv[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int v = min(v0 + a, S.V - 1);
+            stv[a] = __ldg(S.sin_t + v); ctv[a] = __ldg(S.cos_t + v);
+        }
+        for (int h = h0; h < h1; ++h) {
+            const float sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
+#pragma unroll
+            for (int a = 0; a < 4; ++a) if (a < nv && v0 + a < S.V) one(stv[a], ctv[a], sp_, cp);
+        }
+    } else {
+        for (int v = v0; v < v1; ++v) {
+            const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v);
+            for (int h = h0; h < h1; ++h) one(st, ct, __ldg(S.sin_p + h), __ldg(S.cos_p + h));
         }
     }
-    if (!ok) { P.tile_counts[slot] = (uint8_t)kTileFallback; if (STATS) atomicAdd(P.counters + kCntTileFallbacks, 1ull); return; }
-    float4 *out = P.tile_lists + (size_t)slot * (2 * cap);
-    int n_out = 0, visits = 0;
-    // One flat loop (a step = list the entry in hand, or split it): the lanes of a warp -- neighbouring tiles -- stay
-    // in step instead of serialising an outer pop loop against an inner descent loop.
+    return sign_or == sign_and ? (int)sign_or : 8;
+}
+
+// false: the interval touches 0 on some axis (or holds no ray) -- no interval test for this block
+__device__ __forceinline__ bool make_frustum(const float dlo[3], const float dhi[3], const float o3[3], int cls, float eps,
+                                             float max_range, TileFrustum &F)
+{
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        F.neg[k] = ((cls >> k) & 1) != 0;
+        const float amin = F.neg[k] ? -dhi[k] : dlo[k], amax = F.neg[k] ? -dlo[k] : dhi[k];     // |d| interval
+        if (!(amin > 1e-6f)) ok = false;
+        const float in_abs = (1.0f / amax) * 0.999999f, if_abs = (1.0f / fmaxf(amin, 1e-6f)) * 1.000001f;
+        F.in[k] = F.neg[k] ? -in_abs : in_abs;
+        F.ifr[k] = F.neg[k] ? -if_abs : if_abs;
+        F.an[k] = -o3[k] * F.in[k] - eps * in_abs;
+        F.af[k] = -o3[k] * F.ifr[k] + eps * if_abs;
+    }
+    F.max_range = max_range;
+    return ok;
+}
+
+__device__ __forceinline__ int find_sensor_by_super(const SensorDev *s, int lo, int hi, int sup)
+{
+    while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (s[mid].sup_base <= sup) lo = mid; else hi = mid - 1; }
+    return lo;
+}
+
+// Direction intervals depend on the sensor tables and poses only (not on the scene): computed when those change and
+// kept.  Tiles: one thread per queue entry.  Supertiles (512 rays): one WARP per supertile, a lane per azimuth
+// column, intervals merged with shuffles.
+__global__ void __launch_bounds__(128) k_tile_intervals(TraceParams P)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    int total = 0;
+#pragma unroll
+    for (int o = 0; o < 9; ++o) total += (int)__ldg(P.oct_hist + o);
+    if (slot >= total) return;
+    const int4 ud = __ldg(P.unit_list + slot);
+    const SensorDev &S = P.sensors[ud.x];
+    const int tw = 1 << P.tile_w_log2, th = 32 >> P.tile_w_log2;
+    float dlo[3], dhi[3], o3[3], omax;
+    const int cls = block_interval(S, P.world_frame, ud.y, th, ud.z, tw, dlo, dhi, o3, omax);
+    P.tile_iv[2 * (size_t)slot] = make_float4(dlo[0], dlo[1], dlo[2], __int_as_float(cls));
+    P.tile_iv[2 * (size_t)slot + 1] = make_float4(dhi[0], dhi[1], dhi[2], omax);
+}
+
+__global__ void __launch_bounds__(128) k_super_intervals(TraceParams P, int s_first, int s_count, int sup_lo, int sup_hi)
+{
+    const int sup = sup_lo + (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (sup >= sup_hi) return;                                   // whole warps leave together
+    const unsigned lane = lane_id();
+    const int si = find_sensor_by_super(P.sensors, s_first, s_first + s_count - 1, sup);
+    const SensorDev &S = P.sensors[si];
+    const int local = sup - S.sup_base;
+    const int sv = local / S.sup_w, sh = local - sv * S.sup_w;
+    const int tw = 1 << P.tile_w_log2, th = 32 >> P.tile_w_log2;
+    const int v0 = sv * kSuperTiles * th, nv = kSuperTiles * th, h0 = sh * kSuperTiles * tw, nh = kSuperTiles * tw;
+    float dlo[3] = {INFINITY, INFINITY, INFINITY}, dhi[3] = {-INFINITY, -INFINITY, -INFINITY}, o3[3] = {0.f, 0.f, 0.f}, omax = 0.0f;
+    unsigned sign_or = 0u, sign_and = 7u;
+    for (int h = h0 + (int)lane; h < min(h0 + nh, S.H); h += 32) {
+        float lo[3], hi[3], om;
+        const int c = block_interval(S, P.world_frame, v0, nv, h, 1, lo, hi, o3, om);
+        omax = om;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { dlo[k] = fminf(dlo[k], lo[k]); dhi[k] = fmaxf(dhi[k], hi[k]); }
+        if (c == 8) { sign_or = 7u; sign_and = 0u; }
+        else { sign_or |= (unsigned)c; sign_and &= (unsigned)c; }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            dlo[k] = fminf(dlo[k], __shfl_xor_sync(0xffffffffu, dlo[k], off));
+            dhi[k] = fmaxf(dhi[k], __shfl_xor_sync(0xffffffffu, dhi[k], off));
+        }
+        omax = fmaxf(omax, __shfl_xor_sync(0xffffffffu, omax, off));
+        sign_or |= __shfl_xor_sync(0xffffffffu, sign_or, off);
+        sign_and &= __shfl_xor_sync(0xffffffffu, sign_and, off);
+    }
+    if (lane == 0) {
+        const int cls = sign_or == sign_and ? (int)sign_or : 8;
+        P.sup_iv[2 * (size_t)sup] = make_float4(dlo[0], dlo[1], dlo[2], __int_as_float(cls));
+        P.sup_iv[2 * (size_t)sup + 1] = make_float4(dhi[0], dhi[1], dhi[2], omax);
+    }
+}
+
+// The walk: seeds (a list of (box, reference) entries -- the sensor's origin chain, far -> near, or the supertile's
+// list, near -> far) are filtered with the block's interval test, then refined near-first until `cap` entries are
+// listed.  Returns the number of entries written to `out` (near -> far), or -1 when more than `cap` seeds pass.
+// Deferred entries are 16 bytes: (reference, entry distance, where the box is stored); side 0 / 1 = child slot of
+// node `from`, side 2 = seed `from`.  The box itself (24 bytes) is only re-read when a popped entry is listed
+// without having been split.  One flat loop (a step = list the entry in hand, or split it): the lanes of a warp --
+// neighbouring blocks -- stay in step instead of serialising an outer pop loop against an inner descent loop.
+__device__ __forceinline__ int frustum_walk(const float4 *__restrict__ nodes, const TileFrustum &F, const float4 *__restrict__ seeds,
+                                            int n_seeds, bool seeds_near_first, int cap, int max_visits, float4 *__restrict__ out,
+                                            int &visits)
+{
+    int4 stk[kMaxTileEntries];
+    int sp = 0;
+    for (int q = 0; q < n_seeds; ++q) {                          // far -> near: the nearest seed ends on top
+        const int k = seeds_near_first ? n_seeds - 1 - q : q;
+        const float4 e0 = __ldg(seeds + 2 * k), e1 = __ldg(seeds + 2 * k + 1);
+        float n;
+        if (!F.test(e0, e1.x, e1.y, n)) continue;
+        if (sp == cap) return -1;
+        stk[sp++] = make_int4(__float_as_int(e1.z), __float_as_int(n), k, 2);
+    }
+    int n_out = 0;
     int4 cur = make_int4(0, 0, 0, 0);
     float4 cxy = make_float4(0.f, 0.f, 0.f, 0.f);
     float2 cz = make_float2(0.f, 0.f);
@@ -1043,10 +1117,10 @@ __global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_vis
         if (cur.x < 0 || n_out + sp + 2 > cap || visits >= max_visits) {
             if (!have_box) {
                 if (cur.w == 2) {
-                    const float4 e1 = __ldg(chain + 2 * cur.z + 1);
-                    cxy = __ldg(chain + 2 * cur.z); cz = make_float2(e1.x, e1.y);
+                    const float4 e1 = __ldg(seeds + 2 * cur.z + 1);
+                    cxy = __ldg(seeds + 2 * cur.z); cz = make_float2(e1.x, e1.y);
                 } else {
-                    const float4 *nd = P.nodes + 4 * (size_t)cur.z;
+                    const float4 *nd = nodes + 4 * (size_t)cur.z;
                     cxy = __ldg(nd + cur.w);
                     cz = __ldg(reinterpret_cast<const float2 *>(nd + 2) + cur.w);
                 }
@@ -1056,12 +1130,12 @@ __global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_vis
             pop = true;
         } else {
             const int node = cur.x;
-            const float4 *nd = P.nodes + 4 * (size_t)node;
+            const float4 *nd = nodes + 4 * (size_t)node;
             const float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2);
             const float2 q3 = __ldg(reinterpret_cast<const float2 *>(nd + 3));
             ++visits;
             float n0, n1;
-            const bool h0 = tile_test(q0, q2.x, q2.y, n0), h1 = tile_test(q1, q2.z, q2.w, n1);
+            const bool h0 = F.test(q0, q2.x, q2.y, n0), h1 = F.test(q1, q2.z, q2.w, n1);
             const bool first1 = h1 && (!h0 || n1 < n0);              // continue with child 1 (the nearer, or the only one)
             if (h0 && h1)                                            // defer the farther child
                 stk[sp++] = first1 ? make_int4(__float_as_int(q3.x), __float_as_int(n0), node, 0)
@@ -1078,11 +1152,95 @@ __global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_vis
             if (have) cur = stk[--sp];
         }
     }
-    P.tile_counts[slot] = (uint8_t)n_out;
+    return n_out;
+}
+
+__device__ __forceinline__ float scene_smax(const uint32_t *__restrict__ bounds)
+{
+    float smax = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(bounds + k))));
+    return smax;
+}
+
+// One thread per supertile of the traced sensors [s_first, s_first + s_count): list of <= kMaxTileEntries entries from
+// the sensor's origin chain.  sup_counts: entries, or kTileFallback (sign-mixed block / interval touching 0 / too
+// many seeds).
+template <bool STATS>
+__global__ void __launch_bounds__(128) k_super_entries(TraceParams P, int s_first, int s_count, int sup_lo, int sup_hi, int max_visits)
+{
+    const int sup = sup_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (sup >= sup_hi) return;
+    const int si = find_sensor_by_super(P.sensors, s_first, s_first + s_count - 1, sup);
+    const SensorDev &S = P.sensors[si];
+    const int local = sup - S.sup_base;
+    const float4 iv0 = __ldg(P.sup_iv + 2 * (size_t)sup), iv1 = __ldg(P.sup_iv + 2 * (size_t)sup + 1);
+    const float dlo[3] = {iv0.x, iv0.y, iv0.z}, dhi[3] = {iv1.x, iv1.y, iv1.z};
+    const int cls = __float_as_int(iv0.w);
+    const float omax = iv1.w;
+    const float o3[3] = {P.world_frame ? S.T[0] : 0.0f, P.world_frame ? S.T[1] : 0.0f, P.world_frame ? S.T[2] : 0.0f};
+    TileFrustum F;
+    const float eps = 1.5f * (8e-6f * (scene_smax(P.bounds) + omax) + 1e-30f);
+    int n_out = -1, visits = 0;
+    if (cls < 8 && make_frustum(dlo, dhi, o3, cls, eps, S.max_range, F)) {
+        const int list = si * 9 + cls;
+        n_out = frustum_walk(P.nodes, F, P.chains + (size_t)list * (2 * kMaxChain), __ldg(P.chain_counts + list), false,
+                             kMaxTileEntries, max_visits, P.sup_lists + (size_t)sup * (2 * kMaxTileEntries), visits);
+    }
+    P.sup_counts[sup] = (uint8_t)(n_out < 0 ? kTileFallback : n_out);
+    if (STATS) atomicAdd(P.counters + kCntSuperVisits, (unsigned long long)visits);
+}
+
+// One thread per queue entry (32-ray tile).  tile_counts: entries, or kTileFallback.
+template <bool STATS>
+__global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_visits)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    int begin8 = 0;                                    // first slot of class 8 = number of sign-uniform units
+#pragma unroll
+    for (int o = 0; o < 8; ++o) begin8 += (int)__ldg(P.oct_hist + o);
+    const int total = begin8 + (int)__ldg(P.oct_hist + 8);
+    if (slot >= total) return;
+    if (slot >= begin8) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
+    int cls = 0, acc = 0;
+#pragma unroll
+    for (int o = 0; o < 8; ++o) { acc += (int)__ldg(P.oct_hist + o); if (slot >= acc) cls = o + 1; }
+
+    const int4 ud = __ldg(P.unit_list + slot);
+    const SensorDev &S = P.sensors[ud.x];
+    const int tw = 1 << P.tile_w_log2, th = 32 >> P.tile_w_log2;
+    const float4 iv0 = __ldg(P.tile_iv + 2 * (size_t)slot), iv1 = __ldg(P.tile_iv + 2 * (size_t)slot + 1);
+    const float dlo[3] = {iv0.x, iv0.y, iv0.z}, dhi[3] = {iv1.x, iv1.y, iv1.z};
+    const float omax = iv1.w;
+    const float o3[3] = {P.world_frame ? S.T[0] : 0.0f, P.world_frame ? S.T[1] : 0.0f, P.world_frame ? S.T[2] : 0.0f};
+    TileFrustum F;
+    const float eps = 1.5f * (8e-6f * (scene_smax(P.bounds) + omax) + 1e-30f);
+    if (!make_frustum(dlo, dhi, o3, cls, eps, S.max_range, F)) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
+
+    // seeds: the supertile's list when it has one, else the sensor's origin chain
+    const int list = ud.x * 9 + cls;
+    const float4 *seeds = P.chains + (size_t)list * (2 * kMaxChain);
+    int n_seeds = __ldg(P.chain_counts + list);
+    bool near_first = false;
+    if (P.sup_counts != nullptr) {
+        const int sup = S.sup_base + ((ud.y / th) / kSuperTiles) * S.sup_w + (ud.z / tw) / kSuperTiles;
+        const int sc = (int)__ldg(P.sup_counts + sup);
+        if (sc != kTileFallback) { seeds = P.sup_lists + (size_t)sup * (2 * kMaxTileEntries); n_seeds = sc; near_first = true; }
+    }
+    int visits = 0;
+    int n_out = frustum_walk(P.nodes, F, seeds, n_seeds, near_first, P.tile_cap, max_visits,
+                             P.tile_lists + (size_t)slot * (2 * P.tile_cap), visits);
+    if (n_out < 0 && near_first)            // more supertile entries pass than the list holds: start from the chain instead
+        n_out = frustum_walk(P.nodes, F, P.chains + (size_t)list * (2 * kMaxChain), __ldg(P.chain_counts + list), false, P.tile_cap,
+                             max_visits, P.tile_lists + (size_t)slot * (2 * P.tile_cap), visits);
+    P.tile_counts[slot] = (uint8_t)(n_out < 0 ? kTileFallback : n_out);
     if (STATS) {
         atomicAdd(P.counters + kCntTileVisits, (unsigned long long)visits);
-        atomicAdd(P.counters + kCntTileEntries, (unsigned long long)n_out);
-        if (n_out == 0) atomicAdd(P.counters + kCntTileEmpty, 1ull);
+        if (n_out < 0) atomicAdd(P.counters + kCntTileFallbacks, 1ull);
+        else {
+            atomicAdd(P.counters + kCntTileEntries, (unsigned long long)n_out);
+            if (n_out == 0) atomicAdd(P.counters + kCntTileEmpty, 1ull);
+        }
     }
 }
 

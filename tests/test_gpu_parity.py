@@ -452,8 +452,9 @@ def test_tile_entry_lists_xt32_golden(meshes, golden, entries, leaf, tile):
     ctx.close()
 
 
+@pytest.mark.parametrize("super_tiles", [1, 0])
 @pytest.mark.parametrize("entries,visits", [(2, 0), (6, 3), (10, 0), (16, 1000)])
-def test_tile_entry_lists_small_city_vs_oracle_bvh(entries, visits):
+def test_tile_entry_lists_small_city_vs_oracle_bvh(entries, visits, super_tiles):
     """World frame, 4 yawed sensors in a small city: tile lists of every size bit-exact against the oracle's CPU BVH,
     after a rebuild and after a refit (the lists are rebuilt with the tree), with a detection radius and an azimuth
     window (entries beyond the radius are dropped by the tile walk)."""
@@ -464,6 +465,7 @@ def test_tile_entry_lists_small_city_vs_oracle_bvh(entries, visits):
     ctx.set_option(capi.OPT_TILE_ENTRIES, entries)
     ctx.set_option(capi.OPT_TILE_VISITS, visits)
     ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
+    ctx.set_option(capi.OPT_SUPER_TILES, super_tiles)
     for k, (q, t) in enumerate(poses):
         ctx.set_sensor(elev, b, e, H, q, t, index=k)
     A = [IDENT.copy() for _ in meshes]
@@ -530,12 +532,13 @@ def test_city_10m_size_independent_properties():
             assert np.array_equal(res[mode][k][0], res[0][k][0]) and np.array_equal(res[mode][k][1], res[0][k][1])
     # variant 6 with the per-tile entry lists off and at other list sizes
     ctx.set_option(capi.OPT_TRAVERSAL, 6)
-    for entries in (0, 4, 10):
+    for entries, sup in ((0, 1), (4, 1), (10, 0), (16, 1)):
         ctx.set_option(capi.OPT_TILE_ENTRIES, entries)
+        ctx.set_option(capi.OPT_SUPER_TILES, sup)
         for k in range(len(pick)):
             rc, t, tri = ctx.trace_raw(k)
             assert np.array_equal(t, res[0][k][0]) and np.array_equal(tri, res[0][k][1])
-    ctx.set_option(capi.OPT_TILE_ENTRIES, 16)
+    ctx.set_option(capi.OPT_TILE_ENTRIES, 10)
     assert ctx.commit_scene(capi.COMMIT_REFIT) == 0 and ctx.stats().last_commit_was_rebuild == 0
     for k in range(len(pick)):
         rc, t, tri = ctx.trace_raw(k)

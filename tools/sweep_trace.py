@@ -30,7 +30,8 @@ def main():
     ap.add_argument("--tiles", default="8")
     ap.add_argument("--layouts", default="0")
     ap.add_argument("--tile-entries", default="16", help="per-tile entry list sizes (0 = off)")
-    ap.add_argument("--tile-visits", default="0", help="node visits per tile list (0 = 4 x entries)")
+    ap.add_argument("--tile-visits", default="0", help="node visits per tile list (0 = default)")
+    ap.add_argument("--super", default="1", help="two-level lists (supertiles) on / off")
     ap.add_argument("--aspects", default="50")
     ap.add_argument("--scene", default="city", choices=["city", "heightfield"])
     args = ap.parse_args()
@@ -71,8 +72,10 @@ def main():
                             ("transform", "morton", "sort", "hierarchy", "fit", "toplevel")}
                 for mode, chain, tile, te, tv in [(int(x), int(y), int(z), int(u), int(w)) for x in args.modes.split(",") for y in args.chain.split(",")
                                                   for z in args.tiles.split(",") for u in args.tile_entries.split(",") for w in args.tile_visits.split(",")]:
+                  for sup in [int(x) for x in args.super.split(",")]:
                     ctx.set_option(capi.OPT_TRAVERSAL, mode)
                     ctx.set_option(capi.OPT_TILE_VISITS, tv)
+                    ctx.set_option(capi.OPT_SUPER_TILES, sup)
                     ctx.set_option(capi.OPT_ORIGIN_CHAIN, chain)
                     ctx.set_option(capi.OPT_TILE_WIDTH, tile)
                     ctx.set_option(capi.OPT_TRACE_STATS, 0)
@@ -94,7 +97,7 @@ def main():
                     if base_sig is None:
                         base_sig = sig
                     rays = max(cnt["rays"], 1)
-                    row = {"morton_uniform": mu, "morton_layout": layout, "morton_aspect": aspect, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "tile_w": tile, "tile_entries": te, "tile_visits": tv,
+                    row = {"morton_uniform": mu, "morton_layout": layout, "morton_aspect": aspect, "leaf": leaf, "top": top, "mode": mode, "chain": chain, "tile_w": tile, "tile_entries": te, "tile_visits": tv, "super_tiles": sup, "super_visits_per_tile": cnt["super_visits"] / max(cnt["units_uniform"], 1),
                            "tile_visits_per_tile": cnt["tile_visits"] / max(cnt["units_uniform"], 1), "tile_entries_per_tile": cnt["tile_entries"] / max(cnt["units_uniform"], 1),
                            "tile_fallbacks": cnt["tile_fallbacks"], "tile_empty": cnt["tile_empty"], "chain_tests_per_ray": cnt["chain_tests"] / rays,
                            "ms_trace_min": min(ms), "ms_trace_mean": float(np.mean(ms)),
