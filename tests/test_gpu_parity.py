@@ -259,14 +259,18 @@ def test_small_build_equals_pipeline(n_tris):
     assert n_tris < 100 or (a[4] >= 0).sum() > 0
 
 
+@pytest.mark.parametrize("lists", ["default", "tile", "tile+super"])
 @pytest.mark.parametrize("n_tris", [1, 2, 3, 5, 1000, 20000])
-def test_random_soup_vs_brute(n_tris):
+def test_random_soup_vs_brute(n_tris, lists):
     rng = np.random.default_rng(n_tris)
     c = rng.uniform(-20, 20, (n_tris, 1, 3)).astype(np.float32)
     v = (c + rng.normal(0, 0.7, (n_tris, 3, 3)).astype(np.float32)).reshape(-1, 3)
     tr = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
     elev = np.linspace(80, -80, 64).astype(np.float32)
     ctx = capi.Context(0)
+    if lists != "default":          # per-tile entry lists forced on for this small table (sensor inside the soup, tiny trees)
+        ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
+        ctx.set_option(capi.OPT_SUPER_TILES, 1 if lists == "tile+super" else 0)
     ctx.set_sensor(elev, 0.0, 360.0, 181, (1, 0, 0, 0), (0, 0, 0))
     add_mesh(ctx, "soup", v, tr)
     assert ctx.commit_scene() == 0
@@ -286,6 +290,10 @@ def test_duplicate_and_degenerate_triangles():
     add_mesh(ctx, "m", v, tr)
     assert ctx.commit_scene() == 0
     rc, t, tri = ctx.trace_raw()
+    ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)          # same answers through the per-tile entry lists
+    ctx.set_option(capi.OPT_SUPER_TILES, 1)
+    rc2, t2, tri2 = ctx.trace_raw()
+    assert rc2 == 0 and np.array_equal(t2, t) and np.array_equal(tri2, tri)
     s = lso.Sensor(np.array([0.0], np.float32), -10.0, 10.0, 21)
     ref = lso.scan(s, [(v, tr, IDENT)], use_bvh=False)
     assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])

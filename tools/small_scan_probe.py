@@ -18,14 +18,17 @@ for name in ("ground", "ben"):
     ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0])
     ctx.update_geometry(name, v, t, ident)
 ctx.set_option(capi.OPT_STAGE_TIMING, 1)
-for mode in (1, 2, 4, 0, 6):
+for mode, min_units in ((1, 4096), (2, 4096), (4, 4096), (0, 4096), (6, 4096), (6, 0), (7, 0)):
     ctx.set_option(capi.OPT_TRAVERSAL, mode)
+    ctx.set_option(capi.OPT_TILE_MIN_UNITS, min_units)       # 0: per-tile entry lists even for the 150 tiles of an XT-32
     ts = []
     for k in range(8):
         assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
         ctx.trace_device(0, 0)
         ts.append(ctx.stats().ms_trace * 1e3)
-    print("mode", mode, "trace us", " ".join("%.1f" % t for t in ts), flush=True)
+    print("mode", mode, "tile lists" if min_units == 0 else "no tile lists", "trace us", " ".join("%.1f" % t for t in ts), flush=True)
+ctx.set_option(capi.OPT_TRAVERSAL, 6)
+ctx.set_option(capi.OPT_TILE_MIN_UNITS, 4096)
 for k in range(3):
     assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
     rc, pts = ctx.trace_scene(0, 0)
