@@ -85,6 +85,29 @@ __device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+#ifndef LSB_NODE_EVICT_LAST
+#define LSB_NODE_EVICT_LAST 1
+#endif
+// L2 eviction priority for the BVH nodes (the results stream through L2 with evict-first stores)
+__device__ __forceinline__ uint64_t l2_policy_evict_last()
+{
+    uint64_t p;
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ float4 ldg_f4_hint(const float4 *a, uint64_t pol)
+{
+    float4 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ float2 ldg_f2_hint(const float2 *a, uint64_t pol)
+{
+    float2 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v2.f32 {%0, %1}, [%2], %3;" : "=f"(v.x), "=f"(v.y) : "l"(a), "l"(pol));
+    return v;
+}
+
 struct Ray {
     float ox, oy, oz, dx, dy, dz;
 };
@@ -126,7 +149,12 @@ __device__ __forceinline__ void test_leaf(const TraceParams &P, int ref, const R
     const int count = (enc >> kLeafShift) + 1;
     for (int k = 0; k < count; ++k) {
         const float4 *rec = P.tris + 3 * (size_t)(first + k);
+#if LSB_NODE_EVICT_LAST >= 2
+        const uint64_t pol = l2_policy_evict_last();
+        const float4 q0 = ldg_f4_hint(rec, pol), q1 = ldg_f4_hint(rec + 1, pol), q2 = ldg_f4_hint(rec + 2, pol);
+#else
         const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2);
+#endif
         const int g = __ldg(P.leaf_ids + first + k);        // with the record: no dependent round trip after a hit
         float t;
         if (intersect_tri(q0, q1, q2, r, t) && t <= best) {
@@ -351,6 +379,9 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
     const float ax = -(r.ox + eps) * ix, ay = -(r.oy + eps) * iy, az = -(r.oz + eps) * iz;
     const float bx = -(r.ox - eps) * ix, by = -(r.oy - eps) * iy, bz = -(r.oz - eps) * iz;
     constexpr int kDone = 0x7fffffff;       // never a node index (n_tris < 2^28)
+#if LSB_NODE_EVICT_LAST
+    const uint64_t pol = l2_policy_evict_last();
+#endif
     float best = INFINITY, far_lim = INFINITY;
     int bi = -1;
     int2 stack[kStackSize];
@@ -375,8 +406,13 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
         }
         while ((unsigned)cur < (unsigned)kDone) {           // cur >= 0 and not kDone: an inner node
             const float4 *n = P.nodes + 4 * (size_t)cur;
+#if LSB_NODE_EVICT_LAST
+            const float4 q0 = ldg_f4_hint(n, pol), q1 = ldg_f4_hint(n + 1, pol), q2 = ldg_f4_hint(n + 2, pol);
+            const float2 q3 = ldg_f2_hint(reinterpret_cast<const float2 *>(n + 3), pol);
+#else
             const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
             const float2 q3 = __ldg(reinterpret_cast<const float2 *>(n + 3));
+#endif
             if (STATS) ++rs.nodes;
             float n0, f0, n1, f1;
             slab_nf<OCT>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
@@ -523,12 +559,13 @@ __device__ __forceinline__ int find_sensor_by_unit(const SensorDev *s, int n, in
 // Writes one hit.  32-byte record (SRC/XYZIRBytes.cpp:24-40) or 16-byte XYZI.
 __device__ __forceinline__ void store_point(uint8_t *points, uint32_t slot, uint32_t flags, float x, float y, float z, int ring)
 {
+    // streaming stores: the 1.2 GB of results per frame should not evict the BVH from L2
     if (flags & 4u /*LSB200_TRACE_XYZI16*/) {
-        reinterpret_cast<float4 *>(points)[slot] = make_float4(x, y, z, 64.0f);
+        __stcs(reinterpret_cast<float4 *>(points) + slot, make_float4(x, y, z, 64.0f));
     } else {
         float4 *p = reinterpret_cast<float4 *>(points) + 2 * (size_t)slot;
-        p[0] = make_float4(x, y, z, 0.0f);
-        p[1] = make_float4(64.0f, __int_as_float(ring), 0.0f, 0.0f);
+        __stcs(p, make_float4(x, y, z, 0.0f));
+        __stcs(p + 1, make_float4(64.0f, __int_as_float(ring), 0.0f, 0.0f));
     }
 }
 
@@ -652,8 +689,8 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
         }
         if (!(best <= S.max_range)) { best = INFINITY; bi = -1; }                // detection radius (closest hit beyond it: no return)
-        S.t_out[ray] = best;
-        S.tri_out[ray] = bi;
+        __stcs(S.t_out + ray, best);
+        __stcs(S.tri_out + ray, bi);
     }
     if (STATS) {
         unsigned a = __reduce_add_sync(0xffffffffu, rs.nodes), b = __reduce_add_sync(0xffffffffu, rs.leaves);
@@ -1125,7 +1162,8 @@ __device__ __forceinline__ int frustum_walk(const float4 *__restrict__ nodes, co
                     cz = __ldg(reinterpret_cast<const float2 *>(nd + 2) + cur.w);
                 }
             }
-            out[2 * n_out] = cxy; out[2 * n_out + 1] = make_float4(cz.x, cz.y, __int_as_float(cur.x), __int_as_float(cur.y));
+            __stcs(out + 2 * n_out, cxy);                        // read once, by one warp, a kernel later: streaming
+            __stcs(out + 2 * n_out + 1, make_float4(cz.x, cz.y, __int_as_float(cur.x), __int_as_float(cur.y)));
             ++n_out;
             pop = true;
         } else {
