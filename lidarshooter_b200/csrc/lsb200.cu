@@ -751,9 +751,9 @@ template <int MODE, bool STATS>
 static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
 {
     constexpr bool TOP = (MODE == 4);
-    const size_t smem = TOP ? (size_t)P.top_cap * 64 : 0;
+    const size_t smem = TOP ? (size_t)P.top_cap * 64 : (MODE == 6 ? (size_t)LSB_SMEM_STACK * kTraceThreads * sizeof(int2) : 0);
     static bool attr_set = false;          // one flag per instantiation
-    if (TOP && !attr_set) {
+    if ((TOP || (MODE == 6 && LSB_SMEM_STACK)) && !attr_set) {
         LSB_CU(c, cudaFuncSetAttribute(k_trace<MODE, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_set = true;
     }

@@ -15,6 +15,9 @@ namespace lsb {
 #define LSB_TRACE_THREADS 384
 #define LSB_TRACE_CTAS 3
 #endif
+#ifndef LSB_SMEM_STACK
+#define LSB_SMEM_STACK 8         // first N stack entries per ray in shared memory (variant 6; 0 = all in local memory)
+#endif
 #ifndef LSB_LAZY_LIST
 #define LSB_LAZY_LIST 1          // variant 6: list entries are taken lazily instead of being pushed up front
 #endif
@@ -370,7 +373,7 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
 template <int OCT, bool STATS, bool SMEM>
 __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, const Ray &r,
                                              const float4 *__restrict__ chain, int n_chain, bool reversed,
-                                             float &best_out, int &bi_out, RayStats &rs)
+                                             float &best_out, int &bi_out, RayStats &rs, int2 *s_stack = nullptr)
 {
     const float tiny = 1e-30f;
     const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
@@ -386,6 +389,15 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
     int bi = -1;
     int2 stack[kStackSize];
     int sp = 0;
+#if LSB_SMEM_STACK
+    // evidence variant: the first LSB_SMEM_STACK entries of the stack live in shared memory ([slot][thread]: no bank
+    // conflicts), deeper ones in the local array
+    auto push = [&](int2 v) { if (sp < LSB_SMEM_STACK) s_stack[sp * kTraceThreads] = v; else stack[sp] = v; ++sp; };
+    auto pop = [&]() -> int2 { --sp; return sp < LSB_SMEM_STACK ? s_stack[sp * kTraceThreads] : stack[sp]; };
+#else
+    auto push = [&](int2 v) { stack[sp++] = v; };
+    auto pop = [&]() -> int2 { return stack[--sp]; };
+#endif
     // sensor chains are listed far -> near (walked backwards), tile lists near -> far
     const float4 *e = reversed ? chain : chain + 2 * (n_chain - 1);
     const int step = reversed ? 2 : -2;
@@ -424,7 +436,7 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
             if (hit0 && hit1) {
                 const bool swap = n1 < n0;
                 cur = swap ? c1 : c0;
-                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                push(make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1)));
                 if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
             } else if (hit0) {
                 cur = c0;
@@ -433,7 +445,7 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
             } else {
                 cur = kDone;
                 while (sp > 0) {
-                    const int2 t = stack[--sp];
+                    const int2 t = pop();
                     if (__int_as_float(t.y) <= far_lim * 1.0000005f) { cur = t.x; break; }
                     if (STATS) ++rs.culled;
                 }
@@ -445,7 +457,7 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
             far_lim = best * 1.0000005f;
             cur = kDone;
             while (sp > 0) {
-                const int2 t = stack[--sp];
+                const int2 t = pop();
                 if (__int_as_float(t.y) <= far_lim * 1.0000005f) { cur = t.x; break; }
                 if (STATS) ++rs.culled;
             }
@@ -648,7 +660,7 @@ __device__ __forceinline__ void flush_append(const TraceParams &P, PendingAppend
 template <int MODE, int OCT, bool STATS>
 __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 *s_top, int n_top, float smax, int4 ud,
                                              unsigned lane, int tile_n = -1, const float4 *s_list = nullptr,
-                                             PendingAppend *pend = nullptr, float4 *s_pts = nullptr)
+                                             PendingAppend *pend = nullptr, float4 *s_pts = nullptr, int2 *s_stack = nullptr)
 {
     constexpr bool TOP = (MODE == 4);
     const int si = ud.x;
@@ -680,8 +692,8 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
                 else trace_ray_il<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
             } else
             if (MODE == 6 && LSB_LAZY_LIST) {
-                if (w_tile) trace_ray_lz<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
-                else trace_ray_lz<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
+                if (w_tile) trace_ray_lz<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs, s_stack);
+                else trace_ray_lz<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs, s_stack);
             } else
             if (w_tile) trace_ray_ww<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
             else if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
@@ -751,7 +763,7 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int MODE, int OCT, bool STATS>
-__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list, float4 *s_pts)
+__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list, float4 *s_pts, int2 *s_stack)
 {
     int begin = 0;
 #pragma unroll
@@ -794,7 +806,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
         else cp_async_commit();
         cp_async_wait<1>();                                        // everything but the newest group: this unit's list is in
         __syncwarp();
-        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, ud, lane, tn == kTileFallback ? -1 : tn, s_list + b * kBuf, LSB_DEFER_APPEND ? &pend : nullptr, s_pts);
+        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, ud, lane, tn == kTileFallback ? -1 : tn, s_list + b * kBuf, LSB_DEFER_APPEND ? &pend : nullptr, s_pts, s_stack);
         if (!more) break;
         __syncwarp();                                              // all lanes are done with buffer b before it is refilled
         ud = ud_n; tn = tn_n; b ^= 1;
@@ -845,12 +857,13 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     float4 *s_list = s_lists[(MODE >= 6) ? (threadIdx.x >> 5) : 0];
     __shared__ float4 s_points[(MODE >= 6 && LSB_DEFER_APPEND) ? kTraceThreads : 1];                  // parked hit points (deferred append)
     float4 *s_pts = s_points + ((MODE >= 6 && LSB_DEFER_APPEND) ? (threadIdx.x & ~31u) : 0u);
+    int2 *s_stack = (MODE == 6 && LSB_SMEM_STACK) ? reinterpret_cast<int2 *>(smem_raw) + threadIdx.x : nullptr;
     if (MODE == 0 || MODE == 6 || MODE == 7) {
-        run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts);
-        run_phase<MODE, 0, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 1, STATS>(P, smax, lane, s_list, s_pts);
-        run_phase<MODE, 2, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 3, STATS>(P, smax, lane, s_list, s_pts);
-        run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts);
-        run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts);
+        run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        run_phase<MODE, 0, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 1, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        run_phase<MODE, 2, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 3, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack);
     } else if (MODE == 2) {
         const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
         if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
