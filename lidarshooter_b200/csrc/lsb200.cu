@@ -93,6 +93,9 @@ struct lsb200_ctx {
     // octant queues of the traversal (variant 0): valid for (units_first, units_count, units_epoch, units_world)
     int64_t sensors_epoch = 0, units_epoch = -1;
     int units_first = -1, units_count = -1, units_world = -1;
+    int64_t units_build_id = 0;            // bumped whenever the queues are rebuilt: their order is not reproducible (atomics),
+                                           // so everything indexed by queue slot (tile intervals, tile lists) dies with them
+    int64_t iv_units_id = -1, tile_units_id = -1;
     int64_t commit_epoch = 0, chain_commit_epoch = -1, chain_sensors_epoch = -1;
     // tile entry lists: valid for one BVH, one set of sensor poses, one set of octant queues and one list size
     int64_t tile_commit_epoch = -1, tile_sensors_epoch = -1;
@@ -877,6 +880,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
                                                     c->d_unit_list.as<int4>());
             count_launch(c, 2);
             c->units_epoch = c->sensors_epoch; c->units_first = first; c->units_count = count; c->units_world = wf;
+            ++c->units_build_id;
         }
         P.unit_list = c->d_unit_list.as<int4>();
         P.oct_hist = c->d_oct_hist.as<uint32_t>();
@@ -892,7 +896,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         const int max_visits = c->opt_tile_visits > 0 ? c->opt_tile_visits : (16 * cap) / 5;
         P.tile_cap = cap;
         const bool stale = c->tile_commit_epoch != c->commit_epoch || c->tile_sensors_epoch != c->sensors_epoch || c->tile_first != first ||
-                           c->tile_count != count || c->tile_cap != cap || c->tile_visits != max_visits;
+                           c->tile_count != count || c->tile_cap != cap || c->tile_visits != max_visits || c->tile_units_id != c->units_build_id;
         if (stale || c->opt_stats) {
             LSB_CU(c, c->d_tile_lists.reserve((size_t)n_units * cap * 2 * sizeof(float4), st));
             LSB_CU(c, c->d_tile_counts.reserve((size_t)n_units, st));
@@ -908,7 +912,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         {
             const int wf = P.world_frame ? 1 : 0;
             const bool iv_stale = c->iv_sensors_epoch != c->sensors_epoch || c->iv_first != first || c->iv_count != count || c->iv_world != wf ||
-                                  c->iv_super != c->opt_super_tiles;
+                                  c->iv_super != c->opt_super_tiles || c->iv_units_id != c->units_build_id;
             if (iv_stale) {
                 LSB_CU(c, c->d_tile_iv.reserve((size_t)n_units * 2 * sizeof(float4), st));
                 if (c->opt_super_tiles) LSB_CU(c, c->d_sup_iv.reserve((size_t)sup_hi * 2 * sizeof(float4), st));
@@ -922,7 +926,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
                     k_super_intervals<<<(unsigned)((sup_hi - sup_lo + 3) / 4), 128, 0, st>>>(P, first, count, sup_lo, sup_hi);
                     count_launch(c);
                 }
-                c->iv_sensors_epoch = c->sensors_epoch; c->iv_first = first; c->iv_count = count; c->iv_world = wf; c->iv_super = c->opt_super_tiles;
+                c->iv_sensors_epoch = c->sensors_epoch; c->iv_first = first; c->iv_count = count; c->iv_world = wf; c->iv_super = c->opt_super_tiles; c->iv_units_id = c->units_build_id;
             }
         }
         if (c->opt_super_tiles) {
@@ -946,7 +950,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
             else k_tile_entries<false><<<blocks, 128, 0, st>>>(P, max_visits);
             count_launch(c);
             c->tile_commit_epoch = c->commit_epoch; c->tile_sensors_epoch = c->sensors_epoch; c->tile_first = first; c->tile_count = count;
-            c->tile_cap = cap; c->tile_visits = max_visits;
+            c->tile_cap = cap; c->tile_visits = max_visits; c->tile_units_id = c->units_build_id;
             if (timing) cudaEventRecord(c->ev[7], st);
         }
     }

@@ -515,6 +515,37 @@ def test_tile_entry_lists_small_city_vs_oracle_bvh(entries, visits, super_tiles)
     ctx.close()
 
 
+def test_tile_lists_follow_queue_rebuilds():
+    """Tile intervals and tile lists are indexed by queue slot, and the queues are rebuilt (in an order that atomics
+    decide) whenever another sensor range is traced: switching to a variant without lists, tracing other ranges and
+    coming back must not reuse lists of the old queue order."""
+    meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
+    poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
+    elev, b, e, H = synth.lidar_table(64, 1801)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
+    for k, (q, t) in enumerate(poses):
+        ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    for name, v, tr in meshes:
+        add_mesh(ctx, name, v, tr)
+    assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
+    ctx.set_option(capi.OPT_TRAVERSAL, 1)
+    ref = [ctx.trace_raw(k)[1:] for k in range(len(poses))]
+    for rep in range(3):
+        ctx.set_option(capi.OPT_TRAVERSAL, 6)
+        for k in (0, 2):
+            rc, t, tri = ctx.trace_raw(k)
+            assert rc == 0 and np.array_equal(t, ref[k][0]) and np.array_equal(tri, ref[k][1])
+        ctx.set_option(capi.OPT_TRAVERSAL, 0)              # same queues, no lists: rebuilds them for other ranges
+        for k in (1, 2, 3, 2):
+            rc, t, tri = ctx.trace_raw(k)
+            assert rc == 0 and np.array_equal(t, ref[k][0]) and np.array_equal(tri, ref[k][1])
+        ctx.set_option(capi.OPT_TRAVERSAL, 6)              # range (2, 1) again: queue cache hit, lists must be rebuilt
+        rc, t, tri = ctx.trace_raw(2)
+        assert rc == 0 and np.array_equal(t, ref[2][0]) and np.array_equal(tri, ref[2][1])
+    ctx.close()
+
+
 def test_city_10m_size_independent_properties():
     """BASELINE config 4 at full size (10 M triangles): properties that need no CPU re-trace.
     (1) every variant returns the same (t, triangle) bits; (2) each hit point t*d lies on its triangle (float64
