@@ -258,6 +258,17 @@ def xt32_scan_leg(local, reps=1000, cpu=True):
     return leg
 
 
+_RESULT_FD = None
+
+
+def emit_result(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU algorithm for the path.  Embree 3.13.4 (the reference's intersector) is
     a closed binary that is neither in /root/reference nor installable here, so this is the oracle PORT (oracle/),
@@ -267,6 +278,11 @@ def run_reference(args):
         return
     from oracle import lso
     lso.build()
+    # all the host threads the process may use -- torchrun exports OMP_NUM_THREADS=1 to its workers
+    try:
+        lso.set_threads(len(os.sched_getaffinity(0)))
+    except AttributeError:
+        lso.set_threads(os.cpu_count() or 1)
     meshes, poses, table = build_workload(args.small)
     elev, b, e, H = table
     ident = lso.IDENTITY_AFFINE
@@ -301,7 +317,7 @@ def run_reference(args):
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit_result(line)
 
 
 def workload_name(small):
@@ -324,6 +340,12 @@ def main():
     ap.add_argument("--commit", default="rebuild", choices=["rebuild", "auto"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    # stdout carries exactly ONE line, the JSON result: everything libraries print to file descriptor 1 meanwhile
+    # (NCCL's version banner, for one) is sent to stderr, and the line is written to the saved descriptor at the end
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -535,7 +557,7 @@ def main():
                 "t_build_s": c["t_build"], "t_trace_s": c["t_trace"]}
         else:
             line["cpu_baseline"] = None
-        print(json.dumps(line), flush=True)
+        emit_result(line)
 
 
 if __name__ == "__main__":
