@@ -17,6 +17,7 @@ def regions():
     marks = [('intersect_tri', 'tri test'), ('void test_leaf', 'leaf loop'), ('void slab_nf', 'slab_nf'),
              ('void trace_ray(', 'trace_ray (modes 1-4)'), ('void trace_ray_ww', 'ww: set-up + entry loop'),
              ('    while (cur != kDone) {', 'ww: node loop'), ('        if (cur < 0) {', 'ww: leaf + pop'),
+             ('void trace_ray_lz', 'lz: lazy-list traversal (list tests, node loop, pops)'), ('void trace_ray_il', 'il: single-loop traversal'),
              ('void brute_ray', 'brute'), ('void store_point', 'store/hit point'), ('void ray_from_tables', 'make_ray'),
              ('int ray_octant', 'unit descriptor'), ('void process_unit', 'process_unit'), ('void cp_async16', 'run_phase'),
              ('void k_trace(', 'kernel'), ('void __launch_bounds__(256) k_classify_units', 'other kernels')]
