@@ -249,7 +249,10 @@ __device__ __forceinline__ int delta(const Keys &keys, int n, int i, uint32_t ki
     return (ki == kj) ? 32 + __clz((uint32_t)i ^ (uint32_t)j) : __clz(ki ^ kj);
 }
 
-constexpr int kFitBlock = 256;         // leaves per k_fit CTA
+#ifndef LSB_FIT_BLOCK
+#define LSB_FIT_BLOCK 256
+#endif
+constexpr int kFitBlock = LSB_FIT_BLOCK;         // leaves per k_fit CTA
 
 __device__ __forceinline__ int leaf_ref(int first, int count) { return ~(first | ((count - 1) << kLeafShift)); }
 
