@@ -296,11 +296,15 @@ class Context:
 
     def trace_counters(self):
         """Totals of the last OPT_TRACE_STATS launch as a dict."""
-        out = (C.c_uint64 * 15)()
-        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 15))
+        out = (C.c_uint64 * 111)()
+        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 111))
         names = ("rays", "nodes", "leaves", "tris", "units_uniform", "units_mixed", "max_stack", "hits", "culled_pops", "chain_tests",
                  "tile_visits", "tile_entries", "tile_fallbacks", "tile_empty", "super_visits")
-        return {k: int(out[i]) for i, k in enumerate(names)}
+        d = {k: int(out[i]) for i, k in enumerate(names)}
+        # per-unit cost histogram: bin b = units that took [2^b, 2^(b+1)) SM cycles
+        for j, key in enumerate(("cyc_units", "cyc_sum", "cyc_nodes", "cyc_list")):
+            d[key] = [int(out[15 + 24 * j + b]) for b in range(24)]
+        return d
 
     def reset_counters(self):
         self._L.lsb200_reset_counters(self._h)

@@ -59,7 +59,11 @@ constexpr int kTileFallback = 0xFF;
 
 // Instrumented (STATS) launches accumulate these per-launch totals (lsb200_get_trace_counters).
 enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUniform, kCntUnitsMixed, kCntMaxStack, kCntHits, kCntCulled, kCntChainTests,
-                    kCntTileVisits, kCntTileEntries, kCntTileFallbacks, kCntTileEmpty, kCntSuperVisits, kCntCount };
+                    kCntTileVisits, kCntTileEntries, kCntTileFallbacks, kCntTileEmpty, kCntSuperVisits,
+                    // per-unit cost histogram (instrumented launches): bin = log2(SM cycles the unit took); units, cycles, node visits,
+                    // list size per bin
+                    kCntCycUnits, kCntCycSum = kCntCycUnits + 24, kCntCycNodes = kCntCycSum + 24, kCntCycList = kCntCycNodes + 24,
+                    kCntCount = kCntCycList + 24 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -671,6 +675,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
     float best = INFINITY; int bi = -1;
     float dsx = 0.f, dsy = 0.f, dsz = 1.f;
     RayStats rs{0u, 0u, 0u, 0u, 0u, 0u};
+    const long long unit_t0 = STATS ? clock64() : 0ll;
     // MODE 6: a unit whose tile list (k_tile_entries, near -> far) was prefetched into shared memory by run_phase
     // starts from it (tile_n entries, 0 = the tile's pyramid reaches nothing); tile_n < 0: no tile list -- the rays
     // read their sensor's origin chain (far -> near) from global memory.
@@ -710,6 +715,11 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
         unsigned cu = __reduce_add_sync(0xffffffffu, rs.culled), ct = __reduce_add_sync(0xffffffffu, rs.chain_tests);
         unsigned nv = __reduce_add_sync(0xffffffffu, valid ? 1u : 0u), nh = __reduce_add_sync(0xffffffffu, (valid && bi >= 0) ? 1u : 0u);
         if (lane == 0) {
+            const long long cyc = clock64() - unit_t0;
+            const int bin = min(23, max(0, 63 - __clzll(cyc > 0 ? cyc : 1)));
+            atomicAdd(P.counters + kCntCycUnits + bin, 1ull); atomicAdd(P.counters + kCntCycSum + bin, (unsigned long long)cyc);
+            atomicAdd(P.counters + kCntCycNodes + bin, (unsigned long long)a);
+            atomicAdd(P.counters + kCntCycList + bin, (unsigned long long)(tile_n < 0 ? 99 : tile_n));
             atomicAdd(P.counters + kCntRays, (unsigned long long)nv); atomicAdd(P.counters + kCntNodes, (unsigned long long)a);
             atomicAdd(P.counters + kCntLeaves, (unsigned long long)b); atomicAdd(P.counters + kCntTris, (unsigned long long)c);
             atomicAdd(P.counters + kCntHits, (unsigned long long)nh); atomicMax(P.counters + kCntMaxStack, (unsigned long long)d);
