@@ -18,6 +18,9 @@ namespace lsb {
 #ifndef LSB_SMEM_STACK
 #define LSB_SMEM_STACK 8         // first N stack entries per ray in shared memory (variant 6; 0 = all in local memory)
 #endif
+#ifndef LSB_MIXED_TILE_LISTS
+#define LSB_MIXED_TILE_LISTS 1   // sign-mixed tiles (class 8) get entry lists too: interval test with an unbounded 1/d on the flipping axis
+#endif
 #ifndef LSB_LAZY_LIST
 #define LSB_LAZY_LIST 1          // variant 6: list entries are taken lazily instead of being pushed up front
 #endif
@@ -790,7 +793,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
         }
         return;
     }
-    const bool lists = (MODE == 6 || MODE == 7) && OCT < 8 && P.tile_counts != nullptr;
+    const bool lists = (MODE == 6 || MODE == 7) && (OCT < 8 || LSB_MIXED_TILE_LISTS) && P.tile_counts != nullptr;
     constexpr int kBuf = 2 * kMaxTileEntries;                     // float4 per buffer
     auto ticket = [&]() -> int { return lane == 0 ? (int)atomicAdd(&P.work[2 + OCT], 1u) : 0; };
     auto fetch = [&](int k, int4 &ud, int &tn, float4 *buf) {     // descriptor, list size and list of queue entry k
@@ -1003,15 +1006,26 @@ constexpr int kSuperTiles = 4;          // a supertile is kSuperTiles x kSuperTi
 
 // Direction interval of a block of rays -> the constants of the interval slab test.
 struct TileFrustum {
-    bool neg[3];
+    int mode[3];                 // per axis: 0 = every ray goes up the axis, 1 = down, 2 = both signs occur (or |d| touches 0)
     float in[3], an[3], ifr[3], af[3];
     float max_range;
+    // one axis: lower bound of the entry distance, upper bound of the exit distance.  Mode 2: 1/d is unbounded, so a
+    // ray can stay inside the slab for ever (no exit bound) and enters it no earlier than gap / max |d|.
+    __device__ __forceinline__ void axis(int k, float lo, float hi, float &n, float &f) const
+    {
+        if (mode[k] == 2) {
+            n = fmaxf(fmaf(lo, in[k], an[k]), fmaf(hi, -in[k], af[k]));
+            f = INFINITY;
+        } else {
+            n = fmaf(mode[k] ? hi : lo, in[k], an[k]);
+            f = fmaf(mode[k] ? lo : hi, ifr[k], af[k]);
+        }
+    }
     // box = (lo.x, hi.x, lo.y, hi.y), (lo.z, hi.z): can a ray of the block enter it, and not before which distance
     __device__ __forceinline__ bool test(const float4 bxy, float bzlo, float bzhi, float &n) const
     {
-        const float nx = fmaf(neg[0] ? bxy.y : bxy.x, in[0], an[0]), fx = fmaf(neg[0] ? bxy.x : bxy.y, ifr[0], af[0]);
-        const float ny = fmaf(neg[1] ? bxy.w : bxy.z, in[1], an[1]), fy = fmaf(neg[1] ? bxy.z : bxy.w, ifr[1], af[1]);
-        const float nz = fmaf(neg[2] ? bzhi : bzlo, in[2], an[2]), fz = fmaf(neg[2] ? bzlo : bzhi, ifr[2], af[2]);
+        float nx, fx, ny, fy, nz, fz;
+        axis(0, bxy.x, bxy.y, nx, fx); axis(1, bxy.z, bxy.w, ny, fy); axis(2, bzlo, bzhi, nz, fz);
         n = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
         const float f = fminf(fminf(fx, fy), fz);
         return n <= f && n <= max_range;
@@ -1059,21 +1073,32 @@ __device__ __forceinline__ int block_interval(const SensorDev &S, int world_fram
     return sign_or == sign_and ? (int)sign_or : 8;
 }
 
-// false: the interval touches 0 on some axis (or holds no ray) -- no interval test for this block
-__device__ __forceinline__ bool make_frustum(const float dlo[3], const float dhi[3], const float o3[3], int cls, float eps,
-                                             float max_range, TileFrustum &F)
+// The interval itself tells the mode of every axis (for a sign-uniform tile they agree with its octant class).
+// false: the block holds no ray.
+__device__ __forceinline__ bool make_frustum(const float dlo[3], const float dhi[3], const float o3[3], float eps, float max_range,
+                                             TileFrustum &F)
 {
     bool ok = true;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        F.neg[k] = ((cls >> k) & 1) != 0;
-        const float amin = F.neg[k] ? -dhi[k] : dlo[k], amax = F.neg[k] ? -dlo[k] : dhi[k];     // |d| interval
-        if (!(amin > 1e-6f)) ok = false;
-        const float in_abs = (1.0f / amax) * 0.999999f, if_abs = (1.0f / fmaxf(amin, 1e-6f)) * 1.000001f;
-        F.in[k] = F.neg[k] ? -in_abs : in_abs;
-        F.ifr[k] = F.neg[k] ? -if_abs : if_abs;
-        F.an[k] = -o3[k] * F.in[k] - eps * in_abs;
-        F.af[k] = -o3[k] * F.ifr[k] + eps * if_abs;
+        if (!(dlo[k] <= dhi[k])) ok = false;
+        const int mode = dlo[k] > 1e-6f ? 0 : (dhi[k] < -1e-6f ? 1 : 2);
+        F.mode[k] = mode;
+        if (mode == 2) {
+            const float amax = fmaxf(fmaxf(fabsf(dlo[k]), fabsf(dhi[k])), 1e-30f);
+            const float in_abs = (1.0f / amax) * 0.999999f;
+            F.in[k] = in_abs;
+            F.an[k] = -(o3[k] + eps) * in_abs;          // (lo - o - eps) * in
+            F.af[k] = (o3[k] - eps) * in_abs;           // (o - eps - hi) * in   (used with -in)
+            F.ifr[k] = 0.0f;
+        } else {
+            const float amin = mode ? -dhi[k] : dlo[k], amax = mode ? -dlo[k] : dhi[k];     // |d| interval
+            const float in_abs = (1.0f / amax) * 0.999999f, if_abs = (1.0f / amin) * 1.000001f;
+            F.in[k] = mode ? -in_abs : in_abs;
+            F.ifr[k] = mode ? -if_abs : if_abs;
+            F.an[k] = -o3[k] * F.in[k] - eps * in_abs;
+            F.af[k] = -o3[k] * F.ifr[k] + eps * if_abs;
+        }
     }
     F.max_range = max_range;
     return ok;
@@ -1243,7 +1268,7 @@ __global__ void __launch_bounds__(128) k_super_entries(TraceParams P, int s_firs
     TileFrustum F;
     const float eps = 1.5f * (8e-6f * (scene_smax(P.bounds) + omax) + 1e-30f);
     int n_out = -1, visits = 0;
-    if (cls < 8 && make_frustum(dlo, dhi, o3, cls, eps, S.max_range, F)) {
+    if (cls < 8 && make_frustum(dlo, dhi, o3, eps, S.max_range, F)) {
         const int list = si * 9 + cls;
         n_out = frustum_walk(P.nodes, F, P.chains + (size_t)list * (2 * kMaxChain), __ldg(P.chain_counts + list), false,
                              kMaxTileEntries, max_visits, P.sup_lists + (size_t)sup * (2 * kMaxTileEntries), visits);
@@ -1262,8 +1287,8 @@ __global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_vis
     for (int o = 0; o < 8; ++o) begin8 += (int)__ldg(P.oct_hist + o);
     const int total = begin8 + (int)__ldg(P.oct_hist + 8);
     if (slot >= total) return;
-    if (slot >= begin8) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
-    int cls = 0, acc = 0;
+    if (slot >= begin8 && !LSB_MIXED_TILE_LISTS) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
+    int cls = 0, acc = 0;                              // 0..7: the octant queue the slot is in; 8: sign-mixed
 #pragma unroll
     for (int o = 0; o < 8; ++o) { acc += (int)__ldg(P.oct_hist + o); if (slot >= acc) cls = o + 1; }
 
@@ -1276,14 +1301,14 @@ __global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_vis
     const float o3[3] = {P.world_frame ? S.T[0] : 0.0f, P.world_frame ? S.T[1] : 0.0f, P.world_frame ? S.T[2] : 0.0f};
     TileFrustum F;
     const float eps = 1.5f * (8e-6f * (scene_smax(P.bounds) + omax) + 1e-30f);
-    if (!make_frustum(dlo, dhi, o3, cls, eps, S.max_range, F)) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
+    if (!make_frustum(dlo, dhi, o3, eps, S.max_range, F)) { P.tile_counts[slot] = (uint8_t)kTileFallback; return; }
 
     // seeds: the supertile's list when it has one, else the sensor's origin chain
     const int list = ud.x * 9 + cls;
     const float4 *seeds = P.chains + (size_t)list * (2 * kMaxChain);
     int n_seeds = __ldg(P.chain_counts + list);
     bool near_first = false;
-    if (P.sup_counts != nullptr) {
+    if (P.sup_counts != nullptr && cls < 8) {
         const int sup = S.sup_base + ((ud.y / th) / kSuperTiles) * S.sup_w + (ud.z / tw) / kSuperTiles;
         const int sc = (int)__ldg(P.sup_counts + sup);
         if (sc != kTileFallback) { seeds = P.sup_lists + (size_t)sup * (2 * kMaxTileEntries); n_seeds = sc; near_first = true; }
