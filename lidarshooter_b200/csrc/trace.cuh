@@ -1000,8 +1000,9 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
 // rays' padding and the interval is widened by 1e-6, far above the rounding noise of either form).  The union of
 // the listed subtrees therefore covers everything any ray of the tile can hit, and closest hit = min (t, triangle
 // id) does not depend on how the tree was cut: per-ray results are unchanged (tests: every variant bit-identical).
-// Sign-mixed tiles (class 8, ~4 % of a 128 x 3601 table) and tiles whose interval touches 0 keep the sensor chain;
-// tiles of a sign-mixed supertile start from the chain as before.
+// Sign-mixed tiles (class 8, ~1 % of a 128 x 3601 table) and axes whose interval touches 0 use the both-signs form of the
+// test on that axis (1/d unbounded: entry bound from the gap to the slab, no exit bound); tiles of a sign-mixed
+// supertile start from the chain.
 constexpr int kSuperTiles = 4;          // a supertile is kSuperTiles x kSuperTiles tiles
 
 // Direction interval of a block of rays -> the constants of the interval slab test.
