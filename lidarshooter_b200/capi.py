@@ -296,14 +296,16 @@ class Context:
 
     def trace_counters(self):
         """Totals of the last OPT_TRACE_STATS launch as a dict."""
-        out = (C.c_uint64 * 111)()
-        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 111))
+        out = (C.c_uint64 * 152)()
+        self._chk(self._L.lsb200_get_trace_counters(self._h, out, 152))
         names = ("rays", "nodes", "leaves", "tris", "units_uniform", "units_mixed", "max_stack", "hits", "culled_pops", "chain_tests",
                  "tile_visits", "tile_entries", "tile_fallbacks", "tile_empty", "super_visits")
         d = {k: int(out[i]) for i, k in enumerate(names)}
         # per-unit cost histogram: bin b = units that took [2^b, 2^(b+1)) SM cycles
         for j, key in enumerate(("cyc_units", "cyc_sum", "cyc_nodes", "cyc_list")):
             d[key] = [int(out[15 + 24 * j + b]) for b in range(24)]
+        d["heavy_cycles_by_class"] = [int(out[111 + o]) for o in range(9)]
+        d["heavy_cycles_by_band"] = [int(out[120 + b]) for b in range(32)]
         return d
 
     def reset_counters(self):

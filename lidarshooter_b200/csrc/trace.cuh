@@ -21,6 +21,9 @@ namespace lsb {
 #ifndef LSB_MIXED_TILE_LISTS
 #define LSB_MIXED_TILE_LISTS 1   // sign-mixed tiles (class 8) get entry lists too: interval test with an unbounded 1/d on the flipping axis
 #endif
+#ifndef LSB_SPLIT_DOWNWARD
+#define LSB_SPLIT_DOWNWARD 0     // 1: the fronts (most grazing rows) of the downward octant queues are drained before the upward octants
+#endif
 #ifndef LSB_LAZY_LIST
 #define LSB_LAZY_LIST 1          // variant 6: list entries are taken lazily instead of being pushed up front
 #endif
@@ -66,7 +69,9 @@ enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUnif
                     // per-unit cost histogram (instrumented launches): bin = log2(SM cycles the unit took); units, cycles, node visits,
                     // list size per bin
                     kCntCycUnits, kCntCycSum = kCntCycUnits + 24, kCntCycNodes = kCntCycSum + 24, kCntCycList = kCntCycNodes + 24,
-                    kCntCount = kCntCycList + 24 };
+                    // heavy units (>= 2^17 cycles) by octant class [9] and by elevation band [32] (band = first channel * 32 / V)
+                    kCntHeavyClass = kCntCycList + 24, kCntHeavyBand = kCntHeavyClass + 9,
+                    kCntCount = kCntHeavyBand + 32 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -723,6 +728,10 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             atomicAdd(P.counters + kCntCycUnits + bin, 1ull); atomicAdd(P.counters + kCntCycSum + bin, (unsigned long long)cyc);
             atomicAdd(P.counters + kCntCycNodes + bin, (unsigned long long)a);
             atomicAdd(P.counters + kCntCycList + bin, (unsigned long long)(tile_n < 0 ? 99 : tile_n));
+            if (bin >= 17) {
+                atomicAdd(P.counters + kCntHeavyClass + OCT, (unsigned long long)cyc);
+                atomicAdd(P.counters + kCntHeavyBand + min(31, ud.y * 32 / max(S.V, 1)), (unsigned long long)cyc);
+            }
             atomicAdd(P.counters + kCntRays, (unsigned long long)nv); atomicAdd(P.counters + kCntNodes, (unsigned long long)a);
             atomicAdd(P.counters + kCntLeaves, (unsigned long long)b); atomicAdd(P.counters + kCntTris, (unsigned long long)c);
             atomicAdd(P.counters + kCntHits, (unsigned long long)nh); atomicMax(P.counters + kCntMaxStack, (unsigned long long)d);
@@ -776,7 +785,8 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int MODE, int OCT, bool STATS>
-__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list, float4 *s_pts, int2 *s_stack)
+__device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list, float4 *s_pts, int2 *s_stack,
+                                          int part = 0)
 {
     int begin = 0;
 #pragma unroll
@@ -795,7 +805,12 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
     }
     const bool lists = (MODE == 6 || MODE == 7) && (OCT < 8 || LSB_MIXED_TILE_LISTS) && P.tile_counts != nullptr;
     constexpr int kBuf = 2 * kMaxTileEntries;                     // float4 per buffer
-    auto ticket = [&]() -> int { return lane == 0 ? (int)atomicAdd(&P.work[2 + OCT], 1u) : 0; };
+    // part 0: the whole queue; 1 / 2: its front 3/8 / the rest (own ticket counters) -- see the phase order in k_trace
+    const int n_front = (int)(((long long)count * 3) / 8);
+    const int lo = part == 2 ? n_front : 0, hi = part == 1 ? n_front : count;
+    if (lo >= hi) return;
+    uint32_t *ctr = &P.work[(part == 2 ? 11 : 2) + OCT];
+    auto ticket = [&]() -> int { return lane == 0 ? lo + (int)atomicAdd(ctr, 1u) : 0; };
     auto fetch = [&](int k, int4 &ud, int &tn, float4 *buf) {     // descriptor, list size and list of queue entry k
         ud = __ldg(P.unit_list + begin + k);
         tn = kTileFallback;                                        // raw list size; looked at when the unit's turn comes
@@ -806,14 +821,14 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
         cp_async_commit();
     };
     int k_cur = __shfl_sync(0xffffffffu, ticket(), 0);
-    if (k_cur >= count) return;
+    if (k_cur >= hi) return;
     int raw_next = ticket();                                       // consumed at the top of the loop
     int4 ud; int tn; int b = 0;
     PendingAppend pend{0u, 0u, 0};
     fetch(k_cur, ud, tn, s_list);
     while (true) {
         const int k_next = __shfl_sync(0xffffffffu, raw_next, 0);
-        const bool more = k_next < count;
+        const bool more = k_next < hi;
         int4 ud_n = make_int4(0, 0, 0, 0); int tn_n = kTileFallback;
         if (more) { fetch(k_next, ud_n, tn_n, s_list + (b ^ 1) * kBuf); raw_next = ticket(); }
         else cp_async_commit();
@@ -872,11 +887,20 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     float4 *s_pts = s_points + ((MODE >= 6 && LSB_DEFER_APPEND) ? (threadIdx.x & ~31u) : 0u);
     int2 *s_stack = (MODE == 6 && LSB_SMEM_STACK) ? reinterpret_cast<int2 *>(smem_raw) + threadIdx.x : nullptr;
     if (MODE == 0 || MODE == 6 || MODE == 7) {
+        // Order of the queues.  The kernel ends when its last unit ends, and a few units run ~100 x the median (long grazing
+        // rays, design log section 15), so the LAST queue should hold light units only.  The queues are row-major (channel
+        // by channel): the downward octants (4..7) start with their most grazing rows and end with the steep ones that hit the
+        // ground nearby.  Their fronts are therefore drained early and their light remainders make the tail.
         run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        if (MODE == 6 && LSB_SPLIT_DOWNWARD) {
+            run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
+        }
         run_phase<MODE, 0, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 1, STATS>(P, smax, lane, s_list, s_pts, s_stack);
         run_phase<MODE, 2, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 3, STATS>(P, smax, lane, s_list, s_pts, s_stack);
-        run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack);
-        run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        const int rest = (MODE == 6 && LSB_SPLIT_DOWNWARD) ? 2 : 0;
+        run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest);
+        run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest);
     } else if (MODE == 2) {
         const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
         if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
@@ -896,7 +920,7 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
             __threadfence();
             if (atomicAdd(&P.work[1], 1u) == gridDim.x - 1) {
                 P.work[0] = 0; P.work[1] = 0;
-                if (MODE == 0 || MODE == 6 || MODE == 7) for (int o = 0; o < 9; ++o) P.work[2 + o] = 0;
+                if (MODE == 0 || MODE == 6 || MODE == 7) for (int o = 0; o < 18; ++o) P.work[2 + o] = 0;
                 __threadfence();
             }
         }

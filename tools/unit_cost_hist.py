@@ -19,3 +19,6 @@ print('bin  units   %units  %cycles  nodes/ray  list')
 for bn in range(24):
     u = c['cyc_units'][bn]
     if u: print(bn, u, round(100*u/sum(c['cyc_units']),2), round(100*c['cyc_sum'][bn]/tot,2), round(c['cyc_nodes'][bn]/u/32,2), round(c['cyc_list'][bn]/u,1))
+hc, hb = c['heavy_cycles_by_class'], c['heavy_cycles_by_band']
+print('heavy-unit cycles by octant class (0..7, 8 = mixed), % of all unit cycles:', [round(100 * x / tot, 1) for x in hc])
+print('heavy-unit cycles by elevation band (32 bands, +15 deg first .. -25 deg last), %:', [round(100 * x / tot, 1) for x in hb])
