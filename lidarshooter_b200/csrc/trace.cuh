@@ -1032,6 +1032,7 @@ constexpr int kSuperTiles = 4;          // a supertile is kSuperTiles x kSuperTi
 // Direction interval of a block of rays -> the constants of the interval slab test.
 struct TileFrustum {
     int mode[3];                 // per axis: 0 = every ray goes up the axis, 1 = down, 2 = both signs occur (or |d| touches 0)
+    bool any_mixed;              // some axis is in mode 2
     float in[3], an[3], ifr[3], af[3];
     float max_range;
     // one axis: lower bound of the entry distance, upper bound of the exit distance.  Mode 2: 1/d is unbounded, so a
@@ -1050,7 +1051,13 @@ struct TileFrustum {
     __device__ __forceinline__ bool test(const float4 bxy, float bzlo, float bzhi, float &n) const
     {
         float nx, fx, ny, fy, nz, fz;
-        axis(0, bxy.x, bxy.y, nx, fx); axis(1, bxy.z, bxy.w, ny, fy); axis(2, bzlo, bzhi, nz, fz);
+        if (!any_mixed) {            // the usual case, without the per-axis mode branches
+            nx = fmaf(mode[0] ? bxy.y : bxy.x, in[0], an[0]); fx = fmaf(mode[0] ? bxy.x : bxy.y, ifr[0], af[0]);
+            ny = fmaf(mode[1] ? bxy.w : bxy.z, in[1], an[1]); fy = fmaf(mode[1] ? bxy.z : bxy.w, ifr[1], af[1]);
+            nz = fmaf(mode[2] ? bzhi : bzlo, in[2], an[2]); fz = fmaf(mode[2] ? bzlo : bzhi, ifr[2], af[2]);
+        } else {
+            axis(0, bxy.x, bxy.y, nx, fx); axis(1, bxy.z, bxy.w, ny, fy); axis(2, bzlo, bzhi, nz, fz);
+        }
         n = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
         const float f = fminf(fminf(fx, fy), fz);
         return n <= f && n <= max_range;
@@ -1126,6 +1133,7 @@ __device__ __forceinline__ bool make_frustum(const float dlo[3], const float dhi
         }
     }
     F.max_range = max_range;
+    F.any_mixed = F.mode[0] == 2 || F.mode[1] == 2 || F.mode[2] == 2;
     return ok;
 }
 
