@@ -938,7 +938,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
             P.sup_counts = c->d_sup_counts.as<uint8_t>();
         }
         if (stale || c->opt_stats) {
-            const unsigned blocks = (unsigned)((n_units + 127) / 128);
+            const unsigned blocks = (unsigned)((n_units + kTileBlock - 1) / kTileBlock);
             if (timing) { cudaEventRecord(c->ev[11], st); tile_timed = true; }
             if (c->opt_super_tiles) {
                 const unsigned sblocks = (unsigned)((sup_hi - sup_lo + 127) / 128);
@@ -946,8 +946,8 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
                 else k_super_entries<false><<<sblocks, 128, 0, st>>>(P, first, count, sup_lo, sup_hi, 8 * kMaxTileEntries);
                 count_launch(c);
             }
-            if (c->opt_stats) k_tile_entries<true><<<blocks, 128, 0, st>>>(P, max_visits);
-            else k_tile_entries<false><<<blocks, 128, 0, st>>>(P, max_visits);
+            if (c->opt_stats) k_tile_entries<true><<<blocks, kTileBlock, 0, st>>>(P, max_visits);
+            else k_tile_entries<false><<<blocks, kTileBlock, 0, st>>>(P, max_visits);
             count_launch(c);
             c->tile_commit_epoch = c->commit_epoch; c->tile_sensors_epoch = c->sensors_epoch; c->tile_first = first; c->tile_count = count;
             c->tile_cap = cap; c->tile_visits = max_visits; c->tile_units_id = c->units_build_id;

@@ -1027,6 +1027,10 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
 // Sign-mixed tiles (class 8, ~1 % of a 128 x 3601 table) and axes whose interval touches 0 use the both-signs form of the
 // test on that axis (1/d unbounded: entry bound from the gap to the slab, no exit bound); tiles of a sign-mixed
 // supertile start from the chain.
+#ifndef LSB_TILE_BLOCK
+#define LSB_TILE_BLOCK 128
+#endif
+constexpr int kTileBlock = LSB_TILE_BLOCK;   // threads per CTA of k_tile_entries (one thread per tile)
 constexpr int kSuperTiles = 4;          // a supertile is kSuperTiles x kSuperTiles tiles
 
 // Direction interval of a block of rays -> the constants of the interval slab test.
@@ -1312,7 +1316,7 @@ __global__ void __launch_bounds__(128) k_super_entries(TraceParams P, int s_firs
 
 // One thread per queue entry (32-ray tile).  tile_counts: entries, or kTileFallback.
 template <bool STATS>
-__global__ void __launch_bounds__(128) k_tile_entries(TraceParams P, int max_visits)
+__global__ void __launch_bounds__(kTileBlock) k_tile_entries(TraceParams P, int max_visits)
 {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     int begin8 = 0;                                    // first slot of class 8 = number of sign-uniform units
