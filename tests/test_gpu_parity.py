@@ -281,6 +281,44 @@ def test_random_soup_vs_brute(n_tris, lists):
     ctx.close()
 
 
+def _axis_aligned_room(half, z0, z1):
+    """Closed axis-aligned box room around the origin (12 triangles) + a flat plate in the z = 0 plane (2 triangles):
+    every node box has at least one zero-thickness axis somewhere down the tree."""
+    x0, x1, y0, y1 = -half, half, -half, half
+    c = np.array([[x0, y0, z0], [x1, y0, z0], [x1, y1, z0], [x0, y1, z0], [x0, y0, z1], [x1, y0, z1], [x1, y1, z1], [x0, y1, z1],
+                  [1, -1, 0], [3, -1, 0], [3, 1, 0], [1, 1, 0]], np.float32)
+    q = [(0, 1, 2, 3), (4, 5, 6, 7), (0, 1, 5, 4), (1, 2, 6, 5), (2, 3, 7, 6), (3, 0, 4, 7), (8, 9, 10, 11)]
+    tr = np.array([t for a, b, c_, d in q for t in ((a, b, c_), (a, c_, d))], np.uint32)
+    return c, tr
+
+
+@pytest.mark.parametrize("lists", ["default", "tile", "tile+super"])
+@pytest.mark.parametrize("origin", [(0.0, 0.0, 0.0), (0.0, 0.0, 0.5), (2.0, 0.0, 0.0), (1e4, -2e4, 50.0)])
+def test_axis_parallel_rays_and_flat_boxes(origin, lists):
+    """Directions with exactly-zero (or rounding-noise) components -- elevation 0 / +-90 deg, azimuth steps of 45 deg --
+    against axis-aligned walls and a plate in the sensor's own horizontal plane (rays IN the plane of a triangle, rays
+    along box faces, an origin on a triangle): 0 x inf in a slab test must not lose or invent a hit.  Brute-force
+    oracle, bit-exact."""
+    v, tr = _axis_aligned_room(8.0, -2.0, 4.0)
+    v = (v + np.array(origin, np.float32)).astype(np.float32) if abs(origin[0]) > 100 else v
+    pos = origin
+    elev = np.array([90, 45, 1e-3, 0, -1e-3, -45, -90, 30], np.float32)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    if lists != "default":
+        ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
+        ctx.set_option(capi.OPT_SUPER_TILES, 1 if lists == "tile+super" else 0)
+    ctx.set_sensor(elev, 0.0, 360.0, 17, (1, 0, 0, 0), pos)
+    add_mesh(ctx, "room", v, tr)
+    assert ctx.commit_scene() == 0, ctx.last_error()
+    rc, t, tri = ctx.trace_raw()
+    assert rc == 0
+    s = lso.Sensor(elev, 0.0, 360.0, 17, (1, 0, 0, 0), pos)
+    ref = lso.scan(s, [(v, tr, IDENT)], mode=1, use_bvh=False)
+    assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+    assert (tri >= 0).sum() > len(tri) // 2
+    ctx.close()
+
+
 def test_duplicate_and_degenerate_triangles():
     """Coincident triangles (equal t): the smaller global id wins; zero-area triangles never hit."""
     v = np.array([[5, -1, -1], [5, 1, -1], [5, 0, 1], [6, 0, 0], [6, 0, 0], [6, 0, 0]], np.float32)
