@@ -870,8 +870,8 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         if (c->units_epoch != c->sensors_epoch || c->units_first != first || c->units_count != count || c->units_world != wf) {
             LSB_CU(c, c->d_unit_oct.reserve((size_t)n_units, st));
             LSB_CU(c, c->d_unit_list.reserve((size_t)n_units * sizeof(int4), st));
-            LSB_CU(c, c->d_oct_hist.reserve(32 * 4, st));
-            LSB_CU(c, cudaMemsetAsync(c->d_oct_hist.p, 0, 32 * 4, st));
+            LSB_CU(c, c->d_oct_hist.reserve(64 * 4, st));        // [0, 9) class sizes, [16, 25) front cursors, [32, 41) back cursors
+            LSB_CU(c, cudaMemsetAsync(c->d_oct_hist.p, 0, 64 * 4, st));
             const unsigned blocks = (unsigned)((n_units + 255) / 256);
             k_classify_units<<<blocks, 256, 0, st>>>(d_sens, P.n_sensors, unit_lo, unit_hi, wf, P.tile_w_log2, c->d_unit_oct.as<uint8_t>(),
                                                      c->d_oct_hist.as<uint32_t>());

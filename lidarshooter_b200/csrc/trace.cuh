@@ -21,8 +21,11 @@ namespace lsb {
 #ifndef LSB_MIXED_TILE_LISTS
 #define LSB_MIXED_TILE_LISTS 1   // sign-mixed tiles (class 8) get entry lists too: interval test with an unbounded 1/d on the flipping axis
 #endif
+#ifndef LSB_HEAVY_FIRST
+#define LSB_HEAVY_FIRST 1         // 1: heavy units (grazing rays) queued at the front of their octant class (k_scatter_units)
+#endif
 #ifndef LSB_SPLIT_DOWNWARD
-#define LSB_SPLIT_DOWNWARD 0     // 1: the fronts (most grazing rows) of the downward octant queues are drained before the upward octants
+#define LSB_SPLIT_DOWNWARD 1     // 1: the heavy fronts (grazing rows, LSB_HEAVY_FIRST) of the downward octant queues are drained before the upward octants
 #endif
 #ifndef LSB_LAZY_LIST
 #define LSB_LAZY_LIST 1          // variant 6: list entries are taken lazily instead of being pushed up front
@@ -49,7 +52,7 @@ struct TraceParams {
     uint32_t *work;               // [0] next unit, [1] finished CTAs, [2..10] next entry of each octant queue
     unsigned long long *counters; // STATS builds only: see TraceCounter
     const int4 *unit_list;        // MODE 0: unit descriptors (sensor, first ray, its channel, its azimuth step) grouped by octant class
-    const uint32_t *oct_hist;     // MODE 0: [9] units per class (0..7 octants, 8 mixed)
+    const uint32_t *oct_hist;     // MODE 0: [9] units per class (0..7 octants, 8 mixed); [16, 25): heavy units per class
     const float4 *chains;         // [n_sensors][9][kMaxChain][2] origin-chain lists per octant class (k_origin_chain)
     const int *chain_counts;      // [n_sensors][9] entries per list; nullptr = lists off (start at the root)
     float4 *tile_lists;           // [queue slot][tile_cap][2] per-TILE entry lists (k_tile_entries); nullptr = off
@@ -805,8 +808,9 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
     }
     const bool lists = (MODE == 6 || MODE == 7) && (OCT < 8 || LSB_MIXED_TILE_LISTS) && P.tile_counts != nullptr;
     constexpr int kBuf = 2 * kMaxTileEntries;                     // float4 per buffer
-    // part 0: the whole queue; 1 / 2: its front 3/8 / the rest (own ticket counters) -- see the phase order in k_trace
-    const int n_front = (int)(((long long)count * 3) / 8);
+    // part 0: the whole queue; 1 / 2: its heavy front (k_scatter_units' front cursor = number of heavy units of the class) /
+    // the rest (own ticket counters) -- see the phase order in k_trace
+    const int n_front = LSB_HEAVY_FIRST ? min(count, (int)__ldg(P.oct_hist + 16 + OCT)) : (int)(((long long)count * 3) / 8);
     const int lo = part == 2 ? n_front : 0, hi = part == 1 ? n_front : count;
     if (lo >= hi) return;
     uint32_t *ctr = &P.work[(part == 2 ? 11 : 2) + OCT];
@@ -888,9 +892,10 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     int2 *s_stack = (MODE == 6 && LSB_SMEM_STACK) ? reinterpret_cast<int2 *>(smem_raw) + threadIdx.x : nullptr;
     if (MODE == 0 || MODE == 6 || MODE == 7) {
         // Order of the queues.  The kernel ends when its last unit ends, and a few units run ~100 x the median (long grazing
-        // rays, design log section 15), so the LAST queue should hold light units only.  The queues are row-major (channel
-        // by channel): the downward octants (4..7) start with their most grazing rows and end with the steep ones that hit the
-        // ground nearby.  Their fronts are therefore drained early and their light remainders make the tail.
+        // rays, design log section 15), so the launch must END with light units only.  k_scatter_units puts the heavy units
+        // (a ray within ~4 degrees of the horizon or above it) at the front of every queue; the heavy fronts of the downward
+        // octants (4..7) are drained early, together with the sign-mixed and the upward queues, and the light remainders
+        // (steep rays that hit the ground nearby, ~10 us a unit) make the tail: 1.67 -> 1.53 ms for the stage.
         run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
         if (MODE == 6 && LSB_SPLIT_DOWNWARD) {
             run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
@@ -927,6 +932,17 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     }
 }
 
+// Heavy units first (LSB_HEAVY_FIRST): a unit with a ray at or above ~4 degrees below the horizon is "heavy" -- grazing rays
+// fly hundreds of metres along streets and over roofs and cost up to 100 x the median unit (design log, section 15).
+// The queues are filled sensor by sensor, so without this the grazing rows of the LAST sensors sit a few microseconds
+// before the end of a queue and the launch ends with a tail behind them.  Heavy units are queued from the front of
+// their class, the others from the back.  Order of work only: results do not depend on it.
+#ifndef LSB_HEAVY_DZ
+#define LSB_HEAVY_DZ -0.07f
+#endif
+constexpr float kHeavyDz = LSB_HEAVY_DZ;
+constexpr int kUnitHeavy = 0x80;
+
 // ---- octant classification of the 32-ray units (MODE 0) ----------------------------------------------------
 // unit_oct[u - unit_lo] = common octant of the unit's rays (bit k = sign bit of direction component k) or 8 when
 // they disagree; hist[o] = number of units per class.  Only depends on the sensor table: cached by the host.
@@ -936,6 +952,7 @@ __global__ void __launch_bounds__(256) k_classify_units(const SensorDev *__restr
 {
     const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
     int oct = -1;
+    bool heavy = false;
     if (u < unit_hi) {
         const int4 ud = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
         const SensorDev &S = sensors[ud.x];
@@ -946,10 +963,11 @@ __global__ void __launch_bounds__(256) k_classify_units(const SensorDev *__restr
             make_ray(S, world_frame, v, h, r, a, b, c, om);
             const int o = ray_octant(r);
             oct = (oct < 0 || oct == o) ? o : 8;
-            if (oct == 8) break;
+            if (LSB_HEAVY_FIRST) heavy = heavy || r.dz > kHeavyDz;
+            else if (oct == 8) break;
         }
         if (oct < 0) oct = 8;
-        unit_oct[u - unit_lo] = (uint8_t)oct;
+        unit_oct[u - unit_lo] = (uint8_t)(oct | (heavy ? kUnitHeavy : 0));
     }
 #pragma unroll
     for (int o = 0; o < 9; ++o) {
@@ -966,16 +984,24 @@ __global__ void __launch_bounds__(256) k_scatter_units(const SensorDev *__restri
                                                        int4 *__restrict__ unit_list)
 {
     const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
-    const int oct = (u < unit_hi) ? (int)unit_oct[u - unit_lo] : -1;
+    const int raw = (u < unit_hi) ? (int)unit_oct[u - unit_lo] : -1;
+    const int oct = raw < 0 ? -1 : (raw & 15);
+    const bool light = raw >= 0 && LSB_HEAVY_FIRST && !(raw & kUnitHeavy);      // queued from the back of the class
     uint32_t base = 0;
 #pragma unroll
     for (int o = 0; o < 9; ++o) {
-        const unsigned m = __ballot_sync(0xffffffffu, oct == o);
-        if (m == 0) { base += hist[o]; continue; }
-        uint32_t off = 0;
-        if (lane_id() == (unsigned)(__ffs(m) - 1)) off = atomicAdd(&cursor[o], (uint32_t)__popc(m));
-        off = __shfl_sync(0xffffffffu, off, __ffs(m) - 1);
-        if (oct == o) unit_list[base + off + __popc(m & lanemask_lt())] = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
+#pragma unroll
+        for (int back = 0; back < (LSB_HEAVY_FIRST ? 2 : 1); ++back) {
+            const bool mine = oct == o && light == (back != 0);
+            const unsigned m = __ballot_sync(0xffffffffu, mine);
+            if (m == 0) continue;
+            const uint32_t k = (uint32_t)__popc(m);
+            uint32_t off = 0;
+            if (lane_id() == (unsigned)(__ffs(m) - 1)) off = atomicAdd(&cursor[o + 16 * back], k);
+            off = __shfl_sync(0xffffffffu, off, __ffs(m) - 1);
+            if (back) off = hist[o] - off - k;
+            if (mine) unit_list[base + off + __popc(m & lanemask_lt())] = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
+        }
         base += hist[o];
     }
 }
