@@ -24,6 +24,9 @@ namespace lsb {
 #ifndef LSB_HEAVY_FIRST
 #define LSB_HEAVY_FIRST 1         // 1: heavy units (grazing rays) queued at the front of their octant class (k_scatter_units)
 #endif
+#ifndef LSB_PHASE_ORDER
+#define LSB_PHASE_ORDER 1          // 0: mixed, downward heavy fronts, upward, downward rest; 1: mixed, upward, downward heavy fronts, downward rest
+#endif
 #ifndef LSB_SPLIT_DOWNWARD
 #define LSB_SPLIT_DOWNWARD 1     // 1: the heavy fronts (grazing rows, LSB_HEAVY_FIRST) of the downward octant queues are drained before the upward octants
 #endif
@@ -896,13 +899,18 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
         // (a ray within ~4 degrees of the horizon or above it) at the front of every queue; the heavy fronts of the downward
         // octants (4..7) are drained early, together with the sign-mixed and the upward queues, and the light remainders
         // (steep rays that hit the ground nearby, ~10 us a unit) make the tail: 1.67 -> 1.53 ms for the stage.
-        run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
-        if (MODE == 6 && LSB_SPLIT_DOWNWARD) {
+        if (LSB_PHASE_ORDER != 2) run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        if (MODE == 6 && LSB_SPLIT_DOWNWARD && LSB_PHASE_ORDER == 0) {
             run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
             run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
         }
         run_phase<MODE, 0, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 1, STATS>(P, smax, lane, s_list, s_pts, s_stack);
         run_phase<MODE, 2, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 3, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        if (LSB_PHASE_ORDER == 2) run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        if (MODE == 6 && LSB_SPLIT_DOWNWARD && LSB_PHASE_ORDER >= 1) {
+            run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
+        }
         const int rest = (MODE == 6 && LSB_SPLIT_DOWNWARD) ? 2 : 0;
         run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest);
         run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest);

@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--super", default="1", help="two-level lists (supertiles) on / off")
     ap.add_argument("--aspects", default="50")
     ap.add_argument("--scene", default="city", choices=["city", "heightfield"])
+    ap.add_argument("--sway", action="store_true", help="with --recommit: move the geometries as bench.py's frames do")
+    ap.add_argument("--recommit", action="store_true", help="rebuild the scene before every timed launch, as a bench step does (cold L2)")
     args = ap.parse_args()
     from bench import build_workload, frame_affine
     from lidarshooter_b200 import capi
@@ -82,6 +84,11 @@ def main():
                     ms = []
                     for r in range(args.reps + 1):
                         ctx.set_option(capi.OPT_TILE_ENTRIES, te)      # also drops the cached lists: every timed launch rebuilds them
+                        if args.recommit:
+                            if args.sway:
+                                for gi, (name, v_, t_) in enumerate(meshes):
+                                    ctx.update_transform(name, frame_affine(r + 3, gi))
+                            assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
                         assert ctx.trace_batch(0, ns, 0) == 0, ctx.last_error()
                         ms.append(float(ctx.stats().ms_trace))
                     ms = ms[1:]
