@@ -114,10 +114,13 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_trace_sample(meshes, poses, table, n_threads=None, sensors=(0,), repeats=1):
-    """The CPU oracle on the host cores: world-frame transform + binned-SAH BVH build once, then closest-hit trace of
-    the rays of `sensors`.  Returns dict(mrays_trace, t_build, t_trace, rays, cores)."""
-    from oracle import lso
+def cpu_trace_sample(meshes, poses, table, n_threads=None, sensors=(0,), repeats=1, affines=None, gpu_results=None):
+    """The CPU oracle on the host cores: world-frame transform (per-geometry `affines`, identity when None) +
+    binned-SAH BVH build once, then closest-hit trace of the rays of `sensors`.
+    gpu_results: {sensor: (t, tri)} from lsb200_trace_raw of the SAME frame -- compared ray by ray (the parity check of
+    the benchmarked configuration), and the float64 second opinion is run over the same rays (grazing report).
+    Returns dict(mrays_trace, t_build, t_trace, rays, cores[, parity])."""
+    from oracle import lso, grazing
     lso.build()
     if n_threads:
         lso.set_threads(n_threads)
@@ -125,13 +128,16 @@ def cpu_trace_sample(meshes, poses, table, n_threads=None, sensors=(0,), repeats
     elev, b, e, H = table
     t0 = time.perf_counter()
     ident = lso.IDENTITY_AFFINE
+    if affines is None:
+        affines = [ident] * len(meshes)
     s0 = lso.Sensor(elev, b, e, H, poses[0][0], poses[0][1])
-    verts, tris = lso.concat_scene(s0, [(v, t, ident) for _, v, t in meshes], mode=1)
+    verts, tris = lso.concat_scene(s0, [(v, t, a) for (_, v, t), a in zip(meshes, affines)], mode=1)
     t1 = time.perf_counter()
     bvh = lso.Bvh(verts, tris)
     t2 = time.perf_counter()
     rays, t_trace, hits = 0, 0.0, 0
-    for _ in range(repeats):
+    parity = None
+    for rep in range(repeats):
         for si in sensors:
             s = lso.Sensor(elev, b, e, H, poses[si][0], poses[si][1])
             dirs = lso.rotate_dirs(s.R, lso.ray_dirs(s.tables))
@@ -140,9 +146,29 @@ def cpu_trace_sample(meshes, poses, table, n_threads=None, sensors=(0,), repeats
             t_trace += time.perf_counter() - ta
             rays += dirs.shape[0]
             hits += int((tri >= 0).sum())
+            if rep == 0 and gpu_results is not None and si in gpu_results:
+                gt, gtri = gpu_results[si]
+                g = grazing.second_opinion(verts, tris, s.T, dirs, gt, gtri, bvh=bvh)
+                if parity is None:
+                    parity = {"against": "oracle CPU BVH (bit-exact) + float64 second opinion (oracle/grazing.py)",
+                              "sensors": [], "rays": 0, "mismatch_mask": 0, "mismatch_tri": 0, "mismatch_t": 0,
+                              "grazing_rays": 0, "grazing_unexplained": 0, "grazing_by_cause": {"edge": 0, "tie": 0, "edge_on": 0},
+                              "max_edge_ulps": 0.0, "max_rel_range_error_vs_f64": 0.0}
+                parity["sensors"].append(int(si))
+                parity["rays"] += int(dirs.shape[0])
+                parity["mismatch_mask"] += int(((gtri >= 0) != (tri >= 0)).sum())
+                parity["mismatch_tri"] += int((gtri != tri).sum())
+                parity["mismatch_t"] += int((gt.view(np.uint32) != t.view(np.uint32)).sum())
+                parity["grazing_rays"] += g["grazing_rays"]
+                parity["grazing_unexplained"] += g["unexplained"]
+                for k in ("edge", "tie", "edge_on"):
+                    parity["grazing_by_cause"][k] += g[k]
+                parity["max_edge_ulps"] = max(parity["max_edge_ulps"], g["max_edge_ulps"])
+                parity["max_rel_range_error_vs_f64"] = max(parity["max_rel_range_error_vs_f64"],
+                                                           g.get("max_rel_range_error_vs_f64", 0.0))
     bvh.close()
     return {"mrays_trace": rays / t_trace / 1e6, "t_transform": t1 - t0, "t_build": t2 - t1, "t_trace": t_trace,
-            "rays": rays, "hits": hits, "cores": cores, "n_tris": int(tris.shape[0])}
+            "rays": rays, "hits": hits, "cores": cores, "n_tris": int(tris.shape[0]), "parity": parity}
 
 
 def xt32_scan_leg(local, reps=1000, cpu=True):
@@ -333,6 +359,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--small", action="store_true", help="tiny scene for smoke runs (NOT the benchmark)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle / float64 comparison of the benchmarked frame")
     ap.add_argument("--no-xt32", action="store_true", help="skip the XT-32 scan leg (profiling runs of the main step)")
     ap.add_argument("--traversal", type=int, default=None)
     ap.add_argument("--top-nodes", type=int, default=None)
@@ -456,6 +483,18 @@ def main():
     stages["tile_lists"] = round(float(st.ms_tile_lists), 4)
     stages["k_trace"] = round(float(st.ms_trace) - float(st.ms_tile_lists), 4)
 
+    # ---- parity of the benchmarked configuration: per-ray results of one frame, compared with the oracle below ----
+    parity_frame = 3
+    parity_sensors = (0,) if args.small else (0, 27, 63)
+    gpu_results = None
+    if rank == 0 and not args.no_parity:
+        step_resident(parity_frame)
+        gpu_results = {}
+        for si in parity_sensors:
+            rc_, t_, tri_ = ctx.trace_raw(si)
+            assert rc_ == 0, ctx.last_error()
+            gpu_results[si] = (t_, tri_)
+
     # ---- end-to-end leg: host buffers in, host point clouds out --------------------------------------------
     # The public call for a batch of frames is lsb200_run_frames: per frame it uploads every mesh's vertices from
     # pinned host memory, applies the frame's transforms, rebuilds, traces all devices and copies the hit counts and
@@ -500,7 +539,18 @@ def main():
                       "api": "lsb200_run_frames (pipelined: D2H of frame f overlaps frame f+1)"}
     rec = 32
 
-    # ---- roofline of the traversal kernel -------------------------------------------------------------------
+    # ---- roofline ---------------------------------------------------------------------------------------------
+    # Dominant kernels = the trace stage (k_tile_entries + k_trace), timed live above with CUDA events on the launching
+    # stream (ms_trace, every timed step).  Three figures, each <= ~1 by construction, plus the contract's model:
+    #   frac             DRAM bytes the stage really moves (ncu dram__bytes_read + write of THIS build: the capture in
+    #                    profiles/ncu_traffic.json is refused unless it is stamped with this tree's source hash)
+    #                    / ms_trace / measured HBM peak
+    #   algorithmic_frac compulsory bytes of the stage (every node and triangle record once, t + id per ray, one record
+    #                    per hit) / ms_trace / peak
+    #   step_floor_frac  compulsory bytes of the WHOLE step (rebuild 314 B/triangle, SURVEY 8d, + the stage's) /
+    #                    ms_per_step / peak
+    #   contract_frac    SURVEY 8(d)'s per-ray model (a private root-to-leaf path per ray).  Coherent LiDAR rays share
+    #                    that path through the tile lists and L1 / L2, so this one exceeds 1: kept for the record only.
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -508,13 +558,51 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md 6.65 TB/s)"
-    bytes_per_launch = rays_per_step_rank * b_ray(n_tris, hit_fraction)
-    achieved = bytes_per_launch / (ms_trace * 1e-3) / 1e9
-    traffic = None
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from source_hash import source_hash
+    src_hash = source_hash()
+    traffic, ncu_k, ncu_note = None, {}, "no profiles/ncu_traffic.json"
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "trace_traffic.json"))).get("dram_bytes_per_launch")
+        nt = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if nt.get("source_hash") == src_hash:
+            ncu_k = nt["kernels"]
+            traffic = float(ncu_k["k_trace"]["dram_bytes"]) + float(ncu_k.get("k_tile_entries", {}).get("dram_bytes", 0.0))
+            ncu_note = "profiles/ncu_traffic.json (stamped with this build's source hash)"
+        else:
+            ncu_note = (f"profiles/ncu_traffic.json REFUSED: captured from source {nt.get('source_hash')}, "
+                        f"this build is {src_hash}")
     except Exception:
         pass
+    stage_s = ms_trace * 1e-3
+    stage_alg_bytes = (64.0 + 48.0 + 4.0) * n_tris + rays_per_step_rank * (8.0 + rec * hit_fraction)
+    build_alg_bytes = (314.0 if args.commit == "rebuild" else 214.0) * n_tris
+    contract_bytes = rays_per_step_rank * b_ray(n_tris, hit_fraction)
+    roofline = {
+        "kernel": "trace stage = k_tile_entries + k_trace<6> (one launch each per step)", "bound": "hbm",
+        "achieved": (traffic / stage_s / 1e9) if traffic else stage_alg_bytes / stage_s / 1e9,
+        "peak": peak, "unit": "GB/s", "peak_source": peak_src,
+        "traffic": traffic, "traffic_source": ncu_note, "source_hash": src_hash,
+        "ms_per_launch": ms_trace, "rays_per_launch": rays_per_step_rank,
+        "algorithmic_bytes": stage_alg_bytes, "algorithmic_frac": stage_alg_bytes / stage_s / 1e9 / peak,
+        "step_floor_bytes": build_alg_bytes + stage_alg_bytes,
+        "step_floor_frac": (build_alg_bytes + stage_alg_bytes) / (ms_total / args.steps * 1e-3) / 1e9 / peak,
+        "commit_frac": build_alg_bytes / (ms_commit * 1e-3) / 1e9 / peak,
+        "contract_bytes_per_ray": b_ray(n_tris, hit_fraction), "contract_achieved": contract_bytes / stage_s / 1e9,
+        "contract_frac": contract_bytes / stage_s / 1e9 / peak,
+    }
+    roofline["frac"] = roofline["achieved"] / peak
+    roofline["frac_is"] = ("ncu DRAM traffic of this build / live stage time / measured peak" if traffic else
+                           "algorithmic_frac (no valid ncu capture of this build)")
+    if "k_trace" in ncu_k:
+        kt = ncu_k["k_trace"]
+        roofline["actual_bound"] = {
+            "what": "k_trace is latency / issue bound, not bandwidth bound (ncu of this build)",
+            "issue_slots_busy_pct": kt.get("issue_slots_busy_pct"), "warp_exec_eff_threads_of_32": kt.get("warp_exec_eff_threads"),
+            "l1_hit_pct": kt.get("l1_hit_pct"), "l2_hit_pct": kt.get("l2_hit_pct"), "warps_active_pct": kt.get("warps_active_pct"),
+            "registers": kt.get("registers"), "ncu_duration_ms": (kt.get("duration_ns") or 0.0) * 1e-6}
+        roofline["per_kernel"] = {k: {"dram_bytes": v.get("dram_bytes"), "ncu_duration_ms": (v.get("duration_ns") or 0.0) * 1e-6,
+                                      "dram_frac_of_peak": (v.get("dram_bytes", 0.0) / max(v.get("duration_ns", 1.0), 1.0)) / peak}
+                                  for k, v in ncu_k.items()}
 
     line = None
     if rank == 0:
@@ -533,10 +621,7 @@ def main():
             "clocks": clocks,
             "e2e": e2e["xyzi16"], "e2e_pointcloud2_32": e2e["pointcloud2_32"],
             "gpu_launches": launches,
-            "roofline": {"kernel": "trace stage = k_tile_entries + k_trace (stages_ms: tile_lists, k_trace)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "bytes_per_ray": b_ray(n_tris, hit_fraction), "rays_per_launch": rays_per_step_rank,
-                         "ms_per_launch": ms_trace},
+            "roofline": roofline,
         }
     ctx.close()
     if rank == 0 and not args.no_xt32:
@@ -545,12 +630,21 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        if world == 1 and not args.no_cpu_baseline:
-            log("[bench] timing the CPU oracle on the host cores (bounded sample) ...")
-            c = cpu_trace_sample(meshes, poses, table)
+        want_cpu = world == 1 and not args.no_cpu_baseline
+        c = None
+        if want_cpu or gpu_results is not None:
+            log("[bench] CPU oracle on the host cores: parity of the benchmarked frame + bounded timing sample ...")
+            try:      # all the host threads the process may use -- torchrun exports OMP_NUM_THREADS=1 to its workers
+                n_thr = len(os.sched_getaffinity(0))
+            except AttributeError:
+                n_thr = os.cpu_count() or 1
+            c = cpu_trace_sample(meshes, poses, table, n_threads=n_thr, sensors=parity_sensors if gpu_results else (0,),
+                                 affines=[frame_affine(parity_frame, gi) for gi in range(len(names))], gpu_results=gpu_results)
+            line["parity_check"] = c["parity"]
+        if want_cpu:
             line["cpu_baseline"] = {
                 "value": c["mrays_trace"], "unit": "Mrays/s", "cores": c["cores"], "kind": "port",
-                "sample": (f"closest-hit trace of 1 of the {n_sens} devices ({c['rays']} rays) against the same "
+                "sample": (f"closest-hit trace of {len(parity_sensors) if gpu_results else 1} of the {n_sens} devices ({c['rays']} rays) against the same "
                            f"{c['n_tris']}-triangle scene with the oracle's binned-SAH CPU BVH, all host threads; "
                            f"trace only -- CPU transform {c['t_transform']:.2f} s and BVH build {c['t_build']:.2f} s "
                            f"are NOT charged (the GPU value pays its rebuild every frame)"),
@@ -558,6 +652,9 @@ def main():
         else:
             line["cpu_baseline"] = None
         emit_result(line)
+        pc = line.get("parity_check")
+        if pc and (pc["mismatch_mask"] or pc["mismatch_tri"] or pc["mismatch_t"] or pc["grazing_unexplained"]):
+            raise SystemExit(f"bench.py: PARITY FAILURE on the benchmarked configuration: {pc}")
 
 
 if __name__ == "__main__":

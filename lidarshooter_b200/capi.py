@@ -10,6 +10,8 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("LSB200_LIB") or os.path.join(_HERE, "liblsb200.so")   # override: A/B builds of tools/
+# the same library built with -DLSB_LAB: plus every measured-and-rejected variant (A/B tests and tools/ only)
+LAB_LIB_PATH = os.environ.get("LSB200_LAB_LIB") or os.path.join(_HERE, "liblsb200_lab.so")
 
 GEOMETRY_TRIANGLE, GEOMETRY_QUAD = 0, 1
 FRAME_SENSOR, FRAME_WORLD = 0, 1
@@ -54,18 +56,18 @@ class Stats(C.Structure):
                 ("ms_tile_lists", C.c_float), ("reserved0", C.c_int32)]
 
 
-_lib = None
+_libs = {}
 
 
-def lib():
-    """Loads liblsb200.so (raises OSError with the build hint when it is absent)."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
-        raise OSError(f"{LIB_PATH} not found: build it with `make -C lidarshooter_b200` "
+def lib(lab=False):
+    """Loads liblsb200.so -- or, lab=True, liblsb200_lab.so -- (raises OSError with the build hint when it is absent)."""
+    if lab in _libs:
+        return _libs[lab]
+    path = LAB_LIB_PATH if lab else LIB_PATH
+    if not os.path.exists(path):
+        raise OSError(f"{path} not found: build it with `make -C lidarshooter_b200` "
                       "(or __graft_entry__.build()); there is no CPU fallback")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
     vp, f32p, u32p, i32p = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
     L.lsb200_create.argtypes = [C.c_int, C.POINTER(vp)]
     L.lsb200_destroy.argtypes = [vp]
@@ -104,7 +106,7 @@ def lib():
     L.lsb200_debug_copy_bvh.argtypes = [vp, f32p, C.c_int64, i32p, C.c_int64, i32p]
     L.lsb200_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_int64]
     L.lsb200_debug_copy_vertices.argtypes = [vp, f32p, C.c_int64]
-    _lib = L
+    _libs[lab] = L
     return L
 
 
@@ -122,8 +124,8 @@ class Context:
     """Thin object wrapper: one lsb200_ctx.  Methods return the ABI's status codes where the reference's
     interface does (add/remove/commit/trace) and raise Lsb200Error on CUDA failures."""
 
-    def __init__(self, device=0, frame_mode=FRAME_SENSOR, stream=None):
-        self._L = lib()
+    def __init__(self, device=0, frame_mode=FRAME_SENSOR, stream=None, lab=False):
+        self._L = lib(lab)
         h = C.c_void_p()
         rc = self._L.lsb200_create(int(device), C.byref(h))
         if rc != 0:

@@ -108,6 +108,10 @@ struct lsb200_ctx {
     int n_verts = 0, n_tris = 0;
     lsb200_stats stats{};
     cudaEvent_t ev[12] = {};
+    // per-device kernel state (function attributes / occupancy are per device, never per process)
+    bool trace_attr_set[16] = {};
+    int trace_occ[16] = {};
+    size_t trace_occ_smem[16] = {};
     std::string err;
     std::mutex mtx;
 };
@@ -248,6 +252,14 @@ int lsb200_create(int cuda_device, lsb200_ctx **out)
     c->device = cuda_device;
     DeviceGuard dg(cuda_device);
     cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
+    // kernels that need more than 48 KB of dynamic shared memory: the opt-in is a per-DEVICE attribute
+    if (rsort::prepare_device() != cudaSuccess ||
+#ifdef LSB_LAB
+        cudaFuncSetAttribute(k_fit_rmq, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RmqTable)) != cudaSuccess ||
+#endif
+        cudaFuncSetAttribute(k_build_small, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallMaxTris * 4) != cudaSuccess) {
+        delete c; return LSB200_ERR_CUDA;
+    }
     if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
     c->stream = c->own_stream;
     for (auto &e : c->ev) cudaEventCreate(&e);
@@ -308,12 +320,21 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     if (!c) return LSB200_ERR_INVALID;
     std::lock_guard<std::mutex> lk(c->mtx);
     switch (option) {
+#ifdef LSB_LAB
     case LSB200_OPT_TRAVERSAL: if (value < 0 || value > 7) break; c->opt_traversal = value; return LSB200_OK;
     case LSB200_OPT_TRACE_STATS: c->opt_stats = value ? 1 : 0; return LSB200_OK;
-    case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
     case LSB200_OPT_FIT_RMQ: c->opt_fit_rmq = value ? 1 : 0; return LSB200_OK;
-    case LSB200_OPT_TILE_ENTRIES: if (value < 0 || value > kMaxTileEntries || value == 1) break; c->opt_tile_entries = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_SUPER_TILES: c->opt_super_tiles = value ? 1 : 0; c->tile_commit_epoch = -1; return LSB200_OK;
+#else
+    // product build: the shipped traversal (6) and brute force (3); the evidence variants, the instrumented launches,
+    // the range-query fit and the two-level lists live in liblsb200_lab.so (make lab)
+    case LSB200_OPT_TRAVERSAL: if (value != 6 && value != 3) return fail(c, LSB200_ERR_INVALID, "traversal variant %d is built into liblsb200_lab.so only", value); c->opt_traversal = value; return LSB200_OK;
+    case LSB200_OPT_TRACE_STATS: case LSB200_OPT_FIT_RMQ: case LSB200_OPT_SUPER_TILES:
+        if (value) return fail(c, LSB200_ERR_INVALID, "option %d is built into liblsb200_lab.so only", option);
+        return LSB200_OK;
+#endif
+    case LSB200_OPT_ORIGIN_CHAIN: c->opt_chain = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_TILE_ENTRIES: if (value < 0 || value > kMaxTileEntries || value == 1) break; c->opt_tile_entries = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_TILE_MIN_UNITS: if (value < 0) break; c->opt_tile_min_units = value; return LSB200_OK;
     case LSB200_OPT_TILE_VISITS: if (value < 0 || value > 4096) break; c->opt_tile_visits = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
@@ -548,11 +569,6 @@ static int commit_locked(lsb200_ctx *c, int mode)
     auto mark = [&]() { if (timing) cudaEventRecord(c->ev[evi++], st); };
 
     if (small) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            LSB_CU(c, cudaFuncSetAttribute(k_build_small, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallMaxTris * 4));
-            attr_set = true;
-        }
         SmallArgs args;
         std::memcpy(args.geoms, c->h_geoms.data(), ng * sizeof(GeomDesc));
         if (c->frame_mode == LSB200_FRAME_SENSOR) { std::memcpy(args.RinvT, c->sensors[0].Rinv, 36); std::memcpy(args.RinvT + 9, c->sensors[0].T, 12); }
@@ -623,11 +639,12 @@ static int commit_locked(lsb200_ctx *c, int mode)
         mark();
     }
     // (5) leaf records + bottom-up boxes
+#ifdef LSB_LAB
     if (c->opt_fit_rmq) {
-        static bool attr_set = false;
-        if (!attr_set) { LSB_CU(c, cudaFuncSetAttribute(k_fit_rmq, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RmqTable))); attr_set = true; }
         k_fit_rmq<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, sizeof(RmqTable), st>>>(S, S.vals);
-    } else {
+    } else
+#endif
+    {
         k_fit<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, 0, st>>>(S, S.vals);
     }
     count_launch(c);
@@ -755,17 +772,18 @@ static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
 {
     constexpr bool TOP = (MODE == 4);
     const size_t smem = TOP ? (size_t)P.top_cap * 64 : (MODE == 6 ? (size_t)LSB_SMEM_STACK * kTraceThreads * sizeof(int2) : 0);
-    static bool attr_set = false;          // one flag per instantiation
-    if ((TOP || (MODE == 6 && LSB_SMEM_STACK)) && !attr_set) {
+    // function attributes and occupancy are per DEVICE, so they are cached per context (one slot per instantiation)
+    constexpr int kSlot = MODE * 2 + (STATS ? 1 : 0);
+    if ((TOP || (MODE == 6 && LSB_SMEM_STACK)) && !c->trace_attr_set[kSlot]) {
         LSB_CU(c, cudaFuncSetAttribute(k_trace<MODE, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
+        c->trace_attr_set[kSlot] = true;
     }
     int grid;
     if (MODE == 2) {
         grid = (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32);
     } else {
         int per_sm = c->opt_ctas_per_sm;
-        static int occ = 0; static size_t occ_smem = ~size_t(0);      // one query per instantiation and smem size
+        int &occ = c->trace_occ[kSlot]; size_t &occ_smem = c->trace_occ_smem[kSlot];   // one query per instantiation and smem size
         if (per_sm <= 0) {
             if (occ <= 0 || occ_smem != smem) {
                 LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<MODE, STATS>, kTraceThreads, smem));
@@ -788,13 +806,15 @@ template <bool STATS>
 static int launch_trace_mode(lsb200_ctx *c, const TraceParams &P, int n_units, int mode)
 {
     switch (mode) {
+#ifdef LSB_LAB
     case 0: return launch_trace<0, STATS>(c, P, n_units);
     case 1: return launch_trace<1, STATS>(c, P, n_units);
     case 2: return launch_trace<2, STATS>(c, P, n_units);
-    case 3: return launch_trace<3, STATS>(c, P, n_units);
     case 4: return launch_trace<4, STATS>(c, P, n_units);
     case 5: return launch_trace<5, STATS>(c, P, n_units);
     case 7: return launch_trace<7, STATS>(c, P, n_units);
+#endif
+    case 3: return launch_trace<3, STATS>(c, P, n_units);
     default: return launch_trace<6, STATS>(c, P, n_units);
     }
 }
@@ -816,7 +836,8 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         for (int i = first; i < first + count; ++i) {
             Sensor &s = c->sensors[i];
             LSB_CU(c, cudaMemsetAsync(s.tri.p, 0xFF, (size_t)s.n_rays() * 4, st));          // -1
-            LSB_CU(c, cudaMemsetAsync(s.t.p, 0, (size_t)s.n_rays() * 4, st));
+            k_fill_u32<<<(unsigned)((s.n_rays() + 255) / 256), 256, 0, st>>>(s.t.as<uint32_t>(), 0x7f800000u, s.n_rays());   // +inf
+            count_launch(c);
         }
         return fail(c, LSB200_ERR_EMPTY_SCENE, "trace_scene: empty scene");
     }
@@ -922,10 +943,12 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
             if (iv_stale) {
                 k_tile_intervals<<<(unsigned)((n_units + 127) / 128), 128, 0, st>>>(P);
                 count_launch(c);
+#ifdef LSB_LAB
                 if (c->opt_super_tiles) {
                     k_super_intervals<<<(unsigned)((sup_hi - sup_lo + 3) / 4), 128, 0, st>>>(P, first, count, sup_lo, sup_hi);
                     count_launch(c);
                 }
+#endif
                 c->iv_sensors_epoch = c->sensors_epoch; c->iv_first = first; c->iv_count = count; c->iv_world = wf; c->iv_super = c->opt_super_tiles; c->iv_units_id = c->units_build_id;
             }
         }
@@ -940,6 +963,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         if (stale || c->opt_stats) {
             const unsigned blocks = (unsigned)((n_units + kTileBlock - 1) / kTileBlock);
             if (timing) { cudaEventRecord(c->ev[11], st); tile_timed = true; }
+#ifdef LSB_LAB
             if (c->opt_super_tiles) {
                 const unsigned sblocks = (unsigned)((sup_hi - sup_lo + 127) / 128);
                 if (c->opt_stats) k_super_entries<true><<<sblocks, 128, 0, st>>>(P, first, count, sup_lo, sup_hi, 8 * kMaxTileEntries);
@@ -947,18 +971,20 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
                 count_launch(c);
             }
             if (c->opt_stats) k_tile_entries<true><<<blocks, kTileBlock, 0, st>>>(P, max_visits);
-            else k_tile_entries<false><<<blocks, kTileBlock, 0, st>>>(P, max_visits);
+            else
+#endif
+            k_tile_entries<false><<<blocks, kTileBlock, 0, st>>>(P, max_visits);
             count_launch(c);
             c->tile_commit_epoch = c->commit_epoch; c->tile_sensors_epoch = c->sensors_epoch; c->tile_first = first; c->tile_count = count;
             c->tile_cap = cap; c->tile_visits = max_visits; c->tile_units_id = c->units_build_id;
             if (timing) cudaEventRecord(c->ev[7], st);
         }
     }
-    if (c->opt_stats) {
-        rc = launch_trace_mode<true>(c, P, n_units, mode);
-    } else {
-        rc = launch_trace_mode<false>(c, P, n_units, mode);
-    }
+#ifdef LSB_LAB
+    if (c->opt_stats) rc = launch_trace_mode<true>(c, P, n_units, mode);
+    else
+#endif
+    rc = launch_trace_mode<false>(c, P, n_units, mode);
     if (rc) return rc;
     if (timing) cudaEventRecord(c->ev[9], st);
     if ((flags & LSB200_TRACE_ORDERED) && !(flags & LSB200_TRACE_NO_POINTS)) {

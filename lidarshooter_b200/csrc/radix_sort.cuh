@@ -203,6 +203,13 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
     }
 }
 
+// Function attributes are per DEVICE: every context calls this once for its own device (lsb200_create), so that a
+// process may hold contexts on several GPUs.
+inline cudaError_t prepare_device()
+{
+    return cudaFuncSetAttribute(k_onesweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * kTile * sizeof(uint32_t)));
+}
+
 // Sorts n pairs.  keys/vals: input and (after the call) output; keys_tmp/vals_tmp: ping-pong buffers of n.
 // scratch: scratch_words(n) uint32.  `passes` 8-bit passes starting at bit 0 (4 covers 32 bits; an even
 // number leaves the result in keys/vals).  Returns the number of kernel launches issued.
@@ -219,8 +226,6 @@ inline int sort_pairs(uint32_t *keys, uint32_t *vals, uint32_t *keys_tmp, uint32
     const int hist_blocks = (int)(hb < kSmCount * 8 ? hb : kSmCount * 8);
     k_histogram<<<hist_blocks, kThreads, 0, stream>>>(keys, n, ghist);
     k_scan_histograms<<<1, kPasses * 32, 0, stream>>>(ghist);
-    static bool attr_set = false;
-    if (!attr_set) { cudaFuncSetAttribute(k_onesweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * kTile * sizeof(uint32_t))); attr_set = true; }
     uint32_t *ki = keys, *vi = vals, *ko = keys_tmp, *vo = vals_tmp;
     for (int p = 0; p < kPasses; ++p) {
         k_onesweep<<<(unsigned)tiles, kThreads, 2 * kTile * sizeof(uint32_t), stream>>>(ki, vi, ko, vo, n, p * kRadixBits, ghist + p * kRadix,

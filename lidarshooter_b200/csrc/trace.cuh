@@ -132,6 +132,8 @@ __device__ __forceinline__ float2 ldg_f2_hint(const float2 *a, uint64_t pol)
 struct Ray {
     float ox, oy, oz, dx, dy, dz;
 };
+__device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, float &best, int &bi);   // depth-guard fallback
+constexpr int kRayOverflow = -2;       // trace_ray_lz: "my stack overflowed" (never a triangle id)
 
 // Embree-ordered Moeller-Trumbore, bit-identical to lso_intersect().  q0..q2 = the 48-byte triangle record.
 __device__ __forceinline__ bool intersect_tri(const float4 q0, const float4 q1, const float4 q2, const Ray &r, float &t_out)
@@ -211,6 +213,7 @@ __device__ __forceinline__ void slab_nf(float l0, float h0, float l1, float h1, 
 // = min (t, triangle id) does not depend on the visiting order, so results are unchanged.
 // kMaxChain (entries per list, 2 x float4 each) and the walk itself live in build.cuh: origin_chain_walk.
 
+#ifdef LSB_LAB   // evidence variants (modes 0, 1, 2, 4, 5): built into liblsb200_lab.so only
 // Closest hit of one ray.  TOP: node references below n_top are read from the shared-memory copy.
 // OCT 0..7: sign-specialised slab test (the caller guarantees the ray's direction signs); 8: generic.
 // chain / n_chain: the sensor's origin-chain list (n_chain == 0: start at the root).
@@ -237,6 +240,7 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
     // hit has been found it is dropped without loading the node
     int2 stack[kStackSize];
     int sp = 0;
+    bool ovf = false;
     if (n_chain > 0) {
         for (int k = 0; k < n_chain; ++k) {
             const float4 e0 = __ldg(chain + 2 * k), e1 = __ldg(chain + 2 * k + 1);
@@ -244,11 +248,11 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
             slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
                          fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
             if (STATS) ++rs.chain_tests;
-            if (n <= f) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n));
+            if (n <= f) { if (sp < kStackSize) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n)); else ovf = true; }
         }
         if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
     } else {
-        stack[sp++] = make_int2((TOP && n_top > 0) ? 0 : cap, 0);      // root: top slot 0, or Karras node 0
+        { if (sp < kStackSize) stack[sp++] = make_int2((TOP && n_top > 0) ? 0 : cap, 0); else ovf = true; }      // root: top slot 0, or Karras node 0
     }
     while (true) {
         int cur = 0;
@@ -284,7 +288,7 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
             if (hit0 && hit1) {
                 const bool swap = n1 < n0;
                 cur = swap ? c1 : c0;
-                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                { if (sp < kStackSize) stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1)); else ovf = true; }
                 if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
             } else if (hit0) {
                 cur = c0;
@@ -295,6 +299,7 @@ __device__ __forceinline__ void trace_ray(const TraceParams &P, const float4 *s_
             }
         }
     }
+    if (ovf) brute_ray(P, r, best, bi);          // depth guard tripped (see trace_ray_lz)
     best_out = best;
     bi_out = bi;
 }
@@ -318,6 +323,7 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
     int bi = -1;
     int2 stack[kStackSize];
     int sp = 0;
+    bool ovf = false;
     int cur = P.top_cap;
     if (n_chain > 0) {
         // sensor chains are listed far -> near, tile lists (k_tile_entries) near -> far: the nearest entry ends on top
@@ -330,7 +336,7 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
             slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
                          fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
             if (STATS) ++rs.chain_tests;
-            if (n <= f) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n));
+            if (n <= f) { if (sp < kStackSize) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n)); else ovf = true; }
         }
         if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
         cur = sp > 0 ? stack[--sp].x : kDone;
@@ -351,7 +357,7 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
             if (hit0 && hit1) {
                 const bool swap = n1 < n0;
                 cur = swap ? c1 : c0;
-                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                { if (sp < kStackSize) stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1)); else ovf = true; }
                 if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
             } else if (hit0) {
                 cur = c0;
@@ -378,9 +384,13 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
             }
         }
     }
+    if (ovf) brute_ray(P, r, best, bi);          // depth guard tripped (see trace_ray_lz)
     best_out = best;
     bi_out = bi;
 }
+
+#endif  // LSB_LAB
+
 
 // Lazy-list form of trace_ray_ww (variant 6 with LSB_LAZY_LIST): instead of testing every list entry up front and
 // pushing the ones the ray enters (one 8-byte local-memory store per entry and lane -- written through to L2: 2.6 GB
@@ -407,15 +417,27 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
     int bi = -1;
     int2 stack[kStackSize];
     int sp = 0;
+    // Depth guard: a Karras tree over n coincident centroids is ~32 + log2(n) deep, so kStackSize deferred children are
+    // enough for anything but an adversarial scene.  A ray that would overflow drops the push, remembers it (sp gets
+    // the sentinel bit kOvf, popped entries are unaffected) and is re-done by brute force below: never an
+    // out-of-bounds write, never a wrong result.
+    constexpr int kOvf = 1 << 20;
 #if LSB_SMEM_STACK
-    // evidence variant: the first LSB_SMEM_STACK entries of the stack live in shared memory ([slot][thread]: no bank
-    // conflicts), deeper ones in the local array
-    auto push = [&](int2 v) { if (sp < LSB_SMEM_STACK) s_stack[sp * kTraceThreads] = v; else stack[sp] = v; ++sp; };
-    auto pop = [&]() -> int2 { --sp; return sp < LSB_SMEM_STACK ? s_stack[sp * kTraceThreads] : stack[sp]; };
+    // the first LSB_SMEM_STACK entries of the stack live in shared memory ([slot][thread]: no bank conflicts), deeper
+    // ones in the local array
+    auto push = [&](int2 v) {
+        const int d = sp & (kOvf - 1);
+        if (d < LSB_SMEM_STACK) s_stack[d * kTraceThreads] = v;
+        else if (d < kStackSize) stack[d] = v;
+        else { sp |= kOvf; return; }
+        ++sp;
+    };
+    auto pop = [&]() -> int2 { --sp; const int d = sp & (kOvf - 1); return d < LSB_SMEM_STACK ? s_stack[d * kTraceThreads] : stack[d]; };
 #else
-    auto push = [&](int2 v) { stack[sp++] = v; };
-    auto pop = [&]() -> int2 { return stack[--sp]; };
+    auto push = [&](int2 v) { const int d = sp & (kOvf - 1); if (d < kStackSize) { stack[d] = v; ++sp; } else sp |= kOvf; };
+    auto pop = [&]() -> int2 { --sp; return stack[sp & (kOvf - 1)]; };
 #endif
+    auto depth = [&]() -> int { return sp & (kOvf - 1); };
     // sensor chains are listed far -> near (walked backwards), tile lists near -> far
     const float4 *e = reversed ? chain : chain + 2 * (n_chain - 1);
     const int step = reversed ? 2 : -2;
@@ -455,14 +477,14 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
                 const bool swap = n1 < n0;
                 cur = swap ? c1 : c0;
                 push(make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1)));
-                if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
+                if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)depth());
             } else if (hit0) {
                 cur = c0;
             } else if (hit1) {
                 cur = c1;
             } else {
                 cur = kDone;
-                while (sp > 0) {
+                while (depth() > 0) {
                     const int2 t = pop();
                     if (__int_as_float(t.y) <= far_lim * 1.0000005f) { cur = t.x; break; }
                     if (STATS) ++rs.culled;
@@ -474,17 +496,19 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
             test_leaf(P, cur, r, best, bi);
             far_lim = best * 1.0000005f;
             cur = kDone;
-            while (sp > 0) {
+            while (depth() > 0) {
                 const int2 t = pop();
                 if (__int_as_float(t.y) <= far_lim * 1.0000005f) { cur = t.x; break; }
                 if (STATS) ++rs.culled;
             }
         }
     }
+    if (sp & kOvf) bi = kRayOverflow;                 // depth guard tripped: process_unit re-does this ray exhaustively
     best_out = best;
     bi_out = bi;
 }
 
+#ifdef LSB_LAB
 // Single-loop form for the tile-list regime (variant 7): a step of a lane is whatever its next item is -- a node visit
 // or a leaf test -- so a warp needs max-over-lanes(items) dependent memory round trips per unit instead of the
 // while-while form's (node rounds + leaf rounds).  More instructions issued (both bodies per mixed step), fewer
@@ -505,6 +529,7 @@ __device__ __forceinline__ void trace_ray_il(const TraceParams &P, float eps, co
     int bi = -1;
     int2 stack[kStackSize];
     int sp = 0;
+    bool ovf = false;
     int cur = P.top_cap;
     if (n_chain > 0) {
         const float4 *e = reversed ? chain + 2 * (n_chain - 1) : chain;
@@ -515,7 +540,7 @@ __device__ __forceinline__ void trace_ray_il(const TraceParams &P, float eps, co
             slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
                          fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
             if (STATS) ++rs.chain_tests;
-            if (n <= f) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n));
+            if (n <= f) { if (sp < kStackSize) stack[sp++] = make_int2(__float_as_int(e1.z), __float_as_int(n)); else ovf = true; }
         }
         if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
         cur = sp > 0 ? stack[--sp].x : kDone;
@@ -537,7 +562,7 @@ __device__ __forceinline__ void trace_ray_il(const TraceParams &P, float eps, co
             if (hit0 && hit1) {
                 const bool swap = n1 < n0;
                 cur = swap ? c1 : c0;
-                stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1));
+                { if (sp < kStackSize) stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1)); else ovf = true; }
                 if (STATS) rs.max_sp = max(rs.max_sp, (unsigned)sp);
             } else if (hit0) {
                 cur = c0;
@@ -561,9 +586,12 @@ __device__ __forceinline__ void trace_ray_il(const TraceParams &P, float eps, co
             }
         }
     }
+    if (ovf) brute_ray(P, r, best, bi);          // depth guard tripped (see trace_ray_lz)
     best_out = best;
     bi_out = bi;
 }
+
+#endif  // LSB_LAB
 
 // Brute force over all leaf-ordered triangles (validation variant; also the tiny-scene path).
 __device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, float &best, int &bi)
@@ -577,6 +605,14 @@ __device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, fl
             if (t < best || g < bi) { best = t; bi = g; }
         }
     }
+}
+
+// Out-of-line copy for the depth-guard fallback (adversarial scenes only): kept out of the traversal's register budget.
+__device__ __noinline__ void brute_ray_cold(const float4 *tris, const int32_t *leaf_ids, int n_tris, const Ray &r, float &best, int &bi)
+{
+    TraceParams P{};
+    P.tris = tris; P.leaf_ids = leaf_ids; P.n_tris = n_tris;
+    brute_ray(P, r, best, bi);
 }
 
 __device__ __forceinline__ int find_sensor_by_unit(const SensorDev *s, int n, int unit)
@@ -706,6 +742,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
         else {
             const int list = si * 9 + OCT;
             const int n_chain = P.chain_counts ? __ldg(P.chain_counts + list) : 0;
+#ifdef LSB_LAB
             if (MODE == 7) {
                 if (w_tile) trace_ray_il<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
                 else trace_ray_il<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
@@ -718,7 +755,13 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             else if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
             else
             trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
+#else
+            // product build: the one shipped traversal (variant 6, lazy tile / chain list)
+            if (w_tile) trace_ray_lz<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs, s_stack);
+            else trace_ray_lz<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs, s_stack);
+#endif
         }
+        if (bi == kRayOverflow) brute_ray_cold(P.tris, P.leaf_ids, P.n_tris, r, best, bi);
         if (!(best <= S.max_range)) { best = INFINITY; bi = -1; }                // detection radius (closest hit beyond it: no return)
         __stcs(S.t_out + ray, best);
         __stcs(S.tri_out + ray, bi);
@@ -1200,6 +1243,7 @@ __global__ void __launch_bounds__(128) k_tile_intervals(TraceParams P)
     P.tile_iv[2 * (size_t)slot + 1] = make_float4(dhi[0], dhi[1], dhi[2], omax);
 }
 
+#ifdef LSB_LAB
 __global__ void __launch_bounds__(128) k_super_intervals(TraceParams P, int s_first, int s_count, int sup_lo, int sup_hi)
 {
     const int sup = sup_lo + (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
@@ -1239,6 +1283,8 @@ __global__ void __launch_bounds__(128) k_super_intervals(TraceParams P, int s_fi
         P.sup_iv[2 * (size_t)sup + 1] = make_float4(dhi[0], dhi[1], dhi[2], omax);
     }
 }
+
+#endif  // LSB_LAB
 
 // The walk: seeds (a list of (box, reference) entries -- the sensor's origin chain, far -> near, or the supertile's
 // list, near -> far) are filtered with the block's interval test, then refined near-first until `cap` entries are
@@ -1320,6 +1366,7 @@ __device__ __forceinline__ float scene_smax(const uint32_t *__restrict__ bounds)
     return smax;
 }
 
+#ifdef LSB_LAB
 // One thread per supertile of the traced sensors [s_first, s_first + s_count): list of <= kMaxTileEntries entries from
 // the sensor's origin chain.  sup_counts: entries, or kTileFallback (sign-mixed block / interval touching 0 / too
 // many seeds).
@@ -1347,6 +1394,8 @@ __global__ void __launch_bounds__(128) k_super_entries(TraceParams P, int s_firs
     P.sup_counts[sup] = (uint8_t)(n_out < 0 ? kTileFallback : n_out);
     if (STATS) atomicAdd(P.counters + kCntSuperVisits, (unsigned long long)visits);
 }
+
+#endif  // LSB_LAB
 
 // One thread per queue entry (32-ray tile).  tile_counts: entries, or kTileFallback.
 template <bool STATS>
@@ -1399,6 +1448,13 @@ __global__ void __launch_bounds__(kTileBlock) k_tile_entries(TraceParams P, int 
             if (n_out == 0) atomicAdd(P.counters + kCntTileEmpty, 1ull);
         }
     }
+}
+
+// 32-bit fill (empty-scene results: t = +inf)
+__global__ void __launch_bounds__(256) k_fill_u32(uint32_t *__restrict__ p, uint32_t v, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
 }
 
 // ---- ordered compaction: count -> scan -> scatter (points in ray-id order) ---------------------------------

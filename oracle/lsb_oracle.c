@@ -524,6 +524,119 @@ LSO_API void lso_trace_bvh(const lso_bvh *bvh, const float *orgs, int org_stride
         trace_one(bvh, orgs + (size_t)org_stride * r, dirs + 3 * r, &t_out[r], &tri_out[r]);
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Float64 SECOND OPINION (not a restatement of anything in the reference): textbook Moeller-Trumbore 1997
+ * in double precision on the ORIGINAL float32 vertices, closest hit = lexicographic min of (t, triangle id),
+ * through the same CPU BVH (slabs evaluated in double on the padded boxes).  tests/ and bench.py run it over
+ * the same rays as the fp32 oracle; the rays where the two disagree in hit mask or triangle id are the
+ * "grazing" rays north_star asks to be counted and reported -- each is then shown (tests/grazing.py) to pass
+ * within a few fp32 ulp of a triangle edge, of a plane seen edge-on, or of a tie between two triangles.
+ * uvw_out (optional, nR x 3): barycentrics (u, v) and det of the accepted hit.
+ * ---------------------------------------------------------------------------------------------- */
+static inline int mt_f64(const float *a, const float *b, const float *c, const double *o, const double *d,
+                         double *t_out, double *u_out, double *v_out, double *det_out)
+{
+    const double e1[3] = {(double)b[0] - a[0], (double)b[1] - a[1], (double)b[2] - a[2]};
+    const double e2[3] = {(double)c[0] - a[0], (double)c[1] - a[1], (double)c[2] - a[2]};
+    const double p[3] = {d[1] * e2[2] - d[2] * e2[1], d[2] * e2[0] - d[0] * e2[2], d[0] * e2[1] - d[1] * e2[0]};
+    const double det = e1[0] * p[0] + e1[1] * p[1] + e1[2] * p[2];
+    *det_out = det;
+    if (det == 0.0) return 0;
+    const double inv = 1.0 / det;
+    const double tv[3] = {o[0] - a[0], o[1] - a[1], o[2] - a[2]};
+    const double u = (tv[0] * p[0] + tv[1] * p[1] + tv[2] * p[2]) * inv;
+    const double q[3] = {tv[1] * e1[2] - tv[2] * e1[1], tv[2] * e1[0] - tv[0] * e1[2], tv[0] * e1[1] - tv[1] * e1[0]};
+    const double v = (d[0] * q[0] + d[1] * q[1] + d[2] * q[2]) * inv;
+    const double t = (e2[0] * q[0] + e2[1] * q[1] + e2[2] * q[2]) * inv;
+    *u_out = u; *v_out = v; *t_out = t;
+    if (u < 0.0 || v < 0.0 || u + v > 1.0) return 0;
+    if (!(t > 0.0) || !(t <= DBL_MAX)) return 0;
+    return 1;
+}
+
+/* Barycentrics of ray r against triangle tri_ids[r] in double, hit or not (u, v, t, det per ray; NaN for id < 0). */
+LSO_API void lso_bary_f64(const float *verts, const uint32_t *tris, const float *orgs, int org_stride, const float *dirs,
+                          const int32_t *tri_ids, int64_t nR, double *uvtd_out)
+{
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < nR; ++r) {
+        double *out = uvtd_out + 4 * r;
+        if (tri_ids[r] < 0) { out[0] = out[1] = out[2] = out[3] = NAN; continue; }
+        const uint32_t *tv = tris + 3 * (size_t)tri_ids[r];
+        const float *of = orgs + (size_t)org_stride * r, *df = dirs + 3 * r;
+        const double o[3] = {of[0], of[1], of[2]}, d[3] = {df[0], df[1], df[2]};
+        double t = NAN, u = NAN, v = NAN, det = 0.0;
+        mt_f64(verts + 3 * (size_t)tv[0], verts + 3 * (size_t)tv[1], verts + 3 * (size_t)tv[2], o, d, &t, &u, &v, &det);
+        out[0] = u; out[1] = v; out[2] = t; out[3] = det;
+    }
+}
+
+static inline int slab_f64(const lso_node *n, const double *o, const double *inv, double tbest)
+{
+    double t0 = 0.0, t1 = tbest;
+    for (int k = 0; k < 3; ++k) {
+        double a = ((double)n->lo[k] - o[k]) * inv[k];
+        double b = ((double)n->hi[k] - o[k]) * inv[k];
+        double mn = a < b ? a : b, mx = a < b ? b : a;
+        if (mn != mn) mn = -INFINITY;
+        if (mx != mx) mx = INFINITY;
+        if (mn > t0) t0 = mn;
+        if (mx < t1) t1 = mx;
+    }
+    return t0 <= t1 * (1.0 + 1e-9);
+}
+
+LSO_API void lso_trace_bvh_f64(const lso_bvh *bvh, const float *verts, const uint32_t *tris, const float *orgs,
+                               int org_stride, const float *dirs, int64_t nR, double *t_out, int32_t *tri_out)
+{
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t r = 0; r < nR; ++r) {
+        const float *of = orgs + (size_t)org_stride * r, *df = dirs + 3 * r;
+        const double o[3] = {of[0], of[1], of[2]}, d[3] = {df[0], df[1], df[2]};
+        const double inv[3] = {1.0 / d[0], 1.0 / d[1], 1.0 / d[2]};
+        double best = INFINITY; int32_t bi = -1;
+        if (bvh->n_tris > 0) {
+            int32_t stack[128]; int sp = 0;
+            stack[sp++] = 0;
+            while (sp) {
+                const lso_node *n = &bvh->nodes[stack[--sp]];
+                if (!slab_f64(n, o, inv, best)) continue;
+                if (n->count) {
+                    for (int32_t i = n->left; i < n->left + n->count; ++i) {
+                        const int32_t g = bvh->tri_ids[i];
+                        const uint32_t *tv = tris + 3 * (size_t)g;
+                        double t, u, v, det;
+                        if (mt_f64(verts + 3 * (size_t)tv[0], verts + 3 * (size_t)tv[1], verts + 3 * (size_t)tv[2], o, d, &t, &u, &v, &det))
+                            if (t < best || (t == best && g < bi)) { best = t; bi = g; }
+                    }
+                } else if (sp < 126) {
+                    stack[sp++] = n->left; stack[sp++] = n->left + 1;
+                }
+            }
+        }
+        t_out[r] = best; tri_out[r] = bi;
+    }
+}
+
+/* Brute-force form of the same (small scenes). */
+LSO_API void lso_trace_brute_f64(const float *verts, const uint32_t *tris, int64_t nT, const float *orgs, int org_stride,
+                                 const float *dirs, int64_t nR, double *t_out, int32_t *tri_out)
+{
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t r = 0; r < nR; ++r) {
+        const float *of = orgs + (size_t)org_stride * r, *df = dirs + 3 * r;
+        const double o[3] = {of[0], of[1], of[2]}, d[3] = {df[0], df[1], df[2]};
+        double best = INFINITY; int32_t bi = -1;
+        for (int64_t i = 0; i < nT; ++i) {
+            const uint32_t *tv = tris + 3 * (size_t)i;
+            double t, u, v, det;
+            if (mt_f64(verts + 3 * (size_t)tv[0], verts + 3 * (size_t)tv[1], verts + 3 * (size_t)tv[2], o, d, &t, &u, &v, &det))
+                if (t < best) { best = t; bi = (int32_t)i; }
+        }
+        t_out[r] = best; tri_out[r] = bi;
+    }
+}
+
 /* Reference-faithful threading (SRC/EmbreeTracer.cpp:304-313): fixed thread count. */
 LSO_API void lso_set_threads(int n)
 {

@@ -56,6 +56,10 @@ def lib():
         L.lso_bvh_node_count.argtypes = [C.c_void_p]
         L.lso_bvh_node_count.restype = C.c_int64
         L.lso_trace_bvh.argtypes = [C.c_void_p, f32p, C.c_int, f32p, C.c_int64, f32p, i32p]
+        f64p = C.POINTER(C.c_double)
+        L.lso_trace_bvh_f64.argtypes = [C.c_void_p, f32p, u32p, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
+        L.lso_trace_brute_f64.argtypes = [f32p, u32p, C.c_int64, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
+        L.lso_bary_f64.argtypes = [f32p, u32p, f32p, C.c_int, f32p, i32p, C.c_int64, f64p]
         L.lso_set_threads.argtypes = [C.c_int]
         L.lso_max_threads.restype = C.c_int
         L.lso_pack_points.argtypes = [f32p, f32p, i32p, C.c_int64, C.c_int, C.c_int, u8p]
@@ -172,6 +176,30 @@ def trace_brute(verts, tris, orgs, dirs):
     return t, tri
 
 
+def trace_brute_f64(verts, tris, orgs, dirs):
+    verts, dirs = _f32(verts).reshape(-1, 3), _f32(dirs).reshape(-1, 3)
+    tris = np.ascontiguousarray(tris, dtype=np.uint32).reshape(-1, 3)
+    nR = dirs.shape[0]
+    o, stride = _origins(orgs, nR)
+    t, tri = np.empty(nR, np.float64), np.empty(nR, np.int32)
+    lib().lso_trace_brute_f64(_p(verts, C.c_float), _p(tris, C.c_uint32), tris.shape[0], _p(o, C.c_float), stride,
+                              _p(dirs, C.c_float), nR, _p(t, C.c_double), _p(tri, C.c_int32))
+    return t, tri
+
+
+def bary_f64(verts, tris, orgs, dirs, tri_ids):
+    """(u, v, t, det) in float64 of every ray against triangle tri_ids[r], hit or not (NaN rows for id < 0)."""
+    verts, dirs = _f32(verts).reshape(-1, 3), _f32(dirs).reshape(-1, 3)
+    tris = np.ascontiguousarray(tris, dtype=np.uint32).reshape(-1, 3)
+    ids = np.ascontiguousarray(tri_ids, dtype=np.int32)
+    nR = dirs.shape[0]
+    o, stride = _origins(orgs, nR)
+    out = np.empty((nR, 4), np.float64)
+    lib().lso_bary_f64(_p(verts, C.c_float), _p(tris, C.c_uint32), _p(o, C.c_float), stride, _p(dirs, C.c_float),
+                       _p(ids, C.c_int32), nR, _p(out, C.c_double))
+    return out
+
+
 class Bvh:
     """Binned-SAH CPU BVH: stand-in for rtcCommitScene + rtcIntersect (SRC/EmbreeTracer.cpp:290-295, 472-480)."""
 
@@ -187,6 +215,16 @@ class Bvh:
         t, tri = np.empty(nR, np.float32), np.empty(nR, np.int32)
         lib().lso_trace_bvh(self._h, _p(o, C.c_float), stride, _p(dirs, C.c_float), nR, _p(t, C.c_float),
                             _p(tri, C.c_int32))
+        return t, tri
+
+    def trace_f64(self, orgs, dirs):
+        """Float64 second opinion (textbook Moeller-Trumbore in double on the original fp32 vertices)."""
+        dirs = _f32(dirs).reshape(-1, 3)
+        nR = dirs.shape[0]
+        o, stride = _origins(orgs, nR)
+        t, tri = np.empty(nR, np.float64), np.empty(nR, np.int32)
+        lib().lso_trace_bvh_f64(self._h, _p(self._v, C.c_float), _p(self._t, C.c_uint32), _p(o, C.c_float), stride,
+                                _p(dirs, C.c_float), nR, _p(t, C.c_double), _p(tri, C.c_int32))
         return t, tri
 
     def node_count(self):

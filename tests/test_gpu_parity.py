@@ -16,8 +16,8 @@ pytestmark = pytest.mark.gpu
 IDENT = lso.IDENTITY_AFFINE
 
 
-def make_ctx(uid="0000", frame_mode=capi.FRAME_SENSOR, opts=None):
-    ctx = capi.Context(0, frame_mode)
+def make_ctx(uid="0000", frame_mode=capi.FRAME_SENSOR, opts=None, lab=False):
+    ctx = capi.Context(0, frame_mode, lab=lab)
     for k, v in (opts or {}).items():
         ctx.set_option(k, v)
     elev, b, e, H, q, t = xt32_sensor_args(uid)
@@ -93,7 +93,7 @@ def test_xt32_reference_counts_and_golden(meshes, golden, uid, n_ground, n_both)
 @pytest.mark.parametrize("leaf,tile", [(1, 8), (4, 32), (8, 2), (2, 16)])
 def test_traversal_variants_agree(meshes, golden, mode, leaf, tile):
     ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: mode, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TOP_NODES: 256,
-                                 capi.OPT_TILE_WIDTH: tile})
+                                 capi.OPT_TILE_WIDTH: tile}, lab=True)
     add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
     add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
     assert ctx.commit_scene() == 0
@@ -267,7 +267,7 @@ def test_random_soup_vs_brute(n_tris, lists):
     v = (c + rng.normal(0, 0.7, (n_tris, 3, 3)).astype(np.float32)).reshape(-1, 3)
     tr = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
     elev = np.linspace(80, -80, 64).astype(np.float32)
-    ctx = capi.Context(0)
+    ctx = capi.Context(0, lab=True)
     if lists != "default":          # per-tile entry lists forced on for this small table (sensor inside the soup, tiny trees)
         ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
         ctx.set_option(capi.OPT_SUPER_TILES, 1 if lists == "tile+super" else 0)
@@ -303,7 +303,7 @@ def test_axis_parallel_rays_and_flat_boxes(origin, lists):
     v = (v + np.array(origin, np.float32)).astype(np.float32) if abs(origin[0]) > 100 else v
     pos = origin
     elev = np.array([90, 45, 1e-3, 0, -1e-3, -45, -90, 30], np.float32)
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)
     if lists != "default":
         ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
         ctx.set_option(capi.OPT_SUPER_TILES, 1 if lists == "tile+super" else 0)
@@ -323,7 +323,7 @@ def test_duplicate_and_degenerate_triangles():
     """Coincident triangles (equal t): the smaller global id wins; zero-area triangles never hit."""
     v = np.array([[5, -1, -1], [5, 1, -1], [5, 0, 1], [6, 0, 0], [6, 0, 0], [6, 0, 0]], np.float32)
     tr = np.array([[0, 1, 2], [3, 4, 5], [0, 1, 2], [2, 1, 0]], np.uint32)
-    ctx = capi.Context(0)
+    ctx = capi.Context(0, lab=True)
     ctx.set_sensor(np.array([0.0], np.float32), -10.0, 10.0, 21, (1, 0, 0, 0), (0, 0, 0))
     add_mesh(ctx, "m", v, tr)
     assert ctx.commit_scene() == 0
@@ -437,7 +437,7 @@ def test_small_city_world_frame_vs_oracle_bvh(mode):
     meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
     poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
     elev, b, e, H = synth.lidar_table(32, 721)
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)
     ctx.set_option(capi.OPT_TRAVERSAL, mode)
     for k, (q, t) in enumerate(poses):
         ctx.set_sensor(elev, b, e, H, q, t, index=k)
@@ -481,7 +481,7 @@ def test_tile_entry_lists_xt32_golden(meshes, golden, entries, leaf, tile):
     """Per-tile entry lists (k_tile_entries) forced on for the 150-tile XT-32 scan, sensor frame: every list size,
     leaf size and tile shape returns the golden per-ray (t, triangle id) bits."""
     ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: 6, capi.OPT_LEAF_SIZE: leaf, capi.OPT_TILE_WIDTH: tile,
-                                 capi.OPT_TILE_ENTRIES: entries, capi.OPT_TILE_MIN_UNITS: 0})
+                                 capi.OPT_TILE_ENTRIES: entries, capi.OPT_TILE_MIN_UNITS: 0}, lab=True)
     add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
     add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
     assert ctx.commit_scene() == 0
@@ -507,7 +507,7 @@ def test_tile_entry_lists_small_city_vs_oracle_bvh(entries, visits, super_tiles)
     meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
     poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
     elev, b, e, H = synth.lidar_table(32, 721)
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)
     ctx.set_option(capi.OPT_TILE_ENTRIES, entries)
     ctx.set_option(capi.OPT_TILE_VISITS, visits)
     ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
@@ -560,7 +560,7 @@ def test_tile_lists_follow_queue_rebuilds():
     meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
     poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
     elev, b, e, H = synth.lidar_table(64, 1801)
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)
     ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
     for k, (q, t) in enumerate(poses):
         ctx.set_sensor(elev, b, e, H, q, t, index=k)
@@ -591,7 +591,7 @@ def test_city_10m_size_independent_properties():
     meshes = synth.city()
     poses = synth.sensor_lattice(8)
     elev, b, e, H = synth.lidar_table()
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)
     pick = (0, 27, 63)
     for k, si in enumerate(pick):
         ctx.set_sensor(elev, b, e, H, poses[si][0], poses[si][1], index=k)
@@ -641,6 +641,75 @@ def test_city_10m_size_independent_properties():
     w0, w1, w2 = bary(P, bb, c), bary(P, c, a), bary(P, a, bb)
     tol = 2e-3
     assert min(w0.min(), w1.min(), w2.min()) > -tol and abs((w0 + w1 + w2) - 1).max() < 1e-6
+    ctx.close()
+
+
+def test_city_10m_vs_oracle_and_float64_second_opinion():
+    """BASELINE config 4 at FULL size -- the benchmarked configuration: 10 M triangles, world frame, product library.
+    Three of the 64 sensors (a corner, the middle, the opposite corner) are compared ray by ray with the oracle's CPU
+    BVH (hit mask, triangle id AND t bit-exact), under a non-identity per-geometry transform (the bench's frame
+    motion), and the fp32 answer is then held against the float64 second opinion: rays that differ are the grazing
+    rays north_star wants counted -- each must lie within k ulp of an edge / be a tie / be seen edge-on."""
+    from oracle import grazing
+    from bench import frame_affine
+    meshes = synth.city()
+    poses = synth.sensor_lattice(8)
+    elev, b, e, H = synth.lidar_table()
+    pick = (0, 27, 63)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    for k, si in enumerate(pick):
+        ctx.set_sensor(elev, b, e, H, poses[si][0], poses[si][1], index=k)
+    A = [frame_affine(3, gi) for gi in range(len(meshes))]
+    for (name, v, tr), a in zip(meshes, A):
+        add_mesh(ctx, name, v, tr, a)
+    assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
+    s0 = lso.Sensor(elev, b, e, H, poses[0][0], poses[0][1])
+    verts, tris = lso.concat_scene(s0, [(v, t, a) for (_, v, t), a in zip(meshes, A)], mode=1)
+    assert tris.shape[0] == 10_000_000
+    bvh = lso.Bvh(verts, tris)
+    total_grazing = 0
+    for k, si in enumerate(pick):
+        s = lso.Sensor(elev, b, e, H, poses[si][0], poses[si][1])
+        dirs = lso.rotate_dirs(s.R, lso.ray_dirs(s.tables))
+        t_ref, tri_ref = bvh.trace(s.T, dirs)
+        rc, t, tri = ctx.trace_raw(k)
+        assert rc == 0
+        assert int((tri != tri_ref).sum()) == 0, f"sensor {si}: {int((tri != tri_ref).sum())} rays differ in triangle id"
+        assert np.array_equal(t, t_ref), f"sensor {si}: t differs"
+        rep = grazing.second_opinion(verts, tris, s.T, dirs, t, tri, bvh=bvh)
+        assert rep["unexplained"] == 0, rep
+        assert rep["max_rel_range_error_vs_f64"] < 1e-4, rep              # north_star's range tolerance, vs exact arithmetic
+        total_grazing += rep["grazing_rays"]
+    assert total_grazing < 1000                                            # a handful per 460 928 rays
+    bvh.close()
+    ctx.close()
+
+
+def test_heightfield_1m_float64_second_opinion():
+    """BASELINE config 3: the GPU's fp32 answer against the float64 second opinion.  The sensor stands above a grid
+    vertex, so the azimuth 0 / 90 / 180 / 270 rays run exactly along shared edges: the grazing report must find them
+    and explain every one (edge / tie)."""
+    from oracle import grazing
+    v, tr = synth.heightfield()
+    elev, b, e, H = synth.lidar_table()
+    T = (0.0, 0.0, 2.0)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), T)
+    add_mesh(ctx, "terrain", v, tr)
+    assert ctx.commit_scene() == 0
+    rc, t, tri = ctx.trace_raw()
+    assert rc == 0
+    s = lso.Sensor(elev, b, e, H, (1, 0, 0, 0), T)
+    verts, tris = lso.concat_scene(s, [(v, tr, IDENT)], mode=1)
+    dirs = lso.rotate_dirs(s.R, lso.ray_dirs(s.tables))
+    bvh = lso.Bvh(verts, tris)
+    t_ref, tri_ref = bvh.trace(s.T, dirs)
+    assert np.array_equal(tri, tri_ref) and np.array_equal(t, t_ref)
+    rep = grazing.second_opinion(verts, tris, s.T, dirs, t, tri, bvh=bvh)
+    bvh.close()
+    assert rep["unexplained"] == 0, rep
+    assert 0 < rep["grazing_rays"] < 500, rep
+    assert rep["max_rel_range_error_vs_f64"] < 1e-4, rep
     ctx.close()
 
 
@@ -701,7 +770,7 @@ def test_sensor_limits_detection_radius_and_azimuth_window(meshes, mode):
     args = xt32_sensor_args("0000")
     s = lso.Sensor(*args)
     ms = [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)]
-    ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: mode})
+    ctx = make_ctx("0000", opts={capi.OPT_TRAVERSAL: mode}, lab=(mode != 6))
     add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
     add_mesh(ctx, "ben", meshes["ben_v"], meshes["ben_t"])
     assert ctx.commit_scene() == 0
@@ -741,7 +810,7 @@ def test_fit_by_range_queries_equals_climb(n_tris):
     A2 = lso.affine_from_components([1.5, -0.5, 0.25], [0.2, 0.1, -0.3])
     out = []
     for rmq in (1, 0):
-        ctx = capi.Context(0)
+        ctx = capi.Context(0, lab=True)
         ctx.set_option(capi.OPT_SMALL_BUILD, 0)
         ctx.set_option(capi.OPT_FIT_RMQ, rmq)
         ctx.set_option(capi.OPT_LEAF_SIZE, 4)

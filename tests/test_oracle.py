@@ -114,3 +114,56 @@ def test_intersect_conventions():
     assert not hit
     hit, _ = lso.intersect_one(a, a, a, [0, 0, 0], [0, 0, 1])              # degenerate triangle
     assert not hit
+
+
+def test_float64_second_opinion_xt32(meshes):
+    """The float64 second opinion (textbook Moeller-Trumbore in double, oracle/grazing.py) over the reference's own
+    scene: same 1668 / 1781 points as the fp32 oracle and the reference's tests, no grazing ray, range within 1e-6."""
+    from oracle import grazing
+    for uid, n_both in (("0000", 1781), ("0001", 1769)):
+        s = lso.Sensor(*xt32_sensor_args(uid))
+        r = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], lso.IDENTITY_AFFINE),
+                         (meshes["ben_v"], meshes["ben_t"], lso.IDENTITY_AFFINE)])
+        dirs = lso.ray_dirs(s.tables)
+        t64, tri64 = lso.trace_brute_f64(r["verts"], r["tris"], np.zeros(3, np.float32), dirs)
+        assert int((tri64 >= 0).sum()) == n_both
+        rep = grazing.report(r["verts"], r["tris"], np.zeros(3, np.float32), dirs, r["t"], r["tri"], t64, tri64)
+        assert rep["grazing_rays"] == 0 and rep["unexplained"] == 0, rep
+        assert rep["max_rel_range_error_vs_f64"] < 1e-6
+
+
+def test_grazing_report_finds_and_explains_edge_rays():
+    """Rays aimed exactly at the shared diagonal / at the vertices of a tessellated quad, and rays skimming a plane
+    edge-on: wherever fp32 and float64 disagree the report must name a cause; rays aimed at triangle interiors never
+    disagree.  BVH and brute-force forms of the float64 tracer agree."""
+    from oracle import grazing
+    rng = np.random.default_rng(5)
+    n = 24
+    xs = np.linspace(-3.0, 3.0, n + 1, dtype=np.float32)
+    X, Y = np.meshgrid(xs, xs, indexing="xy")
+    Z = (0.3 * np.sin(1.7 * X) * np.cos(1.3 * Y)).astype(np.float32)
+    verts = np.stack([X, Y, Z], -1).reshape(-1, 3).astype(np.float32)
+    i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="xy")
+    v00 = (j * (n + 1) + i).astype(np.uint32)
+    tris = np.concatenate([np.stack([v00, v00 + 1, v00 + n + 2], -1).reshape(-1, 3),
+                           np.stack([v00, v00 + n + 2, v00 + n + 1], -1).reshape(-1, 3)]).astype(np.uint32)
+    org = np.array([0.3, -0.2, 5.0], np.float32)
+    # targets: vertices, edge midpoints (shared edges), random interior points
+    a, b, c = verts[tris[:, 0]], verts[tris[:, 1]], verts[tris[:, 2]]
+    w = rng.dirichlet((1, 1, 1), size=tris.shape[0]).astype(np.float32)
+    interior = w[:, :1] * a + w[:, 1:2] * b + w[:, 2:] * c
+    targets = np.concatenate([verts, 0.5 * (a + b), 0.5 * (b + c), 0.5 * (c + a), interior]).astype(np.float32)
+    dirs = (targets - org).astype(np.float32)
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True).astype(np.float32)
+    t32, tri32 = lso.trace_brute(verts, tris, org, dirs)
+    t64, tri64 = lso.trace_brute_f64(verts, tris, org, dirs)
+    bvh = lso.Bvh(verts, tris)
+    t64b, tri64b = bvh.trace_f64(org, dirs)
+    bvh.close()
+    assert np.array_equal(tri64, tri64b) and np.array_equal(t64, t64b)
+    rep = grazing.report(verts, tris, org, dirs, t32, tri32, t64, tri64)
+    assert rep["unexplained"] == 0, rep
+    assert rep["grazing_rays"] > 0 and rep["grazing_rays"] == rep["edge"] + rep["tie"] + rep["edge_on"], rep
+    n_int = interior.shape[0]
+    assert np.array_equal(tri32[-n_int:], tri64[-n_int:])          # interior targets: never a disagreement
+    assert rep["max_rel_range_error_vs_f64"] < 1e-5

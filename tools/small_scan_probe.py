@@ -10,7 +10,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 from conftest import GOLDEN, xt32_sensor_args
 from lidarshooter_b200 import capi
 z = np.load(os.path.join(GOLDEN, "meshes.npz"))
-ctx = capi.Context(0)
+ctx = capi.Context(0, lab=True)
 ctx.set_sensor(*xt32_sensor_args("0000"))
 ident = [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0]
 for name in ("ground", "ben"):

@@ -49,7 +49,7 @@ def main():
     elev, b, e, H = table
     R = elev.size * H
     ns = len(poses)
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)
     for k, (q, t) in enumerate(poses):
         ctx.set_sensor(elev, b, e, H, q, t, index=k)
     for gi, (name, v, t) in enumerate(meshes):

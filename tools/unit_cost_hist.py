@@ -5,7 +5,7 @@ from bench import build_workload, frame_affine
 from lidarshooter_b200 import capi
 meshes, poses, table = build_workload(False)
 elev, b, e, H = table
-ctx = capi.Context(0, capi.FRAME_WORLD)
+ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)
 for k, (q, t) in enumerate(poses):
     ctx.set_sensor(elev, b, e, H, q, t, index=k)
 for gi, (name, v, t) in enumerate(meshes):
