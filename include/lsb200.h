@@ -60,7 +60,11 @@ enum {
     LSB200_TRACE_RING_ZERO = 1u << 1,  /* ring = 0 for every point (Embree-path quirk, SRC/EmbreeTracer.cpp:333-334) */
     LSB200_TRACE_XYZI16 = 1u << 2,     /* 16-byte x,y,z,intensity records instead of the 32-byte PointCloud2 record */
     LSB200_TRACE_NO_POINTS = 1u << 3,  /* per-ray t / triangle only (lsb200_trace_raw uses this) */
-    LSB200_TRACE_WORLD_POINTS = 1u << 4 /* emit points in the world frame: R p + T (SRC/LidarDevice.cpp:393-401) */
+    LSB200_TRACE_WORLD_POINTS = 1u << 4, /* emit points in the world frame: R p + T (SRC/LidarDevice.cpp:393-401) */
+    LSB200_TRACE_RANGE_IMAGE = 1u << 5  /* output = the dense range image: one f32 range per ray in ray-id order (+inf = no
+                                           return), 4 bytes per RAY over PCIe instead of 16 / 32 per hit -- what a physical
+                                           LiDAR's packets carry.  *n_pts = ray count.  lsb200_expand_range_image turns it
+                                           into the reference's records on the host (same bytes as LSB200_TRACE_ORDERED). */
 };
 
 /* traversal kernel variants (lsb200_set_option LSB200_OPT_TRAVERSAL) -- for the ncu before/after evidence */
@@ -99,10 +103,23 @@ enum {
                                       measured slower overall (1.90 vs 1.74 ms per trace stage); 0 (default) = off */
     LSB200_OPT_TILE_MIN_UNITS = 16, /* tile lists are built for launches of at least this many 32-ray tiles (default 4096: below
                                       that, e.g. an XT-32 with 150 tiles, the extra launch costs more than it saves) */
-    LSB200_OPT_SMALL_BUILD = 10    /* 1 (default) = scenes of <= 16384 triangles in <= 16 geometries are committed by ONE
+    LSB200_OPT_SMALL_BUILD = 10,   /* 1 (default) = scenes of <= 16384 triangles in <= 16 geometries are committed by ONE
                                       fused single-CTA kernel (transform, Morton, sort, hierarchy, fit); 0 = always the
                                       multi-kernel pipeline */
+    LSB200_OPT_WATERTIGHT = 18,    /* 0 (default) = Embree-ordered Moeller-Trumbore, the reference's intersector (drop-in parity;
+                                      SRC/EmbreeTracer.cpp:472-480 -> Embree 3.13.4 triangle_intersector_moeller.h); 1 = watertight
+                                      Woop-Benthin-Wald 2013 shear / scale test (edge functions on the sheared vertices, exact
+                                      double-precision fallback on a zero edge function): a ray can never slip between two
+                                      triangles that share an edge.  Bit-exact against the oracle in the same mode. */
+    LSB200_OPT_INTENSITY_MODEL = 19 /* 0 (default) = constant 64.0, what the reference writes (SRC/EmbreeTracer.cpp:333); 1 =
+                                      Lambertian cos-incidence: 255 * |Ng . d| / (|Ng| |d|) from the hit triangle's normal
+                                      (SURVEY 8f row 4).  Models other than 0 (and an intensity filter) emit the points through the
+                                      ordered compaction. */
 };
+
+/* log levels of lsb200_set_log_callback == spdlog::level (the reference logs through spdlog, SRC/ITracer.cpp:5-14) */
+enum { LSB200_LOG_TRACE = 0, LSB200_LOG_DEBUG = 1, LSB200_LOG_INFO = 2, LSB200_LOG_WARN = 3, LSB200_LOG_ERROR = 4 };
+enum { LSB200_SHARD_FRAMES = 0, LSB200_SHARD_SENSORS = 1 };
 
 /* ---- life cycle -------------------------------------------------------------------------------------- */
 /* replaces EmbreeTracer::create / rtcNewDevice + rtcNewScene (SRC/EmbreeTracer.cpp:20-34, 482-486) */
@@ -113,6 +130,13 @@ LSB200_API int lsb200_set_stream(lsb200_ctx *ctx, void *cuda_stream);
 LSB200_API int lsb200_set_frame_mode(lsb200_ctx *ctx, int frame_mode);
 LSB200_API int lsb200_set_option(lsb200_ctx *ctx, int option, int value);
 LSB200_API const char *lsb200_last_error(const lsb200_ctx *ctx);
+/* Log sink: replaces the std::shared_ptr<spdlog::logger> every reference tracer takes (SRC/EmbreeTracer.hpp:51,
+ * SRC/ITracer.cpp:5-14; OptiX's own log callback: SRC/OptixTracer.cpp:432-441).  Every error of the ABI (the text of
+ * lsb200_last_error) is reported at LSB200_LOG_ERROR, life-cycle events at INFO, per-commit lines at DEBUG.  ctx == NULL
+ * sets the process-wide default that contexts created afterwards inherit (and that lsb200_create's own failures use).
+ * The callback may be invoked from any thread that calls into the ABI; fn == NULL switches logging off. */
+typedef void (*lsb200_log_fn)(int level, const char *message, void *user);
+LSB200_API int lsb200_set_log_callback(lsb200_ctx *ctx, lsb200_log_fn fn, void *user);
 LSB200_API const char *lsb200_version(void);
 
 /* ---- sensor: what LidarDevice holds for the path (SRC/LidarDevice.cpp:598-617 channels, 788-816 transform) ---
@@ -129,6 +153,10 @@ LSB200_API int lsb200_set_sensor(lsb200_ctx *ctx, int sensor_index, const float 
  * (-180, 180], lies outside [az_min_deg, az_max_deg] is not fired.  Cleared by lsb200_set_sensor.  Off by default, so
  * the drop-in behaviour equals the reference's. */
 LSB200_API int lsb200_set_sensor_limits(lsb200_ctx *ctx, int sensor_index, float max_range, float az_min_deg, float az_max_deg);
+/* use_intensity_filtering / minimum_intensity of the device config (config/hesai-pandar-XT-32-lidar_0000.json:19-20; carried
+ * but never applied by the reference): a return whose intensity is below min_intensity is dropped (no point, t = +inf,
+ * triangle = -1).  0 = off (default).  With the constant model (64.0) only thresholds above 64 drop anything. */
+LSB200_API int lsb200_set_sensor_intensity_filter(lsb200_ctx *ctx, int sensor_index, float min_intensity);
 LSB200_API int lsb200_get_ray_count(const lsb200_ctx *ctx, int sensor_index);
 
 /* ---- geometry: ITracer::addGeometry / removeGeometry / updateGeometry (SRC/ITracer.hpp:50-85) ------------- */
@@ -184,7 +212,19 @@ LSB200_API int lsb200_fetch_points(lsb200_ctx *ctx, int sensor_index, void *out_
  * belong to sensor first_sensor + i (host arrays; pinned memory makes the copies asynchronous until the final sync) */
 LSB200_API int lsb200_fetch_batch(lsb200_ctx *ctx, int first_sensor, int n_sensors, void *const *outs, const size_t *caps,
                                   uint32_t *n_pts, uint32_t flags);
+/* host-side expansion of a range image (LSB200_TRACE_RANGE_IMAGE) of `sensor_index` into point records: flags =
+ * XYZI16 / RING_ZERO / WORLD_POINTS as for a trace; hits in ray-id order; *n_pts = hits */
+LSB200_API int lsb200_expand_range_image(lsb200_ctx *ctx, int sensor_index, const float *t, void *out_points, size_t capacity_pts,
+                                         uint32_t *n_pts, uint32_t flags);
+/* per-ray intensity of the last trace (LSB200_OPT_INTENSITY_MODEL != 0): intensity_out[R] host buffer, 0 for a miss */
+LSB200_API int lsb200_fetch_intensity(lsb200_ctx *ctx, int sensor_index, float *intensity_out);
 LSB200_API int lsb200_synchronize(lsb200_ctx *ctx);
+/* Pinned host memory for output clouds / vertex blobs, allocated on the NUMA node the context's GPU is attached to (the
+ * calling thread is bound to that node's CPUs for the allocation and the first touch): with several GPUs in one box the
+ * D2H streams then spread over the sockets' memory controllers instead of converging on one. */
+LSB200_API int lsb200_alloc_host(lsb200_ctx *ctx, size_t bytes, void **out);
+LSB200_API int lsb200_free_host(lsb200_ctx *ctx, void *ptr);
+LSB200_API int lsb200_device_numa_node(const lsb200_ctx *ctx);
 /* ---- pipelined frames: the throughput form of the per-frame loop of MeshProjector::traceMeshWrapper
  * (SRC/MeshProjector.cpp:446-471: updateGeometry for every mesh, commitScene, traceScene) over a batch of
  * trajectory frames.  For each frame: optional vertex re-upload, per-geometry affine, commit, one trace launch
@@ -202,6 +242,17 @@ typedef struct lsb200_frame {
 } lsb200_frame;
 LSB200_API int lsb200_run_frames(lsb200_ctx *ctx, const lsb200_frame *frames, int n_frames, int first_sensor,
                                  int n_sensors, int commit_mode, uint32_t flags);
+
+/* ---- multi-GPU: one process, one context per GPU.  The reference runs one tracer per LiDAR device in one process
+ * (SRC/mainwindow.cpp:256-274) and has no multi-GPU code; this is the entry a C++ host uses to drive a whole box.
+ * lsb200_clone_scene: a new context on `cuda_device` holding a replica of src's scene (options, sensors, limits, every
+ * geometry's vertices / indices copied device to device, transforms).
+ * lsb200_run_batch: lsb200_run_frames on n_ctx contexts at once, one host thread each; LSB200_SHARD_FRAMES deals the
+ * frames round-robin (context g: frames g, g + n_ctx, ...; give every frame its affines), LSB200_SHARD_SENSORS gives
+ * every context every frame and a contiguous share of the sensors.  No data-path collective. */
+LSB200_API int lsb200_clone_scene(lsb200_ctx *src, int cuda_device, lsb200_ctx **out);
+LSB200_API int lsb200_run_batch(lsb200_ctx *const *ctxs, int n_ctx, const lsb200_frame *frames, int n_frames, int first_sensor,
+                                int n_sensors, int commit_mode, uint32_t flags, int sharding);
 
 
 /* ---- PointCloud2 header: replaces LidarDevice::initMessage (SRC/LidarDevice.cpp:94-115) ------------------ */

@@ -16,10 +16,12 @@ LAB_LIB_PATH = os.environ.get("LSB200_LAB_LIB") or os.path.join(_HERE, "liblsb20
 GEOMETRY_TRIANGLE, GEOMETRY_QUAD = 0, 1
 FRAME_SENSOR, FRAME_WORLD = 0, 1
 COMMIT_AUTO, COMMIT_REBUILD, COMMIT_REFIT = 0, 1, 2
-TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS = 1, 2, 4, 8, 16
+TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS, TRACE_RANGE_IMAGE = 1, 2, 4, 8, 16, 32
 OPT_TRAVERSAL, OPT_LEAF_SIZE, OPT_TOP_NODES, OPT_STAGE_TIMING, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
 OPT_TRACE_STATS, OPT_MORTON_UNIFORM, OPT_ORIGIN_CHAIN, OPT_TILE_WIDTH, OPT_SMALL_BUILD, OPT_MORTON_LAYOUT, OPT_MORTON_ASPECT, OPT_FIT_RMQ = 6, 7, 8, 9, 10, 11, 12, 13
-OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES = 14, 15, 16, 17
+OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES, OPT_WATERTIGHT, OPT_INTENSITY_MODEL = 14, 15, 16, 17, 18, 19
+LOG_TRACE, LOG_DEBUG, LOG_INFO, LOG_WARN, LOG_ERROR = 0, 1, 2, 3, 4
+SHARD_FRAMES, SHARD_SENSORS = 0, 1
 ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5
 
 # every symbol include/lsb200.h declares (tests/test_abi.py checks the library exports each one)
@@ -31,7 +33,11 @@ SYMBOLS = [
     "lsb200_commit_scene", "lsb200_trace_scene", "lsb200_trace_device", "lsb200_trace_batch", "lsb200_trace_raw",
     "lsb200_device_results", "lsb200_fetch_points", "lsb200_fetch_batch", "lsb200_synchronize", "lsb200_run_frames", "lsb200_init_message", "lsb200_get_stats",
     "lsb200_reset_counters", "lsb200_get_trace_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
+    "lsb200_set_log_callback", "lsb200_set_sensor_intensity_filter", "lsb200_expand_range_image", "lsb200_fetch_intensity",
+    "lsb200_alloc_host", "lsb200_free_host", "lsb200_device_numa_node", "lsb200_clone_scene", "lsb200_run_batch",
 ]
+
+LOG_FN = C.CFUNCTYPE(None, C.c_int, C.c_char_p, C.c_void_p)
 
 
 class CloudHeader(C.Structure):
@@ -106,6 +112,15 @@ def lib(lab=False):
     L.lsb200_debug_copy_bvh.argtypes = [vp, f32p, C.c_int64, i32p, C.c_int64, i32p]
     L.lsb200_debug_sort_pairs.argtypes = [vp, u32p, u32p, C.c_int64]
     L.lsb200_debug_copy_vertices.argtypes = [vp, f32p, C.c_int64]
+    L.lsb200_set_log_callback.argtypes = [vp, LOG_FN, vp]
+    L.lsb200_set_sensor_intensity_filter.argtypes = [vp, C.c_int, C.c_float]
+    L.lsb200_expand_range_image.argtypes = [vp, C.c_int, f32p, vp, C.c_size_t, u32p, C.c_uint32]
+    L.lsb200_fetch_intensity.argtypes = [vp, C.c_int, f32p]
+    L.lsb200_alloc_host.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
+    L.lsb200_free_host.argtypes = [vp, vp]
+    L.lsb200_device_numa_node.argtypes = [vp]
+    L.lsb200_clone_scene.argtypes = [vp, C.c_int, C.POINTER(vp)]
+    L.lsb200_run_batch.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(Frame), C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_int]
     _libs[lab] = L
     return L
 
@@ -124,14 +139,18 @@ class Context:
     """Thin object wrapper: one lsb200_ctx.  Methods return the ABI's status codes where the reference's
     interface does (add/remove/commit/trace) and raise Lsb200Error on CUDA failures."""
 
-    def __init__(self, device=0, frame_mode=FRAME_SENSOR, stream=None, lab=False):
+    def __init__(self, device=0, frame_mode=FRAME_SENSOR, stream=None, lab=False, _handle=None):
         self._L = lib(lab)
+        self._lab = lab
+        self._keep = {}
+        if _handle is not None:              # adopt a context created by the library (lsb200_clone_scene)
+            self._h = _handle
+            return
         h = C.c_void_p()
         rc = self._L.lsb200_create(int(device), C.byref(h))
         if rc != 0:
             raise Lsb200Error(rc, "lsb200_create failed (no CUDA device? this library has no CPU path)")
         self._h = h
-        self._keep = {}
         if frame_mode != FRAME_SENSOR:
             self._chk(self._L.lsb200_set_frame_mode(h, frame_mode))
         if stream is not None:
@@ -175,6 +194,55 @@ class Context:
 
     def set_sensor_limits(self, max_range=0.0, az_min_deg=-180.0, az_max_deg=180.0, index=0):
         return self._L.lsb200_set_sensor_limits(self._h, index, float(max_range), float(az_min_deg), float(az_max_deg))
+
+    def set_sensor_intensity_filter(self, min_intensity, index=0):
+        return self._L.lsb200_set_sensor_intensity_filter(self._h, index, float(min_intensity))
+
+    def set_log_callback(self, fn):
+        """fn(level, message) or None.  The ctypes thunk is kept alive by the context."""
+        if fn is None:
+            self._keep["log"] = LOG_FN(0)
+        else:
+            self._keep["log"] = LOG_FN(lambda level, msg, user: fn(level, msg.decode(errors="replace")))
+        return self._L.lsb200_set_log_callback(self._h, self._keep["log"], None)
+
+    def clone(self, device):
+        """A replica of this context's scene on another CUDA device (lsb200_clone_scene)."""
+        h = C.c_void_p()
+        rc = self._L.lsb200_clone_scene(self._h, int(device), C.byref(h))
+        if rc != 0:
+            raise Lsb200Error(rc, self.last_error())
+        return Context(lab=self._lab, _handle=h)
+
+    def alloc_host(self, nbytes):
+        """Pinned host memory on the GPU's NUMA node as a uint8 numpy array (free with free_host)."""
+        p = C.c_void_p()
+        self._chk(self._L.lsb200_alloc_host(self._h, int(nbytes), C.byref(p)))
+        arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(int(nbytes),))
+        self._keep.setdefault("host", {})[arr.ctypes.data] = p
+        return arr
+
+    def free_host(self, arr):
+        p = self._keep.get("host", {}).pop(arr.ctypes.data, None)
+        if p is not None:
+            self._L.lsb200_free_host(self._h, p)
+
+    def numa_node(self):
+        return self._L.lsb200_device_numa_node(self._h)
+
+    def fetch_intensity(self, sensor=0):
+        out = np.empty(self.ray_count(sensor), np.float32)
+        rc = self._L.lsb200_fetch_intensity(self._h, sensor, _fp(out))
+        return rc, out
+
+    def expand_range_image(self, t, flags=0, sensor=0):
+        """Host-side expansion of a range image into point records (ray-id order)."""
+        t = np.ascontiguousarray(t, np.float32)
+        rec = 16 if flags & TRACE_XYZI16 else 32
+        out = np.empty((t.size, rec), np.uint8)
+        n = C.c_uint32(0)
+        rc = self._L.lsb200_expand_range_image(self._h, sensor, _fp(t), out.ctypes.data, out.shape[0], C.byref(n), flags)
+        return rc, out[:n.value]
 
     def ray_count(self, index=0):
         return self._L.lsb200_get_ray_count(self._h, index)
@@ -223,7 +291,7 @@ class Context:
     def trace_scene(self, frame_index=0, flags=0, sensor=0, out=None):
         """Returns (status, points) with points a (n, 32|16) uint8 array (host)."""
         R = max(self.ray_count(sensor), 0)
-        rec = 16 if flags & TRACE_XYZI16 else 32
+        rec = 4 if flags & TRACE_RANGE_IMAGE else (16 if flags & TRACE_XYZI16 else 32)
         if out is None:
             out = np.empty((R, rec), np.uint8)
         n = C.c_uint32(0)
@@ -238,7 +306,7 @@ class Context:
 
     def fetch_points(self, sensor=0, flags=0, out=None):
         R = max(self.ray_count(sensor), 0)
-        rec = 16 if flags & TRACE_XYZI16 else 32
+        rec = 4 if flags & TRACE_RANGE_IMAGE else (16 if flags & TRACE_XYZI16 else 32)
         if out is None:
             out = np.empty((R, rec), np.uint8)
         n = C.c_uint32(0)
@@ -334,6 +402,36 @@ class Context:
         out = np.empty((int(s.n_vertices), 3), np.float32)
         self._chk(self._L.lsb200_debug_copy_vertices(self._h, _fp(out), out.shape[0]))
         return out
+
+
+def _build_frames(affines, out_ptrs, caps, count, verts):
+    A = np.ascontiguousarray(affines, np.float32)
+    F = A.shape[0]
+    counts = np.zeros((F, count), np.uint32)
+    cps = (C.c_size_t * count)(*[int(x) for x in caps])
+    vv = None
+    if verts is not None:
+        vv = (C.c_void_p * len(verts))(*[C.c_void_p(int(p)) if p else None for p in verts])
+    frames = (Frame * F)()
+    keep = [A, cps, vv]
+    for f in range(F):
+        outs = (C.c_void_p * count)(*[C.c_void_p(int(p)) for p in out_ptrs[f]])
+        keep.append(outs)
+        frames[f].affines = A[f].ctypes.data_as(C.POINTER(C.c_float))
+        frames[f].verts = C.cast(vv, C.POINTER(C.c_void_p)) if vv is not None else None
+        frames[f].out_points = C.cast(outs, C.POINTER(C.c_void_p))
+        frames[f].capacities = C.cast(cps, C.POINTER(C.c_size_t))
+        frames[f].n_pts = counts[f].ctypes.data_as(C.POINTER(C.c_uint32))
+    return frames, counts, keep
+
+
+def run_batch(contexts, affines, out_ptrs, caps, first=0, count=1, commit_mode=COMMIT_AUTO, flags=0, sharding=SHARD_FRAMES):
+    """lsb200_run_batch: the frames on several contexts (one per GPU) at once, one host thread each inside the library.
+    Returns (status, counts[F, count])."""
+    frames, counts, keep = _build_frames(affines, out_ptrs, caps, count, None)
+    hs = (C.c_void_p * len(contexts))(*[c._h for c in contexts])
+    rc = contexts[0]._L.lsb200_run_batch(hs, len(contexts), frames, len(frames), first, count, commit_mode, flags, sharding)
+    return rc, counts
 
 
 def affine_from_components(translation, euler_xyz):

@@ -25,6 +25,7 @@ struct SceneDev {
     int morton_bxy, morton_bz;   // explicit Morton layout (bits of x and y / of z) when morton_bxy > 0, see morton_plan()
     float morton_alpha;          // otherwise: bit allocation by extent^alpha (0 = round robin, 1 = cubic cells)
     struct MortonPlan *plan;     // device copy of the plan of this commit (k_morton_plan)
+    int watertight;              // 1: leaf records hold the three raw vertices (LSB200_OPT_WATERTIGHT, trace.cuh: intersect_tri_wt)
 };
 
 // Eigen-ordered 3-term dot: a0*b0 + (a1*b1 + a2*b2)  (oracle/lsb_oracle.c: dot3_eigen)
@@ -326,9 +327,15 @@ __device__ __forceinline__ void fit_leaf(const SceneDev &S, int g, int i, uint32
     const float ngy = __fsub_rn(__fmul_rn(e2z, e1x), __fmul_rn(e2x, e1z));
     const float ngz = __fsub_rn(__fmul_rn(e2x, e1y), __fmul_rn(e2y, e1x));
     float4 *rec = S.tris + 3 * (size_t)i;
-    rec[0] = make_float4(A.x, A.y, A.z, e1x);
-    rec[1] = make_float4(e1y, e1z, e2x, e2y);
-    rec[2] = make_float4(e2z, ngx, ngy, ngz);
+    if (S.watertight) {                       // raw vertices: shared edges are evaluated on bit-identical operands
+        rec[0] = make_float4(A.x, A.y, A.z, B.x);
+        rec[1] = make_float4(B.y, B.z, C.x, C.y);
+        rec[2] = make_float4(C.z, 0.0f, 0.0f, 0.0f);
+    } else {
+        rec[0] = make_float4(A.x, A.y, A.z, e1x);
+        rec[1] = make_float4(e1y, e1z, e2x, e2y);
+        rec[2] = make_float4(e2z, ngx, ngy, ngz);
+    }
     S.leaf_ids[i] = g;
 
     float lox = fminf(A.x, fminf(B.x, C.x)), hix = fmaxf(A.x, fmaxf(B.x, C.x));
@@ -401,9 +408,15 @@ __device__ __forceinline__ Box6 leaf_record(const SceneDev &S, int g, int i)
     const float ngy = __fsub_rn(__fmul_rn(e2z, e1x), __fmul_rn(e2x, e1z));
     const float ngz = __fsub_rn(__fmul_rn(e2x, e1y), __fmul_rn(e2y, e1x));
     float4 *rec = S.tris + 3 * (size_t)i;
-    rec[0] = make_float4(A.x, A.y, A.z, e1x);
-    rec[1] = make_float4(e1y, e1z, e2x, e2y);
-    rec[2] = make_float4(e2z, ngx, ngy, ngz);
+    if (S.watertight) {                       // raw vertices: shared edges are evaluated on bit-identical operands
+        rec[0] = make_float4(A.x, A.y, A.z, B.x);
+        rec[1] = make_float4(B.y, B.z, C.x, C.y);
+        rec[2] = make_float4(C.z, 0.0f, 0.0f, 0.0f);
+    } else {
+        rec[0] = make_float4(A.x, A.y, A.z, e1x);
+        rec[1] = make_float4(e1y, e1z, e2x, e2y);
+        rec[2] = make_float4(e2z, ngx, ngy, ngz);
+    }
     S.leaf_ids[i] = g;
     Box6 bx;
     bx.lox = fminf(A.x, fminf(B.x, C.x)); bx.hix = fmaxf(A.x, fmaxf(B.x, C.x));

@@ -47,6 +47,8 @@ struct SensorDev {           // one per LiDAR device
     uint8_t *points;              // [n_rays] records
     uint32_t *count;              // hit count
     uint32_t *block_counts;       // ordered compaction scratch
+    float *intensity;             // [n_rays] per-ray intensity (k_intensity; only with an intensity model / filter)
+    float min_intensity;          // returns below it are dropped (0: none) -- lsb200_set_sensor_intensity_filter
 };
 
 __host__ __device__ inline uint32_t f2ord(float f)

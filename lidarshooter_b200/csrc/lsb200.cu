@@ -13,7 +13,12 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
+
+#include <sched.h>
+#include <sys/syscall.h>
+#include <unistd.h>
 
 #include "common.cuh"
 #include "radix_sort.cuh"
@@ -65,7 +70,11 @@ struct Sensor {
     float max_range = INFINITY;
     std::vector<float> az_deg;         // azimuth of every step, as the ray generator computes it
     DevBuf t, tri, points, blocks;     // per-ray results, compacted points, ordered-compaction scratch
-    DevBuf points_b;                   // second output slot: lsb200_run_frames overlaps its D2H with the next frame
+    DevBuf points_b, t_b;              // second output slot: lsb200_run_frames overlaps its D2H with the next frame
+    std::vector<float> elev, h_tab;    // the set_sensor arguments (lsb200_clone_scene) and the host copy of the tables
+    float az_begin = 0.f, az_end = 0.f, lim_range = 0.f, lim_lo = -180.f, lim_hi = 180.f;
+    float min_intensity = 0.f;         // lsb200_set_sensor_intensity_filter (0 = off)
+    DevBuf inten;                      // per-ray intensity (only with an intensity model / filter)
     int n_rays() const { return V * H; }
 };
 
@@ -75,12 +84,12 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0, opt_watertight = 0, opt_intensity = 0;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
     bool topology_dirty = true, committed = false, top_valid = false;
-    int built_leaf = 0, built_top = 0;
+    int built_leaf = 0, built_top = 0, built_watertight = 0;
     std::vector<Sensor> sensors;
     bool sensors_dirty = true;
     // scene arrays
@@ -109,20 +118,45 @@ struct lsb200_ctx {
     lsb200_stats stats{};
     cudaEvent_t ev[12] = {};
     // per-device kernel state (function attributes / occupancy are per device, never per process)
-    bool trace_attr_set[16] = {};
-    int trace_occ[16] = {};
-    size_t trace_occ_smem[16] = {};
+    bool trace_attr_set[32] = {};
+    int trace_occ[32] = {};
+    size_t trace_occ_smem[32] = {};
+    lsb200_log_fn log_fn = nullptr;
+    void *log_user = nullptr;
     std::string err;
     std::mutex mtx;
 };
 
 namespace {
 
+// process-wide default sink (contexts inherit it at creation; also used when there is no context yet)
+lsb200_log_fn g_log_fn = nullptr;
+void *g_log_user = nullptr;
+std::mutex g_log_mtx;
+
+void emit_log(lsb200_ctx *c, int level, const char *msg)
+{
+    lsb200_log_fn fn = c ? c->log_fn : nullptr;
+    void *user = c ? c->log_user : nullptr;
+    if (!fn) { std::lock_guard<std::mutex> lk(g_log_mtx); fn = g_log_fn; user = g_log_user; }
+    if (fn) fn(level, msg, user);
+}
+
+void logf(lsb200_ctx *c, int level, const char *fmt, ...)
+{
+    if (!(c && c->log_fn) && !g_log_fn) return;          // nobody listens: do not format
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    emit_log(c, level, buf);
+}
+
+// every error path of the ABI goes through here: last_error text + one LSB200_LOG_ERROR line to the log sink
 int fail(lsb200_ctx *c, int code, const char *fmt, ...)
 {
     char buf[512];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
     if (c) c->err = buf;
+    emit_log(c, LSB200_LOG_ERROR, buf);
     return code;
 }
 
@@ -207,6 +241,7 @@ SceneDev scene_dev(lsb200_ctx *c)
     S.morton_bxy = c->opt_morton_layout >> 4; S.morton_bz = c->opt_morton_layout & 15;
     S.morton_alpha = 0.01f * (float)c->opt_morton_aspect;
     S.plan = c->d_plan.as<MortonPlan>();
+    S.watertight = c->built_watertight;
     return S;
 }
 
@@ -245,8 +280,9 @@ int lsb200_create(int cuda_device, lsb200_ctx **out)
     if (!out) return LSB200_ERR_INVALID;
     *out = nullptr;
     int n = 0;
-    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) return LSB200_ERR_CUDA;   // no CPU fallback, by design
-    if (cuda_device < 0 || cuda_device >= n) return LSB200_ERR_INVALID;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0)                            // no CPU fallback, by design
+        return fail(nullptr, LSB200_ERR_CUDA, "lsb200_create: no CUDA device (this library has no CPU path)");
+    if (cuda_device < 0 || cuda_device >= n) return fail(nullptr, LSB200_ERR_INVALID, "lsb200_create: CUDA device %d of %d", cuda_device, n);
     lsb200_ctx *c = new (std::nothrow) lsb200_ctx();
     if (!c) return LSB200_ERR_NOMEM;
     c->device = cuda_device;
@@ -270,6 +306,8 @@ int lsb200_create(int cuda_device, lsb200_ctx **out)
         c->d_plan.reserve(256, c->stream, false, true) != cudaSuccess ||
         c->d_sensor_xf.reserve(256, c->stream) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
     c->sensors.resize(1);
+    { std::lock_guard<std::mutex> lk(g_log_mtx); c->log_fn = g_log_fn; c->log_user = g_log_user; }
+    logf(c, LSB200_LOG_INFO, "lsb200: context created on CUDA device %d (%d SMs)", cuda_device, c->sm_count);
     *out = c;
     return LSB200_OK;
 }
@@ -281,7 +319,7 @@ int lsb200_destroy(lsb200_ctx *c)
         DeviceGuard dg(c->device);
         cudaStreamSynchronize(c->stream);
         for (auto &kv : c->geoms) { kv.second.verts.release(); kv.second.elems.release(); }
-        for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.blocks.release(); }
+        for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.t_b.release(); s.blocks.release(); s.inten.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
                           &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts, &c->d_sup_lists, &c->d_sup_counts, &c->d_tile_iv, &c->d_sup_iv};
@@ -354,6 +392,8 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_LEAF_SIZE: if (value < 1 || value > kMaxLeaf) break; c->opt_leaf = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TOP_NODES: if (value < 0 || value > 3072) break; c->opt_top = value; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_STAGE_TIMING: c->opt_timing = value ? 1 : 0; return LSB200_OK;
+    case LSB200_OPT_WATERTIGHT: c->opt_watertight = value ? 1 : 0; c->committed = false; return LSB200_OK;   // records change layout: re-commit
+    case LSB200_OPT_INTENSITY_MODEL: if (value < 0 || value > 1) break; c->opt_intensity = value; return LSB200_OK;
     case LSB200_OPT_CTAS_PER_SM: if (value < 0 || value > 32) break; c->opt_ctas_per_sm = value; return LSB200_OK;
     default: break;
     }
@@ -391,6 +431,9 @@ int lsb200_set_sensor(lsb200_ctx *c, int idx, const float *elev_deg, int V, floa
     s.az_deg.resize(H);
     for (int h = 0; h < H; ++h) s.az_deg[h] = az_begin + step * (float)h;
     s.has_mask = false; s.max_range = INFINITY;
+    s.elev.assign(elev_deg, elev_deg + V); s.az_begin = az_begin; s.az_end = az_end;
+    s.lim_range = 0.f; s.lim_lo = -180.f; s.lim_hi = 180.f;
+    s.h_tab = tab; s.min_intensity = 0.f;
     LSB_CU(c, s.tables.reserve(tab.size() * 4, c->stream));
     LSB_CU(c, cudaMemcpyAsync(s.tables.p, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, c->stream));
     LSB_CU(c, cudaStreamSynchronize(c->stream));     // tab is a local
@@ -410,6 +453,7 @@ int lsb200_set_sensor_limits(lsb200_ctx *c, int idx, float max_range, float az_m
     if (!(az_min_deg <= az_max_deg)) return fail(c, LSB200_ERR_INVALID, "set_sensor_limits: empty azimuth window");
     DeviceGuard dg(c->device);
     Sensor &s = c->sensors[idx];
+    s.lim_range = max_range; s.lim_lo = az_min_deg; s.lim_hi = az_max_deg;
     s.max_range = (max_range > 0.0f) ? max_range : INFINITY;
     s.has_mask = !(az_min_deg <= -180.0f && az_max_deg >= 180.0f);
     if (s.has_mask) {
@@ -426,6 +470,18 @@ int lsb200_set_sensor_limits(lsb200_ctx *c, int idx, float max_range, float az_m
     }
     c->sensors_dirty = true;
     c->tile_commit_epoch = -1;          // the tile lists bake the detection radius in
+    return LSB200_OK;
+}
+
+int lsb200_set_sensor_intensity_filter(lsb200_ctx *c, int idx, float min_intensity)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set)
+        return fail(c, LSB200_ERR_INVALID, "set_sensor_intensity_filter: sensor %d not set", idx);
+    if (!(min_intensity >= 0.0f)) return fail(c, LSB200_ERR_INVALID, "set_sensor_intensity_filter: negative threshold");
+    c->sensors[idx].min_intensity = min_intensity;
+    c->sensors_dirty = true;
     return LSB200_OK;
 }
 
@@ -528,6 +584,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
     cudaStream_t st = c->stream;
     c->n_verts = (int)nv; c->n_tris = (int)nt;
     if (rebuild) { c->built_leaf = c->opt_leaf; c->built_top = c->opt_top; }
+    c->built_watertight = c->opt_watertight;        // the leaf records are rewritten by every commit, rebuild or refit
 
     // geometry descriptor table (small pageable copy: staged by the runtime before the call returns)
     const size_t ng = c->geoms.size();
@@ -674,6 +731,8 @@ static int commit_locked(lsb200_ctx *c, int mode)
     c->topology_dirty = false;
     c->committed = true;
     ++c->commit_epoch;
+    logf(c, LSB200_LOG_DEBUG, "lsb200: commit (%s) of %lld triangles / %lld vertices in %zu geometries", rebuild ? "rebuild" : "refit",
+         (long long)nt, (long long)nv, ng);
     return LSB200_OK;
 }
 
@@ -711,7 +770,10 @@ int lsb200_remove_geometry(lsb200_ctx *c, const char *name)
 }  // extern "C"
 
 // ---- trace -------------------------------------------------------------------------------------------------
-static size_t record_bytes(uint32_t flags) { return (flags & LSB200_TRACE_XYZI16) ? 16 : 32; }
+static size_t record_bytes(uint32_t flags)
+{
+    return (flags & LSB200_TRACE_RANGE_IMAGE) ? 4 : ((flags & LSB200_TRACE_XYZI16) ? 16 : 32);
+}
 
 // (re)allocates the per-sensor result buffers of [first, first+count) and refreshes the device sensor tables.
 // slot 0 = the context's ordinary output buffers; slot 1 = the second set used by lsb200_run_frames.
@@ -727,10 +789,14 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
         const size_t R = (size_t)s.n_rays();
         const size_t nblk = (R + kCompactRays - 1) / kCompactRays;
         if (s.t.cap < R * 4 || s.tri.cap < R * 4 || s.points.cap < R * 32 || s.blocks.cap < nblk * 4) dirty = true;
-        if (slot == 1 && s.points_b.cap < R * 32) dirty = true;
+        if (slot == 1 && (s.points_b.cap < R * 32 || s.t_b.cap < R * 4)) dirty = true;
         LSB_CU(c, s.t.reserve(R * 4, st)); LSB_CU(c, s.tri.reserve(R * 4, st));
         LSB_CU(c, s.points.reserve(R * 32, st)); LSB_CU(c, s.blocks.reserve(std::max<size_t>(nblk, 4) * 4, st));
-        if (slot == 1) LSB_CU(c, s.points_b.reserve(R * 32, st));
+        if (slot == 1) { LSB_CU(c, s.points_b.reserve(R * 32, st)); LSB_CU(c, s.t_b.reserve(R * 4, st)); }
+        if (c->opt_intensity != 0 || s.min_intensity > 0.0f) {
+            if (s.inten.cap < R * 4) dirty = true;
+            LSB_CU(c, s.inten.reserve(R * 4, st));
+        }
     }
     if (!dirty) return 0;
     c->h_sensors.assign(ns, SensorDev{});
@@ -746,6 +812,7 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
         std::memcpy(d.R, s.R, 36); std::memcpy(d.Rinv, s.Rinv, 36); std::memcpy(d.T, s.T, 12);
         d.V = s.V; d.H = s.H; d.n_rays = s.n_rays();
         d.max_range = s.max_range; d.az_mask = s.has_mask ? s.az_mask.as<uint8_t>() : nullptr;
+        d.intensity = s.inten.as<float>(); d.min_intensity = s.min_intensity;
         d.t_out = s.t.as<float>(); d.tri_out = s.tri.as<int32_t>(); d.points = s.points.as<uint8_t>();
         d.count = c->d_counts.as<uint32_t>() + i; d.block_counts = s.blocks.as<uint32_t>();
         d.tiles_h = (s.H + tw - 1) / tw;
@@ -757,6 +824,7 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
     c->h_sensors_b = c->h_sensors;
     for (size_t i = 0; i < ns; ++i) {
         c->h_sensors_b[i].points = c->sensors[i].points_b.as<uint8_t>();      // null until slot 1 is first used
+        if (c->sensors[i].t_b.p) c->h_sensors_b[i].t_out = c->sensors[i].t_b.as<float>();
         c->h_sensors_b[i].count = c->d_counts.as<uint32_t>() + kMaxSensors + i;
     }
     LSB_CU(c, c->d_sensors.reserve(ns * sizeof(SensorDev), st));
@@ -767,15 +835,15 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
     return 0;
 }
 
-template <int MODE, bool STATS>
+template <int MODE, bool STATS, bool WT = false>
 static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
 {
     constexpr bool TOP = (MODE == 4);
     const size_t smem = TOP ? (size_t)P.top_cap * 64 : (MODE == 6 ? (size_t)LSB_SMEM_STACK * kTraceThreads * sizeof(int2) : 0);
     // function attributes and occupancy are per DEVICE, so they are cached per context (one slot per instantiation)
-    constexpr int kSlot = MODE * 2 + (STATS ? 1 : 0);
+    constexpr int kSlot = MODE * 2 + (STATS ? 1 : 0) + (WT ? 16 : 0);
     if ((TOP || (MODE == 6 && LSB_SMEM_STACK)) && !c->trace_attr_set[kSlot]) {
-        LSB_CU(c, cudaFuncSetAttribute(k_trace<MODE, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        LSB_CU(c, cudaFuncSetAttribute(k_trace<MODE, STATS, WT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         c->trace_attr_set[kSlot] = true;
     }
     int grid;
@@ -786,7 +854,7 @@ static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
         int &occ = c->trace_occ[kSlot]; size_t &occ_smem = c->trace_occ_smem[kSlot];   // one query per instantiation and smem size
         if (per_sm <= 0) {
             if (occ <= 0 || occ_smem != smem) {
-                LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<MODE, STATS>, kTraceThreads, smem));
+                LSB_CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<MODE, STATS, WT>, kTraceThreads, smem));
                 occ_smem = smem;
             }
             per_sm = occ;
@@ -796,7 +864,7 @@ static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
         grid = std::min(grid, (n_units + kTraceThreads / 32 - 1) / (kTraceThreads / 32));
         grid = std::max(grid, 1);
     }
-    k_trace<MODE, STATS><<<grid, kTraceThreads, smem, c->stream>>>(P);
+    k_trace<MODE, STATS, WT><<<grid, kTraceThreads, smem, c->stream>>>(P);
     c->stats.trace_grid = grid; c->stats.trace_block = kTraceThreads;
     count_launch(c);
     return 0;
@@ -805,6 +873,11 @@ static int launch_trace(lsb200_ctx *c, const TraceParams &P, int n_units)
 template <bool STATS>
 static int launch_trace_mode(lsb200_ctx *c, const TraceParams &P, int n_units, int mode)
 {
+    if (c->built_watertight) {             // watertight records: the shipped traversal and brute force only
+        if (mode == 3) return launch_trace<3, false, true>(c, P, n_units);
+        if (mode == 6) return launch_trace<6, false, true>(c, P, n_units);
+        return fail(c, LSB200_ERR_STATE, "traversal variant %d has no watertight build (use 6 or 3)", mode);
+    }
     switch (mode) {
 #ifdef LSB_LAB
     case 0: return launch_trace<0, STATS>(c, P, n_units);
@@ -827,6 +900,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         return fail(c, LSB200_ERR_INVALID, "trace: sensor-frame contexts hold exactly one sensor (index 0)");
     DeviceGuard dg(c->device);
     cudaStream_t st = c->stream;
+    if (flags & LSB200_TRACE_RANGE_IMAGE) flags |= LSB200_TRACE_NO_POINTS;     // the per-ray t array IS the output
     if (int rc = prepare_sensors(c, first, count, slot)) return rc;
     uint32_t *d_cnt = c->d_counts.as<uint32_t>() + (slot ? kMaxSensors : 0);
     const SensorDev *d_sens = slot ? c->d_sensors_b.as<SensorDev>() : c->d_sensors.as<SensorDev>();
@@ -849,6 +923,12 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     P.top_cap = c->built_top; P.n_tris = c->n_tris;
     P.world_frame = c->frame_mode == LSB200_FRAME_WORLD;
     P.tile_w_log2 = c->opt_tile_w_log2;
+    // an intensity model other than the reference's constant, or an intensity filter, is a post-pass over the per-ray
+    // results (k_intensity); the points are then emitted by the ordered compaction, never by the traversal's own append
+    bool need_intensity = c->opt_intensity != 0;
+    for (int i = first; i < first + count; ++i) need_intensity = need_intensity || c->sensors[i].min_intensity > 0.0f;
+    const bool want_points = !(flags & LSB200_TRACE_NO_POINTS);
+    if (need_intensity) flags |= LSB200_TRACE_NO_POINTS;
     P.flags = flags;
     P.work = c->d_misc.as<uint32_t>() + 4;
     // work units of the batch: [unit_base(first), unit_base(last) + units(last))
@@ -987,14 +1067,24 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     rc = launch_trace_mode<false>(c, P, n_units, mode);
     if (rc) return rc;
     if (timing) cudaEventRecord(c->ev[9], st);
-    if ((flags & LSB200_TRACE_ORDERED) && !(flags & LSB200_TRACE_NO_POINTS)) {
-        int max_rays = 0;
-        for (int i = first; i < first + count; ++i) max_rays = std::max(max_rays, c->sensors[i].n_rays());
+    int max_rays = 0;
+    for (int i = first; i < first + count; ++i) max_rays = std::max(max_rays, c->sensors[i].n_rays());
+    if (need_intensity) {
+        const bool small = c->opt_small_build && c->n_tris <= kSmallMaxTris && c->geoms.size() <= (size_t)kSmallMaxGeoms;
+        if (small) {        // the fused small build takes its descriptors as kernel parameters: the post-pass needs them in memory
+            LSB_CU(c, c->d_geoms.reserve(c->h_geoms.size() * sizeof(GeomDesc), st));
+            LSB_CU(c, cudaMemcpyAsync(c->d_geoms.p, c->h_geoms.data(), c->h_geoms.size() * sizeof(GeomDesc), cudaMemcpyHostToDevice, st));
+        }
+        dim3 grid((unsigned)((max_rays + 255) / 256), (unsigned)count);
+        k_intensity<<<grid, 256, 0, st>>>(scene_dev(c), d_sens, first, P.world_frame, c->opt_intensity);
+        count_launch(c);
+    }
+    if (want_points && ((flags & LSB200_TRACE_ORDERED) || need_intensity)) {
         dim3 grid((unsigned)((max_rays + kCompactRays - 1) / kCompactRays), (unsigned)count);
         const SensorDev *sd = d_sens;
         k_count_hits<<<grid, kCompactThreads, 0, st>>>(sd, first);
         k_scan_counts<<<count, 256, 0, st>>>(sd, first);
-        k_scatter_hits<<<grid, kCompactThreads, 0, st>>>(sd, first, flags);
+        k_scatter_hits<<<grid, kCompactThreads, 0, st>>>(sd, first, (flags & ~(uint32_t)LSB200_TRACE_NO_POINTS) | (need_intensity ? kFlagIntensityBuffer : 0u));
         count_launch(c, 3);
     }
     if (timing) {
@@ -1015,6 +1105,17 @@ static int fetch_locked(lsb200_ctx *c, int idx, void *out, size_t capacity, uint
     if (!c->d_counts.p || !c->sensors[idx].points.p) return fail(c, LSB200_ERR_STATE, "fetch: sensor %d was never traced", idx);
     DeviceGuard dg(c->device);
     cudaStream_t st = c->stream;
+    if (flags & LSB200_TRACE_RANGE_IMAGE) {
+        // dense range image: one f32 per ray in ray-id order (+inf = no return); the "point count" is the ray count
+        const uint32_t R = (uint32_t)c->sensors[idx].n_rays();
+        if (n_pts) *n_pts = R;
+        if (out && capacity < R) return fail(c, LSB200_ERR_CAPACITY, "fetch: range image of %u rays, capacity %zu", R, capacity);
+        if (out) {
+            LSB_CU(c, cudaMemcpyAsync(out, c->sensors[idx].t.p, (size_t)R * 4, cudaMemcpyDeviceToHost, st));
+            LSB_CU(c, cudaStreamSynchronize(st));
+        }
+        return LSB200_OK;
+    }
     LSB_CU(c, cudaMemcpyAsync(c->h_count, c->d_counts.as<uint32_t>() + idx, 4, cudaMemcpyDeviceToHost, st));
     LSB_CU(c, cudaStreamSynchronize(st));
     const uint32_t n = c->h_count[0];
@@ -1072,10 +1173,21 @@ int lsb200_fetch_batch(lsb200_ctx *c, int first, int count, void *const *outs, c
     if (!c->d_counts.p) return fail(c, LSB200_ERR_STATE, "fetch_batch: nothing traced yet");
     DeviceGuard dg(c->device);
     cudaStream_t st = c->stream;
+    int rc = LSB200_OK;
+    if (flags & LSB200_TRACE_RANGE_IMAGE) {
+        for (int i = 0; i < count; ++i) {
+            const Sensor &s = c->sensors[first + i];
+            if (!s.set || !s.t.p) return fail(c, LSB200_ERR_STATE, "fetch_batch: sensor %d was never traced", first + i);
+            n_pts[i] = (uint32_t)s.n_rays();
+            if (outs[i] && caps[i] < n_pts[i]) { rc = fail(c, LSB200_ERR_CAPACITY, "fetch_batch: sensor %d: range image of %u rays, capacity %zu", first + i, n_pts[i], caps[i]); continue; }
+            if (outs[i]) LSB_CU(c, cudaMemcpyAsync(outs[i], s.t.p, (size_t)n_pts[i] * 4, cudaMemcpyDeviceToHost, st));
+        }
+        LSB_CU(c, cudaStreamSynchronize(st));
+        return rc;
+    }
     // one copy for all hit counts, one synchronisation, then all point copies back to back
     LSB_CU(c, cudaMemcpyAsync(n_pts, c->d_counts.as<uint32_t>() + first, (size_t)count * 4, cudaMemcpyDeviceToHost, st));
     LSB_CU(c, cudaStreamSynchronize(st));
-    int rc = LSB200_OK;
     for (int i = 0; i < count; ++i) {
         const Sensor &s = c->sensors[first + i];
         if (!s.set || !s.points.p) return fail(c, LSB200_ERR_STATE, "fetch_batch: sensor %d was never traced", first + i);
@@ -1113,12 +1225,13 @@ int lsb200_run_frames(lsb200_ctx *c, const lsb200_frame *frames, int n_frames, i
         const uint32_t *hc = c->h_count + 16 + (size_t)slot * kMaxSensors;
         for (int i = 0; i < count; ++i) {
             const Sensor &s = c->sensors[first + i];
-            const uint32_t n = hc[first + i];
+            const bool range_image = (flags & LSB200_TRACE_RANGE_IMAGE) != 0;
+            const uint32_t n = range_image ? (uint32_t)s.n_rays() : hc[first + i];
             frames[f].n_pts[i] = n;
             const size_t cap = frames[f].capacities[i];
             if (n > cap) result = fail(c, LSB200_ERR_CAPACITY, "run_frames: frame %d sensor %d has %u points, capacity %zu", f, first + i, n, cap);
-            const size_t ncopy = std::min<size_t>(n, cap);
-            const void *src = slot ? s.points_b.p : s.points.p;
+            const size_t ncopy = range_image ? (n > cap ? 0 : n) : std::min<size_t>(n, cap);
+            const void *src = range_image ? (slot ? s.t_b.p : s.t.p) : (slot ? s.points_b.p : s.points.p);
             if (frames[f].out_points[i] && ncopy)
                 LSB_CU(c, cudaMemcpyAsync(frames[f].out_points[i], src, ncopy * rec, cudaMemcpyDeviceToHost, cs));
         }
@@ -1184,6 +1297,19 @@ int lsb200_device_results(lsb200_ctx *c, int idx, void **d_points, uint32_t **d_
     if (d_count) *d_count = c->d_counts.p ? c->d_counts.as<uint32_t>() + idx : nullptr;
     if (d_t) *d_t = s.t.as<float>();
     if (d_tri) *d_tri = s.tri.as<int32_t>();
+    return LSB200_OK;
+}
+
+int lsb200_fetch_intensity(lsb200_ctx *c, int idx, float *out)
+{
+    if (!c || !out) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set) return fail(c, LSB200_ERR_INVALID, "fetch_intensity: bad sensor %d", idx);
+    Sensor &s = c->sensors[idx];
+    if (!s.inten.p) return fail(c, LSB200_ERR_STATE, "fetch_intensity: no intensity model / filter was active in the last trace of sensor %d", idx);
+    DeviceGuard dg(c->device);
+    LSB_CU(c, cudaMemcpyAsync(out, s.inten.p, (size_t)s.n_rays() * 4, cudaMemcpyDeviceToHost, c->stream));
+    LSB_CU(c, cudaStreamSynchronize(c->stream));
     return LSB200_OK;
 }
 
@@ -1305,6 +1431,263 @@ int lsb200_debug_copy_vertices(lsb200_ctx *c, float *xyz, int64_t cap)
     LSB_CU(c, cudaMemcpyAsync(tmp.data(), c->d_xverts.p, tmp.size() * 4, cudaMemcpyDeviceToHost, c->stream));
     LSB_CU(c, cudaStreamSynchronize(c->stream));
     for (int i = 0; i < c->n_verts; ++i) { xyz[3 * i] = tmp[4 * i]; xyz[3 * i + 1] = tmp[4 * i + 1]; xyz[3 * i + 2] = tmp[4 * i + 2]; }
+    return LSB200_OK;
+}
+
+}  // extern "C"
+
+// =============================================================================================================
+//  Round-2 additions to the boundary: log sink, pinned host memory placed next to the GPU, range-image expander,
+//  scene cloning and the multi-GPU batch entry
+// =============================================================================================================
+namespace {
+
+// NUMA node of a CUDA device from sysfs (/sys/bus/pci/devices/<bdf>/numa_node); -1 when unknown
+int device_numa_node(int cuda_device)
+{
+    char bdf[32] = {0};
+    if (cudaDeviceGetPCIBusId(bdf, sizeof(bdf), cuda_device) != cudaSuccess) return -1;
+    for (char *p = bdf; *p; ++p) if (*p >= 'A' && *p <= 'Z') *p = (char)(*p - 'A' + 'a');
+    char path[128];
+    snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/numa_node", bdf);
+    FILE *f = fopen(path, "r");
+    if (!f) return -1;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    return node;
+}
+
+// CPUs of a NUMA node ("0-15,32-47") -> cpu_set_t; false when the node is unknown
+bool node_cpus(int node, cpu_set_t *set)
+{
+    char path[128];
+    snprintf(path, sizeof(path), "/sys/devices/system/node/node%d/cpulist", node);
+    FILE *f = fopen(path, "r");
+    if (!f) return false;
+    char buf[4096] = {0};
+    const bool ok = fgets(buf, sizeof(buf), f) != nullptr;
+    fclose(f);
+    if (!ok) return false;
+    CPU_ZERO(set);
+    int n = 0;
+    for (char *p = buf; *p;) {
+        char *e;
+        long a = strtol(p, &e, 10);
+        if (e == p) break;
+        long b = a;
+        if (*e == '-') { p = e + 1; b = strtol(p, &e, 10); }
+        for (long k = a; k <= b && k < CPU_SETSIZE; ++k) { CPU_SET((int)k, set); ++n; }
+        p = (*e == ',') ? e + 1 : e;
+        if (*e != ',') break;
+    }
+    return n > 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lsb200_set_log_callback(lsb200_ctx *c, lsb200_log_fn fn, void *user)
+{
+    if (!c) {                                   // process-wide default: inherited by contexts created afterwards
+        std::lock_guard<std::mutex> lk(g_log_mtx);
+        g_log_fn = fn; g_log_user = user;
+        return LSB200_OK;
+    }
+    std::lock_guard<std::mutex> lk(c->mtx);
+    c->log_fn = fn; c->log_user = user;
+    return LSB200_OK;
+}
+
+// Pinned host memory for the output clouds / vertex blobs, allocated while the calling thread is bound to the CPUs
+// (and, through the kernel's local-allocation policy, the memory) of the NUMA node the context's GPU hangs off, so
+// the D2H copies of several GPUs do not all land on one socket's memory controller.
+int lsb200_alloc_host(lsb200_ctx *c, size_t bytes, void **out)
+{
+    if (!c || !out) return LSB200_ERR_INVALID;
+    *out = nullptr;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    DeviceGuard dg(c->device);
+    cpu_set_t old_set, node_set;
+    bool bound = false;
+    const int node = device_numa_node(c->device);
+    if (node >= 0 && sched_getaffinity(0, sizeof(old_set), &old_set) == 0 && node_cpus(node, &node_set)) {
+        cpu_set_t both;
+        CPU_AND(&both, &old_set, &node_set);     // never leave the cpuset the process was given
+        if (CPU_COUNT(&both) > 0 && sched_setaffinity(0, sizeof(both), &both) == 0) bound = true;
+    }
+    void *p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e == cudaSuccess && bytes) std::memset(p, 0, bytes);       // first touch while bound
+    if (bound) sched_setaffinity(0, sizeof(old_set), &old_set);
+    if (e != cudaSuccess) return fail(c, LSB200_ERR_NOMEM, "alloc_host: cudaHostAlloc(%zu) -> %s", bytes, cudaGetErrorString(e));
+    logf(c, LSB200_LOG_DEBUG, "lsb200: %zu pinned host bytes for device %d (NUMA node %d, %s)", bytes, c->device, node,
+         bound ? "thread bound during allocation" : "no binding");
+    *out = p;
+    return LSB200_OK;
+}
+
+int lsb200_free_host(lsb200_ctx *c, void *p)
+{
+    if (!p) return LSB200_OK;
+    if (cudaFreeHost(p) != cudaSuccess) return fail(c, LSB200_ERR_CUDA, "free_host failed");
+    return LSB200_OK;
+}
+
+int lsb200_device_numa_node(const lsb200_ctx *c) { return c ? device_numa_node(c->device) : LSB200_ERR_INVALID; }
+
+// Range image -> point records on the HOST, for consumers that asked for LSB200_TRACE_RANGE_IMAGE (4 bytes per ray over
+// PCIe instead of 16 / 32 per hit) but still want the reference's records: the same arithmetic as the device
+// (point = t * d_sensor with d_sensor from the host tables, SRC/EmbreeTracer.cpp:331-333), hits in ray-id order, so the
+// bytes equal those of an LSB200_TRACE_ORDERED trace.
+int lsb200_expand_range_image(lsb200_ctx *c, int idx, const float *t, void *out_points, size_t capacity, uint32_t *n_pts, uint32_t flags)
+{
+    if (!c || !t) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set) return fail(c, LSB200_ERR_INVALID, "expand_range_image: bad sensor %d", idx);
+    const Sensor &s = c->sensors[idx];
+    const int V = s.V, H = s.H;
+    const float *st = s.h_tab.data(), *ct = st + V, *sp = st + 2 * V, *cp = st + 2 * V + H;
+    const bool xyzi16 = (flags & LSB200_TRACE_XYZI16) != 0, world = (flags & LSB200_TRACE_WORLD_POINTS) != 0;
+    const bool ring0 = (flags & LSB200_TRACE_RING_ZERO) != 0;
+    uint8_t *out = static_cast<uint8_t *>(out_points);
+    size_t n = 0;
+    for (int v = 0; v < V; ++v) {
+        for (int h = 0; h < H; ++h) {
+            const float tt = t[(size_t)v * H + h];
+            if (!(tt <= 3.402823466e+38f)) continue;               // +inf / NaN: no return
+            if (n < capacity && out) {
+                const float dsx = st[v] * cp[h], dsy = st[v] * sp[h], dsz = ct[v];
+                float x = tt * dsx, y = tt * dsy, z = tt * dsz;
+                if (world) {
+                    const float wx = (s.R[0] * x + (s.R[1] * y + s.R[2] * z)) + s.T[0];
+                    const float wy = (s.R[3] * x + (s.R[4] * y + s.R[5] * z)) + s.T[1];
+                    const float wz = (s.R[6] * x + (s.R[7] * y + s.R[8] * z)) + s.T[2];
+                    x = wx; y = wy; z = wz;
+                }
+                if (xyzi16) {
+                    const float rec[4] = {x, y, z, 64.0f};
+                    std::memcpy(out + 16 * n, rec, 16);
+                } else {
+                    float rec[8] = {x, y, z, 0.0f, 64.0f, 0.0f, 0.0f, 0.0f};
+                    const int32_t ring = ring0 ? 0 : v;
+                    std::memcpy(&rec[5], &ring, 4);
+                    std::memcpy(out + 32 * n, rec, 32);
+                }
+            }
+            ++n;
+        }
+    }
+    if (n_pts) *n_pts = (uint32_t)n;
+    if (out && n > capacity) return fail(c, LSB200_ERR_CAPACITY, "expand_range_image: %zu points, capacity %zu", n, capacity);
+    return LSB200_OK;
+}
+
+// A second context on another GPU holding the same scene: options, sensors (+ limits), every geometry's vertex and
+// index data (device-to-device copies over NVLink / PCIe peer access) and transforms.  The scene is replicated per
+// GPU, as north_star asks; nothing is shared afterwards.
+int lsb200_clone_scene(lsb200_ctx *src, int cuda_device, lsb200_ctx **out)
+{
+    if (!src || !out) return LSB200_ERR_INVALID;
+    *out = nullptr;
+    lsb200_ctx *dst = nullptr;
+    int rc = lsb200_create(cuda_device, &dst);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(src->mtx);
+    auto bail = [&](int code) { lsb200_destroy(dst); return code; };
+    dst->frame_mode = src->frame_mode;
+    dst->opt_traversal = src->opt_traversal; dst->opt_leaf = src->opt_leaf; dst->opt_top = src->opt_top;
+    dst->opt_ctas_per_sm = src->opt_ctas_per_sm; dst->opt_morton_uniform = src->opt_morton_uniform;
+    dst->opt_morton_layout = src->opt_morton_layout; dst->opt_morton_aspect = src->opt_morton_aspect; dst->opt_chain = src->opt_chain;
+    dst->opt_tile_w_log2 = src->opt_tile_w_log2; dst->opt_small_build = src->opt_small_build; dst->opt_tile_entries = src->opt_tile_entries;
+    dst->opt_tile_visits = src->opt_tile_visits; dst->opt_tile_min_units = src->opt_tile_min_units;
+    dst->opt_watertight = src->opt_watertight; dst->opt_intensity = src->opt_intensity;
+    dst->log_fn = src->log_fn; dst->log_user = src->log_user;
+    for (size_t i = 0; i < src->sensors.size(); ++i) {
+        const Sensor &s = src->sensors[i];
+        if (!s.set) continue;
+        rc = lsb200_set_sensor(dst, (int)i, s.elev.data(), s.V, s.az_begin, s.az_end, s.H, s.q, s.T);
+        if (rc) return bail(rc);
+        if (s.lim_range > 0.0f || s.has_mask) { rc = lsb200_set_sensor_limits(dst, (int)i, s.lim_range, s.lim_lo, s.lim_hi); if (rc) return bail(rc); }
+        if (s.min_intensity > 0.0f) lsb200_set_sensor_intensity_filter(dst, (int)i, s.min_intensity);
+    }
+    {
+        DeviceGuard dgs(src->device);
+        cudaStreamSynchronize(src->stream);         // pending uploads of the source have landed
+    }
+    for (auto &kv : src->geoms) {
+        const Geometry &g = kv.second;
+        // ids are assigned lowest-free-first on both sides and the source's ids may have holes: add under the same id
+        Geometry &d = dst->geoms[g.id];
+        d.name = g.name; d.id = g.id; d.type = g.type; d.n_verts = g.n_verts; d.n_elems = g.n_elems;
+        d.verts_per_elem = g.verts_per_elem; d.stride = g.stride;
+        std::memcpy(d.A, g.A, sizeof(d.A));
+        dst->by_name[g.name] = g.id;
+        DeviceGuard dgd(dst->device);
+        if (g.has_verts) {
+            const size_t bytes = (size_t)g.n_verts * (size_t)g.stride;
+            if (d.verts.reserve(std::max<size_t>(bytes, 16), dst->stream) != cudaSuccess) return bail(LSB200_ERR_NOMEM);
+            if (bytes && cudaMemcpyPeerAsync(d.verts.p, dst->device, g.verts.p, src->device, bytes, dst->stream) != cudaSuccess) return bail(LSB200_ERR_CUDA);
+            d.has_verts = true;
+        }
+        if (g.has_elems) {
+            const size_t bytes = (size_t)g.n_elems * g.verts_per_elem * sizeof(uint32_t);
+            if (d.elems.reserve(std::max<size_t>(bytes, 16), dst->stream) != cudaSuccess) return bail(LSB200_ERR_NOMEM);
+            if (bytes && cudaMemcpyPeerAsync(d.elems.p, dst->device, g.elems.p, src->device, bytes, dst->stream) != cudaSuccess) return bail(LSB200_ERR_CUDA);
+            d.has_elems = true;
+        }
+    }
+    {
+        DeviceGuard dgd(dst->device);
+        if (cudaStreamSynchronize(dst->stream) != cudaSuccess) return bail(LSB200_ERR_CUDA);
+    }
+    dst->topology_dirty = true; dst->committed = false;
+    *out = dst;
+    return LSB200_OK;
+}
+
+// Multi-GPU batch: the C entry for a host that owns the whole box (the reference runs one tracer per LiDAR device in
+// one process, SRC/mainwindow.cpp:256-274).  One context per GPU (lsb200_create + scene, or lsb200_clone_scene), one
+// host thread per context, each running lsb200_run_frames on its share.  No data-path collective: the (device, frame)
+// scans are independent.
+//   LSB200_SHARD_FRAMES   context g takes frames g, g + n, ... (each GPU rebuilds only its own frames' BVH: config 5)
+//   LSB200_SHARD_SENSORS  every context takes every frame and traces a contiguous share of the sensors (a frame is
+//                         finished as early as possible, every GPU pays the commit: config 4's latency view)
+int lsb200_run_batch(lsb200_ctx *const *ctxs, int n_ctx, const lsb200_frame *frames, int n_frames, int first, int count,
+                     int commit_mode, uint32_t flags, int sharding)
+{
+    if (!ctxs || n_ctx <= 0 || !frames || n_frames <= 0 || count <= 0) return LSB200_ERR_INVALID;
+    for (int g = 0; g < n_ctx; ++g) if (!ctxs[g]) return LSB200_ERR_INVALID;
+    if (sharding != LSB200_SHARD_FRAMES && sharding != LSB200_SHARD_SENSORS) return fail(ctxs[0], LSB200_ERR_INVALID, "run_batch: bad sharding %d", sharding);
+    std::vector<int> rcs((size_t)n_ctx, LSB200_OK);
+    std::vector<std::vector<lsb200_frame>> share((size_t)n_ctx);
+    std::vector<int> s_first((size_t)n_ctx, first), s_count((size_t)n_ctx, count);
+    for (int g = 0; g < n_ctx; ++g) {
+        if (sharding == LSB200_SHARD_FRAMES) {
+            for (int f = g; f < n_frames; f += n_ctx) share[g].push_back(frames[f]);
+        } else {
+            const int lo = (int)((long long)count * g / n_ctx), hi = (int)((long long)count * (g + 1) / n_ctx);
+            s_first[g] = first + lo; s_count[g] = hi - lo;
+            if (hi > lo)
+                for (int f = 0; f < n_frames; ++f) {
+                    lsb200_frame fr = frames[f];
+                    fr.out_points = frames[f].out_points ? frames[f].out_points + lo : nullptr;
+                    fr.capacities = frames[f].capacities ? frames[f].capacities + lo : nullptr;
+                    fr.n_pts = frames[f].n_pts ? frames[f].n_pts + lo : nullptr;
+                    share[g].push_back(fr);
+                }
+        }
+    }
+    std::vector<std::thread> threads;
+    for (int g = 0; g < n_ctx; ++g) {
+        if (share[g].empty()) continue;
+        threads.emplace_back([&, g]() {
+            rcs[g] = lsb200_run_frames(ctxs[g], share[g].data(), (int)share[g].size(), s_first[g], s_count[g], commit_mode, flags);
+        });
+    }
+    for (auto &t : threads) t.join();
+    for (int g = 0; g < n_ctx; ++g) if (rcs[g] != LSB200_OK) return rcs[g];
     return LSB200_OK;
 }
 

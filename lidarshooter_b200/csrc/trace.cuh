@@ -132,6 +132,7 @@ __device__ __forceinline__ float2 ldg_f2_hint(const float2 *a, uint64_t pol)
 struct Ray {
     float ox, oy, oz, dx, dy, dz;
 };
+template <bool WT = false>
 __device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, float &best, int &bi);   // depth-guard fallback
 constexpr int kRayOverflow = -2;       // trace_ray_lz: "my stack overflowed" (never a triangle id)
 
@@ -165,6 +166,52 @@ __device__ __forceinline__ bool intersect_tri(const float4 q0, const float4 q1, 
     return true;
 }
 
+// Watertight ray / triangle test (Woop, Benthin, Wald 2013, "Watertight Ray/Triangle Intersection"), the optional
+// LSB200_OPT_WATERTIGHT mode; bit-identical to oracle/lsb_oracle.c: lso_intersect_wt.  The triangle record of this
+// mode holds the three ORIGINAL vertices (q0 = v0.xyz v1.x, q1 = v1.yz v2.xy, q2 = v2.z): two triangles that share
+// an edge then evaluate that edge's function on bit-identical operands with opposite sign, so a ray cannot pass
+// between them.  Ray-space set-up (dominant axis kz, shear Sx Sy, scale Sz) is recomputed from the direction (cheap,
+// and it keeps six registers out of the traversal loop); the edge functions fall back to exact double products when
+// one of them is 0 in fp32.  No back-face culling, tnear = 0 (strict), tfar = +inf, like the default test.
+__device__ __forceinline__ float sel3(int k, float x, float y, float z) { return k == 0 ? x : (k == 1 ? y : z); }
+
+__device__ __forceinline__ bool intersect_tri_wt(const float4 q0, const float4 q1, const float4 q2, const Ray &r, float &t_out)
+{
+    const float ax = fabsf(r.dx), ay = fabsf(r.dy), az = fabsf(r.dz);
+    int kz = (ax > ay) ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+    int kx = kz == 2 ? 0 : kz + 1, ky = kx == 2 ? 0 : kx + 1;
+    const float dkz = sel3(kz, r.dx, r.dy, r.dz);
+    if (dkz < 0.0f) { const int tmp = kx; kx = ky; ky = tmp; }
+    const float Sx = __fdiv_rn(sel3(kx, r.dx, r.dy, r.dz), dkz), Sy = __fdiv_rn(sel3(ky, r.dx, r.dy, r.dz), dkz);
+    const float Sz = __fdiv_rn(1.0f, dkz);
+    const float Ax_ = __fsub_rn(q0.x, r.ox), Ay_ = __fsub_rn(q0.y, r.oy), Az_ = __fsub_rn(q0.z, r.oz);
+    const float Bx_ = __fsub_rn(q0.w, r.ox), By_ = __fsub_rn(q1.x, r.oy), Bz_ = __fsub_rn(q1.y, r.oz);
+    const float Cx_ = __fsub_rn(q1.z, r.ox), Cy_ = __fsub_rn(q1.w, r.oy), Cz_ = __fsub_rn(q2.x, r.oz);
+    const float Akz = sel3(kz, Ax_, Ay_, Az_), Bkz = sel3(kz, Bx_, By_, Bz_), Ckz = sel3(kz, Cx_, Cy_, Cz_);
+    const float Ax = __fsub_rn(sel3(kx, Ax_, Ay_, Az_), __fmul_rn(Sx, Akz)), Ay = __fsub_rn(sel3(ky, Ax_, Ay_, Az_), __fmul_rn(Sy, Akz));
+    const float Bx = __fsub_rn(sel3(kx, Bx_, By_, Bz_), __fmul_rn(Sx, Bkz)), By = __fsub_rn(sel3(ky, Bx_, By_, Bz_), __fmul_rn(Sy, Bkz));
+    const float Cx = __fsub_rn(sel3(kx, Cx_, Cy_, Cz_), __fmul_rn(Sx, Ckz)), Cy = __fsub_rn(sel3(ky, Cx_, Cy_, Cz_), __fmul_rn(Sy, Ckz));
+    float U = __fsub_rn(__fmul_rn(Cx, By), __fmul_rn(Cy, Bx));
+    float V = __fsub_rn(__fmul_rn(Ax, Cy), __fmul_rn(Ay, Cx));
+    float W = __fsub_rn(__fmul_rn(Bx, Ay), __fmul_rn(By, Ax));
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {           // on (or within fp32 rounding of) an edge: exact products
+        U = (float)__dsub_rn(__dmul_rn((double)Cx, (double)By), __dmul_rn((double)Cy, (double)Bx));
+        V = (float)__dsub_rn(__dmul_rn((double)Ax, (double)Cy), __dmul_rn((double)Ay, (double)Cx));
+        W = (float)__dsub_rn(__dmul_rn((double)Bx, (double)Ay), __dmul_rn((double)By, (double)Ax));
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+    const float det = __fadd_rn(__fadd_rn(U, V), W);
+    if (!(det != 0.0f)) return false;
+    const float Az = __fmul_rn(Sz, Akz), Bz = __fmul_rn(Sz, Bkz), Cz = __fmul_rn(Sz, Ckz);
+    const float T = __fadd_rn(__fadd_rn(__fmul_rn(U, Az), __fmul_rn(V, Bz)), __fmul_rn(W, Cz));
+    const float t = __fdiv_rn(T, det);
+    if (!(t > 0.0f)) return false;                         // tnear = 0, strict; also rejects NaN
+    if (!(t <= 3.402823466e+38f)) return false;            // tfar = +inf
+    t_out = t;
+    return true;
+}
+
+template <bool WT = false>
 __device__ __forceinline__ void test_leaf(const TraceParams &P, int ref, const Ray &r, float &best, int &bi)
 {
     const int enc = ~ref;
@@ -180,7 +227,7 @@ __device__ __forceinline__ void test_leaf(const TraceParams &P, int ref, const R
 #endif
         const int g = __ldg(P.leaf_ids + first + k);        // with the record: no dependent round trip after a hit
         float t;
-        if (intersect_tri(q0, q1, q2, r, t) && t <= best) {
+        if ((WT ? intersect_tri_wt(q0, q1, q2, r, t) : intersect_tri(q0, q1, q2, r, t)) && t <= best) {
             if (t < best || g < bi) { best = t; bi = g; }   // lexicographic minimum of (t, global triangle id)
         }
     }
@@ -398,7 +445,7 @@ __device__ __forceinline__ void trace_ray_ww(const TraceParams &P, float eps, co
 // entries are taken in near -> far order only when the ray has nothing else left, and tested against the hit
 // distance known by then, so whatever lies behind the first hit fails its own box test.  The stack holds deferred
 // children only.  Same set of subtrees entered or rejected by conservative tests: same results.
-template <int OCT, bool STATS, bool SMEM>
+template <int OCT, bool STATS, bool SMEM, bool WT = false>
 __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, const Ray &r,
                                              const float4 *__restrict__ chain, int n_chain, bool reversed,
                                              float &best_out, int &bi_out, RayStats &rs, int2 *s_stack = nullptr)
@@ -493,7 +540,7 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
         }
         if (cur < 0) {
             if (STATS) { ++rs.leaves; rs.tris += (unsigned)(((~cur) >> kLeafShift) + 1); }
-            test_leaf(P, cur, r, best, bi);
+            test_leaf<WT>(P, cur, r, best, bi);
             far_lim = best * 1.0000005f;
             cur = kDone;
             while (depth() > 0) {
@@ -594,13 +641,15 @@ __device__ __forceinline__ void trace_ray_il(const TraceParams &P, float eps, co
 #endif  // LSB_LAB
 
 // Brute force over all leaf-ordered triangles (validation variant; also the tiny-scene path).
+template <bool WT>
 __device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, float &best, int &bi)
 {
     best = INFINITY; bi = -1;
     for (int k = 0; k < P.n_tris; ++k) {
         const float4 *rec = P.tris + 3 * (size_t)k;
         float t;
-        if (intersect_tri(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2), r, t) && t <= best) {
+        const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2);
+        if ((WT ? intersect_tri_wt(q0, q1, q2, r, t) : intersect_tri(q0, q1, q2, r, t)) && t <= best) {
             const int g = __ldg(P.leaf_ids + k);
             if (t < best || g < bi) { best = t; bi = g; }
         }
@@ -608,11 +657,12 @@ __device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, fl
 }
 
 // Out-of-line copy for the depth-guard fallback (adversarial scenes only): kept out of the traversal's register budget.
+template <bool WT>
 __device__ __noinline__ void brute_ray_cold(const float4 *tris, const int32_t *leaf_ids, int n_tris, const Ray &r, float &best, int &bi)
 {
     TraceParams P{};
     P.tris = tris; P.leaf_ids = leaf_ids; P.n_tris = n_tris;
-    brute_ray(P, r, best, bi);
+    brute_ray<WT>(P, r, best, bi);
 }
 
 __device__ __forceinline__ int find_sensor_by_unit(const SensorDev *s, int n, int unit)
@@ -623,15 +673,16 @@ __device__ __forceinline__ int find_sensor_by_unit(const SensorDev *s, int n, in
 }
 
 // Writes one hit.  32-byte record (SRC/XYZIRBytes.cpp:24-40) or 16-byte XYZI.
-__device__ __forceinline__ void store_point(uint8_t *points, uint32_t slot, uint32_t flags, float x, float y, float z, int ring)
+__device__ __forceinline__ void store_point(uint8_t *points, uint32_t slot, uint32_t flags, float x, float y, float z, int ring,
+                                            float intensity = 64.0f /* the reference's constant, SRC/EmbreeTracer.cpp:333 */)
 {
     // streaming stores: the 1.2 GB of results per frame should not evict the BVH from L2
     if (flags & 4u /*LSB200_TRACE_XYZI16*/) {
-        __stcs(reinterpret_cast<float4 *>(points) + slot, make_float4(x, y, z, 64.0f));
+        __stcs(reinterpret_cast<float4 *>(points) + slot, make_float4(x, y, z, intensity));
     } else {
         float4 *p = reinterpret_cast<float4 *>(points) + 2 * (size_t)slot;
         __stcs(p, make_float4(x, y, z, 0.0f));
-        __stcs(p + 1, make_float4(64.0f, __int_as_float(ring), 0.0f, 0.0f));
+        __stcs(p + 1, make_float4(intensity, __int_as_float(ring), 0.0f, 0.0f));
     }
 }
 
@@ -711,7 +762,7 @@ __device__ __forceinline__ void flush_append(const TraceParams &P, PendingAppend
 
 // One 32-ray work unit: generate the rays, trace them, store t / triangle id, append the hits.
 // MODE: see k_trace.  OCT: slab form for every ray of the unit (0..7 only when classified uniform).
-template <int MODE, int OCT, bool STATS>
+template <int MODE, int OCT, bool STATS, bool WT = false>
 __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 *s_top, int n_top, float smax, int4 ud,
                                              unsigned lane, int tile_n = -1, const float4 *s_list = nullptr,
                                              PendingAppend *pend = nullptr, float4 *s_pts = nullptr, int2 *s_stack = nullptr)
@@ -737,7 +788,7 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
         float omax;
         make_ray(S, P.world_frame, v, h, r, dsx, dsy, dsz, omax);
         const float eps = 8e-6f * (smax + omax) + 1e-30f;
-        if (MODE == 3) brute_ray(P, r, best, bi);
+        if (MODE == 3) brute_ray<WT>(P, r, best, bi);
         else if (w_tile && tile_n == 0) { /* nothing to hit */ }
         else {
             const int list = si * 9 + OCT;
@@ -748,8 +799,8 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
                 else trace_ray_il<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
             } else
             if (MODE == 6 && LSB_LAZY_LIST) {
-                if (w_tile) trace_ray_lz<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs, s_stack);
-                else trace_ray_lz<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs, s_stack);
+                if (w_tile) trace_ray_lz<OCT, STATS, true, WT>(P, eps, r, s_list, tile_n, true, best, bi, rs, s_stack);
+                else trace_ray_lz<OCT, STATS, false, WT>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs, s_stack);
             } else
             if (w_tile) trace_ray_ww<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs);
             else if (MODE == 5 || MODE == 6) trace_ray_ww<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs);
@@ -757,11 +808,11 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
             trace_ray<TOP, OCT, STATS>(P, s_top, n_top, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, best, bi, rs);
 #else
             // product build: the one shipped traversal (variant 6, lazy tile / chain list)
-            if (w_tile) trace_ray_lz<OCT, STATS, true>(P, eps, r, s_list, tile_n, true, best, bi, rs, s_stack);
-            else trace_ray_lz<OCT, STATS, false>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs, s_stack);
+            if (w_tile) trace_ray_lz<OCT, STATS, true, WT>(P, eps, r, s_list, tile_n, true, best, bi, rs, s_stack);
+            else trace_ray_lz<OCT, STATS, false, WT>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs, s_stack);
 #endif
         }
-        if (bi == kRayOverflow) brute_ray_cold(P.tris, P.leaf_ids, P.n_tris, r, best, bi);
+        if (bi == kRayOverflow) brute_ray_cold<WT>(P.tris, P.leaf_ids, P.n_tris, r, best, bi);
         if (!(best <= S.max_range)) { best = INFINITY; bi = -1; }                // detection radius (closest hit beyond it: no return)
         __stcs(S.t_out + ray, best);
         __stcs(S.tri_out + ray, bi);
@@ -833,7 +884,7 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-template <int MODE, int OCT, bool STATS>
+template <int MODE, int OCT, bool STATS, bool WT = false>
 __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsigned lane, float4 *s_list, float4 *s_pts, int2 *s_stack,
                                           int part = 0)
 {
@@ -848,7 +899,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
             if (lane == 0) k = (int)atomicAdd(&P.work[2 + OCT], 1u);
             k = __shfl_sync(0xffffffffu, k, 0);
             if (k >= count) break;
-            process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, __ldg(P.unit_list + begin + k), lane);
+            process_unit<MODE, OCT, STATS, WT>(P, nullptr, 0, smax, __ldg(P.unit_list + begin + k), lane);
         }
         return;
     }
@@ -884,7 +935,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
         else cp_async_commit();
         cp_async_wait<1>();                                        // everything but the newest group: this unit's list is in
         __syncwarp();
-        process_unit<MODE, OCT, STATS>(P, nullptr, 0, smax, ud, lane, tn == kTileFallback ? -1 : tn, s_list + b * kBuf, LSB_DEFER_APPEND ? &pend : nullptr, s_pts, s_stack);
+        process_unit<MODE, OCT, STATS, WT>(P, nullptr, 0, smax, ud, lane, tn == kTileFallback ? -1 : tn, s_list + b * kBuf, LSB_DEFER_APPEND ? &pend : nullptr, s_pts, s_stack);
         if (!more) break;
         __syncwarp();                                              // all lanes are done with buffer b before it is refilled
         ud = ud_n; tn = tn_n; b ^= 1;
@@ -903,7 +954,8 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
 // MODE 5: MODE 1 in while-while form (node loop and leaf tests separated)
 // MODE 6: MODE 0 in while-while form
 // STATS: per-ray node / leaf / triangle counters summed into P.counters (diagnostic launches only)
-template <int MODE, bool STATS>
+// WT: watertight intersector (LSB200_OPT_WATERTIGHT; variants 6 and 3 only -- the triangle records then hold raw vertices)
+template <int MODE, bool STATS, bool WT = false>
 __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TraceParams P)
 {
     constexpr bool TOP = (MODE == 4);
@@ -942,31 +994,31 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
         // (a ray within ~4 degrees of the horizon or above it) at the front of every queue; the heavy fronts of the downward
         // octants (4..7) are drained early, together with the sign-mixed and the upward queues, and the light remainders
         // (steep rays that hit the ground nearby, ~10 us a unit) make the tail: 1.67 -> 1.53 ms for the stage.
-        if (LSB_PHASE_ORDER != 2) run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        if (LSB_PHASE_ORDER != 2) run_phase<MODE, 8, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
         if (MODE == 6 && LSB_SPLIT_DOWNWARD && LSB_PHASE_ORDER == 0) {
-            run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
-            run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            run_phase<MODE, 4, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            run_phase<MODE, 6, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
         }
-        run_phase<MODE, 0, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 1, STATS>(P, smax, lane, s_list, s_pts, s_stack);
-        run_phase<MODE, 2, STATS>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 3, STATS>(P, smax, lane, s_list, s_pts, s_stack);
-        if (LSB_PHASE_ORDER == 2) run_phase<MODE, 8, STATS>(P, smax, lane, s_list, s_pts, s_stack);
+        run_phase<MODE, 0, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 1, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
+        run_phase<MODE, 2, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 3, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
+        if (LSB_PHASE_ORDER == 2) run_phase<MODE, 8, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
         if (MODE == 6 && LSB_SPLIT_DOWNWARD && LSB_PHASE_ORDER >= 1) {
-            run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
-            run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            run_phase<MODE, 4, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            run_phase<MODE, 6, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
         }
         const int rest = (MODE == 6 && LSB_SPLIT_DOWNWARD) ? 2 : 0;
-        run_phase<MODE, 4, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 5, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest);
-        run_phase<MODE, 6, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 7, STATS>(P, smax, lane, s_list, s_pts, s_stack, rest);
+        run_phase<MODE, 4, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 5, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest);
+        run_phase<MODE, 6, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 7, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest);
     } else if (MODE == 2) {
         const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
-        if (unit < P.n_units) process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
+        if (unit < P.n_units) process_unit<MODE, 8, STATS, WT>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
     } else {
         while (true) {
             int unit = 0;
             if (lane == 0) unit = P.unit_lo + (int)atomicAdd(&P.work[0], 1u);
             unit = __shfl_sync(0xffffffffu, unit, 0);
             if (unit >= P.n_units) break;
-            process_unit<MODE, 8, STATS>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
+            process_unit<MODE, 8, STATS, WT>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
         }
     }
     if (MODE != 2) {
@@ -1457,6 +1509,46 @@ __global__ void __launch_bounds__(256) k_fill_u32(uint32_t *__restrict__ p, uint
     if (i < n) p[i] = v;
 }
 
+// ---- intensity model + intensity filter --------------------------------------------------------
+// The reference writes the constant 64.0 (SRC/EmbreeTracer.cpp:333) and carries `use_intensity_filtering` /
+// `minimum_intensity` in its device config without applying them (config/hesai-pandar-XT-32-lidar_0000.json:19-20).
+// Optional post-pass over the per-ray results, off the traversal's hot path: model 1 = Lambertian cos-incidence
+// 255 * |Ng . d| / (|Ng| |d|) from the hit triangle (Ng = cross(e2, e1) of the transformed vertices, the same
+// normal the intersector uses); a return below the sensor's minimum intensity becomes a miss.  Fixed fp32 operation
+// order == oracle/lsb_oracle.c: lso_intensity.
+constexpr uint32_t kFlagIntensityBuffer = 1u << 30;      // internal: k_scatter_hits takes the intensity from S.intensity
+__global__ void __launch_bounds__(256) k_intensity(SceneDev Sc, const SensorDev *__restrict__ sensors, int sensor_base, int world_frame, int model)
+{
+    const SensorDev &S = sensors[sensor_base + blockIdx.y];
+    const int ray = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ray >= S.n_rays) return;
+    const int g = S.tri_out[ray];
+    float I = 0.0f;
+    if (g >= 0) {
+        I = 64.0f;
+        if (model == 1) {
+            int a, b, c;
+            tri_vertex_ids(Sc, g, a, b, c);
+            const float4 A = Sc.xverts[a], B = Sc.xverts[b], C = Sc.xverts[c];
+            const float e1x = __fsub_rn(A.x, B.x), e1y = __fsub_rn(A.y, B.y), e1z = __fsub_rn(A.z, B.z);
+            const float e2x = __fsub_rn(C.x, A.x), e2y = __fsub_rn(C.y, A.y), e2z = __fsub_rn(C.z, A.z);
+            const float ngx = __fsub_rn(__fmul_rn(e2y, e1z), __fmul_rn(e2z, e1y));
+            const float ngy = __fsub_rn(__fmul_rn(e2z, e1x), __fmul_rn(e2x, e1z));
+            const float ngz = __fsub_rn(__fmul_rn(e2x, e1y), __fmul_rn(e2y, e1x));
+            const int v = ray / S.H, h = ray - v * S.H;
+            Ray r; float dsx, dsy, dsz, om;
+            make_ray(S, world_frame, v, h, r, dsx, dsy, dsz, om);
+            const float den = __fadd_rn(__fadd_rn(__fmul_rn(ngx, r.dx), __fmul_rn(ngy, r.dy)), __fmul_rn(ngz, r.dz));
+            const float nn = __fadd_rn(__fadd_rn(__fmul_rn(ngx, ngx), __fmul_rn(ngy, ngy)), __fmul_rn(ngz, ngz));
+            const float dd = __fadd_rn(__fadd_rn(__fmul_rn(r.dx, r.dx), __fmul_rn(r.dy, r.dy)), __fmul_rn(r.dz, r.dz));
+            const float len = __fsqrt_rn(__fmul_rn(nn, dd));
+            I = len > 0.0f ? __fdiv_rn(__fmul_rn(255.0f, fabsf(den)), len) : 0.0f;
+        }
+        if (I < S.min_intensity) { S.t_out[ray] = INFINITY; S.tri_out[ray] = -1; I = 0.0f; }
+    }
+    S.intensity[ray] = I;
+}
+
 // ---- ordered compaction: count -> scan -> scatter (points in ray-id order) ---------------------------------
 constexpr int kCompactThreads = 256;
 constexpr int kCompactRays = 1024;      // rays per block
@@ -1540,7 +1632,7 @@ __global__ void __launch_bounds__(kCompactThreads) k_scatter_hits(const SensorDe
         const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v), sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
         float x, y, z;
         hit_point(S, flags, S.t_out[ray], __fmul_rn(st, cp), __fmul_rn(st, sp_), ct, x, y, z);
-        store_point(S.points, slot++, flags, x, y, z, (flags & 2u) ? 0 : v);
+        store_point(S.points, slot++, flags, x, y, z, (flags & 2u) ? 0 : v, (flags & kFlagIntensityBuffer) ? S.intensity[ray] : 64.0f);
     }
 }
 

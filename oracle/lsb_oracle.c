@@ -205,7 +205,7 @@ LSO_API void lso_rotate_dirs(const float R[9], const float *dirs_s, int64_t n, f
  * Embree-ordered Moeller-Trumbore (triangle stored as v0, e1 = v0-v1, e2 = v2-v0, Ng = cross(e2,e1)).
  * Returns 1 and *t_out when the ray (org, dir, tnear = 0, tfar = +inf) hits.  No back-face culling.
  * ---------------------------------------------------------------------------------------------- */
-typedef struct { float v0[3], e1[3], e2[3]; } lso_tri;
+typedef struct { float v0[3], e1[3], e2[3]; float v1[3], v2[3]; /* raw vertices: watertight mode */ } lso_tri;
 
 static inline void cross3(const float *a, const float *b, float *o)
 {
@@ -224,6 +224,8 @@ static inline void tri_setup(const float *a, const float *b, const float *c, lso
         t->v0[k] = a[k];
         t->e1[k] = a[k] - b[k];
         t->e2[k] = c[k] - a[k];
+        t->v1[k] = b[k];
+        t->v2[k] = c[k];
     }
 }
 
@@ -250,12 +252,90 @@ static inline int lso_intersect(const lso_tri *tri, const float *org, const floa
     return 1;
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Optional WATERTIGHT mode (not the reference's intersector; north_star asks for it): Woop, Benthin, Wald 2013,
+ * "Watertight Ray/Triangle Intersection", on the triangle's three original vertices.  Ray-space: dominant
+ * axis kz, shear (Sx, Sy), scale Sz; edge functions U V W on the sheared vertices, recomputed with exact
+ * double products when one of them is 0; no back-face culling; tnear = 0 (strict), tfar = +inf.
+ * Same operation order as lidarshooter_b200/csrc/trace.cuh: intersect_tri_wt (bit-exact parity in this mode).
+ * lso_set_watertight(1) switches lso_trace_brute / lso_trace_bvh to it.
+ * ---------------------------------------------------------------------------------------------- */
+static int g_watertight = 0;
+LSO_API void lso_set_watertight(int on) { g_watertight = on ? 1 : 0; }
+LSO_API int lso_get_watertight(void) { return g_watertight; }
+
+static inline int lso_intersect_wt(const lso_tri *tri, const float *org, const float *dir, float *t_out)
+{
+    const float ax = fabsf(dir[0]), ay = fabsf(dir[1]), az = fabsf(dir[2]);
+    int kz = (ax > ay) ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+    int kx = kz == 2 ? 0 : kz + 1, ky = kx == 2 ? 0 : kx + 1;
+    const float dkz = dir[kz];
+    if (dkz < 0.0f) { const int tmp = kx; kx = ky; ky = tmp; }
+    const float Sx = dir[kx] / dkz, Sy = dir[ky] / dkz, Sz = 1.0f / dkz;
+    float A[3], B[3], C[3];
+    for (int k = 0; k < 3; ++k) { A[k] = tri->v0[k] - org[k]; B[k] = tri->v1[k] - org[k]; C[k] = tri->v2[k] - org[k]; }
+    const float Ax = A[kx] - Sx * A[kz], Ay = A[ky] - Sy * A[kz];
+    const float Bx = B[kx] - Sx * B[kz], By = B[ky] - Sy * B[kz];
+    const float Cx = C[kx] - Sx * C[kz], Cy = C[ky] - Sy * C[kz];
+    float U = Cx * By - Cy * Bx;
+    float V = Ax * Cy - Ay * Cx;
+    float W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return 0;
+    const float det = (U + V) + W;
+    if (!(det != 0.0f)) return 0;
+    const float Az = Sz * A[kz], Bz = Sz * B[kz], Cz = Sz * C[kz];
+    const float T = (U * Az + V * Bz) + W * Cz;
+    const float t = T / det;
+    if (!(t > 0.0f)) return 0;
+    if (!(t <= FLT_MAX)) return 0;
+    *t_out = t;
+    return 1;
+}
+
+static inline int lso_intersect_any(const lso_tri *tri, const float *org, const float *dir, float *t_out)
+{
+    return g_watertight ? lso_intersect_wt(tri, org, dir, t_out) : lso_intersect(tri, org, dir, t_out);
+}
+
+/* Intensity models of include/lsb200.h (LSB200_OPT_INTENSITY_MODEL; semantics defined there -- the reference writes the
+ * constant 64.0, SRC/EmbreeTracer.cpp:333, and never applies its config's minimum_intensity): model 0 = 64.0,
+ * model 1 = 255 |Ng . d| / (|Ng| |d|) with Ng = cross(e2, e1) of the hit triangle.  Returns below min_intensity become
+ * misses (t = +inf, tri = -1, intensity 0).  Same fp32 operation order as trace.cuh: k_intensity. */
+LSO_API void lso_intensity(const float *verts, const uint32_t *tris, const float *dirs, int64_t nR, int model,
+                           float min_intensity, float *t, int32_t *tri, float *intensity_out)
+{
+    for (int64_t r = 0; r < nR; ++r) {
+        float I = 0.0f;
+        if (tri[r] >= 0) {
+            I = 64.0f;
+            if (model == 1) {
+                lso_tri T;
+                const uint32_t *tv = tris + 3 * (size_t)tri[r];
+                tri_setup(verts + 3 * (size_t)tv[0], verts + 3 * (size_t)tv[1], verts + 3 * (size_t)tv[2], &T);
+                float Ng[3];
+                cross3(T.e2, T.e1, Ng);
+                const float *d = dirs + 3 * r;
+                const float den = dot3(Ng, d), nn = dot3(Ng, Ng), dd = dot3(d, d);
+                const float len = sqrtf(nn * dd);
+                I = len > 0.0f ? (255.0f * fabsf(den)) / len : 0.0f;
+            }
+            if (I < min_intensity) { t[r] = INFINITY; tri[r] = -1; I = 0.0f; }
+        }
+        intensity_out[r] = I;
+    }
+}
+
 /* Single-triangle entry for unit tests. */
 LSO_API int lso_intersect_one(const float a[3], const float b[3], const float c[3], const float org[3],
                               const float dir[3], float *t_out)
 {
     lso_tri tri; tri_setup(a, b, c, &tri);
-    return lso_intersect(&tri, org, dir, t_out);
+    return lso_intersect_any(&tri, org, dir, t_out);
 }
 
 /* Brute force O(R*T) closest hit; misses -> t = +inf, tri = -1.  dirs: nR x 3.  orgs: per-ray origins
@@ -274,7 +354,7 @@ LSO_API void lso_trace_brute(const float *verts, const uint32_t *tris, int64_t n
         float best = INFINITY; int32_t bi = -1;
         for (int64_t i = 0; i < nT; ++i) {
             float t;
-            if (lso_intersect(&T[i], o, d, &t) && t < best) { best = t; bi = (int32_t)i; }
+            if (lso_intersect_any(&T[i], o, d, &t) && t < best) { best = t; bi = (int32_t)i; }
             /* ascending i with strict '<' == lexicographic min of (t, i) */
         }
         t_out[r] = best; tri_out[r] = bi;
@@ -493,7 +573,7 @@ static void trace_one(const lso_bvh *bvh, const float *o, const float *d, float 
                 if (n->count) {
                     for (int32_t i = n->left; i < n->left + n->count; ++i) {
                         float t;
-                        if (lso_intersect(&bvh->tris[i], o, d, &t)) {
+                        if (lso_intersect_any(&bvh->tris[i], o, d, &t)) {
                             int32_t g = bvh->tri_ids[i];
                             if (t < best || (t == best && g < bi)) { best = t; bi = g; }
                         }

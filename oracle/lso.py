@@ -60,6 +60,9 @@ def lib():
         L.lso_trace_bvh_f64.argtypes = [C.c_void_p, f32p, u32p, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
         L.lso_trace_brute_f64.argtypes = [f32p, u32p, C.c_int64, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
         L.lso_bary_f64.argtypes = [f32p, u32p, f32p, C.c_int, f32p, i32p, C.c_int64, f64p]
+        L.lso_set_watertight.argtypes = [C.c_int]
+        L.lso_get_watertight.restype = C.c_int
+        L.lso_intensity.argtypes = [f32p, u32p, f32p, C.c_int64, C.c_int, C.c_float, f32p, i32p, f32p]
         L.lso_set_threads.argtypes = [C.c_int]
         L.lso_max_threads.restype = C.c_int
         L.lso_pack_points.argtypes = [f32p, f32p, i32p, C.c_int64, C.c_int, C.c_int, u8p]
@@ -242,13 +245,43 @@ class Bvh:
             pass
 
 
-def pack_points(dirs_s, t, tri, H, ring_mode=0):
+def pack_points(dirs_s, t, tri, H, ring_mode=0, intensity=None):
     dirs_s, t = _f32(dirs_s).reshape(-1, 3), _f32(t)
     tri = np.ascontiguousarray(tri, dtype=np.int32)
     out = np.zeros(32 * t.size, np.uint8)
     n = lib().lso_pack_points(_p(dirs_s, C.c_float), _p(t, C.c_float), _p(tri, C.c_int32), t.size, int(H),
                               int(ring_mode), _p(out, C.c_uint8))
-    return out[:32 * n].reshape(n, 32)
+    pts = out[:32 * n].reshape(n, 32)
+    if intensity is not None:                 # per-ray intensities of an intensity model (default: the reference's 64.0)
+        pts.view(np.float32).reshape(n, 8)[:, 4] = _f32(intensity)[tri >= 0]
+    return pts
+
+
+class watertight:
+    """Context manager: the oracle's tracers use the watertight Woop-Benthin-Wald test inside (include/lsb200.h:
+    LSB200_OPT_WATERTIGHT) instead of the reference's Embree-ordered Moeller-Trumbore."""
+
+    def __init__(self, on=True):
+        self.on = on
+
+    def __enter__(self):
+        self.prev = lib().lso_get_watertight()
+        lib().lso_set_watertight(1 if self.on else 0)
+        return self
+
+    def __exit__(self, *a):
+        lib().lso_set_watertight(self.prev)
+
+
+def intensity(verts, tris, dirs, t, tri, model=1, min_intensity=0.0):
+    """Intensity model / filter of include/lsb200.h.  Returns (t, tri, intensity) -- new arrays."""
+    verts, dirs = _f32(verts).reshape(-1, 3), _f32(dirs).reshape(-1, 3)
+    tris = np.ascontiguousarray(tris, dtype=np.uint32).reshape(-1, 3)
+    t2, tri2 = _f32(t).copy(), np.ascontiguousarray(tri, dtype=np.int32).copy()
+    out = np.zeros(t2.size, np.float32)
+    lib().lso_intensity(_p(verts, C.c_float), _p(tris, C.c_uint32), _p(dirs, C.c_float), t2.size, int(model),
+                        float(min_intensity), _p(t2, C.c_float), _p(tri2, C.c_int32), _p(out, C.c_float))
+    return t2, tri2, out
 
 
 def set_threads(n):

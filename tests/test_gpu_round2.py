@@ -1,0 +1,349 @@
+"""GPU tests of the round-2 boundary additions, all through the C ABI (include/lsb200.h) and checked against oracle/:
+log sink, several contexts / devices in one process, lsb200_clone_scene + lsb200_run_batch, range-image output and
+its host expander, pinned host memory from the library, watertight mode (Woop 2013) with a leak count, intensity
+model + minimum-intensity filter, empty-scene device results."""
+import numpy as np
+import pytest
+
+from lidarshooter_b200 import capi, synth
+from oracle import lso
+from conftest import xt32_sensor_args
+
+pytestmark = pytest.mark.gpu
+IDENT = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], np.float32)
+
+
+def n_gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+def xt32_ctx(meshes, uid="0000", device=0, opts=None):
+    ctx = capi.Context(device)
+    for k, v in (opts or {}).items():
+        ctx.set_option(k, v)
+    ctx.set_sensor(*xt32_sensor_args(uid))
+    for name in ("ground", "ben"):
+        v, t = meshes[name + "_v"], meshes[name + "_t"]
+        assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0]) >= 0
+        assert ctx.update_geometry(name, v, t, IDENT) == 0
+    return ctx
+
+
+def xt32_meshes(meshes):
+    return [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)]
+
+
+# ---- several contexts / devices in one process (VERDICT weak #6, ADVICE medium) -------------------------------------
+def test_contexts_on_every_device_of_the_process():
+    """One process, one context per visible GPU (twice device 0 when there is only one), each with a scene large
+    enough to need the > 48 KB dynamic-shared-memory kernels (onesweep sort; a 16 000-triangle fused small build):
+    the per-device function attributes must have been set for EVERY device, and the results must agree."""
+    devices = list(range(n_gpus())) if n_gpus() > 1 else [0, 0]
+    rng = np.random.default_rng(3)
+    big_v, big_t = synth.heightfield(nx=200, ny=150)            # 60 000 triangles: multi-kernel pipeline, onesweep
+    small_v = rng.uniform(-20, 20, (48_000, 3)).astype(np.float32)
+    small_t = np.arange(48_000, dtype=np.uint32).reshape(-1, 3)  # 16 000 triangles: k_build_small with 64 000 B of smem
+    elev, b, e, H = synth.lidar_table(32, 361)
+    results = []
+    ctxs = []
+    for dev in devices:
+        per_dev = []
+        for v, t in ((big_v, big_t), (small_v, small_t)):
+            ctx = capi.Context(dev)
+            ctxs.append(ctx)
+            ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), (0.0, 0.0, 3.0))
+            assert ctx.add_geometry("m", capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0]) >= 0
+            assert ctx.update_geometry("m", v, t, IDENT) == 0
+            assert ctx.commit_scene() == 0, ctx.last_error()
+            rc, tt, tri = ctx.trace_raw()
+            assert rc == 0, ctx.last_error()
+            assert (tri >= 0).sum() > 100
+            per_dev.append((tt, tri))
+        results.append(per_dev)
+    for per_dev in results[1:]:
+        for (t0, i0), (t1, i1) in zip(results[0], per_dev):
+            assert np.array_equal(t0, t1) and np.array_equal(i0, i1)
+    for c in ctxs:
+        c.close()
+
+
+# ---- log sink ------------------------------------------------------------------------------------------------------
+def test_log_callback_receives_errors_and_lifecycle(meshes):
+    ctx = xt32_ctx(meshes)
+    lines = []
+    assert ctx.set_log_callback(lambda level, msg: lines.append((level, msg))) == 0
+    assert ctx.commit_scene() == 0
+    assert any(lv == capi.LOG_DEBUG and "commit" in m and "5651" in m for lv, m in lines), lines
+    assert ctx.remove_geometry("no-such-mesh") == -1
+    assert lines[-1][0] == capi.LOG_ERROR and lines[-1][1] == ctx.last_error() and "no-such-mesh" in lines[-1][1]
+    n = len(lines)
+    ctx.set_log_callback(None)
+    assert ctx.remove_geometry("no-such-mesh") == -1
+    assert len(lines) == n
+    ctx.close()
+
+
+# ---- range image ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("flags", [0, capi.TRACE_XYZI16, capi.TRACE_RING_ZERO, capi.TRACE_WORLD_POINTS | capi.TRACE_XYZI16])
+def test_range_image_and_host_expander(meshes, flags):
+    """LSB200_TRACE_RANGE_IMAGE delivers the per-ray t array (4 B / ray); lsb200_expand_range_image rebuilds, on the
+    host, exactly the bytes an LSB200_TRACE_ORDERED trace writes on the device."""
+    ctx = xt32_ctx(meshes)
+    assert ctx.commit_scene() == 0
+    rc, t_raw, tri = ctx.trace_raw()
+    rc, img = ctx.trace_scene(7, capi.TRACE_RANGE_IMAGE)
+    assert rc == 0 and img.shape == (4800, 4)
+    t_img = img.reshape(-1).view(np.float32)
+    assert np.array_equal(t_img.view(np.uint32), t_raw.view(np.uint32))
+    ref = lso.scan(lso.Sensor(*xt32_sensor_args("0000")), xt32_meshes(meshes))
+    assert np.array_equal(t_img, ref["t"])
+    rc, dev_pts = ctx.trace_scene(7, capi.TRACE_ORDERED | flags)
+    rc2, host_pts = ctx.expand_range_image(t_img, flags)
+    assert rc == 0 and rc2 == 0 and dev_pts.shape[0] == 1781
+    assert np.array_equal(dev_pts, host_pts)
+    ctx.close()
+
+
+def test_run_frames_range_image_matches_per_frame_calls(meshes):
+    """The pipelined batch entry with range-image output (two device slots, copies overlapping the next frame)."""
+    import torch
+    poses = synth.trajectory_poses([(0.5, (0, 5, 0), (0, 0, 1))])
+    ctx = xt32_ctx(meshes)
+    R = ctx.ray_count()
+    A = np.stack([np.stack([IDENT, capi.affine_from_components(tr, eu)]) for tr, eu in poses])
+    outs = [torch.empty(R, dtype=torch.float32).pin_memory() for _ in poses]
+    rc, cnt = ctx.run_frames(A, [[o.data_ptr()] for o in outs], [R], first=0, count=1, commit_mode=capi.COMMIT_AUTO,
+                             flags=capi.TRACE_RANGE_IMAGE)
+    assert rc == 0, ctx.last_error()
+    assert (cnt == R).all()
+    s = lso.Sensor(*xt32_sensor_args("0000"))
+    for f, (tr, eu) in enumerate(poses):
+        ref = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], IDENT),
+                           (meshes["ben_v"], meshes["ben_t"], lso.affine_from_components(tr, eu))])
+        assert np.array_equal(outs[f].numpy(), ref["t"]), f
+    ctx.close()
+
+
+def test_alloc_host_is_usable_as_output(meshes):
+    ctx = xt32_ctx(meshes)
+    assert ctx.commit_scene() == 0
+    buf = ctx.alloc_host(4800 * 32)
+    assert ctx.numa_node() >= -1
+    rc, pts = ctx.trace_scene(0, capi.TRACE_ORDERED, out=buf.reshape(4800, 32))
+    assert rc == 0 and pts.shape[0] == 1781
+    ref = lso.scan(lso.Sensor(*xt32_sensor_args("0000")), xt32_meshes(meshes))
+    assert np.array_equal(pts, ref["points"])
+    ctx.free_host(buf)
+    ctx.close()
+
+
+# ---- clone + multi-GPU batch ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("sharding", [capi.SHARD_FRAMES, capi.SHARD_SENSORS])
+def test_clone_scene_and_run_batch(sharding):
+    """lsb200_clone_scene replicates the scene on another GPU (device 1 when present, else a second context on device
+    0); lsb200_run_batch over both contexts returns, frame by frame and sensor by sensor, the clouds a single context's
+    lsb200_run_frames returns."""
+    import torch
+    meshes = synth.city(n_boxes=120, ground_cells=80, extent=12 * synth.CITY_PITCH, n_groups=3, lots=12)
+    poses = synth.sensor_lattice(2, 4 * synth.CITY_PITCH)
+    elev, b, e, H = synth.lidar_table(16, 181)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    for k, (q, t) in enumerate(poses):
+        ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    ctx.set_sensor_limits(150.0, -170.0, 170.0, index=1)
+    for name, v, tr in meshes:
+        assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], tr.shape[0]) >= 0
+        assert ctx.update_geometry(name, v, tr, IDENT) == 0
+    other = ctx.clone(1 if n_gpus() > 1 else 0)
+    assert other.geometry_count() == ctx.geometry_count() and other.ray_count(3) == ctx.ray_count(3)
+    F, S, R = 5, len(poses), elev.size * H
+    A = np.zeros((F, len(meshes), 12), np.float32)
+    for f in range(F):
+        for gi in range(len(meshes)):
+            A[f, gi] = IDENT
+            if gi:
+                A[f, gi, 3] = 0.3 * f + 0.1 * gi
+    flags = capi.TRACE_ORDERED | capi.TRACE_XYZI16
+
+    def buffers():
+        bufs = [[torch.zeros((R, 16), dtype=torch.uint8).pin_memory() for _ in range(S)] for _ in range(F)]
+        return bufs, [[t.data_ptr() for t in row] for row in bufs]
+
+    b1, p1 = buffers()
+    rc, c1 = ctx.run_frames(A, p1, [R] * S, first=0, count=S, commit_mode=capi.COMMIT_REBUILD, flags=flags)
+    assert rc == 0, ctx.last_error()
+    b2, p2 = buffers()
+    rc, c2 = capi.run_batch([ctx, other], A, p2, [R] * S, first=0, count=S, commit_mode=capi.COMMIT_REBUILD, flags=flags,
+                            sharding=sharding)
+    assert rc == 0, (ctx.last_error(), other.last_error())
+    assert np.array_equal(c1, c2) and c1.sum() > 1000
+    for f in range(F):
+        for k in range(S):
+            n = int(c1[f, k])
+            assert np.array_equal(b1[f][k].numpy()[:n], b2[f][k].numpy()[:n]), (f, k)
+    other.close()
+    ctx.close()
+
+
+# ---- watertight mode (VERDICT missing #1 / N1) ---------------------------------------------------------------------
+@pytest.mark.parametrize("uid", ["0000", "0001"])
+def test_watertight_mode_xt32_vs_oracle(meshes, uid):
+    """LSB200_OPT_WATERTIGHT: GPU == oracle in the same mode, bit for bit (mask, id, t), for the traversal and for brute
+    force; against the default Moeller-Trumbore mode the hit set of the reference scene is the same and ranges agree to
+    1e-5 (both are correct intersectors; they differ only on grazing rays)."""
+    s = lso.Sensor(*xt32_sensor_args(uid))
+    ref_mt = lso.scan(s, xt32_meshes(meshes))
+    with lso.watertight():
+        ref_wt = lso.scan(s, xt32_meshes(meshes))
+    for mode in (6, 3):
+        ctx = xt32_ctx(meshes, uid, opts={capi.OPT_WATERTIGHT: 1, capi.OPT_TRAVERSAL: mode})
+        assert ctx.commit_scene() == 0
+        rc, t, tri = ctx.trace_raw()
+        assert rc == 0, ctx.last_error()
+        assert np.array_equal(tri, ref_wt["tri"]) and np.array_equal(t, ref_wt["t"])
+        rc, pts = ctx.trace_scene(0, capi.TRACE_ORDERED)
+        assert np.array_equal(pts, ref_wt["points"])
+        # back to the default intersector on the same context: records are rewritten by the next commit
+        ctx.set_option(capi.OPT_WATERTIGHT, 0)
+        assert ctx.commit_scene() == 0
+        rc, t0, tri0 = ctx.trace_raw()
+        assert np.array_equal(tri0, ref_mt["tri"]) and np.array_equal(t0, ref_mt["t"])
+        ctx.close()
+    assert np.array_equal(ref_wt["tri"] >= 0, ref_mt["tri"] >= 0)
+    hit = ref_mt["tri"] >= 0
+    assert np.abs(ref_wt["t"][hit] - ref_mt["t"][hit]).max() / ref_mt["t"][hit].max() < 1e-5
+
+
+def ray_aligned_shell(sensor, radius=20.0):
+    """A mesh whose every vertex lies (to fp32 rounding) ON one ray of the sensor: vertex (v, h) = radius * d(v, h),
+    the (v, h) grid triangulated.  Every ray then grazes six triangles at their common vertex -- the worst case for
+    a non-watertight intersector."""
+    d = lso.ray_dirs(sensor.tables).reshape(sensor.V, sensor.H, 3)
+    r = (radius * (1.0 + 0.2 * np.sin(np.arange(sensor.V))[:, None] * np.cos(0.3 * np.arange(sensor.H))[None, :])).astype(np.float32)
+    verts = (r[:, :, None] * d).astype(np.float32).reshape(-1, 3)
+    Hh = sensor.H - 1                                       # the last azimuth step repeats the first direction
+    v, h = np.meshgrid(np.arange(sensor.V - 1), np.arange(Hh - 1), indexing="ij")
+    v00 = (v * sensor.H + h).astype(np.uint32)
+    tris = np.concatenate([np.stack([v00, v00 + 1, v00 + sensor.H + 1], -1).reshape(-1, 3),
+                           np.stack([v00, v00 + sensor.H + 1, v00 + sensor.H], -1).reshape(-1, 3)]).astype(np.uint32)
+    interior = np.zeros((sensor.V, sensor.H), bool)
+    interior[1:-1, 1:Hh - 1] = True
+    return verts, tris, interior.reshape(-1)
+
+
+def test_watertight_mode_closes_the_leaks_of_moeller_trumbore():
+    """The leak count north_star asks to be reported: rays that MISS in the reference's Moeller-Trumbore mode although
+    they pass through the interior of a closed patch of triangles, and HIT in watertight mode.  Scene: the ray-aligned
+    shell (every interior ray pierces a vertex shared by six triangles) around an XT-32 and around the 128 x 3601 device.
+    GPU == oracle bit-exactly in both modes; watertight mode has zero leaks."""
+    for table, tf in ((xt32_sensor_args("0000")[:4], ((1, 0, 0, 0), (0, 0, 0))), (synth.lidar_table(), ((1, 0, 0, 0), (0, 0, 0)))):
+        s = lso.Sensor(*table, *tf)
+        verts, tris, interior = ray_aligned_shell(s)
+        leaks = {}
+        for wt in (0, 1):
+            ctx = capi.Context(0)
+            ctx.set_option(capi.OPT_WATERTIGHT, wt)
+            ctx.set_sensor(*table, *tf)
+            assert ctx.add_geometry("shell", capi.GEOMETRY_TRIANGLE, verts.shape[0], tris.shape[0]) >= 0
+            assert ctx.update_geometry("shell", verts, tris, IDENT) == 0
+            assert ctx.commit_scene() == 0
+            rc, t, tri = ctx.trace_raw()
+            assert rc == 0
+            with lso.watertight(bool(wt)):
+                ref = lso.scan(s, [(verts, tris, IDENT)], use_bvh=True)
+            assert np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
+            leaks[wt] = int(((tri < 0) & interior).sum())
+            ctx.close()
+        print(f"leak count, {s.V} x {s.H} rays through shared vertices: Moeller-Trumbore {leaks[0]}, watertight {leaks[1]}")
+        assert leaks[1] == 0
+        assert leaks[0] > 0            # the reference's intersector does leak on this scene
+
+
+def test_watertight_heightfield_leak_count():
+    """Config 3 (1 M-triangle heightfield, 460 928 rays): rays that miss in Moeller-Trumbore mode but hit in watertight
+    mode = leaks of the reference's intersector on a benchmark scene (reported; few or none -- the LiDAR's directions
+    are not aimed at edges), and the two modes otherwise agree: same triangle wherever both hit away from an edge."""
+    v, tr = synth.heightfield()
+    elev, b, e, H = synth.lidar_table()
+    res = {}
+    for wt in (0, 1):
+        ctx = capi.Context(0, capi.FRAME_WORLD)
+        ctx.set_option(capi.OPT_WATERTIGHT, wt)
+        ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), (0.0, 0.0, 2.0))
+        assert ctx.add_geometry("terrain", capi.GEOMETRY_TRIANGLE, v.shape[0], tr.shape[0]) >= 0
+        assert ctx.update_geometry("terrain", v, tr, IDENT) == 0
+        assert ctx.commit_scene() == 0
+        rc, t, tri = ctx.trace_raw()
+        assert rc == 0
+        res[wt] = (t, tri)
+        ctx.close()
+    s = lso.Sensor(elev, b, e, H, (1, 0, 0, 0), (0.0, 0.0, 2.0))
+    verts, tris = lso.concat_scene(s, [(v, tr, IDENT)], mode=1)
+    dirs = lso.rotate_dirs(s.R, lso.ray_dirs(s.tables))
+    bvh = lso.Bvh(verts, tris)
+    with lso.watertight():
+        t_ref, tri_ref = bvh.trace(s.T, dirs)
+    bvh.close()
+    assert np.array_equal(res[1][1], tri_ref) and np.array_equal(res[1][0], t_ref)
+    leaks = int(((res[0][1] < 0) & (res[1][1] >= 0)).sum())
+    extra = int(((res[0][1] >= 0) & (res[1][1] < 0)).sum())
+    differ = int((res[0][1] != res[1][1]).sum())
+    print(f"heightfield: {leaks} rays leak through Moeller-Trumbore, {extra} hit only there, {differ} differ in triangle id")
+    assert leaks < 100 and extra < 100 and differ < 2000
+
+
+# ---- intensity model + filter --------------------------------------------------------------------
+def test_intensity_model_and_minimum_intensity_filter(meshes):
+    s = lso.Sensor(*xt32_sensor_args("0000"))
+    base = lso.scan(s, xt32_meshes(meshes))
+    dirs = lso.ray_dirs(s.tables)
+    # model 1 (cos incidence), no filter
+    ctx = xt32_ctx(meshes, opts={capi.OPT_INTENSITY_MODEL: 1})
+    assert ctx.commit_scene() == 0
+    rc, pts = ctx.trace_scene(0, 0)                       # unordered requested: an intensity model implies the ordered path
+    assert rc == 0 and pts.shape[0] == 1781
+    t1, tri1, I1 = lso.intensity(base["verts"], base["tris"], dirs, base["t"], base["tri"], model=1)
+    rc, I = ctx.fetch_intensity()
+    assert rc == 0 and np.array_equal(I, I1)
+    assert 0.0 < I1[base["tri"] >= 0].min() and I1.max() <= 255.0 and np.unique(I1).size > 100
+    ref_pts = lso.pack_points(dirs, t1, tri1, s.H, intensity=I1)
+    assert np.array_equal(pts, ref_pts)
+    # the device config's filter (use_intensity_filtering / minimum_intensity), threshold chosen to bite
+    thr = float(np.median(I1[base["tri"] >= 0]))
+    assert ctx.set_sensor_intensity_filter(thr) == 0
+    rc, pts = ctx.trace_scene(1, capi.TRACE_ORDERED)
+    t2, tri2, I2 = lso.intensity(base["verts"], base["tris"], dirs, base["t"], base["tri"], model=1, min_intensity=thr)
+    assert 0 < (tri2 >= 0).sum() < 1781
+    assert pts.shape[0] == int((tri2 >= 0).sum())
+    assert np.array_equal(pts, lso.pack_points(dirs, t2, tri2, s.H, intensity=I2))
+    rc, t, tri = ctx.trace_raw()
+    assert np.array_equal(tri, tri2) and np.array_equal(t, t2)
+    ctx.close()
+    # the reference's constant model with its config's threshold (5 < 64): nothing is dropped, bytes unchanged
+    ctx = xt32_ctx(meshes)
+    assert ctx.set_sensor_intensity_filter(5.0) == 0
+    assert ctx.commit_scene() == 0
+    rc, pts = ctx.trace_scene(0, capi.TRACE_ORDERED)
+    assert np.array_equal(pts, base["points"])
+    ctx.close()
+
+
+def test_empty_scene_device_results_are_misses():
+    """ADVICE: after an empty-scene trace the DEVICE result arrays say 'miss' (t = +inf, triangle -1), like the host copy."""
+    import ctypes as C
+    import torch
+    ctx = capi.Context(0)
+    ctx.set_sensor(*xt32_sensor_args("0000"))
+    assert ctx.trace_device(0, 0) == -1
+    L = capi.lib()
+    dp, dc, dt, dtri = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+    assert L.lsb200_device_results(ctx._h, 0, C.byref(dp), C.byref(dc), C.byref(dt), C.byref(dtri)) == 0
+    ctx.synchronize()
+    t = np.empty(4800, np.float32)
+    tri = np.empty(4800, np.int32)
+    rt = C.CDLL("libcudart.so")
+    assert rt.cudaMemcpy(C.c_void_p(t.ctypes.data), dt, C.c_size_t(4800 * 4), 2) == 0
+    assert rt.cudaMemcpy(C.c_void_p(tri.ctypes.data), dtri, C.c_size_t(4800 * 4), 2) == 0
+    assert np.isinf(t).all() and (tri == -1).all()
+    ctx.close()
