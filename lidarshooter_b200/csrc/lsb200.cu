@@ -667,6 +667,8 @@ static int commit_locked(lsb200_ctx *c, int mode)
         c->committed = true;
         ++c->commit_epoch;
         if (args.n_origins > 0) { c->chain_commit_epoch = c->commit_epoch; c->chain_sensors_epoch = c->sensors_epoch; }
+        logf(c, LSB200_LOG_DEBUG, "lsb200: commit (%s, fused small build) of %lld triangles / %lld vertices in %zu geometries",
+             rebuild ? "rebuild" : "refit", (long long)nt, (long long)nv, ng);
         return LSB200_OK;
     }
 
