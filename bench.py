@@ -483,6 +483,45 @@ def main():
     stages["tile_lists"] = round(float(st.ms_tile_lists), 4)
     stages["k_trace"] = round(float(st.ms_trace) - float(st.ms_tile_lists), 4)
 
+    # ---- optional gather of the per-GPU clouds over NVLink (N > 1): shard.gather_clouds on NCCL with the real clouds ----
+    gather = None
+    if world > 1:
+        import ctypes as C
+        from lidarshooter_b200 import shard
+        rc = ctx.trace_batch(0, n_sens, capi.TRACE_XYZI16)
+        assert rc == 0, ctx.last_error()
+        rc, counts = ctx.fetch_batch(0, n_sens, [0] * n_sens, [0] * n_sens, capi.TRACE_XYZI16)
+        parts = []
+        for k in range(n_sens):
+            dp = C.c_void_p()
+            capi.lib().lsb200_device_results(ctx._h, k, C.byref(dp), None, None, None)
+            parts.append(torch.as_tensor(shard.DeviceArray(dp.value, int(counts[k]) * 16), device="cuda").view(-1, 16))
+        stream.synchronize()
+        cloud = torch.cat(parts)                           # this rank's merged cloud (device memory)
+        for _ in range(2):
+            shard.gather_clouds(cloud, dst=0)
+        sync_all()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        greps = 5
+        g0.record()
+        for _ in range(greps):
+            merged = shard.gather_clouds(cloud, dst=0)
+        g1.record()
+        torch.cuda.synchronize()
+        gms = g0.elapsed_time(g1) / greps
+        tt = torch.tensor([gms, float(cloud.shape[0])], device="cuda", dtype=torch.float64)
+        mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        total_pts = int(sm[1].item())
+        inbound = (total_pts - int(cloud.shape[0])) * 16 if rank == 0 else 0
+        if rank == 0:
+            assert merged.shape[0] == total_pts
+            gather = {"what": "shard.gather_clouds: every rank's merged 16-byte XYZI cloud of one frame to rank 0 "
+                              "(all_gather of counts + batched variable-length isend/irecv, NCCL over NVLink / NVSwitch)",
+                      "ms": float(mx[0].item()), "points_total": total_pts, "bytes_into_rank0": int(inbound),
+                      "gbs_into_rank0": inbound / (float(mx[0].item()) * 1e-3) / 1e9, "timed": "CUDA events, max over ranks, 5 reps"}
+        del merged, cloud, parts
+
     # ---- parity of the benchmarked configuration: per-ray results of one frame, compared with the oracle below ----
     parity_frame = 3
     parity_sensors = (0,) if args.small else (0, 27, 63)
@@ -501,12 +540,20 @@ def main():
     # the point clouds into the caller's pinned host buffers; the D2H of frame f overlaps frame f+1's compute.
     # Headline record = the 16-byte XYZI point north_star names; the 32-byte PointCloud2 record (the XT-32
     # message layout, SRC/XYZIRBytes.cpp:24-40) is measured the same way and reported beside it.
+    # All pinned host memory of this leg comes from the library (lsb200_alloc_host): allocated and first-touched while
+    # the thread is bound to the CPUs of the NUMA node this rank's GPU hangs off, so that with 8 ranks the D2H streams
+    # spread over the sockets' memory controllers (tools/d2h_probe.cu measures plain vs placed buffers).
     n_sets = 2
-    out_bufs = [[torch.empty((R, 32), dtype=torch.uint8).pin_memory() for _ in range(n_sens)] for _ in range(n_sets)]
-    out_ptrs = [[t.data_ptr() for t in row] for row in out_bufs]
+    out_sets = [ctx.alloc_host(n_sens * R * 32) for _ in range(n_sets)]
+    out_ptrs = [[int(buf.ctypes.data) + k * R * 32 for k in range(n_sens)] for buf in out_sets]
     caps = [R] * n_sens
+    pinned_v = []
+    for v in host_v:
+        pv = ctx.alloc_host(v.numel() * 4)
+        pv[:] = v.numpy().view(np.uint8).reshape(-1)
+        pinned_v.append(pv)
     h2d = sum(v.numel() * 4 for v in host_v) + 48 * len(names)
-    vert_ptrs = [v.data_ptr() for v in host_v]
+    vert_ptrs = [int(pv.ctypes.data) for pv in pinned_v]
 
     def run_e2e(first_frame, n_frames, flags):
         A = np.stack([np.stack([frame_affine((first_frame + f) * world + rank, gi) for gi in range(len(names))])
@@ -517,26 +564,50 @@ def main():
         assert rc_ == 0, ctx.last_error()
         return cnt
 
+    def reduce_max_ms(ms):
+        if world > 1:
+            tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item())
+        return ms
+
     e2e = {}
-    for label, flags, rec in (("xyzi16", capi.TRACE_XYZI16, 16), ("pointcloud2_32", 0, 32)):
+    legs = (("xyzi16", capi.TRACE_XYZI16, 16), ("pointcloud2_32", 0, 32), ("range_image", capi.TRACE_RANGE_IMAGE, 4))
+    for label, flags, rec in legs:
         run_e2e(frame, 2, flags); frame += 2                       # warm-up (allocates the second output slot)
         sync_all()
         t0 = time.perf_counter()
         cnt = run_e2e(frame, args.steps, flags); frame += args.steps
         sync_all()
-        ms = (time.perf_counter() - t0) * 1e3                      # blocking call: wall clock covers every copy
-        if world > 1:
-            tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            ms = float(tt.item())
+        ms = reduce_max_ms((time.perf_counter() - t0) * 1e3)       # blocking call: wall clock covers every copy
         pts_per_step = int(cnt.sum()) // args.steps
         # the clouds really arrived: last frame's first record of sensor 0 is a finite point with intensity 64
-        last = out_bufs[(args.steps - 1) % n_sets][0].numpy().reshape(-1)[:rec].view(np.float32)
-        assert np.isfinite(last[:3]).all() and last[3 if rec == 16 else 4] == 64.0
+        last = out_sets[(args.steps - 1) % n_sets][:32].view(np.float32)
+        if rec == 4:
+            assert np.isfinite(out_sets[(args.steps - 1) % n_sets][:R * 4].view(np.float32)).any()
+        else:
+            assert np.isfinite(last[:3]).all() and last[3 if rec == 16 else 4] == 64.0
+        d2h = int(pts_per_step * rec + (4 * n_sens if rec != 4 else 0))
+        # host ceiling: the SAME copies (64 clouds of the last frame, device -> the same pinned buffers) with nothing else
+        # running, all ranks at once -- what this box's PCIe / host memory path gives this copy pattern
+        ctx.trace_batch(0, n_sens, flags)
+        sync_all()
+        t0 = time.perf_counter()
+        ceil_reps = 5
+        for _ in range(ceil_reps):
+            rc_, _cnt = ctx.fetch_batch(0, n_sens, out_ptrs[0], caps, flags)
+            assert rc_ == 0, ctx.last_error()
+        ms_copy = reduce_max_ms((time.perf_counter() - t0) * 1e3) / ceil_reps
         e2e[label] = {"value": world * rays_per_step_rank * args.steps / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
-                      "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(pts_per_step * rec + 4 * n_sens),
+                      "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": d2h,
                       "ms_per_step": ms / args.steps, "record_bytes": rec,
+                      "d2h_gbs_per_gpu": d2h / (ms / args.steps * 1e-3) / 1e9,
+                      "host_ceiling_gbs_per_gpu": d2h / (ms_copy * 1e-3) / 1e9,
+                      "host_ceiling_ms_per_step": ms_copy,
+                      "pinned_memory": f"lsb200_alloc_host (GPU NUMA node {ctx.numa_node()})",
                       "api": "lsb200_run_frames (pipelined: D2H of frame f overlaps frame f+1)"}
+    for buf in out_sets + pinned_v:
+        ctx.free_host(buf)
     rec = 32
 
     # ---- roofline ---------------------------------------------------------------------------------------------
@@ -619,8 +690,9 @@ def main():
             "trace_only_mrays_per_s": world * rays_per_step_rank / (ms_trace * 1e-3) / 1e6,
             "ms_commit": ms_commit, "ms_trace": ms_trace, "stages_ms": stages,
             "clocks": clocks,
-            "e2e": e2e["xyzi16"], "e2e_pointcloud2_32": e2e["pointcloud2_32"],
+            "e2e": e2e["xyzi16"], "e2e_pointcloud2_32": e2e["pointcloud2_32"], "e2e_range_image": e2e["range_image"],
             "gpu_launches": launches,
+            "gather": gather,
             "roofline": roofline,
         }
     ctx.close()

@@ -33,8 +33,12 @@ def reduce_max(values, device=None):
 
 def gather_clouds(points, dst=0):
     """Optional gather of variable-length point clouds: `points` is this rank's (n, record_bytes) uint8 tensor (on the
-    GPU under NCCL).  One all_gather of the counts, then one all_gather of the clouds padded to the largest count.
-    Returns the concatenation in rank order on rank `dst`, None elsewhere."""
+    GPU under NCCL -- the transfers then run over NVLink / NVSwitch peer to peer; on the CPU under gloo).
+    One all_gather of the counts (8 bytes per rank), then every rank sends exactly its own count * record_bytes to
+    `dst` (batched isend / irecv: one NCCL group, no padding to the largest cloud).
+    Returns the concatenation in rank order on rank `dst`, None elsewhere.
+    Counterpart in the reference: each device's cloud is published on its own ROS topic (SRC/MeshProjector.cpp:380-390)
+    and merged by whoever subscribes; there is no collective."""
     world = dist.get_world_size()
     rank = dist.get_rank()
     n = torch.tensor([points.shape[0]], dtype=torch.int64, device=points.device)
@@ -42,11 +46,27 @@ def gather_clouds(points, dst=0):
     dist.all_gather(counts, n)
     counts = [int(c.item()) for c in counts]
     width = points.shape[1]
-    pad = max(max(counts), 1)
-    buf = torch.zeros((pad, width), dtype=torch.uint8, device=points.device)
-    buf[: points.shape[0]] = points
-    parts = [torch.empty_like(buf) for _ in range(world)]
-    dist.all_gather(parts, buf)
-    if rank != dst:
-        return None
-    return torch.cat([p[:c] for p, c in zip(parts, counts)], dim=0)
+    points = points.contiguous()
+    if rank == dst:
+        out = torch.empty((sum(counts), width), dtype=torch.uint8, device=points.device)
+        offs = [0]
+        for c in counts:
+            offs.append(offs[-1] + c)
+        out[offs[rank]:offs[rank + 1]] = points
+        ops = [dist.P2POp(dist.irecv, out[offs[r]:offs[r + 1]], r) for r in range(world) if r != dst and counts[r] > 0]
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+        return out
+    if points.shape[0] > 0:
+        for req in dist.batch_isend_irecv([dist.P2POp(dist.isend, points, dst)]):
+            req.wait()
+    return None
+
+
+class DeviceArray:
+    """A raw device pointer (lsb200_device_results) dressed as a __cuda_array_interface__ object, so that
+    torch.as_tensor(DeviceArray(...), device='cuda') wraps the library's buffer without a copy."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
