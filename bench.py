@@ -284,6 +284,151 @@ def xt32_scan_leg(local, reps=1000, cpu=True):
     return leg
 
 
+def other_configs_leg(local, rank, world, n_scans=60):
+    """BASELINE configs 2, 3 and 5 as extra keys of the bench line -- the headline stays
+    configs[3].  Each is measured end to end through the public call a user of that configuration makes:
+      c2  two XT-32 devices (lidar_0000 + lidar_0001), `ben` along config/trajectory.json over the static ground, through the
+          drop-in B200Tracer adapter (updateGeometry x 2, commitScene = refit, traceScene into the PointCloud2); scans/s
+      c3  one 128 x 3601 device over the 1 M-triangle heightfield: adapter call sequence (refit per scan) and the C ABI with
+          a full rebuild per scan
+      c5  1 M-triangle heightfield + 16 `ben` on looped trajectories, FULL rebuild every frame, frames sharded over the
+          ranks (frame-major): frames/s of the whole job through lsb200_run_frames with host clouds (16-byte records)
+    c2 / c3 run on rank 0 only (single-device configurations); c5 on every rank."""
+    import torch
+    import torch.distributed as dist
+    from lidarshooter_b200 import capi, hostapi, synth
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import GOLDEN
+    out = {}
+    z = np.load(os.path.join(GOLDEN, "meshes.npz"))
+    ident = np.asarray([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], np.float32)
+    if rank == 0:
+        # ---- c2 ----------------------------------------------------------------------------------------------------
+        poses = hostapi.trajectory_poses(os.path.join(GOLDEN, "trajectory.json"), 0.1)        # 150 ticks
+        ground = hostapi.Mesh(os.path.join(GOLDEN, "ground.stl"))
+        ben = hostapi.Mesh(arrays=(z["ben_v"], z["ben_t"]))
+        tracers = []
+        for uid in ("0000", "0001"):
+            dev = hostapi.LidarDevice(os.path.join(GOLDEN, f"xt32_lidar_{uid}.json"))
+            tr = hostapi.B200Tracer(dev, local)
+            tr.addGeometry("ground", 0, 98, 162); tr.addGeometry("ben", 0, 2823, 5489)
+            tracers.append((dev, tr))
+
+        def c2_pass():
+            pts = 0
+            for k in range(poses.shape[0]):
+                for _, tr in tracers:
+                    tr.updateGeometry("ground", ground, translation=(0, 0, 0), rotation=(0, 0, 0))
+                    tr.updateGeometry("ben", ben, translation=poses[k, :3], rotation=poses[k, 3:])
+                    tr.commitScene()
+                    tr.traceScene(k)
+                    pts += tr.getTraceCloudWidth()
+            return pts
+        c2_pass()
+        t0 = time.perf_counter()
+        pts = c2_pass()
+        dt = time.perf_counter() - t0
+        scans = 2 * poses.shape[0]
+        out["c2"] = {"workload": "configs[1]: lidar_0000 + lidar_0001, 150 trajectory frames, per-frame transforms + BVH refit, "
+                                 "through lidarshooter::B200Tracer (sensor frame, host PointCloud2)",
+                     "scans": scans, "us_per_scan": dt / scans * 1e6, "scans_per_s": scans / dt, "mrays_per_s": scans * 4800 / dt / 1e6,
+                     "points_total": int(pts), "reference_design_rate_scans_per_s": 20.0}
+        for dev, tr in tracers:
+            tr.close(); dev.close()
+        # ---- c3 ----------------------------------------------------------------------------------------------------
+        hv, ht = synth.heightfield()
+        elev, b, e, H = synth.lidar_table()
+        R = elev.size * H
+        dev = hostapi.LidarDevice(synthetic=(elev, b, e, H, (1, 0, 0, 0), (0.0, 0.0, 2.0)))
+        tr = hostapi.B200Tracer(dev, local)
+        terrain = hostapi.Mesh(arrays=(hv, ht))
+        tr.addGeometry("terrain", 0, hv.shape[0], ht.shape[0])
+        n3 = 30
+
+        def c3_adapter(n):
+            for k in range(n):
+                tr.updateGeometry("terrain", terrain, translation=(0.01 * k, 0, 0), rotation=(0, 0, 0))
+                tr.commitScene()
+                tr.traceScene(k)
+        c3_adapter(3)
+        t0 = time.perf_counter()
+        c3_adapter(n3)
+        dt_ad = (time.perf_counter() - t0) / n3
+        hits3 = tr.getTraceCloudWidth()
+        tr.close(); dev.close()
+        stream = torch.cuda.Stream()
+        ctx = capi.Context(local, capi.FRAME_SENSOR, stream=stream.cuda_stream)
+        ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), (0.0, 0.0, 2.0))
+        ctx.add_geometry("terrain", capi.GEOMETRY_TRIANGLE, hv.shape[0], ht.shape[0])
+        ctx.update_geometry("terrain", hv, ht, ident)
+        for mode_name, mode in (("rebuild", capi.COMMIT_REBUILD), ("refit", capi.COMMIT_REFIT)):
+            for k in range(3):
+                ctx.commit_scene(capi.COMMIT_REBUILD if k == 0 else mode); ctx.trace_device(0, 0)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            stream.synchronize()
+            e0.record(stream)
+            for k in range(n3):
+                A = ident.copy(); A[3] = 0.01 * k
+                ctx.update_transform("terrain", A)
+                ctx.commit_scene(mode)
+                ctx.trace_device(0, 0)
+            e1.record(stream)
+            stream.synchronize()
+            out.setdefault("c3", {})[f"resident_{mode_name}_ms_per_scan"] = e0.elapsed_time(e1) / n3
+        ctx.close()
+        out["c3"].update({"workload": "configs[2]: 128 ch x 3601 az (460 928 rays), 1 M-triangle heightfield, sensor frame",
+                          "adapter_ms_per_scan": dt_ad * 1e3, "adapter_mrays_per_s": R / dt_ad / 1e6, "adapter_scans_per_s": 1.0 / dt_ad,
+                          "adapter_call": "B200Tracer::updateGeometry (1 M-triangle mesh from host, pageable) + commitScene (refit) + "
+                                          "traceScene (32-byte records into the std::vector of the PointCloud2)",
+                          "resident_rebuild_mrays_per_s": R / (out["c3"]["resident_rebuild_ms_per_scan"] * 1e-3) / 1e6,
+                          "points": int(hits3)})
+    # ---- c5 (every rank) ------------------------------------------------------------------------------------------------
+    hv, ht = synth.heightfield()
+    bv, bt = z["ben_v"], z["ben_t"]
+    loop = synth.trajectory_poses([(10.0, (0, 5, 0), (0, 0, 1)), (5.0, (1, 0, 0), (0, 0, -1))])
+    n_inst = 16
+    elev, b, e, H = synth.lidar_table()
+    R = elev.size * H
+    ctx = capi.Context(local, capi.FRAME_WORLD)
+    ctx.set_sensor(elev, b, e, H, (1, 0, 0, 0), (0.0, 0.0, 4.0))
+    ctx.add_geometry("terrain", capi.GEOMETRY_TRIANGLE, hv.shape[0], ht.shape[0]); ctx.update_geometry("terrain", hv, ht, ident)
+    base = [np.array([(i % 4 - 1.5) * 12.0, (i // 4 - 1.5) * 12.0, 3.0], np.float32) for i in range(n_inst)]
+    for i in range(n_inst):
+        ctx.add_geometry(f"ben{i:02d}", capi.GEOMETRY_TRIANGLE, bv.shape[0], bt.shape[0]); ctx.update_geometry(f"ben{i:02d}", bv, bt, ident)
+    frames = list(range(rank, n_scans * world, world))               # frame-major sharding of the 4096-frame batch's head
+    A = np.zeros((len(frames), 1 + n_inst, 12), np.float32)
+    for k, f in enumerate(frames):
+        A[k, 0] = ident
+        for i in range(n_inst):
+            lin, ang = loop[(f + 9 * i) % len(loop)]
+            A[k, 1 + i] = capi.affine_from_components(lin * np.float32(0.2) + base[i], ang)
+    bufs = [ctx.alloc_host(R * 16) for _ in range(2)]
+    ptrs = [[int(bufs[k % 2].ctypes.data)] for k in range(len(frames))]
+    ctx.run_frames(A[:2], ptrs[:2], [R], first=0, count=1, commit_mode=capi.COMMIT_REBUILD, flags=capi.TRACE_XYZI16)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    rc, cnt = ctx.run_frames(A, ptrs, [R], first=0, count=1, commit_mode=capi.COMMIT_REBUILD, flags=capi.TRACE_XYZI16)
+    dt = time.perf_counter() - t0
+    assert rc == 0, ctx.last_error()
+    if world > 1:
+        tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+    n_tris5 = int(ctx.stats().n_triangles)
+    for bb in bufs:
+        ctx.free_host(bb)
+    ctx.close()
+    if rank == 0:
+        total = len(frames) * world
+        out["c5"] = {"workload": "configs[4]: 1 M-triangle heightfield + 16 ben on looped trajectories, full LBVH rebuild every frame, "
+                                 "128 x 3601 rays, frames sharded over the ranks; head of the 4096-frame batch",
+                     "frames": total, "n_triangles": n_tris5, "frames_per_s": total / dt, "ms_per_frame_per_gpu": dt / len(frames) * 1e3,
+                     "mrays_per_s": total * R / dt / 1e6, "seconds_for_4096_frames": 4096 / (total / dt),
+                     "api": "lsb200_run_frames, 16-byte records to pinned host memory"}
+    return out
+
+
 _RESULT_FD = None
 
 
@@ -361,6 +506,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle / float64 comparison of the benchmarked frame")
     ap.add_argument("--no-xt32", action="store_true", help="skip the XT-32 scan leg (profiling runs of the main step)")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the configs[1] / [2] / [4] legs")
     ap.add_argument("--traversal", type=int, default=None)
     ap.add_argument("--top-nodes", type=int, default=None)
     ap.add_argument("--leaf", type=int, default=None)
@@ -482,6 +628,51 @@ def main():
     # the trace stage = k_tile_entries (per-tile entry lists, rebuilt with every BVH) + k_trace
     stages["tile_lists"] = round(float(st.ms_tile_lists), 4)
     stages["k_trace"] = round(float(st.ms_trace) - float(st.ms_tile_lists), 4)
+
+    # ---- other splits of configs[3] (extra keys; the headline above shards FRAMES) -----------------------------------------
+    def timed_steps(fn, k_steps, warm=2):
+        for w_ in range(warm):
+            fn(10_000 + w_)
+        sync_all()
+        a, bb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for kk in range(k_steps):
+            fn(20_000 + kk)
+        bb.record(stream)
+        sync_all()
+        ms_ = a.elapsed_time(bb) / k_steps
+        if world > 1:
+            tt_ = torch.tensor([ms_], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt_, op=dist.ReduceOp.MAX)
+            ms_ = float(tt_.item())
+        return ms_
+
+    # device-major (SURVEY 8e for C4): ONE frame at a time on all GPUs, the 64 devices sharded over the ranks; every
+    # rank pays the full rebuild, so the frame latency is ~ commit + trace / N (the replicated build is the Amdahl term)
+    lo_s, hi_s = n_sens * rank // world, n_sens * (rank + 1) // world
+
+    def step_device_major(f):
+        step_resident(f)                                    # the SAME frame on every rank
+        assert ctx.trace_batch(lo_s, hi_s - lo_s, 0) == 0, ctx.last_error()
+    ms_dm = timed_steps(step_device_major, args.steps)
+    c4_device_major = {"what": "one frame at a time, 64 devices sharded over the ranks, every rank rebuilds the whole BVH",
+                       "ms_per_frame": ms_dm, "mrays_per_s": n_sens * R / (ms_dm * 1e-3) / 1e6, "frames_per_s": 1e3 / ms_dm,
+                       "devices_per_gpu": hi_s - lo_s}
+
+    # moving sensors (vehicle-mounted LiDARs): every device's pose changes every frame, so the octant queues, tile
+    # intervals, origin chains and tile lists are rebuilt per frame instead of being cached per sensor table
+    def step_moving(f):
+        for k_, (q_, t_) in enumerate(poses):
+            tq = np.array(t_, np.float32); tq[0] += np.float32(0.01 * (f % 100)); tq[1] -= np.float32(0.007 * (f % 100))
+            ctx.set_sensor_pose(q_, tq, index=k_)
+        step_resident(f * world + rank)
+        assert ctx.trace_batch(0, n_sens, 0) == 0, ctx.last_error()
+    ms_mv = timed_steps(step_moving, args.steps)
+    for k_, (q_, t_) in enumerate(poses):
+        ctx.set_sensor_pose(q_, t_, index=k_)
+    c4_moving = {"what": "frames sharded over ranks as in the headline, but all 64 sensor poses change every frame "
+                         "(lsb200_set_sensor_pose): queues / intervals / chains / lists rebuilt per frame",
+                 "ms_per_step": ms_mv, "mrays_per_s": world * rays_per_step_rank / (ms_mv * 1e-3) / 1e6}
 
     # ---- optional gather of the per-GPU clouds over NVLink (N > 1): shard.gather_clouds on NCCL with the real clouds ----
     gather = None
@@ -692,12 +883,16 @@ def main():
             "clocks": clocks,
             "e2e": e2e["xyzi16"], "e2e_pointcloud2_32": e2e["pointcloud2_32"], "e2e_range_image": e2e["range_image"],
             "gpu_launches": launches,
-            "gather": gather,
+            "gather": gather, "c4_device_major": c4_device_major, "c4_moving_sensors": c4_moving,
             "roofline": roofline,
         }
     ctx.close()
     if rank == 0 and not args.no_xt32:
         line["xt32_scan"] = xt32_scan_leg(local, cpu=(world == 1 and not args.no_cpu_baseline))
+    if not args.no_other_configs:
+        oc = other_configs_leg(local, rank, world)
+        if rank == 0:
+            line["other_configs"] = oc
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

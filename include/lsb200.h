@@ -147,6 +147,9 @@ LSB200_API const char *lsb200_version(void);
  * sensor_index 0 is the context's device; indices > 0 are allowed in LSB200_FRAME_WORLD only. */
 LSB200_API int lsb200_set_sensor(lsb200_ctx *ctx, int sensor_index, const float *elev_deg, int V, float az_begin,
                                  float az_end, int H, const float q_wxyz[4], const float t_xyz[3]);
+/* pose-only update of a sensor that is already set (same q / t conventions): no table upload, no synchronisation -- for
+ * sensors that move every frame (the reference re-reads the pose only at start-up, SRC/LidarDevice.cpp:788-816) */
+LSB200_API int lsb200_set_sensor_pose(lsb200_ctx *ctx, int sensor_index, const float q_wxyz[4], const float t_xyz[3]);
 /* Sensor limits the reference carries in its device config but never applies (config/hesai-pandar-XT-32-lidar_0000.json:
  * 14-18 "detection_radius", "horizontal_angle_range").  Semantics defined here: a ray whose closest
  * hit lies beyond max_range returns nothing (max_range <= 0: unlimited); an azimuth step whose angle, wrapped into

@@ -61,7 +61,13 @@ LSB200_API int lsbh_tracer_update_geometry_euler(lsbh_tracer *t, const char *nam
                                                  const float rotation[3]);
 LSB200_API int lsbh_tracer_commit_scene(lsbh_tracer *t);
 LSB200_API int lsbh_tracer_trace_scene(lsbh_tracer *t, uint32_t frame_index);
+/* ring_zero != 0 (the tracer's default): ring = 0 like the Embree path (SRC/EmbreeTracer.cpp:333-334); 0: ring = channel */
 LSB200_API int lsbh_tracer_set_flags(lsbh_tracer *t, int ordered, int ring_zero, int world_points);
+LSB200_API int lsbh_tracer_set_intensity(lsbh_tracer *t, int model, int apply_config_filter);
+LSB200_API int lsbh_tracer_set_watertight(lsbh_tracer *t, int on);
+/* lines the tracer wrote to the spdlog logger it was created with (SRC/EmbreeTracer.hpp:51: third create() argument) */
+LSB200_API int lsbh_tracer_log_count(lsbh_tracer *t);
+LSB200_API int lsbh_tracer_log_line(lsbh_tracer *t, int index, int *level, char *buf, size_t capacity);
 /* getTraceCloud(): header + payload of the cloud the tracer rewrites in place */
 LSB200_API int lsbh_tracer_cloud(lsbh_tracer *t, lsb200_cloud_header *hdr, const uint8_t **data, size_t *n_bytes);
 LSB200_API int lsbh_tracer_trace_raw(lsbh_tracer *t, float *t_out, int32_t *tri_out);

@@ -34,7 +34,7 @@ SYMBOLS = [
     "lsb200_device_results", "lsb200_fetch_points", "lsb200_fetch_batch", "lsb200_synchronize", "lsb200_run_frames", "lsb200_init_message", "lsb200_get_stats",
     "lsb200_reset_counters", "lsb200_get_trace_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
     "lsb200_set_log_callback", "lsb200_set_sensor_intensity_filter", "lsb200_expand_range_image", "lsb200_fetch_intensity",
-    "lsb200_alloc_host", "lsb200_free_host", "lsb200_device_numa_node", "lsb200_clone_scene", "lsb200_run_batch",
+    "lsb200_set_sensor_pose", "lsb200_alloc_host", "lsb200_free_host", "lsb200_device_numa_node", "lsb200_clone_scene", "lsb200_run_batch",
 ]
 
 LOG_FN = C.CFUNCTYPE(None, C.c_int, C.c_char_p, C.c_void_p)
@@ -114,6 +114,7 @@ def lib(lab=False):
     L.lsb200_debug_copy_vertices.argtypes = [vp, f32p, C.c_int64]
     L.lsb200_set_log_callback.argtypes = [vp, LOG_FN, vp]
     L.lsb200_set_sensor_intensity_filter.argtypes = [vp, C.c_int, C.c_float]
+    L.lsb200_set_sensor_pose.argtypes = [vp, C.c_int, f32p, f32p]
     L.lsb200_expand_range_image.argtypes = [vp, C.c_int, f32p, vp, C.c_size_t, u32p, C.c_uint32]
     L.lsb200_fetch_intensity.argtypes = [vp, C.c_int, f32p]
     L.lsb200_alloc_host.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
@@ -194,6 +195,11 @@ class Context:
 
     def set_sensor_limits(self, max_range=0.0, az_min_deg=-180.0, az_max_deg=180.0, index=0):
         return self._L.lsb200_set_sensor_limits(self._h, index, float(max_range), float(az_min_deg), float(az_max_deg))
+
+    def set_sensor_pose(self, q_wxyz, t_xyz, index=0):
+        q = np.ascontiguousarray(q_wxyz, np.float32)
+        t = np.ascontiguousarray(t_xyz, np.float32)
+        return self._L.lsb200_set_sensor_pose(self._h, index, _fp(q), _fp(t))
 
     def set_sensor_intensity_filter(self, min_intensity, index=0):
         return self._L.lsb200_set_sensor_intensity_filter(self._h, index, float(min_intensity))

@@ -444,6 +444,25 @@ int lsb200_set_sensor(lsb200_ctx *c, int idx, const float *elev_deg, int V, floa
     return LSB200_OK;
 }
 
+// pose-only update of a sensor that is already set: no table upload, no synchronisation (a vehicle-mounted LiDAR moves
+// every frame; its ray tables do not).  Everything derived from the pose -- octant queues, tile intervals, origin chains,
+// tile lists -- is rebuilt by the next trace.
+int lsb200_set_sensor_pose(lsb200_ctx *c, int idx, const float q_wxyz[4], const float t_xyz[3])
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set || !q_wxyz || !t_xyz)
+        return fail(c, LSB200_ERR_INVALID, "set_sensor_pose: sensor %d not set", idx);
+    Sensor &s = c->sensors[idx];
+    std::memcpy(s.q, q_wxyz, 16); std::memcpy(s.T, t_xyz, 12);
+    quat_to_rotation(s.q, s.R);
+    inverse3(s.R, s.Rinv);
+    c->sensors_dirty = true;
+    ++c->sensors_epoch;
+    if (idx == 0 && c->frame_mode == LSB200_FRAME_SENSOR) c->committed = false;   // scene lives in this sensor's frame
+    return LSB200_OK;
+}
+
 int lsb200_set_sensor_limits(lsb200_ctx *c, int idx, float max_range, float az_min_deg, float az_max_deg)
 {
     if (!c) return LSB200_ERR_INVALID;

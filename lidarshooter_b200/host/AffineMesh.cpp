@@ -12,7 +12,7 @@ Vector3f AffineMesh::transformToGlobal(Vector3f d) const
     // Translation(0) * Rz * Ry * Rx, the same composition (and code) as MeshTransformer::transformFromComponents
     const float zero[3] = {0.f, 0.f, 0.f};
     float A[12];
-    lsb200_affine_from_components(zero, _angular.v, A);
+    lsb200_affine_from_components(zero, _angular.data(), A);
     Vector3f o;
     for (int r = 0; r < 3; ++r) {
         const float p0 = A[4 * r] * d[0], p1 = A[4 * r + 1] * d[1], p2 = A[4 * r + 2] * d[2];

@@ -6,28 +6,32 @@
 
 namespace lidarshooter {
 
-ITracer::ITracer(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceStorage)
-    : _config(_sensorConfig), _geometryCount(0)
+B200Tracer::Ptr B200Tracer::create(LidarDevice::Ptr _sensorConfig, sensor_msgs::PointCloud2::Ptr _traceStorage,
+                                   std::shared_ptr<spdlog::logger> _logger, int _cudaDevice)
 {
-    // SRC/ITracer.cpp:16-25: own the cloud when none is given; zero width/height
-    _traceCloud = _traceStorage ? _traceStorage : PointCloud2::Ptr(new PointCloud2());
-    _traceCloud->width = 0;
-    _traceCloud->height = 0;
+    return B200Tracer::Ptr(new B200Tracer(_sensorConfig, _traceStorage, _logger, _cudaDevice));
 }
 
-B200Tracer::Ptr B200Tracer::create(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceStorage, int _cudaDevice)
+// the library's log sink -> the spdlog logger every reference tracer logs to (levels are spdlog's)
+void B200Tracer::logThunk(int _level, const char *_message, void *_self)
 {
-    return B200Tracer::Ptr(new B200Tracer(_sensorConfig, _traceStorage, _cudaDevice));
+    B200Tracer *self = static_cast<B200Tracer *>(_self);
+    if (self->_logger) self->_logger->log(static_cast<spdlog::level::level_enum>(_level), std::string(_message));
 }
 
-B200Tracer::B200Tracer(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceStorage, int _cudaDevice)
-    : ITracer(_sensorConfig, _traceStorage)
+B200Tracer::B200Tracer(LidarDevice::Ptr _sensorConfig, sensor_msgs::PointCloud2::Ptr _traceStorage,
+                       std::shared_ptr<spdlog::logger> __logger, int _cudaDevice)
+    : ITracer(_sensorConfig, _traceStorage, __logger)
 {
     const int rc = lsb200_create(_cudaDevice, &_ctx);
-    if (rc != LSB200_OK || !_ctx)
+    if (rc != LSB200_OK || !_ctx) {
+        _logger->error("B200Tracer: lsb200_create failed: no usable CUDA device (there is no CPU path)");
         throw TraceException(__FILE__, "lsb200_create failed: no usable CUDA device (B200Tracer has no CPU path)", rc);
+    }
+    lsb200_set_log_callback(_ctx, &B200Tracer::logThunk, this);
     LidarDevice::Ptr dev = getSensorConfig();
     if (dev) {
+        // the four LidarDevice getters of INTEGRATION.md: channel table, azimuth range, quaternion, translation
         float q[4], t[3];
         dev->quaternion(q);
         dev->translation(t);
@@ -39,6 +43,8 @@ B200Tracer::B200Tracer(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceSt
             lsb200_destroy(_ctx); _ctx = nullptr;
             throw TraceException(__FILE__, "lsb200_set_sensor failed: " + msg, src);
         }
+        _logger->info("B200Tracer: " + dev->getSensorUid() + " on CUDA device " + std::to_string(_cudaDevice) + ", " +
+                      std::to_string(dev->getTotalRays()) + " rays per scan");
     }
 }
 
@@ -49,6 +55,16 @@ int B200Tracer::setSensorLimits(bool _on)
     if (_on) dev->horizontalAngleRange(lo, hi);
     return lsb200_set_sensor_limits(_ctx, 0, _on ? dev->detectionRadius() : 0.0f, lo, hi);
 }
+
+int B200Tracer::setIntensity(int _model, bool _filter)
+{
+    int rc = lsb200_set_option(_ctx, LSB200_OPT_INTENSITY_MODEL, _model);
+    if (rc != LSB200_OK) return rc;
+    auto dev = getSensorConfig();
+    return lsb200_set_sensor_intensity_filter(_ctx, 0, (_filter && dev->useIntensityFiltering()) ? dev->minimumIntensity() : 0.0f);
+}
+
+int B200Tracer::setWatertight(bool _on) { return lsb200_set_option(_ctx, LSB200_OPT_WATERTIGHT, _on ? 1 : 0); }
 
 B200Tracer::~B200Tracer()
 {
@@ -100,21 +116,26 @@ int B200Tracer::removeGeometry(const std::string &_meshName)
     return id;
 }
 
-Affine3f B200Tracer::transformFromComponents(Vector3f _translation, Vector3f _rotation)
+Eigen::Affine3f B200Tracer::transformFromComponents(Eigen::Vector3f _translation, Eigen::Vector3f _rotation)
 {
-    Affine3f A;
-    lsb200_affine_from_components(_translation.v, _rotation.v, A.m);
+    const float t[3] = {_translation.x(), _translation.y(), _translation.z()}, r[3] = {_rotation.x(), _rotation.y(), _rotation.z()};
+    float rows[12];
+    lsb200_affine_from_components(t, r, rows);
+    Eigen::Affine3f A = Eigen::Affine3f::Identity();
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 4; ++j) A(i, j) = rows[4 * i + j];
     return A;
 }
 
-int B200Tracer::update(const std::string &_meshName, const float A[12], PolygonMesh::Ptr &_mesh)
+int B200Tracer::update(const std::string &_meshName, const float A[12], pcl::PolygonMesh::Ptr &_mesh)
 {
     if (!_mesh) throw MeshNotSetException(__FILE__, "No mesh data to transform", 1);       // SRC/MeshTransformer.cpp:144-151
     auto it = _geoms.find(_meshName);
     if (it == _geoms.end()) throw TraceException(__FILE__, "Geometry key does not exist in geometry types map", 8);
     Geom &g = it->second;
     const int arity = g.type == RTC_GEOMETRY_TYPE_QUAD ? 4 : 3;
-    if (static_cast<long>(_mesh->vertexCount()) < g.nVerts || static_cast<long>(_mesh->polygons.size()) < g.nElems)
+    const size_t meshVerts = _mesh->cloud.point_step ? _mesh->cloud.data.size() / _mesh->cloud.point_step : 0;
+    if (static_cast<long>(meshVerts) < g.nVerts || static_cast<long>(_mesh->polygons.size()) < g.nElems)
         return -1;
     const uint32_t *elems = nullptr;
     if (!g.topologySent) {
@@ -124,7 +145,8 @@ int B200Tracer::update(const std::string &_meshName, const float A[12], PolygonM
             const auto &poly = _mesh->polygons[e].vertices;
             if (static_cast<int>(poly.size()) != arity)
                 throw BadGeometryException(__FILE__, "Wrong number of vertices in an element", 1, arity, static_cast<long>(poly.size()));
-            std::memcpy(&_elemScratch[static_cast<size_t>(e) * arity], poly.data(), sizeof(uint32_t) * arity);
+            for (int k = 0; k < arity; ++k)      // pcl::index_t is signed in PCL 1.12: converted, not memcpy'd
+                _elemScratch[static_cast<size_t>(e) * arity + k] = static_cast<uint32_t>(poly[k]);
         }
         elems = _elemScratch.data();
     }
@@ -133,15 +155,20 @@ int B200Tracer::update(const std::string &_meshName, const float A[12], PolygonM
     return rc;
 }
 
-int B200Tracer::updateGeometry(const std::string &_meshName, Affine3f _transform, PolygonMesh::Ptr &_mesh)
+int B200Tracer::updateGeometry(const std::string &_meshName, Eigen::Affine3f _transform, pcl::PolygonMesh::Ptr &_mesh)
 {
-    return update(_meshName, _transform.m, _mesh);
+    float rows[12];                                  // row-major 3x4 [L | t]
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 4; ++j) rows[4 * i + j] = _transform(i, j);
+    return update(_meshName, rows, _mesh);
 }
 
-int B200Tracer::updateGeometry(const std::string &_meshName, Vector3f _translation, Vector3f _rotation, PolygonMesh::Ptr &_mesh)
+int B200Tracer::updateGeometry(const std::string &_meshName, Eigen::Vector3f _translation, Eigen::Vector3f _rotation, pcl::PolygonMesh::Ptr &_mesh)
 {
-    const Affine3f A = transformFromComponents(_translation, _rotation);
-    return update(_meshName, A.m, _mesh);
+    const float t[3] = {_translation.x(), _translation.y(), _translation.z()}, r[3] = {_rotation.x(), _rotation.y(), _rotation.z()};
+    float rows[12];
+    lsb200_affine_from_components(t, r, rows);       // T * Rz * Ry * Rx (SRC/MeshTransformer.cpp:467-477)
+    return update(_meshName, rows, _mesh);
 }
 
 int B200Tracer::commitScene()
@@ -152,14 +179,14 @@ int B200Tracer::commitScene()
 int B200Tracer::traceScene(std::uint32_t _frameIndex)
 {
     // SRC/EmbreeTracer.cpp:297-367: header, clear, trace, width = number of hits.  The cloud is rewritten in place.
-    PointCloud2::Ptr cloud = getTraceCloud();
+    sensor_msgs::PointCloud2::Ptr cloud = getTraceCloud();
     getSensorConfig()->initMessage(cloud, static_cast<int>(_frameIndex));
     const size_t capacity = getSensorConfig()->getTotalRays();
     cloud->data.resize(capacity * 32);
     uint32_t n = 0;
     uint32_t flags = 0;
     if (_ordered) flags |= LSB200_TRACE_ORDERED;
-    if (_ringZero) flags |= LSB200_TRACE_RING_ZERO;
+    if (!_ringChannel) flags |= LSB200_TRACE_RING_ZERO;          // default: the Embree path's ring = 0 (SRC/EmbreeTracer.cpp:333-334)
     if (_worldPoints) flags |= LSB200_TRACE_WORLD_POINTS;
     const int rc = lsb200_trace_scene(_ctx, 0, _frameIndex, cloud->data.data(), capacity, &n, flags);
     cloud->data.resize(static_cast<size_t>(n) * 32);

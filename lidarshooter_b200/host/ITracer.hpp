@@ -1,5 +1,7 @@
-// ITracer.hpp -- the tracer interface of the reference, re-declared 1:1 (SRC/ITracer.hpp:29-152) over this
-// repository's stand-in types.  B200Tracer implements it; MeshProjector::traceAffineMesh's call sequence
+// ITracer.hpp -- the tracer interface of the reference, re-declared 1:1 (SRC/ITracer.hpp:29-152; ctor SRC/ITracer.cpp:
+// 3-26) so that B200Tracer.{hpp,cpp} -- the file a maintainer drops next to EmbreeTracer.hpp -- compiles here exactly as
+// it does against the reference's own ITracer.hpp: same signatures, same third-party type names (Eigen, pcl,
+// sensor_msgs, spdlog, RTCGeometryType), same protected `_logger`.  MeshProjector::traceAffineMesh's call sequence
 // (updateGeometry* -> commitScene -> traceScene, SRC/MeshProjector.cpp:446-471) works unchanged against it.
 #pragma once
 #include <cstdint>
@@ -7,8 +9,19 @@
 #include <stdexcept>
 #include <string>
 
+#include <Eigen/Dense>
+#include <Eigen/Geometry>
+#include <embree3/rtcore.h>
+#include <pcl/PolygonMesh.h>
+#include <sensor_msgs/PointCloud2.h>
+#include <spdlog/spdlog.h>
+#include <spdlog/sinks/stdout_color_sinks.h>
+
 #include "LidarDevice.hpp"
-#include "Types.hpp"
+
+#ifndef LIDARSHOOTER_APPLICATION_NAME
+#define LIDARSHOOTER_APPLICATION_NAME "LiDARShooter"     // SRC/LidarShooter.hpp.in (cmake-configured in the reference)
+#endif
 
 namespace lidarshooter {
 
@@ -43,30 +56,31 @@ public:
     using Ptr = std::shared_ptr<ITracer>;
     using ConstPtr = std::shared_ptr<ITracer const>;
 
-    ITracer(LidarDevice::Ptr _sensorConfig, PointCloud2::Ptr _traceStorage = nullptr);
+    ITracer(LidarDevice::Ptr _sensorConfig, sensor_msgs::PointCloud2::Ptr _traceStorage = nullptr, std::shared_ptr<spdlog::logger> _logger = nullptr);
     virtual ITracer::Ptr getPtr() = 0;
     virtual ~ITracer() = default;
 
     virtual int addGeometry(const std::string &_meshName, enum RTCGeometryType _geometryType, int _numVertices, int _numElements) = 0;
     virtual int removeGeometry(const std::string &_meshName) = 0;
-    virtual int updateGeometry(const std::string &_meshName, Affine3f _transform, PolygonMesh::Ptr &_mesh) = 0;
-    virtual int updateGeometry(const std::string &_meshName, Vector3f _translation, Vector3f _rotation, PolygonMesh::Ptr &_mesh) = 0;
+    virtual int updateGeometry(const std::string &_meshName, Eigen::Affine3f _transform, pcl::PolygonMesh::Ptr &_mesh) = 0;
+    virtual int updateGeometry(const std::string &_meshName, Eigen::Vector3f _translation, Eigen::Vector3f _rotation, pcl::PolygonMesh::Ptr &_mesh) = 0;
     virtual int commitScene() = 0;
     virtual int traceScene(std::uint32_t _frameIndex) = 0;
     virtual long getGeometryCount() const { return _geometryCount; }
 
-    PointCloud2::Ptr getTraceCloud() { return _traceCloud; }
-    void setTraceCloud(PointCloud2::Ptr _traceStorage) { _traceCloud = _traceStorage; }
+    sensor_msgs::PointCloud2::Ptr getTraceCloud() { return _traceCloud; }
+    void setTraceCloud(sensor_msgs::PointCloud2::Ptr _traceStorage) { _traceCloud = _traceStorage; }
     LidarDevice::Ptr getSensorConfig() { return _config; }
     void setSensorConfig(LidarDevice::Ptr __config) { _config = __config; }
 
 protected:
     void setGeometryCount(long _count) { _geometryCount = _count; }
+    std::shared_ptr<spdlog::logger> _logger;       // SRC/ITracer.hpp:139
 
 private:
     LidarDevice::Ptr _config;
     long _geometryCount;
-    PointCloud2::Ptr _traceCloud;
+    sensor_msgs::PointCloud2::Ptr _traceCloud;
 };
 
 }  // namespace lidarshooter

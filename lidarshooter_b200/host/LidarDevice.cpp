@@ -176,6 +176,8 @@ int LidarDevice::loadTransformationFromJson(const json::Value &t)
         updateRotation();
     }
     if (t.isMember("detection_radius")) _device.detectionRadius = t["detection_radius"].asFloat(0.0f);
+    if (t.isMember("use_intensity_filtering")) _device.useIntensityFiltering = t["use_intensity_filtering"].asBool(false);
+    if (t.isMember("minimum_intensity")) _device.minimumIntensity = t["minimum_intensity"].asFloat(0.0f);
     if (t.isMember("horizontal_angle_range") && t["horizontal_angle_range"].size() == 2) {
         _device.horizontalAngleRange[0] = t["horizontal_angle_range"][size_t(0)].asFloat(-180.0f);
         _device.horizontalAngleRange[1] = t["horizontal_angle_range"][size_t(1)].asFloat(180.0f);
@@ -188,10 +190,7 @@ void LidarDevice::initMessage(PointCloud2::Ptr _msg, int _frameIndex)
     _msg->fields.clear();
     for (const auto &field : _message.fields) _msg->fields.push_back(field);
     _msg->header.frame_id = _message.frameId;
-    {
-        const auto ns = std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::system_clock::now().time_since_epoch()).count();
-        _msg->header.stamp = Time((uint32_t)(ns / 1000000000LL), (uint32_t)(ns % 1000000000LL));
-    }
+    _msg->header.stamp = ros::Time::now();            // SRC/LidarDevice.cpp:103
     _msg->header.seq = static_cast<uint32_t>(_frameIndex);
     _msg->height = 1;
     _msg->width = 0;
@@ -275,7 +274,7 @@ void LidarDevice::originToSensor(Vector3f &s) const
 void LidarDevice::originToSensorInverse(Vector3f &s) const
 {
     float o[3];
-    mulMat3(_device.R, s.v, o);
+    mulMat3(_device.R, s.data(), o);
     s = Vector3f(o[0] + _device.tx, o[1] + _device.ty, o[2] + _device.tz);
 }
 

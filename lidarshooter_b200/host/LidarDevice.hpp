@@ -42,6 +42,8 @@ public:
                       const float _qwxyz[4], const float _txyz[3], const std::string &_sensorUid = "synthetic");
     Ptr getPtr() { return shared_from_this(); }
     float detectionRadius() const { return _device.detectionRadius; }
+    bool useIntensityFiltering() const { return _device.useIntensityFiltering; }      // config/hesai-pandar-XT-32-lidar_0000.json:19
+    float minimumIntensity() const { return _device.minimumIntensity; }               // config/hesai-pandar-XT-32-lidar_0000.json:20
     void horizontalAngleRange(float &_lo, float &_hi) const { _lo = _device.horizontalAngleRange[0]; _hi = _device.horizontalAngleRange[1]; }
 
     void initialize(const std::string &_config, const std::string &_sensorUid = "");
@@ -62,7 +64,8 @@ public:
     const std::string &getSensorUid() const { return _device.sensorUid; }
     const std::string &getOutputFolder() const { return _outputFolder; }
 
-    // what the C ABI's lsb200_set_sensor takes
+    // what the C ABI's lsb200_set_sensor takes.  verticalAngles / azimuthBegin / azimuthEnd / quaternion / translation are
+    // THE accessors a lidarshooter tree has to add to its LidarDevice for the drop-in ("LidarDevice getters")
     const std::vector<float> &verticalAngles() const { return _channels.vertical; }
     float azimuthBegin() const { return _channels.horizontal.begin; }
     float azimuthEnd() const { return _channels.horizontal.end; }
@@ -90,6 +93,8 @@ private:
         // carried by the reference's config, never applied by it (config/hesai-pandar-XT-32-lidar_0000.json:14-18)
         float detectionRadius = 0.f;                 // 0 = unlimited
         float horizontalAngleRange[2] = {-180.f, 180.f};
+        bool useIntensityFiltering = false;
+        float minimumIntensity = 0.f;
     } _device;
     struct {
         std::string frameId = "PandarXT-32";

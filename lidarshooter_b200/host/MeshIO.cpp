@@ -72,7 +72,7 @@ int loadAsciiSTL(const std::string &text, PolygonMesh &mesh)
     if (idx.size() % 3) return -2;
     fillCloud(w.xyz(), mesh);
     mesh.polygons.resize(idx.size() / 3);
-    for (size_t t = 0; t < idx.size() / 3; ++t) mesh.polygons[t].vertices = {idx[3 * t], idx[3 * t + 1], idx[3 * t + 2]};
+    for (size_t t = 0; t < idx.size() / 3; ++t) mesh.polygons[t].vertices = {(pcl::index_t)idx[3 * t], (pcl::index_t)idx[3 * t + 1], (pcl::index_t)idx[3 * t + 2]};
     return static_cast<int>(idx.size() / 3);
 }
 
@@ -132,8 +132,8 @@ int loadPolygonFileOBJ(const std::string &_path, PolygonMesh &_mesh)
                 ids.push_back(static_cast<uint32_t>(v > 0 ? v - 1 : nv + v));
             }
             for (size_t k = 2; k < ids.size(); ++k) {
-                Vertices poly;
-                poly.vertices = {ids[0], ids[k - 1], ids[k]};
+                pcl::Vertices poly;
+                poly.vertices = {(pcl::index_t)ids[0], (pcl::index_t)ids[k - 1], (pcl::index_t)ids[k]};
                 _mesh.polygons.push_back(poly);
             }
         }

@@ -16,7 +16,7 @@ using namespace lidarshooter;
 
 struct lsbh_device { LidarDevice::Ptr p; };
 struct lsbh_mesh { PolygonMesh::Ptr p; };
-struct lsbh_tracer { B200Tracer::Ptr p; };
+struct lsbh_tracer { B200Tracer::Ptr p; std::shared_ptr<spdlog::logger> log; };
 
 static void set_err(char *err, size_t n, const char *msg) { if (err && n) std::snprintf(err, n, "%s", msg); }
 
@@ -119,16 +119,16 @@ lsbh_mesh *lsbh_mesh_from_arrays(const float *xyz, size_t nv, const uint32_t *el
 void lsbh_mesh_destroy(lsbh_mesh *m) { delete m; }
 int lsbh_mesh_counts(const lsbh_mesh *m, int *nv, int *np, int *step)
 {
-    *nv = (int)m->p->vertexCount(); *np = (int)m->p->polygons.size(); *step = (int)m->p->cloud.point_step;
+    *nv = (int)vertexCount(*m->p); *np = (int)m->p->polygons.size(); *step = (int)m->p->cloud.point_step;
     return 0;
 }
 int lsbh_mesh_copy(const lsbh_mesh *m, float *xyz, uint32_t *elems, int vpe)
 {
-    const size_t nv = m->p->vertexCount();
+    const size_t nv = vertexCount(*m->p);
     for (size_t i = 0; i < nv; ++i) std::memcpy(xyz + 3 * i, m->p->cloud.data.data() + i * m->p->cloud.point_step, 12);
     for (size_t e = 0; e < m->p->polygons.size(); ++e) {
         if ((int)m->p->polygons[e].vertices.size() != vpe) return -1;
-        std::memcpy(elems + e * vpe, m->p->polygons[e].vertices.data(), 4 * vpe);
+        for (int k = 0; k < vpe; ++k) elems[e * vpe + k] = static_cast<uint32_t>(m->p->polygons[e].vertices[k]);
     }
     return 0;
 }
@@ -137,7 +137,9 @@ lsbh_tracer *lsbh_tracer_create(lsbh_device *d, int dev, char *err, size_t n)
 {
     try {
         auto *t = new lsbh_tracer();
-        t->p = B200Tracer::create(d->p, nullptr, dev);
+        t->log = std::make_shared<spdlog::logger>("lsbh_tracer");
+        t->log->set_echo(false);
+        t->p = B200Tracer::create(d->p, nullptr, t->log, dev);
         return t;
     } catch (const std::exception &e) { set_err(err, n, e.what()); return nullptr; }
 }
@@ -153,7 +155,7 @@ int lsbh_tracer_geometry_id(const lsbh_tracer *t, const char *name) { return t->
 int lsbh_tracer_update_geometry(lsbh_tracer *t, const char *name, lsbh_mesh *mesh, const float A[12])
 {
     return guarded([&] {
-        Affine3f a; std::memcpy(a.m, A, 48);
+        const Affine3f a = affineFromRows(A);
         PolygonMesh::Ptr m = mesh ? mesh->p : nullptr;
         return t->p->updateGeometry(name, a, m);
     });
@@ -169,7 +171,7 @@ int lsbh_tracer_commit_scene(lsbh_tracer *t) { return t->p->commitScene(); }
 int lsbh_tracer_trace_scene(lsbh_tracer *t, uint32_t frame) { return t->p->traceScene(frame); }
 int lsbh_tracer_set_flags(lsbh_tracer *t, int ordered, int ring_zero, int world)
 {
-    t->p->setOrderedOutput(ordered != 0); t->p->setRingZeroCompat(ring_zero != 0); t->p->setWorldFramePoints(world != 0);
+    t->p->setOrderedOutput(ordered != 0); t->p->setRingChannel(ring_zero == 0); t->p->setWorldFramePoints(world != 0);
     return 0;
 }
 int lsbh_tracer_cloud(lsbh_tracer *t, lsb200_cloud_header *h, const uint8_t **data, size_t *n)
@@ -181,6 +183,18 @@ int lsbh_tracer_cloud(lsbh_tracer *t, lsb200_cloud_header *h, const uint8_t **da
     return 0;
 }
 int lsbh_tracer_set_sensor_limits(lsbh_tracer *t, int on) { return t->p->setSensorLimits(on != 0); }
+int lsbh_tracer_set_intensity(lsbh_tracer *t, int model, int filter) { return t->p->setIntensity(model, filter != 0); }
+int lsbh_tracer_set_watertight(lsbh_tracer *t, int on) { return t->p->setWatertight(on != 0); }
+// what the tracer logged through the std::shared_ptr<spdlog::logger> it was created with (shim logger keeps its lines)
+int lsbh_tracer_log_count(lsbh_tracer *t) { return (int)t->log->lines().size(); }
+int lsbh_tracer_log_line(lsbh_tracer *t, int i, int *level, char *buf, size_t n)
+{
+    const auto lines = t->log->lines();
+    if (i < 0 || (size_t)i >= lines.size()) return -1;
+    *level = lines[i].first;
+    std::snprintf(buf, n, "%s", lines[i].second.c_str());
+    return 0;
+}
 int lsbh_device_limits(const lsbh_device *d, float *radius, float *az_lo, float *az_hi)
 {
     *radius = d->p->detectionRadius();

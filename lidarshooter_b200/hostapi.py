@@ -20,7 +20,8 @@ SYMBOLS = [
     "lsbh_tracer_update_geometry", "lsbh_tracer_update_geometry_euler", "lsbh_tracer_commit_scene",
     "lsbh_tracer_trace_scene", "lsbh_tracer_set_flags", "lsbh_tracer_cloud", "lsbh_tracer_trace_raw",
     "lsbh_tracer_serialize_cloud", "lsbh_cloud_reserialize", "lsbh_tracer_append_cloud_to_file",
-    "lsbh_device_limits", "lsbh_tracer_set_sensor_limits",
+    "lsbh_device_limits", "lsbh_tracer_set_sensor_limits", "lsbh_tracer_set_intensity", "lsbh_tracer_set_watertight",
+    "lsbh_tracer_log_count", "lsbh_tracer_log_line",
     "lsbh_trajectory_poses",
 ]
 
@@ -76,6 +77,10 @@ def lib():
         "lsbh_tracer_append_cloud_to_file": (C.c_int, [vp, cp, C.c_int]),
         "lsbh_device_limits": (C.c_int, [vp, f32p, f32p, f32p]),
         "lsbh_tracer_set_sensor_limits": (C.c_int, [vp, C.c_int]),
+        "lsbh_tracer_set_intensity": (C.c_int, [vp, C.c_int, C.c_int]),
+        "lsbh_tracer_set_watertight": (C.c_int, [vp, C.c_int]),
+        "lsbh_tracer_log_count": (C.c_int, [vp]),
+        "lsbh_tracer_log_line": (C.c_int, [vp, C.c_int, C.POINTER(C.c_int), C.c_char_p, C.c_size_t]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -230,8 +235,24 @@ class B200Tracer:
     def traceScene(self, frame):
         return self._L.lsbh_tracer_trace_scene(self._h, frame)
 
-    def setFlags(self, ordered=False, ring_zero=False, world_points=False):
+    def setFlags(self, ordered=False, ring_zero=True, world_points=False):
+        """ring_zero=True is the tracer's default (the Embree path's bytes, SRC/EmbreeTracer.cpp:333-334); False = ring = channel."""
         self._L.lsbh_tracer_set_flags(self._h, int(ordered), int(ring_zero), int(world_points))
+
+    def setIntensity(self, model=0, apply_config_filter=False):
+        return self._L.lsbh_tracer_set_intensity(self._h, int(model), int(apply_config_filter))
+
+    def setWatertight(self, on=True):
+        return self._L.lsbh_tracer_set_watertight(self._h, int(on))
+
+    def logLines(self):
+        """(level, text) pairs the tracer wrote to the spdlog logger it was created with."""
+        out = []
+        for i in range(self._L.lsbh_tracer_log_count(self._h)):
+            lv, buf = C.c_int(0), C.create_string_buffer(600)
+            if self._L.lsbh_tracer_log_line(self._h, i, C.byref(lv), buf, 600) == 0:
+                out.append((lv.value, buf.value.decode(errors="replace")))
+        return out
 
     def getTraceCloud(self):
         h = capi.CloudHeader()
@@ -239,6 +260,12 @@ class B200Tracer:
         self._L.lsbh_tracer_cloud(self._h, C.byref(h), C.byref(data), C.byref(n))
         buf = np.ctypeslib.as_array(data, shape=(n.value,)).copy() if n.value else np.zeros(0, np.uint8)
         return h, buf.reshape(-1, 32)
+
+    def getTraceCloudWidth(self):
+        h = capi.CloudHeader()
+        data, n = C.POINTER(C.c_uint8)(), C.c_size_t()
+        self._L.lsbh_tracer_cloud(self._h, C.byref(h), C.byref(data), C.byref(n))
+        return int(h.width)
 
     def setSensorLimits(self, on=True):
         return self._L.lsbh_tracer_set_sensor_limits(self._h, int(on))

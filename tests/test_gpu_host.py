@@ -59,8 +59,24 @@ def test_trace_scene_cloud(setup, meshes):
     h, pts = tracer.getTraceCloud()
     assert h.width == 1781 and h.seq == 1
     s = lso.Sensor(*xt32_sensor_args("0000"))
-    ref = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)])
+    ms = [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], IDENT)]
+    # default cloud bytes == the Embree path's: ring = 0 for every point (SRC/EmbreeTracer.cpp:333-334)
+    ref0 = lso.scan(s, ms, ring_mode=1)
+    assert np.array_equal(pts, ref0["points"])
+    assert (pts.view(np.int32).reshape(-1, 8)[:, 5] == 0).all()
+    # opt-in: ring = channel index, what the OptiX path writes (SRC/LidarDeviceKernels.cu:51)
+    tracer.setFlags(ordered=True, ring_zero=False)
+    assert tracer.traceScene(1) == 0
+    h, pts = tracer.getTraceCloud()
+    ref = lso.scan(s, ms)
     assert np.array_equal(pts, ref["points"])
+    assert set(np.unique(pts.view(np.int32).reshape(-1, 8)[:, 5])) <= set(range(32)) and pts.view(np.int32).reshape(-1, 8)[:, 5].max() > 0
+    # the spdlog logger given to create() (SRC/EmbreeTracer.hpp:51) received the library's lines
+    lines = tracer.logLines()
+    assert any(lv == 2 and "lidar_0000" in m and "4800 rays" in m for lv, m in lines), lines
+    assert tracer.removeGeometry("no-such-mesh") == -1
+    lines = tracer.logLines()
+    assert lines[-1][0] == 4 and "no-such-mesh" in lines[-1][1]
     rc, t, tri = tracer.traceRaw()
     assert rc == 0 and np.array_equal(tri, ref["tri"]) and np.array_equal(t, ref["t"])
 
@@ -86,13 +102,13 @@ def test_trace_scene_cloud(setup, meshes):
     os.remove(path)
 
     # world-frame points = CloudTransformer::applyInverseTransform (SRC/CloudTransformer.cpp:202-265), on the device
-    tracer.setFlags(ordered=True, world_points=True)
+    tracer.setFlags(ordered=True, ring_zero=False, world_points=True)
     assert tracer.traceScene(2) == 0
     _, wpts = tracer.getTraceCloud()
     sp = ref["points"].view(np.float32).reshape(-1, 8)[:, :3]
     expect = np.stack([dev.origin_to_sensor(p, inverse=True) for p in sp])
     assert np.array_equal(wpts.view(np.float32).reshape(-1, 8)[:, :3], expect)
-    tracer.setFlags(ordered=True)
+    tracer.setFlags(ordered=True, ring_zero=False)
 
     assert tracer.removeGeometry("ben") == 1
     assert tracer.getGeometryCount() == 1
@@ -126,7 +142,7 @@ def test_trajectory_frames_two_devices(meshes):
             assert tracer.traceScene(k) == 0
             h, pts = tracer.getTraceCloud()
             A = lso.affine_from_components(lin, ang)
-            ref = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], A)])
+            ref = lso.scan(s, [(meshes["ground_v"], meshes["ground_t"], IDENT), (meshes["ben_v"], meshes["ben_t"], A)], ring_mode=1)
             assert h.width == ref["points"].shape[0] and h.seq == k
             assert np.array_equal(pts, ref["points"])
         tracer.close()
