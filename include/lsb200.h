@@ -111,10 +111,21 @@ enum {
                                       Woop-Benthin-Wald 2013 shear / scale test (edge functions on the sheared vertices, exact
                                       double-precision fallback on a zero edge function): a ray can never slip between two
                                       triangles that share an edge.  Bit-exact against the oracle in the same mode. */
-    LSB200_OPT_INTENSITY_MODEL = 19 /* 0 (default) = constant 64.0, what the reference writes (SRC/EmbreeTracer.cpp:333); 1 =
+    LSB200_OPT_INTENSITY_MODEL = 19, /* 0 (default) = constant 64.0, what the reference writes (SRC/EmbreeTracer.cpp:333); 1 =
                                       Lambertian cos-incidence: 255 * |Ng . d| / (|Ng| |d|) from the hit triangle's normal
                                       (SURVEY 8f row 4).  Models other than 0 (and an intensity filter) emit the points through the
                                       ordered compaction. */
+    LSB200_OPT_LANE_REFILL = 21,   /* ray compaction inside the traversal: bit mask of the queue groups that are drained ray by ray
+                                      (a lane whose ray has ended takes the next ray of the queue: ballot + rank, unit lists in a
+                                      shared-memory ring) instead of one 32-ray unit per warp at a time.  bit 0 = sign-mixed units,
+                                      1 = upward octants, 2 = heavy (grazing) fronts of the downward octants, 3 = their light
+                                      remainders.  Default 0 (off): measured slower on the 10 M-triangle city, see DESIGN.md / profiles/design_choices_r02.md --
+                                      the traversal is bound by instruction issue and dependent round trips per unit, and the refill
+                                      loop costs more instructions than the idle lanes it fills.  Same per-ray results either way. */
+    LSB200_OPT_FUSED_TREE = 20     /* 1 (default) = hierarchy and node boxes come out of ONE bottom-up pass over the sorted codes
+                                      (k_tree: Apetrei 2014 with Karras node numbering, block-local rendezvous in shared memory);
+                                      0 = the two-kernel form (k_hierarchy: Karras 2012 top-down searches, then k_fit).  Same node
+                                      array bit for bit; kept for the before / after evidence. */
 };
 
 /* log levels of lsb200_set_log_callback == spdlog::level (the reference logs through spdlog, SRC/ITracer.cpp:5-14) */

@@ -375,19 +375,6 @@ __global__ void __launch_bounds__(kFitBlock) k_fit(SceneDev S, const uint32_t *_
     fit_leaf<1>(S, (int)__ldg(sorted_ids + i), i, s_flags, blockIdx.x * kFitBlock);
 }
 
-// ---- (4b) fit without the climb: range queries over the block's leaf boxes --------------------------------
-// k_fit's climb is a chain of dependent L2 round trips (ncu: 29 % issue, 46 % DRAM).  A Karras node whose leaf range
-// lies inside one 256-leaf block (99 % of the nodes; their index lies in the block too) does not need its children
-// to "arrive": its child boxes are min / max over contiguous runs of the block's leaf boxes.  Each CTA therefore
-//   1. writes its 256 leaf records and puts the leaf boxes into shared memory,
-//   2. builds a sparse table over them (windows of 1, 2, 4 .. 64 leaves: 7 levels x 256 x 24 B = 42 KB),
-//   3. lets thread t handle internal node (block base + t): two range queries (2-4 table reads each, min / max
-//      tolerate overlapping windows) give both child boxes, written as three coalesced 16-byte stores,
-//   4. and only the roots of the maximal block-local subtrees (and leaves hanging directly off a straddling node)
-//      continue upwards through the global arrival counters, as k_fit does.
-// Same boxes bit for bit (min / max are exact and order-free).
-constexpr int kRmqLevels = 7;
-
 struct Box6 { float lox, hix, loy, hiy, loz, hiz; };
 __device__ __forceinline__ void box_merge(Box6 &a, const Box6 &b)
 {
@@ -424,6 +411,207 @@ __device__ __forceinline__ Box6 leaf_record(const SceneDev &S, int g, int i)
     bx.loz = fminf(A.z, fminf(B.z, C.z)); bx.hiz = fmaxf(A.z, fmaxf(B.z, C.z));
     return bx;
 }
+
+// ---- (3 + 4) fused: hierarchy and boxes in ONE bottom-up pass over the sorted codes (k_tree) ---------------
+// Replaces k_hierarchy + k_fit (0.23 + 0.53 ms at 10 M triangles) for scenes beyond the small fused build.  The
+// binary radix tree over the (code, index) keys is unique, so it can be discovered from the leaves upwards
+// (Apetrei 2014, "Fast and Simple Agglomerative LBVH Construction"): a node that covers the sorted leaves [F, L]
+// merges across the boundary with the LONGER common prefix -- delta(L) > delta(F - 1): its parent splits at L
+// and the node is the left child; otherwise the parent splits at F - 1 and the node is the right child.  No
+// binary searches, no parent links in memory.  What this kernel adds to that scheme:
+//   * Karras numbering is kept (left child of a split s is node s, right child s + 1, root 0), so the node array is
+//     bit-identical to k_hierarchy + k_fit (tests/test_gpu_round2.py: test_fused_tree_equals_pipeline) and every
+//     consumer (traversal, origin chains, tile lists) is untouched.  A node learns its own index when it picks its
+//     parent; its two children meet at a rendezvous slot indexed by the SPLIT, which both know without it.
+//   * each child leaves (box, far end of its range, delta of its outer boundary) in its half of the slot; the
+//     second to arrive merges and writes the finished 64-byte node in one go.  The deltas travel with the boxes: a merged
+//     node inherits its left delta from its left child and its right delta from its right child -- no key loads
+//     above the leaves.
+//   * rendezvous slots of splits whose node lies inside one kTreeBlock-leaf block live in SHARED memory (~99 % of the
+//     nodes: both children are then completed by threads of this CTA); whether a split is block-local is decided
+//     exactly, from a prefix / suffix minimum of the block's deltas.  Only nodes that straddle blocks meet in
+//     global memory (rendezvous array + the parity arrival counters of k_fit).
+// The same kernel refits: the sorted codes and ids of the last rebuild stay where the sort left them.
+#ifndef LSB_TREE_BLOCK
+#define LSB_TREE_BLOCK 128
+#endif
+constexpr int kTreeBlock = LSB_TREE_BLOCK;        // leaves per k_tree CTA
+
+// common-prefix length of the (code, index) keys of the sorted leaves j and j + 1; -1 outside the scene
+__device__ __forceinline__ int boundary_delta(uint32_t ka, uint32_t kb, int j, int n)
+{
+    if (j < 0 || j >= n - 1) return -1;
+    return (ka == kb) ? 32 + __clz((uint32_t)j ^ (uint32_t)(j + 1)) : __clz(ka ^ kb);
+}
+
+// One merge step, shared by both kernels: this child (range end / outer delta / box in registers) and its sibling's
+// half of the rendezvous slot (sxy, sz) form the node that splits at s.  Writes the finished 64-byte node under its Karras
+// index and returns the merged state; true when the node was the root.
+struct Climber { float lox, hix, loy, hiy, loz, hiz; int F, L, dL, dR; };
+__device__ __forceinline__ bool tree_merge(const SceneDev &S, Climber &c, bool left, int s, const float4 sxy, const float4 sz)
+{
+    const int sib_end = __float_as_int(sz.z), sib_outer = __float_as_int(sz.w);
+    const int nF = left ? c.F : sib_end, nL = left ? sib_end : c.L;
+    const int ndL = left ? c.dL : sib_outer, ndR = left ? sib_outer : c.dR;
+    const int lcount = s - nF + 1, rcount = nL - s;
+    const int c0 = (lcount <= S.leaf_max) ? leaf_ref(nF, lcount) : S.top_cap + s;
+    const int c1 = (rcount <= S.leaf_max) ? leaf_ref(s + 1, rcount) : S.top_cap + s + 1;
+    const bool root = ndL < 0 && ndR < 0;
+    const int idx = root ? 0 : (ndR > ndL ? nL : nF);          // Karras index: left children sit at their last leaf, right at their first
+    float4 *node = S.nodes + 4 * ((size_t)S.top_cap + idx);
+    const float4 mxy = make_float4(c.lox, c.hix, c.loy, c.hiy);
+    node[0] = left ? mxy : sxy;
+    node[1] = left ? sxy : mxy;
+    node[2] = left ? make_float4(c.loz, c.hiz, sz.x, sz.y) : make_float4(sz.x, sz.y, c.loz, c.hiz);
+    node[3] = make_float4(__int_as_float(c0), __int_as_float(c1), __int_as_float(nF), __int_as_float(nL));
+    c.lox = fminf(c.lox, sxy.x); c.hix = fmaxf(c.hix, sxy.y);
+    c.loy = fminf(c.loy, sxy.z); c.hiy = fmaxf(c.hiy, sxy.w);
+    c.loz = fminf(c.loz, sz.x); c.hiz = fmaxf(c.hiz, sz.y);
+    c.F = nF; c.L = nL; c.dL = ndL; c.dR = ndR;
+    return root;
+}
+
+// Phase 1: leaf records + every node whose leaf range lies inside one block, rendezvous in shared memory.  A child of a
+// node that straddles blocks (the root of a maximal block-local subtree, or a leaf) leaves its half of the global
+// rendezvous slot and an entry in the work list of phase 2 -- it does NOT wait or climb on, so the CTA retires as soon as
+// its local subtrees are done (threads that lingered in the global climb held whole warps: 29 % of the stall samples
+// of the one-kernel form, profiles/design_choices_r02.md).
+__global__ void __launch_bounds__(kTreeBlock) k_tree(SceneDev S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
+                                                     float4 *__restrict__ rendezvous /* [4 * n_tris] */,
+                                                     uint32_t *__restrict__ work /* [n_tris]: split << 1 | side */, uint32_t *__restrict__ work_count)
+{
+    __shared__ uint32_t s_key[kTreeBlock + 2];          // codes of the leaves base - 1 .. base + kTreeBlock
+    __shared__ int8_t s_delta[kTreeBlock + 1];          // delta of the boundaries base - 1 .. base + kTreeBlock - 1
+    __shared__ int8_t s_sufmin[kTreeBlock + 2];
+    __shared__ int8_t s_wpre[kTreeBlock / 32], s_wsuf[kTreeBlock / 32];
+    __shared__ uint8_t s_local[kTreeBlock];             // split base + t: its node lies inside this block
+    __shared__ uint32_t s_flag[kTreeBlock];
+    __shared__ float4 s_rxy[2 * kTreeBlock], s_rz[2 * kTreeBlock];   // per split: slot 0 = left child, slot 1 = right child
+    __shared__ uint32_t s_work[kTreeBlock];
+    __shared__ uint32_t s_nwork, s_wbase;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int n = S.n_tris;
+    const int base = blockIdx.x * kTreeBlock;
+    const int i = base + t;
+    s_flag[t] = 0u;
+    if (t == 0) s_nwork = 0u;
+    for (int k = t; k < kTreeBlock + 2; k += kTreeBlock) {
+        const int j = base - 1 + k;
+        s_key[k] = (j >= 0 && j < n) ? __ldg(keys + j) : 0u;
+    }
+    __syncthreads();
+    // delta of boundary b = t (leaves i - 1 | i); thread 0 also owns the block's last boundary
+    const int d_lo = boundary_delta(s_key[t], s_key[t + 1], i - 1, n);
+    s_delta[t] = (int8_t)d_lo;
+    if (t == 0) s_delta[kTreeBlock] = (int8_t)boundary_delta(s_key[kTreeBlock], s_key[kTreeBlock + 1], base + kTreeBlock - 1, n);
+    // inclusive prefix / suffix minima of the deltas over the block's boundaries
+    int pm = d_lo, sm = d_lo;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, pm, o), w = __shfl_down_sync(0xffffffffu, sm, o);
+        if (lane >= o) pm = min(pm, u);
+        if (lane + o < 32) sm = min(sm, w);
+    }
+    if (lane == 31) s_wpre[warp] = (int8_t)pm;
+    if (lane == 0) s_wsuf[warp] = (int8_t)sm;
+    __syncthreads();
+    for (int w = 0; w < warp; ++w) pm = min(pm, (int)s_wpre[w]);
+    for (int w = warp + 1; w < kTreeBlock / 32; ++w) sm = min(sm, (int)s_wsuf[w]);
+    sm = min(sm, (int)s_delta[kTreeBlock]);
+    s_sufmin[t] = (int8_t)sm;
+    if (t == 0) { s_sufmin[kTreeBlock] = s_delta[kTreeBlock]; s_sufmin[kTreeBlock + 1] = 127; }
+    __syncthreads();
+    {
+        // split s = i separates the leaves i | i + 1 (boundary t + 1): its node [F, L] stays inside the block iff a
+        // boundary with a shorter prefix stops it on either side before the block ends
+        const int d_s = s_delta[t + 1];
+        s_local[t] = (t + 1 < kTreeBlock && pm < d_s && (int)s_sufmin[t + 2] < d_s) ? 1 : 0;
+    }
+    __syncthreads();
+    if (i < n) {
+        const Box6 leaf = leaf_record(S, (int)__ldg(sorted_ids + i), i);
+        Climber c{leaf.lox, leaf.hix, leaf.loy, leaf.hiy, leaf.loz, leaf.hiz, i, i, d_lo, (int)s_delta[t + 1]};
+        for (int level = 0; level < 96; ++level) {       // a block-local chain is at most kTreeBlock long; the bound only guards against a hang
+            const bool left = c.dR > c.dL;               // this node is the left child of the split at L
+            const int s = left ? c.L : c.F - 1;
+            const int ls = s - base;
+            const int mine = left ? 0 : 1;
+            const float4 pxy = make_float4(c.lox, c.hix, c.loy, c.hiy);
+            const float4 pz = make_float4(c.loz, c.hiz, __int_as_float(left ? c.F : c.L), __int_as_float(left ? c.dL : c.dR));
+            if (!(ls >= 0 && ls < kTreeBlock && s_local[ls])) {
+                // the parent straddles blocks: park this subtree for phase 2
+                float4 *slot = rendezvous + 4 * (size_t)s + 2 * mine;
+                __stcg(slot, pxy);
+                __stcg(slot + 1, pz);
+                s_work[atomicAdd(&s_nwork, 1u)] = ((uint32_t)s << 1) | (uint32_t)mine;
+                break;
+            }
+            s_rxy[2 * ls + mine] = pxy;
+            s_rz[2 * ls + mine] = pz;
+            __threadfence_block();
+            if (atomicAdd(&s_flag[ls], 1u) == 0u) break;           // first to arrive: the sibling finishes the node
+            __threadfence_block();
+            if (tree_merge(S, c, left, s, s_rxy[2 * ls + (mine ^ 1)], s_rz[2 * ls + (mine ^ 1)])) break;
+        }
+    }
+    __syncthreads();
+    const uint32_t nw = s_nwork;
+    if (t == 0 && nw) s_wbase = atomicAdd(work_count, nw);
+    __syncthreads();
+    if ((uint32_t)t < nw) work[s_wbase + t] = s_work[t];
+}
+
+// Phase 2: the nodes that straddle blocks (~1 % of the tree, its top).  One thread per parked subtree: arrival at the
+// global rendezvous slot (parity counters that are never re-zeroed, see k_fit), the second to arrive merges, writes the
+// node and carries on to the next split.
+__global__ void __launch_bounds__(128) k_tree_top(SceneDev S, float4 *__restrict__ rendezvous, const uint32_t *__restrict__ work,
+                                                  const uint32_t *__restrict__ work_count)
+{
+    const uint32_t nw = *work_count;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < nw; e += gridDim.x * blockDim.x) {
+        const uint32_t w = __ldg(work + e);
+        int s = (int)(w >> 1);
+        bool left = (w & 1u) == 0u;
+        Climber c;
+        {
+            const float4 *slot = rendezvous + 4 * (size_t)s + 2 * (left ? 0 : 1);
+            const float4 pxy = __ldcg(slot), pz = __ldcg(slot + 1);
+            c.lox = pxy.x; c.hix = pxy.y; c.loy = pxy.z; c.hiy = pxy.w; c.loz = pz.x; c.hiz = pz.y;
+            // only the fields the merge reads on this side are known -- and needed
+            c.F = left ? __float_as_int(pz.z) : s + 1; c.L = left ? s : __float_as_int(pz.z);
+            c.dL = left ? __float_as_int(pz.w) : 0; c.dR = left ? 0 : __float_as_int(pz.w);
+        }
+        bool parked = true;                               // the payload of the first level is already in the slot
+        for (int level = 0; level < 96; ++level) {
+            float4 *slot = rendezvous + 4 * (size_t)s;
+            const int mine = left ? 0 : 1;
+            if (!parked) {
+                __stcg(slot + 2 * mine, make_float4(c.lox, c.hix, c.loy, c.hiy));
+                __stcg(slot + 2 * mine + 1, make_float4(c.loz, c.hiz, __int_as_float(left ? c.F : c.L), __int_as_float(left ? c.dL : c.dR)));
+                __threadfence();
+            }
+            if ((atomicAdd(&S.flags[s], 1u) & 1u) == 0u) break;      // first to arrive: the sibling finishes the node
+            __threadfence();
+            if (tree_merge(S, c, left, s, __ldcg(slot + 2 * (mine ^ 1)), __ldcg(slot + 2 * (mine ^ 1) + 1))) break;
+            left = c.dR > c.dL;
+            s = left ? c.L : c.F - 1;
+            parked = false;
+        }
+    }
+}
+
+// ---- (4b) fit without the climb: range queries over the block's leaf boxes --------------------------------
+// k_fit's climb is a chain of dependent L2 round trips (ncu: 29 % issue, 46 % DRAM).  A Karras node whose leaf range
+// lies inside one 256-leaf block (99 % of the nodes; their index lies in the block too) does not need its children
+// to "arrive": its child boxes are min / max over contiguous runs of the block's leaf boxes.  Each CTA therefore
+//   1. writes its 256 leaf records and puts the leaf boxes into shared memory,
+//   2. builds a sparse table over them (windows of 1, 2, 4 .. 64 leaves: 7 levels x 256 x 24 B = 42 KB),
+//   3. lets thread t handle internal node (block base + t): two range queries (2-4 table reads each, min / max
+//      tolerate overlapping windows) give both child boxes, written as three coalesced 16-byte stores,
+//   4. and only the roots of the maximal block-local subtrees (and leaves hanging directly off a straddling node)
+//      continue upwards through the global arrival counters, as k_fit does.
+// Same boxes bit for bit (min / max are exact and order-free).
+constexpr int kRmqLevels = 7;
 
 // Continues upwards from a child of a node that straddles 256-leaf blocks (every ancestor straddles too).
 __device__ __forceinline__ void climb_global(const SceneDev &S, int up, Box6 bx)

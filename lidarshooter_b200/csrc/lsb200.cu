@@ -84,17 +84,17 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0, opt_watertight = 0, opt_intensity = 0;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_fused_tree = 1, opt_lane_refill = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0, opt_watertight = 0, opt_intensity = 0;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
     bool topology_dirty = true, committed = false, top_valid = false;
-    int built_leaf = 0, built_top = 0, built_watertight = 0;
+    int built_leaf = 0, built_top = 0, built_watertight = 0, built_fused_tree = 0;
     std::vector<Sensor> sensors;
     bool sensors_dirty = true;
     // scene arrays
     DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
-        d_nodes, d_node_parent, d_leaf_parent, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts, d_sup_lists, d_sup_counts, d_tile_iv, d_sup_iv;
+        d_nodes, d_node_parent, d_leaf_parent, d_rendezvous, d_tree_count, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts, d_sup_lists, d_sup_counts, d_tile_iv, d_sup_iv;
     std::vector<GeomDesc> h_geoms;
     std::vector<SensorDev> h_sensors, h_sensors_b;
     cudaStream_t copy_stream = nullptr;
@@ -321,7 +321,7 @@ int lsb200_destroy(lsb200_ctx *c)
         for (auto &kv : c->geoms) { kv.second.verts.release(); kv.second.elems.release(); }
         for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.t_b.release(); s.blocks.release(); s.inten.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
-                          &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent,
+                          &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent, &c->d_rendezvous, &c->d_tree_count,
                           &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts, &c->d_sup_lists, &c->d_sup_counts, &c->d_tile_iv, &c->d_sup_iv};
         for (auto *b : bufs) b->release();
         if (c->h_count) cudaFreeHost(c->h_count);
@@ -376,6 +376,8 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_TILE_MIN_UNITS: if (value < 0) break; c->opt_tile_min_units = value; return LSB200_OK;
     case LSB200_OPT_TILE_VISITS: if (value < 0 || value > 4096) break; c->opt_tile_visits = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
+    case LSB200_OPT_LANE_REFILL: if (value < 0 || value > 15) break; c->opt_lane_refill = value; return LSB200_OK;
+    case LSB200_OPT_FUSED_TREE: c->opt_fused_tree = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TILE_WIDTH: {
         int w = 0;
         while (w <= 5 && (1 << w) != value) ++w;
@@ -602,7 +604,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
     const bool rebuild = (mode == LSB200_COMMIT_REBUILD) || c->topology_dirty;
     cudaStream_t st = c->stream;
     c->n_verts = (int)nv; c->n_tris = (int)nt;
-    if (rebuild) { c->built_leaf = c->opt_leaf; c->built_top = c->opt_top; }
+    if (rebuild) { c->built_leaf = c->opt_leaf; c->built_top = c->opt_top; c->built_fused_tree = (c->opt_fused_tree && !c->opt_fit_rmq && nt > 1) ? 1 : 0; }
     c->built_watertight = c->opt_watertight;        // the leaf records are rewritten by every commit, rebuild or refit
 
     // geometry descriptor table (small pageable copy: staged by the runtime before the call returns)
@@ -637,6 +639,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
         if (!small) LSB_CU(c, c->d_sort_scratch.reserve(rsort::scratch_words(nt) * 4, st));
         LSB_CU(c, c->d_nodes.reserve(((size_t)c->built_top + T) * 64, st));
         LSB_CU(c, c->d_node_parent.reserve(T * 4, st)); LSB_CU(c, c->d_leaf_parent.reserve(T * 4, st));
+        if (!small && c->built_fused_tree) { LSB_CU(c, c->d_rendezvous.reserve(T * 64, st)); LSB_CU(c, c->d_tree_count.reserve(16, st)); }
         LSB_CU(c, c->d_flags.reserve(T * 4, st, false, true));
     }
     SceneDev S = scene_dev(c);
@@ -711,12 +714,23 @@ static int commit_locked(lsb200_ctx *c, int mode)
         count_launch(c, rsort::sort_pairs(S.keys, S.vals, c->d_keys_tmp.as<uint32_t>(), c->d_vals_tmp.as<uint32_t>(), nt,
                                           c->d_sort_scratch.as<uint32_t>(), st));
         mark();
-        if (nt > 1) k_hierarchy<<<(unsigned)((nt - 1 + 255) / 256), 256, 0, st>>>(S, S.keys);
-        else k_single_leaf_root<<<1, 1, 0, st>>>(S);
-        count_launch(c);
+        if (!c->built_fused_tree) {
+            if (nt > 1) k_hierarchy<<<(unsigned)((nt - 1 + 255) / 256), 256, 0, st>>>(S, S.keys);
+            else k_single_leaf_root<<<1, 1, 0, st>>>(S);
+            count_launch(c);
+        }
         mark();
     }
-    // (5) leaf records + bottom-up boxes
+    // (5) leaf records + bottom-up boxes; with the fused tree pass (k_tree, the default) the hierarchy comes out of the same launch
+    if (c->built_fused_tree) {
+        // phase 2's work list reuses the (otherwise idle) leaf-parent array; its counter is the first word of d_tree_count
+        uint32_t *work = reinterpret_cast<uint32_t *>(c->d_leaf_parent.as<int32_t>()), *work_count = c->d_tree_count.as<uint32_t>();
+        LSB_CU(c, cudaMemsetAsync(work_count, 0, 4, st));
+        k_tree<<<(unsigned)((nt + kTreeBlock - 1) / kTreeBlock), kTreeBlock, 0, st>>>(S, S.keys, S.vals, c->d_rendezvous.as<float4>(), work, work_count);
+        // one thread per parked subtree (a block parks ~2 log2(kTreeBlock) of them at most in practice; grid-stride beyond that)
+        k_tree_top<<<(unsigned)std::max<int64_t>(kSmCount, ((nt + kTreeBlock - 1) / kTreeBlock) * 16 / 128), 128, 0, st>>>(S, c->d_rendezvous.as<float4>(), work, work_count);
+        count_launch(c);
+    } else
 #ifdef LSB_LAB
     if (c->opt_fit_rmq) {
         k_fit_rmq<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, sizeof(RmqTable), st>>>(S, S.vals);
@@ -1017,6 +1031,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         const int cap = c->opt_tile_entries;
         const int max_visits = c->opt_tile_visits > 0 ? c->opt_tile_visits : (16 * cap) / 5;
         P.tile_cap = cap;
+        P.refill = c->opt_lane_refill;
         const bool stale = c->tile_commit_epoch != c->commit_epoch || c->tile_sensors_epoch != c->sensors_epoch || c->tile_first != first ||
                            c->tile_count != count || c->tile_cap != cap || c->tile_visits != max_visits || c->tile_units_id != c->units_build_id;
         if (stale || c->opt_stats) {
@@ -1623,7 +1638,7 @@ int lsb200_clone_scene(lsb200_ctx *src, int cuda_device, lsb200_ctx **out)
     dst->opt_morton_layout = src->opt_morton_layout; dst->opt_morton_aspect = src->opt_morton_aspect; dst->opt_chain = src->opt_chain;
     dst->opt_tile_w_log2 = src->opt_tile_w_log2; dst->opt_small_build = src->opt_small_build; dst->opt_tile_entries = src->opt_tile_entries;
     dst->opt_tile_visits = src->opt_tile_visits; dst->opt_tile_min_units = src->opt_tile_min_units;
-    dst->opt_watertight = src->opt_watertight; dst->opt_intensity = src->opt_intensity;
+    dst->opt_watertight = src->opt_watertight; dst->opt_intensity = src->opt_intensity; dst->opt_fused_tree = src->opt_fused_tree; dst->opt_lane_refill = src->opt_lane_refill;
     dst->log_fn = src->log_fn; dst->log_user = src->log_user;
     for (size_t i = 0; i < src->sensors.size(); ++i) {
         const Sensor &s = src->sensors[i];

@@ -65,6 +65,8 @@ struct TraceParams {
     uint8_t *sup_counts;          // [supertile] entries, or kTileFallback
     float4 *tile_iv;              // [queue slot][2] direction interval of the tile: (dlo.xyz, class), (dhi.xyz, max |origin|)
     float4 *sup_iv;               // [supertile][2] same for the supertiles.  Both depend on the sensor tables / poses only.
+    int refill;                   // lane refill (run_phase_refill) per group of queues: bit 0 sign-mixed, 1 upward octants, 2 heavy fronts of
+                                  // the downward octants, 3 their light remainders (LSB200_OPT_LANE_REFILL)
 };
 constexpr int kMaxTileEntries = 16;
 constexpr int kTileFallback = 0xFF;
@@ -944,6 +946,243 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
     flush_append(P, pend, s_pts, lane);
 }
 
+// ---- lane refill (ray compaction) ---------------------------------------------------------------------------
+// run_phase hands a warp one 32-ray unit at a time: a lane whose ray ends early waits for the slowest ray of its
+// tile, and the heavy units (grazing rays: 10 - 300 node visits, next to rays that stop at the first wall) are where
+// the warp runs with a handful of live lanes (ncu: 22.9 of 32 threads per instruction over the launch).  Here the
+// RAY is the unit of work inside a warp: the traversal of a lane is a resumable state machine that runs for a
+// quantum of steps; after every quantum the warp reconverges, free lanes are counted with a ballot and the next
+// rays of the feeding unit are dealt to them by rank (popc of the free mask below the lane) -- the reference's
+// analogue is the per-packet loop of SRC/EmbreeTracer.cpp:297-367, which has the same tail per 16-ray packet.
+// The rays in flight may belong to up to kRing different units: a unit's tile list stays in its slot of the warp's
+// shared-memory ring until the last of its rays has ended (ballot over the slot tags), the next unit's descriptor
+// and list are prefetched into a free slot with cp.async while the current one is being dealt out.  Hits are
+// appended per finishing group (match.any on the sensor, one atomic per sensor and round).  Per-ray arithmetic,
+// culling rules and result stores are those of trace_ray_lz / process_unit: same t, same triangle id.
+#ifndef LSB_REFILL_RING
+#define LSB_REFILL_RING 4
+#endif
+#ifndef LSB_REFILL_QUANTUM
+#define LSB_REFILL_QUANTUM 32
+#endif
+constexpr int kRing = LSB_REFILL_RING;              // unit slots per warp (<= 4: the slot travels in two bits of the lane's tag)
+constexpr int kRefillQuantum = LSB_REFILL_QUANTUM;  // traversal steps (list tests + node visits + leaf tests) between two refills
+
+template <int OCT, bool WT>
+__device__ __forceinline__ void run_phase_refill(const TraceParams &P, float smax, unsigned lane, float4 *s_ring, int4 *s_ud,
+                                                 int2 *s_stack, int part)
+{
+    int begin = 0;
+#pragma unroll
+    for (int o = 0; o < OCT; ++o) begin += (int)__ldg(P.oct_hist + o);
+    const int count = (int)__ldg(P.oct_hist + OCT);
+    if (count == 0) return;
+    constexpr int kBuf = 2 * kMaxTileEntries;                     // float4 per ring slot
+    const int n_front = LSB_HEAVY_FIRST ? min(count, (int)__ldg(P.oct_hist + 16 + OCT)) : (int)(((long long)count * 3) / 8);
+    const int lo = part == 2 ? n_front : 0, hi = part == 1 ? n_front : count;
+    if (lo >= hi) return;
+    uint32_t *ctr = &P.work[(part == 2 ? 11 : 2) + OCT];
+    auto ticket = [&]() -> int { return lane == 0 ? lo + (int)atomicAdd(ctr, 1u) : 0; };
+    // descriptor (+ list size in .w) and list of queue entry k into ring slot `slot`
+    auto fetch = [&](int k, int slot) {
+        if (lane == 0) {
+            int4 ud = __ldg(P.unit_list + begin + k);
+            ud.w = (int)__ldg(P.tile_counts + begin + k);
+            s_ud[slot] = ud;
+        }
+        if ((int)lane < 2 * P.tile_cap) cp_async16(s_ring + slot * kBuf + lane, P.tile_lists + (size_t)(begin + k) * (2 * P.tile_cap) + lane);
+        cp_async_commit();
+    };
+    constexpr int kDone = 0x7fffffff;        // lane state in `cur`: nothing in hand (take the next list entry)
+    constexpr int kFinished = 0x7ffffffe;    //                      ray ended, results not yet stored
+    constexpr int kIdle = 0x7ffffffd;        //                      no ray
+    constexpr unsigned kNodeLimit = 0x7ffffff0u;   // cur < kNodeLimit (unsigned): inner node; negative: leaf reference
+    constexpr int kOvf = 1 << 20;            // depth-guard sentinel in sp (see trace_ray_lz)
+#if LSB_NODE_EVICT_LAST
+    const uint64_t pol = l2_policy_evict_last();
+#endif
+    // per-lane ray state
+    Ray r{0.f, 0.f, 0.f, 0.f, 0.f, 1.f};
+    float ix = 0.f, iy = 0.f, iz = 0.f, ax = 0.f, ay = 0.f, az = 0.f, bx = 0.f, by = 0.f, bz = 0.f;
+    float best = INFINITY, far_lim = INFINITY;
+    int bi = -1, cur = kIdle, sp = 0, left = 0, tag = 0;     // tag = ring slot | ray of the unit << 2
+    int eo = 0;                               // next list entry: float4 index into the warp's ring
+    int2 stack[kStackSize];
+    auto push = [&](int2 v) {
+        const int d = sp & (kOvf - 1);
+        if (d < LSB_SMEM_STACK) s_stack[d * kTraceThreads] = v;
+        else if (d < kStackSize) stack[d] = v;
+        else { sp |= kOvf; return; }
+        ++sp;
+    };
+    auto pop = [&]() -> int2 { --sp; const int d = sp & (kOvf - 1); return d < LSB_SMEM_STACK ? s_stack[d * kTraceThreads] : stack[d]; };
+    auto pop_next = [&]() {                  // next deferred child that can still hold a closer hit, else kDone
+        cur = kDone;
+        while ((sp & (kOvf - 1)) > 0) {
+            const int2 t = pop();
+            if (__int_as_float(t.y) <= far_lim * 1.0000005f) { cur = t.x; break; }
+        }
+    };
+
+    // warp-uniform queue / ring state
+    int feed = -1, feed_next = 32;           // slot being dealt out, rays already dealt
+    int load = -1;                           // slot being prefetched
+    bool more = true;                        // the queue may hold further units
+    int k0 = __shfl_sync(0xffffffffu, ticket(), 0);
+    if (k0 >= hi) return;
+    int raw_next = ticket();
+    fetch(k0, 0);
+    load = 0;
+    while (true) {
+        unsigned idle = __ballot_sync(0xffffffffu, cur == kIdle);
+        // prefetch the next unit into a free slot (not the feeding one, no ray of it in flight)
+        if (load < 0 && more) {
+            int slot = -1;
+#pragma unroll
+            for (int k = 0; k < kRing; ++k) {
+                const unsigned inflight = __ballot_sync(0xffffffffu, cur != kIdle && (tag & 3) == k);
+                if (slot < 0 && (k != feed || feed_next >= 32) && inflight == 0u) slot = k;
+            }
+            if (slot >= 0) {
+                const int k_next = __shfl_sync(0xffffffffu, raw_next, 0);
+                if (k_next < hi) { __syncwarp(); fetch(k_next, slot); load = slot; raw_next = ticket(); }
+                else more = false;
+            }
+        }
+        // deal rays to the free lanes
+        while (idle != 0u) {
+            if (feed_next >= 32) {
+                if (load < 0) break;                               // nothing prefetched: ring full or queue exhausted
+                cp_async_wait<0>();
+                __syncwarp();
+                feed = load; load = -1; feed_next = 0;
+                if (s_ud[feed].w == kTileFallback) {
+                    // no tile list for this unit (its pyramid could not be bounded): drained warp, classic path from the origin chain
+                    if (idle != 0xffffffffu) { load = feed; feed = -1; feed_next = 32; break; }
+                    process_unit<6, OCT, false, WT>(P, nullptr, 0, smax, s_ud[feed], lane, -1, nullptr, nullptr, nullptr, s_stack);
+                    feed_next = 32; feed = -1;
+                    continue;
+                }
+            }
+            const int4 ud = s_ud[feed];
+            const unsigned rank = __popc(idle & lanemask_lt());
+            const int n_avail = 32 - feed_next;
+            if (((idle >> lane) & 1u) && (int)rank < n_avail) {
+                const int j = feed_next + (int)rank;
+                const SensorDev &S = P.sensors[ud.x];
+                int v, h;
+                const bool valid = unit_lane_ray(S, ud, P.tile_w_log2, (unsigned)j, v, h);
+                const bool fired = valid && (S.az_mask == nullptr || __ldg(S.az_mask + h) != 0);
+                if (valid && (!fired || ud.w == 0)) {             // outside the azimuth window, or the tile's pyramid reaches nothing
+                    __stcs(S.t_out + v * S.H + h, INFINITY); __stcs(S.tri_out + v * S.H + h, -1);
+                } else if (fired) {
+                    float dsx, dsy, dsz, omax;
+                    make_ray(S, P.world_frame, v, h, r, dsx, dsy, dsz, omax);
+                    const float eps = 8e-6f * (smax + omax) + 1e-30f;
+                    const float tiny = 1e-30f;
+                    ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
+                    iy = 1.0f / (fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
+                    iz = 1.0f / (fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
+                    ax = -(r.ox + eps) * ix; ay = -(r.oy + eps) * iy; az = -(r.oz + eps) * iz;
+                    bx = -(r.ox - eps) * ix; by = -(r.oy - eps) * iy; bz = -(r.oz - eps) * iz;
+                    best = INFINITY; far_lim = INFINITY; bi = -1; sp = 0;
+                    left = ud.w; eo = feed * kBuf;
+                    tag = feed | (j << 2);
+                    cur = kDone;
+                }
+            }
+            feed_next += min(n_avail, (int)__popc(idle));
+            idle = __ballot_sync(0xffffffffu, cur == kIdle);      // lanes whose ray needed no traversal are served again
+        }
+        if (idle == 0xffffffffu && feed_next >= 32 && load < 0 && !more) break;
+
+        // one quantum of traversal per lane (trace_ray_lz, resumable)
+        if (cur != kIdle) {
+            int budget = kRefillQuantum;
+            while (budget > 0) {
+                if (cur == kDone) {                  // nothing in hand: next list entry the ray enters
+                    while (left > 0) {
+                        const float4 e0 = s_ring[eo], e1 = s_ring[eo + 1];
+                        eo += 2; --left; --budget;
+                        float n, f;
+                        slab_nf<OCT>(fmaf(e0.x, ix, ax), fmaf(e0.y, ix, bx), fmaf(e0.z, iy, ay), fmaf(e0.w, iy, by),
+                                     fmaf(e1.x, iz, az), fmaf(e1.y, iz, bz), far_lim, n, f);
+                        if (n <= f) { cur = __float_as_int(e1.z); break; }
+                    }
+                    if (cur == kDone) { cur = kFinished; break; }
+                }
+                while ((unsigned)cur < kNodeLimit && budget > 0) {
+                    const float4 *nd = P.nodes + 4 * (size_t)cur;
+#if LSB_NODE_EVICT_LAST
+                    const float4 q0 = ldg_f4_hint(nd, pol), q1 = ldg_f4_hint(nd + 1, pol), q2 = ldg_f4_hint(nd + 2, pol);
+                    const float2 q3 = ldg_f2_hint(reinterpret_cast<const float2 *>(nd + 3), pol);
+#else
+                    const float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2);
+                    const float2 q3 = __ldg(reinterpret_cast<const float2 *>(nd + 3));
+#endif
+                    --budget;
+                    float n0, f0, n1, f1;
+                    slab_nf<OCT>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
+                                 fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
+                    slab_nf<OCT>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
+                                 fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
+                    const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
+                    const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+                    if (hit0 && hit1) {
+                        const bool swap = n1 < n0;
+                        cur = swap ? c1 : c0;
+                        push(make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1)));
+                    } else if (hit0) {
+                        cur = c0;
+                    } else if (hit1) {
+                        cur = c1;
+                    } else {
+                        pop_next();
+                    }
+                }
+                if (cur < 0) {
+                    test_leaf<WT>(P, cur, r, best, bi);
+                    far_lim = best * 1.0000005f;
+                    --budget;
+                    pop_next();
+                }
+            }
+        }
+        __syncwarp();
+        // rays that ended in this quantum: results, hit append, lane free again
+        const bool fin = cur == kFinished;
+        int v = 0, h = 0, si = 0;
+        if (fin) {
+            const int4 ud = s_ud[tag & 3];
+            si = ud.x;
+            const SensorDev &S = P.sensors[si];
+            unit_lane_ray(S, ud, P.tile_w_log2, (unsigned)(tag >> 2), v, h);
+            if (sp & kOvf) brute_ray_cold<WT>(P.tris, P.leaf_ids, P.n_tris, r, best, bi);     // depth guard tripped
+            if (!(best <= S.max_range)) { best = INFINITY; bi = -1; }                          // detection radius
+            __stcs(S.t_out + v * S.H + h, best);
+            __stcs(S.tri_out + v * S.H + h, bi);
+        }
+        if (!(P.flags & (1u | 8u))) {                // neither ORDERED nor NO_POINTS: warp-aggregated atomic append, per sensor
+            const bool hit = fin && bi >= 0;
+            const unsigned hm = __ballot_sync(0xffffffffu, hit);
+            if (hit) {
+                const SensorDev &S = P.sensors[si];
+                const unsigned m = __match_any_sync(hm, si);
+                const int leader = __ffs(m) - 1;
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(S.count, (uint32_t)__popc(m));
+                base = __shfl_sync(m, base, leader);
+                Ray r2; float dsx, dsy, dsz, omax, x, y, z;
+                make_ray(S, P.world_frame, v, h, r2, dsx, dsy, dsz, omax);
+                hit_point(S, P.flags, best, dsx, dsy, dsz, x, y, z);
+                store_point(S.points, base + __popc(m & lanemask_lt()), P.flags, x, y, z, (P.flags & 2u) ? 0 : v);
+            }
+        }
+        if (fin) cur = kIdle;
+    }
+    cp_async_wait<0>();
+}
+
 // MODE 0: persistent CTAs, nodes through L1/L2, units pre-sorted by ray octant (k_classify_units / k_scatter_units)
 //         and drained octant by octant with a sign-specialised slab test -- every CTA runs the same small loop at
 //         a time, so the eight specialisations do not compete for the instruction cache
@@ -983,32 +1222,47 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
 
     const unsigned lane = lane_id();
-    __shared__ float4 s_lists[(MODE >= 6) ? kTraceThreads / 32 : 1][(MODE >= 6) ? 4 * kMaxTileEntries : 1];      // 2 buffers per warp
+    __shared__ float4 s_lists[(MODE >= 6) ? kTraceThreads / 32 : 1][(MODE >= 6) ? kRing * 2 * kMaxTileEntries : 1];      // per warp: 2 list buffers (run_phase) / a ring of kRing (run_phase_refill)
     float4 *s_list = s_lists[(MODE >= 6) ? (threadIdx.x >> 5) : 0];
+    __shared__ int4 s_uds[(MODE == 6) ? kTraceThreads / 32 : 1][kRing];
+    int4 *s_ud = s_uds[(MODE == 6) ? (threadIdx.x >> 5) : 0];
     __shared__ float4 s_points[(MODE >= 6 && LSB_DEFER_APPEND) ? kTraceThreads : 1];                  // parked hit points (deferred append)
     float4 *s_pts = s_points + ((MODE >= 6 && LSB_DEFER_APPEND) ? (threadIdx.x & ~31u) : 0u);
     int2 *s_stack = (MODE == 6 && LSB_SMEM_STACK) ? reinterpret_cast<int2 *>(smem_raw) + threadIdx.x : nullptr;
+    // a queue (or its heavy front / light remainder) is drained unit by unit (run_phase) or ray by ray with lane refill
+    // (run_phase_refill: MODE 6 with tile lists, per group of queues as P.refill says)
+#define LSB_PHASE(OCTV, PART) do { \
+        bool refilled_ = false; \
+        if constexpr (MODE == 6 && !STATS && LSB_LAZY_LIST != 0 && ((OCTV) < 8 || LSB_MIXED_TILE_LISTS != 0)) { \
+            const int group_ = (OCTV) == 8 ? 0 : ((OCTV) < 4 ? 1 : ((PART) == 2 ? 3 : 2)); \
+            if (P.tile_counts != nullptr && ((P.refill >> group_) & 1)) { \
+                run_phase_refill<OCTV, WT>(P, smax, lane, s_list, s_ud, s_stack, PART); \
+                refilled_ = true; \
+            } \
+        } \
+        if (!refilled_) run_phase<MODE, OCTV, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, PART); \
+    } while (0)
     if (MODE == 0 || MODE == 6 || MODE == 7) {
         // Order of the queues.  The kernel ends when its last unit ends, and a few units run ~100 x the median (long grazing
         // rays, design log section 15), so the launch must END with light units only.  k_scatter_units puts the heavy units
         // (a ray within ~4 degrees of the horizon or above it) at the front of every queue; the heavy fronts of the downward
         // octants (4..7) are drained early, together with the sign-mixed and the upward queues, and the light remainders
         // (steep rays that hit the ground nearby, ~10 us a unit) make the tail: 1.67 -> 1.53 ms for the stage.
-        if (LSB_PHASE_ORDER != 2) run_phase<MODE, 8, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
+        if (LSB_PHASE_ORDER != 2) LSB_PHASE(8, 0);
         if (MODE == 6 && LSB_SPLIT_DOWNWARD && LSB_PHASE_ORDER == 0) {
-            run_phase<MODE, 4, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
-            run_phase<MODE, 6, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            LSB_PHASE(4, 1); LSB_PHASE(5, 1);
+            LSB_PHASE(6, 1); LSB_PHASE(7, 1);
         }
-        run_phase<MODE, 0, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 1, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
-        run_phase<MODE, 2, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack); run_phase<MODE, 3, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
-        if (LSB_PHASE_ORDER == 2) run_phase<MODE, 8, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack);
+        LSB_PHASE(0, 0); LSB_PHASE(1, 0);
+        LSB_PHASE(2, 0); LSB_PHASE(3, 0);
+        if (LSB_PHASE_ORDER == 2) LSB_PHASE(8, 0);
         if (MODE == 6 && LSB_SPLIT_DOWNWARD && LSB_PHASE_ORDER >= 1) {
-            run_phase<MODE, 4, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 5, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
-            run_phase<MODE, 6, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1); run_phase<MODE, 7, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, 1);
+            LSB_PHASE(4, 1); LSB_PHASE(5, 1);
+            LSB_PHASE(6, 1); LSB_PHASE(7, 1);
         }
         const int rest = (MODE == 6 && LSB_SPLIT_DOWNWARD) ? 2 : 0;
-        run_phase<MODE, 4, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 5, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest);
-        run_phase<MODE, 6, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest); run_phase<MODE, 7, STATS, WT>(P, smax, lane, s_list, s_pts, s_stack, rest);
+        LSB_PHASE(4, rest); LSB_PHASE(5, rest);
+        LSB_PHASE(6, rest); LSB_PHASE(7, rest);
     } else if (MODE == 2) {
         const int unit = P.unit_lo + (int)(blockIdx.x * (kTraceThreads / 32) + (threadIdx.x >> 5));
         if (unit < P.n_units) process_unit<MODE, 8, STATS, WT>(P, s_top, n_top, smax, unit_descriptor(P.sensors, P.n_sensors, unit, P.tile_w_log2), lane);
@@ -1034,6 +1288,8 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
         }
     }
 }
+
+#undef LSB_PHASE
 
 // Heavy units first (LSB_HEAVY_FIRST): a unit with a ray at or above ~4 degrees below the horizon is "heavy" -- grazing rays
 // fly hundreds of metres along streets and over roofs and cost up to 100 x the median unit (design log, section 15).

@@ -347,3 +347,91 @@ def test_empty_scene_device_results_are_misses():
     assert rt.cudaMemcpy(C.c_void_p(tri.ctypes.data), dtri, C.c_size_t(4800 * 4), 2) == 0
     assert np.isinf(t).all() and (tri == -1).all()
     ctx.close()
+
+
+@pytest.mark.parametrize("leaf", [1, 2, 8])
+@pytest.mark.parametrize("n_tris", [2, 3, 255, 256, 257, 511, 513, 20000, 300001])
+def test_fused_tree_equals_pipeline(n_tris, leaf):
+    """k_tree (hierarchy + boxes in one bottom-up pass, Apetrei 2014 with Karras numbering; replaces rtcCommitScene,
+    SRC/EmbreeTracer.cpp:290-295) writes the SAME node array, leaf order and per-ray results as k_hierarchy + k_fit,
+    rebuild and refit, with many equal Morton codes (ties broken by index) and a ragged last block."""
+    rng = np.random.default_rng(11 * n_tris + leaf)
+    c = rng.uniform(-30, 30, (n_tris, 1, 3)).astype(np.float32)
+    c[: n_tris // 3] = c[0]                                  # a third of the centroids coincide
+    c[n_tris // 3: n_tris // 2, 0, 2] = 0.0                  # and a flat sheet (long common prefixes)
+    v = (c + rng.normal(0, 0.4, (n_tris, 3, 3)).astype(np.float32)).reshape(-1, 3)
+    tr = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
+    elev = np.linspace(50, -50, 16).astype(np.float32)
+    A2 = lso.affine_from_components([0.5, -0.25, 0.125], [0.1, -0.2, 0.3])
+    out = []
+    for fused in (1, 0):
+        ctx = capi.Context(0)
+        ctx.set_option(capi.OPT_SMALL_BUILD, 0)
+        ctx.set_option(capi.OPT_FUSED_TREE, fused)
+        ctx.set_option(capi.OPT_LEAF_SIZE, leaf)
+        ctx.set_sensor(elev, 0.0, 360.0, 64, (0.9, 0.1, -0.2, 0.3), (1.0, -2.0, 0.5))
+        assert ctx.add_geometry("soup", capi.GEOMETRY_TRIANGLE, v.shape[0], tr.shape[0]) >= 0
+        assert ctx.update_geometry("soup", v, tr, IDENT) == 0
+        res = []
+        for rep in range(2):                                 # twice: the global arrival counters are parity-based
+            assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
+            nodes, ids, root = ctx.debug_copy_bvh()
+            rc, t, tri = ctx.trace_raw()
+            res += [nodes.copy(), ids.copy(), root, t, tri]
+        assert ctx.update_transform("soup", A2) == 0
+        assert ctx.commit_scene(capi.COMMIT_REFIT) == 0 and ctx.stats().last_commit_was_rebuild == 0
+        nodes2, ids2, _ = ctx.debug_copy_bvh()
+        rc, t2, tri2 = ctx.trace_raw()
+        out.append(res + [nodes2.copy(), ids2.copy(), t2, tri2])
+        ctx.close()
+    a, b = out
+    for k, (x, y) in enumerate(zip(a, b)):
+        assert np.array_equal(np.atleast_1d(x).view(np.uint8), np.atleast_1d(y).view(np.uint8)), k
+    assert n_tris < 100 or (a[4] >= 0).sum() > 0
+
+
+@pytest.mark.parametrize("refill", [0, 15, 6])
+def test_lane_refill_small_city_vs_oracle_bvh(refill):
+    """Ray compaction inside the traversal (run_phase_refill: free lanes take the next rays of the queue by ballot +
+    rank, unit lists in a shared-memory ring; the reference's counterpart is the per-packet loop of
+    SRC/EmbreeTracer.cpp:297-367): per-ray t / triangle id bit-exact against the oracle's CPU BVH for every group of
+    queues, ragged tables (721 azimuth steps: tiles that fall off the table), a detection radius + azimuth window,
+    and the unordered warp-aggregated append delivers exactly the ordered cloud's points."""
+    meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
+    poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
+    elev, b, e, H = synth.lidar_table(30, 721)
+    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
+    ctx.set_option(capi.OPT_LANE_REFILL, refill)
+    for k, (q, t) in enumerate(poses):
+        ctx.set_sensor(elev, b, e, H, q, t, index=k)
+    for gi, (name, v, tr) in enumerate(meshes):
+        assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], tr.shape[0]) >= 0
+        assert ctx.update_geometry(name, v, tr, IDENT) == 0
+    assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0
+    s0 = lso.Sensor(elev, b, e, H, poses[0][0], poses[0][1])
+    verts, tris = lso.concat_scene(s0, [(v, tr, IDENT) for (_, v, tr) in meshes], mode=1)
+    bvh = lso.Bvh(verts, tris)
+    assert ctx.set_sensor_limits(60.0, 30.0, 170.0, index=1) == 0
+    assert ctx.trace_batch(0, len(poses), capi.TRACE_XYZI16) == 0            # unordered append
+    unordered = [ctx.fetch_points(k, capi.TRACE_XYZI16)[1].copy() for k in range(len(poses))]
+    raw = [ctx.trace_raw(k) for k in range(len(poses))]
+    assert ctx.trace_batch(0, len(poses), capi.TRACE_XYZI16 | capi.TRACE_ORDERED) == 0
+    for k, (q, t) in enumerate(poses):
+        s = lso.Sensor(elev, b, e, H, q, t)
+        t_ref, tri_ref = bvh.trace(s.T, lso.rotate_dirs(s.R, lso.ray_dirs(s.tables)))
+        if k == 1:
+            t_ref, tri_ref = lso.apply_limits(s, t_ref, tri_ref, 60.0, (30.0, 170.0))
+        rc, tt, tri = raw[k]
+        assert rc == 0 and np.array_equal(tri, tri_ref) and np.array_equal(tt, t_ref), k
+        rc, tt, tri = ctx.trace_raw(k)
+        assert rc == 0 and np.array_equal(tri, tri_ref) and np.array_equal(tt, t_ref), k
+        rc, ordered = ctx.fetch_points(k, capi.TRACE_XYZI16 | capi.TRACE_ORDERED)
+        assert rc == 0 and ordered.shape[0] == int((tri_ref >= 0).sum())
+        a = np.ascontiguousarray(unordered[k]).view(np.uint8).reshape(-1, 16)
+        o = np.ascontiguousarray(ordered).view(np.uint8).reshape(-1, 16)
+        assert a.shape == o.shape
+        key = lambda x: x[np.lexsort(x.T[::-1])]
+        assert np.array_equal(key(a), key(o)), k
+    bvh.close()
+    ctx.close()
