@@ -24,6 +24,7 @@
 #include "radix_sort.cuh"
 #include "build.cuh"
 #include "trace.cuh"
+#include <nvtx3/nvToolsExt.h>
 
 using namespace lsb;
 
@@ -645,7 +646,14 @@ static int commit_locked(lsb200_ctx *c, int mode)
     SceneDev S = scene_dev(c);
     const bool timing = c->opt_timing != 0;
     int evi = 0;
-    auto mark = [&]() { if (timing) cudaEventRecord(c->ev[evi++], st); };
+    // stage boundary: CUDA event (LSB200_OPT_STAGE_TIMING) + NVTX range of the stage that starts here (nullptr ends the last one)
+    struct NvtxScope { NvtxScope(const char *n) { nvtxRangePushA(n); } ~NvtxScope() { nvtxRangePop(); } } nvtx_commit("lsb200:commit");
+    struct NvtxStage { bool open = false; ~NvtxStage() { if (open) nvtxRangePop(); } } nvtx_stage;      // closed on every return path
+    auto mark = [&](const char *next_stage) {
+        if (timing) cudaEventRecord(c->ev[evi++], st);
+        if (nvtx_stage.open) { nvtxRangePop(); nvtx_stage.open = false; }
+        if (next_stage) { nvtxRangePushA(next_stage); nvtx_stage.open = true; }
+    };
 
     if (small) {
         SmallArgs args;
@@ -665,11 +673,11 @@ static int commit_locked(lsb200_ctx *c, int mode)
             for (size_t i = 0; i < ns; ++i)
                 for (int k = 0; k < 3; ++k) args.origins[i][k] = c->frame_mode == LSB200_FRAME_WORLD ? c->sensors[i].T[k] : 0.0f;
         }
-        mark();
+        mark("lsb200:build_small");
         // one cluster of kClusterCtas CTAs (__cluster_dims__ on the kernel)
         k_build_small<<<kClusterCtas, kSmallThreads, (size_t)nt * 4, st>>>(S, args, c->frame_mode == LSB200_FRAME_SENSOR, rebuild ? 1 : 0);
         count_launch(c);
-        mark();
+        mark(nullptr);
         c->top_valid = false;
         if (c->built_top > 0 && c->opt_traversal == 4) {
             k_top_level<<<1, 1024, (size_t)c->built_top * sizeof(int), st>>>(S, c->d_misc.as<int>());
@@ -701,25 +709,25 @@ static int commit_locked(lsb200_ctx *c, int mode)
     }
     LSB_CU(c, cudaMemsetAsync(S.bounds, 0xFF, 12, st));
     LSB_CU(c, cudaMemsetAsync(S.bounds + 3, 0x00, 12, st));
-    mark();
+    mark("lsb200:transform");
     k_transform<<<(unsigned)((nv + 255) / 256), 256, 0, st>>>(S, c->frame_mode == LSB200_FRAME_SENSOR, c->d_sensor_xf.as<float>());
     count_launch(c);
-    mark();
+    mark(rebuild ? "lsb200:morton" : "lsb200:tree");
     if (rebuild) {
         // (2) Morton codes  (3) radix sort  (4) Karras hierarchy
         k_morton_plan<<<1, 1, 0, st>>>(S);
         k_morton<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(S);
         count_launch(c, 2);
-        mark();
+        mark("lsb200:sort");
         count_launch(c, rsort::sort_pairs(S.keys, S.vals, c->d_keys_tmp.as<uint32_t>(), c->d_vals_tmp.as<uint32_t>(), nt,
                                           c->d_sort_scratch.as<uint32_t>(), st));
-        mark();
+        mark("lsb200:hierarchy");
         if (!c->built_fused_tree) {
             if (nt > 1) k_hierarchy<<<(unsigned)((nt - 1 + 255) / 256), 256, 0, st>>>(S, S.keys);
             else k_single_leaf_root<<<1, 1, 0, st>>>(S);
             count_launch(c);
         }
-        mark();
+        mark("lsb200:tree");
     }
     // (5) leaf records + bottom-up boxes; with the fused tree pass (k_tree, the default) the hierarchy comes out of the same launch
     if (c->built_fused_tree) {
@@ -740,7 +748,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
         k_fit<<<(unsigned)((nt + kFitBlock - 1) / kFitBlock), kFitBlock, 0, st>>>(S, S.vals);
     }
     count_launch(c);
-    mark();
+    mark("lsb200:toplevel");
     // (6) top-level block for the TMA-staged traversal
     c->top_valid = false;
     if (c->built_top > 0 && c->opt_traversal == 4) {       // only the TMA-staged variant reads the top block
@@ -748,7 +756,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
         count_launch(c);
         c->top_valid = true;
     }
-    mark();
+    mark(nullptr);
     LSB_CU(c, cudaGetLastError());
     c->stats.last_commit_was_rebuild = rebuild ? 1 : 0;
     if (timing) {
@@ -935,6 +943,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         return fail(c, LSB200_ERR_INVALID, "trace: sensor-frame contexts hold exactly one sensor (index 0)");
     DeviceGuard dg(c->device);
     cudaStream_t st = c->stream;
+    struct NvtxScope { NvtxScope(const char *n) { nvtxRangePushA(n); } ~NvtxScope() { nvtxRangePop(); } } nvtx_trace("lsb200:trace");
     if (flags & LSB200_TRACE_RANGE_IMAGE) flags |= LSB200_TRACE_NO_POINTS;     // the per-ray t array IS the output
     if (int rc = prepare_sensors(c, first, count, slot)) return rc;
     uint32_t *d_cnt = c->d_counts.as<uint32_t>() + (slot ? kMaxSensors : 0);

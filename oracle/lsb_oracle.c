@@ -179,6 +179,7 @@ LSO_API void lso_ray_tables(const float *elev_deg, int V, float az_begin, float 
 LSO_API void lso_ray_dirs(const float *sin_t, const float *cos_t, int V, const float *sin_p, const float *cos_p,
                           int H, float *dirs)
 {
+#pragma omp parallel for schedule(static) if ((int64_t)V * H > 65536)
     for (int v = 0; v < V; ++v)
         for (int h = 0; h < H; ++h) {
             float *d = dirs + 3 * ((size_t)v * H + h);
@@ -605,6 +606,149 @@ LSO_API void lso_trace_bvh(const lso_bvh *bvh, const float *orgs, int org_stride
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * PACKET form of lso_trace_bvh: 8 consecutive rays (AVX2) walk the BVH together with one shared stack, the way
+ * rtcIntersect16 walks a ray packet (SRC/EmbreeTracer.cpp:297-367, 472-480: the reference traces 16-ray
+ * packets).  It exists to give bench.py a CPU baseline closer to what Embree would do than the one-ray-at-a-time
+ * walk above.  Per lane the arithmetic is lso_intersect's, operation for operation (separate mul / add / sub,
+ * IEEE division, no FMA: the function is compiled for AVX2 without FMA), a node is entered when ANY lane's slab
+ * test passes (a superset of what each ray alone would enter) and closest hit = min (t, triangle id) does not
+ * depend on the order: results are bit-identical to lso_trace_bvh (tests/test_oracle.py).
+ * Default (Moeller-Trumbore) mode only; returns 0 without touching the outputs when AVX2 is missing or the
+ * watertight mode is on -- the caller then uses lso_trace_bvh.
+ * ---------------------------------------------------------------------------------------------- */
+#if defined(__x86_64__) && defined(__GNUC__)
+#include <immintrin.h>
+#define LSO_AVX2 __attribute__((target("avx2")))
+
+LSO_AVX2 static inline __m256 dot3_v(__m256 a0, __m256 a1, __m256 a2, __m256 b0, __m256 b1, __m256 b2)
+{
+    return _mm256_add_ps(_mm256_add_ps(_mm256_mul_ps(a0, b0), _mm256_mul_ps(a1, b1)), _mm256_mul_ps(a2, b2));
+}
+
+/* slab() for 8 rays: bit i of the result = ray i enters the box; tnear per lane in *tn */
+LSO_AVX2 static inline int slab_v(const lso_node *n, const __m256 *o, const __m256 *inv, __m256 tbest, __m256 *tn)
+{
+    const __m256 ninf = _mm256_set1_ps(-INFINITY), pinf = _mm256_set1_ps(INFINITY);
+    __m256 t0 = _mm256_setzero_ps(), t1 = tbest;
+    for (int k = 0; k < 3; ++k) {
+        const __m256 a = _mm256_mul_ps(_mm256_sub_ps(_mm256_set1_ps(n->lo[k]), o[k]), inv[k]);
+        const __m256 b = _mm256_mul_ps(_mm256_sub_ps(_mm256_set1_ps(n->hi[k]), o[k]), inv[k]);
+        __m256 mn = _mm256_min_ps(a, b);          /* a < b ? a : b  (b when unordered) */
+        __m256 mx = _mm256_max_ps(b, a);          /* a < b ? b : a  (a when unordered) */
+        mn = _mm256_blendv_ps(mn, ninf, _mm256_cmp_ps(mn, mn, _CMP_UNORD_Q));
+        mx = _mm256_blendv_ps(mx, pinf, _mm256_cmp_ps(mx, mx, _CMP_UNORD_Q));
+        t0 = _mm256_blendv_ps(t0, mn, _mm256_cmp_ps(mn, t0, _CMP_GT_OQ));
+        t1 = _mm256_blendv_ps(t1, mx, _mm256_cmp_ps(mx, t1, _CMP_LT_OQ));
+    }
+    *tn = t0;
+    return _mm256_movemask_ps(_mm256_cmp_ps(t0, _mm256_mul_ps(t1, _mm256_set1_ps(1.0000005f)), _CMP_LE_OQ));
+}
+
+LSO_AVX2 static void trace_packet8(const lso_bvh *bvh, const float *orgs, int org_stride, const float *dirs, int64_t r0, int cnt,
+                                   float *t_out, int32_t *tri_out)
+{
+    float tmp[6][8];
+    for (int l = 0; l < 8; ++l) {
+        const int64_t r = r0 + (l < cnt ? l : cnt - 1);          /* ragged tail: repeat the last ray */
+        const float *o = orgs + (size_t)org_stride * r, *d = dirs + 3 * r;
+        for (int k = 0; k < 3; ++k) { tmp[k][l] = o[k]; tmp[3 + k][l] = d[k]; }
+    }
+    __m256 o[3], d[3], inv[3];
+    for (int k = 0; k < 3; ++k) {
+        o[k] = _mm256_loadu_ps(tmp[k]); d[k] = _mm256_loadu_ps(tmp[3 + k]);
+        inv[k] = _mm256_div_ps(_mm256_set1_ps(1.0f), d[k]);
+    }
+    __m256 best = _mm256_set1_ps(INFINITY);
+    __m256i bi = _mm256_set1_epi32(-1);
+    const __m256 sign = _mm256_set1_ps(-0.0f), zero = _mm256_setzero_ps(), fmax = _mm256_set1_ps(FLT_MAX);
+    int32_t stack[128]; int sp = 0;
+    stack[sp++] = 0;
+    while (sp) {
+        const lso_node *n = &bvh->nodes[stack[--sp]];
+        __m256 tn;
+        if (!slab_v(n, o, inv, best, &tn)) continue;
+        for (;;) {
+            if (n->count) {
+                for (int32_t i = n->left; i < n->left + n->count; ++i) {
+                    const lso_tri *tri = &bvh->tris[i];
+                    float Ng[3];
+                    cross3(tri->e2, tri->e1, Ng);
+                    const __m256 C0 = _mm256_sub_ps(_mm256_set1_ps(tri->v0[0]), o[0]);
+                    const __m256 C1 = _mm256_sub_ps(_mm256_set1_ps(tri->v0[1]), o[1]);
+                    const __m256 C2 = _mm256_sub_ps(_mm256_set1_ps(tri->v0[2]), o[2]);
+                    const __m256 R0 = _mm256_sub_ps(_mm256_mul_ps(C1, d[2]), _mm256_mul_ps(C2, d[1]));
+                    const __m256 R1 = _mm256_sub_ps(_mm256_mul_ps(C2, d[0]), _mm256_mul_ps(C0, d[2]));
+                    const __m256 R2 = _mm256_sub_ps(_mm256_mul_ps(C0, d[1]), _mm256_mul_ps(C1, d[0]));
+                    const __m256 n0 = _mm256_set1_ps(Ng[0]), n1 = _mm256_set1_ps(Ng[1]), n2 = _mm256_set1_ps(Ng[2]);
+                    const __m256 den = dot3_v(n0, n1, n2, d[0], d[1], d[2]);
+                    const __m256 absDen = _mm256_andnot_ps(sign, den), sgn = _mm256_and_ps(sign, den);
+                    const __m256 U = _mm256_xor_ps(dot3_v(R0, R1, R2, _mm256_set1_ps(tri->e2[0]), _mm256_set1_ps(tri->e2[1]), _mm256_set1_ps(tri->e2[2])), sgn);
+                    const __m256 V = _mm256_xor_ps(dot3_v(R0, R1, R2, _mm256_set1_ps(tri->e1[0]), _mm256_set1_ps(tri->e1[1]), _mm256_set1_ps(tri->e1[2])), sgn);
+                    __m256 ok = _mm256_cmp_ps(den, zero, _CMP_NEQ_UQ);
+                    ok = _mm256_and_ps(ok, _mm256_cmp_ps(U, zero, _CMP_GE_OQ));
+                    ok = _mm256_and_ps(ok, _mm256_cmp_ps(V, zero, _CMP_GE_OQ));
+                    ok = _mm256_and_ps(ok, _mm256_cmp_ps(_mm256_add_ps(U, V), absDen, _CMP_LE_OQ));
+                    if (!_mm256_movemask_ps(ok)) continue;
+                    const __m256 T = _mm256_xor_ps(dot3_v(n0, n1, n2, C0, C1, C2), sgn);
+                    ok = _mm256_and_ps(ok, _mm256_cmp_ps(_mm256_mul_ps(absDen, zero), T, _CMP_LT_OQ));
+                    const __m256 t = _mm256_div_ps(T, absDen);
+                    ok = _mm256_and_ps(ok, _mm256_cmp_ps(t, fmax, _CMP_LE_OQ));
+                    const __m256i g = _mm256_set1_epi32(bvh->tri_ids[i]);
+                    const __m256 closer = _mm256_cmp_ps(t, best, _CMP_LT_OQ);
+                    const __m256 tie = _mm256_and_ps(_mm256_cmp_ps(t, best, _CMP_EQ_OQ), _mm256_castsi256_ps(_mm256_cmpgt_epi32(bi, g)));
+                    const __m256 take = _mm256_and_ps(ok, _mm256_or_ps(closer, tie));
+                    best = _mm256_blendv_ps(best, t, take);
+                    bi = _mm256_castps_si256(_mm256_blendv_ps(_mm256_castsi256_ps(bi), _mm256_castsi256_ps(g), take));
+                }
+                break;
+            }
+            const lso_node *l = &bvh->nodes[n->left], *r = l + 1;
+            __m256 tl, tr;
+            const int hl = slab_v(l, o, inv, best, &tl), hr = slab_v(r, o, inv, best, &tr);
+            if (hl && hr) {
+                /* near child = the one most of the lanes that enter both reach first */
+                const int both = hl & hr;
+                const int r_first = _mm256_movemask_ps(_mm256_cmp_ps(tr, tl, _CMP_LT_OQ)) & both;
+                if (2 * __builtin_popcount(r_first) > __builtin_popcount(both)) { const lso_node *x = l; l = r; r = x; }
+                if (sp < 127) stack[sp++] = (int32_t)(r - bvh->nodes);
+                n = l;
+            } else if (hl) n = l;
+            else if (hr) n = r;
+            else break;
+        }
+    }
+    float tb[8]; int32_t ib[8];
+    _mm256_storeu_ps(tb, best); _mm256_storeu_si256((__m256i *)ib, bi);
+    for (int l = 0; l < cnt; ++l) { t_out[r0 + l] = tb[l]; tri_out[r0 + l] = ib[l]; }
+}
+
+LSO_API int lso_trace_bvh_packet(const lso_bvh *bvh, const float *orgs, int org_stride, const float *dirs, int64_t nR,
+                                 float *t_out, int32_t *tri_out)
+{
+    if (g_watertight || !__builtin_cpu_supports("avx2")) return 0;
+    if (bvh->n_tris <= 0) {
+        for (int64_t r = 0; r < nR; ++r) { t_out[r] = INFINITY; tri_out[r] = -1; }
+        return 1;
+    }
+    const int64_t nP = (nR + 7) / 8;
+#pragma omp parallel for schedule(dynamic, 32)
+    for (int64_t p = 0; p < nP; ++p) {
+        const int64_t r0 = 8 * p;
+        const int cnt = (int)(nR - r0 < 8 ? nR - r0 : 8);
+        trace_packet8(bvh, orgs, org_stride, dirs, r0, cnt, t_out, tri_out);
+    }
+    return 1;
+}
+#else
+LSO_API int lso_trace_bvh_packet(const lso_bvh *bvh, const float *orgs, int org_stride, const float *dirs, int64_t nR,
+                                 float *t_out, int32_t *tri_out)
+{
+    (void)bvh; (void)orgs; (void)org_stride; (void)dirs; (void)nR; (void)t_out; (void)tri_out;
+    return 0;
+}
+#endif
+
+/* ------------------------------------------------------------------------------------------------
  * Float64 SECOND OPINION (not a restatement of anything in the reference): textbook Moeller-Trumbore 1997
  * in double precision on the ORIGINAL float32 vertices, closest hit = lexicographic min of (t, triangle id),
  * through the same CPU BVH (slabs evaluated in double on the padded boxes).  tests/ and bench.py run it over
@@ -745,19 +889,43 @@ LSO_API int lso_max_threads(void)
 LSO_API int64_t lso_pack_points(const float *dirs_s, const float *t, const int32_t *tri, int64_t nR, int H,
                                 int ring_mode, uint8_t *out)
 {
+    /* ray-id order, threaded: per-chunk hit counts, exclusive prefix, then every chunk writes its own range */
+    enum { MAXC = 256 };
+    int64_t counts[MAXC + 1];
+#ifdef _OPENMP
+    int nc = omp_get_max_threads();
+#else
+    int nc = 1;
+#endif
+    if (nc > MAXC) nc = MAXC;
+    if (nR < 65536) nc = 1;
+    const int64_t per = (nR + nc - 1) / nc;
+#pragma omp parallel for schedule(static, 1) if (nc > 1)
+    for (int c = 0; c < nc; ++c) {
+        const int64_t lo = c * per, hi = lo + per < nR ? lo + per : nR;
+        int64_t k = 0;
+        for (int64_t r = lo; r < hi; ++r) k += tri[r] >= 0;
+        counts[c] = k;
+    }
     int64_t n = 0;
-    for (int64_t r = 0; r < nR; ++r) {
-        if (tri[r] < 0) continue;
-        float rec[8];
-        memset(rec, 0, sizeof(rec));
-        rec[0] = t[r] * dirs_s[3 * r + 0];
-        rec[1] = t[r] * dirs_s[3 * r + 1];
-        rec[2] = t[r] * dirs_s[3 * r + 2];
-        rec[4] = 64.0f;
-        int32_t ring = ring_mode ? 0 : (int32_t)(r / H);
-        memcpy(&rec[5], &ring, 4);
-        memcpy(out + 32 * n, rec, 32);
-        ++n;
+    for (int c = 0; c < nc; ++c) { const int64_t k = counts[c]; counts[c] = n; n += k; }
+#pragma omp parallel for schedule(static, 1) if (nc > 1)
+    for (int c = 0; c < nc; ++c) {
+        const int64_t lo = c * per, hi = lo + per < nR ? lo + per : nR;
+        int64_t w = counts[c];
+        for (int64_t r = lo; r < hi; ++r) {
+            if (tri[r] < 0) continue;
+            float rec[8];
+            memset(rec, 0, sizeof(rec));
+            rec[0] = t[r] * dirs_s[3 * r + 0];
+            rec[1] = t[r] * dirs_s[3 * r + 1];
+            rec[2] = t[r] * dirs_s[3 * r + 2];
+            rec[4] = 64.0f;
+            int32_t ring = ring_mode ? 0 : (int32_t)(r / H);
+            memcpy(&rec[5], &ring, 4);
+            memcpy(out + 32 * w, rec, 32);
+            ++w;
+        }
     }
     return n;
 }

@@ -56,6 +56,8 @@ def lib():
         L.lso_bvh_node_count.argtypes = [C.c_void_p]
         L.lso_bvh_node_count.restype = C.c_int64
         L.lso_trace_bvh.argtypes = [C.c_void_p, f32p, C.c_int, f32p, C.c_int64, f32p, i32p]
+        L.lso_trace_bvh_packet.argtypes = [C.c_void_p, f32p, C.c_int, f32p, C.c_int64, f32p, i32p]
+        L.lso_trace_bvh_packet.restype = C.c_int
         f64p = C.POINTER(C.c_double)
         L.lso_trace_bvh_f64.argtypes = [C.c_void_p, f32p, u32p, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
         L.lso_trace_brute_f64.argtypes = [f32p, u32p, C.c_int64, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
@@ -219,6 +221,17 @@ class Bvh:
         lib().lso_trace_bvh(self._h, _p(o, C.c_float), stride, _p(dirs, C.c_float), nR, _p(t, C.c_float),
                             _p(tri, C.c_int32))
         return t, tri
+
+    def trace_packet(self, orgs, dirs):
+        """8-ray AVX2 packets through the same BVH (the CPU baseline closer to rtcIntersect16); bit-identical to trace().
+        Returns None when the host has no AVX2 or the watertight mode is on."""
+        dirs = _f32(dirs).reshape(-1, 3)
+        nR = dirs.shape[0]
+        o, stride = _origins(orgs, nR)
+        t, tri = np.empty(nR, np.float32), np.empty(nR, np.int32)
+        ok = lib().lso_trace_bvh_packet(self._h, _p(o, C.c_float), stride, _p(dirs, C.c_float), nR, _p(t, C.c_float),
+                                        _p(tri, C.c_int32))
+        return (t, tri) if ok else None
 
     def trace_f64(self, orgs, dirs):
         """Float64 second opinion (textbook Moeller-Trumbore in double on the original fp32 vertices)."""

@@ -211,3 +211,27 @@ def test_watertight_oracle_closes_leaks_on_edge_aimed_rays(meshes):
         r = lso.scan(s, ms)
     assert r["points"].shape[0] == 1781
     assert lso.lib().lso_get_watertight() == 0
+
+
+@pytest.mark.parametrize("n_rays", [1, 7, 8, 9, 4801])
+def test_packet_tracer_is_bit_identical_to_the_scalar_walk(n_rays):
+    """lso_trace_bvh_packet (8-ray AVX2 packets, the CPU baseline closer to rtcIntersect16 of
+    SRC/EmbreeTracer.cpp:472-480) returns exactly the scalar oracle's (t, triangle id): ragged tails, misses,
+    per-ray origins, ties between duplicated triangles."""
+    rng = np.random.default_rng(n_rays)
+    n_tris = 3000
+    c = rng.uniform(-20, 20, (n_tris, 1, 3)).astype(np.float32)
+    v = (c + rng.normal(0, 0.8, (n_tris, 3, 3)).astype(np.float32)).reshape(-1, 3)
+    tr = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
+    tr = np.concatenate([tr, tr[:200]])                       # duplicates: ties in t resolved by the smaller id
+    bvh = lso.Bvh(v, tr)
+    d = rng.normal(0, 1, (n_rays, 3)).astype(np.float32)
+    d[::5, 2] = 0.0                                           # axis-parallel components: 0 * inf in the slab test
+    for orgs in (np.zeros(3, np.float32), rng.uniform(-5, 5, (n_rays, 3)).astype(np.float32)):
+        t0, i0 = bvh.trace(orgs, d)
+        res = bvh.trace_packet(orgs, d)
+        if res is None:
+            pytest.skip("host without AVX2")
+        assert np.array_equal(res[1], i0) and np.array_equal(res[0].view(np.uint32), t0.view(np.uint32))
+    assert n_rays < 100 or (i0 >= 0).sum() > 100
+    bvh.close()
