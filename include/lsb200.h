@@ -187,7 +187,11 @@ LSB200_API int lsb200_get_geometry_id(const lsb200_ctx *ctx, const char *name);
  * MeshTransformer::transformIntoBuffer (SRC/MeshTransformer.cpp:142-205).  verts: n_vertices records of
  * vert_stride_bytes, xyz float32 at offset 0 (pcl::PCLPointCloud2 blob).  elems: n_elements x 3 (or x 4)
  * uint32; NULL = topology unchanged since the last call (the reference re-copies it every frame,
- * SRC/MeshTransformer.cpp:486-552).  affine3x4 row-major [L | t].  Host pointers are read before return. */
+ * SRC/MeshTransformer.cpp:486-552).  affine3x4 row-major [L | t].
+ * Buffer lifetime: pageable host memory is staged by the CUDA runtime before the call returns and may be reused at
+ * once.  PINNED host memory (lsb200_alloc_host, cudaHostAlloc) is copied by DMA on the context's stream: it must stay
+ * untouched until lsb200_synchronize(ctx) -- or any call that returns results to the host (lsb200_trace_scene,
+ * lsb200_fetch_points, lsb200_run_frames) -- has returned. */
 LSB200_API int lsb200_update_geometry(lsb200_ctx *ctx, const char *name, const void *verts, int vert_stride_bytes,
                                       const uint32_t *elems, const float affine3x4[12]);
 /* replaces updateGeometry(name, translation, eulerXYZ, mesh): A = T * Rz * Ry * Rx (SRC/MeshTransformer.cpp:467-477) */

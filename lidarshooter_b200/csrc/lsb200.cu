@@ -95,7 +95,7 @@ struct lsb200_ctx {
     bool sensors_dirty = true;
     // scene arrays
     DevBuf d_geoms, d_xverts, d_bounds, d_keys, d_vals, d_keys_tmp, d_vals_tmp, d_sort_scratch, d_tris, d_leaf_ids,
-        d_nodes, d_node_parent, d_leaf_parent, d_rendezvous, d_tree_count, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts, d_sup_lists, d_sup_counts, d_tile_iv, d_sup_iv;
+        d_nodes, d_node_parent, d_leaf_parent, d_rendezvous, d_tree_count, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts, d_sup_lists, d_sup_counts, d_tile_iv, d_sup_iv, d_unit_iv;
     std::vector<GeomDesc> h_geoms;
     std::vector<SensorDev> h_sensors, h_sensors_b;
     cudaStream_t copy_stream = nullptr;
@@ -323,7 +323,7 @@ int lsb200_destroy(lsb200_ctx *c)
         for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.t_b.release(); s.blocks.release(); s.inten.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent, &c->d_rendezvous, &c->d_tree_count,
-                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts, &c->d_sup_lists, &c->d_sup_counts, &c->d_tile_iv, &c->d_sup_iv};
+                          &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts, &c->d_sup_lists, &c->d_sup_counts, &c->d_tile_iv, &c->d_sup_iv, &c->d_unit_iv};
         for (auto *b : bufs) b->release();
         if (c->h_count) cudaFreeHost(c->h_count);
         for (auto &e : c->ev) if (e) cudaEventDestroy(e);
@@ -1018,14 +1018,25 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
             LSB_CU(c, c->d_oct_hist.reserve(64 * 4, st));        // [0, 9) class sizes, [16, 25) front cursors, [32, 41) back cursors
             LSB_CU(c, cudaMemsetAsync(c->d_oct_hist.p, 0, 64 * 4, st));
             const unsigned blocks = (unsigned)((n_units + 255) / 256);
+            // when this launch will use per-tile entry lists, the same pass over the rays also yields the tiles' direction
+            // intervals (k_tile_intervals' job): a moving sensor rebuilds queues and intervals every frame
+            const bool with_iv = mode >= 6 && c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units && !c->opt_super_tiles;
+            if (with_iv) {
+                LSB_CU(c, c->d_unit_iv.reserve((size_t)n_units * 2 * sizeof(float4), st));
+                LSB_CU(c, c->d_tile_iv.reserve((size_t)n_units * 2 * sizeof(float4), st));
+            }
             k_classify_units<<<blocks, 256, 0, st>>>(d_sens, P.n_sensors, unit_lo, unit_hi, wf, P.tile_w_log2, c->d_unit_oct.as<uint8_t>(),
-                                                     c->d_oct_hist.as<uint32_t>());
+                                                     c->d_oct_hist.as<uint32_t>(), with_iv ? c->d_unit_iv.as<float4>() : nullptr);
             k_scatter_units<<<blocks, 256, 0, st>>>(d_sens, P.n_sensors, unit_lo, unit_hi, P.tile_w_log2, c->d_unit_oct.as<uint8_t>(),
                                                     c->d_oct_hist.as<uint32_t>(), c->d_oct_hist.as<uint32_t>() + 16,
-                                                    c->d_unit_list.as<int4>());
+                                                    c->d_unit_list.as<int4>(), with_iv ? c->d_unit_iv.as<float4>() : nullptr,
+                                                    with_iv ? c->d_tile_iv.as<float4>() : nullptr);
             count_launch(c, 2);
             c->units_epoch = c->sensors_epoch; c->units_first = first; c->units_count = count; c->units_world = wf;
             ++c->units_build_id;
+            if (with_iv) {      // the intervals of this queue order are in place: k_tile_intervals is not needed
+                c->iv_sensors_epoch = c->sensors_epoch; c->iv_first = first; c->iv_count = count; c->iv_world = wf; c->iv_super = 0; c->iv_units_id = c->units_build_id;
+            }
         }
         P.unit_list = c->d_unit_list.as<int4>();
         P.oct_hist = c->d_oct_hist.as<uint32_t>();

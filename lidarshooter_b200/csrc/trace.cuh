@@ -1302,31 +1302,70 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
 constexpr float kHeavyDz = LSB_HEAVY_DZ;
 constexpr int kUnitHeavy = 0x80;
 
+// Rays (channels [v0, v0 + nv) x azimuth steps [h0, h0 + nh)) of sensor S, generated with the traversal's own
+// arithmetic: their direction interval and origin.  Returns the common sign class (bit k = component k negative) or
+// 8 when the signs differ.  The tables are read once per row / column.
+__device__ __forceinline__ int block_interval(const SensorDev &S, int world_frame, int v0, int nv, int h0, int nh,
+                                              float dlo[3], float dhi[3], float o3[3], float &omax)
+{
+    dlo[0] = dlo[1] = dlo[2] = INFINITY; dhi[0] = dhi[1] = dhi[2] = -INFINITY;
+    o3[0] = o3[1] = o3[2] = 0.0f; omax = 0.0f;
+    unsigned sign_or = 0u, sign_and = 7u;
+    const int v1 = min(v0 + nv, S.V), h1 = min(h0 + nh, S.H);
+    auto one = [&](float st, float ct, float sp_, float cp) {
+        Ray r; float x, y, z;
+        ray_from_tables(S, world_frame, st, ct, sp_, cp, r, x, y, z, omax);
+        o3[0] = r.ox; o3[1] = r.oy; o3[2] = r.oz;
+        dlo[0] = fminf(dlo[0], r.dx); dhi[0] = fmaxf(dhi[0], r.dx);
+        dlo[1] = fminf(dlo[1], r.dy); dhi[1] = fmaxf(dhi[1], r.dy);
+        dlo[2] = fminf(dlo[2], r.dz); dhi[2] = fmaxf(dhi[2], r.dz);
+        const unsigned o = (unsigned)ray_octant(r);
+        sign_or |= o; sign_and &= o;
+    };
+    if (nv <= 4) {
+        float stv[4], ctv[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int v = min(v0 + a, S.V - 1);
+            stv[a] = __ldg(S.sin_t + v); ctv[a] = __ldg(S.cos_t + v);
+        }
+        for (int h = h0; h < h1; ++h) {
+            const float sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
+#pragma unroll
+            for (int a = 0; a < 4; ++a) if (a < nv && v0 + a < S.V) one(stv[a], ctv[a], sp_, cp);
+        }
+    } else {
+        for (int v = v0; v < v1; ++v) {
+            const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v);
+            for (int h = h0; h < h1; ++h) one(st, ct, __ldg(S.sin_p + h), __ldg(S.cos_p + h));
+        }
+    }
+    return sign_or == sign_and ? (int)sign_or : 8;
+}
+
 // ---- octant classification of the 32-ray units (MODE 0) ----------------------------------------------------
 // unit_oct[u - unit_lo] = common octant of the unit's rays (bit k = sign bit of direction component k) or 8 when
 // they disagree; hist[o] = number of units per class.  Only depends on the sensor table: cached by the host.
 __global__ void __launch_bounds__(256) k_classify_units(const SensorDev *__restrict__ sensors, int n_sensors, int unit_lo,
                                                         int unit_hi, int world_frame, int tile_w_log2,
-                                                        uint8_t *__restrict__ unit_oct, uint32_t *__restrict__ hist)
+                                                        uint8_t *__restrict__ unit_oct, uint32_t *__restrict__ hist,
+                                                        float4 *__restrict__ unit_iv /* [unit][2] direction interval, or nullptr */)
 {
     const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
     int oct = -1;
-    bool heavy = false;
     if (u < unit_hi) {
+        // one pass over the unit's rays gives its octant class, its heavy flag AND its direction interval (what
+        // k_tile_intervals computes per queue slot): a moving sensor pays this every frame, so it is done once
         const int4 ud = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
         const SensorDev &S = sensors[ud.x];
-        for (unsigned l = 0; l < 32u; ++l) {
-            int v, h;
-            if (!unit_lane_ray(S, ud, tile_w_log2, l, v, h)) continue;
-            Ray r; float a, b, c, om;
-            make_ray(S, world_frame, v, h, r, a, b, c, om);
-            const int o = ray_octant(r);
-            oct = (oct < 0 || oct == o) ? o : 8;
-            if (LSB_HEAVY_FIRST) heavy = heavy || r.dz > kHeavyDz;
-            else if (oct == 8) break;
-        }
-        if (oct < 0) oct = 8;
+        float dlo[3], dhi[3], o3[3], omax;
+        oct = block_interval(S, world_frame, ud.y, 32 >> tile_w_log2, ud.z, 1 << tile_w_log2, dlo, dhi, o3, omax);
+        const bool heavy = LSB_HEAVY_FIRST && dhi[2] > kHeavyDz;          // some ray of the unit has d.z > kHeavyDz
         unit_oct[u - unit_lo] = (uint8_t)(oct | (heavy ? kUnitHeavy : 0));
+        if (unit_iv != nullptr) {
+            unit_iv[2 * (size_t)(u - unit_lo)] = make_float4(dlo[0], dlo[1], dlo[2], __int_as_float(oct));
+            unit_iv[2 * (size_t)(u - unit_lo) + 1] = make_float4(dhi[0], dhi[1], dhi[2], omax);
+        }
     }
 #pragma unroll
     for (int o = 0; o < 9; ++o) {
@@ -1340,7 +1379,8 @@ __global__ void __launch_bounds__(256) k_classify_units(const SensorDev *__restr
 __global__ void __launch_bounds__(256) k_scatter_units(const SensorDev *__restrict__ sensors, int n_sensors, int unit_lo,
                                                        int unit_hi, int tile_w_log2, const uint8_t *__restrict__ unit_oct,
                                                        const uint32_t *__restrict__ hist, uint32_t *__restrict__ cursor,
-                                                       int4 *__restrict__ unit_list)
+                                                       int4 *__restrict__ unit_list, const float4 *__restrict__ unit_iv = nullptr,
+                                                       float4 *__restrict__ tile_iv = nullptr /* [queue slot][2] */)
 {
     const int u = unit_lo + blockIdx.x * blockDim.x + threadIdx.x;
     const int raw = (u < unit_hi) ? (int)unit_oct[u - unit_lo] : -1;
@@ -1359,7 +1399,14 @@ __global__ void __launch_bounds__(256) k_scatter_units(const SensorDev *__restri
             if (lane_id() == (unsigned)(__ffs(m) - 1)) off = atomicAdd(&cursor[o + 16 * back], k);
             off = __shfl_sync(0xffffffffu, off, __ffs(m) - 1);
             if (back) off = hist[o] - off - k;
-            if (mine) unit_list[base + off + __popc(m & lanemask_lt())] = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
+            if (mine) {
+                const uint32_t slot = base + off + __popc(m & lanemask_lt());
+                unit_list[slot] = unit_descriptor(sensors, n_sensors, u, tile_w_log2);
+                if (tile_iv != nullptr) {
+                    tile_iv[2 * (size_t)slot] = unit_iv[2 * (size_t)(u - unit_lo)];
+                    tile_iv[2 * (size_t)slot + 1] = unit_iv[2 * (size_t)(u - unit_lo) + 1];
+                }
+            }
         }
         base += hist[o];
     }
@@ -1452,47 +1499,6 @@ struct TileFrustum {
         return n <= f && n <= max_range;
     }
 };
-
-// Rays (channels [v0, v0 + nv) x azimuth steps [h0, h0 + nh)) of sensor S, generated with the traversal's own
-// arithmetic: their direction interval and origin.  Returns the common sign class (bit k = component k negative) or
-// 8 when the signs differ.  The tables are read once per row / column.
-__device__ __forceinline__ int block_interval(const SensorDev &S, int world_frame, int v0, int nv, int h0, int nh,
-                                              float dlo[3], float dhi[3], float o3[3], float &omax)
-{
-    dlo[0] = dlo[1] = dlo[2] = INFINITY; dhi[0] = dhi[1] = dhi[2] = -INFINITY;
-    o3[0] = o3[1] = o3[2] = 0.0f; omax = 0.0f;
-    unsigned sign_or = 0u, sign_and = 7u;
-    const int v1 = min(v0 + nv, S.V), h1 = min(h0 + nh, S.H);
-    auto one = [&](float st, float ct, float sp_, float cp) {
-        Ray r; float x, y, z;
-        ray_from_tables(S, world_frame, st, ct, sp_, cp, r, x, y, z, omax);
-        o3[0] = r.ox; o3[1] = r.oy; o3[2] = r.oz;
-        dlo[0] = fminf(dlo[0], r.dx); dhi[0] = fmaxf(dhi[0], r.dx);
-        dlo[1] = fminf(dlo[1], r.dy); dhi[1] = fmaxf(dhi[1], r.dy);
-        dlo[2] = fminf(dlo[2], r.dz); dhi[2] = fmaxf(dhi[2], r.dz);
-        const unsigned o = (unsigned)ray_octant(r);
-        sign_or |= o; sign_and &= o;
-    };
-    if (nv <= 4) {
-        float stv[4], ctv[4];
-#pragma unroll
-        for (int a = 0; a < 4; ++a) {
-            const int v = min(v0 + a, S.V - 1);
-            stv[a] = __ldg(S.sin_t + v); ctv[a] = __ldg(S.cos_t + v);
-        }
-        for (int h = h0; h < h1; ++h) {
-            const float sp_ = __ldg(S.sin_p + h), cp = __ldg(S.cos_p + h);
-#pragma unroll
-            for (int a = 0; a < 4; ++a) if (a < nv && v0 + a < S.V) one(stv[a], ctv[a], sp_, cp);
-        }
-    } else {
-        for (int v = v0; v < v1; ++v) {
-            const float st = __ldg(S.sin_t + v), ct = __ldg(S.cos_t + v);
-            for (int h = h0; h < h1; ++h) one(st, ct, __ldg(S.sin_p + h), __ldg(S.cos_p + h));
-        }
-    }
-    return sign_or == sign_and ? (int)sign_or : 8;
-}
 
 // The interval itself tells the mode of every axis (for a sign-uniform tile they agree with its octant class).
 // false: the block holds no ray.

@@ -435,3 +435,36 @@ def test_lane_refill_small_city_vs_oracle_bvh(refill):
         assert np.array_equal(key(a), key(o)), k
     bvh.close()
     ctx.close()
+
+
+@pytest.mark.parametrize("leaf", [1, 2, 8])
+def test_km_scale_grazing_rays_over_a_fine_plane_vs_brute_force(leaf):
+    """Stress case for the culling rules: a sensor 2 m above a 2 km x 2 km ground tessellated into
+    720 000 triangles, plus a near-coplanar second sheet 1 mm above part of it, and rays within 0.02 .. 3 degrees of the
+    horizon -- Moeller-Trumbore's t is ill-conditioned there (absolute error of centimetres at several hundred
+    metres).  The shipped traversal (tile lists forced on, every leaf size) must return exactly what the exhaustive
+    variant returns, t and triangle id: a box or list entry is only ever culled on a distance bound that the exact
+    test could not beat.  Reference behaviour being matched: rtcIntersect16's closest hit, SRC/EmbreeTracer.cpp:472-480."""
+    flat = lambda X, Y: np.zeros_like(X)
+    v0, t0 = synth.grid_mesh(600, 600, -1000.0, 1000.0, -1000.0, 1000.0, flat)
+    v1, t1 = synth.grid_mesh(60, 60, 100.0, 700.0, -300.0, 300.0, lambda X, Y: np.full_like(X, 1e-3))
+    elev = np.linspace(-0.02, -3.0, 24).astype(np.float32)
+    res = []
+    for mode in (6, 3):
+        ctx = capi.Context(0, capi.FRAME_WORLD)
+        ctx.set_option(capi.OPT_TRAVERSAL, mode)
+        ctx.set_option(capi.OPT_LEAF_SIZE, leaf)
+        ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
+        ctx.set_sensor(elev, 0.0, 360.0, 96, synth.yaw_quat(0.1), np.array([3.0, -7.0, 2.0], np.float32))
+        for name, v, t in (("ground", v0, t0), ("sheet", v1, t1)):
+            assert ctx.add_geometry(name, capi.GEOMETRY_TRIANGLE, v.shape[0], t.shape[0]) >= 0
+            assert ctx.update_geometry(name, v, t, IDENT) == 0
+        assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
+        assert ctx.trace_batch(0, 1, capi.TRACE_NO_POINTS) == 0, ctx.last_error()
+        rc, t, tri = ctx.trace_raw(0)
+        assert rc == 0
+        res.append((t, tri))
+        ctx.close()
+    (t6, i6), (t3, i3) = res
+    assert (i3 >= 0).sum() > 0.9 * i3.size and (t3[i3 >= 0] > 300.0).sum() > 100          # long grazing hits are in the set
+    assert np.array_equal(i6, i3) and np.array_equal(t6.view(np.uint32), t3.view(np.uint32))
