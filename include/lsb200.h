@@ -122,6 +122,10 @@ enum {
                                       remainders.  Default 0 (off): measured slower on the 10 M-triangle city, see DESIGN.md / profiles/design_choices_r02.md --
                                       the traversal is bound by instruction issue and dependent round trips per unit, and the refill
                                       loop costs more instructions than the idle lanes it fills.  Same per-ray results either way. */
+    LSB200_OPT_RETURNS = 22,       /* returns per ray: 1 (default, what the reference produces) or 2 = dual return -- every trace also
+                                      finds, per ray, the NEXT surface behind the first hit: the smallest (t, triangle id) greater
+                                      than the first hit's (the any-hit multi-return the reference only plans, SRC/LidarShooter.hpp.in:
+                                      87-93).  Read with lsb200_fetch_second_returns.  The cloud itself is unchanged. */
     LSB200_OPT_FUSED_TREE = 20     /* 1 (default) = hierarchy and node boxes come out of ONE bottom-up pass over the sorted codes
                                       (k_tree: Apetrei 2014 with Karras node numbering, block-local rendezvous in shared memory);
                                       0 = the two-kernel form (k_hierarchy: Karras 2012 top-down searches, then k_fit).  Same node
@@ -220,6 +224,9 @@ LSB200_API int lsb200_trace_device(lsb200_ctx *ctx, int sensor_index, uint32_t f
 LSB200_API int lsb200_trace_batch(lsb200_ctx *ctx, int first_sensor, int n_sensors, uint32_t flags);
 /* per-ray results for parity tests: t_out[R], tri_out[R] host buffers */
 LSB200_API int lsb200_trace_raw(lsb200_ctx *ctx, int sensor_index, float *t_out, int32_t *tri_out);
+/* second return of every ray of the last trace of `sensor_index` (LSB200_OPT_RETURNS = 2): t2[R] (+inf = none) and the
+ * triangle id tri2[R] (-1 = none); either pointer may be NULL.  Rays without a first hit have no second one. */
+LSB200_API int lsb200_fetch_second_returns(lsb200_ctx *ctx, int sensor_index, float *t2_out, int32_t *tri2_out);
 /* device pointers of the last trace of `sensor_index`: points, point count (uint32), t, triangle id */
 LSB200_API int lsb200_device_results(lsb200_ctx *ctx, int sensor_index, void **d_points, uint32_t **d_count,
                                      float **d_t, int32_t **d_tri);

@@ -19,7 +19,7 @@ COMMIT_AUTO, COMMIT_REBUILD, COMMIT_REFIT = 0, 1, 2
 TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS, TRACE_RANGE_IMAGE = 1, 2, 4, 8, 16, 32
 OPT_TRAVERSAL, OPT_LEAF_SIZE, OPT_TOP_NODES, OPT_STAGE_TIMING, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
 OPT_TRACE_STATS, OPT_MORTON_UNIFORM, OPT_ORIGIN_CHAIN, OPT_TILE_WIDTH, OPT_SMALL_BUILD, OPT_MORTON_LAYOUT, OPT_MORTON_ASPECT, OPT_FIT_RMQ = 6, 7, 8, 9, 10, 11, 12, 13
-OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES, OPT_WATERTIGHT, OPT_INTENSITY_MODEL, OPT_FUSED_TREE, OPT_LANE_REFILL = 14, 15, 16, 17, 18, 19, 20, 21
+OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES, OPT_WATERTIGHT, OPT_INTENSITY_MODEL, OPT_FUSED_TREE, OPT_LANE_REFILL, OPT_RETURNS = 14, 15, 16, 17, 18, 19, 20, 21, 22
 LOG_TRACE, LOG_DEBUG, LOG_INFO, LOG_WARN, LOG_ERROR = 0, 1, 2, 3, 4
 SHARD_FRAMES, SHARD_SENSORS = 0, 1
 ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5
@@ -34,7 +34,7 @@ SYMBOLS = [
     "lsb200_device_results", "lsb200_fetch_points", "lsb200_fetch_batch", "lsb200_synchronize", "lsb200_run_frames", "lsb200_init_message", "lsb200_get_stats",
     "lsb200_reset_counters", "lsb200_get_trace_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
     "lsb200_set_log_callback", "lsb200_set_sensor_intensity_filter", "lsb200_expand_range_image", "lsb200_fetch_intensity",
-    "lsb200_set_sensor_pose", "lsb200_alloc_host", "lsb200_free_host", "lsb200_device_numa_node", "lsb200_clone_scene", "lsb200_run_batch",
+    "lsb200_set_sensor_pose", "lsb200_alloc_host", "lsb200_free_host", "lsb200_device_numa_node", "lsb200_clone_scene", "lsb200_run_batch", "lsb200_fetch_second_returns",
 ]
 
 LOG_FN = C.CFUNCTYPE(None, C.c_int, C.c_char_p, C.c_void_p)
@@ -100,6 +100,7 @@ def lib(lab=False):
     L.lsb200_trace_device.argtypes = [vp, C.c_int, C.c_uint32]
     L.lsb200_trace_batch.argtypes = [vp, C.c_int, C.c_int, C.c_uint32]
     L.lsb200_trace_raw.argtypes = [vp, C.c_int, f32p, i32p]
+    L.lsb200_fetch_second_returns.argtypes = [vp, C.c_int, f32p, i32p]
     L.lsb200_device_results.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     L.lsb200_fetch_points.argtypes = [vp, C.c_int, vp, C.c_size_t, u32p, C.c_uint32]
     L.lsb200_fetch_batch.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), C.POINTER(C.c_size_t), u32p, C.c_uint32]
@@ -355,6 +356,13 @@ class Context:
         R = self.ray_count(sensor)
         t, tri = np.empty(R, np.float32), np.empty(R, np.int32)
         rc = self._L.lsb200_trace_raw(self._h, sensor, _fp(t), tri.ctypes.data_as(C.POINTER(C.c_int32)))
+        return rc, t, tri
+
+    def fetch_second_returns(self, sensor=0):
+        """(status, t2, tri2) of the last trace of `sensor` with OPT_RETURNS = 2."""
+        R = self.ray_count(sensor)
+        t, tri = np.empty(R, np.float32), np.empty(R, np.int32)
+        rc = self._L.lsb200_fetch_second_returns(self._h, sensor, _fp(t), tri.ctypes.data_as(C.POINTER(C.c_int32)))
         return rc, t, tri
 
     def synchronize(self):

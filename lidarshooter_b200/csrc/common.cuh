@@ -49,6 +49,8 @@ struct SensorDev {           // one per LiDAR device
     uint32_t *block_counts;       // ordered compaction scratch
     float *intensity;             // [n_rays] per-ray intensity (k_intensity; only with an intensity model / filter)
     float min_intensity;          // returns below it are dropped (0: none) -- lsb200_set_sensor_intensity_filter
+    float *t2_out;                // [n_rays] second return (LSB200_OPT_RETURNS = 2): the next surface behind the first hit
+    int32_t *tri2_out;            // [n_rays]
 };
 
 __host__ __device__ inline uint32_t f2ord(float f)

@@ -76,6 +76,7 @@ struct Sensor {
     float az_begin = 0.f, az_end = 0.f, lim_range = 0.f, lim_lo = -180.f, lim_hi = 180.f;
     float min_intensity = 0.f;         // lsb200_set_sensor_intensity_filter (0 = off)
     DevBuf inten;                      // per-ray intensity (only with an intensity model / filter)
+    DevBuf t2, tri2;                   // second return per ray (LSB200_OPT_RETURNS = 2)
     int n_rays() const { return V * H; }
 };
 
@@ -85,7 +86,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_fused_tree = 1, opt_lane_refill = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0, opt_watertight = 0, opt_intensity = 0;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_fused_tree = 1, opt_lane_refill = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0, opt_watertight = 0, opt_intensity = 0, opt_returns = 1;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -98,8 +99,9 @@ struct lsb200_ctx {
         d_nodes, d_node_parent, d_leaf_parent, d_rendezvous, d_tree_count, d_flags, d_misc /* n_top, work[2] */, d_sensors, d_sensors_b, d_counts, d_sensor_xf, d_counters, d_unit_oct, d_unit_list, d_oct_hist, d_chains, d_chain_counts, d_plan, d_tile_lists, d_tile_counts, d_sup_lists, d_sup_counts, d_tile_iv, d_sup_iv, d_unit_iv;
     std::vector<GeomDesc> h_geoms;
     std::vector<SensorDev> h_sensors, h_sensors_b;
-    cudaStream_t copy_stream = nullptr;
+    cudaStream_t copy_stream = nullptr, upload_stream = nullptr;
     cudaEvent_t ev_traced[2] = {}, ev_copied[2] = {};
+    cudaEvent_t ev_xform = nullptr, ev_uploaded = nullptr;   // lsb200_run_frames: vertex upload of frame f+1 overlaps frame f after its transform
     // octant queues of the traversal (variant 0): valid for (units_first, units_count, units_epoch, units_world)
     int64_t sensors_epoch = 0, units_epoch = -1;
     int units_first = -1, units_count = -1, units_world = -1;
@@ -246,13 +248,14 @@ SceneDev scene_dev(lsb200_ctx *c)
     return S;
 }
 
-int upload_geometry(lsb200_ctx *c, Geometry &g, const void *verts, int stride, const uint32_t *elems)
+int upload_geometry(lsb200_ctx *c, Geometry &g, const void *verts, int stride, const uint32_t *elems, cudaStream_t on = nullptr)
 {
+    const cudaStream_t ust = on ? on : c->stream;
     if (verts) {
         if (stride < 12 || (stride & 3)) return fail(c, LSB200_ERR_INVALID, "vertex stride %d must be >= 12 and a multiple of 4", stride);
         const size_t bytes = (size_t)g.n_verts * (size_t)stride;
-        LSB_CU(c, g.verts.reserve(std::max<size_t>(bytes, 16), c->stream));
-        if (bytes) LSB_CU(c, cudaMemcpyAsync(g.verts.p, verts, bytes, cudaMemcpyHostToDevice, c->stream));
+        LSB_CU(c, g.verts.reserve(std::max<size_t>(bytes, 16), ust));
+        if (bytes) LSB_CU(c, cudaMemcpyAsync(g.verts.p, verts, bytes, cudaMemcpyHostToDevice, ust));
         g.stride = stride; g.has_verts = true;
     }
     if (elems) {
@@ -302,6 +305,8 @@ int lsb200_create(int cuda_device, lsb200_ctx **out)
     for (auto &e : c->ev) cudaEventCreate(&e);
     cudaMallocHost((void **)&c->h_count, (16 + 2 * kMaxSensors) * sizeof(uint32_t));
     cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&c->upload_stream, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&c->ev_xform, cudaEventDisableTiming); cudaEventCreateWithFlags(&c->ev_uploaded, cudaEventDisableTiming);
     for (int k = 0; k < 2; ++k) { cudaEventCreateWithFlags(&c->ev_traced[k], cudaEventDisableTiming); cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming); }
     if (c->d_bounds.reserve(256, c->stream) != cudaSuccess || c->d_misc.reserve(256, c->stream, false, true) != cudaSuccess ||
         c->d_plan.reserve(256, c->stream, false, true) != cudaSuccess ||
@@ -320,7 +325,7 @@ int lsb200_destroy(lsb200_ctx *c)
         DeviceGuard dg(c->device);
         cudaStreamSynchronize(c->stream);
         for (auto &kv : c->geoms) { kv.second.verts.release(); kv.second.elems.release(); }
-        for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.t_b.release(); s.blocks.release(); s.inten.release(); }
+        for (auto &s : c->sensors) { s.tables.release(); s.az_mask.release(); s.t.release(); s.tri.release(); s.points.release(); s.points_b.release(); s.t_b.release(); s.blocks.release(); s.inten.release(); s.t2.release(); s.tri2.release(); }
         DevBuf *bufs[] = {&c->d_geoms, &c->d_xverts, &c->d_bounds, &c->d_keys, &c->d_vals, &c->d_keys_tmp, &c->d_vals_tmp,
                           &c->d_sort_scratch, &c->d_tris, &c->d_leaf_ids, &c->d_nodes, &c->d_node_parent, &c->d_leaf_parent, &c->d_rendezvous, &c->d_tree_count,
                           &c->d_flags, &c->d_misc, &c->d_sensors, &c->d_sensors_b, &c->d_counts, &c->d_sensor_xf, &c->d_counters, &c->d_unit_oct, &c->d_unit_list, &c->d_oct_hist, &c->d_chains, &c->d_chain_counts, &c->d_plan, &c->d_tile_lists, &c->d_tile_counts, &c->d_sup_lists, &c->d_sup_counts, &c->d_tile_iv, &c->d_sup_iv, &c->d_unit_iv};
@@ -329,6 +334,9 @@ int lsb200_destroy(lsb200_ctx *c)
         for (auto &e : c->ev) if (e) cudaEventDestroy(e);
         for (int k = 0; k < 2; ++k) { if (c->ev_traced[k]) cudaEventDestroy(c->ev_traced[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
         if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+        if (c->upload_stream) { cudaStreamSynchronize(c->upload_stream); cudaStreamDestroy(c->upload_stream); }
+        if (c->ev_xform) cudaEventDestroy(c->ev_xform);
+        if (c->ev_uploaded) cudaEventDestroy(c->ev_uploaded);
         if (c->own_stream) cudaStreamDestroy(c->own_stream);
     }
     delete c;
@@ -377,6 +385,7 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_TILE_MIN_UNITS: if (value < 0) break; c->opt_tile_min_units = value; return LSB200_OK;
     case LSB200_OPT_TILE_VISITS: if (value < 0 || value > 4096) break; c->opt_tile_visits = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
+    case LSB200_OPT_RETURNS: if (value < 1 || value > 2) break; c->opt_returns = value; return LSB200_OK;
     case LSB200_OPT_LANE_REFILL: if (value < 0 || value > 15) break; c->opt_lane_refill = value; return LSB200_OK;
     case LSB200_OPT_FUSED_TREE: c->opt_fused_tree = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TILE_WIDTH: {
@@ -677,6 +686,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
         // one cluster of kClusterCtas CTAs (__cluster_dims__ on the kernel)
         k_build_small<<<kClusterCtas, kSmallThreads, (size_t)nt * 4, st>>>(S, args, c->frame_mode == LSB200_FRAME_SENSOR, rebuild ? 1 : 0);
         count_launch(c);
+        cudaEventRecord(c->ev_xform, st);
         mark(nullptr);
         c->top_valid = false;
         if (c->built_top > 0 && c->opt_traversal == 4) {
@@ -712,6 +722,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
     mark("lsb200:transform");
     k_transform<<<(unsigned)((nv + 255) / 256), 256, 0, st>>>(S, c->frame_mode == LSB200_FRAME_SENSOR, c->d_sensor_xf.as<float>());
     count_launch(c);
+    cudaEventRecord(c->ev_xform, st);        // the raw vertex blobs have been read: the next frame's upload may overwrite them
     mark(rebuild ? "lsb200:morton" : "lsb200:tree");
     if (rebuild) {
         // (2) Morton codes  (3) radix sort  (4) Karras hierarchy
@@ -836,6 +847,7 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
         LSB_CU(c, s.t.reserve(R * 4, st)); LSB_CU(c, s.tri.reserve(R * 4, st));
         LSB_CU(c, s.points.reserve(R * 32, st)); LSB_CU(c, s.blocks.reserve(std::max<size_t>(nblk, 4) * 4, st));
         if (slot == 1) { LSB_CU(c, s.points_b.reserve(R * 32, st)); LSB_CU(c, s.t_b.reserve(R * 4, st)); }
+        if (c->opt_returns == 2) { LSB_CU(c, s.t2.reserve(R * 4, st)); LSB_CU(c, s.tri2.reserve(R * 4, st)); }
         if (c->opt_intensity != 0 || s.min_intensity > 0.0f) {
             if (s.inten.cap < R * 4) dirty = true;
             LSB_CU(c, s.inten.reserve(R * 4, st));
@@ -856,6 +868,7 @@ static int prepare_sensors(lsb200_ctx *c, int first, int count, int slot = 0)
         d.V = s.V; d.H = s.H; d.n_rays = s.n_rays();
         d.max_range = s.max_range; d.az_mask = s.has_mask ? s.az_mask.as<uint8_t>() : nullptr;
         d.intensity = s.inten.as<float>(); d.min_intensity = s.min_intensity;
+        d.t2_out = s.t2.as<float>(); d.tri2_out = s.tri2.as<int32_t>();
         d.t_out = s.t.as<float>(); d.tri_out = s.tri.as<int32_t>(); d.points = s.points.as<uint8_t>();
         d.count = c->d_counts.as<uint32_t>() + i; d.block_counts = s.blocks.as<uint32_t>();
         d.tiles_h = (s.H + tw - 1) / tw;
@@ -1125,6 +1138,12 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     if (timing) cudaEventRecord(c->ev[9], st);
     int max_rays = 0;
     for (int i = first; i < first + count; ++i) max_rays = std::max(max_rays, c->sensors[i].n_rays());
+    if (c->opt_returns == 2) {           // second return of every ray: the next surface behind its first hit (k_second_return)
+        dim3 grid((unsigned)((max_rays + 255) / 256), (unsigned)count);
+        if (c->built_watertight) k_second_return<true><<<grid, 256, 0, st>>>(P, first);
+        else k_second_return<false><<<grid, 256, 0, st>>>(P, first);
+        count_launch(c);
+    }
     if (need_intensity) {
         const bool small = c->opt_small_build && c->n_tris <= kSmallMaxTris && c->geoms.size() <= (size_t)kSmallMaxGeoms;
         if (small) {        // the fused small build takes its descriptors as kernel parameters: the post-pass needs them in memory
@@ -1274,6 +1293,7 @@ int lsb200_run_frames(lsb200_ctx *c, const lsb200_frame *frames, int n_frames, i
     const size_t rec = record_bytes(flags);
     int result = LSB200_OK;
     bool slot_used[2] = {false, false};
+    bool pre_uploaded = false;          // the vertex blobs of the frame about to be committed are already on their way (upload stream)
 
     auto finish = [&](int f) -> int {             // frame f is traced (or being traced): counts, then the clouds
         const int slot = f & 1;
@@ -1302,12 +1322,37 @@ int lsb200_run_frames(lsb200_ctx *c, const lsb200_frame *frames, int n_frames, i
             for (auto &kv : c->geoms) {
                 Geometry &g = kv.second;
                 const void *v = (frames[f].verts && frames[f].verts[k]) ? frames[f].verts[k] : nullptr;
-                if (v) { if (int rc = upload_geometry(c, g, v, g.stride, nullptr)) return rc; }
+                // frame 0 uploads in order; later frames were uploaded on the upload stream while frame f-1 was traced
+                if (v && !pre_uploaded) { if (int rc = upload_geometry(c, g, v, g.stride, nullptr)) return rc; }
                 if (frames[f].affines) std::memcpy(g.A, frames[f].affines + 12 * k, sizeof(g.A));
                 ++k;
             }
+            if (pre_uploaded) LSB_CU(c, cudaStreamWaitEvent(st, c->ev_uploaded, 0));
+            pre_uploaded = false;
             if (int rc = commit_locked(c, commit_mode)) return rc;
             if (int rc = trace_locked(c, first, count, flags, slot)) return rc;
+            // vertex blobs of frame f+1: host -> device on the upload stream as soon as this frame's transform has read the
+            // buffers (ev_xform), i.e. under this frame's sort / tree / trace -- only when no buffer has to grow
+            if (f + 1 < n_frames && frames[f + 1].verts) {
+                bool fits = true, any = false;
+                size_t j = 0;
+                for (auto &kv : c->geoms) {
+                    Geometry &g = kv.second;
+                    if (frames[f + 1].verts[j]) { any = true; fits = fits && g.has_verts && g.verts.cap >= (size_t)g.n_verts * (size_t)g.stride; }
+                    ++j;
+                }
+                if (any && fits) {
+                    LSB_CU(c, cudaStreamWaitEvent(c->upload_stream, c->ev_xform, 0));
+                    j = 0;
+                    for (auto &kv : c->geoms) {
+                        Geometry &g = kv.second;
+                        if (frames[f + 1].verts[j]) { if (int rc = upload_geometry(c, g, frames[f + 1].verts[j], g.stride, nullptr, c->upload_stream)) return rc; }
+                        ++j;
+                    }
+                    LSB_CU(c, cudaEventRecord(c->ev_uploaded, c->upload_stream));
+                    pre_uploaded = true;
+                }
+            }
             LSB_CU(c, cudaMemcpyAsync(c->h_count + 16 + (size_t)slot * kMaxSensors + first,
                                       c->d_counts.as<uint32_t>() + (size_t)slot * kMaxSensors + first, (size_t)count * 4,
                                       cudaMemcpyDeviceToHost, st));
@@ -1319,6 +1364,7 @@ int lsb200_run_frames(lsb200_ctx *c, const lsb200_frame *frames, int n_frames, i
     };
     const int rc = body();
     cudaStreamSynchronize(cs);
+    cudaStreamSynchronize(c->upload_stream);
     cudaStreamSynchronize(st);
     if (rc) return rc;
     return result;
@@ -1339,6 +1385,22 @@ int lsb200_trace_raw(lsb200_ctx *c, int idx, float *t_out, int32_t *tri_out)
     }
     if (t_out) LSB_CU(c, cudaMemcpyAsync(t_out, s.t.p, R * 4, cudaMemcpyDeviceToHost, c->stream));
     if (tri_out) LSB_CU(c, cudaMemcpyAsync(tri_out, s.tri.p, R * 4, cudaMemcpyDeviceToHost, c->stream));
+    LSB_CU(c, cudaStreamSynchronize(c->stream));
+    return LSB200_OK;
+}
+
+int lsb200_fetch_second_returns(lsb200_ctx *c, int idx, float *t2_out, int32_t *tri2_out)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (idx < 0 || (size_t)idx >= c->sensors.size() || !c->sensors[idx].set) return fail(c, LSB200_ERR_INVALID, "bad sensor %d", idx);
+    if (c->opt_returns != 2) return fail(c, LSB200_ERR_STATE, "fetch_second_returns: LSB200_OPT_RETURNS is not 2");
+    Sensor &s = c->sensors[idx];
+    if (!s.t2.p || !s.tri2.p) return fail(c, LSB200_ERR_STATE, "fetch_second_returns: sensor %d has not been traced with two returns", idx);
+    DeviceGuard dg(c->device);
+    const size_t R = (size_t)s.n_rays();
+    if (t2_out) LSB_CU(c, cudaMemcpyAsync(t2_out, s.t2.p, R * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (tri2_out) LSB_CU(c, cudaMemcpyAsync(tri2_out, s.tri2.p, R * 4, cudaMemcpyDeviceToHost, c->stream));
     LSB_CU(c, cudaStreamSynchronize(c->stream));
     return LSB200_OK;
 }
@@ -1658,7 +1720,7 @@ int lsb200_clone_scene(lsb200_ctx *src, int cuda_device, lsb200_ctx **out)
     dst->opt_morton_layout = src->opt_morton_layout; dst->opt_morton_aspect = src->opt_morton_aspect; dst->opt_chain = src->opt_chain;
     dst->opt_tile_w_log2 = src->opt_tile_w_log2; dst->opt_small_build = src->opt_small_build; dst->opt_tile_entries = src->opt_tile_entries;
     dst->opt_tile_visits = src->opt_tile_visits; dst->opt_tile_min_units = src->opt_tile_min_units;
-    dst->opt_watertight = src->opt_watertight; dst->opt_intensity = src->opt_intensity; dst->opt_fused_tree = src->opt_fused_tree; dst->opt_lane_refill = src->opt_lane_refill;
+    dst->opt_watertight = src->opt_watertight; dst->opt_intensity = src->opt_intensity; dst->opt_fused_tree = src->opt_fused_tree; dst->opt_lane_refill = src->opt_lane_refill; dst->opt_returns = src->opt_returns;
     dst->log_fn = src->log_fn; dst->log_user = src->log_user;
     for (size_t i = 0; i < src->sensors.size(); ++i) {
         const Sensor &s = src->sensors[i];

@@ -1764,6 +1764,91 @@ __global__ void __launch_bounds__(kTileBlock) k_tile_entries(TraceParams P, int 
     }
 }
 
+// ---- second return (multi-return) ---------------------------------------------------------------------------
+// The reference leaves multi-return to "an anyhit program which will produce multiple returns" (SRC/LidarShooter.hpp.in:
+// 87-93, never written).  LSB200_OPT_RETURNS = 2 reports, next to the closest hit (t1, id1), the NEXT surface the ray
+// would reach behind it: the lexicographically smallest (t, triangle id) > (t1, id1) -- a triangle at exactly the same
+// distance counts (two sheets in contact), the first-hit triangle itself does not.  One thread per ray, plain
+// depth-first walk from the root with the traversal's own conservative slab test (only the upper bound prunes; the
+// lower bound is applied to accepted triangles, never to boxes).  Bit-identical to oracle/lsb_oracle.c:
+// lso_trace_bvh_second.  An optional feature off the benchmarked path: no tile lists, no queues.
+template <bool WT>
+__global__ void __launch_bounds__(256) k_second_return(TraceParams P, int sensor_base)
+{
+    const SensorDev &S = P.sensors[sensor_base + blockIdx.y];
+    const int ray = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ray >= S.n_rays) return;
+    const float t1 = S.t_out[ray];
+    const int id1 = S.tri_out[ray];
+    float best = INFINITY; int bi = -1;
+    if (id1 >= 0) {
+        float smax = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
+        const int v = ray / S.H, h = ray - v * S.H;
+        Ray r; float dsx, dsy, dsz, omax;
+        make_ray(S, P.world_frame, v, h, r, dsx, dsy, dsz, omax);
+        const float eps = 8e-6f * (smax + omax) + 1e-30f;
+        const float tiny = 1e-30f;
+        const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
+        const float iy = 1.0f / (fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
+        const float iz = 1.0f / (fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
+        const float ax = -(r.ox + eps) * ix, ay = -(r.oy + eps) * iy, az = -(r.oz + eps) * iz;
+        const float bx = -(r.ox - eps) * ix, by = -(r.oy - eps) * iy, bz = -(r.oz - eps) * iz;
+        auto accept = [&](float t, int g) {          // (t1, id1) < (t, g) < (best, bi), lexicographically
+            if (!(t > t1 || (t == t1 && g > id1))) return;
+            if (t < best || (t == best && (bi < 0 || g < bi))) { best = t; bi = g; }
+        };
+        auto leaf = [&](int ref) {
+            const int enc = ~ref;
+            const int first = enc & ((1 << kLeafShift) - 1), count = (enc >> kLeafShift) + 1;
+            for (int k = 0; k < count; ++k) {
+                const float4 *rec = P.tris + 3 * (size_t)(first + k);
+                const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2);
+                float t;
+                if (WT ? intersect_tri_wt(q0, q1, q2, r, t) : intersect_tri(q0, q1, q2, r, t)) accept(t, __ldg(P.leaf_ids + first + k));
+            }
+        };
+        int stack[kStackSize];
+        int sp = 0;
+        bool overflow = false;
+        int cur = P.top_cap;                         // Karras node 0 (a single-triangle scene has a root too: leaf + empty box)
+        while (cur != 0x7fffffff) {
+            if (cur < 0) { leaf(cur); cur = sp > 0 ? stack[--sp] : 0x7fffffff; continue; }
+            const float4 *n = P.nodes + 4 * (size_t)cur;
+            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
+            const float2 q3 = __ldg(reinterpret_cast<const float2 *>(n + 3));
+            const float far_lim = best * 1.0000005f;
+            float n0, f0, n1, f1;
+            slab_nf<8>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
+                       fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
+            slab_nf<8>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
+                       fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
+            const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
+            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+            if (hit0 && hit1) {
+                const bool swap = n1 < n0;
+                if (sp < kStackSize) stack[sp++] = swap ? c0 : c1; else overflow = true;
+                cur = swap ? c1 : c0;
+            } else if (hit0) cur = c0;
+            else if (hit1) cur = c1;
+            else cur = sp > 0 ? stack[--sp] : 0x7fffffff;
+        }
+        if (overflow) {                              // depth guard tripped (adversarial scene): exhaustive
+            best = INFINITY; bi = -1;
+            for (int k = 0; k < P.n_tris; ++k) {
+                const float4 *rec = P.tris + 3 * (size_t)k;
+                const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2);
+                float t;
+                if (WT ? intersect_tri_wt(q0, q1, q2, r, t) : intersect_tri(q0, q1, q2, r, t)) accept(t, __ldg(P.leaf_ids + k));
+            }
+        }
+        if (!(best <= S.max_range)) { best = INFINITY; bi = -1; }
+    }
+    S.t2_out[ray] = best;
+    S.tri2_out[ray] = bi;
+}
+
 // 32-bit fill (empty-scene results: t = +inf)
 __global__ void __launch_bounds__(256) k_fill_u32(uint32_t *__restrict__ p, uint32_t v, int n)
 {

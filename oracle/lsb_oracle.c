@@ -605,6 +605,40 @@ LSO_API void lso_trace_bvh(const lso_bvh *bvh, const float *orgs, int org_stride
         trace_one(bvh, orgs + (size_t)org_stride * r, dirs + 3 * r, &t_out[r], &tri_out[r]);
 }
 
+/* Second return (include/lsb200.h: LSB200_OPT_RETURNS = 2; the reference only plans it, SRC/LidarShooter.hpp.in:87-93):
+ * per ray with a first hit (t1, id1), the lexicographically smallest (t, triangle id) greater than it -- the next
+ * surface behind the first one.  Same walk and padding as trace_one; the lower bound applies to triangles only. */
+LSO_API void lso_trace_bvh_second(const lso_bvh *bvh, const float *orgs, int org_stride, const float *dirs, int64_t nR,
+                                  const float *t1, const int32_t *tri1, float *t2_out, int32_t *tri2_out)
+{
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t r = 0; r < nR; ++r) {
+        float best = INFINITY; int32_t bi = -1;
+        if (tri1[r] >= 0 && bvh->n_tris > 0) {
+            const float *o = orgs + (size_t)org_stride * r, *d = dirs + 3 * r;
+            const float lo_t = t1[r]; const int32_t lo_i = tri1[r];
+            float inv[3] = {1.0f / d[0], 1.0f / d[1], 1.0f / d[2]};
+            int32_t stack[128]; int sp = 0;
+            stack[sp++] = 0;
+            while (sp) {
+                const lso_node *n = &bvh->nodes[stack[--sp]];
+                float tn;
+                if (!slab(n, o, inv, best, &tn)) continue;
+                if (n->count) {
+                    for (int32_t i = n->left; i < n->left + n->count; ++i) {
+                        float t;
+                        if (!lso_intersect_any(&bvh->tris[i], o, d, &t)) continue;
+                        const int32_t g = bvh->tri_ids[i];
+                        if (!(t > lo_t || (t == lo_t && g > lo_i))) continue;
+                        if (t < best || (t == best && (bi < 0 || g < bi))) { best = t; bi = g; }
+                    }
+                } else if (sp < 126) { stack[sp++] = n->left; stack[sp++] = n->left + 1; }
+            }
+        }
+        t2_out[r] = best; tri2_out[r] = bi;
+    }
+}
+
 /* ------------------------------------------------------------------------------------------------
  * PACKET form of lso_trace_bvh: 8 consecutive rays (AVX2) walk the BVH together with one shared stack, the way
  * rtcIntersect16 walks a ray packet (SRC/EmbreeTracer.cpp:297-367, 472-480: the reference traces 16-ray

@@ -58,6 +58,7 @@ def lib():
         L.lso_trace_bvh.argtypes = [C.c_void_p, f32p, C.c_int, f32p, C.c_int64, f32p, i32p]
         L.lso_trace_bvh_packet.argtypes = [C.c_void_p, f32p, C.c_int, f32p, C.c_int64, f32p, i32p]
         L.lso_trace_bvh_packet.restype = C.c_int
+        L.lso_trace_bvh_second.argtypes = [C.c_void_p, f32p, C.c_int, f32p, C.c_int64, f32p, i32p, f32p, i32p]
         f64p = C.POINTER(C.c_double)
         L.lso_trace_bvh_f64.argtypes = [C.c_void_p, f32p, u32p, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
         L.lso_trace_brute_f64.argtypes = [f32p, u32p, C.c_int64, f32p, C.c_int, f32p, C.c_int64, f64p, i32p]
@@ -220,6 +221,17 @@ class Bvh:
         t, tri = np.empty(nR, np.float32), np.empty(nR, np.int32)
         lib().lso_trace_bvh(self._h, _p(o, C.c_float), stride, _p(dirs, C.c_float), nR, _p(t, C.c_float),
                             _p(tri, C.c_int32))
+        return t, tri
+
+    def trace_second(self, orgs, dirs, t1, tri1):
+        """Second return per ray: the smallest (t, triangle id) greater than the first hit (t1, tri1); (+inf, -1) if none."""
+        dirs = _f32(dirs).reshape(-1, 3)
+        nR = dirs.shape[0]
+        o, stride = _origins(orgs, nR)
+        t1 = _f32(t1); tri1 = np.ascontiguousarray(tri1, dtype=np.int32)
+        t, tri = np.empty(nR, np.float32), np.empty(nR, np.int32)
+        lib().lso_trace_bvh_second(self._h, _p(o, C.c_float), stride, _p(dirs, C.c_float), nR, _p(t1, C.c_float),
+                                   _p(tri1, C.c_int32), _p(t, C.c_float), _p(tri, C.c_int32))
         return t, tri
 
     def trace_packet(self, orgs, dirs):

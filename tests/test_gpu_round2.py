@@ -468,3 +468,59 @@ def test_km_scale_grazing_rays_over_a_fine_plane_vs_brute_force(leaf):
     (t6, i6), (t3, i3) = res
     assert (i3 >= 0).sum() > 0.9 * i3.size and (t3[i3 >= 0] > 300.0).sum() > 100          # long grazing hits are in the set
     assert np.array_equal(i6, i3) and np.array_equal(t6.view(np.uint32), t3.view(np.uint32))
+
+
+@pytest.mark.parametrize("watertight", [0, 1])
+def test_second_return_vs_oracle(meshes, watertight):
+    """LSB200_OPT_RETURNS = 2 (the any-hit multi-return the reference only plans, SRC/LidarShooter.hpp.in:87-93): per ray
+    the next surface behind the first hit, bit-exact against the oracle -- XT-32 over ground + ben (rays that graze ben
+    have the ground behind it) and a soup with duplicated triangles (second return at the SAME distance, larger id)."""
+    args = xt32_sensor_args("0000")
+    ctx = xt32_ctx(meshes, opts={capi.OPT_RETURNS: 2, capi.OPT_WATERTIGHT: watertight})
+    assert ctx.commit_scene() == 0
+    rc, t1, i1 = ctx.trace_raw()
+    assert rc == 0
+    rc, t2, i2 = ctx.fetch_second_returns()
+    assert rc == 0, ctx.last_error()
+    s = lso.Sensor(*args)
+    with lso.watertight(bool(watertight)):
+        verts, tris = lso.concat_scene(s, xt32_meshes(meshes), mode=0)
+        bvh = lso.Bvh(verts, tris)
+        dirs = lso.ray_dirs(s.tables)
+        r1 = bvh.trace(np.zeros(3, np.float32), dirs)
+        r2 = bvh.trace_second(np.zeros(3, np.float32), dirs, r1[0], r1[1])
+        bvh.close()
+    assert np.array_equal(i1, r1[1]) and np.array_equal(t1, r1[0])
+    assert np.array_equal(i2, r2[1]) and np.array_equal(t2.view(np.uint32), r2[0].view(np.uint32))
+    assert (i2 >= 0).sum() > 50 and np.all(t2[i2 >= 0] >= t1[i2 >= 0]) and np.all(i2[i1 < 0] == -1)
+    ctx.close()
+
+    rng = np.random.default_rng(3)
+    n = 3000
+    c = rng.uniform(-15, 15, (n, 1, 3)).astype(np.float32)
+    v = (c + rng.normal(0, 1.2, (n, 3, 3)).astype(np.float32)).reshape(-1, 3)
+    tr = np.arange(3 * n, dtype=np.uint32).reshape(-1, 3)
+    tr = np.concatenate([tr, tr[:300]])
+    elev = np.linspace(70, -70, 40).astype(np.float32)
+    ctx = capi.Context(0)
+    ctx.set_option(capi.OPT_RETURNS, 2)
+    ctx.set_option(capi.OPT_WATERTIGHT, watertight)
+    sargs = (elev, 0.0, 360.0, 120, (1, 0, 0, 0), (0, 0, 0))
+    ctx.set_sensor(*sargs)
+    assert ctx.add_geometry("soup", capi.GEOMETRY_TRIANGLE, v.shape[0], tr.shape[0]) >= 0
+    assert ctx.update_geometry("soup", v, tr, IDENT) == 0
+    assert ctx.commit_scene() == 0
+    rc, t1, i1 = ctx.trace_raw()
+    rc2, t2, i2 = ctx.fetch_second_returns()
+    assert rc == 0 and rc2 == 0
+    s = lso.Sensor(*sargs)
+    with lso.watertight(bool(watertight)):
+        verts, tris = lso.concat_scene(s, [(v, tr, IDENT)], mode=0)
+        bvh = lso.Bvh(verts, tris)
+        dirs = lso.ray_dirs(s.tables)
+        r1 = bvh.trace(np.zeros(3, np.float32), dirs)
+        r2 = bvh.trace_second(np.zeros(3, np.float32), dirs, r1[0], r1[1])
+        bvh.close()
+    assert np.array_equal(i1, r1[1]) and np.array_equal(i2, r2[1]) and np.array_equal(t2.view(np.uint32), r2[0].view(np.uint32))
+    assert ((t2 == t1) & (i2 > i1) & (i1 >= 0)).sum() > 0
+    ctx.close()

@@ -235,3 +235,33 @@ def test_packet_tracer_is_bit_identical_to_the_scalar_walk(n_rays):
         assert np.array_equal(res[1], i0) and np.array_equal(res[0].view(np.uint32), t0.view(np.uint32))
     assert n_rays < 100 or (i0 >= 0).sum() > 100
     bvh.close()
+
+
+def test_second_return_of_the_oracle_against_numpy_brute_force():
+    """lso_trace_bvh_second: per ray the smallest (t, id) greater than the first hit -- checked against an exhaustive
+    numpy evaluation built from lso.intersect_one-compatible brute force (trace_brute on the scene minus nothing:
+    all hits enumerated per ray)."""
+    rng = np.random.default_rng(5)
+    n_tris = 400
+    c = rng.uniform(-6, 6, (n_tris, 1, 3)).astype(np.float32)
+    v = (c + rng.normal(0, 1.5, (n_tris, 3, 3)).astype(np.float32)).reshape(-1, 3)
+    tr = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
+    tr = np.concatenate([tr, tr[:40]])                        # duplicated triangles: second return at the SAME distance
+    d = rng.normal(0, 1, (300, 3)).astype(np.float32)
+    o = np.zeros(3, np.float32)
+    bvh = lso.Bvh(v, tr)
+    t1, i1 = bvh.trace(o, d)
+    t2, i2 = bvh.trace_second(o, d, t1, i1)
+    # exhaustive: every (ray, triangle) hit through the single-triangle entry
+    for r in range(d.shape[0]):
+        hits = []
+        for g in range(tr.shape[0]):
+            hit, t = lso.intersect_one(v[tr[g, 0]], v[tr[g, 1]], v[tr[g, 2]], o, d[r])
+            if hit:
+                hits.append((np.float32(t), g))
+        hits.sort()
+        assert (hits[0] if hits else (np.float32(np.inf), -1)) == (t1[r], i1[r]) or (not hits and i1[r] < 0)
+        want = hits[1] if len(hits) > 1 else (np.float32(np.inf), -1)
+        assert (t2[r], i2[r]) == want, r
+    assert (i2 >= 0).sum() > 20 and (t2[:] == t1[:]).sum() > 0
+    bvh.close()
