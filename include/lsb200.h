@@ -126,6 +126,9 @@ enum {
                                       finds, per ray, the NEXT surface behind the first hit: the smallest (t, triangle id) greater
                                       than the first hit's (the any-hit multi-return the reference only plans, SRC/LidarShooter.hpp.in:
                                       87-93).  Read with lsb200_fetch_second_returns.  The cloud itself is unchanged. */
+    LSB200_OPT_SMALL_TRACE_UNITS = 23, /* trace launches of fewer 32-ray units than this (default 512 = 16 384 rays; an XT-32 scan has 150)
+                                      run one thread per ray from the root (k_trace_small) instead of the persistent queue kernel,
+                                      whose fixed costs dominate at that size; 0 = never.  Same per-ray results. */
     LSB200_OPT_FUSED_TREE = 20     /* 1 (default) = hierarchy and node boxes come out of ONE bottom-up pass over the sorted codes
                                       (k_tree: Apetrei 2014 with Karras node numbering, block-local rendezvous in shared memory);
                                       0 = the two-kernel form (k_hierarchy: Karras 2012 top-down searches, then k_fit).  Same node

@@ -19,7 +19,7 @@ COMMIT_AUTO, COMMIT_REBUILD, COMMIT_REFIT = 0, 1, 2
 TRACE_ORDERED, TRACE_RING_ZERO, TRACE_XYZI16, TRACE_NO_POINTS, TRACE_WORLD_POINTS, TRACE_RANGE_IMAGE = 1, 2, 4, 8, 16, 32
 OPT_TRAVERSAL, OPT_LEAF_SIZE, OPT_TOP_NODES, OPT_STAGE_TIMING, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
 OPT_TRACE_STATS, OPT_MORTON_UNIFORM, OPT_ORIGIN_CHAIN, OPT_TILE_WIDTH, OPT_SMALL_BUILD, OPT_MORTON_LAYOUT, OPT_MORTON_ASPECT, OPT_FIT_RMQ = 6, 7, 8, 9, 10, 11, 12, 13
-OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES, OPT_WATERTIGHT, OPT_INTENSITY_MODEL, OPT_FUSED_TREE, OPT_LANE_REFILL, OPT_RETURNS = 14, 15, 16, 17, 18, 19, 20, 21, 22
+OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES, OPT_WATERTIGHT, OPT_INTENSITY_MODEL, OPT_FUSED_TREE, OPT_LANE_REFILL, OPT_RETURNS, OPT_SMALL_TRACE_UNITS = 14, 15, 16, 17, 18, 19, 20, 21, 22, 23
 LOG_TRACE, LOG_DEBUG, LOG_INFO, LOG_WARN, LOG_ERROR = 0, 1, 2, 3, 4
 SHARD_FRAMES, SHARD_SENSORS = 0, 1
 ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5

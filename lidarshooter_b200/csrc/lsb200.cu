@@ -86,7 +86,7 @@ struct lsb200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     int frame_mode = LSB200_FRAME_SENSOR;
-    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_fused_tree = 1, opt_lane_refill = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0, opt_watertight = 0, opt_intensity = 0, opt_returns = 1;
+    int opt_traversal = 6, opt_leaf = 2, opt_top = 1024, opt_timing = 0, opt_ctas_per_sm = 0, opt_stats = 0, opt_morton_uniform = 0, opt_morton_layout = 0, opt_morton_aspect = 60, opt_chain = 1, opt_tile_w_log2 = 3, opt_small_build = 1, opt_fit_rmq = 0, opt_fused_tree = 1, opt_lane_refill = 0, opt_tile_entries = 10, opt_tile_visits = 0, opt_tile_min_units = 4096, opt_super_tiles = 0, opt_watertight = 0, opt_intensity = 0, opt_returns = 1, opt_small_trace_units = 512;
     int sm_count = kSmCount;
     std::map<int, Geometry> geoms;           // ascending geometry id == concatenation order
     std::map<std::string, int> by_name;
@@ -385,6 +385,7 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_TILE_MIN_UNITS: if (value < 0) break; c->opt_tile_min_units = value; return LSB200_OK;
     case LSB200_OPT_TILE_VISITS: if (value < 0 || value > 4096) break; c->opt_tile_visits = value; c->tile_commit_epoch = -1; return LSB200_OK;
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
+    case LSB200_OPT_SMALL_TRACE_UNITS: if (value < 0) break; c->opt_small_trace_units = value; return LSB200_OK;
     case LSB200_OPT_RETURNS: if (value < 1 || value > 2) break; c->opt_returns = value; return LSB200_OK;
     case LSB200_OPT_LANE_REFILL: if (value < 0 || value > 15) break; c->opt_lane_refill = value; return LSB200_OK;
     case LSB200_OPT_FUSED_TREE: c->opt_fused_tree = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
@@ -675,7 +676,11 @@ static int commit_locked(lsb200_ctx *c, int mode)
         const size_t ns = c->sensors.size();
         bool all_set = ns > 0;
         for (const Sensor &sn : c->sensors) all_set = all_set && sn.set;
-        if (c->opt_chain && all_set && ns <= 8 && c->opt_traversal != 3) {
+        int units_total = 0;
+        for (const Sensor &sn : c->sensors) units_total += ((sn.V + (32 >> c->opt_tile_w_log2) - 1) / (32 >> c->opt_tile_w_log2)) * ((sn.H + (1 << c->opt_tile_w_log2) - 1) >> c->opt_tile_w_log2);
+        const bool chains_unused = c->opt_traversal == 6 && !c->opt_stats && units_total < c->opt_small_trace_units &&
+                                   !(c->opt_tile_entries >= 2 && units_total >= c->opt_tile_min_units);      // k_trace_small starts at the root
+        if (c->opt_chain && all_set && ns <= 8 && c->opt_traversal != 3 && !chains_unused) {
             LSB_CU(c, c->d_chains.reserve(ns * 9 * 2 * kMaxChain * sizeof(float4), st));
             LSB_CU(c, c->d_chain_counts.reserve(ns * 9 * 4, st));
             args.n_origins = (int)ns; args.chains = c->d_chains.as<float4>(); args.chain_counts = c->d_chain_counts.as<int>();
@@ -1006,7 +1011,20 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         c->top_valid = true;
     }
     const int n_units = unit_hi - unit_lo;
-    if (c->opt_chain && mode != 3) {
+    // small launches (an XT-32 scan is 150 units): one thread per ray from the root, no queues / chains / lists (k_trace_small)
+    // (not when per-tile entry lists were asked for at this size -- LSB200_OPT_TILE_MIN_UNITS lowered by the caller)
+    const bool lists_wanted = c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units;
+    const bool small_trace = mode == 6 && !c->opt_stats && n_units < c->opt_small_trace_units && !lists_wanted;
+    if (small_trace) {
+        int max_r = 0;
+        for (int i = first; i < first + count; ++i) max_r = std::max(max_r, c->sensors[i].n_rays());
+        dim3 grid((unsigned)((max_r + 127) / 128), (unsigned)count);
+        if (c->built_watertight) k_trace_small<true><<<grid, 128, 0, st>>>(P, first);
+        else k_trace_small<false><<<grid, 128, 0, st>>>(P, first);
+        count_launch(c);
+        c->stats.trace_grid = (int)(grid.x * grid.y); c->stats.trace_block = 128;
+    }
+    if (c->opt_chain && mode != 3 && !small_trace) {
         // origin chains: one list per sensor, valid for this BVH and these sensor poses
         const size_t ns = c->sensors.size();
         if (c->chain_commit_epoch != c->commit_epoch || c->chain_sensors_epoch != c->sensors_epoch) {
@@ -1022,7 +1040,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         P.chains = c->d_chains.as<float4>();
         P.chain_counts = c->d_chain_counts.as<int>();
     }
-    if (mode == 0 || mode == 6 || mode == 7) {
+    if ((mode == 0 || mode == 6 || mode == 7) && !small_trace) {
         // octant queues: depend on the sensor table only, rebuilt when it (or the traced range) changes
         const int wf = P.world_frame ? 1 : 0;
         if (c->units_epoch != c->sensors_epoch || c->units_first != first || c->units_count != count || c->units_world != wf) {
@@ -1060,7 +1078,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         P.counters = c->d_counters.as<unsigned long long>();
     }
     // per-tile entry lists (k_tile_entries): worth their launch from a few thousand 32-ray tiles on
-    if (mode >= 6 && c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units) {
+    if (mode >= 6 && c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units && !small_trace) {
         const int cap = c->opt_tile_entries;
         const int max_visits = c->opt_tile_visits > 0 ? c->opt_tile_visits : (16 * cap) / 5;
         P.tile_cap = cap;
@@ -1129,6 +1147,8 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
             if (timing) cudaEventRecord(c->ev[7], st);
         }
     }
+    if (small_trace) rc = 0;
+    else
 #ifdef LSB_LAB
     if (c->opt_stats) rc = launch_trace_mode<true>(c, P, n_units, mode);
     else
@@ -1720,7 +1740,7 @@ int lsb200_clone_scene(lsb200_ctx *src, int cuda_device, lsb200_ctx **out)
     dst->opt_morton_layout = src->opt_morton_layout; dst->opt_morton_aspect = src->opt_morton_aspect; dst->opt_chain = src->opt_chain;
     dst->opt_tile_w_log2 = src->opt_tile_w_log2; dst->opt_small_build = src->opt_small_build; dst->opt_tile_entries = src->opt_tile_entries;
     dst->opt_tile_visits = src->opt_tile_visits; dst->opt_tile_min_units = src->opt_tile_min_units;
-    dst->opt_watertight = src->opt_watertight; dst->opt_intensity = src->opt_intensity; dst->opt_fused_tree = src->opt_fused_tree; dst->opt_lane_refill = src->opt_lane_refill; dst->opt_returns = src->opt_returns;
+    dst->opt_watertight = src->opt_watertight; dst->opt_intensity = src->opt_intensity; dst->opt_fused_tree = src->opt_fused_tree; dst->opt_lane_refill = src->opt_lane_refill; dst->opt_returns = src->opt_returns; dst->opt_small_trace_units = src->opt_small_trace_units;
     dst->log_fn = src->log_fn; dst->log_user = src->log_user;
     for (size_t i = 0; i < src->sensors.size(); ++i) {
         const Sensor &s = src->sensors[i];

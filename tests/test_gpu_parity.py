@@ -38,9 +38,11 @@ def sort_rows(p):
     return p[np.lexsort(w.T[::-1])]
 
 
+@pytest.mark.parametrize("small_trace_units", [512, 0])     # one thread per ray (k_trace_small, the default at this size) / the persistent queue kernel
 @pytest.mark.parametrize("uid,n_ground,n_both", [("0000", 1668, 1781), ("0001", 1633, 1769)])
-def test_xt32_reference_counts_and_golden(meshes, golden, uid, n_ground, n_both):
+def test_xt32_reference_counts_and_golden(meshes, golden, uid, n_ground, n_both, small_trace_units):
     ctx = make_ctx(uid)
+    ctx.set_option(capi.OPT_SMALL_TRACE_UNITS, small_trace_units)
     add_mesh(ctx, "ground", meshes["ground_v"], meshes["ground_t"])
     assert ctx.commit_scene() == 0
     rc, pts = ctx.trace_scene(0, capi.TRACE_ORDERED)
