@@ -38,9 +38,9 @@ __device__ __forceinline__ float dot3_eigen(float a0, float b0, float a1, float 
 // SRC/MeshTransformer.cpp:187-188, SRC/LidarDevice.cpp:383-391.  One thread per vertex of the whole scene;
 // block-reduced scene bounds (needed to normalise the Morton codes) go to `bounds` with ordered-uint atomics.
 __device__ __forceinline__ void transform_vertex(const SceneDev &S, int sensor_frame, const float *__restrict__ RinvT, int j,
-                                                 float &x, float &y, float &z)
+                                                 float &x, float &y, float &z, int geom_hint = -1)
 {
-    const int gi = find_geom_by_vert(S.geoms, S.n_geoms, j);
+    const int gi = geom_hint >= 0 ? geom_hint : find_geom_by_vert(S.geoms, S.n_geoms, j);
     const GeomDesc &G = S.geoms[gi];
     const float *src = reinterpret_cast<const float *>(G.verts + (size_t)(j - G.vert_off) * (size_t)G.stride);
     const float px = __ldg(src), py = __ldg(src + 1), pz = __ldg(src + 2);
@@ -60,9 +60,17 @@ __global__ void __launch_bounds__(256) k_transform(SceneDev S, int sensor_frame,
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    // vertices are numbered geometry by geometry: almost every block lies inside ONE geometry, found once per block
+    __shared__ int s_geom;
+    if (threadIdx.x == 0) {
+        const int j0 = blockIdx.x * blockDim.x, j1 = min(j0 + (int)blockDim.x, S.n_verts) - 1;
+        const int g0 = find_geom_by_vert(S.geoms, S.n_geoms, j0);
+        s_geom = (g0 == find_geom_by_vert(S.geoms, S.n_geoms, j1)) ? g0 : -1;
+    }
+    __syncthreads();
     if (j < S.n_verts) {
         float x, y, z;
-        transform_vertex(S, sensor_frame, RinvT, j, x, y, z);
+        transform_vertex(S, sensor_frame, RinvT, j, x, y, z, s_geom);
         lo[0] = hi[0] = x; lo[1] = hi[1] = y; lo[2] = hi[2] = z;
     }
 #pragma unroll
@@ -87,9 +95,9 @@ __global__ void __launch_bounds__(256) k_transform(SceneDev S, int sensor_frame,
 
 // Vertex ids (into the concatenated vertex array) of global triangle g.  Quads (v0 v1 v2 v3) are split like
 // Embree does: (v0 v1 v3) and (v2 v3 v1).
-__device__ __forceinline__ void tri_vertex_ids(const SceneDev &S, int g, int &a, int &b, int &c)
+__device__ __forceinline__ void tri_vertex_ids(const SceneDev &S, int g, int &a, int &b, int &c, int geom_hint = -1)
 {
-    const int gi = find_geom_by_tri(S.geoms, S.n_geoms, g);
+    const int gi = geom_hint >= 0 ? geom_hint : find_geom_by_tri(S.geoms, S.n_geoms, g);
     const GeomDesc &G = S.geoms[gi];
     const int k = g - G.tri_off;
     if (G.verts_per_elem == 3) {
@@ -188,10 +196,11 @@ __device__ __forceinline__ uint32_t morton_lookup(const MortonTables &T, int a, 
     return T.tab[a][0][i & 15u] | T.tab[a][1][(i >> 4) & 15u] | T.tab[a][2][(i >> 8) & 15u] | T.tab[a][3][(i >> 12) & 15u];
 }
 
-__device__ __forceinline__ uint32_t morton_key(const SceneDev &S, int g, const float slo[3], const float shi[3], const MortonTables &P)
+__device__ __forceinline__ uint32_t morton_key(const SceneDev &S, int g, const float slo[3], const float shi[3], const MortonTables &P,
+                                               int geom_hint = -1)
 {
     int a, b, c;
-    tri_vertex_ids(S, g, a, b, c);
+    tri_vertex_ids(S, g, a, b, c, geom_hint);
     const float4 A = S.xverts[a], B = S.xverts[b], C = S.xverts[c];
     const float cx = 0.5f * (fminf(A.x, fminf(B.x, C.x)) + fmaxf(A.x, fmaxf(B.x, C.x)));
     const float cy = 0.5f * (fminf(A.y, fminf(B.y, C.y)) + fmaxf(A.y, fmaxf(B.y, C.y)));
@@ -220,13 +229,19 @@ __global__ void k_morton_plan(SceneDev S)
 __global__ void __launch_bounds__(256) k_morton(SceneDev S)
 {
     __shared__ MortonTables s_plan;
+    __shared__ int s_geom;                   // the one geometry this block's triangles belong to, or -1 (see k_transform)
     morton_tables_fill(*S.plan, s_plan, threadIdx.x);
+    if (threadIdx.x == 255) {
+        const int g0 = blockIdx.x * blockDim.x, g1 = min(g0 + (int)blockDim.x, S.n_tris) - 1;
+        const int q0 = find_geom_by_tri(S.geoms, S.n_geoms, g0);
+        s_geom = (q0 == find_geom_by_tri(S.geoms, S.n_geoms, g1)) ? q0 : -1;
+    }
     __syncthreads();
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= S.n_tris) return;
     const float slo[3] = {ord2f(S.bounds[0]), ord2f(S.bounds[1]), ord2f(S.bounds[2])};
     const float shi[3] = {ord2f(S.bounds[3]), ord2f(S.bounds[4]), ord2f(S.bounds[5])};
-    S.keys[g] = morton_key(S, g, slo, shi, s_plan);
+    S.keys[g] = morton_key(S, g, slo, shi, s_plan, s_geom);
     S.vals[g] = (uint32_t)g;
 }
 
