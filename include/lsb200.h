@@ -119,7 +119,7 @@ enum {
                                       (a lane whose ray has ended takes the next ray of the queue: ballot + rank, unit lists in a
                                       shared-memory ring) instead of one 32-ray unit per warp at a time.  bit 0 = sign-mixed units,
                                       1 = upward octants, 2 = heavy (grazing) fronts of the downward octants, 3 = their light
-                                      remainders.  Default 0 (off): measured slower on the 10 M-triangle city, see DESIGN.md / profiles/design_choices_r02.md --
+                                      remainders.  Built into liblsb200_lab.so only; default 0 (off): measured slower on the 10 M-triangle city, see DESIGN.md / profiles/design_choices_r02.md --
                                       the traversal is bound by instruction issue and dependent round trips per unit, and the refill
                                       loop costs more instructions than the idle lanes it fills.  Same per-ray results either way. */
     LSB200_OPT_RETURNS = 22,       /* returns per ray: 1 (default, what the reference produces) or 2 = dual return -- every trace also

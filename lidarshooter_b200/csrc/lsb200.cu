@@ -387,7 +387,12 @@ int lsb200_set_option(lsb200_ctx *c, int option, int value)
     case LSB200_OPT_SMALL_BUILD: c->opt_small_build = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_SMALL_TRACE_UNITS: if (value < 0) break; c->opt_small_trace_units = value; return LSB200_OK;
     case LSB200_OPT_RETURNS: if (value < 1 || value > 2) break; c->opt_returns = value; return LSB200_OK;
-    case LSB200_OPT_LANE_REFILL: if (value < 0 || value > 15) break; c->opt_lane_refill = value; return LSB200_OK;
+    case LSB200_OPT_LANE_REFILL:
+        if (value < 0 || value > 15) break;
+#if !LSB_REFILL
+        if (value) return fail(c, LSB200_ERR_INVALID, "lane refill is built into liblsb200_lab.so only (measured slower, see DESIGN.md)");
+#endif
+        c->opt_lane_refill = value; return LSB200_OK;
     case LSB200_OPT_FUSED_TREE: c->opt_fused_tree = value ? 1 : 0; c->topology_dirty = true; return LSB200_OK;
     case LSB200_OPT_TILE_WIDTH: {
         int w = 0;

@@ -959,6 +959,13 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
 // and list are prefetched into a free slot with cp.async while the current one is being dealt out.  Hits are
 // appended per finishing group (match.any on the sensor, one atomic per sensor and round).  Per-ray arithmetic,
 // culling rules and result stores are those of trace_ray_lz / process_unit: same t, same triangle id.
+#ifndef LSB_REFILL
+#ifdef LSB_LAB
+#define LSB_REFILL 1             // measured slower (design log 18): compiled into liblsb200_lab.so only, like the other rejected variants
+#else
+#define LSB_REFILL 0
+#endif
+#endif
 #ifndef LSB_REFILL_RING
 #define LSB_REFILL_RING 4
 #endif
@@ -1222,7 +1229,7 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     for (int k = 0; k < 6; ++k) smax = fmaxf(smax, fabsf(ord2f(__ldg(P.bounds + k))));
 
     const unsigned lane = lane_id();
-    __shared__ float4 s_lists[(MODE >= 6) ? kTraceThreads / 32 : 1][(MODE >= 6) ? kRing * 2 * kMaxTileEntries : 1];      // per warp: 2 list buffers (run_phase) / a ring of kRing (run_phase_refill)
+    __shared__ float4 s_lists[(MODE >= 6) ? kTraceThreads / 32 : 1][(MODE >= 6) ? (LSB_REFILL ? kRing : 2) * 2 * kMaxTileEntries : 1];      // per warp: 2 list buffers (run_phase) / a ring of kRing (run_phase_refill)
     float4 *s_list = s_lists[(MODE >= 6) ? (threadIdx.x >> 5) : 0];
     __shared__ int4 s_uds[(MODE == 6) ? kTraceThreads / 32 : 1][kRing];
     int4 *s_ud = s_uds[(MODE == 6) ? (threadIdx.x >> 5) : 0];
@@ -1233,7 +1240,7 @@ __global__ void __launch_bounds__(kTraceThreads, LSB_TRACE_CTAS) k_trace(TracePa
     // (run_phase_refill: MODE 6 with tile lists, per group of queues as P.refill says)
 #define LSB_PHASE(OCTV, PART) do { \
         bool refilled_ = false; \
-        if constexpr (MODE == 6 && !STATS && LSB_LAZY_LIST != 0 && ((OCTV) < 8 || LSB_MIXED_TILE_LISTS != 0)) { \
+        if constexpr (LSB_REFILL != 0 && MODE == 6 && !STATS && LSB_LAZY_LIST != 0 && ((OCTV) < 8 || LSB_MIXED_TILE_LISTS != 0)) { \
             const int group_ = (OCTV) == 8 ? 0 : ((OCTV) < 4 ? 1 : ((PART) == 2 ? 3 : 2)); \
             if (P.tile_counts != nullptr && ((P.refill >> group_) & 1)) { \
                 run_phase_refill<OCTV, WT>(P, smax, lane, s_list, s_ud, s_stack, PART); \

@@ -400,7 +400,7 @@ def test_lane_refill_small_city_vs_oracle_bvh(refill):
     meshes = synth.city(n_boxes=380, ground_cells=200, extent=20 * synth.CITY_PITCH, n_groups=4, lots=20)
     poses = synth.sensor_lattice(2, 10 * synth.CITY_PITCH)
     elev, b, e, H = synth.lidar_table(30, 721)
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)       # the refill phases are compiled into the lab library only
     ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
     ctx.set_option(capi.OPT_LANE_REFILL, refill)
     for k, (q, t) in enumerate(poses):

@@ -26,7 +26,7 @@ def main():
     meshes, poses, table = build_workload(args.small)
     elev, b, e, H = table
     ns = len(poses)
-    ctx = capi.Context(0, capi.FRAME_WORLD)
+    ctx = capi.Context(0, capi.FRAME_WORLD, lab=True)      # run_phase_refill lives in the lab library
     if args.small:
         ctx.set_option(capi.OPT_TILE_MIN_UNITS, 0)
     for k, (q, t) in enumerate(poses):
