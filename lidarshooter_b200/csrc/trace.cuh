@@ -83,6 +83,17 @@ enum TraceCounter { kCntRays = 0, kCntNodes, kCntLeaves, kCntTris, kCntUnitsUnif
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// One lane's atomic add as the plain instruction.  atomicAdd() on a global address lets nvcc wrap the call in its
+// warp-aggregation sequence (activemask, match, leader election, popc, shuffle: ~25 instructions) even when the call
+// site already runs in exactly one lane -- the traversal's ticket and hit-append atomics are such sites (2.4 % of
+// k_trace's instructions, profiles/ncu_r02 source view).
+__device__ __forceinline__ uint32_t atom_add_u32(uint32_t *p, uint32_t v)
+{
+    uint32_t old;
+    asm volatile("atom.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -111,6 +122,9 @@ __device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_
 #ifndef LSB_NODE_EVICT_LAST
 #define LSB_NODE_EVICT_LAST 1
 #endif
+#ifndef LSB_BRANCHY_INTERSECT
+#define LSB_BRANCHY_INTERSECT 0   // 1: Moeller-Trumbore with its five early exits (round 1); 0: one predicate
+#endif
 // L2 eviction priority for the BVH nodes (the results stream through L2 with evict-first stores)
 __device__ __forceinline__ uint64_t l2_policy_evict_last()
 {
@@ -134,6 +148,19 @@ __device__ __forceinline__ float2 ldg_f2_hint(const float2 *a, uint64_t pol)
 struct Ray {
     float ox, oy, oz, dx, dy, dz;
 };
+#ifndef LSB_EXACT_RCP
+#define LSB_EXACT_RCP 1          // 1: IEEE 1 / d for the slab set-up; 0: MUFU.RCP (measured: no gain, 10 344 - 10 410 vs 10 312 - 10 380 Mrays/s)
+#endif
+__device__ __forceinline__ float rcp_approx(float x)
+{
+#if LSB_EXACT_RCP
+    return 1.0f / x;
+#else
+    float y;
+    asm("rcp.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+#endif
+}
 template <bool WT = false>
 __device__ __forceinline__ void brute_ray(const TraceParams &P, const Ray &r, float &best, int &bi);   // depth-guard fallback
 constexpr int kRayOverflow = -2;       // trace_ray_lz: "my stack overflowed" (never a triangle id)
@@ -155,6 +182,7 @@ __device__ __forceinline__ bool intersect_tri(const float4 q0, const float4 q1, 
     float U = __fadd_rn(__fadd_rn(__fmul_rn(rx, e2x), __fmul_rn(ry, e2y)), __fmul_rn(rz, e2z));
     float V = __fadd_rn(__fadd_rn(__fmul_rn(rx, e1x), __fmul_rn(ry, e1y)), __fmul_rn(rz, e1z));
     if (neg) { U = -U; V = -V; }
+#if LSB_BRANCHY_INTERSECT
     if (!(den != 0.0f)) return false;
     if (!(U >= 0.0f)) return false;
     if (!(V >= 0.0f)) return false;
@@ -166,6 +194,18 @@ __device__ __forceinline__ bool intersect_tri(const float4 q0, const float4 q1, 
     if (!(t <= 3.402823466e+38f)) return false;            // tfar = +inf; rejects inf / NaN
     t_out = t;
     return true;
+#else
+    // the same tests as one predicate: in a warp whose lanes test different triangles the five early exits save nothing
+    // (some lane always goes on) and cost a divergence stack push / pop each -- 16 % of k_trace's instructions were
+    // BRA / BSSY / BSYNC / BREAK.  Same arithmetic, same accept set: den = 0 gives t = NaN or inf, rejected by the last test.
+    float T = __fadd_rn(__fadd_rn(__fmul_rn(ngx, cx), __fmul_rn(ngy, cy)), __fmul_rn(ngz, cz));
+    if (neg) T = -T;
+    const float t = __fdiv_rn(T, absDen);
+    const bool ok = (den != 0.0f) & (U >= 0.0f) & (V >= 0.0f) & (__fadd_rn(U, V) <= absDen) & (__fmul_rn(absDen, 0.0f) < T) &
+                    (t <= 3.402823466e+38f);
+    t_out = t;
+    return ok;
+#endif
 }
 
 // Watertight ray / triangle test (Woop, Benthin, Wald 2013, "Watertight Ray/Triangle Intersection"), the optional
@@ -452,10 +492,12 @@ __device__ __forceinline__ void trace_ray_lz(const TraceParams &P, float eps, co
                                              const float4 *__restrict__ chain, int n_chain, bool reversed,
                                              float &best_out, int &bi_out, RayStats &rs, int2 *s_stack = nullptr)
 {
+    // 1 / d only feeds the BOX tests (rcp_approx: IEEE by default; the MUFU.RCP form would be safe -- <= 1.2e-7 relative
+    // against a box padding of 8e-6 x the scene's extent -- but measured no faster, so the exact quotient stays)
     const float tiny = 1e-30f;
-    const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
-    const float iy = 1.0f / (fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
-    const float iz = 1.0f / (fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
+    const float ix = rcp_approx(fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
+    const float iy = rcp_approx(fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
+    const float iz = rcp_approx(fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
     const float ax = -(r.ox + eps) * ix, ay = -(r.oy + eps) * iy, az = -(r.oz + eps) * iz;
     const float bx = -(r.ox - eps) * ix, by = -(r.oy - eps) * iy, bz = -(r.oz - eps) * iz;
     constexpr int kDone = 0x7fffffff;       // never a node index (n_tris < 2^28)
@@ -855,12 +897,12 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
                     hit_point(S, P.flags, best, dsx, dsy, dsz, x, y, z);
                     s_pts[lane] = make_float4(x, y, z, __int_as_float((P.flags & 2u) ? 0 : v));
                 }
-                if (lane == (unsigned)(__ffs(m) - 1)) pend->raw = atomicAdd(S.count, (uint32_t)__popc(m));
+                if (lane == (unsigned)(__ffs(m) - 1)) pend->raw = atom_add_u32(S.count, (uint32_t)__popc(m));
                 pend->mask = m; pend->sensor = si;
             }
         } else if (m) {
             uint32_t base = 0;
-            if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(S.count, (uint32_t)__popc(m));
+            if (lane == (unsigned)(__ffs(m) - 1)) base = atom_add_u32(S.count, (uint32_t)__popc(m));
             base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
             if (hit) {
                 float x, y, z;
@@ -913,7 +955,7 @@ __device__ __forceinline__ void run_phase(const TraceParams &P, float smax, unsi
     const int lo = part == 2 ? n_front : 0, hi = part == 1 ? n_front : count;
     if (lo >= hi) return;
     uint32_t *ctr = &P.work[(part == 2 ? 11 : 2) + OCT];
-    auto ticket = [&]() -> int { return lane == 0 ? lo + (int)atomicAdd(ctr, 1u) : 0; };
+    auto ticket = [&]() -> int { return lane == 0 ? lo + (int)atom_add_u32(ctr, 1u) : 0; };
     auto fetch = [&](int k, int4 &ud, int &tn, float4 *buf) {     // descriptor, list size and list of queue entry k
         ud = __ldg(P.unit_list + begin + k);
         tn = kTileFallback;                                        // raw list size; looked at when the unit's turn comes
@@ -989,7 +1031,7 @@ __device__ __forceinline__ void run_phase_refill(const TraceParams &P, float sma
     const int lo = part == 2 ? n_front : 0, hi = part == 1 ? n_front : count;
     if (lo >= hi) return;
     uint32_t *ctr = &P.work[(part == 2 ? 11 : 2) + OCT];
-    auto ticket = [&]() -> int { return lane == 0 ? lo + (int)atomicAdd(ctr, 1u) : 0; };
+    auto ticket = [&]() -> int { return lane == 0 ? lo + (int)atom_add_u32(ctr, 1u) : 0; };
     // descriptor (+ list size in .w) and list of queue entry k into ring slot `slot`
     auto fetch = [&](int k, int slot) {
         if (lane == 0) {
@@ -1177,7 +1219,7 @@ __device__ __forceinline__ void run_phase_refill(const TraceParams &P, float sma
                 const unsigned m = __match_any_sync(hm, si);
                 const int leader = __ffs(m) - 1;
                 uint32_t base = 0;
-                if ((int)lane == leader) base = atomicAdd(S.count, (uint32_t)__popc(m));
+                if ((int)lane == leader) base = atom_add_u32(S.count, (uint32_t)__popc(m));
                 base = __shfl_sync(m, base, leader);
                 Ray r2; float dsx, dsy, dsz, omax, x, y, z;
                 make_ray(S, P.world_frame, v, h, r2, dsx, dsy, dsz, omax);
@@ -1850,7 +1892,7 @@ __global__ void __launch_bounds__(128) k_trace_small(TraceParams P, int sensor_b
         if (m) {
             const unsigned lane = lane_id();
             uint32_t base = 0;
-            if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(S.count, (uint32_t)__popc(m));
+            if (lane == (unsigned)(__ffs(m) - 1)) base = atom_add_u32(S.count, (uint32_t)__popc(m));
             base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
             if (hit) {
                 float x, y, z;
