@@ -122,6 +122,9 @@ __device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_
 #ifndef LSB_NODE_EVICT_LAST
 #define LSB_NODE_EVICT_LAST 1
 #endif
+#ifndef LSB_LEAF_PAIR
+#define LSB_LEAF_PAIR 0          // 1: leaves of <= 2 triangles load both records before testing either
+#endif
 #ifndef LSB_BRANCHY_INTERSECT
 #define LSB_BRANCHY_INTERSECT 0   // 1: Moeller-Trumbore with its five early exits (round 1); 0: one predicate
 #endif
@@ -259,6 +262,35 @@ __device__ __forceinline__ void test_leaf(const TraceParams &P, int ref, const R
     const int enc = ~ref;
     const int first = enc & ((1 << kLeafShift) - 1);
     const int count = (enc >> kLeafShift) + 1;
+#if LSB_LEAF_PAIR == 2
+    // the second record of a two-triangle leaf is requested (into L1, no registers) while the first is loaded and tested
+    if (count >= 2) {
+        const float4 *nx = P.tris + 3 * (size_t)first + 3;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + 2));
+    }
+#endif
+#if LSB_LEAF_PAIR == 1
+    if (count <= 2) {
+        // the default leaf holds one or two triangles: both records are requested before either is tested, so a leaf costs
+        // ONE memory round trip instead of two, and there is no loop to diverge on
+        const float4 *rec = P.tris + 3 * (size_t)first;
+        const bool two = count == 2;
+        const float4 a0 = __ldg(rec), a1 = __ldg(rec + 1), a2 = __ldg(rec + 2);
+        const int ga = __ldg(P.leaf_ids + first);
+        float4 b0 = a0, b1 = a1, b2 = a2;
+        int gb = ga;
+        if (two) { b0 = __ldg(rec + 3); b1 = __ldg(rec + 4); b2 = __ldg(rec + 5); gb = __ldg(P.leaf_ids + first + 1); }
+        float t;
+        if ((WT ? intersect_tri_wt(a0, a1, a2, r, t) : intersect_tri(a0, a1, a2, r, t)) && t <= best) {
+            if (t < best || ga < bi) { best = t; bi = ga; }
+        }
+        if (two && (WT ? intersect_tri_wt(b0, b1, b2, r, t) : intersect_tri(b0, b1, b2, r, t)) && t <= best) {
+            if (t < best || gb < bi) { best = t; bi = gb; }
+        }
+        return;
+    }
+#endif
     for (int k = 0; k < count; ++k) {
         const float4 *rec = P.tris + 3 * (size_t)(first + k);
 #if LSB_NODE_EVICT_LAST >= 2
