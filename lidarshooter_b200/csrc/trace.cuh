@@ -843,7 +843,9 @@ __device__ __forceinline__ void process_unit(const TraceParams &P, const float4 
                                              unsigned lane, int tile_n = -1, const float4 *s_list = nullptr,
                                              PendingAppend *pend = nullptr, float4 *s_pts = nullptr, int2 *s_stack = nullptr)
 {
+#ifdef LSB_LAB
     constexpr bool TOP = (MODE == 4);
+#endif
     const int si = ud.x;
     const SensorDev &S = P.sensors[si];
     int v, h;
@@ -1772,7 +1774,6 @@ __global__ void __launch_bounds__(128) k_super_entries(TraceParams P, int s_firs
     if (sup >= sup_hi) return;
     const int si = find_sensor_by_super(P.sensors, s_first, s_first + s_count - 1, sup);
     const SensorDev &S = P.sensors[si];
-    const int local = sup - S.sup_base;
     const float4 iv0 = __ldg(P.sup_iv + 2 * (size_t)sup), iv1 = __ldg(P.sup_iv + 2 * (size_t)sup + 1);
     const float dlo[3] = {iv0.x, iv0.y, iv0.z}, dhi[3] = {iv1.x, iv1.y, iv1.z};
     const int cls = __float_as_int(iv0.w);
