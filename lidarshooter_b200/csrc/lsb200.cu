@@ -681,11 +681,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
         const size_t ns = c->sensors.size();
         bool all_set = ns > 0;
         for (const Sensor &sn : c->sensors) all_set = all_set && sn.set;
-        int units_total = 0;
-        for (const Sensor &sn : c->sensors) units_total += ((sn.V + (32 >> c->opt_tile_w_log2) - 1) / (32 >> c->opt_tile_w_log2)) * ((sn.H + (1 << c->opt_tile_w_log2) - 1) >> c->opt_tile_w_log2);
-        const bool chains_unused = c->opt_traversal == 6 && !c->opt_stats && units_total < c->opt_small_trace_units &&
-                                   !(c->opt_tile_entries >= 2 && units_total >= c->opt_tile_min_units);      // k_trace_small starts at the root
-        if (c->opt_chain && all_set && ns <= 8 && c->opt_traversal != 3 && !chains_unused) {
+        if (c->opt_chain && all_set && ns <= 8 && c->opt_traversal != 3) {
             LSB_CU(c, c->d_chains.reserve(ns * 9 * 2 * kMaxChain * sizeof(float4), st));
             LSB_CU(c, c->d_chain_counts.reserve(ns * 9 * 4, st));
             args.n_origins = (int)ns; args.chains = c->d_chains.as<float4>(); args.chain_counts = c->d_chain_counts.as<int>();
@@ -1020,16 +1016,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
     // (not when per-tile entry lists were asked for at this size -- LSB200_OPT_TILE_MIN_UNITS lowered by the caller)
     const bool lists_wanted = c->opt_chain && c->opt_tile_entries >= 2 && n_units >= c->opt_tile_min_units;
     const bool small_trace = mode == 6 && !c->opt_stats && n_units < c->opt_small_trace_units && !lists_wanted;
-    if (small_trace) {
-        int max_r = 0;
-        for (int i = first; i < first + count; ++i) max_r = std::max(max_r, c->sensors[i].n_rays());
-        dim3 grid((unsigned)((max_r + 127) / 128), (unsigned)count);
-        if (c->built_watertight) k_trace_small<true><<<grid, 128, 0, st>>>(P, first);
-        else k_trace_small<false><<<grid, 128, 0, st>>>(P, first);
-        count_launch(c);
-        c->stats.trace_grid = (int)(grid.x * grid.y); c->stats.trace_block = 128;
-    }
-    if (c->opt_chain && mode != 3 && !small_trace) {
+    if (c->opt_chain && mode != 3) {
         // origin chains: one list per sensor, valid for this BVH and these sensor poses
         const size_t ns = c->sensors.size();
         if (c->chain_commit_epoch != c->commit_epoch || c->chain_sensors_epoch != c->sensors_epoch) {
@@ -1044,6 +1031,18 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         }
         P.chains = c->d_chains.as<float4>();
         P.chain_counts = c->d_chain_counts.as<int>();
+    }
+    if (small_trace) {
+        int max_r = 0;
+        for (int i = first; i < first + count; ++i) max_r = std::max(max_r, c->sensors[i].n_rays());
+        // rays per warp: as few as keeps the launch within ~32 warps per SM (an XT-32 scan: one ray per warp)
+        int spread = 0;
+        while (spread < 5 && ((int64_t)max_r * count << (spread + 1)) <= (int64_t)c->sm_count * 32 * 32) ++spread;
+        dim3 grid((unsigned)((((int64_t)max_r << spread) + 127) / 128), (unsigned)count);
+        if (c->built_watertight) k_trace_small<true><<<grid, 128, 0, st>>>(P, first, spread);
+        else k_trace_small<false><<<grid, 128, 0, st>>>(P, first, spread);
+        count_launch(c);
+        c->stats.trace_grid = (int)(grid.x * grid.y); c->stats.trace_block = 128;
     }
     if ((mode == 0 || mode == 6 || mode == 7) && !small_trace) {
         // octant queues: depend on the sensor table only, rebuilt when it (or the traced range) changes

@@ -1850,16 +1850,22 @@ __global__ void __launch_bounds__(kTileBlock) k_tile_entries(TraceParams P, int 
 // A single XT-32 scan is 4 800 rays = 150 work units: the persistent kernel's machinery (444 CTAs that mostly find no
 // work, ticket / descriptor / list fetches, origin chains read ray by ray) is pure latency at that size (50 - 55 us per
 // launch, design log 6).  Launches of fewer than LSB200_OPT_SMALL_TRACE_UNITS units take this kernel instead: one thread
-// per ray, 128-thread CTAs spread over the SMs, depth-first walk from the root (near child first, deferred children
-// carry their entry distance), generic slab test.  Same conservative culling, same intersector, same stores and the same
+// per ray, 128-thread CTAs spread over the SMs, the shipped lazy-list traversal (trace_ray_lz) started from the sensor's
+// origin chain, generic slab test.  Same conservative culling, same intersector, same stores and the same
 // warp-aggregated append as process_unit: identical per-ray results.  grid.y = sensor of the batch.
 template <bool WT>
-__global__ void __launch_bounds__(128) k_trace_small(TraceParams P, int sensor_base)
+__global__ void __launch_bounds__(128) k_trace_small(TraceParams P, int sensor_base, int spread_log2)
 {
+    // trace_ray_lz keeps the first LSB_SMEM_STACK stack entries of a thread at s_stack[d * kTraceThreads]
+    __shared__ int2 s_stack_buf[(LSB_SMEM_STACK ? LSB_SMEM_STACK : 1) * kTraceThreads];
     const int si = sensor_base + blockIdx.y;
     const SensorDev &S = P.sensors[si];
-    const int ray = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = ray < S.n_rays;
+    // Only every 2^spread-th lane carries a ray.  An XT-32's neighbouring rays are 2.4 degrees apart: 32 of them in one warp
+    // walk 32 different paths one after the other (3 000 warp instructions at ~29 cycles each = 45 us, with the machine
+    // otherwise empty); spread over 32 warps the same rays run side by side.
+    const int gthread = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ray = gthread >> spread_log2;
+    const bool valid = ray < S.n_rays && (gthread & ((1 << spread_log2) - 1)) == 0;
     const int v = valid ? ray / S.H : 0, h = valid ? ray - v * S.H : 0;
     const bool fired = valid && (S.az_mask == nullptr || __ldg(S.az_mask + h) != 0);
     float best = INFINITY; int bi = -1;
@@ -1871,51 +1877,15 @@ __global__ void __launch_bounds__(128) k_trace_small(TraceParams P, int sensor_b
         Ray r; float omax;
         make_ray(S, P.world_frame, v, h, r, dsx, dsy, dsz, omax);
         const float eps = 8e-6f * (smax + omax) + 1e-30f;
-        const float tiny = 1e-30f;
-        const float ix = 1.0f / (fabsf(r.dx) < tiny ? copysignf(tiny, r.dx) : r.dx);
-        const float iy = 1.0f / (fabsf(r.dy) < tiny ? copysignf(tiny, r.dy) : r.dy);
-        const float iz = 1.0f / (fabsf(r.dz) < tiny ? copysignf(tiny, r.dz) : r.dz);
-        const float ax = -(r.ox + eps) * ix, ay = -(r.oy + eps) * iy, az = -(r.oz + eps) * iz;
-        const float bx = -(r.ox - eps) * ix, by = -(r.oy - eps) * iy, bz = -(r.oz - eps) * iz;
-        int2 stack[kStackSize];
-        int sp = 0;
-        bool overflow = false;
-        float far_lim = INFINITY;
-        constexpr int kDone = 0x7fffffff;
-        int cur = P.top_cap;                         // Karras node 0
-        auto pop_next = [&]() {
-            cur = kDone;
-            while (sp > 0) {
-                const int2 e = stack[--sp];
-                if (__int_as_float(e.y) <= far_lim * 1.0000005f) { cur = e.x; break; }
-            }
-        };
-        while (cur != kDone) {
-            if (cur < 0) {
-                test_leaf<WT>(P, cur, r, best, bi);
-                far_lim = best * 1.0000005f;
-                pop_next();
-                continue;
-            }
-            const float4 *n = P.nodes + 4 * (size_t)cur;
-            const float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
-            const float2 q3 = __ldg(reinterpret_cast<const float2 *>(n + 3));
-            float n0, f0, n1, f1;
-            slab_nf<8>(fmaf(q0.x, ix, ax), fmaf(q0.y, ix, bx), fmaf(q0.z, iy, ay), fmaf(q0.w, iy, by),
-                       fmaf(q2.x, iz, az), fmaf(q2.y, iz, bz), far_lim, n0, f0);
-            slab_nf<8>(fmaf(q1.x, ix, ax), fmaf(q1.y, ix, bx), fmaf(q1.z, iy, ay), fmaf(q1.w, iy, by),
-                       fmaf(q2.z, iz, az), fmaf(q2.w, iz, bz), far_lim, n1, f1);
-            const bool hit0 = n0 <= f0, hit1 = n1 <= f1;
-            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-            if (hit0 && hit1) {
-                const bool swap = n1 < n0;
-                if (sp < kStackSize) stack[sp++] = make_int2(swap ? c0 : c1, __float_as_int(swap ? n0 : n1)); else overflow = true;
-                cur = swap ? c1 : c0;
-            } else if (hit0) cur = c0;
-            else if (hit1) cur = c1;
-            else pop_next();
-        }
-        if (overflow) brute_ray_cold<WT>(P.tris, P.leaf_ids, P.n_tris, r, best, bi);      // depth guard tripped
+        // the sensor's origin chain for the ray's own octant (the entries no ray of these signs can reach are already
+        // dropped) replaces the ~17-level descent from the root by a handful of box tests: at this size a ray is one
+        // dependent instruction stream with nothing to hide its latency behind, so fewer instructions per ray is what counts
+        const int list = si * 9 + ray_octant(r);
+        const int n_chain = P.chain_counts ? __ldg(P.chain_counts + list) : 0;
+        RayStats rs{0u, 0u, 0u, 0u, 0u, 0u};
+        trace_ray_lz<8, false, false, WT>(P, eps, r, P.chains + (size_t)list * (2 * kMaxChain), n_chain, false, best, bi, rs,
+                                          s_stack_buf + threadIdx.x);
+        if (bi == kRayOverflow) brute_ray_cold<WT>(P.tris, P.leaf_ids, P.n_tris, r, best, bi);      // depth guard tripped
         if (!(best <= S.max_range)) { best = INFINITY; bi = -1; }
     }
     if (valid) { S.t_out[ray] = best; S.tri_out[ray] = bi; }
