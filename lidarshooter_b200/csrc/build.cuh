@@ -491,34 +491,40 @@ __device__ __forceinline__ bool tree_merge(const SceneDev &S, Climber &c, bool l
 // rendezvous slot and an entry in the work list of phase 2 -- it does NOT wait or climb on, so the CTA retires as soon as
 // its local subtrees are done (threads that lingered in the global climb held whole warps: 29 % of the stall samples
 // of the one-kernel form, profiles/design_choices_r02.md).
-__global__ void __launch_bounds__(kTreeBlock) k_tree(SceneDev S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
-                                                     float4 *__restrict__ rendezvous /* [4 * n_tris] */,
-                                                     uint32_t *__restrict__ work /* [n_tris]: split << 1 | side */, uint32_t *__restrict__ work_count)
+// tree_block<B>: one block of B leaves [base, base + B) by B threads (all of them call it; it synchronises the CTA).
+// Used by k_tree (B = kTreeBlock, one block per CTA) and by the fused small build (B = 1024, a CTA's round).
+template <int B>
+struct TreeSmem {
+    uint32_t key[B + 2];              // codes of the leaves base - 1 .. base + B
+    int8_t delta[B + 1];              // delta of the boundaries base - 1 .. base + B - 1
+    int8_t sufmin[B + 2];
+    int8_t wpre[B / 32], wsuf[B / 32];
+    uint8_t local[B];                 // split base + t: its node lies inside this block
+    uint32_t flag[B];
+    uint32_t work[B];
+    uint32_t nwork, wbase;
+    float4 rxy[2 * B], rz[2 * B];     // per split: slot 0 = left child, slot 1 = right child
+};
+
+template <int B>
+__device__ __forceinline__ void tree_block(const SceneDev &S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
+                                           float4 *__restrict__ rendezvous, uint32_t *__restrict__ work, uint32_t *__restrict__ work_count,
+                                           int base, int t, TreeSmem<B> &M, bool ids_uncached)
 {
-    __shared__ uint32_t s_key[kTreeBlock + 2];          // codes of the leaves base - 1 .. base + kTreeBlock
-    __shared__ int8_t s_delta[kTreeBlock + 1];          // delta of the boundaries base - 1 .. base + kTreeBlock - 1
-    __shared__ int8_t s_sufmin[kTreeBlock + 2];
-    __shared__ int8_t s_wpre[kTreeBlock / 32], s_wsuf[kTreeBlock / 32];
-    __shared__ uint8_t s_local[kTreeBlock];             // split base + t: its node lies inside this block
-    __shared__ uint32_t s_flag[kTreeBlock];
-    __shared__ float4 s_rxy[2 * kTreeBlock], s_rz[2 * kTreeBlock];   // per split: slot 0 = left child, slot 1 = right child
-    __shared__ uint32_t s_work[kTreeBlock];
-    __shared__ uint32_t s_nwork, s_wbase;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int lane = t & 31, warp = t >> 5;
     const int n = S.n_tris;
-    const int base = blockIdx.x * kTreeBlock;
     const int i = base + t;
-    s_flag[t] = 0u;
-    if (t == 0) s_nwork = 0u;
-    for (int k = t; k < kTreeBlock + 2; k += kTreeBlock) {
+    M.flag[t] = 0u;
+    if (t == 0) M.nwork = 0u;
+    for (int k = t; k < B + 2; k += B) {
         const int j = base - 1 + k;
-        s_key[k] = (j >= 0 && j < n) ? __ldg(keys + j) : 0u;
+        M.key[k] = (j >= 0 && j < n) ? __ldcg(keys + j) : 0u;
     }
     __syncthreads();
     // delta of boundary b = t (leaves i - 1 | i); thread 0 also owns the block's last boundary
-    const int d_lo = boundary_delta(s_key[t], s_key[t + 1], i - 1, n);
-    s_delta[t] = (int8_t)d_lo;
-    if (t == 0) s_delta[kTreeBlock] = (int8_t)boundary_delta(s_key[kTreeBlock], s_key[kTreeBlock + 1], base + kTreeBlock - 1, n);
+    const int d_lo = boundary_delta(M.key[t], M.key[t + 1], i - 1, n);
+    M.delta[t] = (int8_t)d_lo;
+    if (t == 0) M.delta[B] = (int8_t)boundary_delta(M.key[B], M.key[B + 1], base + B - 1, n);
     // inclusive prefix / suffix minima of the deltas over the block's boundaries
     int pm = d_lo, sm = d_lo;
 #pragma unroll
@@ -527,64 +533,116 @@ __global__ void __launch_bounds__(kTreeBlock) k_tree(SceneDev S, const uint32_t 
         if (lane >= o) pm = min(pm, u);
         if (lane + o < 32) sm = min(sm, w);
     }
-    if (lane == 31) s_wpre[warp] = (int8_t)pm;
-    if (lane == 0) s_wsuf[warp] = (int8_t)sm;
+    if (lane == 31) M.wpre[warp] = (int8_t)pm;
+    if (lane == 0) M.wsuf[warp] = (int8_t)sm;
     __syncthreads();
-    for (int w = 0; w < warp; ++w) pm = min(pm, (int)s_wpre[w]);
-    for (int w = warp + 1; w < kTreeBlock / 32; ++w) sm = min(sm, (int)s_wsuf[w]);
-    sm = min(sm, (int)s_delta[kTreeBlock]);
-    s_sufmin[t] = (int8_t)sm;
-    if (t == 0) { s_sufmin[kTreeBlock] = s_delta[kTreeBlock]; s_sufmin[kTreeBlock + 1] = 127; }
+    for (int w = 0; w < warp; ++w) pm = min(pm, (int)M.wpre[w]);
+    for (int w = warp + 1; w < B / 32; ++w) sm = min(sm, (int)M.wsuf[w]);
+    sm = min(sm, (int)M.delta[B]);
+    M.sufmin[t] = (int8_t)sm;
+    if (t == 0) { M.sufmin[B] = M.delta[B]; M.sufmin[B + 1] = 127; }
     __syncthreads();
     {
         // split s = i separates the leaves i | i + 1 (boundary t + 1): its node [F, L] stays inside the block iff a
         // boundary with a shorter prefix stops it on either side before the block ends
-        const int d_s = s_delta[t + 1];
-        s_local[t] = (t + 1 < kTreeBlock && pm < d_s && (int)s_sufmin[t + 2] < d_s) ? 1 : 0;
+        const int d_s = M.delta[t + 1];
+        M.local[t] = (t + 1 < B && pm < d_s && (int)M.sufmin[t + 2] < d_s) ? 1 : 0;
     }
     __syncthreads();
     if (i < n) {
-        const Box6 leaf = leaf_record(S, (int)__ldg(sorted_ids + i), i);
-        Climber c{leaf.lox, leaf.hix, leaf.loy, leaf.hiy, leaf.loz, leaf.hiz, i, i, d_lo, (int)s_delta[t + 1]};
-        for (int level = 0; level < 96; ++level) {       // a block-local chain is at most kTreeBlock long; the bound only guards against a hang
+        const Box6 leaf = leaf_record(S, (int)(ids_uncached ? __ldcg(sorted_ids + i) : __ldg(sorted_ids + i)), i);
+        Climber c{leaf.lox, leaf.hix, leaf.loy, leaf.hiy, leaf.loz, leaf.hiz, i, i, d_lo, (int)M.delta[t + 1]};
+        for (int level = 0; level < 96; ++level) {       // a chain is at most the tree's depth (< 64) long; the bound only guards against a hang
             const bool left = c.dR > c.dL;               // this node is the left child of the split at L
             const int s = left ? c.L : c.F - 1;
             const int ls = s - base;
             const int mine = left ? 0 : 1;
             const float4 pxy = make_float4(c.lox, c.hix, c.loy, c.hiy);
             const float4 pz = make_float4(c.loz, c.hiz, __int_as_float(left ? c.F : c.L), __int_as_float(left ? c.dL : c.dR));
-            if (!(ls >= 0 && ls < kTreeBlock && s_local[ls])) {
+            if (!(ls >= 0 && ls < B && M.local[ls])) {
                 // the parent straddles blocks: park this subtree for phase 2
                 float4 *slot = rendezvous + 4 * (size_t)s + 2 * mine;
                 __stcg(slot, pxy);
                 __stcg(slot + 1, pz);
-                s_work[atomicAdd(&s_nwork, 1u)] = ((uint32_t)s << 1) | (uint32_t)mine;
+                M.work[atomicAdd(&M.nwork, 1u)] = ((uint32_t)s << 1) | (uint32_t)mine;
                 break;
             }
-            s_rxy[2 * ls + mine] = pxy;
-            s_rz[2 * ls + mine] = pz;
+            M.rxy[2 * ls + mine] = pxy;
+            M.rz[2 * ls + mine] = pz;
             __threadfence_block();
-            if (atomicAdd(&s_flag[ls], 1u) == 0u) break;           // first to arrive: the sibling finishes the node
+            if (atomicAdd(&M.flag[ls], 1u) == 0u) break;           // first to arrive: the sibling finishes the node
             __threadfence_block();
-            if (tree_merge(S, c, left, s, s_rxy[2 * ls + (mine ^ 1)], s_rz[2 * ls + (mine ^ 1)])) break;
+            if (tree_merge(S, c, left, s, M.rxy[2 * ls + (mine ^ 1)], M.rz[2 * ls + (mine ^ 1)])) break;
         }
     }
     __syncthreads();
-    const uint32_t nw = s_nwork;
-    if (t == 0 && nw) s_wbase = atomicAdd(work_count, nw);
+    const uint32_t nw = M.nwork;
+    if (t == 0 && nw) M.wbase = atomicAdd(work_count, nw);
     __syncthreads();
-    if ((uint32_t)t < nw) work[s_wbase + t] = s_work[t];
+    if ((uint32_t)t < nw) work[M.wbase + t] = M.work[t];
+}
+
+__global__ void __launch_bounds__(kTreeBlock) k_tree(SceneDev S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
+                                                     float4 *__restrict__ rendezvous /* [4 * n_tris] */,
+                                                     uint32_t *__restrict__ work /* [n_tris]: split << 1 | side */, uint32_t *__restrict__ work_count)
+{
+    __shared__ TreeSmem<kTreeBlock> M;
+    tree_block<kTreeBlock>(S, keys, sorted_ids, rendezvous, work, work_count, blockIdx.x * kTreeBlock, threadIdx.x, M, false);
 }
 
 // Phase 2: the nodes that straddle blocks (~1 % of the tree, its top).  One thread per parked subtree: arrival at the
 // global rendezvous slot (parity counters that are never re-zeroed, see k_fit), the second to arrive merges, writes the
 // node and carries on to the next split.
-__global__ void __launch_bounds__(128) k_tree_top(SceneDev S, float4 *__restrict__ rendezvous, const uint32_t *__restrict__ work,
-                                                  const uint32_t *__restrict__ work_count)
+__device__ __forceinline__ void tree_top_entry(const SceneDev &S, float4 *__restrict__ rendezvous, uint32_t w)
 {
-    const uint32_t nw = *work_count;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < nw; e += gridDim.x * blockDim.x) {
-        const uint32_t w = __ldg(work + e);
+    int s = (int)(w >> 1);
+    bool left = (w & 1u) == 0u;
+    Climber c;
+    {
+        const float4 *slot = rendezvous + 4 * (size_t)s + 2 * (left ? 0 : 1);
+        const float4 pxy = __ldcg(slot), pz = __ldcg(slot + 1);
+        c.lox = pxy.x; c.hix = pxy.y; c.loy = pxy.z; c.hiy = pxy.w; c.loz = pz.x; c.hiz = pz.y;
+        // only the fields the merge reads on this side are known -- and needed
+        c.F = left ? __float_as_int(pz.z) : s + 1; c.L = left ? s : __float_as_int(pz.z);
+        c.dL = left ? __float_as_int(pz.w) : 0; c.dR = left ? 0 : __float_as_int(pz.w);
+    }
+    bool parked = true;                               // the payload of the first level is already in the slot
+    for (int level = 0; level < 96; ++level) {
+        float4 *slot = rendezvous + 4 * (size_t)s;
+        const int mine = left ? 0 : 1;
+        if (!parked) {
+            __stcg(slot + 2 * mine, make_float4(c.lox, c.hix, c.loy, c.hiy));
+            __stcg(slot + 2 * mine + 1, make_float4(c.loz, c.hiz, __int_as_float(left ? c.F : c.L), __int_as_float(left ? c.dL : c.dR)));
+            __threadfence();
+        }
+        if ((atomicAdd(&S.flags[s], 1u) & 1u) == 0u) break;      // first to arrive: the sibling finishes the node
+        __threadfence();
+        if (tree_merge(S, c, left, s, __ldcg(slot + 2 * (mine ^ 1)), __ldcg(slot + 2 * (mine ^ 1) + 1))) break;
+        left = c.dR > c.dL;
+        s = left ? c.L : c.F - 1;
+        parked = false;
+    }
+}
+
+// The top of a SMALL tree (fused small build) finished by ONE CTA.  The nodes that straddle the 1024-leaf rounds form, per
+// round boundary, a chain up to the root -- a dozen dependent levels; through global memory each level costs two
+// device-scope fences and two L2 round trips (~4 k cycles: the old climb's 58 k-cycle critical path).  Here the children
+// meet in a shared-memory hash table keyed by the split (CTA-scope fences, shared-memory atomics: a few hundred cycles a
+// level).  At most (rounds - 1) x depth < 16 x 60 distinct splits exist, so 1024 slots never fill.
+constexpr int kTopSlots = 1024;
+struct TopSmem {
+    int key[kTopSlots];
+    uint32_t flag[kTopSlots];
+    float4 rxy[2 * kTopSlots], rz[2 * kTopSlots];
+};
+
+__device__ __forceinline__ void tree_top_local(const SceneDev &S, const float4 *__restrict__ rendezvous, const uint32_t *__restrict__ work,
+                                               uint32_t nw, int tid, int n_threads, TopSmem &T)
+{
+    for (int k = tid; k < kTopSlots; k += n_threads) { T.key[k] = -1; T.flag[k] = 0u; }
+    __syncthreads();
+    for (uint32_t e = (uint32_t)tid; e < nw; e += (uint32_t)n_threads) {
+        const uint32_t w = __ldcg(work + e);
         int s = (int)(w >> 1);
         bool left = (w & 1u) == 0u;
         Climber c;
@@ -592,27 +650,36 @@ __global__ void __launch_bounds__(128) k_tree_top(SceneDev S, float4 *__restrict
             const float4 *slot = rendezvous + 4 * (size_t)s + 2 * (left ? 0 : 1);
             const float4 pxy = __ldcg(slot), pz = __ldcg(slot + 1);
             c.lox = pxy.x; c.hix = pxy.y; c.loy = pxy.z; c.hiy = pxy.w; c.loz = pz.x; c.hiz = pz.y;
-            // only the fields the merge reads on this side are known -- and needed
             c.F = left ? __float_as_int(pz.z) : s + 1; c.L = left ? s : __float_as_int(pz.z);
             c.dL = left ? __float_as_int(pz.w) : 0; c.dR = left ? 0 : __float_as_int(pz.w);
         }
-        bool parked = true;                               // the payload of the first level is already in the slot
         for (int level = 0; level < 96; ++level) {
-            float4 *slot = rendezvous + 4 * (size_t)s;
-            const int mine = left ? 0 : 1;
-            if (!parked) {
-                __stcg(slot + 2 * mine, make_float4(c.lox, c.hix, c.loy, c.hiy));
-                __stcg(slot + 2 * mine + 1, make_float4(c.loz, c.hiz, __int_as_float(left ? c.F : c.L), __int_as_float(left ? c.dL : c.dR)));
-                __threadfence();
+            // slot of split s: linear probing, claimed with a compare-and-swap on the key
+            int hslot = (int)(((uint32_t)s * 2654435761u) >> 22) & (kTopSlots - 1);
+            for (int probe = 0; probe < kTopSlots; ++probe) {
+                const int prev = atomicCAS(&T.key[hslot], -1, s);
+                if (prev == -1 || prev == s) break;
+                hslot = (hslot + 1) & (kTopSlots - 1);
             }
-            if ((atomicAdd(&S.flags[s], 1u) & 1u) == 0u) break;      // first to arrive: the sibling finishes the node
-            __threadfence();
-            if (tree_merge(S, c, left, s, __ldcg(slot + 2 * (mine ^ 1)), __ldcg(slot + 2 * (mine ^ 1) + 1))) break;
+            const int mine = left ? 0 : 1;
+            T.rxy[2 * hslot + mine] = make_float4(c.lox, c.hix, c.loy, c.hiy);
+            T.rz[2 * hslot + mine] = make_float4(c.loz, c.hiz, __int_as_float(left ? c.F : c.L), __int_as_float(left ? c.dL : c.dR));
+            __threadfence_block();
+            if (atomicAdd(&T.flag[hslot], 1u) == 0u) break;          // first to arrive: the sibling finishes the node
+            __threadfence_block();
+            if (tree_merge(S, c, left, s, T.rxy[2 * hslot + (mine ^ 1)], T.rz[2 * hslot + (mine ^ 1)])) break;
             left = c.dR > c.dL;
             s = left ? c.L : c.F - 1;
-            parked = false;
         }
     }
+}
+
+__global__ void __launch_bounds__(128) k_tree_top(SceneDev S, float4 *__restrict__ rendezvous, const uint32_t *__restrict__ work,
+                                                  const uint32_t *__restrict__ work_count)
+{
+    const uint32_t nw = *work_count;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < nw; e += gridDim.x * blockDim.x)
+        tree_top_entry(S, rendezvous, __ldg(work + e));
 }
 
 // ---- (4b) fit without the climb: range queries over the block's leaf boxes --------------------------------
@@ -791,6 +858,8 @@ struct SmallArgs {
     float origins[8][3];                  // ray origins of the first n_origins sensors (sensor frame: one origin, 0)
     int n_origins;                        // 0 = the trace call computes the origin chains itself
     float4 *chains; int *chain_counts;    // [n_origins][9] lists (trace.cuh: TraceParams)
+    float4 *rendezvous;                   // tree phase: global rendezvous slots of the nodes that straddle CTA rounds (k_tree)
+    uint32_t *work, *work_count;          // tree phase: parked subtrees
 };
 
 struct KeysShared {
@@ -814,7 +883,7 @@ __device__ __forceinline__ uint32_t dsmem_ld_u32(const uint32_t *p, int rank)
 __global__ void __cluster_dims__(kClusterCtas, 1, 1) __launch_bounds__(kSmallThreads, 1)
 k_build_small(SceneDev S, const __grid_constant__ SmallArgs args, int sensor_frame, int rebuild)
 {
-    extern __shared__ __align__(16) uint32_t s_codes[];                  // [n_tris] sorted Morton codes (hierarchy phase)
+    extern __shared__ __align__(16) uint32_t s_codes[];                  // the tree phase's TreeSmem<kSmallThreads>
     __shared__ uint32_t s_hist[kSmallThreads / 32][256];                 // per-warp digit counts -> running offsets
     __shared__ uint32_t s_ctot[256], s_base[256], s_wsum[8];
     __shared__ uint32_t s_bounds[6], s_gbounds[6];
@@ -834,6 +903,7 @@ k_build_small(SceneDev S, const __grid_constant__ SmallArgs args, int sensor_fra
 #endif
     LSB_CLK();
     if (tid < 3) s_bounds[tid] = 0xFFFFFFFFu; else if (tid < 6) s_bounds[tid] = 0u;
+    if (gtid == 0) *args.work_count = 0u;      // parked-subtree counter of the tree phase (ordered by the cluster barriers in between)
     __syncthreads();
     // (1) transform + bounds
     {
@@ -937,27 +1007,36 @@ k_build_small(SceneDev S, const __grid_constant__ SmallArgs args, int sensor_fra
             uint32_t *t = src_k; src_k = dst_k; dst_k = t;
             t = src_v; src_v = dst_v; dst_v = t;
         }
-        // (4) hierarchy, sorted codes staged in shared memory
-        for (int i = tid; i < n; i += kSmallThreads) s_codes[i] = __ldcg(S.keys + i);
-        __syncthreads();
-        if (n > 1) { for (int i = gtid; i < n - 1; i += kAll) hierarchy_node(S, KeysShared{s_codes}, i); }
-        else if (gtid == 0) {
+        // (4) single-triangle scene: the root is (leaf 0, empty box); larger scenes get their hierarchy from the tree phase below
+        if (n == 1 && gtid == 0) {
             float4 *node = S.nodes + 4 * (size_t)S.top_cap;
             node[1] = make_float4(INFINITY, -INFINITY, INFINITY, -INFINITY);
             reinterpret_cast<float2 *>(node + 2)[1] = make_float2(INFINITY, -INFINITY);
             node[3] = make_float4(__int_as_float(leaf_ref(0, 1)), __int_as_float(leaf_ref(0, 1)), __int_as_float(0), __int_as_float(0));
             S.leaf_parent[0] = 0; S.node_parent[0] = -1; S.flags[0] |= 1u;
         }
-        cluster_sync_all();
+        if (n == 1) cluster_sync_all();
         LSB_CLK();
     }
-    // (5) leaf records + bottom-up boxes: CTA r, round k owns the leaves [k * 8192 + r * 1024, +1024)
-    for (int base = rank * kSmallThreads; base < n; base += kAll) {
-        s_flags[tid] = 0u;
-        __syncthreads();
-        const int i = base + tid;
-        if (i < n) fit_leaf<1>(S, (int)__ldcg(S.vals + i), i, s_flags, base);
-        __syncthreads();
+    if (n == 1) {
+        // (5') the lone leaf: record + its box into slot 0 of the root (the arrival protocol of k_fit, parity counter)
+        if (rank == 0) {
+            s_flags[tid] = 0u;
+            __syncthreads();
+            if (tid == 0) fit_leaf<1>(S, (int)__ldcg(S.vals), 0, s_flags, 0);
+        }
+    } else {
+        // (5) hierarchy AND boxes in one bottom-up pass (tree_block, the scheme of k_tree): CTA r, round k owns the leaves
+        // [k * 8192 + r * 1024, +1024); nodes inside a round meet in shared memory, the few that straddle rounds are
+        // parked and finished after a cluster barrier by tree_top_entry.  The same pass refits (sorted codes persist).
+        TreeSmem<kSmallThreads> &M = *reinterpret_cast<TreeSmem<kSmallThreads> *>(s_codes);
+        for (int base = rank * kSmallThreads; base < n; base += kAll) {
+            tree_block<kSmallThreads>(S, S.keys, S.vals, args.rendezvous, args.work, args.work_count, base, tid, M, true);
+            __syncthreads();
+        }
+        cluster_sync_all();
+        // the nodes that straddle rounds: one CTA, rendezvous in its shared memory (tree_top_local)
+        if (rank == 0) tree_top_local(S, args.rendezvous, args.work, __ldcg(args.work_count), tid, kSmallThreads, *reinterpret_cast<TopSmem *>(s_codes));
     }
     cluster_sync_all();                       // every box is final; no CTA leaves while its shared memory may still be read
     // (6) origin chains

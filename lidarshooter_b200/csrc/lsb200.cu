@@ -297,7 +297,7 @@ int lsb200_create(int cuda_device, lsb200_ctx **out)
 #ifdef LSB_LAB
         cudaFuncSetAttribute(k_fit_rmq, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RmqTable)) != cudaSuccess ||
 #endif
-        cudaFuncSetAttribute(k_build_small, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallMaxTris * 4) != cudaSuccess) {
+        cudaFuncSetAttribute(k_build_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TreeSmem<kSmallThreads>)) != cudaSuccess) {
         delete c; return LSB200_ERR_CUDA;
     }
     if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return LSB200_ERR_CUDA; }
@@ -655,7 +655,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
         if (!small) LSB_CU(c, c->d_sort_scratch.reserve(rsort::scratch_words(nt) * 4, st));
         LSB_CU(c, c->d_nodes.reserve(((size_t)c->built_top + T) * 64, st));
         LSB_CU(c, c->d_node_parent.reserve(T * 4, st)); LSB_CU(c, c->d_leaf_parent.reserve(T * 4, st));
-        if (!small && c->built_fused_tree) { LSB_CU(c, c->d_rendezvous.reserve(T * 64, st)); LSB_CU(c, c->d_tree_count.reserve(16, st)); }
+        if (small || c->built_fused_tree) { LSB_CU(c, c->d_rendezvous.reserve(T * 64, st)); LSB_CU(c, c->d_tree_count.reserve(16, st)); }
         LSB_CU(c, c->d_flags.reserve(T * 4, st, false, true));
     }
     SceneDev S = scene_dev(c);
@@ -690,7 +690,9 @@ static int commit_locked(lsb200_ctx *c, int mode)
         }
         mark("lsb200:build_small");
         // one cluster of kClusterCtas CTAs (__cluster_dims__ on the kernel)
-        k_build_small<<<kClusterCtas, kSmallThreads, (size_t)nt * 4, st>>>(S, args, c->frame_mode == LSB200_FRAME_SENSOR, rebuild ? 1 : 0);
+        args.rendezvous = c->d_rendezvous.as<float4>();
+        args.work = reinterpret_cast<uint32_t *>(c->d_leaf_parent.as<int32_t>()); args.work_count = c->d_tree_count.as<uint32_t>();
+        k_build_small<<<kClusterCtas, kSmallThreads, sizeof(TreeSmem<kSmallThreads>), st>>>(S, args, c->frame_mode == LSB200_FRAME_SENSOR, rebuild ? 1 : 0);
         count_launch(c);
         cudaEventRecord(c->ev_xform, st);
         mark(nullptr);
