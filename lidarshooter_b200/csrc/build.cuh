@@ -613,10 +613,12 @@ __device__ __forceinline__ void tree_top_entry(const SceneDev &S, float4 *__rest
         if (!parked) {
             __stcg(slot + 2 * mine, make_float4(c.lox, c.hix, c.loy, c.hiy));
             __stcg(slot + 2 * mine + 1, make_float4(c.loz, c.hiz, __int_as_float(left ? c.F : c.L), __int_as_float(left ? c.dL : c.dR)));
-            __threadfence();
         }
-        if ((atomicAdd(&S.flags[s], 1u) & 1u) == 0u) break;      // first to arrive: the sibling finishes the node
-        __threadfence();
+        // arrival: ONE acquire-release atomic (releases the payload stores above, acquires the sibling's) instead of
+        // fence + relaxed atomic + fence -- the chain of straddling nodes is a dozen dependent levels deep
+        uint32_t old;
+        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(S.flags + s) : "memory");
+        if ((old & 1u) == 0u) break;                             // first to arrive: the sibling finishes the node
         if (tree_merge(S, c, left, s, __ldcg(slot + 2 * (mine ^ 1)), __ldcg(slot + 2 * (mine ^ 1) + 1))) break;
         left = c.dR > c.dL;
         s = left ? c.L : c.F - 1;
