@@ -217,7 +217,8 @@ LSB200_API int lsb200_commit_scene(lsb200_ctx *ctx, int mode);
 /* ---- trace: replaces EmbreeTracer::traceScene (SRC/EmbreeTracer.cpp:297-367) ---------------------------
  * out_points: HOST buffer of capacity_pts records (32 B, or 16 B with LSB200_TRACE_XYZI16); *n_pts = hits.
  * Record (SRC/XYZIRBytes.cpp:24-40): x y z f32 | 4 zero bytes | intensity f32 = 64.0 | ring i32 | 8 zero bytes;
- * point = t * d_sensor.  Empty scene: *n_pts = 0 and -1 (SRC/OptixTracer.cpp:279-288). */
+ * point = t * d_sensor.  Empty scene: *n_pts = 0 and -1 (SRC/OptixTracer.cpp:279-288).  Only the first *n_pts records of
+ * out_points are meaningful; the rest of the buffer is unspecified after the call (small clouds are copied speculatively). */
 LSB200_API int lsb200_trace_scene(lsb200_ctx *ctx, int sensor_index, uint32_t frame_index, void *out_points,
                                   size_t capacity_pts, uint32_t *n_pts, uint32_t flags);
 /* same, results stay in device memory (lsb200_device_results) -- no synchronisation, no copies */

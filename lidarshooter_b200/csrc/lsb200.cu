@@ -1218,6 +1218,17 @@ static int fetch_locked(lsb200_ctx *c, int idx, void *out, size_t capacity, uint
         return LSB200_OK;
     }
     LSB_CU(c, cudaMemcpyAsync(c->h_count, c->d_counts.as<uint32_t>() + idx, 4, cudaMemcpyDeviceToHost, st));
+    // small clouds (an XT-32 scan: 4 800 rays): the records are copied speculatively -- as many as could exist -- right behind
+    // the count, so the call pays ONE host synchronisation instead of two; records past *n_pts in `out` are then unspecified
+    const size_t spec = std::min<size_t>((size_t)c->sensors[idx].n_rays(), capacity);
+    if (out && spec && spec * record_bytes(flags) <= (size_t)256 * 1024) {
+        LSB_CU(c, cudaMemcpyAsync(out, c->sensors[idx].points.p, spec * record_bytes(flags), cudaMemcpyDeviceToHost, st));
+        LSB_CU(c, cudaStreamSynchronize(st));
+        const uint32_t n1 = c->h_count[0];
+        if (n_pts) *n_pts = n1;
+        if (n1 > capacity) return fail(c, LSB200_ERR_CAPACITY, "fetch: %u points, capacity %zu", n1, capacity);
+        return LSB200_OK;
+    }
     LSB_CU(c, cudaStreamSynchronize(st));
     const uint32_t n = c->h_count[0];
     if (n_pts) *n_pts = n;
