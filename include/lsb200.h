@@ -325,6 +325,24 @@ LSB200_API int lsb200_debug_sort_pairs(lsb200_ctx *ctx, uint32_t *keys, uint32_t
 /* transformed vertices (n x 3 f32, concatenation order) of the last commit, for bit-exact transform tests */
 LSB200_API int lsb200_debug_copy_vertices(lsb200_ctx *ctx, float *xyz, int64_t capacity_vertices);
 
+/* ---- allocation-free sort --------------------------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same device radix sort
+ * as lsb200_debug_sort_pairs (the sort of the BVH build), on DEVICE arrays the caller owns: d_keys / d_vals hold the n
+ * pairs on entry and the pairs in ascending key order (stable) on return; d_keys_tmp / d_vals_tmp are the caller's
+ * ping-pong buffers of n words each (contents destroyed).  The sort's scratch (digit histograms, tile tickets, look-back
+ * status words) lives in a file-scope __device__ array of the library sized for LSB200_SORT_STATIC_MAX_PAIRS pairs
+ * (2.0 MiB, held by every GPU that loads the library until the process exits): the call issues no cudaMalloc / cudaFree
+ * and no allocating library routine.  n > LSB200_SORT_STATIC_MAX_PAIRS returns LSB200_ERR_CAPACITY and
+ * lsb200_last_error names the limit.  The work is enqueued on the context's stream and NOT synchronised
+ * (lsb200_synchronize, or order your own stream work behind it).  The first call on a device resolves the array's
+ * device address (cudaGetSymbolAddress, once per device; n = 0 does only that) -- make it before a capture begins.
+ * Every call on a device shares the one array (it is cleared at the start of each call): calls that overlap on the GPU
+ * -- two contexts, or two streams of one device -- race; serialise them. */
+#define LSB200_SORT_STATIC_MAX_PAIRS (1 << 22)
+LSB200_API int lsb200_sort_pairs_static(lsb200_ctx *ctx, uint32_t *d_keys, uint32_t *d_vals, uint32_t *d_keys_tmp,
+                                        uint32_t *d_vals_tmp, int64_t n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,6 +22,7 @@ OPT_TRACE_STATS, OPT_MORTON_UNIFORM, OPT_ORIGIN_CHAIN, OPT_TILE_WIDTH, OPT_SMALL
 OPT_TILE_ENTRIES, OPT_TILE_VISITS, OPT_TILE_MIN_UNITS, OPT_SUPER_TILES, OPT_WATERTIGHT, OPT_INTENSITY_MODEL, OPT_FUSED_TREE, OPT_LANE_REFILL, OPT_RETURNS, OPT_SMALL_TRACE_UNITS = 14, 15, 16, 17, 18, 19, 20, 21, 22, 23
 LOG_TRACE, LOG_DEBUG, LOG_INFO, LOG_WARN, LOG_ERROR = 0, 1, 2, 3, 4
 SHARD_FRAMES, SHARD_SENSORS = 0, 1
+SORT_STATIC_MAX_PAIRS = 1 << 22          # LSB200_SORT_STATIC_MAX_PAIRS
 ERR_INVALID, ERR_EMPTY_SCENE, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOMEM = -1, -1, -2, -3, -4, -5
 
 # every symbol include/lsb200.h declares (tests/test_abi.py checks the library exports each one)
@@ -34,7 +35,7 @@ SYMBOLS = [
     "lsb200_device_results", "lsb200_fetch_points", "lsb200_fetch_batch", "lsb200_synchronize", "lsb200_run_frames", "lsb200_init_message", "lsb200_get_stats",
     "lsb200_reset_counters", "lsb200_get_trace_counters", "lsb200_debug_copy_bvh", "lsb200_debug_sort_pairs", "lsb200_debug_copy_vertices",
     "lsb200_set_log_callback", "lsb200_set_sensor_intensity_filter", "lsb200_expand_range_image", "lsb200_fetch_intensity",
-    "lsb200_set_sensor_pose", "lsb200_alloc_host", "lsb200_free_host", "lsb200_device_numa_node", "lsb200_clone_scene", "lsb200_run_batch", "lsb200_fetch_second_returns",
+    "lsb200_set_sensor_pose", "lsb200_alloc_host", "lsb200_free_host", "lsb200_device_numa_node", "lsb200_clone_scene", "lsb200_run_batch", "lsb200_fetch_second_returns", "lsb200_sort_pairs_static",
 ]
 
 LOG_FN = C.CFUNCTYPE(None, C.c_int, C.c_char_p, C.c_void_p)
@@ -123,6 +124,7 @@ def lib(lab=False):
     L.lsb200_device_numa_node.argtypes = [vp]
     L.lsb200_clone_scene.argtypes = [vp, C.c_int, C.POINTER(vp)]
     L.lsb200_run_batch.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(Frame), C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_int]
+    L.lsb200_sort_pairs_static.argtypes = [vp, vp, vp, vp, vp, C.c_int64]
     _libs[lab] = L
     return L
 
@@ -410,6 +412,12 @@ class Context:
         self._chk(self._L.lsb200_debug_sort_pairs(self._h, k.ctypes.data_as(C.POINTER(C.c_uint32)),
                                                   v.ctypes.data_as(C.POINTER(C.c_uint32)), k.size))
         return k, v
+
+    def sort_pairs_static(self, d_keys, d_vals, d_keys_tmp, d_vals_tmp, n):
+        """lsb200_sort_pairs_static: DEVICE addresses (ints) of the caller's arrays; enqueued on the context's stream,
+        not synchronised; allocates nothing.  Returns the ABI's status code (ERR_CAPACITY beyond SORT_STATIC_MAX_PAIRS)."""
+        return self._L.lsb200_sort_pairs_static(self._h, C.c_void_p(d_keys), C.c_void_p(d_vals), C.c_void_p(d_keys_tmp),
+                                                C.c_void_p(d_vals_tmp), int(n))
 
     def debug_copy_vertices(self):
         s = self.stats()

@@ -1847,3 +1847,57 @@ int lsb200_run_batch(lsb200_ctx *const *ctxs, int n_ctx, const lsb200_frame *fra
 }
 
 }  // extern "C"
+
+// =============================================================================================================
+//  Allocation-free sort (no counterpart in the reference).
+//  The radix sort's scratch in a file-scope __device__ array: no cudaMalloc / cudaFree on this path.
+// =============================================================================================================
+namespace {
+
+constexpr int64_t kStaticSortTiles = ((int64_t)LSB200_SORT_STATIC_MAX_PAIRS + rsort::kTile - 1) / rsort::kTile;
+// rsort::scratch_words(LSB200_SORT_STATIC_MAX_PAIRS), as a constant expression
+constexpr size_t kStaticSortWords = (size_t)rsort::kPasses * rsort::kRadix + 16 + (size_t)rsort::kPasses * kStaticSortTiles * rsort::kRadix;
+
+// Held by every GPU that loads the library, until the process exits (2.0 MiB).  In HOST code this name is only a
+// stand-in for the symbol, never a device address: kernels get the pointer cudaGetSymbolAddress returns.
+static __device__ __align__(256) uint32_t g_static_sort_scratch[kStaticSortWords];
+
+constexpr int kMaxStaticDevices = 64;
+uint32_t *g_static_sort_ptr[kMaxStaticDevices] = {};   // the array's address on each device (it differs per device)
+std::mutex g_static_sort_mtx;
+
+// Set-up, once per device, with that device current (the caller holds a DeviceGuard).
+int static_sort_scratch(lsb200_ctx *c, uint32_t **out)
+{
+    if (c->device < 0 || c->device >= kMaxStaticDevices) return fail(c, LSB200_ERR_INVALID, "sort_pairs_static: device %d out of range", c->device);
+    std::lock_guard<std::mutex> lk(g_static_sort_mtx);
+    if (!g_static_sort_ptr[c->device]) {
+        void *p = nullptr;
+        LSB_CU(c, cudaGetSymbolAddress(&p, g_static_sort_scratch));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255u)) return fail(c, LSB200_ERR_CUDA, "sort_pairs_static: bad symbol address %p", p);
+        g_static_sort_ptr[c->device] = static_cast<uint32_t *>(p);
+    }
+    *out = g_static_sort_ptr[c->device];
+    return LSB200_OK;
+}
+
+}  // namespace
+
+extern "C" int lsb200_sort_pairs_static(lsb200_ctx *c, uint32_t *d_keys, uint32_t *d_vals, uint32_t *d_keys_tmp, uint32_t *d_vals_tmp, int64_t n)
+{
+    if (!c) return LSB200_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(c->mtx);
+    if (n < 0) return fail(c, LSB200_ERR_INVALID, "sort_pairs_static: n = %lld", (long long)n);
+    if (n > (int64_t)LSB200_SORT_STATIC_MAX_PAIRS)
+        return fail(c, LSB200_ERR_CAPACITY, "sort_pairs_static: %lld pairs exceed LSB200_SORT_STATIC_MAX_PAIRS = %d (the static scratch array is sized for that many)",
+                    (long long)n, (int)LSB200_SORT_STATIC_MAX_PAIRS);
+    if (n > 0 && (!d_keys || !d_vals || !d_keys_tmp || !d_vals_tmp)) return fail(c, LSB200_ERR_INVALID, "sort_pairs_static: null device pointer");
+    DeviceGuard dg(c->device);
+    uint32_t *scratch = nullptr;
+    const int rc = static_sort_scratch(c, &scratch);
+    if (rc != LSB200_OK || n == 0) return rc;
+    // sort_pairs clears the words it uses (histograms, tickets, status) on the stream before its first kernel
+    count_launch(c, rsort::sort_pairs(d_keys, d_vals, d_keys_tmp, d_vals_tmp, n, scratch, c->stream));
+    LSB_CU(c, cudaGetLastError());
+    return LSB200_OK;
+}
