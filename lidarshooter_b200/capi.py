@@ -133,6 +133,22 @@ def _fp(a):
     return a.ctypes.data_as(C.POINTER(C.c_float))
 
 
+def reachable_nodes(nodes, root):
+    """Copy of a debug_copy_bvh node array with every record that no child reference leads to zeroed.  The fused tree
+    build does not write the records of nodes whose whole range fits a leaf (their parents reference them as leaves), so
+    those rows hold whatever the allocation held: tree comparisons look at the reachable records only."""
+    child = nodes[:, 12:14].view(np.int32)
+    seen = np.zeros(nodes.shape[0], bool)
+    frontier = np.zeros(1, np.int64)
+    while frontier.size:
+        seen[frontier] = True
+        c = child[frontier].ravel().astype(np.int64)
+        frontier = c[c >= 0] - root
+    out = nodes.copy()
+    out[~seen] = 0
+    return out
+
+
 class Lsb200Error(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"lsb200 error {code}: {msg}")

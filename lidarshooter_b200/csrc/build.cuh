@@ -450,6 +450,9 @@ __device__ __forceinline__ Box6 leaf_record(const SceneDev &S, int g, int i)
 #ifndef LSB_TREE_BLOCK
 #define LSB_TREE_BLOCK 128
 #endif
+#ifndef LSB_TREE_SKIP_LEAF_NODES
+#define LSB_TREE_SKIP_LEAF_NODES 1
+#endif
 constexpr int kTreeBlock = LSB_TREE_BLOCK;        // leaves per k_tree CTA
 
 // common-prefix length of the (code, index) keys of the sorted leaves j and j + 1; -1 outside the scene
@@ -473,12 +476,16 @@ __device__ __forceinline__ bool tree_merge(const SceneDev &S, Climber &c, bool l
     const int c1 = (rcount <= S.leaf_max) ? leaf_ref(s + 1, rcount) : S.top_cap + s + 1;
     const bool root = ndL < 0 && ndR < 0;
     const int idx = root ? 0 : (ndR > ndL ? nL : nF);          // Karras index: left children sit at their last leaf, right at their first
-    float4 *node = S.nodes + 4 * ((size_t)S.top_cap + idx);
-    const float4 mxy = make_float4(c.lox, c.hix, c.loy, c.hiy);
-    node[0] = left ? mxy : sxy;
-    node[1] = left ? sxy : mxy;
-    node[2] = left ? make_float4(c.loz, c.hiz, sz.x, sz.y) : make_float4(sz.x, sz.y, c.loz, c.hiz);
-    node[3] = make_float4(__int_as_float(c0), __int_as_float(c1), __int_as_float(nF), __int_as_float(nL));
+    // A node whose whole range fits a leaf is referenced by its parent as a leaf (leaf_ref above), never by index:
+    // nobody reads its record, so it is not written (a third of the nodes at leaf size 2: 64 bytes each).
+    if (!LSB_TREE_SKIP_LEAF_NODES || root || nL - nF >= S.leaf_max) {
+        float4 *node = S.nodes + 4 * ((size_t)S.top_cap + idx);
+        const float4 mxy = make_float4(c.lox, c.hix, c.loy, c.hiy);
+        node[0] = left ? mxy : sxy;
+        node[1] = left ? sxy : mxy;
+        node[2] = left ? make_float4(c.loz, c.hiz, sz.x, sz.y) : make_float4(sz.x, sz.y, c.loz, c.hiz);
+        node[3] = make_float4(__int_as_float(c0), __int_as_float(c1), __int_as_float(nF), __int_as_float(nL));
+    }
     c.lox = fminf(c.lox, sxy.x); c.hix = fmaxf(c.hix, sxy.y);
     c.loy = fminf(c.loy, sxy.z); c.hiy = fmaxf(c.hiy, sxy.w);
     c.loz = fminf(c.loz, sz.x); c.hiz = fmaxf(c.hiz, sz.y);

@@ -250,9 +250,9 @@ def test_small_build_equals_pipeline(n_tris):
         rc, t, tri = ctx.trace_raw()
         assert ctx.update_transform("soup", A2) == 0
         assert ctx.commit_scene(capi.COMMIT_REFIT) == 0 and ctx.stats().last_commit_was_rebuild == 0
-        nodes2, ids2, _ = ctx.debug_copy_bvh()
+        nodes2, ids2, root2 = ctx.debug_copy_bvh()
         rc, t2, tri2 = ctx.trace_raw()
-        out.append((nodes.copy(), ids.copy(), root, t, tri, nodes2.copy(), ids2.copy(), t2, tri2))
+        out.append((capi.reachable_nodes(nodes, root), ids.copy(), root, t, tri, capi.reachable_nodes(nodes2, root2), ids2.copy(), t2, tri2))
         ctx.close()
     a, b = out
     names = ("nodes", "leaf ids", "root", "t", "tri", "nodes after refit", "leaf ids after refit", "t after refit", "tri after refit")
@@ -814,6 +814,7 @@ def test_fit_by_range_queries_equals_climb(n_tris):
     for rmq in (1, 0):
         ctx = capi.Context(0, lab=True)
         ctx.set_option(capi.OPT_SMALL_BUILD, 0)
+        ctx.set_option(capi.OPT_FUSED_TREE, 0)
         ctx.set_option(capi.OPT_FIT_RMQ, rmq)
         ctx.set_option(capi.OPT_LEAF_SIZE, 4)
         ctx.set_sensor(np.linspace(40, -40, 16).astype(np.float32), 0.0, 360.0, 64, (1, 0, 0, 0), (0, 0, 0))

@@ -377,12 +377,12 @@ def test_fused_tree_equals_pipeline(n_tris, leaf):
             assert ctx.commit_scene(capi.COMMIT_REBUILD) == 0, ctx.last_error()
             nodes, ids, root = ctx.debug_copy_bvh()
             rc, t, tri = ctx.trace_raw()
-            res += [nodes.copy(), ids.copy(), root, t, tri]
+            res += [capi.reachable_nodes(nodes, root), ids.copy(), root, t, tri]
         assert ctx.update_transform("soup", A2) == 0
         assert ctx.commit_scene(capi.COMMIT_REFIT) == 0 and ctx.stats().last_commit_was_rebuild == 0
-        nodes2, ids2, _ = ctx.debug_copy_bvh()
+        nodes2, ids2, root2 = ctx.debug_copy_bvh()
         rc, t2, tri2 = ctx.trace_raw()
-        out.append(res + [nodes2.copy(), ids2.copy(), t2, tri2])
+        out.append(res + [capi.reachable_nodes(nodes2, root2), ids2.copy(), t2, tri2])
         ctx.close()
     a, b = out
     for k, (x, y) in enumerate(zip(a, b)):
