@@ -589,12 +589,133 @@ __device__ __forceinline__ void tree_block(const SceneDev &S, const uint32_t *__
     if ((uint32_t)t < nw) work[M.wbase + t] = M.work[t];
 }
 
+#ifndef LSB_TREE_ROUNDS
+#define LSB_TREE_ROUNDS 0
+#endif
+#if LSB_TREE_ROUNDS
+// Round-synchronous form of tree_block (measured and rejected: -DLSB_TREE_ROUNDS=1 builds it for the A/B, design log 22;
+// 0.648 vs 0.631 ms -- k_tree is bound by the L1 data pipe, gathers + scattered stores + the shared-memory rendezvous,
+// 68 % of its peak, and those wavefronts are the same in both forms; the rounds only add barriers): same block set-up, same rendezvous slots, same
+// parked subtrees and the same node records -- but the climb is not a chain per thread.  In tree_block a thread follows its
+// own subtree upwards for as long as it is the second child to arrive, so every level halves the live lanes of a warp
+// (14.7 of 32 threads per instruction over the kernel, ~100 instructions per level and warp whatever the lane count).  Here
+// a node whose second child has arrived is put on a shared-memory queue; after a block barrier the queue of the round is
+// dealt to threads 0 .. n - 1, so the merges of a round sit in full warps (the other warps only pass the barrier), and
+// the barrier orders the children's shared-memory stores: no fences.  Rounds = height of the block's tallest subtree.
+template <int B>
+struct TreeRounds {
+    uint16_t q[2][B / 2];             // splits (block-local) whose two children have arrived, by round parity
+    uint32_t cnt[3];                  // entries of the queue of round r: cnt[r % 3]
+};
+
+template <int B>
+__device__ __forceinline__ void tree_block_rounds(const SceneDev &S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
+                                                  float4 *__restrict__ rendezvous, uint32_t *__restrict__ work, uint32_t *__restrict__ work_count,
+                                                  int base, int t, TreeSmem<B> &M, TreeRounds<B> &Q, bool ids_uncached)
+{
+    const int lane = t & 31, warp = t >> 5;
+    const int n = S.n_tris;
+    const int i = base + t;
+    M.flag[t] = 0u;
+    if (t == 0) { M.nwork = 0u; Q.cnt[0] = 0u; Q.cnt[1] = 0u; Q.cnt[2] = 0u; }
+    for (int k = t; k < B + 2; k += B) {
+        const int j = base - 1 + k;
+        M.key[k] = (j >= 0 && j < n) ? __ldcg(keys + j) : 0u;
+    }
+    __syncthreads();
+    const int d_lo = boundary_delta(M.key[t], M.key[t + 1], i - 1, n);
+    M.delta[t] = (int8_t)d_lo;
+    if (t == 0) M.delta[B] = (int8_t)boundary_delta(M.key[B], M.key[B + 1], base + B - 1, n);
+    int pm = d_lo, sm = d_lo;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, pm, o), w = __shfl_down_sync(0xffffffffu, sm, o);
+        if (lane >= o) pm = min(pm, u);
+        if (lane + o < 32) sm = min(sm, w);
+    }
+    if (lane == 31) M.wpre[warp] = (int8_t)pm;
+    if (lane == 0) M.wsuf[warp] = (int8_t)sm;
+    __syncthreads();
+    for (int w = 0; w < warp; ++w) pm = min(pm, (int)M.wpre[w]);
+    for (int w = warp + 1; w < B / 32; ++w) sm = min(sm, (int)M.wsuf[w]);
+    sm = min(sm, (int)M.delta[B]);
+    M.sufmin[t] = (int8_t)sm;
+    if (t == 0) { M.sufmin[B] = M.delta[B]; M.sufmin[B + 1] = 127; }
+    __syncthreads();
+    {
+        const int d_s = M.delta[t + 1];
+        M.local[t] = (t + 1 < B && pm < d_s && (int)M.sufmin[t + 2] < d_s) ? 1 : 0;
+    }
+    __syncthreads();
+    // a finished subtree [F, L] with outer deltas (dL, dR) goes to its parent's slot: queue of the NEXT round when it is
+    // the second child there, the global rendezvous + work list when the parent straddles blocks
+    auto deposit = [&](const float4 pxy, float loz, float hiz, int F, int L, int dL, int dR, uint32_t *next_cnt, uint16_t *next_q) {
+        const bool left = dR > dL;
+        const int s = left ? L : F - 1;
+        const int ls = s - base;
+        const int mine = left ? 0 : 1;
+        const float4 pz = make_float4(loz, hiz, __int_as_float(left ? F : L), __int_as_float(left ? dL : dR));
+        if (!(ls >= 0 && ls < B && M.local[ls])) {
+            float4 *slot = rendezvous + 4 * (size_t)s + 2 * mine;
+            __stcg(slot, pxy);
+            __stcg(slot + 1, pz);
+            M.work[atomicAdd(&M.nwork, 1u)] = ((uint32_t)s << 1) | (uint32_t)mine;
+            return;
+        }
+        M.rxy[2 * ls + mine] = pxy;
+        M.rz[2 * ls + mine] = pz;
+        if (atomicAdd(&M.flag[ls], 1u) != 0u) next_q[atomicAdd(next_cnt, 1u)] = (uint16_t)ls;
+    };
+    if (i < n) {
+        const Box6 leaf = leaf_record(S, (int)(ids_uncached ? __ldcg(sorted_ids + i) : __ldg(sorted_ids + i)), i);
+        deposit(make_float4(leaf.lox, leaf.hix, leaf.loy, leaf.hiy), leaf.loz, leaf.hiz, i, i, d_lo, (int)M.delta[t + 1], &Q.cnt[0], Q.q[0]);
+    }
+    for (int r = 0; r < B; ++r) {                          // r < B only guards against a hang
+        __syncthreads();
+        const int nq = (int)Q.cnt[r % 3];
+        if (nq == 0) break;
+        if (t == 0) Q.cnt[(r + 2) % 3] = 0u;               // last read before this round's barrier; next filled in round r + 1
+        if (t < nq) {
+            const int ls = Q.q[r & 1][t];
+            const int s = base + ls;
+            const float4 lxy = M.rxy[2 * ls], lz = M.rz[2 * ls], rxy = M.rxy[2 * ls + 1], rz = M.rz[2 * ls + 1];
+            const int nF = __float_as_int(lz.z), ndL = __float_as_int(lz.w), nL = __float_as_int(rz.z), ndR = __float_as_int(rz.w);
+            const int lcount = s - nF + 1, rcount = nL - s;
+            const bool root = ndL < 0 && ndR < 0;
+            if (!LSB_TREE_SKIP_LEAF_NODES || root || nL - nF >= S.leaf_max) {
+                const int c0 = (lcount <= S.leaf_max) ? leaf_ref(nF, lcount) : S.top_cap + s;
+                const int c1 = (rcount <= S.leaf_max) ? leaf_ref(s + 1, rcount) : S.top_cap + s + 1;
+                const int idx = root ? 0 : (ndR > ndL ? nL : nF);
+                float4 *node = S.nodes + 4 * ((size_t)S.top_cap + idx);
+                node[0] = lxy;
+                node[1] = rxy;
+                node[2] = make_float4(lz.x, lz.y, rz.x, rz.y);
+                node[3] = make_float4(__int_as_float(c0), __int_as_float(c1), __int_as_float(nF), __int_as_float(nL));
+            }
+            if (!root)
+                deposit(make_float4(fminf(lxy.x, rxy.x), fmaxf(lxy.y, rxy.y), fminf(lxy.z, rxy.z), fmaxf(lxy.w, rxy.w)),
+                        fminf(lz.x, rz.x), fmaxf(lz.y, rz.y), nF, nL, ndL, ndR, &Q.cnt[(r + 1) % 3], Q.q[(r + 1) & 1]);
+        }
+    }
+    __syncthreads();
+    const uint32_t nw = M.nwork;
+    if (t == 0 && nw) M.wbase = atomicAdd(work_count, nw);
+    __syncthreads();
+    if ((uint32_t)t < nw) work[M.wbase + t] = M.work[t];
+}
+
+#endif  // LSB_TREE_ROUNDS
 __global__ void __launch_bounds__(kTreeBlock) k_tree(SceneDev S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
                                                      float4 *__restrict__ rendezvous /* [4 * n_tris] */,
                                                      uint32_t *__restrict__ work /* [n_tris]: split << 1 | side */, uint32_t *__restrict__ work_count)
 {
     __shared__ TreeSmem<kTreeBlock> M;
+#if LSB_TREE_ROUNDS
+    __shared__ TreeRounds<kTreeBlock> Q;
+    tree_block_rounds<kTreeBlock>(S, keys, sorted_ids, rendezvous, work, work_count, blockIdx.x * kTreeBlock, threadIdx.x, M, Q, false);
+#else
     tree_block<kTreeBlock>(S, keys, sorted_ids, rendezvous, work, work_count, blockIdx.x * kTreeBlock, threadIdx.x, M, false);
+#endif
 }
 
 // Phase 2: the nodes that straddle blocks (~1 % of the tree, its top).  One thread per parked subtree: arrival at the
