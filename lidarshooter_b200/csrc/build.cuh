@@ -510,8 +510,24 @@ struct TreeSmem {
     uint32_t flag[B];
     uint32_t work[B];
     uint32_t nwork, wbase;
-    float4 rxy[2 * B], rz[2 * B];     // per split: slot 0 = left child, slot 1 = right child
+    float4 rxy[2 * B], rz[2 * B];     // per split: the left child's half and the right child's half, at rslot()
 };
+// Where the children of block-local split ls leave their halves.  Left halves at [ls], right halves at [B + (ls + 1) % B]:
+// at the leaf level lane t deposits at split t (left child) or t - 1 (right child) -- either way its 16-byte slot index is
+// t modulo 8, so the eight lanes of a quarter warp hit eight different bank groups (the interleaved [2 ls + side] layout
+// put them at a 32-byte stride: two-way conflicts, twice the conflict-free wavefronts in ncu).
+#ifndef LSB_TREE_SPLIT_SLOTS
+#define LSB_TREE_SPLIT_SLOTS 1
+#endif
+template <int B>
+__device__ __forceinline__ int rslot(int ls, int side)
+{
+#if LSB_TREE_SPLIT_SLOTS
+    return side ? B + ((ls + 1) & (B - 1)) : ls;
+#else
+    return 2 * ls + side;
+#endif
+}
 
 template <int B>
 __device__ __forceinline__ void tree_block(const SceneDev &S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
@@ -574,12 +590,12 @@ __device__ __forceinline__ void tree_block(const SceneDev &S, const uint32_t *__
                 M.work[atomicAdd(&M.nwork, 1u)] = ((uint32_t)s << 1) | (uint32_t)mine;
                 break;
             }
-            M.rxy[2 * ls + mine] = pxy;
-            M.rz[2 * ls + mine] = pz;
+            M.rxy[rslot<B>(ls, mine)] = pxy;
+            M.rz[rslot<B>(ls, mine)] = pz;
             __threadfence_block();
             if (atomicAdd(&M.flag[ls], 1u) == 0u) break;           // first to arrive: the sibling finishes the node
             __threadfence_block();
-            if (tree_merge(S, c, left, s, M.rxy[2 * ls + (mine ^ 1)], M.rz[2 * ls + (mine ^ 1)])) break;
+            if (tree_merge(S, c, left, s, M.rxy[rslot<B>(ls, mine ^ 1)], M.rz[rslot<B>(ls, mine ^ 1)])) break;
         }
     }
     __syncthreads();
@@ -662,8 +678,8 @@ __device__ __forceinline__ void tree_block_rounds(const SceneDev &S, const uint3
             M.work[atomicAdd(&M.nwork, 1u)] = ((uint32_t)s << 1) | (uint32_t)mine;
             return;
         }
-        M.rxy[2 * ls + mine] = pxy;
-        M.rz[2 * ls + mine] = pz;
+        M.rxy[rslot<B>(ls, mine)] = pxy;
+        M.rz[rslot<B>(ls, mine)] = pz;
         if (atomicAdd(&M.flag[ls], 1u) != 0u) next_q[atomicAdd(next_cnt, 1u)] = (uint16_t)ls;
     };
     if (i < n) {
@@ -678,7 +694,7 @@ __device__ __forceinline__ void tree_block_rounds(const SceneDev &S, const uint3
         if (t < nq) {
             const int ls = Q.q[r & 1][t];
             const int s = base + ls;
-            const float4 lxy = M.rxy[2 * ls], lz = M.rz[2 * ls], rxy = M.rxy[2 * ls + 1], rz = M.rz[2 * ls + 1];
+            const float4 lxy = M.rxy[rslot<B>(ls, 0)], lz = M.rz[rslot<B>(ls, 0)], rxy = M.rxy[rslot<B>(ls, 1)], rz = M.rz[rslot<B>(ls, 1)];
             const int nF = __float_as_int(lz.z), ndL = __float_as_int(lz.w), nL = __float_as_int(rz.z), ndR = __float_as_int(rz.w);
             const int lcount = s - nF + 1, rcount = nL - s;
             const bool root = ndL < 0 && ndR < 0;
