@@ -1135,6 +1135,7 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
         }
         if (stale || c->opt_stats) {
             const unsigned blocks = (unsigned)((n_units + kTileBlock - 1) / kTileBlock);
+            const size_t tile_stk_bytes = LSB_TILE_SMEM_STACK ? (size_t)P.tile_cap * kTileBlock * sizeof(int4) : 0;   // <= 32 KB
             if (timing) { cudaEventRecord(c->ev[11], st); tile_timed = true; }
 #ifdef LSB_LAB
             if (c->opt_super_tiles) {
@@ -1143,10 +1144,10 @@ static int trace_locked(lsb200_ctx *c, int first, int count, uint32_t flags, int
                 else k_super_entries<false><<<sblocks, 128, 0, st>>>(P, first, count, sup_lo, sup_hi, 8 * kMaxTileEntries);
                 count_launch(c);
             }
-            if (c->opt_stats) k_tile_entries<true><<<blocks, kTileBlock, 0, st>>>(P, max_visits);
+            if (c->opt_stats) k_tile_entries<true><<<blocks, kTileBlock, tile_stk_bytes, st>>>(P, max_visits);
             else
 #endif
-            k_tile_entries<false><<<blocks, kTileBlock, 0, st>>>(P, max_visits);
+            k_tile_entries<false><<<blocks, kTileBlock, tile_stk_bytes, st>>>(P, max_visits);
             count_launch(c);
             c->tile_commit_epoch = c->commit_epoch; c->tile_sensors_epoch = c->sensors_epoch; c->tile_first = first; c->tile_count = count;
             c->tile_cap = cap; c->tile_visits = max_visits; c->tile_units_id = c->units_build_id;

@@ -1545,6 +1545,9 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
 #ifndef LSB_TILE_BLOCK
 #define LSB_TILE_BLOCK 128
 #endif
+#ifndef LSB_TILE_SMEM_STACK
+#define LSB_TILE_SMEM_STACK 1     // k_tile_entries: deferred entries of the walk in shared memory ([slot][thread]) instead of a local array
+#endif
 constexpr int kTileBlock = LSB_TILE_BLOCK;   // threads per CTA of k_tile_entries (one thread per tile)
 constexpr int kSuperTiles = 4;          // a supertile is kSuperTiles x kSuperTiles tiles
 
@@ -1690,11 +1693,15 @@ __global__ void __launch_bounds__(128) k_super_intervals(TraceParams P, int s_fi
 // node `from`, side 2 = seed `from`.  The box itself (24 bytes) is only re-read when a popped entry is listed
 // without having been split.  One flat loop (a step = list the entry in hand, or split it): the lanes of a warp --
 // neighbouring blocks -- stay in step instead of serialising an outer pop loop against an inner descent loop.
+// The deferred entries live at stk[d * STRIDE]: a local array (STRIDE 1; k_super_entries) or a [slot][thread] block of
+// shared memory (STRIDE = threads per CTA; k_tile_entries).  Lanes of a warp sit at different depths: in local memory
+// every distinct depth of a 16-byte access is its own four wavefronts (a third of the kernel's L1 wavefronts were
+// local loads / stores), in shared memory the bank is the thread's column whatever the depth -- always four.
+template <int STRIDE>
 __device__ __forceinline__ int frustum_walk(const float4 *__restrict__ nodes, const TileFrustum &F, const float4 *__restrict__ seeds,
                                             int n_seeds, bool seeds_near_first, int cap, int max_visits, float4 *__restrict__ out,
-                                            int &visits)
+                                            int &visits, int4 *__restrict__ stk)
 {
-    int4 stk[kMaxTileEntries];
     int sp = 0;
     for (int q = 0; q < n_seeds; ++q) {                          // far -> near: the nearest seed ends on top
         const int k = seeds_near_first ? n_seeds - 1 - q : q;
@@ -1702,14 +1709,14 @@ __device__ __forceinline__ int frustum_walk(const float4 *__restrict__ nodes, co
         float n;
         if (!F.test(e0, e1.x, e1.y, n)) continue;
         if (sp == cap) return -1;
-        stk[sp++] = make_int4(__float_as_int(e1.z), __float_as_int(n), k, 2);
+        stk[(sp++) * STRIDE] = make_int4(__float_as_int(e1.z), __float_as_int(n), k, 2);
     }
     int n_out = 0;
     int4 cur = make_int4(0, 0, 0, 0);
     float4 cxy = make_float4(0.f, 0.f, 0.f, 0.f);
     float2 cz = make_float2(0.f, 0.f);
     bool have = sp > 0, have_box = false;
-    if (have) cur = stk[--sp];
+    if (have) cur = stk[(--sp) * STRIDE];
     while (have) {
         bool pop = false;
         // a split turns the entry in hand into two: only while the list has room for it
@@ -1738,7 +1745,7 @@ __device__ __forceinline__ int frustum_walk(const float4 *__restrict__ nodes, co
             const bool h0 = F.test(q0, q2.x, q2.y, n0), h1 = F.test(q1, q2.z, q2.w, n1);
             const bool first1 = h1 && (!h0 || n1 < n0);              // continue with child 1 (the nearer, or the only one)
             if (h0 && h1)                                            // defer the farther child
-                stk[sp++] = first1 ? make_int4(__float_as_int(q3.x), __float_as_int(n0), node, 0)
+                stk[(sp++) * STRIDE] = first1 ? make_int4(__float_as_int(q3.x), __float_as_int(n0), node, 0)
                                    : make_int4(__float_as_int(q3.y), __float_as_int(n1), node, 1);
             cur = first1 ? make_int4(__float_as_int(q3.y), __float_as_int(n1), node, 1) : make_int4(__float_as_int(q3.x), __float_as_int(n0), node, 0);
             cxy = first1 ? q1 : q0;
@@ -1749,7 +1756,7 @@ __device__ __forceinline__ int frustum_walk(const float4 *__restrict__ nodes, co
         if (pop) {
             have = sp > 0;
             have_box = false;
-            if (have) cur = stk[--sp];
+            if (have) cur = stk[(--sp) * STRIDE];
         }
     }
     return n_out;
@@ -1784,8 +1791,9 @@ __global__ void __launch_bounds__(128) k_super_entries(TraceParams P, int s_firs
     int n_out = -1, visits = 0;
     if (cls < 8 && make_frustum(dlo, dhi, o3, eps, S.max_range, F)) {
         const int list = si * 9 + cls;
-        n_out = frustum_walk(P.nodes, F, P.chains + (size_t)list * (2 * kMaxChain), __ldg(P.chain_counts + list), false,
-                             kMaxTileEntries, max_visits, P.sup_lists + (size_t)sup * (2 * kMaxTileEntries), visits);
+        int4 stk[kMaxTileEntries];
+        n_out = frustum_walk<1>(P.nodes, F, P.chains + (size_t)list * (2 * kMaxChain), __ldg(P.chain_counts + list), false,
+                                kMaxTileEntries, max_visits, P.sup_lists + (size_t)sup * (2 * kMaxTileEntries), visits, stk);
     }
     P.sup_counts[sup] = (uint8_t)(n_out < 0 ? kTileFallback : n_out);
     if (STATS) atomicAdd(P.counters + kCntSuperVisits, (unsigned long long)visits);
@@ -1830,11 +1838,19 @@ __global__ void __launch_bounds__(kTileBlock) k_tile_entries(TraceParams P, int 
         if (sc != kTileFallback) { seeds = P.sup_lists + (size_t)sup * (2 * kMaxTileEntries); n_seeds = sc; near_first = true; }
     }
     int visits = 0;
-    int n_out = frustum_walk(P.nodes, F, seeds, n_seeds, near_first, P.tile_cap, max_visits,
-                             P.tile_lists + (size_t)slot * (2 * P.tile_cap), visits);
+#if LSB_TILE_SMEM_STACK
+    extern __shared__ int4 s_tile_stk[];                // [tile_cap][kTileBlock]
+    int4 *stk = s_tile_stk + threadIdx.x;
+    constexpr int kStride = kTileBlock;
+#else
+    int4 stk[kMaxTileEntries];
+    constexpr int kStride = 1;
+#endif
+    int n_out = frustum_walk<kStride>(P.nodes, F, seeds, n_seeds, near_first, P.tile_cap, max_visits,
+                                      P.tile_lists + (size_t)slot * (2 * P.tile_cap), visits, stk);
     if (n_out < 0 && near_first)            // more supertile entries pass than the list holds: start from the chain instead
-        n_out = frustum_walk(P.nodes, F, P.chains + (size_t)list * (2 * kMaxChain), __ldg(P.chain_counts + list), false, P.tile_cap,
-                             max_visits, P.tile_lists + (size_t)slot * (2 * P.tile_cap), visits);
+        n_out = frustum_walk<kStride>(P.nodes, F, P.chains + (size_t)list * (2 * kMaxChain), __ldg(P.chain_counts + list), false, P.tile_cap,
+                                      max_visits, P.tile_lists + (size_t)slot * (2 * P.tile_cap), visits, stk);
     P.tile_counts[slot] = (uint8_t)(n_out < 0 ? kTileFallback : n_out);
     if (STATS) {
         atomicAdd(P.counters + kCntTileVisits, (unsigned long long)visits);
