@@ -56,40 +56,51 @@ __device__ __forceinline__ void transform_vertex(const SceneDev &S, int sensor_f
     S.xverts[j] = make_float4(x, y, z, 0.0f);
 }
 
+#ifndef LSB_XFORM_PER_THREAD
+#define LSB_XFORM_PER_THREAD 4
+#endif
+constexpr int kXformPerThread = LSB_XFORM_PER_THREAD;     // vertices per thread of k_transform
+constexpr int kXformBlock = 256 * kXformPerThread;        // vertices per CTA
+
+// One thread transforms kXformPerThread vertices (block-strided: coalesced) and keeps their bounds in registers; the warp
+// reduction is ONE redux.sync per bound on the ordered-uint encoding (the shuffle tree of the one-vertex-per-thread form
+// was 30 SHFL per 32 vertices: two thirds of the kernel's L1 data-pipe wavefronts, which it was bound by at 74 %).
 __global__ void __launch_bounds__(256) k_transform(SceneDev S, int sensor_frame, const float *__restrict__ RinvT /*9+3*/)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j0 = blockIdx.x * kXformBlock;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     // vertices are numbered geometry by geometry: almost every block lies inside ONE geometry, found once per block
     __shared__ int s_geom;
     if (threadIdx.x == 0) {
-        const int j0 = blockIdx.x * blockDim.x, j1 = min(j0 + (int)blockDim.x, S.n_verts) - 1;
+        const int j1 = min(j0 + kXformBlock, S.n_verts) - 1;
         const int g0 = find_geom_by_vert(S.geoms, S.n_geoms, j0);
         s_geom = (g0 == find_geom_by_vert(S.geoms, S.n_geoms, j1)) ? g0 : -1;
     }
     __syncthreads();
-    if (j < S.n_verts) {
-        float x, y, z;
-        transform_vertex(S, sensor_frame, RinvT, j, x, y, z, s_geom);
-        lo[0] = hi[0] = x; lo[1] = hi[1] = y; lo[2] = hi[2] = z;
-    }
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-#pragma unroll
-        for (int o = 16; o; o >>= 1) {
-            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
-            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+    for (int k = 0; k < kXformPerThread; ++k) {
+        const int j = j0 + k * 256 + (int)threadIdx.x;
+        if (j < S.n_verts) {
+            float x, y, z;
+            transform_vertex(S, sensor_frame, RinvT, j, x, y, z, s_geom);
+            lo[0] = fminf(lo[0], x); hi[0] = fmaxf(hi[0], x);       // a NaN coordinate leaves the bounds alone, as before
+            lo[1] = fminf(lo[1], y); hi[1] = fmaxf(hi[1], y);
+            lo[2] = fminf(lo[2], z); hi[2] = fmaxf(hi[2], z);
         }
     }
-    __shared__ float s_lo[8][3], s_hi[8][3];
+    __shared__ uint32_t s_lo[8][3], s_hi[8][3];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) for (int k = 0; k < 3; ++k) { s_lo[warp][k] = lo[k]; s_hi[warp][k] = hi[k]; }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const uint32_t l = __reduce_min_sync(0xffffffffu, f2ord(lo[k])), h = __reduce_max_sync(0xffffffffu, f2ord(hi[k]));
+        if (lane == 0) { s_lo[warp][k] = l; s_hi[warp][k] = h; }
+    }
     __syncthreads();
     if (threadIdx.x < 3) {
         const int k = threadIdx.x;
-        float l = s_lo[0][k], h = s_hi[0][k];
-        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { l = fminf(l, s_lo[w][k]); h = fmaxf(h, s_hi[w][k]); }
-        if (l <= h) { atomicMin(&S.bounds[k], f2ord(l)); atomicMax(&S.bounds[3 + k], f2ord(h)); }
+        uint32_t l = s_lo[0][k], h = s_hi[0][k];
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { l = min(l, s_lo[w][k]); h = max(h, s_hi[w][k]); }
+        if (l <= h) { atomicMin(&S.bounds[k], l); atomicMax(&S.bounds[3 + k], h); }
     }
 }
 

@@ -728,7 +728,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
     LSB_CU(c, cudaMemsetAsync(S.bounds, 0xFF, 12, st));
     LSB_CU(c, cudaMemsetAsync(S.bounds + 3, 0x00, 12, st));
     mark("lsb200:transform");
-    k_transform<<<(unsigned)((nv + 255) / 256), 256, 0, st>>>(S, c->frame_mode == LSB200_FRAME_SENSOR, c->d_sensor_xf.as<float>());
+    k_transform<<<(unsigned)((nv + kXformBlock - 1) / kXformBlock), 256, 0, st>>>(S, c->frame_mode == LSB200_FRAME_SENSOR, c->d_sensor_xf.as<float>());
     count_launch(c);
     cudaEventRecord(c->ev_xform, st);        // the raw vertex blobs have been read: the next frame's upload may overwrite them
     mark(rebuild ? "lsb200:morton" : "lsb200:tree");
