@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
     uint32_t *s_keys = s_dyn, *s_vals = s_dyn + kTile;
     __shared__ uint32_t s_whist[kWarps][kRadix];   // per-warp digit counts -> per-warp digit bases within the tile
     __shared__ uint32_t s_local[kRadix];           // tile-local exclusive digit offsets
-    __shared__ uint32_t s_global[kRadix];          // global position of the tile's first pair of each digit
+    __shared__ uint32_t s_global[kRadix];          // global position of the tile's first pair of each digit, minus its tile-local offset
     __shared__ uint32_t s_tile;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -193,7 +193,10 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
         uint32_t woff = 0;
 #pragma unroll
         for (int w = 0; w < kRadix / 32; ++w) if (w < warp) woff += s_wsum[w];
-        if (d < kRadix) s_local[d] = woff + incl - run;
+        if (d < kRadix) {
+            s_local[d] = woff + incl - run;
+            s_global[d] -= woff + incl - run;      // global position of the tile's pair j of digit d = s_global[d] + j (one load per pair at write-out)
+        }
     }
     __syncthreads();
 
@@ -210,7 +213,7 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
     for (int j = tid; j < n_valid; j += kThreads) {
         const uint32_t k = s_keys[j];
         const uint32_t d = (k >> shift) & (kRadix - 1);
-        const uint32_t g = s_global[d] + (uint32_t)(j - (int)s_local[d]);
+        const uint32_t g = s_global[d] + (uint32_t)j;
         keys_out[g] = k;
         vals_out[g] = s_vals[j];
     }
