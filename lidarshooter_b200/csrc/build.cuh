@@ -237,23 +237,34 @@ __global__ void k_morton_plan(SceneDev S)
     *S.plan = P;
 }
 
+#ifndef LSB_MORTON_PER_THREAD
+#define LSB_MORTON_PER_THREAD 4
+#endif
+constexpr int kMortonPerThread = LSB_MORTON_PER_THREAD;   // triangles per thread of k_morton (block-strided)
+constexpr int kMortonBlock = 256 * kMortonPerThread;      // triangles per CTA: the plan's tables, the bounds and the geometry are set up once for all of them
+
 __global__ void __launch_bounds__(256) k_morton(SceneDev S)
 {
     __shared__ MortonTables s_plan;
     __shared__ int s_geom;                   // the one geometry this block's triangles belong to, or -1 (see k_transform)
     morton_tables_fill(*S.plan, s_plan, threadIdx.x);
+    const int g_base = blockIdx.x * kMortonBlock;
     if (threadIdx.x == 255) {
-        const int g0 = blockIdx.x * blockDim.x, g1 = min(g0 + (int)blockDim.x, S.n_tris) - 1;
+        const int g0 = g_base, g1 = min(g0 + kMortonBlock, S.n_tris) - 1;
         const int q0 = find_geom_by_tri(S.geoms, S.n_geoms, g0);
         s_geom = (q0 == find_geom_by_tri(S.geoms, S.n_geoms, g1)) ? q0 : -1;
     }
     __syncthreads();
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= S.n_tris) return;
     const float slo[3] = {ord2f(S.bounds[0]), ord2f(S.bounds[1]), ord2f(S.bounds[2])};
     const float shi[3] = {ord2f(S.bounds[3]), ord2f(S.bounds[4]), ord2f(S.bounds[5])};
-    S.keys[g] = morton_key(S, g, slo, shi, s_plan, s_geom);
-    S.vals[g] = (uint32_t)g;
+#pragma unroll
+    for (int k = 0; k < kMortonPerThread; ++k) {
+        const int g = g_base + k * 256 + (int)threadIdx.x;
+        if (g < S.n_tris) {
+            S.keys[g] = morton_key(S, g, slo, shi, s_plan, s_geom);
+            S.vals[g] = (uint32_t)g;
+        }
+    }
 }
 
 // ---- (3) Karras 2012 hierarchy over the sorted codes ------------------------------------------------------

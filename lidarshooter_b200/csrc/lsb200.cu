@@ -735,7 +735,7 @@ static int commit_locked(lsb200_ctx *c, int mode)
     if (rebuild) {
         // (2) Morton codes  (3) radix sort  (4) Karras hierarchy
         k_morton_plan<<<1, 1, 0, st>>>(S);
-        k_morton<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(S);
+        k_morton<<<(unsigned)((nt + kMortonBlock - 1) / kMortonBlock), 256, 0, st>>>(S);
         count_launch(c, 2);
         mark("lsb200:sort");
         count_launch(c, rsort::sort_pairs(S.keys, S.vals, c->d_keys_tmp.as<uint32_t>(), c->d_vals_tmp.as<uint32_t>(), nt,
