@@ -317,7 +317,9 @@ LSB200_API int lsb200_reset_counters(lsb200_ctx *ctx);
 /* totals of the last LSB200_OPT_TRACE_STATS launch: out[0..n) = rays, nodes visited, leaves visited, triangles tested,
  * 32-ray units with one octant, units with mixed octants, deepest stack, hits, culled pops, origin-chain box tests */
 LSB200_API int lsb200_get_trace_counters(lsb200_ctx *ctx, uint64_t *out, int n);
-/* copies the BVH to the host for structural tests: nodes (n_nodes x 16 floats), leaf-ordered triangle ids */
+/* copies the BVH to the host for structural tests: nodes (n_nodes x 16 floats), leaf-ordered triangle ids.  Only the
+ * records a child reference leads to are defined: the fused tree build does not write the records of nodes whose whole
+ * range fits a leaf (their parents reference them as leaves); walk from the root (capi.reachable_nodes in the tests). */
 LSB200_API int lsb200_debug_copy_bvh(lsb200_ctx *ctx, float *nodes16, int64_t node_capacity, int32_t *leaf_tri_ids,
                                      int64_t tri_capacity, int32_t *root);
 /* device sort self-test entry (parity tests of the radix sort): sorts n (key,value) pairs held in HOST arrays */

@@ -1576,6 +1576,17 @@ int lsb200_debug_sort_pairs(lsb200_ctx *c, uint32_t *keys, uint32_t *vals, int64
     return rc;
 }
 
+#ifdef LSB_SORT_PROF
+// A/B instrumentation only (tools/sort_phase_prof.py): reads and clears the phase counters of k_onesweep
+LSB200_API int lsb200_debug_sort_prof(unsigned long long *out8)
+{
+    unsigned long long z[8] = {};
+    if (cudaMemcpyFromSymbol(out8, rsort::g_sort_prof, sizeof(z)) != cudaSuccess) return LSB200_ERR_CUDA;
+    if (cudaMemcpyToSymbol(rsort::g_sort_prof, z, sizeof(z)) != cudaSuccess) return LSB200_ERR_CUDA;
+    return LSB200_OK;
+}
+#endif
+
 int lsb200_debug_copy_vertices(lsb200_ctx *c, float *xyz, int64_t cap)
 {
     if (!c || !xyz) return LSB200_ERR_INVALID;

@@ -37,6 +37,13 @@ constexpr int kTile = kThreads * kItems;            // 8192 pairs per tile
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagIncl = 2u << 30, kFlagMask = 3u << 30, kValMask = ~kFlagMask;
 
 inline int64_t num_tiles(int64_t n) { return (n + kTile - 1) / kTile; }
+#ifdef LSB_SORT_PROF
+// A/B instrumentation only: cycles thread 0 of every CTA spends in each phase of k_onesweep (summed over CTAs and passes)
+__device__ unsigned long long g_sort_prof[8];
+#define LSB_SORT_STAMP(k) do { if (threadIdx.x == 0) { const long long now__ = clock64(); atomicAdd(&g_sort_prof[k], (unsigned long long)(now__ - t_prof)); t_prof = now__; } } while (0)
+#else
+#define LSB_SORT_STAMP(k) do { } while (0)
+#endif
 // scratch layout (uint32): [kPasses*kRadix] global histograms -> exclusive digit bases,
 //                          [kPasses] tile tickets, pad to 16, then [kPasses][tiles][kRadix] status words
 inline size_t scratch_words(int64_t n) { return (size_t)kPasses * kRadix + 16 + (size_t)kPasses * num_tiles(n) * kRadix; }
@@ -115,6 +122,9 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
     __shared__ uint32_t s_tile;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef LSB_SORT_PROF
+    long long t_prof = clock64();
+#endif
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     for (int i = tid; i < kWarps * kRadix; i += kThreads) (&s_whist[0][0])[i] = 0;
     __syncthreads();
@@ -125,14 +135,17 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
     // warp-striped load: item i of lane l is element warp*512 + i*32 + l of the tile
     uint32_t key[kItems], val[kItems];
     uint16_t rank[kItems];
-    const int64_t wbase = tile_base + warp * (32 * kItems);
+    {
+        const int64_t wbase = tile_base + warp * (32 * kItems);
 #pragma unroll
-    for (int i = 0; i < kItems; ++i) {
-        const int64_t idx = wbase + i * 32 + lane;
-        const bool ok = idx < n;
-        key[i] = ok ? keys_in[idx] : 0xffffffffu;
-        val[i] = ok ? vals_in[idx] : 0u;
+        for (int i = 0; i < kItems; ++i) {
+            const int64_t idx = wbase + i * 32 + lane;
+            const bool ok = idx < n;
+            key[i] = ok ? keys_in[idx] : 0xffffffffu;
+            val[i] = ok ? vals_in[idx] : 0u;
+        }
     }
+    LSB_SORT_STAMP(0);       // ticket + zeroing + barrier + load issue (the loads are only waited for below)
     // stable multi-split inside the warp
     const unsigned lt = lanemask_lt();
 #pragma unroll
@@ -145,7 +158,9 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
         __syncwarp();
         rank[i] = (uint16_t)(prev + __popc(peers & lt));
     }
+    LSB_SORT_STAMP(1);       // load latency + ranking of warp 0
     __syncthreads();
+    LSB_SORT_STAMP(2);       // barrier: the slowest warp's ranking
 
     // thread d < 256 owns digit d: scan over warps, publish, look back
     {
@@ -183,6 +198,7 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
             }
             s_global[d] = digit_base[d] + excl;
         }
+        LSB_SORT_STAMP(3);   // scan over warps + look-back (thread 0 = digit 0)
         // tile-local exclusive scan over digits (block scan of `run`; threads beyond the radix carry 0)
         uint32_t incl = run;
 #pragma unroll
@@ -199,6 +215,7 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
         }
     }
     __syncthreads();
+    LSB_SORT_STAMP(4);       // block scan + barrier: the slowest digit's look-back
 
     // reorder the tile in shared memory
 #pragma unroll
@@ -208,7 +225,9 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
         s_keys[pos] = key[i];
         s_vals[pos] = val[i];
     }
+    LSB_SORT_STAMP(5);       // reorder of thread 0
     __syncthreads();
+    LSB_SORT_STAMP(6);       // barrier
     // write out: consecutive threads write consecutive positions of a digit run
     for (int j = tid; j < n_valid; j += kThreads) {
         const uint32_t k = s_keys[j];
@@ -217,6 +236,7 @@ __global__ void __launch_bounds__(kThreads, LSB_SORT_MINB) k_onesweep(const uint
         keys_out[g] = k;
         vals_out[g] = s_vals[j];
     }
+    LSB_SORT_STAMP(7);       // write-out issue
 }
 
 // Function attributes are per DEVICE: every context calls this once for its own device (lsb200_create), so that a

@@ -1549,6 +1549,7 @@ __global__ void k_origin_chain(const float4 *__restrict__ nodes, int top_cap, co
 #define LSB_TILE_SMEM_STACK 1     // k_tile_entries: deferred entries of the walk in shared memory ([slot][thread]) instead of a local array
 #endif
 constexpr int kTileBlock = LSB_TILE_BLOCK;   // threads per CTA of k_tile_entries (one thread per tile)
+static_assert(!LSB_TILE_SMEM_STACK || 16 * LSB_TILE_BLOCK * 16 <= 48 * 1024, "k_tile_entries: [kMaxTileEntries][kTileBlock] int4 walk stack must fit the default 48 KB of dynamic shared memory");
 constexpr int kSuperTiles = 4;          // a supertile is kSuperTiles x kSuperTiles tiles
 
 // Direction interval of a block of rays -> the constants of the interval slab test.
