@@ -86,6 +86,14 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append((time.time(), line.strip()))
 
+    def wait_first(self, timeout_s=5.0):
+        """Blocks until nvidia-smi has delivered its first sample: its start-up (NVML init over every GPU of the box, hundreds
+        of milliseconds on an 8-GPU node, under driver locks that stall kernel launches of every rank) must not overlap the
+        timed region -- at 8 ranks it cost 0.17 ms per step of a 27 ms region (profiles/scale_diag_r02_8gpu.txt)."""
+        t0 = time.time()
+        while self.proc and not self.rows and time.time() - t0 < timeout_s:
+            time.sleep(0.01)
+
     def stop(self, t0, t1):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -592,13 +600,15 @@ def main():
 
     # ---- device-resident leg (value) ---------------------------------------------------------------------
     frame = 0
+    sampler = ClockSampler(local) if rank == 0 else None      # started before the warm-up: sampling, not starting up, during the timed region
     for w in range(args.warmup):
         step_resident(frame * world + rank); rc = ctx.trace_batch(0, n_sens, 0); assert rc == 0, ctx.last_error()
         frame += 1
+    if sampler:
+        sampler.wait_first()
     sync_all()
     ctx.reset_counters()
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
-    sampler = ClockSampler(local) if rank == 0 else None
     t_wall0 = time.time()
     e_begin, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e_begin.record(stream)
