@@ -156,3 +156,23 @@ def test_pointcloud2_wire_reader_round_trip():
     for cut in (3, 20, len(msg) - 1, len(msg) - 40):
         with pytest.raises(ValueError):
             hostapi.reserialize_cloud(np.frombuffer(msg[:cut], np.uint8))
+
+
+def test_reachable_nodes_masks_records_no_reference_leads_to():
+    """capi.reachable_nodes (tree comparisons of the GPU tests): rows reached from the root through child references >= 0
+    (minus the root offset) are kept, every other row is zeroed; negative references are leaves."""
+    import numpy as np
+    from lidarshooter_b200 import capi
+    root = 1024
+    nodes = np.full((6, 16), 7.0, np.float32)
+    child = nodes[:, 12:14].view(np.int32)
+    child[0] = (root + 1, root + 4)          # root -> nodes 1 and 4
+    child[1] = (~3, ~(5 | (1 << 28)))        # two leaf references
+    child[4] = (root + 5, ~9)
+    child[5] = (~1, ~2)
+    child[2] = (root + 3, root + 3)          # rows 2 and 3: garbage nobody references
+    child[3] = (~0, ~0)
+    out = capi.reachable_nodes(nodes, root)
+    assert np.array_equal(out[[0, 1, 4, 5]], nodes[[0, 1, 4, 5]])
+    assert not out[[2, 3]].any()
+    assert nodes[2].any()                    # the input is not modified
