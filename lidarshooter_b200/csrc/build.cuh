@@ -541,26 +541,11 @@ struct TreeSmem {
 #ifndef LSB_TREE_SPLIT_SLOTS
 #define LSB_TREE_SPLIT_SLOTS 1
 #endif
-// Above the leaves the live lanes of a warp sit at splits a power of two apart (3, 7, 11, ... then 7, 15, 23, ...): unswizzled,
-// their 16-byte slots share one or two bank groups and their arrival counters four banks (ncu source view: 2.5 of 5.6 M
-// wavefronts of each rendezvous store were conflicts).  slot_swz folds the higher index bits into the low three -- a bijection
-// that keeps eight consecutive splits on eight bank groups and spreads every power-of-two stride as well.
-#ifndef LSB_TREE_SWIZZLE
-#define LSB_TREE_SWIZZLE 1
-#endif
-__device__ __forceinline__ int slot_swz(int x)
-{
-#if LSB_TREE_SWIZZLE
-    return x ^ ((x >> 3) & 7) ^ ((x >> 6) & 7);
-#else
-    return x;
-#endif
-}
 template <int B>
 __device__ __forceinline__ int rslot(int ls, int side)
 {
 #if LSB_TREE_SPLIT_SLOTS
-    return side ? B + slot_swz((ls + 1) & (B - 1)) : slot_swz(ls);
+    return side ? B + ((ls + 1) & (B - 1)) : ls;
 #else
     return 2 * ls + side;
 #endif
@@ -630,7 +615,7 @@ __device__ __forceinline__ void tree_block(const SceneDev &S, const uint32_t *__
             M.rxy[rslot<B>(ls, mine)] = pxy;
             M.rz[rslot<B>(ls, mine)] = pz;
             __threadfence_block();
-            if (atomicAdd(&M.flag[slot_swz(ls)], 1u) == 0u) break;           // first to arrive: the sibling finishes the node
+            if (atomicAdd(&M.flag[ls], 1u) == 0u) break;           // first to arrive: the sibling finishes the node
             __threadfence_block();
             if (tree_merge(S, c, left, s, M.rxy[rslot<B>(ls, mine ^ 1)], M.rz[rslot<B>(ls, mine ^ 1)])) break;
         }
@@ -717,7 +702,7 @@ __device__ __forceinline__ void tree_block_rounds(const SceneDev &S, const uint3
         }
         M.rxy[rslot<B>(ls, mine)] = pxy;
         M.rz[rslot<B>(ls, mine)] = pz;
-        if (atomicAdd(&M.flag[slot_swz(ls)], 1u) != 0u) next_q[atomicAdd(next_cnt, 1u)] = (uint16_t)ls;
+        if (atomicAdd(&M.flag[ls], 1u) != 0u) next_q[atomicAdd(next_cnt, 1u)] = (uint16_t)ls;
     };
     if (i < n) {
         const Box6 leaf = leaf_record(S, (int)(ids_uncached ? __ldcg(sorted_ids + i) : __ldg(sorted_ids + i)), i);
@@ -758,7 +743,7 @@ __device__ __forceinline__ void tree_block_rounds(const SceneDev &S, const uint3
 }
 
 #endif  // LSB_TREE_ROUNDS
-__global__ void __launch_bounds__(kTreeBlock, 2048 / kTreeBlock) k_tree(SceneDev S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
+__global__ void __launch_bounds__(kTreeBlock) k_tree(SceneDev S, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ sorted_ids,
                                                      float4 *__restrict__ rendezvous /* [4 * n_tris] */,
                                                      uint32_t *__restrict__ work /* [n_tris]: split << 1 | side */, uint32_t *__restrict__ work_count)
 {
